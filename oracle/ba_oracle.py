@@ -1,0 +1,175 @@
+"""oracle/ba_oracle.py -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+
+ctypes binding of oracle/ba_ref.c (libvio360_oracle_ba.so).  Only tests/,
+__graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import it.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int)
+_up = C.POINTER(C.c_ubyte)
+
+
+class _Window(C.Structure):
+    _fields_ = [("K", C.c_int), ("M", C.c_int), ("O", C.c_int),
+                ("pose_idx", _ip), ("point_idx", _ip), ("obs_u", _dp), ("obs_v", _dp),
+                ("outlier", _up), ("Twb_init", _dp), ("Tcb", C.c_double * 16),
+                ("cols", C.c_double), ("rows", C.c_double), ("info", C.c_double * 4),
+                ("huber_a", C.c_double), ("pose_fixed", _up), ("point_fixed", _up)]
+
+
+class _Factor(C.Structure):
+    _fields_ = [("obs", C.c_double * 2), ("cols", C.c_double), ("rows", C.c_double),
+                ("Tcb", C.c_double * 16), ("Twb_init", C.c_double * 16),
+                ("info", C.c_double * 4), ("is_outlier", C.c_int),
+                ("world_point", C.c_double * 3)]
+
+
+def build(force=False):
+    so = os.path.join(_HERE, "libvio360_oracle_ba.so")
+    src = os.path.join(_HERE, "ba_ref.c")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "libvio360_oracle_ba.so"],
+                              stdout=subprocess.DEVNULL)
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        _LIB = C.CDLL(build())
+        _LIB.vo_ba_chi2.restype = C.c_double
+        _LIB.vo_pnp_chi2.restype = C.c_double
+        _LIB.vo_apply_loss.restype = C.c_double
+    return _LIB
+
+
+def _d(a):
+    return a.ctypes.data_as(_dp)
+
+
+class Window:
+    """Keeps the numpy arrays alive for the lifetime of the C struct."""
+
+    def __init__(self, win):
+        self.win = win
+        self.keep = dict(
+            pose_idx=np.ascontiguousarray(win["pose_idx"], np.int32),
+            point_idx=np.ascontiguousarray(win["point_idx"], np.int32),
+            obs_u=np.ascontiguousarray(win["obs_u"], np.float64),
+            obs_v=np.ascontiguousarray(win["obs_v"], np.float64),
+            outlier=np.ascontiguousarray(win.get("outlier", np.zeros(win["O"], np.uint8)), np.uint8),
+            Twb=np.ascontiguousarray(win["Twb_init"], np.float64),
+            pose_fixed=np.ascontiguousarray(win["pose_fixed"], np.uint8),
+            point_fixed=np.ascontiguousarray(win["point_fixed"], np.uint8))
+        k = self.keep
+        w = _Window()
+        w.K, w.M, w.O = int(win["K"]), int(win["M"]), int(win["O"])
+        w.pose_idx = k["pose_idx"].ctypes.data_as(_ip)
+        w.point_idx = k["point_idx"].ctypes.data_as(_ip)
+        w.obs_u = _d(k["obs_u"]); w.obs_v = _d(k["obs_v"])
+        w.outlier = k["outlier"].ctypes.data_as(_up)
+        w.Twb_init = _d(k["Twb"])
+        w.Tcb = (C.c_double * 16)(*np.asarray(win["Tcb"], np.float64).reshape(-1))
+        w.cols, w.rows = float(win["cols"]), float(win["rows"])
+        w.info = (C.c_double * 4)(*np.asarray(win["info"], np.float64).reshape(-1))
+        w.huber_a = float(win["huber_a"])
+        w.pose_fixed = k["pose_fixed"].ctypes.data_as(_up)
+        w.point_fixed = k["point_fixed"].ctypes.data_as(_up)
+        self.c = w
+
+    def evaluate(self, pose_delta, points, apply_loss=True, nthreads=1, hoisted=False,
+                 outputs=True):
+        O = self.c.O
+        pd = np.ascontiguousarray(pose_delta, np.float64); pts = np.ascontiguousarray(points, np.float64)
+        cost = C.c_double(0.0)
+        fn = lib().vo_window_evaluate_hoisted if hoisted else lib().vo_window_evaluate
+        if outputs:
+            r = np.empty((O, 2)); Jp = np.empty((O, 2, 6)); Jl = np.empty((O, 2, 3))
+            fn(C.byref(self.c), _d(pd), _d(pts), int(apply_loss), _d(r), _d(Jp), _d(Jl),
+               C.byref(cost), int(nthreads))
+            return r, Jp, Jl, cost.value
+        fn(C.byref(self.c), _d(pd), _d(pts), int(apply_loss), None, None, None,
+           C.byref(cost), int(nthreads))
+        return cost.value
+
+    def normal_blocks(self, r, Jp, Jl):
+        K, M, O = self.c.K, self.c.M, self.c.O
+        Hpp = np.empty((K, 6, 6)); bp = np.empty((K, 6)); Hll = np.empty((M, 3, 3))
+        bl = np.empty((M, 3)); Hpl = np.empty((O, 6, 3))
+        lib().vo_normal_blocks(C.byref(self.c), _d(r), _d(Jp), _d(Jl), _d(Hpp), _d(bp),
+                               _d(Hll), _d(bl), _d(Hpl))
+        return Hpp, bp, Hll, bl, Hpl
+
+    def schur(self, r, Jp, Jl, D=None):
+        K = self.c.K
+        nf = int(K - np.count_nonzero(self.keep["pose_fixed"]))
+        n = 6 * nf
+        S = np.empty((n, n)); rhs = np.empty(n); fm = np.empty(K, np.int32)
+        Dp = None if D is None else _d(np.ascontiguousarray(D, np.float64))
+        lib().vo_schur_eliminate(C.byref(self.c), _d(r), _d(Jp), _d(Jl), Dp, _d(S), _d(rhs),
+                                 fm.ctypes.data_as(_ip))
+        return S, rhs, fm
+
+    def lm_diagonal(self, Jp, Jl, radius=1e4):
+        D = np.empty(6 * self.c.K + 3 * self.c.M)
+        lib().vo_lm_diagonal(C.byref(self.c), _d(Jp), _d(Jl), C.c_double(radius), _d(D))
+        return D
+
+    def chi2(self, pose_delta, points, thr=5.991):
+        O = self.c.O
+        pd = np.ascontiguousarray(pose_delta, np.float64); pts = np.ascontiguousarray(points, np.float64)
+        chi2 = np.empty(O); flag = np.empty(O, np.uint8)
+        lib().vo_window_chi2(C.byref(self.c), _d(pd), _d(pts), C.c_double(thr), _d(chi2),
+                             flag.ctypes.data_as(_up))
+        return chi2, flag
+
+
+def make_factor(obs, cols, rows, Tcb, Twb_init, info, is_outlier=False, world_point=(0, 0, 0)):
+    f = _Factor()
+    f.obs = (C.c_double * 2)(*obs)
+    f.cols, f.rows = float(cols), float(rows)
+    f.Tcb = (C.c_double * 16)(*np.asarray(Tcb, np.float64).reshape(-1))
+    f.Twb_init = (C.c_double * 16)(*np.asarray(Twb_init, np.float64).reshape(-1))
+    f.info = (C.c_double * 4)(*np.asarray(info, np.float64).reshape(-1))
+    f.is_outlier = int(bool(is_outlier))
+    f.world_point = (C.c_double * 3)(*world_point)
+    return f
+
+
+def ba_evaluate(f, pose6, pt, want_jac=True, want_pose=True, want_point=True):
+    r = np.full(2, np.nan); Jp = np.full((2, 6), np.nan); Jl = np.full((2, 3), np.nan)
+    p6 = np.ascontiguousarray(pose6, np.float64); p3 = np.ascontiguousarray(pt, np.float64)
+    ok = lib().vo_ba_evaluate(C.byref(f), _d(p6), _d(p3), _d(r), int(want_jac),
+                              _d(Jp) if want_pose else None, _d(Jl) if want_point else None)
+    return ok, r, Jp, Jl
+
+
+def pnp_evaluate(f, pose6, want_jac=True):
+    r = np.full(2, np.nan); Jp = np.full((2, 6), np.nan)
+    p6 = np.ascontiguousarray(pose6, np.float64)
+    ok = lib().vo_pnp_evaluate(C.byref(f), _d(p6), _d(r), _d(Jp) if want_jac else None)
+    return ok, r, Jp
+
+
+def ba_chi2(f, pose6, pt):
+    p6 = np.ascontiguousarray(pose6, np.float64); p3 = np.ascontiguousarray(pt, np.float64)
+    return lib().vo_ba_chi2(C.byref(f), _d(p6), _d(p3))
+
+
+def pnp_chi2(f, pose6):
+    p6 = np.ascontiguousarray(pose6, np.float64)
+    return lib().vo_pnp_chi2(C.byref(f), _d(p6))
+
+
+def so3_project(M):
+    R = np.empty((3, 3)); Mc = np.ascontiguousarray(M, np.float64)
+    lib().vo_so3_project(_d(Mc), _d(R))
+    return R

@@ -1,0 +1,134 @@
+"""oracle/fe_oracle.py -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+
+ctypes binding of oracle/fe_ref.c plus thin wrappers that call cv2 (the third-party
+dependency the reference's front-end delegates to) with EXACTLY the reference's
+arguments (FeatureTracker.cpp:33-38, 222-223, 238-240).  Only tests/,
+__graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import it.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+# The reference builds cv::TermCriteria(EPS|COUNT, 30, 0.01f): the float literal widens
+# to this double; the same value is re-used as minEigThreshold (FeatureTracker.cpp:35,240)
+LK_EPS = float(np.float32(0.01))
+LK_WIN = 21
+LK_MAX_LEVEL = 3
+LK_MAX_ITER = 30
+GFTT_QUALITY = float(np.float32(0.01))   # float m_quality_level widened to double
+GFTT_MIN_DIST = float(np.float32(30.0))
+
+
+def build(force=False):
+    so = os.path.join(_HERE, "libvio360_oracle_fe.so")
+    src = os.path.join(_HERE, "fe_ref.c")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "libvio360_oracle_fe.so"],
+                              stdout=subprocess.DEVNULL)
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        _LIB = C.CDLL(build())
+    return _LIB
+
+
+def _p(a, t):
+    return a.ctypes.data_as(C.POINTER(t))
+
+
+def pyr_down(img):
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape
+    out = np.empty(((h + 1) // 2, (w + 1) // 2), np.uint8)
+    lib().vf_pyr_down(_p(img, C.c_ubyte), w, h, C.c_size_t(img.strides[0]), _p(out, C.c_ubyte),
+                      C.c_size_t(out.strides[0]))
+    return out
+
+
+def scharr(img):
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape
+    out = np.empty((h, w, 2), np.int16)
+    lib().vf_scharr(_p(img, C.c_ubyte), w, h, C.c_size_t(img.strides[0]), _p(out, C.c_short))
+    return out
+
+
+def lk_track(prev, cur, pts, max_level=LK_MAX_LEVEL, win=LK_WIN, max_iter=LK_MAX_ITER,
+             eps=LK_EPS, min_eig=LK_EPS, want_err=True):
+    prev = np.ascontiguousarray(prev, np.uint8); cur = np.ascontiguousarray(cur, np.uint8)
+    pts = np.ascontiguousarray(pts, np.float32).reshape(-1, 2)
+    n = pts.shape[0]
+    h, w = prev.shape
+    out = np.zeros((n, 2), np.float32); st = np.zeros(n, np.uint8); err = np.zeros(n, np.float32)
+    cnt = lib().vf_lk_track(_p(prev, C.c_ubyte), C.c_size_t(prev.strides[0]), _p(cur, C.c_ubyte),
+                            C.c_size_t(cur.strides[0]), w, h, max_level, win, max_iter,
+                            C.c_double(eps), C.c_double(min_eig), _p(pts, C.c_float), n,
+                            _p(out, C.c_float), _p(st, C.c_ubyte),
+                            _p(err, C.c_float) if want_err else None)
+    return out, st, err, cnt
+
+
+def min_eigen_val(img):
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape
+    out = np.empty((h, w), np.float32)
+    lib().vf_min_eigen_val(_p(img, C.c_ubyte), w, h, C.c_size_t(img.strides[0]), _p(out, C.c_float))
+    return out
+
+
+def good_features(img, mask=None, max_corners=1000, quality=GFTT_QUALITY, min_dist=GFTT_MIN_DIST):
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape
+    cap = max_corners if max_corners > 0 else w * h
+    out = np.zeros((cap, 2), np.float32)
+    if mask is not None:
+        mask = np.ascontiguousarray(mask, np.uint8)
+        n = lib().vf_good_features(_p(img, C.c_ubyte), w, h, C.c_size_t(img.strides[0]),
+                                   _p(mask, C.c_ubyte), C.c_size_t(mask.strides[0]), max_corners,
+                                   C.c_double(quality), C.c_double(min_dist), _p(out, C.c_float))
+    else:
+        n = lib().vf_good_features(_p(img, C.c_ubyte), w, h, C.c_size_t(img.strides[0]), None,
+                                   C.c_size_t(0), max_corners, C.c_double(quality),
+                                   C.c_double(min_dist), _p(out, C.c_float))
+    return out[:n].copy()
+
+
+def base_mask(w, h, polar_ratio=0.15, boundary_margin=20):
+    m = np.empty((h, w), np.uint8)
+    lib().vf_base_mask(w, h, C.c_float(polar_ratio), boundary_margin, _p(m, C.c_ubyte))
+    return m
+
+
+def post_filter(xy, status, w, h, polar_thr=0.15, margin=20.0):
+    xy = np.ascontiguousarray(xy, np.float32); status = np.ascontiguousarray(status, np.uint8)
+    keep = np.empty(status.shape[0], np.uint8)
+    lib().vf_post_filter(_p(xy, C.c_float), _p(status, C.c_ubyte), status.shape[0], w, h,
+                         C.c_float(polar_thr), C.c_float(margin), _p(keep, C.c_ubyte))
+    return keep
+
+
+# ------------------------------------------------------------------ the real dependency
+def cv2_lk_track(prev, cur, pts):
+    """cv::calcOpticalFlowPyrLK exactly as FeatureTracker.cpp:238-240 calls it."""
+    import cv2
+    crit = (cv2.TERM_CRITERIA_EPS | cv2.TERM_CRITERIA_COUNT, LK_MAX_ITER, LK_EPS)
+    nxt, st, err = cv2.calcOpticalFlowPyrLK(prev, cur, np.ascontiguousarray(pts, np.float32).reshape(-1, 1, 2),
+                                            None, winSize=(LK_WIN, LK_WIN), maxLevel=LK_MAX_LEVEL,
+                                            criteria=crit, flags=0, minEigThreshold=LK_EPS)
+    return nxt.reshape(-1, 2), st.reshape(-1), err.reshape(-1)
+
+
+def cv2_good_features(img, mask=None, max_corners=1000):
+    """cv::goodFeaturesToTrack exactly as FeatureTracker.cpp:222-223 calls it."""
+    import cv2
+    c = cv2.goodFeaturesToTrack(img, max_corners, GFTT_QUALITY, GFTT_MIN_DIST, mask=mask,
+                                blockSize=3, useHarrisDetector=False, k=0.04)
+    return np.zeros((0, 2), np.float32) if c is None else c.reshape(-1, 2)
