@@ -1,0 +1,346 @@
+"""ctypes binding of libvio360_cuda.so (include/vio360.h).
+
+This is the Python-side twin of the C++ host shims in host/: thin, no arithmetic, no
+fallback.  Loading fails loudly when the library has not been built, and every call
+raises Vio360Error when the C ABI reports an error (e.g. no CUDA device).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libvio360_cuda.so")
+
+MEM_HOST, MEM_DEVICE = 0, 1
+
+EXPORTS = [
+    "vio360_version", "vio360_create", "vio360_destroy", "vio360_last_error", "vio360_synchronize",
+    "vio360_stream", "vio360_launch_count", "vio360_probe_fma_peak",
+    "vio360_fe_configure", "vio360_fe_track", "vio360_fe_track_batch", "vio360_fe_detect",
+    "vio360_fe_detect_batch", "vio360_fe_pyramid", "vio360_fe_min_eigen_val",
+    "vio360_ba_create", "vio360_ba_destroy", "vio360_ba_set_structure", "vio360_ba_set_outliers",
+    "vio360_ba_set_shard", "vio360_ba_set_parameters", "vio360_ba_evaluate",
+    "vio360_ba_get_residuals_jacobians", "vio360_ba_normal_blocks", "vio360_ba_reduced_dim",
+    "vio360_ba_build_reduced_system", "vio360_ba_reduced_system_dev", "vio360_ba_fetch_reduced_system",
+    "vio360_ba_column_sqnorm", "vio360_ba_chi2", "vio360_pnp_evaluate",
+]
+
+
+class Vio360Error(RuntimeError):
+    pass
+
+
+class TrackJob(C.Structure):
+    _fields_ = [("prev", C.c_void_p), ("prev_pitch", C.c_size_t), ("prev_key", C.c_uint64),
+                ("cur", C.c_void_p), ("cur_pitch", C.c_size_t), ("cur_key", C.c_uint64),
+                ("prev_xy", C.c_void_p), ("n", C.c_int),
+                ("cur_xy", C.c_void_p), ("status", C.c_void_p), ("err", C.c_void_p), ("keep", C.c_void_p)]
+
+
+class DetectJob(C.Structure):
+    _fields_ = [("img", C.c_void_p), ("pitch", C.c_size_t), ("key", C.c_uint64),
+                ("mask", C.c_void_p), ("mask_pitch", C.c_size_t),
+                ("out_xy", C.c_void_p), ("out_n", C.c_void_p)]
+
+
+_lib = None
+
+
+def load():
+    """dlopen the in-tree library; no fallback of any kind."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise Vio360Error("%s is missing: run `make` (or __graft_entry__.build()) first; "
+                          "there is no CPU fallback for the CUDA paths" % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    lib.vio360_last_error.restype = C.c_char_p
+    lib.vio360_last_error.argtypes = [C.c_void_p]
+    lib.vio360_stream.restype = C.c_void_p
+    lib.vio360_stream.argtypes = [C.c_void_p]
+    lib.vio360_launch_count.restype = C.c_longlong
+    lib.vio360_launch_count.argtypes = [C.c_void_p]
+    lib.vio360_destroy.restype = None
+    lib.vio360_destroy.argtypes = [C.c_void_p]
+    lib.vio360_ba_destroy.restype = None
+    lib.vio360_ba_destroy.argtypes = [C.c_void_p]
+    lib.vio360_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+    lib.vio360_synchronize.argtypes = [C.c_void_p]
+    lib.vio360_probe_fma_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    lib.vio360_fe_configure.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double,
+                                        C.c_double, C.c_float, C.c_int, C.c_int, C.c_int]
+    lib.vio360_fe_track.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p, C.c_size_t,
+                                    C.c_uint64, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.POINTER(C.c_int)]
+    lib.vio360_fe_track_batch.argtypes = [C.c_void_p, C.POINTER(TrackJob), C.c_int, C.c_int]
+    lib.vio360_fe_detect.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p, C.c_size_t,
+                                     C.c_int, C.c_double, C.c_double, C.c_void_p, C.POINTER(C.c_int)]
+    lib.vio360_fe_detect_batch.argtypes = [C.c_void_p, C.POINTER(DetectJob), C.c_int, C.c_int, C.c_double,
+                                           C.c_double, C.c_int]
+    lib.vio360_fe_pyramid.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.POINTER(C.c_void_p),
+                                      C.POINTER(C.c_size_t)]
+    lib.vio360_fe_min_eigen_val.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.vio360_ba_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+    lib.vio360_ba_set_structure.argtypes = [C.c_void_p] + [C.c_void_p] * 6 + [C.c_double, C.c_double, C.c_void_p,
+                                                                               C.c_double, C.c_void_p, C.c_void_p]
+    lib.vio360_ba_set_outliers.argtypes = [C.c_void_p, C.c_void_p]
+    lib.vio360_ba_set_shard.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    lib.vio360_ba_set_parameters.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.vio360_ba_evaluate.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double)]
+    lib.vio360_ba_get_residuals_jacobians.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.vio360_ba_normal_blocks.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 5
+    lib.vio360_ba_reduced_dim.argtypes = [C.c_void_p]
+    lib.vio360_ba_build_reduced_system.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                                   C.POINTER(C.c_double)]
+    lib.vio360_ba_reduced_system_dev.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
+    lib.vio360_ba_fetch_reduced_system.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]
+    lib.vio360_ba_column_sqnorm.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+    lib.vio360_ba_chi2.argtypes = [C.c_void_p, C.c_double, C.c_void_p, C.c_void_p]
+    lib.vio360_pnp_evaluate.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 5 + [C.c_double, C.c_double, C.c_void_p,
+                                                                                   C.c_double] + [C.c_void_p] * 8
+    _lib = lib
+    return lib
+
+
+def _ptr(a):
+    return None if a is None else C.c_void_p(a.ctypes.data)
+
+
+class Context:
+    """vio360_ctx: one device, one stream."""
+
+    def __init__(self, device=0):
+        self.lib = load()
+        h = C.c_void_p()
+        rc = self.lib.vio360_create(int(device), C.byref(h))
+        if rc != 0:
+            raise Vio360Error("vio360_create failed (%d): %s" % (rc, self.lib.vio360_last_error(None).decode()))
+        self.h = h
+        self.device = device
+
+    def check(self, rc):
+        if rc != 0:
+            raise Vio360Error("vio360 error %d: %s" % (rc, self.lib.vio360_last_error(self.h).decode()))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.vio360_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def synchronize(self):
+        self.check(self.lib.vio360_synchronize(self.h))
+
+    @property
+    def stream(self):
+        return self.lib.vio360_stream(self.h)
+
+    @property
+    def launch_count(self):
+        return int(self.lib.vio360_launch_count(self.h))
+
+    def probe_fma_peak(self):
+        a, b = C.c_double(0), C.c_double(0)
+        self.check(self.lib.vio360_probe_fma_peak(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    # ---------------------------------------------------------------- front-end
+    def fe_configure(self, width, height, max_level=3, win=21, max_iters=30,
+                     eps=float(np.float32(0.01)), min_eig_thr=float(np.float32(0.01)),
+                     polar_ratio=0.15, boundary_margin=20, max_points=1000, max_batch=1):
+        self.fe_cfg = dict(W=width, H=height, max_points=max_points, max_batch=max_batch)
+        self.check(self.lib.vio360_fe_configure(self.h, width, height, max_level, win, max_iters, eps, min_eig_thr,
+                                                polar_ratio, boundary_margin, max_points, max_batch))
+
+    def fe_track(self, prev, cur, pts, prev_key=0, cur_key=0, want_err=True):
+        prev = np.ascontiguousarray(prev, np.uint8); cur = np.ascontiguousarray(cur, np.uint8)
+        pts = np.ascontiguousarray(pts, np.float32).reshape(-1, 2)
+        n = pts.shape[0]
+        out = np.zeros((n, 2), np.float32); st = np.zeros(n, np.uint8); err = np.zeros(n, np.float32)
+        nt = C.c_int(0)
+        self.check(self.lib.vio360_fe_track(self.h, _ptr(prev), prev.strides[0], prev_key, _ptr(cur), cur.strides[0],
+                                            cur_key, _ptr(pts), n, _ptr(out), _ptr(st),
+                                            _ptr(err) if want_err else None, C.byref(nt)))
+        return out, st, err, nt.value
+
+    def fe_track_batch_host(self, pairs, want_keep=True):
+        """pairs: list of (prev, cur, pts, prev_key, cur_key) host arrays -> list of (xy, status, err, keep)."""
+        jobs = (TrackJob * len(pairs))()
+        keep_alive, outs = [], []
+        for i, (prev, cur, pts, pk, ck) in enumerate(pairs):
+            prev = np.ascontiguousarray(prev, np.uint8); cur = np.ascontiguousarray(cur, np.uint8)
+            pts = np.ascontiguousarray(pts, np.float32).reshape(-1, 2)
+            n = pts.shape[0]
+            xy = np.zeros((n, 2), np.float32); st = np.zeros(n, np.uint8); err = np.zeros(n, np.float32)
+            keep = np.zeros(n, np.uint8)
+            keep_alive.append((prev, cur, pts))
+            outs.append((xy, st, err, keep))
+            j = jobs[i]
+            j.prev, j.prev_pitch, j.prev_key = prev.ctypes.data, prev.strides[0], pk
+            j.cur, j.cur_pitch, j.cur_key = cur.ctypes.data, cur.strides[0], ck
+            j.prev_xy, j.n = pts.ctypes.data, n
+            j.cur_xy, j.status, j.err = xy.ctypes.data, st.ctypes.data, err.ctypes.data
+            j.keep = keep.ctypes.data if want_keep else None
+        self.check(self.lib.vio360_fe_track_batch(self.h, jobs, len(pairs), MEM_HOST))
+        return outs
+
+    def fe_track_batch_raw(self, jobs, n_jobs, mem_space):
+        self.check(self.lib.vio360_fe_track_batch(self.h, jobs, n_jobs, mem_space))
+
+    def fe_detect(self, img, mask=None, max_corners=1000, quality=float(np.float32(0.01)),
+                  min_dist=float(np.float32(30.0)), key=0):
+        img = np.ascontiguousarray(img, np.uint8)
+        if mask is not None:
+            mask = np.ascontiguousarray(mask, np.uint8)
+        cap = max_corners if max_corners > 0 else 1 << 18
+        out = np.zeros((cap, 2), np.float32)
+        n = C.c_int(0)
+        self.check(self.lib.vio360_fe_detect(self.h, _ptr(img), img.strides[0], key, _ptr(mask),
+                                             mask.strides[0] if mask is not None else 0, max_corners, quality,
+                                             min_dist, _ptr(out), C.byref(n)))
+        return out[:n.value].copy()
+
+    def fe_detect_batch_raw(self, jobs, n_jobs, max_corners, quality, min_dist, mem_space):
+        self.check(self.lib.vio360_fe_detect_batch(self.h, jobs, n_jobs, max_corners, quality, min_dist, mem_space))
+
+    def fe_pyramid(self, img, n_levels):
+        img = np.ascontiguousarray(img, np.uint8)
+        h, w = img.shape
+        outs = []
+        for _ in range(n_levels):
+            outs.append(np.zeros((h, w), np.uint8))
+            w, h = (w + 1) // 2, (h + 1) // 2
+        ptrs = (C.c_void_p * n_levels)(*[o.ctypes.data for o in outs])
+        pitches = (C.c_size_t * n_levels)(*[o.strides[0] for o in outs])
+        self.check(self.lib.vio360_fe_pyramid(self.h, _ptr(img), img.strides[0], n_levels, ptrs, pitches))
+        return outs
+
+    def fe_min_eigen_val(self, img):
+        img = np.ascontiguousarray(img, np.uint8)
+        out = np.zeros(img.shape, np.float32)
+        self.check(self.lib.vio360_fe_min_eigen_val(self.h, _ptr(img), img.strides[0], _ptr(out)))
+        return out
+
+    # ---------------------------------------------------------------- PnP
+    def pnp_evaluate(self, obs_uv, world_pts, Twb_init, Tcb, cols, rows, info, huber_delta, pose_delta,
+                     outlier=None, want_jac=True, want_chi2=True):
+        obs_uv = np.ascontiguousarray(obs_uv, np.float64); world_pts = np.ascontiguousarray(world_pts, np.float64)
+        N = obs_uv.shape[0]
+        Twb_init = np.ascontiguousarray(Twb_init, np.float64); Tcb = np.ascontiguousarray(Tcb, np.float64)
+        info = np.ascontiguousarray(info, np.float64); pose_delta = np.ascontiguousarray(pose_delta, np.float64)
+        if outlier is not None:
+            outlier = np.ascontiguousarray(outlier, np.uint8)
+        r = np.zeros((N, 2)); Jp = np.zeros((N, 2, 6)) if want_jac else None
+        valid = np.zeros(N, np.uint8); H = np.zeros((6, 6)); b = np.zeros(6); cost = np.zeros(1)
+        chi2 = np.zeros(N) if want_chi2 else None
+        self.check(self.lib.vio360_pnp_evaluate(self.h, N, _ptr(obs_uv), _ptr(world_pts), _ptr(outlier), _ptr(Twb_init),
+                                                _ptr(Tcb), float(cols), float(rows), _ptr(info), float(huber_delta),
+                                                _ptr(pose_delta), _ptr(r), _ptr(Jp), _ptr(valid), _ptr(H), _ptr(b),
+                                                _ptr(cost), _ptr(chi2)))
+        return dict(r=r, Jp=Jp, valid=valid, H=H, b=b, cost=float(cost[0]), chi2=chi2)
+
+
+class BAWindow:
+    """vio360_ba: the device twin of one Optimizer::RunLocalBA problem."""
+
+    def __init__(self, ctx, win):
+        self.ctx = ctx
+        self.lib = ctx.lib
+        self.K, self.M, self.O = int(win["K"]), int(win["M"]), int(win["O"])
+        h = C.c_void_p()
+        ctx.check(self.lib.vio360_ba_create(ctx.h, self.K, self.M, self.O, C.byref(h)))
+        self.h = h
+        a = dict(pose_idx=np.ascontiguousarray(win["pose_idx"], np.int32),
+                 point_idx=np.ascontiguousarray(win["point_idx"], np.int32),
+                 u=np.ascontiguousarray(win["obs_u"], np.float64), v=np.ascontiguousarray(win["obs_v"], np.float64),
+                 Twb=np.ascontiguousarray(win["Twb_init"], np.float64), Tcb=np.ascontiguousarray(win["Tcb"], np.float64),
+                 info=np.ascontiguousarray(win["info"], np.float64),
+                 pf=np.ascontiguousarray(win["pose_fixed"], np.uint8), lf=np.ascontiguousarray(win["point_fixed"], np.uint8))
+        ctx.check(self.lib.vio360_ba_set_structure(self.h, _ptr(a["pose_idx"]), _ptr(a["point_idx"]), _ptr(a["u"]),
+                                                   _ptr(a["v"]), _ptr(a["Twb"]), _ptr(a["Tcb"]), float(win["cols"]),
+                                                   float(win["rows"]), _ptr(a["info"]), float(win["huber_a"]),
+                                                   _ptr(a["pf"]), _ptr(a["lf"])))
+        if "outlier" in win and win["outlier"] is not None:
+            self.set_outliers(win["outlier"])
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.vio360_ba_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_outliers(self, outlier):
+        o = None if outlier is None else np.ascontiguousarray(outlier, np.uint8)
+        self.ctx.check(self.lib.vio360_ba_set_outliers(self.h, _ptr(o)))
+
+    def set_shard(self, rank, world):
+        self.ctx.check(self.lib.vio360_ba_set_shard(self.h, rank, world))
+
+    def set_parameters(self, pose_delta, points):
+        pd = np.ascontiguousarray(pose_delta, np.float64); pts = np.ascontiguousarray(points, np.float64)
+        self.ctx.check(self.lib.vio360_ba_set_parameters(self.h, _ptr(pd), _ptr(pts)))
+
+    def evaluate(self, want_jacobians=True, apply_loss=True, fetch=True):
+        cost = C.c_double(0)
+        self.ctx.check(self.lib.vio360_ba_evaluate(self.h, int(want_jacobians), int(apply_loss), C.byref(cost)))
+        if not fetch:
+            return cost.value
+        r = np.zeros((self.O, 2)); Jp = np.zeros((self.O, 2, 6)) if want_jacobians else None
+        Jl = np.zeros((self.O, 2, 3)) if want_jacobians else None
+        self.ctx.check(self.lib.vio360_ba_get_residuals_jacobians(self.h, _ptr(r), _ptr(Jp), _ptr(Jl)))
+        return r, Jp, Jl, cost.value
+
+    def normal_blocks(self, apply_loss=True):
+        Hpp = np.zeros((self.K, 6, 6)); bp = np.zeros((self.K, 6)); Hll = np.zeros((self.M, 3, 3))
+        bl = np.zeros((self.M, 3)); Hpl = np.zeros((self.O, 6, 3))
+        self.ctx.check(self.lib.vio360_ba_normal_blocks(self.h, int(apply_loss), _ptr(Hpp), _ptr(bp), _ptr(Hll),
+                                                        _ptr(bl), _ptr(Hpl)))
+        return Hpp, bp, Hll, bl, Hpl
+
+    @property
+    def reduced_dim(self):
+        return int(self.lib.vio360_ba_reduced_dim(self.h))
+
+    def build_reduced_system(self, lm_diag=None, apply_loss=True, fetch=True):
+        n = self.reduced_dim
+        D = None if lm_diag is None else np.ascontiguousarray(lm_diag, np.float64)
+        if not fetch:
+            self.ctx.check(self.lib.vio360_ba_build_reduced_system(self.h, _ptr(D), int(apply_loss), None, None, None))
+            return None
+        S = np.zeros((n, n)); rhs = np.zeros(n); cost = C.c_double(0)
+        self.ctx.check(self.lib.vio360_ba_build_reduced_system(self.h, _ptr(D), int(apply_loss), _ptr(S), _ptr(rhs),
+                                                               C.byref(cost)))
+        return S, rhs, cost.value
+
+    def reduced_system_dev(self):
+        p = C.c_void_p(); n = C.c_size_t(0)
+        self.ctx.check(self.lib.vio360_ba_reduced_system_dev(self.h, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def fetch_reduced_system(self):
+        n = self.reduced_dim
+        S = np.zeros((n, n)); rhs = np.zeros(n); cost = C.c_double(0)
+        self.ctx.check(self.lib.vio360_ba_fetch_reduced_system(self.h, _ptr(S), _ptr(rhs), C.byref(cost)))
+        return S, rhs, cost.value
+
+    def column_sqnorm(self, apply_loss=True):
+        out = np.zeros(6 * self.K + 3 * self.M)
+        self.ctx.check(self.lib.vio360_ba_column_sqnorm(self.h, int(apply_loss), _ptr(out)))
+        return out
+
+    def chi2(self, thr=5.991):
+        c = np.zeros(self.O); f = np.zeros(self.O, np.uint8)
+        self.ctx.check(self.lib.vio360_ba_chi2(self.h, float(thr), _ptr(c), _ptr(f)))
+        return c, f

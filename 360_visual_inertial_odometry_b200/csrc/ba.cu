@@ -1,0 +1,898 @@
+// ba.cu -- path B: bundle-adjustment factor evaluation on sm_100a.
+//
+// Kernels (SURVEY.md section 2.1 numbering):
+//   K6  k_pose_prepare      per-pose chain (Factors.cpp:357-364), once per pose
+//   K7  k_evaluate          residual + Jacobians (+Huber), one thread per observation
+//   K8  k_blocks_landmark / k_blocks_pose   J^T J / J^T r blocks by segmented reductions
+//   K9  k_schur_warp        factor evaluation fused with per-landmark Schur elimination
+//   K10 k_chi2              chi-square classification
+// Observations are re-ordered landmark-major once, in set_structure, so that every
+// landmark is a contiguous segment; results are scattered back to the caller's order.
+#include <algorithm>
+#include <numeric>
+
+#include "ba_math.cuh"
+#include "common.cuh"
+
+using namespace vio360;
+
+struct BaDev {           // device view handed to kernels by value
+    int K, M, O;
+    const double* u;     // [O] landmark-major order
+    const double* v;
+    const int* pose;     // [O]
+    const int* point;    // [O]
+    const int* orig;     // [O] position in the caller's order
+    const unsigned char* outlier;  // [O] landmark-major
+    const int* lm_ptr;   // [M+1]
+    const int* pose_ptr; // [K+1] segments of pose_order
+    const int* pose_order; // [O] landmark-major indices grouped by pose
+    const double* posebuf;   // [K*33]
+    const double* points;    // [M*3]
+    const int* free_map;     // [K]  reduced index or -1
+    const unsigned char* point_fixed;  // [M]
+    const double* D;         // [6K+3M] or nullptr
+    CamConst cam;
+};
+
+struct vio360_ba {
+    vio360_ctx* ctx = nullptr;
+    int K = 0, M = 0, O = 0;
+    bool has_structure = false, has_params = false, has_eval = false, has_eval_jac = false;
+    bool has_reduced = false;
+    int n_free = 0;
+    int shard_rank = 0, shard_world = 1, lm_begin = 0, lm_end = 0;
+    std::vector<int> lm_ptr, perm, free_map;
+    std::vector<unsigned char> pose_fixed, point_fixed;
+    double Tcb[16];
+    CamConst cam;
+    DevBuf d_u, d_v, d_pose, d_point, d_orig, d_outlier, d_lm_ptr, d_pose_ptr, d_pose_order;
+    DevBuf d_Twb, d_Tcb, d_posebuf, d_pose_delta, d_points, d_free_map, d_point_fixed, d_D;
+    DevBuf d_r, d_Jp, d_Jl, d_partials, d_packed, d_blocks, d_chi2, d_flag;
+    PinBuf pin;
+    bool use_D = false;
+};
+
+// ------------------------------------------------------------------------ kernels
+__global__ void k_pose_prepare(int K, const double* __restrict__ Twb, const double* __restrict__ Tcb,
+                               const double* __restrict__ delta, double* __restrict__ out) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= K) return;
+    double T0[16], Tc[16], xi[6], o[kPoseStride];
+    for (int i = 0; i < 16; ++i) { T0[i] = Twb[16 * (size_t)k + i]; Tc[i] = Tcb[i]; }
+    for (int i = 0; i < 6; ++i) xi[i] = delta[6 * (size_t)k + i];
+    pose_prepare(T0, Tc, xi, o);
+    for (int i = 0; i < kPoseStride; ++i) out[kPoseStride * (size_t)k + i] = o[i];
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// deterministic block sum -> partials[blockIdx.x]
+__device__ __forceinline__ void block_sum_to(double v, double* partials) {
+    __shared__ double sm[32];
+    v = warp_sum(v);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) sm[w] = v;
+    __syncthreads();
+    if (w == 0) {
+        const int nw = (blockDim.x + 31) >> 5;
+        double t = lane < nw ? sm[lane] : 0.0;
+        t = warp_sum(t);
+        if (lane == 0) partials[blockIdx.x] = t;
+    }
+}
+
+__global__ void k_sum_partials(const double* __restrict__ partials, int n, double* __restrict__ out) {
+    double t = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) t += partials[i];
+    __shared__ double sm[32];
+    t = warp_sum(t);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) sm[w] = t;
+    __syncthreads();
+    if (w == 0) {
+        const int nw = (blockDim.x + 31) >> 5;
+        double s = lane < nw ? sm[lane] : 0.0;
+        s = warp_sum(s);
+        if (lane == 0) *out = s;
+    }
+}
+
+template <bool WANT_JAC>
+__global__ void __launch_bounds__(128) k_evaluate(BaDev d, bool apply_loss, double* __restrict__ r_out,
+                                                  double* __restrict__ Jp_out, double* __restrict__ Jl_out,
+                                                  double* __restrict__ partials) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    double cost = 0.0;
+    if (i < d.O) {
+        const int p = d.pose[i], l = d.point[i];
+        double pose[kPoseStride];
+#pragma unroll
+        for (int j = 0; j < kPoseStride; ++j) pose[j] = __ldg(d.posebuf + kPoseStride * (size_t)p + j);
+        const double Pw[3] = {__ldg(d.points + 3 * (size_t)l), __ldg(d.points + 3 * (size_t)l + 1),
+                              __ldg(d.points + 3 * (size_t)l + 2)};
+        double r[2], F[12], E[6];
+        cost = obs_evaluate<WANT_JAC>(pose, Pw, d.u[i], d.v[i], d.outlier[i] != 0, d.cam, apply_loss, r, F, E);
+        const size_t o = (size_t)d.orig[i];
+        r_out[2 * o] = r[0]; r_out[2 * o + 1] = r[1];
+        if (WANT_JAC) {
+#pragma unroll
+            for (int j = 0; j < 12; ++j) Jp_out[12 * o + j] = F[j];
+#pragma unroll
+            for (int j = 0; j < 6; ++j) Jl_out[6 * o + j] = E[j];
+        }
+    }
+    block_sum_to(cost, partials);
+}
+
+__global__ void __launch_bounds__(128) k_chi2(BaDev d, double thr, double* __restrict__ chi2,
+                                              unsigned char* __restrict__ flag) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= d.O) return;
+    const int p = d.pose[i], l = d.point[i];
+    double pose[12];
+#pragma unroll
+    for (int j = 0; j < 12; ++j) pose[j] = __ldg(d.posebuf + kPoseStride * (size_t)p + j);
+    const double Pw[3] = {__ldg(d.points + 3 * (size_t)l), __ldg(d.points + 3 * (size_t)l + 1),
+                          __ldg(d.points + 3 * (size_t)l + 2)};
+    const double c = obs_chi2(pose, Pw, d.u[i], d.v[i], d.outlier[i] != 0, d.cam);
+    const size_t o = (size_t)d.orig[i];
+    chi2[o] = c;
+    flag[o] = (unsigned char)(c > thr);
+}
+
+__device__ __forceinline__ void load_pose(const BaDev& d, int p, double* pose) {
+#pragma unroll
+    for (int j = 0; j < kPoseStride; ++j) pose[j] = __ldg(d.posebuf + kPoseStride * (size_t)p + j);
+}
+
+// K8a: one warp per landmark: Hll (3x3), bl (3) by warp reduction; Hpl per observation.
+__global__ void __launch_bounds__(128) k_blocks_landmark(BaDev d, bool apply_loss, double* __restrict__ Hll,
+                                                         double* __restrict__ bl, double* __restrict__ Hpl) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= d.M) return;
+    const int l = warp, lo = d.lm_ptr[l], hi = d.lm_ptr[l + 1];
+    const bool lfix = d.point_fixed[l] != 0;
+    const double Pw[3] = {d.points[3 * (size_t)l], d.points[3 * (size_t)l + 1], d.points[3 * (size_t)l + 2]};
+    double h[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};
+    for (int base = lo; base < hi; base += 32) {
+        const int i = base + lane;
+        if (i < hi) {
+            const int pk = d.pose[i];
+            double pose[kPoseStride], r[2], F[12], E[6];
+            load_pose(d, pk, pose);
+            obs_evaluate<true>(pose, Pw, d.u[i], d.v[i], d.outlier[i] != 0, d.cam, apply_loss, r, F, E);
+            const bool pfix = d.free_map[pk] < 0;
+            if (!lfix) {
+                h[0] += E[0] * E[0] + E[3] * E[3]; h[1] += E[0] * E[1] + E[3] * E[4];
+                h[2] += E[0] * E[2] + E[3] * E[5]; h[3] += E[1] * E[1] + E[4] * E[4];
+                h[4] += E[1] * E[2] + E[4] * E[5]; h[5] += E[2] * E[2] + E[5] * E[5];
+                g[0] += E[0] * r[0] + E[3] * r[1]; g[1] += E[1] * r[0] + E[4] * r[1];
+                g[2] += E[2] * r[0] + E[5] * r[1];
+            }
+            if (Hpl) {
+                const size_t o = 18 * (size_t)d.orig[i];
+#pragma unroll
+                for (int a = 0; a < 6; ++a)
+#pragma unroll
+                    for (int b = 0; b < 3; ++b)
+                        Hpl[o + a * 3 + b] = (lfix || pfix) ? 0.0 : F[a] * E[b] + F[6 + a] * E[3 + b];
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 6; ++j) h[j] = warp_sum(h[j]);
+#pragma unroll
+    for (int j = 0; j < 3; ++j) g[j] = warp_sum(g[j]);
+    if (lane == 0) {
+        if (Hll) {
+            double* H = Hll + 9 * (size_t)l;
+            H[0] = h[0]; H[1] = h[1]; H[2] = h[2]; H[3] = h[1]; H[4] = h[3]; H[5] = h[4];
+            H[6] = h[2]; H[7] = h[4]; H[8] = h[5];
+        }
+        if (bl) { bl[3 * (size_t)l] = g[0]; bl[3 * (size_t)l + 1] = g[1]; bl[3 * (size_t)l + 2] = g[2]; }
+    }
+}
+
+// K8b: one block per pose: Hpp (6x6), bp (6) by a segmented block reduction over the
+// pose's observations (no atomics, fixed summation order).
+__global__ void __launch_bounds__(256) k_blocks_pose(BaDev d, bool apply_loss, bool skip_fixed_points_never,
+                                                     double* __restrict__ Hpp, double* __restrict__ bp) {
+    const int k = blockIdx.x;
+    const int lo = d.pose_ptr[k], hi = d.pose_ptr[k + 1];
+    double acc[27];
+#pragma unroll
+    for (int j = 0; j < 27; ++j) acc[j] = 0.0;
+    if (d.free_map[k] >= 0) {
+        double pose[kPoseStride];
+        load_pose(d, k, pose);
+        for (int q = lo + threadIdx.x; q < hi; q += blockDim.x) {
+            const int i = d.pose_order[q];
+            const int l = d.point[i];
+            const double Pw[3] = {d.points[3 * (size_t)l], d.points[3 * (size_t)l + 1], d.points[3 * (size_t)l + 2]};
+            double r[2], F[12], E[6];
+            obs_evaluate<true>(pose, Pw, d.u[i], d.v[i], d.outlier[i] != 0, d.cam, apply_loss, r, F, E);
+            int t = 0;
+#pragma unroll
+            for (int a = 0; a < 6; ++a)
+#pragma unroll
+                for (int b = a; b < 6; ++b) acc[t++] += F[a] * F[b] + F[6 + a] * F[6 + b];
+#pragma unroll
+            for (int a = 0; a < 6; ++a) acc[21 + a] += F[a] * r[0] + F[6 + a] * r[1];
+        }
+    }
+    (void)skip_fixed_points_never;
+    __shared__ double sm[8][27];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int j = 0; j < 27; ++j) {
+        const double s = warp_sum(acc[j]);
+        if (lane == 0) sm[w][j] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x < 27) {
+        double s = 0.0;
+        for (int ww = 0; ww < (int)(blockDim.x >> 5); ++ww) s += sm[ww][threadIdx.x];
+        sm[0][threadIdx.x] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x < 36 && Hpp) {
+        const int a = threadIdx.x / 6, b = threadIdx.x % 6;
+        const int aa = a < b ? a : b, bb = a < b ? b : a;
+        const int t = aa * 6 - aa * (aa - 1) / 2 + (bb - aa);
+        Hpp[36 * (size_t)k + threadIdx.x] = sm[0][t];
+    }
+    if (threadIdx.x < 6 && bp) bp[6 * (size_t)k + threadIdx.x] = sm[0][21 + threadIdx.x];
+}
+
+// K9 (general form): one warp per landmark.  Lanes hold observations; E'E and E'r are
+// reduced with shuffles; each lane then owns the row-block of its own pose and walks
+// the landmark's observations (broadcast by shuffle) to emit -Y_i W_k^T into the upper
+// block triangle of S.  Accumulation into S / rhs uses fp64 RED (order-insensitive to
+// ~1e-16); the tiled kernel below removes the atomics for the regular case.
+__global__ void __launch_bounds__(128) k_schur_warp(BaDev d, int lm_begin, int lm_end, bool apply_loss,
+                                                    double* __restrict__ S, int n, double* __restrict__ rhs,
+                                                    double* __restrict__ partials) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    const int l = lm_begin + warp;
+    double cost = 0.0;
+    if (l < lm_end) {
+        const int lo = d.lm_ptr[l], hi = d.lm_ptr[l + 1];
+        const bool lfix = d.point_fixed[l] != 0;
+        const double Pw[3] = {d.points[3 * (size_t)l], d.points[3 * (size_t)l + 1], d.points[3 * (size_t)l + 2]};
+        const bool single = (hi - lo) <= 32;
+        double r[2], F[12], E[6];
+        int pf = -1;
+        // ---- pass 1: E'E (+D^2), g = E'r, cost
+        double h[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};
+        for (int base = lo; base < hi; base += 32) {
+            const int i = base + lane;
+            if (i < hi) {
+                const int pk = d.pose[i];
+                double pose[kPoseStride];
+                load_pose(d, pk, pose);
+                cost += obs_evaluate<true>(pose, Pw, d.u[i], d.v[i], d.outlier[i] != 0, d.cam, apply_loss, r, F, E);
+                pf = d.free_map[pk];
+                h[0] += E[0] * E[0] + E[3] * E[3]; h[1] += E[0] * E[1] + E[3] * E[4];
+                h[2] += E[0] * E[2] + E[3] * E[5]; h[3] += E[1] * E[1] + E[4] * E[4];
+                h[4] += E[1] * E[2] + E[4] * E[5]; h[5] += E[2] * E[2] + E[5] * E[5];
+                g[0] += E[0] * r[0] + E[3] * r[1]; g[1] += E[1] * r[0] + E[4] * r[1];
+                g[2] += E[2] * r[0] + E[5] * r[1];
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 6; ++j) h[j] = warp_sum(h[j]);
+#pragma unroll
+        for (int j = 0; j < 3; ++j) g[j] = warp_sum(g[j]);
+        double inv[6] = {0, 0, 0, 0, 0, 0}, ig[3] = {0, 0, 0};
+        if (!lfix) {
+            if (d.D) {
+                const double d0 = d.D[6 * (size_t)d.K + 3 * (size_t)l], d1 = d.D[6 * (size_t)d.K + 3 * (size_t)l + 1],
+                             d2 = d.D[6 * (size_t)d.K + 3 * (size_t)l + 2];
+                h[0] += d0 * d0; h[3] += d1 * d1; h[5] += d2 * d2;
+            }
+            inv_spd3(h, inv);
+            bool ok = true;
+#pragma unroll
+            for (int j = 0; j < 6; ++j) ok = ok && isfinite(inv[j]);
+            if (!ok) { for (int j = 0; j < 6; ++j) inv[j] = 0.0; }   // rank-deficient landmark: not eliminated
+            ig[0] = inv[0] * g[0] + inv[1] * g[1] + inv[2] * g[2];
+            ig[1] = inv[1] * g[0] + inv[3] * g[1] + inv[4] * g[2];
+            ig[2] = inv[2] * g[0] + inv[4] * g[1] + inv[5] * g[2];
+        }
+        // ---- pass 2
+        for (int baseA = lo; baseA < hi; baseA += 32) {
+            const int i = baseA + lane;
+            const bool act = i < hi;
+            if (!single && act) {
+                const int pk = d.pose[i];
+                double pose[kPoseStride];
+                load_pose(d, pk, pose);
+                obs_evaluate<true>(pose, Pw, d.u[i], d.v[i], d.outlier[i] != 0, d.cam, apply_loss, r, F, E);
+                pf = d.free_map[pk];
+            }
+            const int pA = act ? pf : -1;
+            double W[18], Y[18];
+#pragma unroll
+            for (int j = 0; j < 18; ++j) { W[j] = 0.0; Y[j] = 0.0; }
+            if (pA >= 0) {
+                // S_pp += F'F ; rhs_p += F'(r - E ig)
+                const double s0 = r[0] - (E[0] * ig[0] + E[1] * ig[1] + E[2] * ig[2]);
+                const double s1 = r[1] - (E[3] * ig[0] + E[4] * ig[1] + E[5] * ig[2]);
+#pragma unroll
+                for (int a = 0; a < 6; ++a) {
+#pragma unroll
+                    for (int b = 0; b < 6; ++b)
+                        atomicAdd(S + (size_t)(6 * pA + a) * n + 6 * pA + b, F[a] * F[b] + F[6 + a] * F[6 + b]);
+                    atomicAdd(rhs + 6 * pA + a, F[a] * s0 + F[6 + a] * s1);
+                }
+                if (!lfix) {
+#pragma unroll
+                    for (int a = 0; a < 6; ++a) {
+                        W[a * 3 + 0] = F[a] * E[0] + F[6 + a] * E[3];
+                        W[a * 3 + 1] = F[a] * E[1] + F[6 + a] * E[4];
+                        W[a * 3 + 2] = F[a] * E[2] + F[6 + a] * E[5];
+                        Y[a * 3 + 0] = W[a * 3] * inv[0] + W[a * 3 + 1] * inv[1] + W[a * 3 + 2] * inv[2];
+                        Y[a * 3 + 1] = W[a * 3] * inv[1] + W[a * 3 + 1] * inv[3] + W[a * 3 + 2] * inv[4];
+                        Y[a * 3 + 2] = W[a * 3] * inv[2] + W[a * 3 + 1] * inv[4] + W[a * 3 + 2] * inv[5];
+                    }
+                }
+            }
+            if (lfix) continue;
+            for (int baseB = lo; baseB < hi; baseB += 32) {
+                double WB[18];
+                int pB = -1;
+                if (baseB == baseA) {
+#pragma unroll
+                    for (int j = 0; j < 18; ++j) WB[j] = W[j];
+                    pB = pA;
+                } else {
+                    const int k = baseB + lane;
+#pragma unroll
+                    for (int j = 0; j < 18; ++j) WB[j] = 0.0;
+                    if (k < hi) {
+                        const int pk = d.pose[k];
+                        double pose[kPoseStride], r2[2], F2[12], E2[6];
+                        load_pose(d, pk, pose);
+                        obs_evaluate<true>(pose, Pw, d.u[k], d.v[k], d.outlier[k] != 0, d.cam, apply_loss, r2, F2, E2);
+                        pB = d.free_map[pk];
+                        if (pB >= 0) {
+#pragma unroll
+                            for (int a = 0; a < 6; ++a) {
+                                WB[a * 3 + 0] = F2[a] * E2[0] + F2[6 + a] * E2[3];
+                                WB[a * 3 + 1] = F2[a] * E2[1] + F2[6 + a] * E2[4];
+                                WB[a * 3 + 2] = F2[a] * E2[2] + F2[6 + a] * E2[5];
+                            }
+                        }
+                    }
+                }
+                const int nB = min(32, hi - baseB);
+                for (int k = 0; k < nB; ++k) {
+                    const int pk = __shfl_sync(0xffffffffu, pB, k);
+                    double Wk[18];
+#pragma unroll
+                    for (int j = 0; j < 18; ++j) Wk[j] = __shfl_sync(0xffffffffu, WB[j], k);
+                    if (pA >= 0 && pk >= 0 && pA <= pk) {
+                        double* Sb = S + (size_t)(6 * pA) * n + 6 * pk;
+#pragma unroll
+                        for (int a = 0; a < 6; ++a)
+#pragma unroll
+                            for (int b = 0; b < 6; ++b)
+                                atomicAdd(Sb + (size_t)a * n + b,
+                                          -(Y[a * 3] * Wk[b * 3] + Y[a * 3 + 1] * Wk[b * 3 + 1] + Y[a * 3 + 2] * Wk[b * 3 + 2]));
+                    }
+                }
+            }
+        }
+    }
+    block_sum_to(cost, partials);
+}
+
+// mirror the upper block triangle into the lower one and add the pose part of D^2
+__global__ void k_finish_S(double* __restrict__ S, int n, const double* __restrict__ D, const int* __restrict__ free_map,
+                           int K, bool add_diag) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n * n) return;
+    const int i = idx / n, j = idx % n;
+    const int bi = i / 6, bj = j / 6;
+    if (bi > bj) { S[idx] = S[(size_t)j * n + i]; return; }
+    if (bi == bj && i > j) { S[idx] = S[(size_t)j * n + i]; return; }   // exact symmetry inside diagonal blocks
+    if (i == j && add_diag && D) {
+        // find pose k with free_map[k] == bi (K is small relative to n*n work; linear scan per diagonal entry)
+        for (int k = 0; k < K; ++k)
+            if (free_map[k] == bi) { const double dd = D[6 * (size_t)k + (i - 6 * bi)]; S[idx] += dd * dd; break; }
+    }
+}
+
+// --------------------------------------------------------------------- host side
+static BaDev make_dev(const vio360_ba* ba) {
+    BaDev d;
+    d.K = ba->K; d.M = ba->M; d.O = ba->O;
+    d.u = ba->d_u.as<double>(); d.v = ba->d_v.as<double>();
+    d.pose = ba->d_pose.as<int>(); d.point = ba->d_point.as<int>(); d.orig = ba->d_orig.as<int>();
+    d.outlier = ba->d_outlier.as<unsigned char>();
+    d.lm_ptr = ba->d_lm_ptr.as<int>(); d.pose_ptr = ba->d_pose_ptr.as<int>();
+    d.pose_order = ba->d_pose_order.as<int>();
+    d.posebuf = ba->d_posebuf.as<double>(); d.points = ba->d_points.as<double>();
+    d.free_map = ba->d_free_map.as<int>(); d.point_fixed = ba->d_point_fixed.as<unsigned char>();
+    d.D = ba->use_D ? ba->d_D.as<double>() : nullptr;
+    d.cam = ba->cam;
+    return d;
+}
+
+extern "C" int vio360_ba_create(vio360_ctx* ctx, int K, int M, int O, vio360_ba** out) {
+    if (!ctx || !out || K <= 0 || M <= 0 || O < 0) return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_create: bad sizes");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    vio360_ba* ba = new vio360_ba();
+    ba->ctx = ctx; ba->K = K; ba->M = M; ba->O = O;
+    *out = ba;
+    return VIO360_OK;
+}
+
+extern "C" void vio360_ba_destroy(vio360_ba* ba) {
+    if (!ba) return;
+    cudaSetDevice(ba->ctx->device);
+    cudaStreamSynchronize(ba->ctx->stream);
+    DevBuf* bufs[] = {&ba->d_u, &ba->d_v, &ba->d_pose, &ba->d_point, &ba->d_orig, &ba->d_outlier, &ba->d_lm_ptr,
+                      &ba->d_pose_ptr, &ba->d_pose_order, &ba->d_Twb, &ba->d_Tcb, &ba->d_posebuf, &ba->d_pose_delta,
+                      &ba->d_points, &ba->d_free_map, &ba->d_point_fixed, &ba->d_D, &ba->d_r, &ba->d_Jp, &ba->d_Jl,
+                      &ba->d_partials, &ba->d_packed, &ba->d_blocks, &ba->d_chi2, &ba->d_flag};
+    for (DevBuf* b : bufs) b->release();
+    ba->pin.release();
+    delete ba;
+}
+
+static void compute_shard(vio360_ba* ba) {
+    // contiguous landmark ranges balanced by sum of (degree^2 + degree)
+    const int M = ba->M;
+    std::vector<double> w(M + 1, 0.0);
+    for (int l = 0; l < M; ++l) {
+        const double dg = ba->lm_ptr[l + 1] - ba->lm_ptr[l];
+        w[l + 1] = w[l] + dg * dg + 4.0 * dg;
+    }
+    auto cut = [&](int r) {
+        if (r <= 0) return 0;
+        if (r >= ba->shard_world) return M;
+        const double target = w[M] * r / ba->shard_world;
+        return (int)(std::lower_bound(w.begin(), w.end(), target) - w.begin());
+    };
+    ba->lm_begin = std::min(cut(ba->shard_rank), M);
+    ba->lm_end = std::min(cut(ba->shard_rank + 1), M);
+    if (ba->lm_end < ba->lm_begin) ba->lm_end = ba->lm_begin;
+}
+
+extern "C" int vio360_ba_set_shard(vio360_ba* ba, int rank, int world) {
+    if (!ba) return VIO360_ERR_INVALID;
+    if (world < 1 || rank < 0 || rank >= world) return vio360_fail(ba->ctx, VIO360_ERR_INVALID, "ba_set_shard: bad rank/world");
+    ba->shard_rank = rank; ba->shard_world = world;
+    if (ba->has_structure) compute_shard(ba);
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_set_structure(vio360_ba* ba, const int32_t* pose_idx, const int32_t* point_idx,
+                                       const double* obs_u, const double* obs_v, const double* T_wb_init,
+                                       const double* T_cb, double cols, double rows, const double* info,
+                                       double huber_delta, const uint8_t* pose_fixed, const uint8_t* point_fixed) {
+    if (!ba) return VIO360_ERR_INVALID;
+    vio360_ctx* ctx = ba->ctx;
+    if (!pose_idx || !point_idx || !obs_u || !obs_v || !T_wb_init || !T_cb || !info)
+        return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_set_structure: null argument");
+    const int K = ba->K, M = ba->M, O = ba->O;
+    for (int i = 0; i < O; ++i)
+        if (pose_idx[i] < 0 || pose_idx[i] >= K || point_idx[i] < 0 || point_idx[i] >= M)
+            return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_set_structure: index out of range at observation %d", i);
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    // landmark-major stable ordering (counting sort), pose-major ordering of those
+    ba->lm_ptr.assign(M + 1, 0);
+    for (int i = 0; i < O; ++i) ba->lm_ptr[point_idx[i] + 1]++;
+    for (int l = 0; l < M; ++l) ba->lm_ptr[l + 1] += ba->lm_ptr[l];
+    ba->perm.resize(O);
+    {
+        std::vector<int> fill(ba->lm_ptr.begin(), ba->lm_ptr.end() - 1);
+        for (int i = 0; i < O; ++i) ba->perm[fill[point_idx[i]]++] = i;
+    }
+    std::vector<int> s_pose(O), s_point(O), pose_ptr(K + 1, 0), pose_order(O);
+    std::vector<double> s_u(O), s_v(O);
+    for (int q = 0; q < O; ++q) {
+        const int i = ba->perm[q];
+        s_pose[q] = pose_idx[i]; s_point[q] = point_idx[i]; s_u[q] = obs_u[i]; s_v[q] = obs_v[i];
+        pose_ptr[pose_idx[i] + 1]++;
+    }
+    for (int k = 0; k < K; ++k) pose_ptr[k + 1] += pose_ptr[k];
+    {
+        std::vector<int> fill(pose_ptr.begin(), pose_ptr.end() - 1);
+        for (int q = 0; q < O; ++q) pose_order[fill[s_pose[q]]++] = q;
+    }
+    ba->pose_fixed.assign(K, 0); ba->point_fixed.assign(M, 0);
+    if (pose_fixed) ba->pose_fixed.assign(pose_fixed, pose_fixed + K);
+    if (point_fixed) ba->point_fixed.assign(point_fixed, point_fixed + M);
+    ba->free_map.assign(K, -1);
+    ba->n_free = 0;
+    for (int k = 0; k < K; ++k) if (!ba->pose_fixed[k]) ba->free_map[k] = ba->n_free++;
+    memcpy(ba->Tcb, T_cb, sizeof(ba->Tcb));
+    cam_const_init(ba->cam, cols, rows, info, T_cb, huber_delta);
+    compute_shard(ba);
+
+    cudaStream_t st = ctx->stream;
+    const size_t Os = (size_t)std::max(O, 1);
+    VIO_CUDA(ctx, ba->d_u.reserve(Os * 8)); VIO_CUDA(ctx, ba->d_v.reserve(Os * 8));
+    VIO_CUDA(ctx, ba->d_pose.reserve(Os * 4)); VIO_CUDA(ctx, ba->d_point.reserve(Os * 4));
+    VIO_CUDA(ctx, ba->d_orig.reserve(Os * 4)); VIO_CUDA(ctx, ba->d_outlier.reserve(Os));
+    VIO_CUDA(ctx, ba->d_lm_ptr.reserve((size_t)(M + 1) * 4)); VIO_CUDA(ctx, ba->d_pose_ptr.reserve((size_t)(K + 1) * 4));
+    VIO_CUDA(ctx, ba->d_pose_order.reserve(Os * 4));
+    VIO_CUDA(ctx, ba->d_Twb.reserve((size_t)K * 16 * 8)); VIO_CUDA(ctx, ba->d_Tcb.reserve(16 * 8));
+    VIO_CUDA(ctx, ba->d_posebuf.reserve((size_t)K * kPoseStride * 8));
+    VIO_CUDA(ctx, ba->d_pose_delta.reserve((size_t)K * 6 * 8)); VIO_CUDA(ctx, ba->d_points.reserve((size_t)M * 3 * 8));
+    VIO_CUDA(ctx, ba->d_free_map.reserve((size_t)K * 4)); VIO_CUDA(ctx, ba->d_point_fixed.reserve((size_t)M));
+    VIO_CUDA(ctx, ba->d_D.reserve(((size_t)6 * K + (size_t)3 * M) * 8));
+    if (O > 0) {
+        VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_u.p, s_u.data(), Os * 8, cudaMemcpyHostToDevice, st));
+        VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_v.p, s_v.data(), Os * 8, cudaMemcpyHostToDevice, st));
+        VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_pose.p, s_pose.data(), Os * 4, cudaMemcpyHostToDevice, st));
+        VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_point.p, s_point.data(), Os * 4, cudaMemcpyHostToDevice, st));
+        VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_orig.p, ba->perm.data(), Os * 4, cudaMemcpyHostToDevice, st));
+        VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_pose_order.p, pose_order.data(), Os * 4, cudaMemcpyHostToDevice, st));
+        VIO_CUDA(ctx, cudaMemsetAsync(ba->d_outlier.p, 0, Os, st));
+    }
+    VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_lm_ptr.p, ba->lm_ptr.data(), (size_t)(M + 1) * 4, cudaMemcpyHostToDevice, st));
+    VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_pose_ptr.p, pose_ptr.data(), (size_t)(K + 1) * 4, cudaMemcpyHostToDevice, st));
+    VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_Twb.p, T_wb_init, (size_t)K * 16 * 8, cudaMemcpyHostToDevice, st));
+    VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_Tcb.p, T_cb, 16 * 8, cudaMemcpyHostToDevice, st));
+    VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_free_map.p, ba->free_map.data(), (size_t)K * 4, cudaMemcpyHostToDevice, st));
+    VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_point_fixed.p, ba->point_fixed.data(), (size_t)M, cudaMemcpyHostToDevice, st));
+    VIO_CUDA(ctx, cudaStreamSynchronize(st));   // host vectors above go out of scope
+    ba->has_structure = true; ba->has_params = false; ba->has_eval = false; ba->has_reduced = false;
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_set_outliers(vio360_ba* ba, const uint8_t* outlier) {
+    if (!ba) return VIO360_ERR_INVALID;
+    vio360_ctx* ctx = ba->ctx;
+    if (!ba->has_structure) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_set_outliers before ba_set_structure");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (ba->O == 0) return VIO360_OK;
+    if (!outlier) { VIO_CUDA(ctx, cudaMemsetAsync(ba->d_outlier.p, 0, (size_t)ba->O, ctx->stream)); return VIO360_OK; }
+    VIO_CUDA(ctx, ba->pin.reserve((size_t)ba->O));
+    unsigned char* h = ba->pin.as<unsigned char>();
+    for (int q = 0; q < ba->O; ++q) h[q] = outlier[ba->perm[q]];
+    VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_outlier.p, h, (size_t)ba->O, cudaMemcpyHostToDevice, ctx->stream));
+    VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_set_parameters(vio360_ba* ba, const double* pose_delta, const double* points) {
+    if (!ba) return VIO360_ERR_INVALID;
+    vio360_ctx* ctx = ba->ctx;
+    if (!ba->has_structure) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_set_parameters before ba_set_structure");
+    if (!pose_delta || !points) return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_set_parameters: null argument");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t nb_p = (size_t)ba->K * 6 * 8, nb_l = (size_t)ba->M * 3 * 8;
+    VIO_CUDA(ctx, ba->pin.reserve(nb_p + nb_l));
+    memcpy(ba->pin.p, pose_delta, nb_p);
+    memcpy((char*)ba->pin.p + nb_p, points, nb_l);
+    VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_pose_delta.p, ba->pin.p, nb_p, cudaMemcpyHostToDevice, ctx->stream));
+    VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_points.p, (char*)ba->pin.p + nb_p, nb_l, cudaMemcpyHostToDevice, ctx->stream));
+    k_pose_prepare<<<(ba->K + 63) / 64, 64, 0, ctx->stream>>>(ba->K, ba->d_Twb.as<double>(), ba->d_Tcb.as<double>(),
+                                                             ba->d_pose_delta.as<double>(), ba->d_posebuf.as<double>());
+    VIO_LAUNCH_CHECK(ctx);
+    VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));   // pinned staging is reused by the next call
+    ba->has_params = true; ba->has_eval = false; ba->has_reduced = false;
+    return VIO360_OK;
+}
+
+static int sum_partials(vio360_ba* ba, int nblocks, double* dev_out) {
+    vio360_ctx* ctx = ba->ctx;
+    k_sum_partials<<<1, 256, 0, ctx->stream>>>(ba->d_partials.as<double>(), nblocks, dev_out);
+    VIO_LAUNCH_CHECK(ctx);
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_evaluate(vio360_ba* ba, int want_jacobians, int apply_loss, double* cost) {
+    if (!ba) return VIO360_ERR_INVALID;
+    vio360_ctx* ctx = ba->ctx;
+    if (!ba->has_params) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_evaluate before ba_set_parameters");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int O = ba->O;
+    const size_t Os = (size_t)std::max(O, 1);
+    VIO_CUDA(ctx, ba->d_r.reserve(Os * 2 * 8));
+    if (want_jacobians) { VIO_CUDA(ctx, ba->d_Jp.reserve(Os * 12 * 8)); VIO_CUDA(ctx, ba->d_Jl.reserve(Os * 6 * 8)); }
+    const int nb = std::max(1, (O + 127) / 128);
+    VIO_CUDA(ctx, ba->d_partials.reserve((size_t)(nb + 1) * 8));
+    BaDev d = make_dev(ba);
+    if (want_jacobians)
+        k_evaluate<true><<<nb, 128, 0, ctx->stream>>>(d, apply_loss != 0, ba->d_r.as<double>(), ba->d_Jp.as<double>(),
+                                                     ba->d_Jl.as<double>(), ba->d_partials.as<double>());
+    else
+        k_evaluate<false><<<nb, 128, 0, ctx->stream>>>(d, apply_loss != 0, ba->d_r.as<double>(), nullptr, nullptr,
+                                                      ba->d_partials.as<double>());
+    VIO_LAUNCH_CHECK(ctx);
+    int rc = sum_partials(ba, nb, ba->d_partials.as<double>() + nb);
+    if (rc) return rc;
+    double h = 0.0;
+    VIO_CUDA(ctx, cudaMemcpyAsync(&h, ba->d_partials.as<double>() + nb, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (cost) *cost = h;
+    ba->has_eval = true; ba->has_eval_jac = want_jacobians != 0;
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_get_residuals_jacobians(vio360_ba* ba, double* r, double* Jp, double* Jl) {
+    if (!ba) return VIO360_ERR_INVALID;
+    vio360_ctx* ctx = ba->ctx;
+    if (!ba->has_eval) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_get_residuals_jacobians before ba_evaluate");
+    if ((Jp || Jl) && !ba->has_eval_jac) return vio360_fail(ctx, VIO360_ERR_STATE, "last ba_evaluate had want_jacobians=0");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t O = (size_t)ba->O;
+    if (O == 0) return VIO360_OK;
+    if (r) VIO_CUDA(ctx, cudaMemcpyAsync(r, ba->d_r.p, O * 16, cudaMemcpyDeviceToHost, ctx->stream));
+    if (Jp) VIO_CUDA(ctx, cudaMemcpyAsync(Jp, ba->d_Jp.p, O * 96, cudaMemcpyDeviceToHost, ctx->stream));
+    if (Jl) VIO_CUDA(ctx, cudaMemcpyAsync(Jl, ba->d_Jl.p, O * 48, cudaMemcpyDeviceToHost, ctx->stream));
+    VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return VIO360_OK;
+}
+
+static int run_blocks(vio360_ba* ba, int apply_loss) {
+    // layout of d_blocks: Hpp K*36 | bp K*6 | Hll M*9 | bl M*3 | Hpl O*18
+    vio360_ctx* ctx = ba->ctx;
+    const size_t K = ba->K, M = ba->M, O = ba->O;
+    const size_t tot = K * 42 + M * 12 + O * 18;
+    VIO_CUDA(ctx, ba->d_blocks.reserve(std::max<size_t>(tot, 1) * 8));
+    double* Hpp = ba->d_blocks.as<double>(); double* bp = Hpp + K * 36; double* Hll = bp + K * 6;
+    double* bl = Hll + M * 9; double* Hpl = bl + M * 3;
+    BaDev d = make_dev(ba);
+    k_blocks_landmark<<<(int)((M * 32 + 127) / 128), 128, 0, ctx->stream>>>(d, apply_loss != 0, Hll, bl, Hpl);
+    VIO_LAUNCH_CHECK(ctx);
+    k_blocks_pose<<<(int)K, 256, 0, ctx->stream>>>(d, apply_loss != 0, false, Hpp, bp);
+    VIO_LAUNCH_CHECK(ctx);
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_normal_blocks(vio360_ba* ba, int apply_loss, double* Hpp, double* bp, double* Hll,
+                                       double* bl, double* Hpl) {
+    if (!ba) return VIO360_ERR_INVALID;
+    vio360_ctx* ctx = ba->ctx;
+    if (!ba->has_params) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_normal_blocks before ba_set_parameters");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc = run_blocks(ba, apply_loss);
+    if (rc) return rc;
+    const size_t K = ba->K, M = ba->M, O = ba->O;
+    double* dHpp = ba->d_blocks.as<double>(); double* dbp = dHpp + K * 36; double* dHll = dbp + K * 6;
+    double* dbl = dHll + M * 9; double* dHpl = dbl + M * 3;
+    cudaStream_t st = ctx->stream;
+    if (Hpp) VIO_CUDA(ctx, cudaMemcpyAsync(Hpp, dHpp, K * 36 * 8, cudaMemcpyDeviceToHost, st));
+    if (bp) VIO_CUDA(ctx, cudaMemcpyAsync(bp, dbp, K * 6 * 8, cudaMemcpyDeviceToHost, st));
+    if (Hll) VIO_CUDA(ctx, cudaMemcpyAsync(Hll, dHll, M * 9 * 8, cudaMemcpyDeviceToHost, st));
+    if (bl) VIO_CUDA(ctx, cudaMemcpyAsync(bl, dbl, M * 3 * 8, cudaMemcpyDeviceToHost, st));
+    if (Hpl && O) VIO_CUDA(ctx, cudaMemcpyAsync(Hpl, dHpl, O * 18 * 8, cudaMemcpyDeviceToHost, st));
+    VIO_CUDA(ctx, cudaStreamSynchronize(st));
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_column_sqnorm(vio360_ba* ba, int apply_loss, double* out) {
+    if (!ba || !out) return VIO360_ERR_INVALID;
+    vio360_ctx* ctx = ba->ctx;
+    if (!ba->has_params) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_column_sqnorm before ba_set_parameters");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc = run_blocks(ba, apply_loss);
+    if (rc) return rc;
+    const size_t K = ba->K, M = ba->M;
+    double* dHpp = ba->d_blocks.as<double>(); double* dHll = dHpp + K * 42;
+    std::vector<double> hpp(K * 36), hll(M * 9);
+    VIO_CUDA(ctx, cudaMemcpyAsync(hpp.data(), dHpp, K * 36 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    VIO_CUDA(ctx, cudaMemcpyAsync(hll.data(), dHll, M * 9 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (size_t k = 0; k < K; ++k) for (int a = 0; a < 6; ++a) out[6 * k + a] = hpp[36 * k + 7 * a];
+    for (size_t l = 0; l < M; ++l) for (int a = 0; a < 3; ++a) out[6 * K + 3 * l + a] = hll[9 * l + 4 * a];
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_reduced_dim(const vio360_ba* ba) { return ba ? 6 * ba->n_free : VIO360_ERR_INVALID; }
+
+extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_diag, int apply_loss, double* S,
+                                              double* rhs, double* cost) {
+    if (!ba) return VIO360_ERR_INVALID;
+    vio360_ctx* ctx = ba->ctx;
+    if (!ba->has_params) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_build_reduced_system before ba_set_parameters");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int n = 6 * ba->n_free;
+    const size_t K = ba->K, M = ba->M;
+    const size_t packed = (size_t)n * n + n + 1;
+    VIO_CUDA(ctx, ba->d_packed.reserve(packed * 8));
+    cudaStream_t st = ctx->stream;
+    ba->use_D = lm_diag != nullptr;
+    if (lm_diag) {
+        VIO_CUDA(ctx, ba->pin.reserve((6 * K + 3 * M) * 8));
+        memcpy(ba->pin.p, lm_diag, (6 * K + 3 * M) * 8);
+        VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_D.p, ba->pin.p, (6 * K + 3 * M) * 8, cudaMemcpyHostToDevice, st));
+    }
+    VIO_CUDA(ctx, cudaMemsetAsync(ba->d_packed.p, 0, packed * 8, st));
+    double* dS = ba->d_packed.as<double>(); double* drhs = dS + (size_t)n * n; double* dcost = drhs + n;
+    const int nlm = ba->lm_end - ba->lm_begin;
+    const int nb = std::max(1, (nlm * 32 + 127) / 128);
+    VIO_CUDA(ctx, ba->d_partials.reserve((size_t)(nb + 1) * 8));
+    BaDev d = make_dev(ba);
+    k_schur_warp<<<nb, 128, 0, st>>>(d, ba->lm_begin, ba->lm_end, apply_loss != 0, dS, n, drhs, ba->d_partials.as<double>());
+    VIO_LAUNCH_CHECK(ctx);
+    int rc = sum_partials(ba, nb, dcost);
+    if (rc) return rc;
+    if (n > 0) {
+        k_finish_S<<<(n * n + 255) / 256, 256, 0, st>>>(dS, n, ba->use_D ? ba->d_D.as<double>() : nullptr,
+                                                       ba->d_free_map.as<int>(), ba->K, ba->shard_rank == 0);
+        VIO_LAUNCH_CHECK(ctx);
+    }
+    ba->has_reduced = true;
+    if (S || rhs || cost) return vio360_ba_fetch_reduced_system(ba, S, rhs, cost);
+    VIO_CUDA(ctx, cudaStreamSynchronize(st));   // pinned staging of lm_diag is reused by later calls
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_reduced_system_dev(vio360_ba* ba, double** packed_dev, size_t* n_doubles) {
+    if (!ba || !packed_dev || !n_doubles) return VIO360_ERR_INVALID;
+    if (!ba->has_reduced) return vio360_fail(ba->ctx, VIO360_ERR_STATE, "no reduced system built yet");
+    const size_t n = 6 * (size_t)ba->n_free;
+    *packed_dev = ba->d_packed.as<double>();
+    *n_doubles = n * n + n + 1;
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_fetch_reduced_system(vio360_ba* ba, double* S, double* rhs, double* cost) {
+    if (!ba) return VIO360_ERR_INVALID;
+    vio360_ctx* ctx = ba->ctx;
+    if (!ba->has_reduced) return vio360_fail(ctx, VIO360_ERR_STATE, "no reduced system built yet");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t n = 6 * (size_t)ba->n_free;
+    double* dS = ba->d_packed.as<double>();
+    if (S && n) VIO_CUDA(ctx, cudaMemcpyAsync(S, dS, n * n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (rhs && n) VIO_CUDA(ctx, cudaMemcpyAsync(rhs, dS + n * n, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (cost) VIO_CUDA(ctx, cudaMemcpyAsync(cost, dS + n * n + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_chi2(vio360_ba* ba, double thr, double* chi2, uint8_t* flag) {
+    if (!ba) return VIO360_ERR_INVALID;
+    vio360_ctx* ctx = ba->ctx;
+    if (!ba->has_params) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_chi2 before ba_set_parameters");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t O = (size_t)ba->O;
+    if (O == 0) return VIO360_OK;
+    VIO_CUDA(ctx, ba->d_chi2.reserve(O * 8)); VIO_CUDA(ctx, ba->d_flag.reserve(O));
+    BaDev d = make_dev(ba);
+    k_chi2<<<(int)((O + 127) / 128), 128, 0, ctx->stream>>>(d, thr, ba->d_chi2.as<double>(), ba->d_flag.as<unsigned char>());
+    VIO_LAUNCH_CHECK(ctx);
+    if (chi2) VIO_CUDA(ctx, cudaMemcpyAsync(chi2, ba->d_chi2.p, O * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (flag) VIO_CUDA(ctx, cudaMemcpyAsync(flag, ba->d_flag.p, O, cudaMemcpyDeviceToHost, ctx->stream));
+    VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return VIO360_OK;
+}
+
+// ------------------------------------------------------------------ PnP (pose only)
+// PnPFactor::Evaluate / compute_chi_square (Factors.cpp:33-210, 212-265): same projection
+// and Jacobian as the BA factor with the point held constant and one shared pose.
+__global__ void __launch_bounds__(128) k_pnp(int N, const double* __restrict__ obs_uv, const double* __restrict__ pts,
+                                             const unsigned char* __restrict__ outlier, const double* __restrict__ posebuf,
+                                             CamConst cam, double* __restrict__ r_out, double* __restrict__ Jp_out,
+                                             unsigned char* __restrict__ valid, double* __restrict__ chi2,
+                                             double* __restrict__ partials /* [gridDim.x][28] */) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    double acc[28];
+#pragma unroll
+    for (int j = 0; j < 28; ++j) acc[j] = 0.0;
+    if (i < N) {
+        double pose[kPoseStride];
+#pragma unroll
+        for (int j = 0; j < kPoseStride; ++j) pose[j] = __ldg(posebuf + j);
+        const double Pw[3] = {pts[3 * (size_t)i], pts[3 * (size_t)i + 1], pts[3 * (size_t)i + 2]};
+        const double u = obs_uv[2 * (size_t)i], v = obs_uv[2 * (size_t)i + 1];
+        const bool outl = outlier && outlier[i];
+        ObsProj p;
+        obs_project(pose, Pw, u, v, cam, p);
+        const bool bad = !outl && p.branch == 1;        // Evaluate returns false, residual untouched (:74-80)
+        double r[2] = {0.0, 0.0}, F[12], E[6];
+        double cost = 0.0;
+        if (!bad) cost = obs_evaluate<true>(pose, Pw, u, v, outl, cam, true, r, F, E);
+        else { for (int j = 0; j < 12; ++j) F[j] = 0.0; }
+        r_out[2 * (size_t)i] = r[0]; r_out[2 * (size_t)i + 1] = r[1];
+        if (Jp_out) for (int j = 0; j < 12; ++j) Jp_out[12 * (size_t)i + j] = F[j];
+        valid[i] = bad ? 0 : 1;
+        if (chi2) {   // ignores the outlier flag (:212-265); DBL_MAX for a point at the centre
+            double c;
+            if (p.branch == 1) c = 1.7976931348623157e308;
+            else {
+                const double a0 = p.du * cam.info[0] + p.dv * cam.info[2], a1 = p.du * cam.info[1] + p.dv * cam.info[3];
+                c = a0 * p.du + a1 * p.dv;
+            }
+            chi2[i] = c;
+        }
+        if (!bad) {
+            int t = 0;
+#pragma unroll
+            for (int a = 0; a < 6; ++a)
+#pragma unroll
+                for (int b = a; b < 6; ++b) acc[t++] = F[a] * F[b] + F[6 + a] * F[6 + b];
+#pragma unroll
+            for (int a = 0; a < 6; ++a) acc[21 + a] = F[a] * r[0] + F[6 + a] * r[1];
+            acc[27] = cost;
+        }
+    }
+    __shared__ double sm[4][28];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int j = 0; j < 28; ++j) {
+        const double s = warp_sum(acc[j]);
+        if (lane == 0) sm[w][j] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x < 28)
+        partials[28 * (size_t)blockIdx.x + threadIdx.x] = sm[0][threadIdx.x] + sm[1][threadIdx.x] + sm[2][threadIdx.x] + sm[3][threadIdx.x];
+}
+
+__global__ void k_pnp_reduce(const double* __restrict__ partials, int nb, double* __restrict__ out28) {
+    const int j = threadIdx.x;
+    if (j >= 28) return;
+    double s = 0.0;
+    for (int b = 0; b < nb; ++b) s += partials[28 * (size_t)b + j];
+    out28[j] = s;
+}
+
+extern "C" int vio360_pnp_evaluate(vio360_ctx* ctx, int N, const double* obs_uv, const double* world_pts,
+                                   const uint8_t* outlier, const double* T_wb_init, const double* T_cb, double cols,
+                                   double rows, const double* info, double huber_delta, const double* pose_delta,
+                                   double* r, double* Jp, uint8_t* valid, double* H, double* b, double* cost,
+                                   double* chi2) {
+    if (!ctx) return VIO360_ERR_INVALID;
+    if (N <= 0 || !obs_uv || !world_pts || !T_wb_init || !T_cb || !info || !pose_delta || !r || !valid)
+        return vio360_fail(ctx, VIO360_ERR_INVALID, "pnp_evaluate: bad arguments");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const size_t n = (size_t)N;
+    const int nb = (N + 127) / 128;
+    // one scratch allocation: inputs | outputs
+    const size_t in_d = n * 2 + n * 3 + 16 + 16 + 6;          // doubles
+    const size_t out_d = n * 2 + n * 12 + n + (size_t)nb * 28 + 28 + kPoseStride;
+    DevBuf scratch, flags;
+    VIO_CUDA(ctx, scratch.reserve((in_d + out_d) * 8));
+    VIO_CUDA(ctx, flags.reserve(n * 2));
+    double* d_obs = scratch.as<double>(); double* d_pts = d_obs + n * 2; double* d_Twb = d_pts + n * 3;
+    double* d_Tcb = d_Twb + 16; double* d_xi = d_Tcb + 16;
+    double* d_r = d_xi + 6; double* d_J = d_r + n * 2; double* d_chi = d_J + n * 12; double* d_part = d_chi + n;
+    double* d_out28 = d_part + (size_t)nb * 28; double* d_pose = d_out28 + 28;
+    unsigned char* d_outl = flags.as<unsigned char>(); unsigned char* d_valid = d_outl + n;
+    auto cleanup = [&]() { scratch.release(); flags.release(); };
+#define PNP_CUDA(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { cleanup(); return vio360_fail(ctx, VIO360_ERR_CUDA, "%s -> %s", #call, cudaGetErrorString(e_)); } } while (0)
+    PNP_CUDA(cudaMemcpyAsync(d_obs, obs_uv, n * 16, cudaMemcpyHostToDevice, st));
+    PNP_CUDA(cudaMemcpyAsync(d_pts, world_pts, n * 24, cudaMemcpyHostToDevice, st));
+    PNP_CUDA(cudaMemcpyAsync(d_Twb, T_wb_init, 128, cudaMemcpyHostToDevice, st));
+    PNP_CUDA(cudaMemcpyAsync(d_Tcb, T_cb, 128, cudaMemcpyHostToDevice, st));
+    PNP_CUDA(cudaMemcpyAsync(d_xi, pose_delta, 48, cudaMemcpyHostToDevice, st));
+    if (outlier) PNP_CUDA(cudaMemcpyAsync(d_outl, outlier, n, cudaMemcpyHostToDevice, st));
+    CamConst cam;
+    cam_const_init(cam, cols, rows, info, T_cb, huber_delta);
+    k_pose_prepare<<<1, 32, 0, st>>>(1, d_Twb, d_Tcb, d_xi, d_pose);
+    ctx->launches++;
+    k_pnp<<<nb, 128, 0, st>>>(N, d_obs, d_pts, outlier ? d_outl : nullptr, d_pose, cam, d_r, d_J, d_valid, d_chi, d_part);
+    ctx->launches++;
+    k_pnp_reduce<<<1, 32, 0, st>>>(d_part, nb, d_out28);
+    ctx->launches++;
+    PNP_CUDA(cudaGetLastError());
+    double h28[28];
+    PNP_CUDA(cudaMemcpyAsync(r, d_r, n * 16, cudaMemcpyDeviceToHost, st));
+    if (Jp) PNP_CUDA(cudaMemcpyAsync(Jp, d_J, n * 96, cudaMemcpyDeviceToHost, st));
+    if (chi2) PNP_CUDA(cudaMemcpyAsync(chi2, d_chi, n * 8, cudaMemcpyDeviceToHost, st));
+    PNP_CUDA(cudaMemcpyAsync(valid, d_valid, n, cudaMemcpyDeviceToHost, st));
+    PNP_CUDA(cudaMemcpyAsync(h28, d_out28, sizeof(h28), cudaMemcpyDeviceToHost, st));
+    PNP_CUDA(cudaStreamSynchronize(st));
+#undef PNP_CUDA
+    cleanup();
+    if (H) {
+        int t = 0;
+        for (int a = 0; a < 6; ++a) for (int c = a; c < 6; ++c) { H[a * 6 + c] = h28[t]; H[c * 6 + a] = h28[t]; ++t; }
+    }
+    if (b) for (int a = 0; a < 6; ++a) b[a] = h28[21 + a];
+    if (cost) *cost = h28[27];
+    return VIO360_OK;
+}

@@ -1,0 +1,89 @@
+// common.cuh -- context object and error plumbing shared by all translation units of
+// libvio360_cuda.so.  No torch types, no CPU fallbacks.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/vio360.h"
+
+struct vio360_fe_state;  // fe.cu
+
+struct vio360_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaDeviceProp prop{};
+    int num_sms = 148;
+    long long launches = 0;
+    std::string err;
+    vio360_fe_state* fe = nullptr;
+    // small pinned + device scratch used to ship descriptor tables
+    void* pinned = nullptr;
+    size_t pinned_bytes = 0;
+};
+
+inline int vio360_fail(vio360_ctx* ctx, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->err = buf;
+    return code;
+}
+
+#define VIO_CUDA(ctx, call)                                                              \
+    do {                                                                                 \
+        cudaError_t e_ = (call);                                                         \
+        if (e_ != cudaSuccess)                                                           \
+            return vio360_fail((ctx), VIO360_ERR_CUDA, "%s:%d %s -> %s", __FILE__, __LINE__, \
+                               #call, cudaGetErrorString(e_));                           \
+    } while (0)
+
+#define VIO_LAUNCH_CHECK(ctx)                                                            \
+    do {                                                                                 \
+        (ctx)->launches++;                                                               \
+        cudaError_t e_ = cudaGetLastError();                                             \
+        if (e_ != cudaSuccess)                                                           \
+            return vio360_fail((ctx), VIO360_ERR_CUDA, "%s:%d kernel launch -> %s", __FILE__, \
+                               __LINE__, cudaGetErrorString(e_));                        \
+    } while (0)
+
+// RAII-less device buffer helper (explicit free; sized lazily)
+struct DevBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= bytes) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; bytes = 0;
+        cudaError_t e = cudaMalloc(&p, n);
+        if (e == cudaSuccess) bytes = n;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+    template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+struct PinBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    cudaError_t reserve(size_t n) {
+        if (n <= bytes) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr; bytes = 0;
+        cudaError_t e = cudaMallocHost(&p, n);
+        if (e == cudaSuccess) bytes = n;
+        return e;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; bytes = 0; }
+    template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+void vio360_fe_release(vio360_ctx* ctx);  // fe.cu

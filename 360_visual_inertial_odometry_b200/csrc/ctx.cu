@@ -1,0 +1,104 @@
+// ctx.cu -- context lifetime, stream, launch accounting and the FMA-peak probe.
+#include "common.cuh"
+
+static std::string g_create_error;
+
+extern "C" int vio360_version(void) { return 100; }
+
+extern "C" const char* vio360_last_error(const vio360_ctx* ctx) {
+    return ctx ? ctx->err.c_str() : g_create_error.c_str();
+}
+
+extern "C" int vio360_create(int device, vio360_ctx** out) {
+    if (!out) { g_create_error = "vio360_create: out is NULL"; return VIO360_ERR_INVALID; }
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count <= 0) {
+        g_create_error = std::string("vio360_create: no CUDA device (") + cudaGetErrorString(e) +
+                         "); this library has no CPU fallback";
+        return VIO360_ERR_CUDA;
+    }
+    if (device < 0 || device >= count) { g_create_error = "vio360_create: bad device index"; return VIO360_ERR_INVALID; }
+    vio360_ctx* ctx = new vio360_ctx();
+    ctx->device = device;
+    if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaGetDeviceProperties(&ctx->prop, device)) != cudaSuccess ||
+        (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+        g_create_error = std::string("vio360_create: ") + cudaGetErrorString(e);
+        delete ctx;
+        return VIO360_ERR_CUDA;
+    }
+    if (ctx->prop.major < 10) {
+        g_create_error = "vio360_create: device is not sm_100-class (kernels are built for sm_100a only)";
+        cudaStreamDestroy(ctx->stream);
+        delete ctx;
+        return VIO360_ERR_CUDA;
+    }
+    ctx->num_sms = ctx->prop.multiProcessorCount;
+    *out = ctx;
+    return VIO360_OK;
+}
+
+extern "C" void vio360_destroy(vio360_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    vio360_fe_release(ctx);
+    if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+extern "C" int vio360_synchronize(vio360_ctx* ctx) {
+    if (!ctx) return VIO360_ERR_INVALID;
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return VIO360_OK;
+}
+
+extern "C" void* vio360_stream(vio360_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+extern "C" long long vio360_launch_count(const vio360_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+// ---- FMA pipe probe: 8 independent dependent-FMA chains per thread, all SMs busy
+template <typename T>
+__global__ void __launch_bounds__(256) k_fma_probe(T* out, int iters, T a, T b) {
+    T x0 = a + threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+    for (int i = 0; i < iters; ++i) {
+        x0 = x0 * a + b; x1 = x1 * a + b; x2 = x2 * a + b; x3 = x3 * a + b;
+        x4 = x4 * a + b; x5 = x5 * a + b; x6 = x6 * a + b; x7 = x7 * a + b;
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+}
+
+template <typename T>
+static int probe(vio360_ctx* ctx, double* tflops) {
+    const int blocks = ctx->num_sms * 8, threads = 256, iters = 4096;
+    T* d = nullptr;
+    VIO_CUDA(ctx, cudaMalloc(&d, sizeof(T) * blocks * threads));
+    cudaEvent_t e0, e1;
+    VIO_CUDA(ctx, cudaEventCreate(&e0)); VIO_CUDA(ctx, cudaEventCreate(&e1));
+    double best = 0.0;
+    for (int rep = 0; rep < 5; ++rep) {
+        VIO_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
+        k_fma_probe<T><<<blocks, threads, 0, ctx->stream>>>(d, iters, (T)0.999, (T)0.001);
+        ctx->launches++;
+        VIO_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
+        VIO_CUDA(ctx, cudaEventSynchronize(e1));
+        float ms = 0;
+        VIO_CUDA(ctx, cudaEventElapsedTime(&ms, e0, e1));
+        const double flops = 2.0 * 8.0 * iters * (double)blocks * threads;
+        if (rep > 0 && ms > 0) best = std::max(best, flops / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+    *tflops = best;
+    return VIO360_OK;
+}
+
+extern "C" int vio360_probe_fma_peak(vio360_ctx* ctx, double* fp64_tflops, double* fp32_tflops) {
+    if (!ctx) return VIO360_ERR_INVALID;
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc;
+    if (fp64_tflops && (rc = probe<double>(ctx, fp64_tflops))) return rc;
+    if (fp32_tflops && (rc = probe<float>(ctx, fp32_tflops))) return rc;
+    return VIO360_OK;
+}

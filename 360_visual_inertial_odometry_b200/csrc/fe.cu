@@ -1,0 +1,474 @@
+// fe.cu -- path A host side: device pyramid cache, batched tracking and detection.
+// Compiled with --fmad=false (see fe_lk.cuh / fe_detect.cuh); explicit fmaf() calls mark
+// the places where OpenCV's dispatched code fuses.
+#include <algorithm>
+#include <cub/cub.cuh>
+
+#include "common.cuh"
+#include "fe_detect.cuh"
+#include "fe_lk.cuh"
+#include "fe_pyr.cuh"
+
+using namespace vio360;
+
+struct FeSlot {
+    uint64_t key = 0;
+    uint64_t last_use = 0;
+    uint64_t batch_tag = 0;      // slot is pinned by the batch with this tag
+    bool has_pyramid = false;
+    DevBuf mem;                  // levels 0..L-1 (level 0 unused when aliased)
+    uint8_t* own[kMaxLevels] = {};
+    const uint8_t* p[kMaxLevels] = {};
+    int pitch[kMaxLevels] = {};
+};
+
+struct vio360_fe_state {
+    bool configured = false;
+    int W = 0, H = 0, nlevels = 0, win = 21, max_iters = 30;
+    double eps2 = 0, min_eig = 0;
+    float polar_ratio = 0.15f;
+    int margin = 20, max_points = 0, max_batch = 0;
+    int lw[kMaxLevels] = {}, lh[kMaxLevels] = {}, lpitch[kMaxLevels] = {};
+    size_t loff[kMaxLevels] = {}, slot_bytes = 0;
+    std::vector<FeSlot> slots;
+    std::unordered_map<uint64_t, int> by_key;
+    uint64_t clock = 0, batch_tag = 0;
+    // tracking pools
+    DevBuf d_jobs, d_pyrjobs, d_pts_in, d_pts_out, d_status, d_err, d_keep;
+    PinBuf h_jobs, h_pyrjobs, h_pts_in, h_out;
+    // detection pools
+    DevBuf d_djobs, d_eig, d_mask, d_small, d_cand, d_cand_sorted, d_grid, d_cub, d_corners;
+    PinBuf h_djobs, h_dout;
+    int det_batch_cap = 0, max_cand = 1 << 18;
+    size_t cub_bytes = 0;
+};
+
+void vio360_fe_release(vio360_ctx* ctx) {
+    vio360_fe_state* s = ctx->fe;
+    if (!s) return;
+    for (auto& sl : s->slots) sl.mem.release();
+    DevBuf* db[] = {&s->d_jobs, &s->d_pyrjobs, &s->d_pts_in, &s->d_pts_out, &s->d_status, &s->d_err, &s->d_keep,
+                    &s->d_djobs, &s->d_eig, &s->d_mask, &s->d_small, &s->d_cand, &s->d_cand_sorted, &s->d_grid,
+                    &s->d_cub, &s->d_corners};
+    for (DevBuf* b : db) b->release();
+    PinBuf* pb[] = {&s->h_jobs, &s->h_pyrjobs, &s->h_pts_in, &s->h_out, &s->h_djobs, &s->h_dout};
+    for (PinBuf* b : pb) b->release();
+    delete s;
+    ctx->fe = nullptr;
+}
+
+static inline int align_up(int v, int a) { return (v + a - 1) / a * a; }
+
+extern "C" int vio360_fe_configure(vio360_ctx* ctx, int width, int height, int max_level, int win, int max_iters,
+                                   double eps, double min_eig_thr, float polar_ratio, int boundary_margin,
+                                   int max_points, int max_batch) {
+    if (!ctx) return VIO360_ERR_INVALID;
+    if (width < 32 || height < 32 || max_level < 0 || max_level >= kMaxLevels || max_points <= 0 || max_batch <= 0)
+        return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_configure: bad size/level arguments");
+    if (win != kWin)
+        return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_configure: only the reference's 21x21 window is built (FeatureTracker.cpp:33)");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    vio360_fe_release(ctx);
+    vio360_fe_state* s = new vio360_fe_state();
+    ctx->fe = s;
+    s->W = width; s->H = height; s->win = win;
+    // calcOpticalFlowPyrLK: maxCount clamped to [0,100], epsilon to [0,10] then squared
+    s->max_iters = std::min(std::max(max_iters, 0), 100);
+    const double e = std::min(std::max(eps, 0.0), 10.0);
+    s->eps2 = e * e;
+    s->min_eig = min_eig_thr;
+    s->polar_ratio = polar_ratio; s->margin = boundary_margin;
+    s->max_points = max_points; s->max_batch = max_batch;
+    // buildOpticalFlowPyramid: stop before a level that does not exceed the window
+    int w = width, h = height, L = 0;
+    size_t off = 0;
+    for (int l = 0; l <= max_level; ++l) {
+        s->lw[l] = w; s->lh[l] = h; s->lpitch[l] = align_up(w, 128);
+        s->loff[l] = off; off += (size_t)s->lpitch[l] * h;
+        L = l + 1;
+        const int nw = (w + 1) / 2, nh = (h + 1) / 2;
+        if (nw <= win || nh <= win) break;
+        w = nw; h = nh;
+    }
+    s->nlevels = L; s->slot_bytes = off;
+    s->slots.resize((size_t)2 * max_batch + 2);
+    for (auto& sl : s->slots) {
+        VIO_CUDA(ctx, sl.mem.reserve(s->slot_bytes));
+        for (int l = 0; l < L; ++l) { sl.own[l] = sl.mem.as<uint8_t>() + s->loff[l]; sl.p[l] = sl.own[l]; sl.pitch[l] = s->lpitch[l]; }
+    }
+    const size_t np = (size_t)max_points * max_batch;
+    VIO_CUDA(ctx, s->d_jobs.reserve(sizeof(TrackJobDev) * (size_t)max_batch));
+    VIO_CUDA(ctx, s->h_jobs.reserve(sizeof(TrackJobDev) * (size_t)max_batch));
+    VIO_CUDA(ctx, s->d_pyrjobs.reserve(sizeof(PyrJob) * (size_t)2 * max_batch * kMaxLevels));
+    VIO_CUDA(ctx, s->h_pyrjobs.reserve(sizeof(PyrJob) * (size_t)2 * max_batch * kMaxLevels));
+    VIO_CUDA(ctx, s->d_pts_in.reserve(np * 8)); VIO_CUDA(ctx, s->d_pts_out.reserve(np * 8));
+    VIO_CUDA(ctx, s->d_status.reserve(np)); VIO_CUDA(ctx, s->d_err.reserve(np * 4)); VIO_CUDA(ctx, s->d_keep.reserve(np));
+    VIO_CUDA(ctx, s->h_pts_in.reserve(np * 8));
+    VIO_CUDA(ctx, s->h_out.reserve(np * (8 + 1 + 4 + 1)));
+    s->configured = true;
+    return VIO360_OK;
+}
+
+// ---- pyramid cache -------------------------------------------------------------------
+static int acquire_slot(vio360_ctx* ctx, uint64_t key, bool* hit, int* out_idx) {
+    vio360_fe_state* s = ctx->fe;
+    *hit = false;
+    if (key != 0) {
+        auto it = s->by_key.find(key);
+        if (it != s->by_key.end()) {
+            FeSlot& sl = s->slots[it->second];
+            sl.last_use = ++s->clock; sl.batch_tag = s->batch_tag;
+            *hit = true; *out_idx = it->second;
+            return VIO360_OK;
+        }
+    }
+    int best = -1;
+    for (int i = 0; i < (int)s->slots.size(); ++i) {
+        const FeSlot& sl = s->slots[i];
+        if (sl.batch_tag == s->batch_tag) continue;   // in use by this batch
+        if (best < 0 || sl.last_use < s->slots[best].last_use) best = i;
+    }
+    if (best < 0) return vio360_fail(ctx, VIO360_ERR_STATE, "pyramid cache exhausted (batch larger than max_batch?)");
+    FeSlot& sl = s->slots[best];
+    if (sl.key != 0) s->by_key.erase(sl.key);
+    sl.key = key; sl.last_use = ++s->clock; sl.batch_tag = s->batch_tag; sl.has_pyramid = false;
+    sl.p[0] = sl.own[0]; sl.pitch[0] = s->lpitch[0];
+    if (key != 0) s->by_key[key] = best;
+    *out_idx = best;
+    return VIO360_OK;
+}
+
+static int load_frame(vio360_ctx* ctx, int slot, const uint8_t* img, size_t pitch, int mem_space) {
+    vio360_fe_state* s = ctx->fe;
+    FeSlot& sl = s->slots[slot];
+    if (mem_space == VIO360_MEM_DEVICE) {
+        if ((reinterpret_cast<uintptr_t>(img) & 3) == 0 && (pitch & 3) == 0) {
+            sl.p[0] = img; sl.pitch[0] = (int)pitch;   // alias: no copy of level 0
+            return VIO360_OK;
+        }
+        VIO_CUDA(ctx, cudaMemcpy2DAsync(sl.own[0], s->lpitch[0], img, pitch, s->W, s->H, cudaMemcpyDeviceToDevice, ctx->stream));
+    } else {
+        VIO_CUDA(ctx, cudaMemcpy2DAsync(sl.own[0], s->lpitch[0], img, pitch, s->W, s->H, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    sl.p[0] = sl.own[0]; sl.pitch[0] = s->lpitch[0];
+    return VIO360_OK;
+}
+
+// build levels 1..L-1 for the listed slots, one launch per level for the whole batch
+static int build_pyramids(vio360_ctx* ctx, const std::vector<int>& todo) {
+    vio360_fe_state* s = ctx->fe;
+    if (todo.empty() || s->nlevels <= 1) { for (int i : todo) s->slots[i].has_pyramid = true; return VIO360_OK; }
+    const int nb = (int)todo.size();
+    PyrJob* hj = s->h_pyrjobs.as<PyrJob>();
+    for (int l = 0; l + 1 < s->nlevels; ++l)
+        for (int b = 0; b < nb; ++b) {
+            FeSlot& sl = s->slots[todo[b]];
+            PyrJob& j = hj[(size_t)l * nb + b];
+            j.src = sl.p[l]; j.spitch = sl.pitch[l]; j.dst = sl.own[l + 1]; j.dpitch = s->lpitch[l + 1];
+        }
+    const size_t bytes = sizeof(PyrJob) * (size_t)nb * (s->nlevels - 1);
+    VIO_CUDA(ctx, cudaMemcpyAsync(s->d_pyrjobs.p, hj, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    for (int l = 0; l + 1 < s->nlevels; ++l) {
+        const int dw = s->lw[l + 1], dh = s->lh[l + 1];
+        dim3 grid((dw + kPyrTW - 1) / kPyrTW, (dh + kPyrTH - 1) / kPyrTH, nb);
+        k_pyr_down<<<grid, 256, 0, ctx->stream>>>(s->d_pyrjobs.as<PyrJob>() + (size_t)l * nb, s->lw[l], s->lh[l], dw, dh);
+        VIO_LAUNCH_CHECK(ctx);
+    }
+    for (int i : todo) s->slots[i].has_pyramid = true;
+    return VIO360_OK;
+}
+
+static void fill_levels(const vio360_fe_state* s, const FeSlot& sl, FrameLevels& f) {
+    for (int l = 0; l < kMaxLevels; ++l) { f.p[l] = l < s->nlevels ? sl.p[l] : nullptr; f.pitch[l] = l < s->nlevels ? sl.pitch[l] : 0; }
+}
+
+static LkParams lk_params(const vio360_fe_state* s) {
+    LkParams P;
+    P.nlevels = s->nlevels;
+    for (int l = 0; l < kMaxLevels; ++l) { P.w[l] = s->lw[l]; P.h[l] = s->lh[l]; }
+    P.max_iters = s->max_iters; P.eps2 = s->eps2; P.min_eig = s->min_eig;
+    P.polar_thr = s->polar_ratio; P.margin = (float)s->margin;
+    return P;
+}
+
+extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jobs, int n_jobs, int mem_space) {
+    if (!ctx) return VIO360_ERR_INVALID;
+    vio360_fe_state* s = ctx->fe;
+    if (!s || !s->configured) return vio360_fail(ctx, VIO360_ERR_STATE, "fe_track before fe_configure");
+    if (!jobs || n_jobs < 0 || n_jobs > s->max_batch) return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_track_batch: bad job count");
+    if (n_jobs == 0) return VIO360_OK;
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    // pinned staging is shared between calls: wait for the previous call's copies
+    VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    s->batch_tag++;
+    std::vector<int> todo;
+    TrackJobDev* hj = s->h_jobs.as<TrackJobDev>();
+    int max_n = 0;
+    size_t off = 0;
+    for (int b = 0; b < n_jobs; ++b) {
+        const vio360_track_job& j = jobs[b];
+        if (j.n < 0 || j.n > s->max_points) return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_track_batch: job %d has %d points (max %d)", b, j.n, s->max_points);
+        if (!j.prev || !j.cur || (j.n > 0 && (!j.prev_xy || !j.cur_xy || !j.status)))
+            return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_track_batch: job %d has a null pointer", b);
+        if (j.prev_pitch < (size_t)s->W || j.cur_pitch < (size_t)s->W) return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_track_batch: pitch < width");
+        int sp, sc; bool hit;
+        const uint8_t* imgs[2] = {j.prev, j.cur};
+        const size_t pitches[2] = {j.prev_pitch, j.cur_pitch};
+        const uint64_t keys[2] = {j.prev_key, j.cur_key};
+        int idx[2];
+        for (int f = 0; f < 2; ++f) {
+            int rc = acquire_slot(ctx, keys[f], &hit, &idx[f]);
+            if (rc) return rc;
+            if (!hit) {
+                rc = load_frame(ctx, idx[f], imgs[f], pitches[f], mem_space);
+                if (rc) return rc;
+            }
+            if (!s->slots[idx[f]].has_pyramid && std::find(todo.begin(), todo.end(), idx[f]) == todo.end()) todo.push_back(idx[f]);
+        }
+        sp = idx[0]; sc = idx[1];
+        TrackJobDev& d = hj[b];
+        fill_levels(s, s->slots[sp], d.prev); fill_levels(s, s->slots[sc], d.cur);
+        d.n = j.n;
+        if (mem_space == VIO360_MEM_DEVICE) {
+            d.prev_xy = j.prev_xy; d.cur_xy = j.cur_xy; d.status = j.status; d.err = j.err; d.keep = j.keep;
+        } else {
+            d.prev_xy = s->d_pts_in.as<float>() + 2 * off; d.cur_xy = s->d_pts_out.as<float>() + 2 * off;
+            d.status = s->d_status.as<uint8_t>() + off; d.err = j.err ? s->d_err.as<float>() + off : nullptr;
+            d.keep = j.keep ? s->d_keep.as<uint8_t>() + off : nullptr;
+            if (j.n) memcpy(s->h_pts_in.as<float>() + 2 * off, j.prev_xy, (size_t)j.n * 8);
+        }
+        off += (size_t)j.n;
+        max_n = std::max(max_n, j.n);
+    }
+    int rc = build_pyramids(ctx, todo);
+    if (rc) return rc;
+    if (max_n == 0) return VIO360_OK;
+    cudaStream_t st = ctx->stream;
+    VIO_CUDA(ctx, cudaMemcpyAsync(s->d_jobs.p, hj, sizeof(TrackJobDev) * (size_t)n_jobs, cudaMemcpyHostToDevice, st));
+    if (mem_space == VIO360_MEM_HOST)
+        VIO_CUDA(ctx, cudaMemcpyAsync(s->d_pts_in.p, s->h_pts_in.p, off * 8, cudaMemcpyHostToDevice, st));
+    dim3 grid((max_n + kLkWarps - 1) / kLkWarps, n_jobs);
+    k_lk_track<<<grid, kLkWarps * 32, 0, st>>>(s->d_jobs.as<TrackJobDev>(), lk_params(s));
+    VIO_LAUNCH_CHECK(ctx);
+    if (mem_space == VIO360_MEM_HOST) {
+        // one pinned block: [xy off*8 | err off*4 | status off | keep off]
+        uint8_t* ho = s->h_out.as<uint8_t>();
+        VIO_CUDA(ctx, cudaMemcpyAsync(ho, s->d_pts_out.p, off * 8, cudaMemcpyDeviceToHost, st));
+        VIO_CUDA(ctx, cudaMemcpyAsync(ho + off * 8, s->d_err.p, off * 4, cudaMemcpyDeviceToHost, st));
+        VIO_CUDA(ctx, cudaMemcpyAsync(ho + off * 12, s->d_status.p, off, cudaMemcpyDeviceToHost, st));
+        VIO_CUDA(ctx, cudaMemcpyAsync(ho + off * 13, s->d_keep.p, off, cudaMemcpyDeviceToHost, st));
+        VIO_CUDA(ctx, cudaStreamSynchronize(st));
+        size_t o = 0;
+        for (int b = 0; b < n_jobs; ++b) {
+            const vio360_track_job& j = jobs[b];
+            if (j.n) {
+                memcpy(j.cur_xy, ho + o * 8, (size_t)j.n * 8);
+                memcpy(j.status, ho + off * 12 + o, (size_t)j.n);
+                if (j.err) memcpy(j.err, ho + off * 8 + o * 4, (size_t)j.n * 4);
+                if (j.keep) memcpy(j.keep, ho + off * 13 + o, (size_t)j.n);
+            }
+            o += (size_t)j.n;
+        }
+    }
+    return VIO360_OK;
+}
+
+extern "C" int vio360_fe_track(vio360_ctx* ctx, const uint8_t* prev, size_t prev_pitch, uint64_t prev_key,
+                               const uint8_t* cur, size_t cur_pitch, uint64_t cur_key, const float* prev_xy, int n,
+                               float* cur_xy, uint8_t* status, float* err, int* n_tracked) {
+    if (!ctx) return VIO360_ERR_INVALID;
+    if (n == 0) { if (n_tracked) *n_tracked = 0; return VIO360_OK; }   // FeatureTracker.cpp:233-235
+    vio360_track_job j;
+    j.prev = prev; j.prev_pitch = prev_pitch; j.prev_key = prev_key;
+    j.cur = cur; j.cur_pitch = cur_pitch; j.cur_key = cur_key;
+    j.prev_xy = prev_xy; j.n = n; j.cur_xy = cur_xy; j.status = status; j.err = err; j.keep = nullptr;
+    const int rc = vio360_fe_track_batch(ctx, &j, 1, VIO360_MEM_HOST);
+    if (rc) return rc;
+    if (n_tracked) { int c = 0; for (int i = 0; i < n; ++i) c += status[i] != 0; *n_tracked = c; }
+    return VIO360_OK;
+}
+
+extern "C" int vio360_fe_pyramid(vio360_ctx* ctx, const uint8_t* img, size_t pitch, int n_levels, uint8_t* const* out,
+                                 const size_t* out_pitch) {
+    if (!ctx) return VIO360_ERR_INVALID;
+    vio360_fe_state* s = ctx->fe;
+    if (!s || !s->configured) return vio360_fail(ctx, VIO360_ERR_STATE, "fe_pyramid before fe_configure");
+    if (!img || !out || !out_pitch || n_levels < 1 || n_levels > s->nlevels || pitch < (size_t)s->W)
+        return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_pyramid: bad arguments");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    s->batch_tag++;
+    bool hit; int idx;
+    int rc = acquire_slot(ctx, 0, &hit, &idx);
+    if (rc) return rc;
+    if ((rc = load_frame(ctx, idx, img, pitch, VIO360_MEM_HOST))) return rc;
+    if ((rc = build_pyramids(ctx, std::vector<int>{idx}))) return rc;
+    const FeSlot& sl = s->slots[idx];
+    for (int l = 0; l < n_levels; ++l)
+        VIO_CUDA(ctx, cudaMemcpy2DAsync(out[l], out_pitch[l], sl.p[l], sl.pitch[l], s->lw[l], s->lh[l], cudaMemcpyDeviceToHost, ctx->stream));
+    VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return VIO360_OK;
+}
+
+// ---- detection -----------------------------------------------------------------------
+static int ensure_detect_pools(vio360_ctx* ctx, int n_jobs, int max_corners) {
+    vio360_fe_state* s = ctx->fe;
+    const size_t WH = (size_t)s->W * s->H;
+    if (n_jobs > s->det_batch_cap) {
+        VIO_CUDA(ctx, s->d_eig.reserve(WH * 4 * n_jobs));
+        VIO_CUDA(ctx, s->d_cand.reserve((size_t)s->max_cand * 8 * n_jobs));
+        VIO_CUDA(ctx, s->d_cand_sorted.reserve((size_t)s->max_cand * 8 * n_jobs));
+        VIO_CUDA(ctx, s->d_small.reserve(16 * (size_t)n_jobs));
+        VIO_CUDA(ctx, s->d_djobs.reserve(sizeof(DetectJobDev) * (size_t)n_jobs));
+        VIO_CUDA(ctx, s->h_djobs.reserve(sizeof(DetectJobDev) * (size_t)n_jobs));
+        size_t tb = 0;
+        cub::DeviceRadixSort::SortKeysDescending(nullptr, tb, (const unsigned long long*)nullptr, (unsigned long long*)nullptr, s->max_cand);
+        s->cub_bytes = tb;
+        VIO_CUDA(ctx, s->d_cub.reserve(tb));
+        s->det_batch_cap = n_jobs;
+    }
+    const size_t cap = (size_t)(max_corners > 0 ? max_corners : s->max_cand);
+    VIO_CUDA(ctx, s->d_corners.reserve(cap * 8 * n_jobs));
+    VIO_CUDA(ctx, s->h_dout.reserve(cap * 8 * n_jobs + 16 * (size_t)n_jobs));
+    return VIO360_OK;
+}
+
+static DetectParams detect_params(const vio360_fe_state* s) {
+    DetectParams P;
+    P.W = s->W; P.H = s->H;
+    P.top_rows = (int)(s->H * s->polar_ratio);                    // Camera.cpp:104
+    P.bottom_start = (int)(s->H * (1.0f - s->polar_ratio));       // Camera.cpp:105
+    P.margin = s->margin; P.max_cand = s->max_cand;
+    return P;
+}
+
+extern "C" int vio360_fe_detect_batch(vio360_ctx* ctx, const vio360_detect_job* jobs, int n_jobs, int max_corners,
+                                      double quality, double min_dist, int mem_space) {
+    if (!ctx) return VIO360_ERR_INVALID;
+    vio360_fe_state* s = ctx->fe;
+    if (!s || !s->configured) return vio360_fail(ctx, VIO360_ERR_STATE, "fe_detect before fe_configure");
+    if (!jobs || n_jobs < 0 || n_jobs > s->max_batch) return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_detect_batch: bad job count");
+    if (n_jobs == 0) return VIO360_OK;
+    if (max_corners > s->max_cand) return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_detect_batch: max_corners too large");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    int rc = ensure_detect_pools(ctx, n_jobs, max_corners);
+    if (rc) return rc;
+    cudaStream_t st = ctx->stream;
+    const size_t WH = (size_t)s->W * s->H;
+    const size_t cap = (size_t)(max_corners > 0 ? max_corners : s->max_cand);
+    const int cell = min_dist >= 1.0 ? (int)lrint(min_dist) : 1;
+    const int gw = (s->W + cell - 1) / cell, gh = (s->H + cell - 1) / cell;
+    const size_t grid_ints = min_dist >= 1.0 ? (size_t)gw * gh * (1 + kCellCap) : 1;
+    VIO_CUDA(ctx, s->d_grid.reserve(grid_ints * 4 * n_jobs));
+    VIO_CUDA(ctx, cudaMemsetAsync(s->d_grid.p, 0, grid_ints * 4 * n_jobs, st));
+    VIO_CUDA(ctx, cudaMemsetAsync(s->d_small.p, 0, 16 * (size_t)n_jobs, st));
+    s->batch_tag++;
+    bool any_mask = false;
+    for (int b = 0; b < n_jobs; ++b) any_mask = any_mask || jobs[b].mask;
+    if (any_mask && mem_space == VIO360_MEM_HOST) VIO_CUDA(ctx, s->d_mask.reserve(WH * n_jobs));
+    DetectJobDev* hj = s->h_djobs.as<DetectJobDev>();
+    for (int b = 0; b < n_jobs; ++b) {
+        const vio360_detect_job& j = jobs[b];
+        if (!j.img || !j.out_xy || !j.out_n || j.pitch < (size_t)s->W) return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_detect_batch: job %d invalid", b);
+        bool hit; int idx;
+        if ((rc = acquire_slot(ctx, j.key, &hit, &idx))) return rc;
+        if (!hit && (rc = load_frame(ctx, idx, j.img, j.pitch, mem_space))) return rc;
+        DetectJobDev& d = hj[b];
+        d.img = s->slots[idx].p[0]; d.pitch = s->slots[idx].pitch[0];
+        d.mask = nullptr; d.mask_pitch = 0;
+        if (j.mask) {
+            if (mem_space == VIO360_MEM_DEVICE) { d.mask = j.mask; d.mask_pitch = (int)j.mask_pitch; }
+            else {
+                uint8_t* dm = s->d_mask.as<uint8_t>() + WH * b;
+                VIO_CUDA(ctx, cudaMemcpy2DAsync(dm, s->W, j.mask, j.mask_pitch, s->W, s->H, cudaMemcpyHostToDevice, st));
+                d.mask = dm; d.mask_pitch = s->W;
+            }
+        }
+        d.eig = s->d_eig.as<float>() + WH * b;
+        unsigned int* small = s->d_small.as<unsigned int>() + 4 * b;
+        d.max_bits = small; d.n_cand = small + 1; d.out_n = (int*)(small + 2);
+        d.cand = s->d_cand.as<unsigned long long>() + (size_t)s->max_cand * b;
+        d.grid = s->d_grid.as<int>() + grid_ints * b;
+        d.out_xy = mem_space == VIO360_MEM_DEVICE ? j.out_xy : s->d_corners.as<float>() + cap * 2 * b;
+    }
+    VIO_CUDA(ctx, cudaMemcpyAsync(s->d_djobs.p, hj, sizeof(DetectJobDev) * (size_t)n_jobs, cudaMemcpyHostToDevice, st));
+    const DetectParams P = detect_params(s);
+    const DetectJobDev* dj = s->d_djobs.as<DetectJobDev>();
+    k_min_eig<<<dim3((s->W + kEigCols - 1) / kEigCols, n_jobs), kEigThreads, 0, st>>>(dj, P);
+    VIO_LAUNCH_CHECK(ctx);
+    k_candidates<<<dim3((s->W - 2 + 31) / 32, (s->H - 2 + 7) / 8, n_jobs), 256, 0, st>>>(dj, P, quality);
+    VIO_LAUNCH_CHECK(ctx);
+    // sort each job's candidates by (value, raster index) descending; the count lives on the
+    // device, so sort the whole zero-padded buffer (zeros sort last)
+    VIO_CUDA(ctx, cudaMemcpyAsync(s->h_dout.p, s->d_small.p, 16 * (size_t)n_jobs, cudaMemcpyDeviceToHost, st));
+    VIO_CUDA(ctx, cudaStreamSynchronize(st));
+    const unsigned int* hs = s->h_dout.as<unsigned int>();
+    std::vector<int> ncand(n_jobs);
+    for (int b = 0; b < n_jobs; ++b) ncand[b] = (int)std::min<unsigned int>(hs[4 * b + 1], (unsigned int)s->max_cand);
+    for (int b = 0; b < n_jobs; ++b) {
+        if (ncand[b] == 0) continue;
+        size_t tb = s->cub_bytes;
+        unsigned long long* in = s->d_cand.as<unsigned long long>() + (size_t)s->max_cand * b;
+        unsigned long long* outk = s->d_cand_sorted.as<unsigned long long>() + (size_t)s->max_cand * b;
+        cudaError_t e = cub::DeviceRadixSort::SortKeysDescending(s->d_cub.p, tb, in, outk, ncand[b], 0, 64, st);
+        if (e != cudaSuccess) return vio360_fail(ctx, VIO360_ERR_CUDA, "cub sort: %s", cudaGetErrorString(e));
+        ctx->launches += 4;   // upsweep/scan/downsweep passes of the library sort (not our kernels)
+        hj[b].cand = outk;
+    }
+    VIO_CUDA(ctx, cudaMemcpyAsync(s->d_djobs.p, hj, sizeof(DetectJobDev) * (size_t)n_jobs, cudaMemcpyHostToDevice, st));
+    k_select<<<n_jobs, 32, 0, st>>>(dj, P, max_corners, min_dist);
+    VIO_LAUNCH_CHECK(ctx);
+    if (mem_space == VIO360_MEM_HOST) {
+        uint8_t* ho = s->h_dout.as<uint8_t>();
+        VIO_CUDA(ctx, cudaMemcpyAsync(ho, s->d_small.p, 16 * (size_t)n_jobs, cudaMemcpyDeviceToHost, st));
+        VIO_CUDA(ctx, cudaMemcpyAsync(ho + 16 * (size_t)n_jobs, s->d_corners.p, cap * 8 * n_jobs, cudaMemcpyDeviceToHost, st));
+        VIO_CUDA(ctx, cudaStreamSynchronize(st));
+        for (int b = 0; b < n_jobs; ++b) {
+            const int n = ((const int*)ho)[4 * b + 2];
+            *jobs[b].out_n = n;
+            if (n > 0) memcpy(jobs[b].out_xy, ho + 16 * (size_t)n_jobs + cap * 8 * b, (size_t)n * 8);
+        }
+    } else {
+        VIO_CUDA(ctx, cudaMemcpyAsync(s->h_dout.p, s->d_small.p, 16 * (size_t)n_jobs, cudaMemcpyDeviceToHost, st));
+        VIO_CUDA(ctx, cudaStreamSynchronize(st));
+        for (int b = 0; b < n_jobs; ++b) *jobs[b].out_n = ((const int*)s->h_dout.p)[4 * b + 2];
+    }
+    return VIO360_OK;
+}
+
+extern "C" int vio360_fe_detect(vio360_ctx* ctx, const uint8_t* img, size_t pitch, uint64_t key, const uint8_t* mask,
+                                size_t mask_pitch, int max_corners, double quality, double min_dist, float* out_xy,
+                                int* out_n) {
+    vio360_detect_job j;
+    j.img = img; j.pitch = pitch; j.key = key; j.mask = mask; j.mask_pitch = mask_pitch; j.out_xy = out_xy; j.out_n = out_n;
+    return vio360_fe_detect_batch(ctx, &j, 1, max_corners, quality, min_dist, VIO360_MEM_HOST);
+}
+
+extern "C" int vio360_fe_min_eigen_val(vio360_ctx* ctx, const uint8_t* img, size_t pitch, float* out) {
+    if (!ctx) return VIO360_ERR_INVALID;
+    vio360_fe_state* s = ctx->fe;
+    if (!s || !s->configured) return vio360_fail(ctx, VIO360_ERR_STATE, "fe_min_eigen_val before fe_configure");
+    if (!img || !out || pitch < (size_t)s->W) return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_min_eigen_val: bad arguments");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    int rc = ensure_detect_pools(ctx, 1, 1);
+    if (rc) return rc;
+    s->batch_tag++;
+    bool hit; int idx;
+    if ((rc = acquire_slot(ctx, 0, &hit, &idx))) return rc;
+    if ((rc = load_frame(ctx, idx, img, pitch, VIO360_MEM_HOST))) return rc;
+    cudaStream_t st = ctx->stream;
+    VIO_CUDA(ctx, cudaMemsetAsync(s->d_small.p, 0, 16, st));
+    DetectJobDev* hj = s->h_djobs.as<DetectJobDev>();
+    memset(hj, 0, sizeof(DetectJobDev));
+    hj->img = s->slots[idx].p[0]; hj->pitch = s->slots[idx].pitch[0];
+    hj->eig = s->d_eig.as<float>();
+    hj->max_bits = s->d_small.as<unsigned int>(); hj->n_cand = hj->max_bits + 1; hj->out_n = (int*)(hj->max_bits + 2);
+    VIO_CUDA(ctx, cudaMemcpyAsync(s->d_djobs.p, hj, sizeof(DetectJobDev), cudaMemcpyHostToDevice, st));
+    k_min_eig<<<dim3((s->W + kEigCols - 1) / kEigCols, 1), kEigThreads, 0, st>>>(s->d_djobs.as<DetectJobDev>(), detect_params(s));
+    VIO_LAUNCH_CHECK(ctx);
+    VIO_CUDA(ctx, cudaMemcpyAsync(out, s->d_eig.p, (size_t)s->W * s->H * 4, cudaMemcpyDeviceToHost, st));
+    VIO_CUDA(ctx, cudaStreamSynchronize(st));
+    return VIO360_OK;
+}

@@ -1,0 +1,206 @@
+/*
+ * vio360.h -- C ABI of libvio360_cuda.so: the B200 (sm_100a) implementation of the two
+ * data-parallel hot paths of 93won/360_visual_inertial_odometry.
+ *
+ *   path A  ERP feature front-end  (reference: src/processing/FeatureTracker.{h,cpp})
+ *   path B  BA factor evaluation   (reference: src/optimization/Factors.{h,cpp} + the
+ *           Schur block accumulation of vendored Ceres 2.0.0)
+ *
+ * Conventions: plain pointers and sizes only; every function returns VIO360_OK (0) or
+ * a negative error code and never throws; vio360_last_error() gives the message.  One
+ * context = one device + one stream; a context is not re-entrant.  Pointers are HOST
+ * memory unless the parameter is documented as device memory or a VIO360_MEM_DEVICE
+ * flag is passed.  There is NO CPU fallback: every entry point fails with
+ * VIO360_ERR_CUDA when no sm_100-class device is usable.
+ *
+ * "file:line" citations are relative to the reference repository root.
+ */
+#ifndef VIO360_H
+#define VIO360_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VIO360_OK 0
+#define VIO360_ERR_INVALID (-1) /* bad argument                                  */
+#define VIO360_ERR_CUDA (-2)    /* CUDA runtime error / no usable device          */
+#define VIO360_ERR_STATE (-3)   /* call order violated (e.g. evaluate before set) */
+#define VIO360_ERR_NOMEM (-4)
+
+#define VIO360_MEM_HOST 0
+#define VIO360_MEM_DEVICE 1
+
+typedef struct vio360_ctx vio360_ctx;
+typedef struct vio360_ba vio360_ba;
+
+/* ------------------------------------------------------------------ context ---- */
+int vio360_version(void);
+int vio360_create(int device, vio360_ctx** out);
+void vio360_destroy(vio360_ctx* ctx);
+const char* vio360_last_error(const vio360_ctx* ctx); /* ctx may be NULL: create() errors */
+int vio360_synchronize(vio360_ctx* ctx);
+void* vio360_stream(vio360_ctx* ctx);                 /* the context's cudaStream_t */
+/* number of kernels this context has launched so far (bench.py's gpu_launches) */
+long long vio360_launch_count(const vio360_ctx* ctx);
+/* measured FP64 / FP32 FMA pipe peak of the device in TFLOP/s (dependent-FMA loops on
+ * all SMs), the denominator SURVEY.md section 8-D asks for.                        */
+int vio360_probe_fma_peak(vio360_ctx* ctx, double* fp64_tflops, double* fp32_tflops);
+
+/* ------------------------------------------------------- path A: front-end ---- */
+/* Replaces the constructor state of vio_360::FeatureTracker
+ * (src/processing/FeatureTracker.cpp:24-59): LK window / levels / criteria
+ * (:33-35, hard-coded 21x21, maxLevel 3, 30 iterations, eps 0.01f), the polar mask
+ * (src/database/Camera.cpp:100-118) and the boundary mask (:47-58), which are evaluated
+ * analytically on the device instead of being materialised.  eps is the TermCriteria
+ * epsilon before OpenCV squares it; min_eig_thr is calcOpticalFlowPyrLK's
+ * minEigThreshold.  max_points / max_batch size the device pools.                    */
+int vio360_fe_configure(vio360_ctx* ctx, int width, int height, int max_level, int win,
+                        int max_iters, double eps, double min_eig_thr, float polar_ratio,
+                        int boundary_margin, int max_points, int max_batch);
+
+/* One frame pair.  `*_key` != 0 lets the context keep the frame's device pyramid and
+ * re-use it when the same key shows up again (the reference rebuilds both pyramids on
+ * every call, FeatureTracker.cpp:238); key 0 = never cache.                          */
+typedef struct {
+    const uint8_t* prev; size_t prev_pitch; uint64_t prev_key;
+    const uint8_t* cur;  size_t cur_pitch;  uint64_t cur_key;
+    const float* prev_xy;  /* n x 2, AoS like std::vector<cv::Point2f>              */
+    int n;
+    float* cur_xy;         /* n x 2 out                                             */
+    uint8_t* status;       /* n out, 0/1 (cv::calcOpticalFlowPyrLK status)          */
+    float* err;            /* n out or NULL                                         */
+    uint8_t* keep;         /* n out or NULL: status && !polar && !near-boundary,
+                              the post filter of FeatureTracker.cpp:118-126          */
+} vio360_track_job;
+
+/* Replaces FeatureTracker::TrackOpticalFlow (src/processing/FeatureTracker.cpp:228-251,
+ * i.e. cv::calcOpticalFlowPyrLK(prev, cur, prevPts, nextPts, status, err, Size(21,21),
+ * 3, TermCriteria(EPS|COUNT,30,0.01), 0, 0.01)).  n == 0 returns OK without touching
+ * the outputs (:233-235).  *n_tracked (may be NULL) = count of status != 0 (:242-249). */
+int vio360_fe_track(vio360_ctx* ctx, const uint8_t* prev, size_t prev_pitch,
+                    uint64_t prev_key, const uint8_t* cur, size_t cur_pitch,
+                    uint64_t cur_key, const float* prev_xy, int n, float* cur_xy,
+                    uint8_t* status, float* err, int* n_tracked);
+/* Batched form for independent frame pairs (BASELINE config 4: one job per sequence).
+ * mem_space says where ALL pointers inside the jobs live (the job array itself is
+ * host memory).  Device-space images need 4-byte aligned base and pitch.             */
+int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jobs, int n_jobs,
+                          int mem_space);
+
+typedef struct {
+    const uint8_t* img; size_t pitch; uint64_t key;
+    const uint8_t* mask; size_t mask_pitch; /* optional extra mask (the occupancy mask of
+                                               FeatureTracker::CreateFeatureMask, :386-402);
+                                               NULL = base mask only                  */
+    float* out_xy;   /* max_corners x 2 out, integer coordinates as float           */
+    int* out_n;      /* out: corners found                                          */
+} vio360_detect_job;
+
+/* Replaces FeatureTracker::DetectNewFeatures (src/processing/FeatureTracker.cpp:208-226,
+ * i.e. cv::goodFeaturesToTrack(image, corners, max_features, quality, min_distance,
+ * polar & boundary & mask, 3, false, 0.04)).                                         */
+int vio360_fe_detect(vio360_ctx* ctx, const uint8_t* img, size_t pitch, uint64_t key,
+                     const uint8_t* mask, size_t mask_pitch, int max_corners,
+                     double quality, double min_dist, float* out_xy, int* out_n);
+int vio360_fe_detect_batch(vio360_ctx* ctx, const vio360_detect_job* jobs, int n_jobs,
+                           int max_corners, double quality, double min_dist, int mem_space);
+
+/* Integer pyramid of one frame (cv::buildOpticalFlowPyramid levels without aprons):
+ * level l is written to out[l] with pitch out_pitch[l]; sizes are ((w+1)>>1,(h+1)>>1)
+ * per level.  Exposed for the bit-exact pyramid parity tests.                         */
+int vio360_fe_pyramid(vio360_ctx* ctx, const uint8_t* img, size_t pitch, int n_levels,
+                      uint8_t* const* out, const size_t* out_pitch);
+/* cv::cornerMinEigenVal(img, dst, 3, 3) response map (float, W x H, dense pitch). */
+int vio360_fe_min_eigen_val(vio360_ctx* ctx, const uint8_t* img, size_t pitch, float* out);
+
+/* ------------------------------------------- path B: BA factor evaluation ---- */
+/* A window = what Optimizer::RunLocalBA / RunBA assemble (src/optimization/
+ * Optimizer.cpp:741-840): K poses, M landmarks, O observations.                     */
+int vio360_ba_create(vio360_ctx* ctx, int K, int M, int O, vio360_ba** out);
+void vio360_ba_destroy(vio360_ba* ba);
+
+/* Replaces the O heap-allocated BAFactor objects (src/optimization/Factors.h:198-203,
+ * built at Optimizer.cpp:795-840) by one SoA upload.  T_wb_init is K x 16 row-major
+ * (m_T_wb_init), T_cb 16 row-major (m_Tcb), info the 2x2 information matrix shared by
+ * all factors (Optimizer.cpp:824), huber_delta the ceres::HuberLoss parameter
+ * (Optimizer.cpp:835; <= 0 = no loss function).  pose_fixed / point_fixed mirror
+ * Problem::SetParameterBlockConstant (Optimizer.cpp:854-877); NULL = none.           */
+int vio360_ba_set_structure(vio360_ba* ba, const int32_t* pose_idx, const int32_t* point_idx,
+                            const double* obs_u, const double* obs_v,
+                            const double* T_wb_init, const double* T_cb, double cols,
+                            double rows, const double* info, double huber_delta,
+                            const uint8_t* pose_fixed, const uint8_t* point_fixed);
+/* BAFactor::set_outlier for every factor at once (Factors.h:137; Optimizer.cpp:903-906).
+ * NULL clears all flags.                                                            */
+int vio360_ba_set_outliers(vio360_ba* ba, const uint8_t* outlier);
+/* Multi-GPU: this instance only processes the landmarks of shard `rank` of `world`
+ * (contiguous landmark ranges balanced by sum of squared degrees).  Partial reduced
+ * systems of all ranks sum to the full one.  Default (0, 1).                        */
+int vio360_ba_set_shard(vio360_ba* ba, int rank, int world);
+
+/* The evaluation point: pose_delta K x 6 ([rho, phi], LieUtils.cpp:305-308) and
+ * points M x 3 -- what Ceres copies into the user's parameter blocks before
+ * EvaluationCallback::PrepareForEvaluation (program_evaluator.h:155-160).  Runs the
+ * per-pose chain of Factors.cpp:357-364 once per pose instead of once per factor.   */
+int vio360_ba_set_parameters(vio360_ba* ba, const double* pose_delta, const double* points);
+
+/* Replaces the ParallelFor over ResidualBlock::Evaluate -> BAFactor::Evaluate
+ * (program_evaluator.h:187-258; Factors.cpp:327-542) incl. HuberLoss + Corrector
+ * (residual_block.cc:161-195) when apply_loss != 0.  *cost = sum of 0.5*rho(s).      */
+int vio360_ba_evaluate(vio360_ba* ba, int want_jacobians, int apply_loss, double* cost);
+/* Copy out the last evaluate(): r O x 2, Jp O x 12 (2x6 row-major), Jl O x 6 (2x3
+ * row-major), in the caller's observation order.  Any pointer may be NULL.          */
+int vio360_ba_get_residuals_jacobians(vio360_ba* ba, double* r, double* Jp, double* Jl);
+
+/* Gauss-Newton blocks of J^T J and J^T r at the current parameters (fused with the
+ * factor evaluation, nothing materialised): Hpp K x 36, bp K x 6, Hll M x 9, bl M x 3,
+ * Hpl O x 18 (F^T E per observation, 6x3).  Blocks of fixed parameters are zero.
+ * Any pointer may be NULL.                                                          */
+int vio360_ba_normal_blocks(vio360_ba* ba, int apply_loss, double* Hpp, double* bp,
+                            double* Hll, double* bl, double* Hpl);
+
+/* Number of rows of the reduced camera system: 6 * (number of free poses). */
+int vio360_ba_reduced_dim(const vio360_ba* ba);
+/* Replaces SchurEliminator<2,3,6>::Eliminate (thirdparty/ceres-solver/internal/ceres/
+ * schur_eliminator_impl.h:179-308) fused with the factor evaluation: builds
+ * S = F'F + Dp^2 - F'E (E'E + Dl^2)^-1 E'F and rhs = F'r - F'E (E'E + Dl^2)^-1 E'r at
+ * the current parameters.  lm_diag (6K + 3M, pose part first; NULL = 0) is the
+ * Levenberg-Marquardt diagonal of levenberg_marquardt_strategy.cc:78-89.  S (n x n
+ * dense row-major, full symmetric) / rhs (n) / cost may be NULL: the result then stays
+ * on the device (see vio360_ba_reduced_system_dev).  With a shard set, the result is
+ * the shard's partial sum.                                                           */
+int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_diag, int apply_loss,
+                                   double* S, double* rhs, double* cost);
+/* Device view of the last reduced system as ONE packed buffer [S n*n | rhs n | cost 1]
+ * so that a single ncclAllReduce(sum, double) combines the shards.  */
+int vio360_ba_reduced_system_dev(vio360_ba* ba, double** packed_dev, size_t* n_doubles);
+/* Copy the (possibly all-reduced) packed device buffer back to the host. */
+int vio360_ba_fetch_reduced_system(vio360_ba* ba, double* S, double* rhs, double* cost);
+
+/* diag(J^T J) per parameter (6K + 3M), the input of the LM diagonal. */
+int vio360_ba_column_sqnorm(vio360_ba* ba, int apply_loss, double* out);
+
+/* Replaces the per-factor BAFactor::compute_chi_square loop (Factors.cpp:544-612;
+ * Optimizer.cpp:898-915): chi2 O (may be NULL), flag O = chi2 > thr (may be NULL).   */
+int vio360_ba_chi2(vio360_ba* ba, double thr, double* chi2, uint8_t* flag);
+
+/* ------------------------------------------------ path B (pose only): PnP ---- */
+/* Replaces PnPFactor::Evaluate / compute_chi_square (Factors.cpp:33-210, 212-265) for
+ * the N factors of one Optimizer::SolvePnP round (Optimizer.cpp:162-177): one shared
+ * pose delta, constant world points.  r N x 2, Jp N x 12 (may be NULL), valid N (0 where
+ * Evaluate returns false, :74-80), H 36 / b 6 = sum of J^T J / J^T r with Huber
+ * (may be NULL), chi2 N (may be NULL).                                              */
+int vio360_pnp_evaluate(vio360_ctx* ctx, int N, const double* obs_uv, const double* world_pts,
+                        const uint8_t* outlier, const double* T_wb_init, const double* T_cb,
+                        double cols, double rows, const double* info, double huber_delta,
+                        const double* pose_delta, double* r, double* Jp, uint8_t* valid,
+                        double* H, double* b, double* cost, double* chi2);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VIO360_H */

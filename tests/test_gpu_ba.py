@@ -1,0 +1,193 @@
+"""GPU parity tests for path B through the C ABI (include/vio360.h) against the oracle.
+Tolerance: 1e-9 relative (max-norm) in fp64, BASELINE.json north_star."""
+import os
+
+import numpy as np
+import pytest
+
+import ba_oracle
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-9
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "ba_golden.npz")
+
+
+def _oracle_all(win, radius=1e4):
+    W = ba_oracle.Window(win)
+    r, Jp, Jl, cost = W.evaluate(win["pose_delta"], win["points"])
+    D = W.lm_diagonal(Jp, Jl, radius)
+    S, rhs, fm = W.schur(r, Jp, Jl, D)
+    blocks = W.normal_blocks(r, Jp, Jl)
+    chi2, flag = W.chi2(win["pose_delta"], win["points"], 5.991)
+    return dict(r=r, Jp=Jp, Jl=Jl, cost=cost, D=D, S=S, rhs=rhs, blocks=blocks, chi2=chi2, flag=flag)
+
+
+def _check_window(bindings, ctx, win, ref=None):
+    ref = ref or _oracle_all(win)
+    ba = bindings.BAWindow(ctx, win)
+    ba.set_parameters(win["pose_delta"], win["points"])
+    r, Jp, Jl, cost = ba.evaluate(True, True)
+    assert rel_err(r, ref["r"]) < TOL and rel_err(Jp, ref["Jp"]) < TOL and rel_err(Jl, ref["Jl"]) < TOL
+    assert abs(cost - ref["cost"]) < TOL * ref["cost"]
+    # special-case rows must be reproduced exactly
+    special = (np.abs(ref["Jp"]).reshape(len(r), -1).max(axis=1) == 0)
+    assert np.array_equal(r[special], ref["r"][special]) and not Jp[special].any() and not Jl[special].any()
+    r2, _, _, cost2 = ba.evaluate(True, False)
+    Wo = ba_oracle.Window(win)
+    ro, _, _, co = Wo.evaluate(win["pose_delta"], win["points"], apply_loss=False)
+    assert rel_err(r2, ro) < TOL and abs(cost2 - co) < TOL * co
+    colsq = ba.column_sqnorm(True)
+    D = np.sqrt(np.clip(colsq, 1e-6, 1e32) / 1e4)
+    free = np.concatenate([np.repeat(win["pose_fixed"] == 0, 6), np.repeat(win["point_fixed"] == 0, 3)])
+    assert rel_err(D[free], ref["D"][free]) < TOL
+    S, rhs, cost3 = ba.build_reduced_system(ref["D"], True)
+    assert S.shape == ref["S"].shape
+    assert rel_err(S, ref["S"]) < TOL and rel_err(rhs, ref["rhs"]) < TOL and abs(cost3 - ref["cost"]) < TOL * ref["cost"]
+    assert np.array_equal(S, S.T)
+    Hpp, bp, Hll, bl, Hpl = ba.normal_blocks(True)
+    for a, b in zip((Hpp, bp, Hll, bl, Hpl), ref["blocks"]):
+        assert rel_err(a, b) < TOL
+    chi2, flag = ba.chi2(5.991)
+    assert rel_err(chi2, ref["chi2"]) < TOL
+    amb = np.abs(ref["chi2"] - 5.991) < 1e-6
+    assert np.array_equal(flag[~amb], ref["flag"][~amb])
+    ba.close()
+    return S, rhs
+
+
+def test_golden_window(bindings, ctx):
+    g = np.load(GOLD)
+    K, M, O, cols, rows, huber = g["scalars"]
+    win = {k[3:]: g[k] for k in g.files if k.startswith("in_")}
+    win.update(K=int(K), M=int(M), O=int(O), cols=float(cols), rows=float(rows), huber_a=float(huber))
+    ref = dict(r=g["r"], Jp=g["Jp"], Jl=g["Jl"], cost=float(g["cost"]), D=g["D"], S=g["S"], rhs=g["rhs"],
+               blocks=(g["Hpp"], g["bp"], g["Hll"], g["bl"], g["Hpl"]), chi2=g["chi2"], flag=g["flag"])
+    _check_window(bindings, ctx, win, ref)
+
+
+def test_local_window_c3(bindings, ctx, synthetic):
+    """BASELINE config 3: 10 keyframes, ~20k observations, mid-iteration state."""
+    win = synthetic.make_ba_window(K=10, M=2000, seed=20000, mid_iteration=True)
+    assert 18000 < win["O"] <= 20000
+    _check_window(bindings, ctx, win)
+    win0 = synthetic.make_ba_window(K=10, M=2000, seed=20000, mid_iteration=False)
+    _check_window(bindings, ctx, win0)
+
+
+def test_unsorted_observations_and_ragged_structure(bindings, ctx, synthetic):
+    win = synthetic.make_ba_window(K=12, M=300, degree=5, seed=5, mid_iteration=True, sort_by_landmark=False)
+    # ragged: a landmark with no observation, one with a single observation, duplicates of a (pose, landmark) pair
+    keep = ~((win["point_idx"] == 7) | ((win["point_idx"] == 9) & (np.arange(win["O"]) % 5 != 0)))
+    for k in ("pose_idx", "point_idx", "obs_u", "obs_v", "outlier"):
+        win[k] = np.ascontiguousarray(win[k][keep])
+    dup = np.where(win["point_idx"] == 20)[0][:2]
+    for k in ("pose_idx", "point_idx", "obs_u", "obs_v", "outlier"):
+        win[k] = np.ascontiguousarray(np.concatenate([win[k], win[k][dup]]))
+    win["obs_u"][-1] += 0.5
+    win["O"] = int(win["obs_u"].shape[0])
+    _check_window(bindings, ctx, win)
+
+
+def test_high_degree_landmarks(bindings, ctx, synthetic):
+    """landmarks seen by more than 32 poses exercise the multi-chunk path"""
+    win = synthetic.make_ba_window(K=48, M=60, seed=9, mid_iteration=True, yaw_spread_deg=340.0)
+    deg = np.bincount(win["point_idx"], minlength=win["M"])
+    assert deg.max() > 32
+    _check_window(bindings, ctx, win)
+
+
+def test_outlier_flags_and_reuse(bindings, ctx, synthetic):
+    win = synthetic.make_ba_window(K=6, M=150, seed=3, mid_iteration=True)
+    ba = bindings.BAWindow(ctx, win)
+    ba.set_parameters(win["pose_delta"], win["points"])
+    chi2, flag = ba.chi2(5.991)
+    win2 = dict(win); win2["outlier"] = flag.copy()
+    ba.set_outliers(flag)                                  # Optimizer.cpp:903-906
+    r, Jp, Jl, cost = ba.evaluate(True, True)
+    ref = ba_oracle.Window(win2).evaluate(win["pose_delta"], win["points"])
+    assert rel_err(r, ref[0]) < TOL and rel_err(Jp, ref[1]) < TOL and abs(cost - ref[3]) < TOL * ref[3]
+    assert np.all(r[flag == 1] == (640.0, 480.0))
+    ba.set_outliers(None)
+    r, _, _, _ = ba.evaluate(False, True)
+    ref = ba_oracle.Window(dict(win, outlier=np.zeros(win["O"], np.uint8))).evaluate(win["pose_delta"], win["points"])
+    assert rel_err(r, ref[0]) < TOL
+    ba.close()
+
+
+def test_sharded_partials_sum_to_full_system(bindings, ctx, synthetic):
+    """multi-GPU decomposition emulated on one device: the landmark shards'
+    partial reduced systems add up to the single-GPU one."""
+    win = synthetic.make_ba_window(K=40, M=1500, degree=8, seed=77, mid_iteration=True)
+    ref = _oracle_all(win)
+    ba = bindings.BAWindow(ctx, win)
+    ba.set_parameters(win["pose_delta"], win["points"])
+    for world in (2, 4, 8):
+        S = 0; rhs = 0; cost = 0
+        for rank in range(world):
+            ba.set_shard(rank, world)
+            s, b, c = ba.build_reduced_system(ref["D"], True)
+            S = S + s; rhs = rhs + b; cost += c
+        assert rel_err(S, ref["S"]) < TOL and rel_err(rhs, ref["rhs"]) < TOL and abs(cost - ref["cost"]) < TOL * ref["cost"]
+    ba.close()
+
+
+def test_large_window_properties(bindings, ctx, synthetic):
+    """BASELINE config 5 size (200 keyframes, 1M observations): size-independent checks --
+    S symmetric PSD-ish, cost equals the evaluate() cost, linearity of the shard sum, and
+    a sampled subset of residual rows against the oracle."""
+    win = synthetic.make_ba_window(K=200, M=50000, degree=20, seed=1000000, mid_iteration=True, loop_radius=6.0)
+    assert win["O"] > 900000
+    ba = bindings.BAWindow(ctx, win)
+    ba.set_parameters(win["pose_delta"], win["points"])
+    r, Jp, Jl, cost = ba.evaluate(True, True)
+    colsq = ba.column_sqnorm(True)
+    D = np.sqrt(np.clip(colsq, 1e-6, 1e32) / 1e4)
+    S, rhs, cost2 = ba.build_reduced_system(D, True)
+    assert abs(cost - cost2) < 1e-12 * cost and np.array_equal(S, S.T)
+    assert np.linalg.eigvalsh(S).min() > -1e-6 * np.abs(S).max()
+    # sampled rows vs oracle
+    rng = np.random.default_rng(0)
+    idx = np.sort(rng.choice(win["O"], 3000, replace=False))
+    sub = dict(win, O=len(idx), pose_idx=win["pose_idx"][idx], point_idx=win["point_idx"][idx],
+               obs_u=np.ascontiguousarray(win["obs_u"][idx]), obs_v=np.ascontiguousarray(win["obs_v"][idx]),
+               outlier=win["outlier"][idx])
+    ro, Jpo, Jlo, _ = ba_oracle.Window(sub).evaluate(win["pose_delta"], win["points"])
+    assert rel_err(r[idx], ro) < TOL and rel_err(Jp[idx], Jpo) < TOL and rel_err(Jl[idx], Jlo) < TOL
+    # full Schur parity on this size too (the oracle needs a few seconds)
+    Wo = ba_oracle.Window(win)
+    So, rhso, _ = Wo.schur(r, Jp, Jl, D)
+    assert rel_err(S, So) < TOL and rel_err(rhs, rhso) < TOL
+    ba.close()
+
+
+def test_pnp(bindings, ctx, synthetic):
+    win = synthetic.make_ba_window(K=3, M=400, seed=31, mid_iteration=True)
+    k = 1
+    sel = np.where(win["pose_idx"] == k)[0]
+    obs = np.stack([win["obs_u"][sel], win["obs_v"][sel]], axis=1)
+    pts = win["points"][win["point_idx"][sel]].copy()
+    outl = win["outlier"][sel].copy(); outl[:3] = 1
+    # a point at the camera centre -> Evaluate returns false
+    import ba_ref_np
+    Rcw, tcw, _, _ = ba_ref_np.pose_chain(win["Twb_init"][k], win["Tcb"], win["pose_delta"][k])
+    pts[5] = -Rcw.T @ tcw
+    out = ctx.pnp_evaluate(obs, pts, win["Twb_init"][k], win["Tcb"], win["cols"], win["rows"], win["info"], 1.0,
+                           win["pose_delta"][k], outlier=outl)
+    H = np.zeros((6, 6)); b = np.zeros(6); cost = 0.0
+    for i in range(len(sel)):
+        f = ba_oracle.make_factor(obs[i], win["cols"], win["rows"], win["Tcb"], win["Twb_init"][k], win["info"],
+                                  is_outlier=bool(outl[i]), world_point=tuple(pts[i]))
+        ok, r, Jp = ba_oracle.pnp_evaluate(f, win["pose_delta"][k])
+        assert out["valid"][i] == ok
+        c2 = ba_oracle.pnp_chi2(f, win["pose_delta"][k])
+        assert out["chi2"][i] == c2 or abs(out["chi2"][i] - c2) < TOL * max(1.0, abs(c2))
+        if not ok:
+            continue
+        import ctypes as C
+        rr = r.copy(); JJ = Jp.copy()
+        dp = C.POINTER(C.c_double)
+        cost += ba_oracle.lib().vo_apply_loss(C.c_double(1.0), rr.ctypes.data_as(dp), 2, JJ.ctypes.data_as(dp), 6, None, 0)
+        assert np.allclose(out["r"][i], rr, rtol=TOL, atol=TOL * 100) and rel_err(out["Jp"][i], JJ) < TOL or not JJ.any()
+        H += JJ.T @ JJ; b += JJ.T @ rr
+    assert rel_err(out["H"], H) < TOL and rel_err(out["b"], b) < TOL and abs(out["cost"] - cost) < TOL * cost

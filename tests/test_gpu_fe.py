@@ -1,0 +1,134 @@
+"""GPU parity tests for path A through the C ABI against the oracle (oracle/fe_ref.c,
+itself pinned to cv2) and the committed cv2 golden vectors.
+Bars (BASELINE.json north_star): pyramid / status / keypoint indices bit exact,
+tracked positions within 0.05 px."""
+import os
+
+import numpy as np
+import pytest
+
+import fe_oracle as fo
+
+pytestmark = pytest.mark.gpu
+POS_TOL = 0.05
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "fe_golden.npz")
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(GOLD)
+
+
+def _bits_sum(a):
+    return np.array([a.view(np.uint32).astype(np.uint64).sum()], np.uint64)
+
+
+def test_golden_pyramid_lk_gftt(ctx, gold):
+    f0, f1, pts = gold["f0"], gold["f1"], gold["pts"]
+    H, W = f0.shape
+    ctx.fe_configure(W, H, max_points=len(pts), max_batch=2)
+    pyr = ctx.fe_pyramid(f0, 4)
+    for l, name in ((1, "pyr1"), (2, "pyr2"), (3, "pyr3")):
+        g = gold[name]
+        assert np.array_equal(pyr[l][:g.shape[0], :g.shape[1]], g)
+    xy, st, err, nt = ctx.fe_track(f0, f1, pts)
+    assert np.array_equal(st, gold["cv_status"]) and nt == int(gold["cv_status"].sum())
+    ok = st == 1
+    assert np.abs(xy - gold["cv_next"])[ok].max() < POS_TOL
+    assert np.abs(err - gold["cv_err"])[ok].max() < 0.05
+    eig = ctx.fe_min_eigen_val(f0)
+    assert np.array_equal(eig[::8], gold["eig_rows"]) and np.array_equal(_bits_sum(eig), gold["eig_bits_sum"])
+    assert np.array_equal(ctx.fe_detect(f0, None, 1000), gold["gftt_base"])
+    assert np.array_equal(ctx.fe_detect(f0, gold["occ_mask"], 1000), gold["gftt_occ"])
+    assert np.array_equal(ctx.fe_detect(f0, None, 25), gold["gftt_top25"])
+
+
+@pytest.mark.parametrize("shape", [(481, 963), (240, 320), (67, 91), (1920, 3840)])
+def test_pyramid_bit_exact(ctx, shape):
+    H, W = shape
+    rng = np.random.default_rng(H)
+    img = rng.integers(0, 256, (H, W), dtype=np.uint8)
+    ctx.fe_configure(W, H, max_points=8, max_batch=1)
+    lv = img
+    got = ctx.fe_pyramid(img, 4 if min(H, W) > 200 else 2)
+    for l in range(1, len(got)):
+        lv = fo.pyr_down(lv)
+        assert np.array_equal(got[l][:lv.shape[0], :lv.shape[1]], lv), "level %d" % l
+
+
+@pytest.mark.parametrize("size,seed,n", [((640, 320), 3, 500), ((1280, 640), 4, 1000), ((963, 481), 6, 300)])
+def test_lk_vs_oracle(ctx, synthetic, size, seed, n):
+    W, H = size
+    f0 = synthetic.render_erp_frame(W, H, 0, seed=seed, n_waves=48, sigma_omega=40.0)
+    f1 = synthetic.render_erp_frame(W, H, 2, seed=seed, n_waves=48, sigma_omega=40.0)
+    f0[H // 2:H // 2 + 40, W // 2:W // 2 + 60] = 77; f1[H // 2:H // 2 + 40, W // 2:W // 2 + 60] = 77
+    pts = synthetic.make_track_points(W, H, n, seed=seed, seam_frac=0.1)
+    rng = np.random.default_rng(seed)
+    pts[:20] = rng.uniform([-30, -30], [W + 30, H + 30], (20, 2)).astype(np.float32)   # border / out-of-image
+    ctx.fe_configure(W, H, max_points=n, max_batch=2)
+    xy, st, err, nt = ctx.fe_track(f0, f1, pts)
+    oxy, ost, oerr, ocnt = fo.lk_track(f0, f1, pts)
+    assert np.array_equal(st, ost) and nt == ocnt
+    ok = ost == 1
+    assert np.abs(xy - oxy)[ok].max() < POS_TOL
+    assert np.abs(err - oerr)[ok].max() < 0.05
+    assert (ost == 0).sum() > 0
+    # untracked points still report OpenCV's last estimate
+    assert np.abs(xy - oxy)[~ok].max() < POS_TOL if (~ok).any() else True
+
+
+def test_track_batch_cache_and_keep(ctx, synthetic):
+    W, H = 640, 320
+    frames = [synthetic.render_erp_frame(W, H, t, seed=21, n_waves=32, sigma_omega=40.0) for t in range(3)]
+    pts = synthetic.make_track_points(W, H, 200, seed=2)
+    ctx.fe_configure(W, H, max_points=256, max_batch=4)
+    # two "sequences" in one batch; keys let the second call re-use frame 1's pyramid
+    out1 = ctx.fe_track_batch_host([(frames[0], frames[1], pts, 100, 101), (frames[1], frames[2], pts[:150], 101, 102)])
+    out2 = ctx.fe_track_batch_host([(frames[1], frames[2], pts[:150], 101, 102)])
+    assert np.array_equal(out1[1][0], out2[0][0]) and np.array_equal(out1[1][1], out2[0][1])
+    for (prev, cur, p), (xy, st, err, keep) in zip(((frames[0], frames[1], pts), (frames[1], frames[2], pts[:150])), out1):
+        oxy, ost, _, _ = fo.lk_track(prev, cur, p)
+        assert np.array_equal(st, ost) and np.abs(xy - oxy)[ost == 1].max() < POS_TOL
+        assert np.array_equal(keep, fo.post_filter(xy, st, W, H, 0.15, 20.0))
+    # empty input: returns 0 tracked and touches nothing (FeatureTracker.cpp:233-235)
+    xy, st, err, nt = ctx.fe_track(frames[0], frames[1], np.zeros((0, 2), np.float32))
+    assert nt == 0 and len(st) == 0
+
+
+@pytest.mark.parametrize("size,seed", [((960, 480), 3), ((1920, 960), 4), ((3840, 1920), 5)])
+def test_detect_vs_oracle(ctx, synthetic, size, seed):
+    W, H = size
+    f0 = synthetic.render_erp_frame(W, H, 0, seed=seed, n_waves=48, sigma_omega=40.0 * W / 960)
+    ctx.fe_configure(W, H, max_points=8, max_batch=1)
+    eig = ctx.fe_min_eigen_val(f0)
+    assert np.array_equal(eig, fo.min_eigen_val(f0))
+    mask = fo.base_mask(W, H)
+    ref = fo.good_features(f0, mask, 1000)
+    got = ctx.fe_detect(f0, None, 1000)
+    assert np.array_equal(got, ref) and len(ref) > 50
+    occ = mask.copy()
+    yy, xx = np.mgrid[0:H, 0:W]
+    for p in ref[::2]:
+        occ[(xx - p[0]) ** 2 + (yy - p[1]) ** 2 <= 900] = 0
+    assert np.array_equal(ctx.fe_detect(f0, occ, 1000), fo.good_features(f0, occ, 1000))
+    assert np.array_equal(ctx.fe_detect(f0, None, 10), ref[:10])
+    # empty mask -> no corners
+    assert len(ctx.fe_detect(f0, np.zeros_like(mask), 1000)) == 0
+
+
+def test_full_size_properties_c2(ctx, synthetic):
+    """BASELINE config 2 size: a frame tracked onto itself does not move; status all ones."""
+    W, H = 3840, 1920
+    f0 = synthetic.render_erp_frame(W, H, 0, seed=360, n_waves=32, sigma_omega=120.0)
+    pts = synthetic.make_track_points(W, H, 1000, seed=1000)
+    ctx.fe_configure(W, H, max_points=1000, max_batch=1)
+    xy, st, err, nt = ctx.fe_track(f0, f0, pts)
+    ost = fo.lk_track(f0, f0, pts)[1]
+    assert np.array_equal(st, ost)
+    assert np.abs(xy - pts)[st == 1].max() < 1e-3 and err[st == 1].max() == 0.0
+    f1 = np.roll(f0, 3, axis=1)             # pure horizontal shift by 3 px
+    xy, st, err, nt = ctx.fe_track(f0, f1, pts)
+    oxy, ost, _, _ = fo.lk_track(f0, f1, pts)
+    assert np.array_equal(st, ost) and np.abs(xy - oxy)[ost == 1].max() < POS_TOL
+    inner = (ost == 1) & (pts[:, 0] > 200) & (pts[:, 0] < W - 200)
+    assert np.median(np.abs(xy[inner, 0] - pts[inner, 0] - 3.0)) < 0.05

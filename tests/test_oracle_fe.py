@@ -1,0 +1,100 @@
+"""CPU tests pinning oracle/fe_ref.c against (a) the committed cv2 golden vectors and
+(b) cv2 itself, live, with the reference's exact arguments."""
+import os
+
+import numpy as np
+import pytest
+
+import fe_oracle as fo
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "fe_golden.npz")
+POS_TOL = 0.05      # px, BASELINE.json north_star
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(GOLD)
+
+
+def _bits_sum(a):
+    return np.array([a.view(np.uint32).astype(np.uint64).sum()], np.uint64)
+
+
+def test_pyramid_bit_exact_golden(gold):
+    lv = gold["f0"]
+    for name in ("pyr1", "pyr2", "pyr3"):
+        lv = fo.pyr_down(lv)
+        assert np.array_equal(lv, gold[name])
+
+
+def test_lk_against_golden(gold):
+    xy, st, err, cnt = fo.lk_track(gold["f0"], gold["f1"], gold["pts"])
+    assert np.array_equal(st, gold["cv_status"]) and cnt == int(gold["cv_status"].sum())
+    ok = st == 1
+    assert np.abs(xy - gold["cv_next"])[ok].max() < POS_TOL
+    assert np.abs(err - gold["cv_err"])[ok].max() < 0.05
+    assert (st == 0).sum() >= 10          # the fixture exercises the status=0 branches
+
+
+def test_gftt_against_golden(gold):
+    f0 = gold["f0"]
+    h, w = f0.shape
+    mask = fo.base_mask(w, h, 0.15, 20)
+    assert np.array_equal(fo.good_features(f0, mask, 1000), gold["gftt_base"])
+    assert np.array_equal(fo.good_features(f0, gold["occ_mask"], 1000), gold["gftt_occ"])
+    assert np.array_equal(fo.good_features(f0, mask, 25), gold["gftt_top25"])
+    eig = fo.min_eigen_val(f0)
+    assert np.array_equal(eig[::8], gold["eig_rows"]) and np.array_equal(_bits_sum(eig), gold["eig_bits_sum"])
+
+
+def test_post_filter_and_masks():
+    m = fo.base_mask(960, 480, 0.15, 20)
+    assert m[:72].max() == 0 and m[72, 20] == 255 and m[72, 19] == 0 and m[407, 939] == 255
+    assert m[408:].max() == 0 and m[300, 940] == 0       # int(480*(1-0.15f)) == 408
+    xy = np.array([[100, 100], [100, 71.9], [19.9, 200], [940.1, 200], [940, 200], [100, 408.1], [100, 200]], np.float32)
+    st = np.array([1, 1, 1, 1, 1, 1, 0], np.uint8)
+    assert list(fo.post_filter(xy, st, 960, 480)) == [1, 0, 0, 0, 1, 0, 0]
+
+
+# ---- live comparisons with the dependency itself -------------------------------------
+cv2 = pytest.importorskip("cv2")
+
+
+@pytest.mark.parametrize("shape", [(481, 963), (240, 320), (67, 45)])
+def test_pyr_scharr_vs_cv2(shape):
+    rng = np.random.default_rng(shape[0])
+    img = rng.integers(0, 256, shape, dtype=np.uint8)
+    assert np.array_equal(fo.pyr_down(img), cv2.pyrDown(img))
+    s = fo.scharr(img)
+    assert np.array_equal(s[..., 0], cv2.Scharr(img, cv2.CV_16S, 1, 0))
+    assert np.array_equal(s[..., 1], cv2.Scharr(img, cv2.CV_16S, 0, 1))
+
+
+@pytest.mark.parametrize("size,seed", [((640, 320), 3), ((1280, 640), 4)])
+def test_lk_vs_cv2_live(synthetic, size, seed):
+    W, H = size
+    f0 = synthetic.render_erp_frame(W, H, 0, seed=seed, n_waves=48, sigma_omega=40.0)
+    f1 = synthetic.render_erp_frame(W, H, 2, seed=seed, n_waves=48, sigma_omega=40.0)
+    pts = synthetic.make_track_points(W, H, 400, seed=seed, seam_frac=0.1)
+    a, sa, ea, _ = fo.lk_track(f0, f1, pts)
+    b, sb, eb = fo.cv2_lk_track(f0, f1, pts)
+    assert np.array_equal(sa, sb)
+    ok = sb == 1
+    assert np.abs(a - b)[ok].max() < POS_TOL
+    for nt in (1, 4):                      # thread-count invariance of the dependency
+        cv2.setNumThreads(nt)
+        b2, sb2, _ = fo.cv2_lk_track(f0, f1, pts)
+        assert np.array_equal(sb2, sb) and np.array_equal(b2, b)
+    cv2.setNumThreads(-1)
+
+
+@pytest.mark.parametrize("size,seed", [((960, 480), 3), ((1920, 960), 4)])
+def test_gftt_vs_cv2_live(synthetic, size, seed):
+    W, H = size
+    f0 = synthetic.render_erp_frame(W, H, 0, seed=seed, n_waves=48, sigma_omega=50.0)
+    mask = fo.base_mask(W, H)
+    if not np.array_equal(cv2.cornerMinEigenVal(f0, 3, ksize=3), fo.min_eigen_val(f0)):
+        pytest.skip("this host's OpenCV dispatch rounds the Sobel/box pipeline differently (non-FMA CPU?)")
+    a = fo.cv2_good_features(f0, mask)
+    b = fo.good_features(f0, mask)
+    assert np.array_equal(a, b) and len(a) > 50
