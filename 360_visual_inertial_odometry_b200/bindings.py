@@ -17,12 +17,13 @@ MEM_HOST, MEM_DEVICE = 0, 1
 EXPORTS = [
     "vio360_version", "vio360_create", "vio360_destroy", "vio360_last_error", "vio360_synchronize",
     "vio360_stream", "vio360_launch_count", "vio360_probe_fma_peak",
+    "vio360_enable_kernel_timing", "vio360_kernel_time", "vio360_reset_kernel_times",
     "vio360_fe_configure", "vio360_fe_track", "vio360_fe_track_batch", "vio360_fe_detect",
     "vio360_fe_detect_batch", "vio360_fe_pyramid", "vio360_fe_min_eigen_val",
     "vio360_ba_create", "vio360_ba_destroy", "vio360_ba_set_structure", "vio360_ba_set_outliers",
     "vio360_ba_set_shard", "vio360_ba_set_parameters", "vio360_ba_evaluate",
     "vio360_ba_get_residuals_jacobians", "vio360_ba_normal_blocks", "vio360_ba_reduced_dim",
-    "vio360_ba_build_reduced_system", "vio360_ba_reduced_system_dev", "vio360_ba_fetch_reduced_system",
+    "vio360_ba_build_reduced_system", "vio360_ba_set_lm_diagonal", "vio360_ba_reduced_system_dev", "vio360_ba_fetch_reduced_system",
     "vio360_ba_column_sqnorm", "vio360_ba_chi2", "vio360_pnp_evaluate",
 ]
 
@@ -69,6 +70,9 @@ def load():
     lib.vio360_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
     lib.vio360_synchronize.argtypes = [C.c_void_p]
     lib.vio360_probe_fma_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    lib.vio360_enable_kernel_timing.argtypes = [C.c_void_p, C.c_int]
+    lib.vio360_kernel_time.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
+    lib.vio360_reset_kernel_times.argtypes = [C.c_void_p]
     lib.vio360_fe_configure.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double,
                                         C.c_double, C.c_float, C.c_int, C.c_int, C.c_int]
     lib.vio360_fe_track.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p, C.c_size_t,
@@ -94,6 +98,7 @@ def load():
     lib.vio360_ba_reduced_dim.argtypes = [C.c_void_p]
     lib.vio360_ba_build_reduced_system.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                                    C.POINTER(C.c_double)]
+    lib.vio360_ba_set_lm_diagonal.argtypes = [C.c_void_p, C.c_void_p]
     lib.vio360_ba_reduced_system_dev.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
     lib.vio360_ba_fetch_reduced_system.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]
     lib.vio360_ba_column_sqnorm.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
@@ -145,6 +150,17 @@ class Context:
     @property
     def launch_count(self):
         return int(self.lib.vio360_launch_count(self.h))
+
+    def enable_kernel_timing(self, on=True):
+        self.check(self.lib.vio360_enable_kernel_timing(self.h, int(on)))
+
+    def reset_kernel_times(self):
+        self.check(self.lib.vio360_reset_kernel_times(self.h))
+
+    def kernel_time(self, name):
+        ms = C.c_double(0); n = C.c_longlong(0)
+        self.check(self.lib.vio360_kernel_time(self.h, name.encode(), C.byref(ms), C.byref(n)))
+        return ms.value, int(n.value)
 
     def probe_fma_peak(self):
         a, b = C.c_double(0), C.c_double(0)
@@ -323,6 +339,10 @@ class BAWindow:
         self.ctx.check(self.lib.vio360_ba_build_reduced_system(self.h, _ptr(D), int(apply_loss), _ptr(S), _ptr(rhs),
                                                                C.byref(cost)))
         return S, rhs, cost.value
+
+    def set_lm_diagonal(self, lm_diag):
+        D = None if lm_diag is None else np.ascontiguousarray(lm_diag, np.float64)
+        self.ctx.check(self.lib.vio360_ba_set_lm_diagonal(self.h, _ptr(D)))
 
     def reduced_system_dev(self):
         p = C.c_void_p(); n = C.c_size_t(0)

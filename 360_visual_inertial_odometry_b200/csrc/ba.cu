@@ -586,7 +586,9 @@ extern "C" int vio360_ba_set_parameters(vio360_ba* ba, const double* pose_delta,
 
 static int sum_partials(vio360_ba* ba, int nblocks, double* dev_out) {
     vio360_ctx* ctx = ba->ctx;
+    { KernelTimer kt_(ctx, "k_sum_partials");
     k_sum_partials<<<1, 256, 0, ctx->stream>>>(ba->d_partials.as<double>(), nblocks, dev_out);
+    }
     VIO_LAUNCH_CHECK(ctx);
     return VIO360_OK;
 }
@@ -604,11 +606,15 @@ extern "C" int vio360_ba_evaluate(vio360_ba* ba, int want_jacobians, int apply_l
     VIO_CUDA(ctx, ba->d_partials.reserve((size_t)(nb + 1) * 8));
     BaDev d = make_dev(ba);
     if (want_jacobians)
+        { KernelTimer kt_(ctx, "k_evaluate");
         k_evaluate<true><<<nb, 128, 0, ctx->stream>>>(d, apply_loss != 0, ba->d_r.as<double>(), ba->d_Jp.as<double>(),
                                                      ba->d_Jl.as<double>(), ba->d_partials.as<double>());
+        }
     else
+        { KernelTimer kt_(ctx, "k_evaluate");
         k_evaluate<false><<<nb, 128, 0, ctx->stream>>>(d, apply_loss != 0, ba->d_r.as<double>(), nullptr, nullptr,
                                                       ba->d_partials.as<double>());
+        }
     VIO_LAUNCH_CHECK(ctx);
     int rc = sum_partials(ba, nb, ba->d_partials.as<double>() + nb);
     if (rc) return rc;
@@ -644,9 +650,13 @@ static int run_blocks(vio360_ba* ba, int apply_loss) {
     double* Hpp = ba->d_blocks.as<double>(); double* bp = Hpp + K * 36; double* Hll = bp + K * 6;
     double* bl = Hll + M * 9; double* Hpl = bl + M * 3;
     BaDev d = make_dev(ba);
+    { KernelTimer kt_(ctx, "k_blocks_landmark");
     k_blocks_landmark<<<(int)((M * 32 + 127) / 128), 128, 0, ctx->stream>>>(d, apply_loss != 0, Hll, bl, Hpl);
+    }
     VIO_LAUNCH_CHECK(ctx);
+    { KernelTimer kt_(ctx, "k_blocks_pose");
     k_blocks_pose<<<(int)K, 256, 0, ctx->stream>>>(d, apply_loss != 0, false, Hpp, bp);
+    }
     VIO_LAUNCH_CHECK(ctx);
     return VIO360_OK;
 }
@@ -690,6 +700,22 @@ extern "C" int vio360_ba_column_sqnorm(vio360_ba* ba, int apply_loss, double* ou
     return VIO360_OK;
 }
 
+extern "C" int vio360_ba_set_lm_diagonal(vio360_ba* ba, const double* lm_diag) {
+    if (!ba) return VIO360_ERR_INVALID;
+    vio360_ctx* ctx = ba->ctx;
+    if (!ba->has_structure) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_set_lm_diagonal before ba_set_structure");
+    ba->use_D = lm_diag != nullptr;
+    if (!lm_diag) return VIO360_OK;
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t nb = (6 * (size_t)ba->K + 3 * (size_t)ba->M) * 8;
+    VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));   // pinned staging may still be in flight
+    VIO_CUDA(ctx, ba->pin.reserve(nb));
+    memcpy(ba->pin.p, lm_diag, nb);
+    VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_D.p, ba->pin.p, nb, cudaMemcpyHostToDevice, ctx->stream));
+    VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return VIO360_OK;
+}
+
 extern "C" int vio360_ba_reduced_dim(const vio360_ba* ba) { return ba ? 6 * ba->n_free : VIO360_ERR_INVALID; }
 
 extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_diag, int apply_loss, double* S,
@@ -703,11 +729,9 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
     const size_t packed = (size_t)n * n + n + 1;
     VIO_CUDA(ctx, ba->d_packed.reserve(packed * 8));
     cudaStream_t st = ctx->stream;
-    ba->use_D = lm_diag != nullptr;
     if (lm_diag) {
-        VIO_CUDA(ctx, ba->pin.reserve((6 * K + 3 * M) * 8));
-        memcpy(ba->pin.p, lm_diag, (6 * K + 3 * M) * 8);
-        VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_D.p, ba->pin.p, (6 * K + 3 * M) * 8, cudaMemcpyHostToDevice, st));
+        int rcD = vio360_ba_set_lm_diagonal(ba, lm_diag);
+        if (rcD) return rcD;
     }
     VIO_CUDA(ctx, cudaMemsetAsync(ba->d_packed.p, 0, packed * 8, st));
     double* dS = ba->d_packed.as<double>(); double* drhs = dS + (size_t)n * n; double* dcost = drhs + n;
@@ -715,19 +739,22 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
     const int nb = std::max(1, (nlm * 32 + 127) / 128);
     VIO_CUDA(ctx, ba->d_partials.reserve((size_t)(nb + 1) * 8));
     BaDev d = make_dev(ba);
+    { KernelTimer kt_(ctx, "k_schur_warp");
     k_schur_warp<<<nb, 128, 0, st>>>(d, ba->lm_begin, ba->lm_end, apply_loss != 0, dS, n, drhs, ba->d_partials.as<double>());
+    }
     VIO_LAUNCH_CHECK(ctx);
     int rc = sum_partials(ba, nb, dcost);
     if (rc) return rc;
     if (n > 0) {
+        { KernelTimer kt_(ctx, "k_finish_S");
         k_finish_S<<<(n * n + 255) / 256, 256, 0, st>>>(dS, n, ba->use_D ? ba->d_D.as<double>() : nullptr,
                                                        ba->d_free_map.as<int>(), ba->K, ba->shard_rank == 0);
+        }
         VIO_LAUNCH_CHECK(ctx);
     }
     ba->has_reduced = true;
     if (S || rhs || cost) return vio360_ba_fetch_reduced_system(ba, S, rhs, cost);
-    VIO_CUDA(ctx, cudaStreamSynchronize(st));   // pinned staging of lm_diag is reused by later calls
-    return VIO360_OK;
+    return VIO360_OK;   // asynchronous on the context's stream
 }
 
 extern "C" int vio360_ba_reduced_system_dev(vio360_ba* ba, double** packed_dev, size_t* n_doubles) {

@@ -27,6 +27,25 @@ struct vio360_ctx {
     // small pinned + device scratch used to ship descriptor tables
     void* pinned = nullptr;
     size_t pinned_bytes = 0;
+    // optional per-kernel CUDA-event timing (bench.py's roofline numbers)
+    bool timing = false;
+    struct TimedLaunch { const char* name; cudaEvent_t e0, e1; };
+    std::vector<TimedLaunch> timed;
+    std::vector<cudaEvent_t> event_pool;
+    std::unordered_map<std::string, std::pair<double, long long>> kernel_ms;   // name -> (total ms, launches)
+};
+
+// Brackets one kernel launch with events on the context's stream when timing is on.
+struct KernelTimer {
+    vio360_ctx* ctx; size_t idx; bool on;
+    KernelTimer(vio360_ctx* c, const char* name) : ctx(c), idx(0), on(c->timing) {
+        if (!on) return;
+        auto get = [&]() { cudaEvent_t e; if (!ctx->event_pool.empty()) { e = ctx->event_pool.back(); ctx->event_pool.pop_back(); } else cudaEventCreate(&e); return e; };
+        vio360_ctx::TimedLaunch t{name, get(), get()};
+        cudaEventRecord(t.e0, ctx->stream);
+        ctx->timed.push_back(t); idx = ctx->timed.size() - 1;
+    }
+    ~KernelTimer() { if (on) cudaEventRecord(ctx->timed[idx].e1, ctx->stream); }
 };
 
 inline int vio360_fail(vio360_ctx* ctx, int code, const char* fmt, ...) {

@@ -44,6 +44,8 @@ extern "C" void vio360_destroy(vio360_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     vio360_fe_release(ctx);
+    for (auto& t : ctx->timed) { cudaEventDestroy(t.e0); cudaEventDestroy(t.e1); }
+    for (auto e : ctx->event_pool) cudaEventDestroy(e);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -53,6 +55,46 @@ extern "C" int vio360_synchronize(vio360_ctx* ctx) {
     if (!ctx) return VIO360_ERR_INVALID;
     VIO_CUDA(ctx, cudaSetDevice(ctx->device));
     VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return VIO360_OK;
+}
+
+extern "C" int vio360_enable_kernel_timing(vio360_ctx* ctx, int on) {
+    if (!ctx) return VIO360_ERR_INVALID;
+    ctx->timing = on != 0;
+    return VIO360_OK;
+}
+
+// folds finished launches into the per-name totals
+static int drain_timed(vio360_ctx* ctx) {
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (auto& t : ctx->timed) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, t.e0, t.e1) == cudaSuccess) {
+            auto& acc = ctx->kernel_ms[t.name];
+            acc.first += ms; acc.second += 1;
+        }
+        ctx->event_pool.push_back(t.e0); ctx->event_pool.push_back(t.e1);
+    }
+    ctx->timed.clear();
+    return VIO360_OK;
+}
+
+extern "C" int vio360_kernel_time(vio360_ctx* ctx, const char* name, double* total_ms, long long* launches) {
+    if (!ctx || !name) return VIO360_ERR_INVALID;
+    int rc = drain_timed(ctx);
+    if (rc) return rc;
+    auto it = ctx->kernel_ms.find(name);
+    if (total_ms) *total_ms = it == ctx->kernel_ms.end() ? 0.0 : it->second.first;
+    if (launches) *launches = it == ctx->kernel_ms.end() ? 0 : it->second.second;
+    return VIO360_OK;
+}
+
+extern "C" int vio360_reset_kernel_times(vio360_ctx* ctx) {
+    if (!ctx) return VIO360_ERR_INVALID;
+    int rc = drain_timed(ctx);
+    if (rc) return rc;
+    ctx->kernel_ms.clear();
     return VIO360_OK;
 }
 

@@ -35,7 +35,14 @@ struct vio360_fe_state {
     uint64_t clock = 0, batch_tag = 0;
     // tracking pools
     DevBuf d_jobs, d_pyrjobs, d_pts_in, d_pts_out, d_status, d_err, d_keep;
-    PinBuf h_jobs, h_pyrjobs, h_pts_in, h_out;
+    PinBuf h_pts_in, h_out;
+    // ring of pinned descriptor staging so that device-space calls never wait for the stream
+    struct Stage { PinBuf jobs, pyrjobs; cudaEvent_t ev = nullptr; bool used = false; };
+    Stage stage[4];
+    DevBuf d_jobs_ring[4], d_pyrjobs_ring[4];
+    unsigned stage_idx = 0;
+    Stage* cur_stage = nullptr;
+    int cur_stage_i = 0;
     // detection pools
     DevBuf d_djobs, d_eig, d_mask, d_small, d_cand, d_cand_sorted, d_grid, d_cub, d_corners;
     PinBuf h_djobs, h_dout;
@@ -51,8 +58,11 @@ void vio360_fe_release(vio360_ctx* ctx) {
                     &s->d_djobs, &s->d_eig, &s->d_mask, &s->d_small, &s->d_cand, &s->d_cand_sorted, &s->d_grid,
                     &s->d_cub, &s->d_corners};
     for (DevBuf* b : db) b->release();
-    PinBuf* pb[] = {&s->h_jobs, &s->h_pyrjobs, &s->h_pts_in, &s->h_out, &s->h_djobs, &s->h_dout};
+    PinBuf* pb[] = {&s->h_pts_in, &s->h_out, &s->h_djobs, &s->h_dout};
     for (PinBuf* b : pb) b->release();
+    for (auto& sg : s->stage) { sg.jobs.release(); sg.pyrjobs.release(); if (sg.ev) cudaEventDestroy(sg.ev); }
+    for (auto& d : s->d_jobs_ring) d.release();
+    for (auto& d : s->d_pyrjobs_ring) d.release();
     delete s;
     ctx->fe = nullptr;
 }
@@ -97,15 +107,32 @@ extern "C" int vio360_fe_configure(vio360_ctx* ctx, int width, int height, int m
         for (int l = 0; l < L; ++l) { sl.own[l] = sl.mem.as<uint8_t>() + s->loff[l]; sl.p[l] = sl.own[l]; sl.pitch[l] = s->lpitch[l]; }
     }
     const size_t np = (size_t)max_points * max_batch;
-    VIO_CUDA(ctx, s->d_jobs.reserve(sizeof(TrackJobDev) * (size_t)max_batch));
-    VIO_CUDA(ctx, s->h_jobs.reserve(sizeof(TrackJobDev) * (size_t)max_batch));
-    VIO_CUDA(ctx, s->d_pyrjobs.reserve(sizeof(PyrJob) * (size_t)2 * max_batch * kMaxLevels));
-    VIO_CUDA(ctx, s->h_pyrjobs.reserve(sizeof(PyrJob) * (size_t)2 * max_batch * kMaxLevels));
+    for (int i = 0; i < 4; ++i) {
+        VIO_CUDA(ctx, s->stage[i].jobs.reserve(sizeof(TrackJobDev) * (size_t)max_batch));
+        VIO_CUDA(ctx, s->stage[i].pyrjobs.reserve(sizeof(PyrJob) * (size_t)2 * max_batch * kMaxLevels));
+        VIO_CUDA(ctx, cudaEventCreateWithFlags(&s->stage[i].ev, cudaEventDisableTiming));
+        VIO_CUDA(ctx, s->d_jobs_ring[i].reserve(sizeof(TrackJobDev) * (size_t)max_batch));
+        VIO_CUDA(ctx, s->d_pyrjobs_ring[i].reserve(sizeof(PyrJob) * (size_t)2 * max_batch * kMaxLevels));
+    }
     VIO_CUDA(ctx, s->d_pts_in.reserve(np * 8)); VIO_CUDA(ctx, s->d_pts_out.reserve(np * 8));
     VIO_CUDA(ctx, s->d_status.reserve(np)); VIO_CUDA(ctx, s->d_err.reserve(np * 4)); VIO_CUDA(ctx, s->d_keep.reserve(np));
     VIO_CUDA(ctx, s->h_pts_in.reserve(np * 8));
     VIO_CUDA(ctx, s->h_out.reserve(np * (8 + 1 + 4 + 1)));
     s->configured = true;
+    return VIO360_OK;
+}
+
+// Picks the next pinned descriptor stage; waits only for the copies that last used it.
+static int begin_stage(vio360_ctx* ctx) {
+    vio360_fe_state* s = ctx->fe;
+    s->cur_stage_i = (int)(s->stage_idx++ & 3u);
+    s->cur_stage = &s->stage[s->cur_stage_i];
+    if (s->cur_stage->used) VIO_CUDA(ctx, cudaEventSynchronize(s->cur_stage->ev));
+    s->cur_stage->used = true;
+    return VIO360_OK;
+}
+static int end_stage(vio360_ctx* ctx) {
+    VIO_CUDA(ctx, cudaEventRecord(ctx->fe->cur_stage->ev, ctx->stream));
     return VIO360_OK;
 }
 
@@ -159,7 +186,8 @@ static int build_pyramids(vio360_ctx* ctx, const std::vector<int>& todo) {
     vio360_fe_state* s = ctx->fe;
     if (todo.empty() || s->nlevels <= 1) { for (int i : todo) s->slots[i].has_pyramid = true; return VIO360_OK; }
     const int nb = (int)todo.size();
-    PyrJob* hj = s->h_pyrjobs.as<PyrJob>();
+    PyrJob* hj = s->cur_stage->pyrjobs.as<PyrJob>();
+    PyrJob* dj = s->d_pyrjobs_ring[s->cur_stage_i].as<PyrJob>();
     for (int l = 0; l + 1 < s->nlevels; ++l)
         for (int b = 0; b < nb; ++b) {
             FeSlot& sl = s->slots[todo[b]];
@@ -167,11 +195,13 @@ static int build_pyramids(vio360_ctx* ctx, const std::vector<int>& todo) {
             j.src = sl.p[l]; j.spitch = sl.pitch[l]; j.dst = sl.own[l + 1]; j.dpitch = s->lpitch[l + 1];
         }
     const size_t bytes = sizeof(PyrJob) * (size_t)nb * (s->nlevels - 1);
-    VIO_CUDA(ctx, cudaMemcpyAsync(s->d_pyrjobs.p, hj, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    VIO_CUDA(ctx, cudaMemcpyAsync(dj, hj, bytes, cudaMemcpyHostToDevice, ctx->stream));
     for (int l = 0; l + 1 < s->nlevels; ++l) {
         const int dw = s->lw[l + 1], dh = s->lh[l + 1];
         dim3 grid((dw + kPyrTW - 1) / kPyrTW, (dh + kPyrTH - 1) / kPyrTH, nb);
-        k_pyr_down<<<grid, 256, 0, ctx->stream>>>(s->d_pyrjobs.as<PyrJob>() + (size_t)l * nb, s->lw[l], s->lh[l], dw, dh);
+        { KernelTimer kt_(ctx, "k_pyr_down");
+        k_pyr_down<<<grid, 256, 0, ctx->stream>>>(dj + (size_t)l * nb, s->lw[l], s->lh[l], dw, dh);
+        }
         VIO_LAUNCH_CHECK(ctx);
     }
     for (int i : todo) s->slots[i].has_pyramid = true;
@@ -198,11 +228,14 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
     if (!jobs || n_jobs < 0 || n_jobs > s->max_batch) return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_track_batch: bad job count");
     if (n_jobs == 0) return VIO360_OK;
     VIO_CUDA(ctx, cudaSetDevice(ctx->device));
-    // pinned staging is shared between calls: wait for the previous call's copies
-    VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    // host-space calls share one pinned point staging block: wait for the previous call
+    if (mem_space == VIO360_MEM_HOST) VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    int rc0 = begin_stage(ctx);
+    if (rc0) return rc0;
     s->batch_tag++;
     std::vector<int> todo;
-    TrackJobDev* hj = s->h_jobs.as<TrackJobDev>();
+    TrackJobDev* hj = s->cur_stage->jobs.as<TrackJobDev>();
+    TrackJobDev* dj = s->d_jobs_ring[s->cur_stage_i].as<TrackJobDev>();
     int max_n = 0;
     size_t off = 0;
     for (int b = 0; b < n_jobs; ++b) {
@@ -242,14 +275,17 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
     }
     int rc = build_pyramids(ctx, todo);
     if (rc) return rc;
-    if (max_n == 0) return VIO360_OK;
+    if (max_n == 0) return end_stage(ctx);
     cudaStream_t st = ctx->stream;
-    VIO_CUDA(ctx, cudaMemcpyAsync(s->d_jobs.p, hj, sizeof(TrackJobDev) * (size_t)n_jobs, cudaMemcpyHostToDevice, st));
+    VIO_CUDA(ctx, cudaMemcpyAsync(dj, hj, sizeof(TrackJobDev) * (size_t)n_jobs, cudaMemcpyHostToDevice, st));
     if (mem_space == VIO360_MEM_HOST)
         VIO_CUDA(ctx, cudaMemcpyAsync(s->d_pts_in.p, s->h_pts_in.p, off * 8, cudaMemcpyHostToDevice, st));
     dim3 grid((max_n + kLkWarps - 1) / kLkWarps, n_jobs);
-    k_lk_track<<<grid, kLkWarps * 32, 0, st>>>(s->d_jobs.as<TrackJobDev>(), lk_params(s));
+    { KernelTimer kt_(ctx, "k_lk_track");
+    k_lk_track<<<grid, kLkWarps * 32, 0, st>>>(dj, lk_params(s));
+    }
     VIO_LAUNCH_CHECK(ctx);
+    if ((rc = end_stage(ctx))) return rc;
     if (mem_space == VIO360_MEM_HOST) {
         // one pinned block: [xy off*8 | err off*4 | status off | keep off]
         uint8_t* ho = s->h_out.as<uint8_t>();
@@ -297,12 +333,14 @@ extern "C" int vio360_fe_pyramid(vio360_ctx* ctx, const uint8_t* img, size_t pit
         return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_pyramid: bad arguments");
     VIO_CUDA(ctx, cudaSetDevice(ctx->device));
     VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    int rc = begin_stage(ctx);
+    if (rc) return rc;
     s->batch_tag++;
     bool hit; int idx;
-    int rc = acquire_slot(ctx, 0, &hit, &idx);
-    if (rc) return rc;
+    if ((rc = acquire_slot(ctx, 0, &hit, &idx))) return rc;
     if ((rc = load_frame(ctx, idx, img, pitch, VIO360_MEM_HOST))) return rc;
     if ((rc = build_pyramids(ctx, std::vector<int>{idx}))) return rc;
+    if ((rc = end_stage(ctx))) return rc;
     const FeSlot& sl = s->slots[idx];
     for (int l = 0; l < n_levels; ++l)
         VIO_CUDA(ctx, cudaMemcpy2DAsync(out[l], out_pitch[l], sl.p[l], sl.pitch[l], s->lw[l], s->lh[l], cudaMemcpyDeviceToHost, ctx->stream));
@@ -395,9 +433,13 @@ extern "C" int vio360_fe_detect_batch(vio360_ctx* ctx, const vio360_detect_job* 
     VIO_CUDA(ctx, cudaMemcpyAsync(s->d_djobs.p, hj, sizeof(DetectJobDev) * (size_t)n_jobs, cudaMemcpyHostToDevice, st));
     const DetectParams P = detect_params(s);
     const DetectJobDev* dj = s->d_djobs.as<DetectJobDev>();
+    { KernelTimer kt_(ctx, "k_min_eig");
     k_min_eig<<<dim3((s->W + kEigCols - 1) / kEigCols, n_jobs), kEigThreads, 0, st>>>(dj, P);
+    }
     VIO_LAUNCH_CHECK(ctx);
+    { KernelTimer kt_(ctx, "k_candidates");
     k_candidates<<<dim3((s->W - 2 + 31) / 32, (s->H - 2 + 7) / 8, n_jobs), 256, 0, st>>>(dj, P, quality);
+    }
     VIO_LAUNCH_CHECK(ctx);
     // sort each job's candidates by (value, raster index) descending; the count lives on the
     // device, so sort the whole zero-padded buffer (zeros sort last)
@@ -417,7 +459,9 @@ extern "C" int vio360_fe_detect_batch(vio360_ctx* ctx, const vio360_detect_job* 
         hj[b].cand = outk;
     }
     VIO_CUDA(ctx, cudaMemcpyAsync(s->d_djobs.p, hj, sizeof(DetectJobDev) * (size_t)n_jobs, cudaMemcpyHostToDevice, st));
+    { KernelTimer kt_(ctx, "k_select");
     k_select<<<n_jobs, 32, 0, st>>>(dj, P, max_corners, min_dist);
+    }
     VIO_LAUNCH_CHECK(ctx);
     if (mem_space == VIO360_MEM_HOST) {
         uint8_t* ho = s->h_dout.as<uint8_t>();
@@ -466,7 +510,9 @@ extern "C" int vio360_fe_min_eigen_val(vio360_ctx* ctx, const uint8_t* img, size
     hj->eig = s->d_eig.as<float>();
     hj->max_bits = s->d_small.as<unsigned int>(); hj->n_cand = hj->max_bits + 1; hj->out_n = (int*)(hj->max_bits + 2);
     VIO_CUDA(ctx, cudaMemcpyAsync(s->d_djobs.p, hj, sizeof(DetectJobDev), cudaMemcpyHostToDevice, st));
+    { KernelTimer kt_(ctx, "k_min_eig");
     k_min_eig<<<dim3((s->W + kEigCols - 1) / kEigCols, 1), kEigThreads, 0, st>>>(s->d_djobs.as<DetectJobDev>(), detect_params(s));
+    }
     VIO_LAUNCH_CHECK(ctx);
     VIO_CUDA(ctx, cudaMemcpyAsync(out, s->d_eig.p, (size_t)s->W * s->H * 4, cudaMemcpyDeviceToHost, st));
     VIO_CUDA(ctx, cudaStreamSynchronize(st));

@@ -1,0 +1,476 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the two hot paths on N B200s of one node.
+
+  python bench.py --gpus N --steps K --warmup W            (this repo's CUDA path)
+  python bench.py --impl reference --gpus N ...             (the reference's CPU path)
+
+Metric (BASELINE.json): ERP frames/s @3840x1920, 1000 features (config 2), with the BA
+factor-evaluation figure (observations/s, config 5 = 200 keyframes / 1M observations,
+plus config 3 at N=1) reported in the "ba" object of the same JSON line.
+
+One step of the headline path = one tracking pass over a batch of independent frame pairs
+(one per sequence, `--batch` sequences per GPU): pyramid of the new frame + pyramidal LK of
+1000 features; the previous frame's pyramid is cached on the device exactly as a sequence
+would have it.  Inputs (2 x batch frames per GPU = 0.94 GB) are far larger than L2.
+"""
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = "360_visual_inertial_odometry_b200"
+sys.path.insert(0, ROOT)
+
+W, H, NFEAT, LEVELS, WIN = 3840, 1920, 1000, 4, 21
+METRIC = "ERP tracking frames/s @3840x1920, 1000 features, 4-level pyramid, 21x21 KLT"
+
+
+def algorithmic_bytes():
+    pyr = 1.640625 * W * H                                   # SURVEY 8-D, K1 per new frame
+    lk = NFEAT * LEVELS * ((WIN + 2) ** 2 + (WIN + 1) ** 2) + 21 * NFEAT   # K3 per frame pair
+    return pyr, lk
+
+
+class ClockSampler(threading.Thread):
+    """samples nvidia-smi during the timed region (B200_PROFILING.md clocks line)"""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index; self.stop_flag = False; self.rows = []
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def measured_peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+def make_frames(torch, syn, batch, rank, device):
+    """2 x batch synthetic textured-sphere frames on the device (consecutive time steps)."""
+    ring = [[], []]
+    for s in range(batch):
+        seed = 360 + rank * batch + s
+        for t in (0, 1):
+            ring[t].append(syn.render_erp_frame(W, H, t, seed=seed, n_waves=24, sigma_omega=120.0, xp=torch, device=device))
+    return ring
+
+
+# =========================================================================== our arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    rank, local_rank, world = dist_env()
+    if args.gpus != world and world > 1:
+        pass
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+    b = importlib.import_module(PKG + ".bindings")
+    syn = importlib.import_module(PKG + ".synthetic")
+    ctx = b.Context(local_rank)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=device)
+    B = args.batch
+    ctx.fe_configure(W, H, max_points=NFEAT, max_batch=B)
+    ring = make_frames(torch, syn, B, rank, device)
+    pts_h = np.stack([syn.make_track_points(W, H, NFEAT, seed=1000 + rank * B + s) for s in range(B)])
+    pts_d = torch.from_numpy(pts_h).to(device)
+    out_xy = torch.zeros((B, NFEAT, 2), dtype=torch.float32, device=device)
+    out_st = torch.zeros((B, NFEAT), dtype=torch.uint8, device=device)
+    out_err = torch.zeros((B, NFEAT), dtype=torch.float32, device=device)
+    out_keep = torch.zeros((B, NFEAT), dtype=torch.uint8, device=device)
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ctx.synchronize()
+
+    key_base = [1 << 32]
+
+    dev_jobs = []
+    for par in range(2):      # job tables for even / odd steps; only the keys change per step
+        jobs = (b.TrackJob * B)()
+        for s in range(B):
+            j = jobs[s]
+            prev, cur = ring[par][s], ring[1 - par][s]
+            j.prev, j.prev_pitch, j.cur, j.cur_pitch = prev.data_ptr(), W, cur.data_ptr(), W
+            j.prev_xy, j.n = pts_d[s].data_ptr(), NFEAT
+            j.cur_xy, j.status, j.err, j.keep = out_xy[s].data_ptr(), out_st[s].data_ptr(), out_err[s].data_ptr(), out_keep[s].data_ptr()
+        dev_jobs.append(jobs)
+
+    def dev_step(i):
+        jobs = dev_jobs[i % 2]
+        for s in range(B):
+            jobs[s].prev_key = key_base[0] + i * B + s
+            jobs[s].cur_key = key_base[0] + (i + 1) * B + s
+        ctx.fe_track_batch_raw(jobs, B, b.MEM_DEVICE)
+
+    # ---- device-resident throughput ("value")
+    for i in range(args.warmup):
+        dev_step(i)
+    barrier()
+    ctx.enable_kernel_timing(True); ctx.reset_kernel_times()
+    l0 = ctx.launch_count
+    sampler = ClockSampler(local_rank); sampler.start()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for i in range(args.warmup, args.warmup + args.steps):
+        dev_step(i)
+    e1.record(stream)
+    barrier()
+    sampler.stop_flag = True
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    launches = ctx.launch_count - l0
+    lk_ms, lk_n = ctx.kernel_time("k_lk_track")
+    pyr_ms, pyr_n = ctx.kernel_time("k_pyr_down")
+    ctx.enable_kernel_timing(False)
+    frames = B * args.steps * world
+    value = frames / (ms_total * 1e-3)
+    tracked = int(out_st.sum().item())
+
+    # ---- end to end through the C ABI with pinned HOST buffers
+    e2e_steps = max(2, min(args.steps, 6))
+    hring = [[torch.empty((H, W), dtype=torch.uint8).pin_memory() for _ in range(B)] for _ in range(2)]
+    for t in range(2):
+        for s in range(B):
+            hring[t][s].copy_(ring[t][s])
+    hpts = torch.from_numpy(pts_h).pin_memory()
+    hxy = torch.zeros((B, NFEAT, 2), dtype=torch.float32).pin_memory()
+    hst = torch.zeros((B, NFEAT), dtype=torch.uint8).pin_memory()
+    herr = torch.zeros((B, NFEAT), dtype=torch.float32).pin_memory()
+    key_base[0] = 1 << 40
+
+    def host_step(i):
+        jobs = (b.TrackJob * B)()
+        for s in range(B):
+            j = jobs[s]
+            j.prev, j.prev_pitch, j.prev_key = hring[i % 2][s].data_ptr(), W, key_base[0] + i * B + s
+            j.cur, j.cur_pitch, j.cur_key = hring[(i + 1) % 2][s].data_ptr(), W, key_base[0] + (i + 1) * B + s
+            j.prev_xy, j.n = hpts[s].data_ptr(), NFEAT
+            j.cur_xy, j.status, j.err, j.keep = hxy[s].data_ptr(), hst[s].data_ptr(), herr[s].data_ptr(), None
+        ctx.fe_track_batch_raw(jobs, B, b.MEM_HOST)
+
+    host_step(0); host_step(1)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(2, 2 + e2e_steps):
+        host_step(i)
+    barrier()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_value = B * e2e_steps * world / float(e2e_s.item())
+    e2e_status_equal = bool((hst.to(device) == out_st).all().item()) if (args.warmup + args.steps - (2 + e2e_steps)) % 2 == 0 else None
+
+    # ---- roofline of the dominant kernel
+    hbm_peak, peak_src = measured_peaks()
+    pyr_b, lk_b = algorithmic_bytes()
+    dominant = "k_lk_track" if lk_ms >= pyr_ms else "k_pyr_down"
+    if dominant == "k_lk_track":
+        per_launch_bytes = lk_b * B; dur_ms = lk_ms / max(lk_n, 1)
+    else:
+        per_launch_bytes = pyr_b * B; dur_ms = pyr_ms / max(args.steps, 1)   # three level launches per step
+    achieved = per_launch_bytes / (dur_ms * 1e-3) / 1e9
+    frame_bytes = (pyr_b + lk_b) * B
+    step_ms = ms_total / args.steps
+    roofline = {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": per_launch_bytes, "avg_launch_ms": dur_ms,
+                "kernel_share_of_step": {"k_lk_track": lk_ms / ms_total, "k_pyr_down": pyr_ms / ms_total},
+                "tracking_frame": {"algorithmic_bytes_per_step": frame_bytes,
+                                   "achieved_gbs": frame_bytes / (step_ms * 1e-3) / 1e9,
+                                   "frac": frame_bytes / (step_ms * 1e-3) / 1e9 / hbm_peak},
+                "k_pyr_down": {"achieved_gbs": pyr_b * B / (pyr_ms / max(args.steps, 1) * 1e-3) / 1e9 if pyr_ms > 0 else None}}
+
+    line = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+            "data": "synthetic",
+            "config": {"workload": "configs[1]: ERP tracking 3840x1920, 4-level pyramid, 1000 features/frame, 21x21 KLT",
+                       "frames_per_step_per_gpu": B, "sequences": B * world, "sharding": "independent sequences, no collective",
+                       "l2": "inputs (2 x %d frames = %.2f GB per GPU) exceed the 126 MB L2" % (B, 2 * B * W * H / 1e9),
+                       "prev_pyramid": "cached on device (sequence mode)"},
+            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": B * (W * H + NFEAT * 8),
+                    "d2h_bytes_per_step": B * NFEAT * (8 + 4 + 1 + 1), "steps": e2e_steps,
+                    "note": "vio360_fe_track_batch with pinned host buffers; H2D of each new frame and D2H of results inside the timed region"},
+            "gpu_launches": launches, "roofline": roofline, "clocks": sampler.summary(),
+            "tracked_points_last_step": tracked, "e2e_status_equals_device_path": e2e_status_equal}
+
+    # ---- detection (reported separately)
+    if not args.skip_detect:
+        line["detect"] = bench_detect(ctx, b, torch, ring, B, world, device, barrier, stream)
+    # ---- BA factor evaluation
+    if not args.skip_ba:
+        line["ba"] = bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, args)
+    if rank == 0 and world == 1 and not args.skip_cpu:
+        line["cpu_baseline"] = cpu_baseline_tracking(ring, pts_h, torch)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(line))
+
+
+def bench_detect(ctx, b, torch, ring, B, world, device, barrier, stream):
+    nb = min(B, 16)
+    out_xy = torch.zeros((nb, 1000, 2), dtype=torch.float32, device=device)
+    out_n = (C.c_int * nb)()
+
+    def step():
+        jobs = (b.DetectJob * nb)()
+        for s in range(nb):
+            j = jobs[s]
+            j.img, j.pitch, j.key = ring[0][s].data_ptr(), W, 0
+            j.mask, j.mask_pitch = None, 0
+            j.out_xy, j.out_n = out_xy[s].data_ptr(), C.addressof(out_n) + 4 * s
+        ctx.fe_detect_batch_raw(jobs, nb, 1000, float(np.float32(0.01)), float(np.float32(30.0)), b.MEM_DEVICE)
+
+    step()
+    barrier()
+    ctx.enable_kernel_timing(True); ctx.reset_kernel_times()
+    t0 = time.perf_counter()
+    reps = 3
+    for _ in range(reps):
+        step()
+    barrier()
+    dt = (time.perf_counter() - t0) / reps
+    eig_ms, eig_n = ctx.kernel_time("k_min_eig")
+    ctx.enable_kernel_timing(False)
+    return {"metric": "ERP detection frames/s @3840x1920 (goodFeaturesToTrack, 1000 corners)", "value": nb * world / dt,
+            "unit": "frames/s", "frames_per_step_per_gpu": nb, "corners_first_frame": int(out_n[0]),
+            "k_min_eig_ms_per_launch": eig_ms / max(eig_n, 1)}
+
+
+def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, args):
+    fp64_peak, fp32_peak = ctx.probe_fma_peak()
+    res = {"metric": "BA factor evals (observations/s), fused residual+Jacobian+Huber+Schur blocks", "unit": "obs/s",
+           "fp64_peak_tflops_measured": fp64_peak, "dtype": "f64"}
+
+    def run(win, steps, warmup, sharded):
+        ba = b.BAWindow(ctx, win)
+        if sharded:
+            ba.set_shard(rank, world)
+        ba.set_parameters(win["pose_delta"], win["points"])
+        colsq = ba.column_sqnorm(True)
+        D = np.sqrt(np.clip(colsq, 1e-6, 1e32) / 1e4)
+        ba.set_lm_diagonal(D)
+        ba.build_reduced_system(None, True, fetch=False)
+        ptr, nd = ba.reduced_system_dev()
+
+        class _Buf:   # zero-copy torch view of the packed [S | rhs | cost] device buffer
+            __cuda_array_interface__ = {"shape": (nd,), "typestr": "<f8", "data": (ptr, False), "version": 2}
+        packed = torch.as_tensor(_Buf(), device=device)
+
+        def step():
+            ba.build_reduced_system(None, True, fetch=False)
+            if sharded and world > 1:
+                with torch.cuda.stream(stream):
+                    dist.all_reduce(packed)     # one allreduce of [S | rhs | cost]
+        for _ in range(warmup):
+            step()
+        barrier()
+        ctx.enable_kernel_timing(True); ctx.reset_kernel_times()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            step()
+        e1.record(stream)
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        k_ms, k_n = ctx.kernel_time("k_schur_warp")
+        ctx.enable_kernel_timing(False)
+        # end to end: parameters from the host, reduced system back to the host
+        t0 = time.perf_counter()
+        for _ in range(max(2, steps // 2)):
+            ba.set_parameters(win["pose_delta"], win["points"])
+            ba.build_reduced_system(D, True, fetch=not (sharded and world > 1))
+            if sharded and world > 1:
+                with torch.cuda.stream(stream):
+                    dist.all_reduce(packed)
+                ba.fetch_reduced_system()
+        barrier()
+        e2e_s = (time.perf_counter() - t0) / max(2, steps // 2)
+        S, rhs, cost = ba.fetch_reduced_system()
+        deg = np.bincount(win["point_idx"], minlength=win["M"]).astype(np.float64)
+        flops = 451.0 * win["O"] + float(np.sum(50 + 130 * deg + 216 * deg * (deg + 1) / 2))
+        out = {"O": int(win["O"]), "K": int(win["K"]), "M": int(win["M"]), "ms_per_step": float(ms.item()) / steps,
+               "value": win["O"] / (float(ms.item()) / steps * 1e-3), "e2e_value": win["O"] / e2e_s,
+               "algorithmic_flop_per_step": flops,
+               "roofline": {"bound": "fp64", "kernel": "k_schur_warp", "achieved": flops / world / (k_ms / max(k_n, 1) * 1e-3) / 1e12 if k_ms > 0 else None,
+                            "peak": fp64_peak, "unit": "TFLOP/s"},
+               "cost": cost, "S_trace": float(np.trace(S))}
+        if out["roofline"]["achieved"]:
+            out["roofline"]["frac"] = out["roofline"]["achieved"] / fp64_peak
+        ba.close()
+        return out
+
+    if world == 1:
+        win3 = syn.make_ba_window(K=10, M=2000, seed=20000, mid_iteration=True)
+        res["c3_local_window"] = run(win3, args.ba_steps * 4, 3, False)
+    win5 = syn.make_ba_window(K=200, M=50000, degree=20, seed=1000000, mid_iteration=True, loop_radius=6.0)
+    r5 = run(win5, args.ba_steps, 3, True)
+    res["c5_large_window"] = r5
+    res["value"] = r5["value"]; res["n_gpus"] = world
+    res["config"] = {"workload": "configs[4]: 200 keyframes, 1M observations, landmark-range sharding, NCCL allreduce of [S|rhs|cost]"}
+    if rank == 0 and world == 1 and not args.skip_cpu:
+        res["cpu_baseline"] = cpu_baseline_ba(syn, win5)
+    return res
+
+
+# ===================================================================== CPU baselines
+def cpu_baseline_tracking(ring, pts_h, torch, max_pairs=24, budget_s=25.0):
+    """cv2.calcOpticalFlowPyrLK = the reference's own CPU implementation of the path
+    (FeatureTracker.cpp:238-240), exact arguments, all host threads."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import cv2
+    import fe_oracle
+    n = min(len(ring[0]), 4)
+    pairs = [(ring[0][s].cpu().numpy(), ring[1][s].cpu().numpy(), pts_h[s]) for s in range(n)]
+    for p in pairs[:2]:
+        fe_oracle.cv2_lk_track(*p)
+    t0 = time.perf_counter(); done = 0
+    while done < max_pairs and time.perf_counter() - t0 < budget_s:
+        fe_oracle.cv2_lk_track(*pairs[done % n]); done += 1
+    dt = time.perf_counter() - t0
+    return {"value": done / dt, "unit": "frames/s", "cores": int(cv2.getNumThreads()), "kind": "reference",
+            "sample": "%d calls of cv2.calcOpticalFlowPyrLK %s (both pyramids rebuilt per call, as the reference does) on the same synthetic frames" % (done, cv2.__version__),
+            "host_cpus": os.cpu_count()}
+
+
+def cpu_baseline_ba(syn, win5):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import ba_oracle
+    nthreads = min(4, os.cpu_count() or 1)     # the reference's options.num_threads = 4 (Optimizer.cpp:79)
+    sub_M = 5000                                # bounded sample: the first 5000 landmarks (100k observations)
+    keep = win5["point_idx"] < sub_M
+    sub = dict(win5, M=sub_M, O=int(keep.sum()), pose_idx=np.ascontiguousarray(win5["pose_idx"][keep]),
+               point_idx=np.ascontiguousarray(win5["point_idx"][keep]), obs_u=np.ascontiguousarray(win5["obs_u"][keep]),
+               obs_v=np.ascontiguousarray(win5["obs_v"][keep]), outlier=np.ascontiguousarray(win5["outlier"][keep]),
+               points=np.ascontiguousarray(win5["points"][:sub_M]), point_fixed=np.ascontiguousarray(win5["point_fixed"][:sub_M]))
+    Wo = ba_oracle.Window(sub)
+    r, Jp, Jl, _ = Wo.evaluate(sub["pose_delta"], sub["points"], nthreads=nthreads)
+    D = Wo.lm_diagonal(Jp, Jl)
+    t0 = time.perf_counter(); reps = 0
+    while reps < 20 and time.perf_counter() - t0 < 20.0:
+        r, Jp, Jl, _ = Wo.evaluate(sub["pose_delta"], sub["points"], nthreads=nthreads)
+        Wo.schur(r, Jp, Jl, D); reps += 1
+    dt = (time.perf_counter() - t0) / reps
+    t0 = time.perf_counter()
+    for _ in range(3):
+        r, Jp, Jl, _ = Wo.evaluate(sub["pose_delta"], sub["points"], nthreads=nthreads, hoisted=True)
+        Wo.schur(r, Jp, Jl, D)
+    dth = (time.perf_counter() - t0) / 3
+    return {"value": sub["O"] / dt, "unit": "obs/s", "cores": nthreads, "kind": "port",
+            "sample": "%d observations (first %d landmarks of the 1M window), per-factor 6-SVD pose chain as the reference executes it + Huber + Schur elimination (C restatement, Schur single-threaded)" % (sub["O"], sub_M),
+            "hoisted_pose_chain_value": sub["O"] / dth}
+
+
+# ================================================================= reference arm
+def run_reference(args):
+    rank, local_rank, world = dist_env()
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import cv2
+    import fe_oracle
+    syn = importlib.import_module(PKG + ".synthetic")
+    n_pairs = 4
+    try:
+        import torch
+        use_cuda = torch.cuda.is_available()
+    except Exception:
+        use_cuda = False
+    frames = []
+    for s in range(n_pairs):
+        for t in (0, 1):
+            if use_cuda:
+                frames.append(syn.render_erp_frame(W, H, t, seed=360 + s, n_waves=24, sigma_omega=120.0, xp=torch, device="cuda").cpu().numpy())
+            else:
+                frames.append(syn.render_erp_frame(W, H, t, seed=360 + s, n_waves=8, sigma_omega=120.0))
+    pts = [syn.make_track_points(W, H, NFEAT, seed=1000 + s) for s in range(n_pairs)]
+
+    def step():
+        for s in range(n_pairs):
+            fe_oracle.cv2_lk_track(frames[2 * s], frames[2 * s + 1], pts[s])
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    value = n_pairs * args.steps / dt
+    sample = "each step = %d calls of cv2.calcOpticalFlowPyrLK %s with the reference's arguments (FeatureTracker.cpp:238-240)" % (n_pairs, cv2.__version__)
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "configs[1]: ERP tracking 3840x1920, 4-level pyramid, 1000 features/frame, 21x21 KLT",
+                       "frames_per_step": n_pairs, "note": "rank 0 only; the reference has no multi-GPU or multi-process path"},
+            "cpu_baseline": {"value": value, "unit": "frames/s", "cores": int(cv2.getNumThreads()), "kind": "reference", "sample": sample},
+            "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=64, help="independent sequences (frame pairs) per GPU per step")
+    ap.add_argument("--ba-steps", type=int, default=5)
+    ap.add_argument("--skip-ba", action="store_true")
+    ap.add_argument("--skip-detect", action="store_true")
+    ap.add_argument("--skip-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -46,6 +46,13 @@ int vio360_synchronize(vio360_ctx* ctx);
 void* vio360_stream(vio360_ctx* ctx);                 /* the context's cudaStream_t */
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 long long vio360_launch_count(const vio360_ctx* ctx);
+/* Per-kernel device timing: when enabled, every kernel launch of this context is bracketed
+ * by CUDA events on the context's stream.  vio360_kernel_time() synchronises and returns
+ * the accumulated duration and launch count of the kernel called `name` (e.g.
+ * "k_lk_track", "k_pyr_down", "k_schur_tile").                                        */
+int vio360_enable_kernel_timing(vio360_ctx* ctx, int on);
+int vio360_kernel_time(vio360_ctx* ctx, const char* name, double* total_ms, long long* launches);
+int vio360_reset_kernel_times(vio360_ctx* ctx);
 /* measured FP64 / FP32 FMA pipe peak of the device in TFLOP/s (dependent-FMA loops on
  * all SMs), the denominator SURVEY.md section 8-D asks for.                        */
 int vio360_probe_fma_peak(vio360_ctx* ctx, double* fp64_tflops, double* fp32_tflops);
@@ -168,13 +175,16 @@ int vio360_ba_reduced_dim(const vio360_ba* ba);
 /* Replaces SchurEliminator<2,3,6>::Eliminate (thirdparty/ceres-solver/internal/ceres/
  * schur_eliminator_impl.h:179-308) fused with the factor evaluation: builds
  * S = F'F + Dp^2 - F'E (E'E + Dl^2)^-1 E'F and rhs = F'r - F'E (E'E + Dl^2)^-1 E'r at
- * the current parameters.  lm_diag (6K + 3M, pose part first; NULL = 0) is the
- * Levenberg-Marquardt diagonal of levenberg_marquardt_strategy.cc:78-89.  S (n x n
+ * the current parameters.  lm_diag (6K + 3M, pose part first) is the Levenberg-Marquardt
+ * diagonal of levenberg_marquardt_strategy.cc:78-89; NULL = keep the diagonal installed by
+ * vio360_ba_set_lm_diagonal (none by default).  S (n x n
  * dense row-major, full symmetric) / rhs (n) / cost may be NULL: the result then stays
  * on the device (see vio360_ba_reduced_system_dev).  With a shard set, the result is
  * the shard's partial sum.                                                           */
 int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_diag, int apply_loss,
                                    double* S, double* rhs, double* cost);
+/* Installs (or, with NULL, clears) the LM diagonal used by later build calls. */
+int vio360_ba_set_lm_diagonal(vio360_ba* ba, const double* lm_diag);
 /* Device view of the last reduced system as ONE packed buffer [S n*n | rhs n | cost 1]
  * so that a single ncclAllReduce(sum, double) combines the shards.  */
 int vio360_ba_reduced_system_dev(vio360_ba* ba, double** packed_dev, size_t* n_doubles);
