@@ -1,0 +1,75 @@
+// FeatureTrackerCuda.cpp -- see FeatureTrackerCuda.h.
+#include "FeatureTrackerCuda.h"
+
+#include <stdexcept>
+
+namespace vio_360 {
+
+void FeatureTrackerCuda::check(int rc, const char* what) const {
+    if (rc != VIO360_OK)
+        throw std::runtime_error(std::string(what) + ": " + vio360_last_error(m_ctx));
+}
+
+FeatureTrackerCuda::FeatureTrackerCuda(int width, int height, int max_features, float min_distance,
+                                       float quality_level, int boundary_margin, int device)
+    : m_width(width), m_height(height), m_max_features(max_features), m_min_distance(min_distance),
+      m_quality_level(quality_level), m_boundary_margin(boundary_margin) {
+    if (vio360_create(device, &m_ctx) != VIO360_OK)
+        throw std::runtime_error(std::string("FeatureTrackerCuda: ") + vio360_last_error(nullptr));
+    ensure_capacity(max_features > 0 ? max_features : 1);
+}
+
+FeatureTrackerCuda::~FeatureTrackerCuda() { vio360_destroy(m_ctx); }
+
+void FeatureTrackerCuda::ensure_capacity(int n_points) {
+    if (n_points <= m_point_capacity) return;
+    m_point_capacity = n_points;
+    // FeatureTracker.cpp:33-35: window 21x21, maxLevel 3, TermCriteria(EPS|COUNT, 30, 0.01f); the float
+    // epsilon widens to double and doubles as minEigThreshold (:240).  Polar ratio 0.15 (Camera.h:76,84).
+    const double eps = (double)0.01f;
+    check(vio360_fe_configure(m_ctx, m_width, m_height, 3, 21, 30, eps, eps, 0.15f, m_boundary_margin,
+                              m_point_capacity, 1),
+          "vio360_fe_configure");
+}
+
+std::vector<cv::Point2f> FeatureTrackerCuda::DetectNewFeatures(const cv::Mat& image, const cv::Mat& mask) {
+    if (image.empty() || image.cols != m_width || image.rows != m_height)
+        throw std::runtime_error("FeatureTrackerCuda::DetectNewFeatures: image must be 8-bit single channel of the configured size");
+    std::vector<cv::Point2f> corners((size_t)(m_max_features > 0 ? m_max_features : 0));
+    int n = 0;
+    if (m_max_features <= 0) return corners;
+    static_assert(sizeof(cv::Point2f) == 2 * sizeof(float), "Point2f must be two packed floats");
+    check(vio360_fe_detect(m_ctx, image.data, (size_t)image.step, m_curr_key, mask.empty() ? nullptr : mask.data,
+                           mask.empty() ? 0 : (size_t)mask.step, m_max_features, (double)m_quality_level,
+                           (double)m_min_distance, reinterpret_cast<float*>(corners.data()), &n),
+          "vio360_fe_detect");
+    corners.resize((size_t)n);
+    m_num_detected = n;
+    return corners;
+}
+
+int FeatureTrackerCuda::TrackOpticalFlow(const cv::Mat& prev_image, const cv::Mat& curr_image,
+                                         const std::vector<cv::Point2f>& prev_points,
+                                         std::vector<cv::Point2f>& curr_points, std::vector<uchar>& status) {
+    if (prev_points.empty()) return 0;   // FeatureTracker.cpp:233-235: outputs untouched
+    const int n = (int)prev_points.size();
+    ensure_capacity(n);
+    curr_points.resize((size_t)n);
+    status.resize((size_t)n);
+    m_keep.resize((size_t)n);
+    std::vector<float> error((size_t)n);   // the reference requests err and discards it (:237)
+    vio360_track_job job;
+    job.prev = prev_image.data; job.prev_pitch = (size_t)prev_image.step; job.prev_key = m_prev_key;
+    job.cur = curr_image.data; job.cur_pitch = (size_t)curr_image.step; job.cur_key = m_curr_key;
+    job.prev_xy = reinterpret_cast<const float*>(prev_points.data()); job.n = n;
+    job.cur_xy = reinterpret_cast<float*>(curr_points.data()); job.status = status.data();
+    job.err = error.data(); job.keep = m_keep.data();
+    check(vio360_fe_track_batch(m_ctx, &job, 1, VIO360_MEM_HOST), "vio360_fe_track_batch");
+    int num_tracked = 0;
+    for (size_t i = 0; i < status.size(); ++i)
+        if (status[i]) num_tracked++;
+    m_num_tracked = num_tracked;
+    return num_tracked;
+}
+
+}  // namespace vio_360

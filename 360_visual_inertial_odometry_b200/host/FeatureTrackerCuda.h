@@ -1,0 +1,74 @@
+// FeatureTrackerCuda.h -- drop-in for the two hot methods of vio_360::FeatureTracker
+// (reference: src/processing/FeatureTracker.h:54-83, src/processing/FeatureTracker.cpp).
+//
+//   std::vector<cv::Point2f> DetectNewFeatures(const cv::Mat& image, const cv::Mat& mask = cv::Mat());
+//   int TrackOpticalFlow(const cv::Mat& prev, const cv::Mat& cur, const std::vector<cv::Point2f>& prev_pts,
+//                        std::vector<cv::Point2f>& cur_pts, std::vector<uchar>& status);
+//
+// Same names, argument meaning and return values; the arithmetic runs in libvio360_cuda.so
+// through the C ABI (include/vio360.h).  There is no CPU fallback: construction throws
+// std::runtime_error when no B200-class device is usable, and every call throws on a C-ABI
+// error (the reference itself has no error channel; OpenCV would throw cv::Exception).
+// INTEGRATION.md shows the three-line change in FeatureTracker.cpp that routes the
+// reference through this class.
+#pragma once
+
+#include <cstdint>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/vio360.h"
+#include "cv_compat.h"
+
+namespace vio_360 {
+
+class FeatureTrackerCuda {
+public:
+    // Mirrors FeatureTracker::FeatureTracker (FeatureTracker.cpp:24-59).  `camera` is anything with
+    // GetWidth()/GetHeight() (the reference's std::shared_ptr<Camera>).
+    template <class CameraPtr>
+    explicit FeatureTrackerCuda(CameraPtr camera, int max_features = 500, float min_distance = 30.0f,
+                                float quality_level = 0.01f, int boundary_margin = 20, int device = 0)
+        : FeatureTrackerCuda(camera->GetWidth(), camera->GetHeight(), max_features, min_distance, quality_level,
+                             boundary_margin, device) {}
+    FeatureTrackerCuda(int width, int height, int max_features = 500, float min_distance = 30.0f,
+                       float quality_level = 0.01f, int boundary_margin = 20, int device = 0);
+    ~FeatureTrackerCuda();
+    FeatureTrackerCuda(const FeatureTrackerCuda&) = delete;
+    FeatureTrackerCuda& operator=(const FeatureTrackerCuda&) = delete;
+
+    // FeatureTracker.cpp:208-226
+    std::vector<cv::Point2f> DetectNewFeatures(const cv::Mat& image, const cv::Mat& mask = cv::Mat());
+    // FeatureTracker.cpp:228-251
+    int TrackOpticalFlow(const cv::Mat& prev_image, const cv::Mat& curr_image,
+                         const std::vector<cv::Point2f>& prev_points, std::vector<cv::Point2f>& curr_points,
+                         std::vector<uchar>& status);
+    // The post filter of TrackFeatures (FeatureTracker.cpp:118-126) computed on the device
+    // during the last TrackOpticalFlow call: status && !polar && !near-boundary.
+    const std::vector<uchar>& LastKeepMask() const { return m_keep; }
+
+    // Frame identity for the device pyramid cache: when the caller tags images (e.g. with the
+    // Frame id) the pyramid of `prev` is re-used instead of being rebuilt every call as
+    // cv::calcOpticalFlowPyrLK does.  0 = no caching (exact reference behaviour, slower).
+    void SetFrameKeys(uint64_t prev_key, uint64_t curr_key) { m_prev_key = prev_key; m_curr_key = curr_key; }
+
+    void SetMaxFeatures(int max_features) { m_max_features = max_features; }
+    void SetMinDistance(float min_distance) { m_min_distance = min_distance; }
+    int GetMaxFeatures() const { return m_max_features; }
+    void GetTrackingStats(int& num_tracked, int& num_detected) const { num_tracked = m_num_tracked; num_detected = m_num_detected; }
+
+private:
+    void check(int rc, const char* what) const;
+    vio360_ctx* m_ctx = nullptr;
+    int m_width, m_height, m_max_features;
+    float m_min_distance, m_quality_level;
+    int m_boundary_margin;
+    int m_point_capacity = 0;
+    uint64_t m_prev_key = 0, m_curr_key = 0;
+    int m_num_tracked = 0, m_num_detected = 0;
+    std::vector<uchar> m_keep;
+    void ensure_capacity(int n_points);
+};
+
+}  // namespace vio_360

@@ -7,7 +7,7 @@ NVFLAGS := $(ARCH) -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -Xcompiler -Wall -X
 LIB := $(PKG)/libvio360_cuda.so
 OBJS := $(CSRC)/ctx.o $(CSRC)/ba.o $(CSRC)/fe.o
 
-all: $(LIB) oracle host
+all: $(LIB) oracle host hosttest
 
 $(CSRC)/ctx.o: $(CSRC)/ctx.cu $(CSRC)/common.cuh include/vio360.h
 	$(NVCC) $(NVFLAGS) -c $< -o $@
@@ -24,11 +24,14 @@ $(LIB): $(OBJS)
 oracle:
 	$(MAKE) -C oracle
 
-host:
+host: $(LIB)
 	@if [ -f $(PKG)/host/Makefile ]; then $(MAKE) -C $(PKG)/host; fi
 
 clean:
 	rm -f $(OBJS) $(LIB)
 	$(MAKE) -C oracle clean
 
-.PHONY: all oracle host clean
+hosttest: host oracle
+	$(MAKE) -C tests/host
+
+.PHONY: all oracle host hosttest clean
