@@ -47,6 +47,7 @@ struct vio360_fe_state {
     DevBuf d_djobs, d_eig, d_mask, d_small, d_cand, d_cand_sorted, d_grid, d_cub, d_corners;
     PinBuf h_djobs, h_dout;
     int det_batch_cap = 0, max_cand = 1 << 18;
+    int lk_mb = 2;               // occupancy variant of k_lk_track (tuning knob: VIO360_LK_MB)
     size_t cub_bytes = 0;
 };
 
@@ -118,6 +119,7 @@ extern "C" int vio360_fe_configure(vio360_ctx* ctx, int width, int height, int m
     VIO_CUDA(ctx, s->d_status.reserve(np)); VIO_CUDA(ctx, s->d_err.reserve(np * 4)); VIO_CUDA(ctx, s->d_keep.reserve(np));
     VIO_CUDA(ctx, s->h_pts_in.reserve(np * 8));
     VIO_CUDA(ctx, s->h_out.reserve(np * (8 + 1 + 4 + 1)));
+    if (const char* e = getenv("VIO360_LK_MB")) s->lk_mb = atoi(e) == 3 ? 3 : 2;
     s->configured = true;
     return VIO360_OK;
 }
@@ -198,9 +200,24 @@ static int build_pyramids(vio360_ctx* ctx, const std::vector<int>& todo) {
     VIO_CUDA(ctx, cudaMemcpyAsync(dj, hj, bytes, cudaMemcpyHostToDevice, ctx->stream));
     for (int l = 0; l + 1 < s->nlevels; ++l) {
         const int dw = s->lw[l + 1], dh = s->lh[l + 1];
-        dim3 grid((dw + kPyrTW - 1) / kPyrTW, (dh + kPyrTH - 1) / kPyrTH, nb);
-        { KernelTimer kt_(ctx, "k_pyr_down");
-        k_pyr_down<<<grid, 256, 0, ctx->stream>>>(dj + (size_t)l * nb, s->lw[l], s->lh[l], dw, dh);
+        // fast path: 8-column lanes need w % 8 == 0 and 8-byte aligned source rows
+        bool fast = (s->lw[l] % 8) == 0 && s->lw[l] >= 16 && (s->lpitch[l + 1] % 4) == 0;
+        for (int b = 0; b < nb && fast; ++b) {
+            const PyrJob& j = hj[(size_t)l * nb + b];
+            fast = (reinterpret_cast<uintptr_t>(j.src) % 8) == 0 && (j.spitch % 8) == 0 &&
+                   (reinterpret_cast<uintptr_t>(j.dst) % 4) == 0;
+        }
+        if (fast) {
+            const int nwx = (s->lw[l] + kPyrWarpCols - 1) / kPyrWarpCols, nsy = (dh + kPyrStripRows - 1) / kPyrStripRows;
+            const int total = nwx * nsy * nb, wpb = kPyrFastThreads / 32;
+            { KernelTimer kt_(ctx, "k_pyr_down");
+            k_pyr_down8<<<(total + wpb - 1) / wpb, kPyrFastThreads, 0, ctx->stream>>>(dj + (size_t)l * nb, s->lw[l], s->lh[l], dw, dh, nwx, nsy, total);
+            }
+        } else {
+            dim3 grid((dw + kPyrTW - 1) / kPyrTW, (dh + kPyrTH - 1) / kPyrTH, nb);
+            { KernelTimer kt_(ctx, "k_pyr_down");
+            k_pyr_down<<<grid, 256, 0, ctx->stream>>>(dj + (size_t)l * nb, s->lw[l], s->lh[l], dw, dh);
+            }
         }
         VIO_LAUNCH_CHECK(ctx);
     }
@@ -282,7 +299,8 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
         VIO_CUDA(ctx, cudaMemcpyAsync(s->d_pts_in.p, s->h_pts_in.p, off * 8, cudaMemcpyHostToDevice, st));
     dim3 grid((max_n + kLkWarps - 1) / kLkWarps, n_jobs);
     { KernelTimer kt_(ctx, "k_lk_track");
-    k_lk_track<<<grid, kLkWarps * 32, 0, st>>>(dj, lk_params(s));
+    if (s->lk_mb == 3) k_lk_track<3><<<grid, kLkWarps * 32, 0, st>>>(dj, lk_params(s));
+    else k_lk_track<2><<<grid, kLkWarps * 32, 0, st>>>(dj, lk_params(s));
     }
     VIO_LAUNCH_CHECK(ctx);
     if ((rc = end_stage(ctx))) return rc;

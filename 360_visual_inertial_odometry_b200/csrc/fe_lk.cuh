@@ -4,13 +4,22 @@
 // modules/video/src/lkpyramid.cpp) as called by FeatureTracker::TrackOpticalFlow
 // (src/processing/FeatureTracker.cpp:238-240): fixed-point bilinear sampling with 14-bit
 // weights, 5 fractional bits on the patch, Scharr derivatives (computed here from a
-// 24x24 shared-memory tile instead of a materialised derivative image), REFLECT_101
+// 24-row shared-memory tile instead of a materialised derivative image), REFLECT_101
 // image apron, zero derivative apron, float 2x2 solve, the eps^2 / oscillation exits and
-// the level-0 error epilogue.  The 2x2 normal-equation sums are exact integer warp
-// reductions (OpenCV accumulates the same integers in float lanes; the difference is
-// below 2^-23 relative and is what the 0.05 px position tolerance absorbs).
-// This translation unit is compiled with --fmad=false so float expressions round like
-// the non-FMA baseline build of lkpyramid.cpp.
+// the level-0 error epilogue.
+//
+// Mapping.  The 21x21 window is covered by 126 horizontal runs of 4 pixels (6 runs per
+// row, the last three columns of a row are padding with zero derivatives); lane l owns
+// runs l, l+32, l+64, l+96.  A run reads two 32-bit words per tile row and realigns them
+// with funnel shifts; one dp2a (16-bit weight pair x 8-bit pixel pair) evaluates half of
+// a bilinear tap, so a pixel costs two dp2a instead of four multiply-adds.  The
+// derivative samples of the template stay in registers for all iterations.  The
+// mismatch vector is accumulated as sum(J*Ix) - sum(I*Ix) in exact integers (identical to
+// OpenCV's sum((J-I)*Ix)); the 2x2 normal-equation sums are exact 64-bit warp reductions
+// built from two 32-bit REDUX per sum (OpenCV accumulates the same integers in float
+// lanes; the difference is below 2^-23 relative and is what the 0.05 px position
+// tolerance absorbs).  This translation unit is compiled with --fmad=false so float
+// expressions round like the non-FMA baseline build of lkpyramid.cpp.
 #pragma once
 
 #include "fe_pyr.cuh"
@@ -41,68 +50,112 @@ struct LkParams {
 };
 
 constexpr int kWin = 21;
-constexpr int kNpx = kWin * kWin;       // 441
-constexpr int kPpl = (kNpx + 31) / 32;  // 14 window pixels per lane
-constexpr int kTRows = 24, kTPitch = 32;
-constexpr int kDDim = 22;
-constexpr int kJRows = 32, kJPitch = 36;
-constexpr int kLkWarps = 4;
+constexpr int kRunsPerRow = 6;                    // 6 x 4 = 24 >= 21 columns
+constexpr int kRuns = kWin * kRunsPerRow;         // 126
+constexpr int kRpl = 4;                           // runs per lane
+constexpr int kTRows = 24, kTWords = 8;           // template tile: 24 rows x 32 bytes
+constexpr int kDRows = 22, kDWords = 28;          // derivative grid: 22 rows x 28 packed (ix | iy << 16)
+constexpr int kJRows = 32, kJWords = 9;           // search tile: 32 rows x 36 bytes
+constexpr int kLkWarps = 8;
 
-__device__ __forceinline__ long long warp_sum_ll(long long v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
+// exact 64-bit warp sum of 32-bit lane partials from two hardware integer reductions
+__device__ __forceinline__ long long warp_sum_i32(int v) {
+    const int lo = __reduce_add_sync(0xffffffffu, v & 0xffff);
+    const int hi = __reduce_add_sync(0xffffffffu, v >> 16);
+    return (long long)hi * 65536ll + (long long)lo;
 }
 
-// Fill a (rows x pitch) shared tile with image bytes starting at (x0, y0); x0 % 4 == 0.
-// Interior tiles use aligned 32-bit loads; tiles touching the border index with
-// REFLECT_101 byte by byte (the pyramid apron of buildOpticalFlowPyramid).
-template <int ROWS, int PITCH, int WORDS>
-__device__ __forceinline__ void stage_tile(uint8_t* s, const uint8_t* __restrict__ img, int pitch, int w, int h,
-                                           int x0, int y0, int lane) {
-    const bool interior = x0 >= 0 && y0 >= 0 && (x0 + 4 * WORDS) <= w && (y0 + ROWS) <= h && ((pitch & 3) == 0) &&
-                          ((reinterpret_cast<uintptr_t>(img) & 3) == 0);
-    if (interior) {
-        for (int it = lane; it < ROWS * WORDS; it += 32) {
-            const int r = it / WORDS, c = it - r * WORDS;
-            const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(img + (size_t)(y0 + r) * pitch + x0) + c);
-            *reinterpret_cast<uint32_t*>(s + r * PITCH + 4 * c) = v;
-        }
-    } else {
-        for (int it = lane; it < ROWS * WORDS * 4; it += 32) {
-            const int r = it / (WORDS * 4), c = it - r * (WORDS * 4);
-            s[r * PITCH + c] = img[(size_t)reflect101(y0 + r, h) * pitch + reflect101(x0 + c, w)];
-        }
-    }
+// d = c + a.lo16 * b.byte[0|2] + a.hi16 * b.byte[1|3]   (a signed 16-bit pair, b unsigned bytes)
+__device__ __forceinline__ int dp2a_lo_su(int a, unsigned b, int c) {
+    int d;
+    asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int dp2a_hi_su(int a, unsigned b, int c) {
+    int d;
+    asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+// d = c + sum_i a.byte[i] (unsigned) * b.byte[i] (signed)
+__device__ __forceinline__ int dp4a_us(unsigned a, int b, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
 }
 
-__device__ __forceinline__ void bilinear_weights(float a, float b, int& w00, int& w01, int& w10, int& w11) {
-    w00 = __float2int_rn((1.f - a) * (1.f - b) * 16384.f);
-    w01 = __float2int_rn(a * (1.f - b) * 16384.f);
-    w10 = __float2int_rn((1.f - a) * b * 16384.f);
-    w11 = 16384 - w00 - w01 - w10;
+// Global -> registers half of a tile fill: word `it` of a (rows x WORDS) tile whose top-left
+// byte is image pixel (x0, y0), x0 % 4 == 0.  Interior tiles use aligned 32-bit loads; tiles
+// touching the border index with REFLECT_101 byte by byte (the pyramid apron of
+// buildOpticalFlowPyramid).
+template <int WORDS>
+__device__ __forceinline__ uint32_t tile_word(const uint8_t* __restrict__ img, int pitch, int w, int h, int x0, int y0,
+                                              bool interior, int it) {
+    const int r = it / WORDS, c = it - r * WORDS;
+    if (interior) return __ldg(reinterpret_cast<const uint32_t*>(img + (size_t)(y0 + r) * pitch + x0) + c);
+    const uint8_t* row = img + (size_t)reflect101(y0 + r, h) * pitch;
+    const int x = x0 + 4 * c;
+    return (uint32_t)row[reflect101(x, w)] | ((uint32_t)row[reflect101(x + 1, w)] << 8) |
+           ((uint32_t)row[reflect101(x + 2, w)] << 16) | ((uint32_t)row[reflect101(x + 3, w)] << 24);
+}
+template <int ROWS, int WORDS>
+__device__ __forceinline__ bool tile_interior(const uint8_t* img, int pitch, int w, int h, int x0, int y0) {
+    return x0 >= 0 && y0 >= 0 && (x0 + 4 * WORDS) <= w && (y0 + ROWS) <= h && ((pitch & 3) == 0) &&
+           ((reinterpret_cast<uintptr_t>(img) & 3) == 0);
 }
 
-__global__ void __launch_bounds__(kLkWarps * 32) k_lk_track(const TrackJobDev* __restrict__ jobs, LkParams P) {
-    __shared__ __align__(16) uint8_t sT_all[kLkWarps][kTRows * kTPitch];
-    __shared__ __align__(16) uint32_t sD_all[kLkWarps][kDDim * kDDim];
-    __shared__ __align__(16) uint8_t sJ_all[kLkWarps][kJRows * kJPitch];
+__device__ __forceinline__ void bilinear_weights(float a, float b, int& wt, int& wb) {
+    const int w00 = __float2int_rn((1.f - a) * (1.f - b) * 16384.f);
+    const int w01 = __float2int_rn(a * (1.f - b) * 16384.f);
+    const int w10 = __float2int_rn((1.f - a) * b * 16384.f);
+    const int w11 = 16384 - w00 - w01 - w10;
+    wt = (w00 & 0xffff) | (w01 << 16);   // (w00, w01) as a signed 16-bit pair
+    wb = (w10 & 0xffff) | (w11 << 16);
+}
+
+// The four bilinear patch values (5 fractional bits) of a run whose first tap is byte
+// (4 * k + s) of tile row `top`; `bot` is the row below.
+__device__ __forceinline__ void run_sample(const uint32_t* __restrict__ top, const uint32_t* __restrict__ bot, int s8,
+                                           int wt, int wb, int* v) {
+    const uint32_t t0 = top[0], t1 = top[1], b0 = bot[0], b1 = bot[1];
+    const uint32_t ta = __funnelshift_rc(t0, t1, s8), tb = __funnelshift_rc(t0, t1, s8 + 8);
+    const uint32_t ba = __funnelshift_rc(b0, b1, s8), bb = __funnelshift_rc(b0, b1, s8 + 8);
+    v[0] = dp2a_lo_su(wt, ta, dp2a_lo_su(wb, ba, 256)) >> 9;
+    v[1] = dp2a_lo_su(wt, tb, dp2a_lo_su(wb, bb, 256)) >> 9;
+    v[2] = dp2a_hi_su(wt, ta, dp2a_hi_su(wb, ba, 256)) >> 9;
+    v[3] = dp2a_hi_su(wt, tb, dp2a_hi_su(wb, bb, 256)) >> 9;
+}
+
+// MB = resident CTAs per SM the register allocator targets (2 -> 128 registers, 3 -> 80)
+template <int MB>
+__global__ void __launch_bounds__(kLkWarps * 32, MB) k_lk_track(const TrackJobDev* __restrict__ jobs, LkParams P) {
+    __shared__ __align__(16) uint32_t sT_all[kLkWarps][kTRows * kTWords];
+    __shared__ __align__(16) uint32_t sD_all[kLkWarps][kDRows * kDWords];
+    __shared__ __align__(16) uint32_t sJ_all[kLkWarps][kJRows * kJWords];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const TrackJobDev& job = jobs[blockIdx.y];
     const int pt = blockIdx.x * kLkWarps + warp;
     if (pt >= job.n) return;   // warp-uniform; only __syncwarp is used below
-    uint8_t* sT = sT_all[warp];
+    uint32_t* sT = sT_all[warp];
     uint32_t* sD = sD_all[warp];
-    uint8_t* sJ = sJ_all[warp];
+    uint32_t* sJ = sJ_all[warp];
 
-    // window pixel owned by this lane in round k: idx = lane + 32k
-    int wofs[kPpl];   // (wy << 8) | wx, or -1
+    // runs owned by this lane: window row wy, column segment seg (columns 4*seg .. 4*seg+3);
+    // offJ = wy * kJWords + seg is the only per-run register kept across the level loop
+    int offJ[kRpl];
+    unsigned colmask = 0;   // bit (4k + j): pixel j of run k is a real window pixel
 #pragma unroll
-    for (int k = 0; k < kPpl; ++k) {
-        const int idx = lane + 32 * k;
-        const int wy = idx / kWin, wx = idx - wy * kWin;
-        wofs[k] = idx < kNpx ? ((wy << 8) | wx) : -1;
+    for (int k = 0; k < kRpl; ++k) {
+        const int r = lane + 32 * k;
+        const bool real = r < kRuns;
+        const int rr = real ? r : kRuns - 1;
+        const int wy = rr / kRunsPerRow, seg = rr - wy * kRunsPerRow;
+        offJ[k] = wy * kJWords + seg;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if (real && 4 * seg + j < kWin) colmask |= 1u << (4 * k + j);
     }
+#define LK_OFF_T(k) ((offJ[k] / kJWords + 1) * kTWords + offJ[k] % kJWords)
+#define LK_OFF_D(k) ((offJ[k] / kJWords) * kDWords + 4 * (offJ[k] % kJWords))
 
     const float px0 = job.prev_xy[2 * pt], py0 = job.prev_xy[2 * pt + 1];
     const float half = (kWin - 1) * 0.5f;
@@ -124,55 +177,121 @@ __global__ void __launch_bounds__(kLkWarps * 32) k_lk_track(const TrackJobDev* _
             if (level == 0) { status = 0; errv = 0.f; }
             continue;
         }
-        // ---- template: raw 24x24 tile -> Scharr 22x22 -> 21x21 fixed-point patch in registers
+        nx -= half; ny -= half;
         const uint8_t* imgI = job.prev.p[level];
         const int pitchI = job.prev.pitch[level];
-        const int xT0 = (ipx - 1) & ~3, sh = (ipx - 1) - xT0;
-        __syncwarp();
-        stage_tile<kTRows, kTPitch, 7>(sT, imgI, pitchI, w, h, xT0, ipy - 1, lane);
-        __syncwarp();
-        for (int it = lane; it < kDDim * kDDim; it += 32) {
-            const int dy = it / kDDim, dx = it - dy * kDDim;
-            const int gx = ipx + dx, gy = ipy + dy;
-            uint32_t packed = 0;
-            if (gx >= 0 && gx < w && gy >= 0 && gy < h) {   // derivative apron is zero
-                const uint8_t* t = sT + (dy + 1) * kTPitch + sh + dx + 1;   // centre
-                const int a00 = t[-kTPitch - 1], a01 = t[-kTPitch], a02 = t[-kTPitch + 1];
-                const int a10 = t[-1], a12 = t[1];
-                const int a20 = t[kTPitch - 1], a21 = t[kTPitch], a22 = t[kTPitch + 1];
-                const int ix = (3 * (a02 + a22) + 10 * a12) - (3 * (a00 + a20) + 10 * a10);
-                const int iy = 3 * ((a20 - a00) + (a22 - a02)) + 10 * (a21 - a01);
-                packed = ((uint32_t)ix & 0xffffu) | ((uint32_t)iy << 16);
+        const uint8_t* imgJ = job.cur.p[level];
+        const int pitchJ = job.cur.pitch[level];
+        // ---- one global round trip: template tile and the first search tile together
+        const int xT0 = (ipx - 1) & ~3, yT0 = ipy - 1;
+        const int oT = ipx - xT0;                  // byte column of window pixel 0 in the tile (1..4)
+        int tx0 = 0, ty0 = 0;
+        bool tile_ok = false;
+        {
+            const bool intT = tile_interior<kTRows, kTWords>(imgI, pitchI, w, h, xT0, yT0);
+            uint32_t tw[6], jw[9];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) tw[i] = tile_word<kTWords>(imgI, pitchI, w, h, xT0, yT0, intT, lane + 32 * i);
+            const int inx = (int)floorf(nx), iny = (int)floorf(ny);
+            const bool jin = !(inx < -kWin || inx >= w || iny < -kWin || iny >= h);
+            if (jin) {
+                tx0 = (inx - 4) & ~3; ty0 = iny - 5;
+                const bool intJ = tile_interior<kJRows, kJWords>(imgJ, pitchJ, w, h, tx0, ty0);
+#pragma unroll
+                for (int i = 0; i < 9; ++i) jw[i] = tile_word<kJWords>(imgJ, pitchJ, w, h, tx0, ty0, intJ, lane + 32 * i);
             }
-            sD[it] = packed;
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 6; ++i) sT[lane + 32 * i] = tw[i];
+            if (jin) {
+#pragma unroll
+                for (int i = 0; i < 9; ++i) sJ[lane + 32 * i] = jw[i];
+                tile_ok = true;
+            }
+            __syncwarp();
+        }
+        // ---- Scharr on the 22 x 22 grid (ipx + dx, ipy + dy): lane = (4-column run cr, row group g)
+        {
+            const int cr = lane % 6, g = lane / 6;            // g 0..5 (g == 5: lanes 30, 31 idle)
+            const int r0 = g * 5, r1 = min(r0 + 5, kDRows);   // groups of 5 rows: 0-4 ... 15-19, 20-21 (g == 4 -> rows 20,21)
+            if (g < 5) {
+                const int b0 = oT - 1 + 4 * cr;               // tile byte of column (dx0 - 1), dx0 = 4 * cr
+                const int kw = b0 >> 2, s = b0 & 3;
+                int h0[4], h1[4], h2[4], d0[4], d1[4], d2[4];
+#define LK_ROW_HD(tr, H, Dd)                                                                        \
+                {                                                                                   \
+                    const uint32_t* q = sT + (tr) * kTWords + kw;                                   \
+                    const uint32_t w0 = q[0], w1 = q[1], w2 = (kw + 2 < kTWords) ? q[2] : 0u;       \
+                    _Pragma("unroll") for (int j = 0; j < 4; ++j) {                                 \
+                        const int t = s + j; /* bytes b0+j .. b0+j+3 = columns dx-1 .. dx+2 */      \
+                        const uint32_t x = t < 4 ? __funnelshift_rc(w0, w1, 8 * t) : __funnelshift_rc(w1, w2, 8 * (t - 4)); \
+                        H[j] = dp4a_us(x, 0x00030a03, 0);  /* 3 a + 10 b + 3 c */                   \
+                        Dd[j] = dp4a_us(x, 0x000100ff, 0); /* c - a */                              \
+                    }                                                                               \
+                }
+                LK_ROW_HD(r0, h0, d0)
+                LK_ROW_HD(r0 + 1, h1, d1)
+                for (int dy = r0; dy < r1; ++dy) {
+                    LK_ROW_HD(dy + 2, h2, d2)
+                    const int gy = ipy + dy;
+                    const bool rowin = gy >= 0 && gy < h;
+                    uint32_t o[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const int dx = 4 * cr + j, gx = ipx + dx;
+                        const int ix = 3 * (d0[j] + d2[j]) + 10 * d1[j];
+                        const int iy = h2[j] - h0[j];
+                        const bool in = rowin && dx < kDRows && gx >= 0 && gx < w;   // derivative apron is zero
+                        o[j] = in ? (((uint32_t)ix & 0xffffu) | ((uint32_t)iy << 16)) : 0u;
+                        h0[j] = h1[j]; h1[j] = h2[j]; d0[j] = d1[j]; d1[j] = d2[j];
+                    }
+                    *reinterpret_cast<uint4*>(sD + dy * kDWords + 4 * cr) = make_uint4(o[0], o[1], o[2], o[3]);
+                }
+#undef LK_ROW_HD
+            }
+            // column 24 of every row is read by the last run's right tap: keep it zero
+            if (lane < kDRows) sD[lane * kDWords + 24] = 0u;
         }
         __syncwarp();
-        int w00, w01, w10, w11;
-        bilinear_weights(px - ipx, py - ipy, w00, w01, w10, w11);
-        int Iv[kPpl], Ixy[kPpl];   // patch value (5 frac bits); packed (Ix | Iy << 16)
-        int sA11 = 0, sA12 = 0, sA22 = 0;
+        // ---- template samples: I (only for sum I*Ix, sum I*Iy), Ix, Iy per owned pixel
+        int wtI, wbI;   // template weights, kept for the error epilogue
+        bilinear_weights(px - ipx, py - ipy, wtI, wbI);
+        const int w00 = (int)(short)(wtI & 0xffff), w01 = wtI >> 16, w10 = (int)(short)(wbI & 0xffff), w11 = wbI >> 16;
+        int Ix[kRpl * 4], Iy[kRpl * 4];
+        int sA11 = 0, sA12 = 0, sA22 = 0, cI1 = 0, cI2 = 0;
+        {
+            const int kT = oT >> 2, sT8 = 8 * (oT & 3);
 #pragma unroll
-        for (int k = 0; k < kPpl; ++k) {
-            Iv[k] = 0; Ixy[k] = 0;
-            if (wofs[k] >= 0) {
-                const int wy = wofs[k] >> 8, wx = wofs[k] & 255;
-                const uint8_t* t = sT + (wy + 1) * kTPitch + sh + wx + 1;
-                const int iv = (t[0] * w00 + t[1] * w01 + t[kTPitch] * w10 + t[kTPitch + 1] * w11 + (1 << 8)) >> 9;
-                const uint32_t* dp = sD + wy * kDDim + wx;
-                const uint32_t d00 = dp[0], d01 = dp[1], d10 = dp[kDDim], d11 = dp[kDDim + 1];
-                const int ixv = ((int)(short)(d00 & 0xffff) * w00 + (int)(short)(d01 & 0xffff) * w01 +
-                                 (int)(short)(d10 & 0xffff) * w10 + (int)(short)(d11 & 0xffff) * w11 + (1 << 13)) >> 14;
-                const int iyv = (((int)d00 >> 16) * w00 + ((int)d01 >> 16) * w01 + ((int)d10 >> 16) * w10 +
-                                 ((int)d11 >> 16) * w11 + (1 << 13)) >> 14;
-                Iv[k] = iv;
-                Ixy[k] = (ixv & 0xffff) | (iyv << 16);
-                sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
+            for (int k = 0; k < kRpl; ++k) {
+                int iv[4];
+                run_sample(sT + LK_OFF_T(k) + kT, sT + LK_OFF_T(k) + kT + kTWords, sT8, wtI, wbI, iv);
+                const int oD = LK_OFF_D(k);
+                const uint4 da = *reinterpret_cast<const uint4*>(sD + oD);
+                const uint4 db = *reinterpret_cast<const uint4*>(sD + oD + kDWords);
+                const uint32_t dt[5] = {da.x, da.y, da.z, da.w, sD[oD + 4]};
+                const uint32_t dbt[5] = {db.x, db.y, db.z, db.w, sD[oD + kDWords + 4]};
+                int tx[5], ty[5], bx[5], by[5];
+#pragma unroll
+                for (int j = 0; j < 5; ++j) {
+                    tx[j] = (int)(short)(dt[j] & 0xffff); ty[j] = (int)dt[j] >> 16;
+                    bx[j] = (int)(short)(dbt[j] & 0xffff); by[j] = (int)dbt[j] >> 16;
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const bool real = (colmask >> (4 * k + j)) & 1u;
+                    int ixv = (tx[j] * w00 + tx[j + 1] * w01 + bx[j] * w10 + bx[j + 1] * w11 + (1 << 13)) >> 14;
+                    int iyv = (ty[j] * w00 + ty[j + 1] * w01 + by[j] * w10 + by[j + 1] * w11 + (1 << 13)) >> 14;
+                    if (!real) { ixv = 0; iyv = 0; }
+                    Ix[4 * k + j] = ixv; Iy[4 * k + j] = iyv;
+                    sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
+                    cI1 += iv[j] * ixv; cI2 += iv[j] * iyv;
+                }
             }
         }
         const float FLT_SCALE = 1.f / (1 << 20);
-        const float A11 = (float)warp_sum_ll(sA11) * FLT_SCALE;
-        const float A12 = (float)warp_sum_ll(sA12) * FLT_SCALE;
-        const float A22 = (float)warp_sum_ll(sA22) * FLT_SCALE;
+        const float A11 = (float)warp_sum_i32(sA11) * FLT_SCALE;
+        const float A12 = (float)warp_sum_i32(sA12) * FLT_SCALE;
+        const float A22 = (float)warp_sum_i32(sA22) * FLT_SCALE;
         float D = A11 * A22 - A12 * A12;
         const float tt = A11 - A22;
         const float minEig = (A22 + A11 - sqrtf(tt * tt + 4.f * A12 * A12)) / (float)(2 * kWin * kWin);
@@ -181,39 +300,44 @@ __global__ void __launch_bounds__(kLkWarps * 32) k_lk_track(const TrackJobDev* _
             continue;
         }
         D = 1.f / D;
-        nx -= half; ny -= half;
         float pdx = 0.f, pdy = 0.f;
-        const uint8_t* imgJ = job.cur.p[level];
-        const int pitchJ = job.cur.pitch[level];
-        int tx0 = 0, ty0 = 0;
-        bool tile_ok = false;
+        // (re)load the search tile around (inx, iny) when the window leaves the staged one
+        auto ensure_tile = [&](int inx, int iny) {
+            if (!tile_ok || inx < tx0 || inx + 25 > tx0 + 4 * kJWords || iny < ty0 || iny + 22 > ty0 + kJRows) {
+                tx0 = (inx - 4) & ~3; ty0 = iny - 5;
+                const bool intJ = tile_interior<kJRows, kJWords>(imgJ, pitchJ, w, h, tx0, ty0);
+                uint32_t jw[9];
+#pragma unroll
+                for (int i = 0; i < 9; ++i) jw[i] = tile_word<kJWords>(imgJ, pitchJ, w, h, tx0, ty0, intJ, lane + 32 * i);
+                __syncwarp();
+#pragma unroll
+                for (int i = 0; i < 9; ++i) sJ[lane + 32 * i] = jw[i];
+                __syncwarp();
+                tile_ok = true;
+            }
+        };
         for (int j = 0; j < P.max_iters; ++j) {
             const int inx = (int)floorf(nx), iny = (int)floorf(ny);
             if (inx < -kWin || inx >= w || iny < -kWin || iny >= h) {
                 if (level == 0) status = 0;
                 break;
             }
-            if (!tile_ok || inx < tx0 || inx + 22 > tx0 + kJPitch || iny < ty0 || iny + 22 > ty0 + kJRows) {
-                tx0 = (inx - 5) & ~3; ty0 = iny - 5;
-                __syncwarp();
-                stage_tile<kJRows, kJPitch, 9>(sJ, imgJ, pitchJ, w, h, tx0, ty0, lane);
-                __syncwarp();
-                tile_ok = true;
-            }
-            bilinear_weights(nx - inx, ny - iny, w00, w01, w10, w11);
-            const uint8_t* base = sJ + (iny - ty0) * kJPitch + (inx - tx0);
-            int sb1 = 0, sb2 = 0;
+            ensure_tile(inx, iny);
+            int wt, wb;
+            bilinear_weights(nx - inx, ny - iny, wt, wb);
+            const int ox = inx - tx0;
+            const uint32_t* base = sJ + (iny - ty0) * kJWords + (ox >> 2);
+            const int s8 = 8 * (ox & 3);
+            int sb1 = -cI1, sb2 = -cI2;
 #pragma unroll
-            for (int k = 0; k < kPpl; ++k) {
-                if (wofs[k] >= 0) {
-                    const uint8_t* q = base + (wofs[k] >> 8) * kJPitch + (wofs[k] & 255);
-                    const int diff = ((q[0] * w00 + q[1] * w01 + q[kJPitch] * w10 + q[kJPitch + 1] * w11 + (1 << 8)) >> 9) - Iv[k];
-                    sb1 += diff * (int)(short)(Ixy[k] & 0xffff);
-                    sb2 += diff * (Ixy[k] >> 16);
-                }
+            for (int k = 0; k < kRpl; ++k) {
+                int jv[4];
+                run_sample(base + offJ[k], base + offJ[k] + kJWords, s8, wt, wb, jv);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) { sb1 += jv[q] * Ix[4 * k + q]; sb2 += jv[q] * Iy[4 * k + q]; }
             }
-            const float b1 = (float)warp_sum_ll(sb1) * FLT_SCALE;
-            const float b2 = (float)warp_sum_ll(sb2) * FLT_SCALE;
+            const float b1 = (float)warp_sum_i32(sb1) * FLT_SCALE;
+            const float b2 = (float)warp_sum_i32(sb2) * FLT_SCALE;
             const float dx = (A12 * b2 - A22 * b1) * D;
             const float dy = (A12 * b1 - A11 * b2) * D;
             nx += dx; ny += dy;
@@ -231,24 +355,24 @@ __global__ void __launch_bounds__(kLkWarps * 32) k_lk_track(const TrackJobDev* _
             if (inx < -kWin || inx >= w || iny < -kWin || iny >= h) {
                 status = 0;
             } else if (job.err) {
-                if (!tile_ok || inx < tx0 || inx + 22 > tx0 + kJPitch || iny < ty0 || iny + 22 > ty0 + kJRows) {
-                    tx0 = (inx - 5) & ~3; ty0 = iny - 5;
-                    __syncwarp();
-                    stage_tile<kJRows, kJPitch, 9>(sJ, imgJ, pitchJ, w, h, tx0, ty0, lane);
-                    __syncwarp();
-                }
-                bilinear_weights(qx - inx, qy - iny, w00, w01, w10, w11);
-                const uint8_t* base = sJ + (iny - ty0) * kJPitch + (inx - tx0);
+                ensure_tile(inx, iny);
+                int wtJ, wbJ;
+                bilinear_weights(qx - inx, qy - iny, wtJ, wbJ);
+                const int ox = inx - tx0;
+                const uint32_t* base = sJ + (iny - ty0) * kJWords + (ox >> 2);
+                const int s8 = 8 * (ox & 3);
+                const int kT = oT >> 2, sT8 = 8 * (oT & 3);
                 int se = 0;
 #pragma unroll
-                for (int k = 0; k < kPpl; ++k) {
-                    if (wofs[k] >= 0) {
-                        const uint8_t* q = base + (wofs[k] >> 8) * kJPitch + (wofs[k] & 255);
-                        const int diff = ((q[0] * w00 + q[1] * w01 + q[kJPitch] * w10 + q[kJPitch + 1] * w11 + (1 << 8)) >> 9) - Iv[k];
-                        se += diff < 0 ? -diff : diff;
-                    }
+                for (int k = 0; k < kRpl; ++k) {
+                    int jv[4], iv[4];
+                    run_sample(base + offJ[k], base + offJ[k] + kJWords, s8, wtJ, wbJ, jv);
+                    run_sample(sT + LK_OFF_T(k) + kT, sT + LK_OFF_T(k) + kT + kTWords, sT8, wtI, wbI, iv);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        if ((colmask >> (4 * k + q)) & 1u) { const int d = jv[q] - iv[q]; se += d < 0 ? -d : d; }
                 }
-                errv = (float)warp_sum_ll(se) / (float)(32 * kWin * kWin);
+                errv = (float)warp_sum_i32(se) / (float)(32 * kWin * kWin);
             }
         }
     }

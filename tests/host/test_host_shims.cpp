@@ -62,11 +62,16 @@ static void test_ba() {
             vo_factor f; std::memset(&f, 0, sizeof(f));
             f.cols = cols; f.rows = rows; std::memcpy(f.Tcb, Tcb, sizeof(Tcb)); std::memcpy(f.Twb_init, &Twb[k * 16], 128);
             std::memcpy(f.info, info, sizeof(info));
-            f.obs[0] = cols / 2; f.obs[1] = rows / 2;
-            double r[2];
-            vo_ba_evaluate(&f, pose_params[k].data(), point_params[j].data(), r, 0, nullptr, nullptr);
-            if (r[0] == 100.0 && r[1] == 100.0) continue;   // behind the seam relative to the probe pixel
-            const double u = cols / 2 - r[0] + nrand(), v = rows / 2 - r[1] + nrand();
+            // the factor clamps errors beyond 100 px to (100,100) (Factors.cpp:424-441): probe on a
+            // 150-px grid until the probe pixel is within 100 px of the projection
+            double r[2] = {100.0, 100.0};
+            for (double pu = 75; pu < cols && r[0] == 100.0 && r[1] == 100.0; pu += 150)
+                for (double pv = 75; pv < rows && r[0] == 100.0 && r[1] == 100.0; pv += 150) {
+                    f.obs[0] = pu; f.obs[1] = pv;
+                    vo_ba_evaluate(&f, pose_params[k].data(), point_params[j].data(), r, 0, nullptr, nullptr);
+                }
+            if (r[0] == 100.0 && r[1] == 100.0) continue;
+            const double u = f.obs[0] - r[0] + nrand(), v = f.obs[1] - r[1] + nrand();
             if (u < 20 || u > cols - 20 || v < 20 || v > rows - 20) continue;
             f.obs[0] = (double)(float)u; f.obs[1] = (double)(float)v;
             factors.push_back(ev.AddFactor(k, j, f.obs[0], f.obs[1]));
