@@ -208,10 +208,13 @@ static int build_pyramids(vio360_ctx* ctx, const std::vector<int>& todo) {
                    (reinterpret_cast<uintptr_t>(j.dst) % 4) == 0;
         }
         if (fast) {
-            const int nwx = (s->lw[l] + kPyrWarpCols - 1) / kPyrWarpCols, nsy = (dh + kPyrStripRows - 1) / kPyrStripRows;
-            const int total = nwx * nsy * nb, wpb = kPyrFastThreads / 32;
+            const int nwx = (s->lw[l] + kPyrWarpCols - 1) / kPyrWarpCols, wpb = kPyrFastThreads / 32;
+            // shorter strips while the launch has fewer than ~24 warps per SM
+            int strip = kPyrStripRows;
+            while (strip > 4 && (long long)nwx * ((dh + strip - 1) / strip) * nb < 24ll * ctx->num_sms) strip >>= 1;
+            const int nsy = (dh + strip - 1) / strip, total = nwx * nsy * nb;
             { KernelTimer kt_(ctx, "k_pyr_down");
-            k_pyr_down8<<<(total + wpb - 1) / wpb, kPyrFastThreads, 0, ctx->stream>>>(dj + (size_t)l * nb, s->lw[l], s->lh[l], dw, dh, nwx, nsy, total);
+            k_pyr_down8<<<(total + wpb - 1) / wpb, kPyrFastThreads, 0, ctx->stream>>>(dj + (size_t)l * nb, s->lw[l], s->lh[l], dw, dh, nwx, nsy, total, strip);
             }
         } else {
             dim3 grid((dw + kPyrTW - 1) / kPyrTW, (dh + kPyrTH - 1) / kPyrTH, nb);

@@ -54,7 +54,7 @@ constexpr int kRunsPerRow = 6;                    // 6 x 4 = 24 >= 21 columns
 constexpr int kRuns = kWin * kRunsPerRow;         // 126
 constexpr int kRpl = 4;                           // runs per lane
 constexpr int kTRows = 24, kTWords = 8;           // template tile: 24 rows x 32 bytes
-constexpr int kDRows = 22, kDWords = 28;          // derivative grid: 22 rows x 28 packed (ix | iy << 16)
+constexpr int kDRows = 22, kDWords = 28;          // derivative grid: 22 (+2 zero) rows x 28 packed (ix | iy << 16)
 constexpr int kJRows = 32, kJWords = 9;           // search tile: 32 rows x 36 bytes
 constexpr int kLkWarps = 8;
 
@@ -83,24 +83,30 @@ __device__ __forceinline__ int dp4a_us(unsigned a, int b, int c) {
     return d;
 }
 
-// Global -> registers half of a tile fill: word `it` of a (rows x WORDS) tile whose top-left
-// byte is image pixel (x0, y0), x0 % 4 == 0.  Interior tiles use aligned 32-bit loads; tiles
-// touching the border index with REFLECT_101 byte by byte (the pyramid apron of
-// buildOpticalFlowPyramid).
-template <int WORDS>
-__device__ __forceinline__ uint32_t tile_word(const uint8_t* __restrict__ img, int pitch, int w, int h, int x0, int y0,
-                                              bool interior, int it) {
-    const int r = it / WORDS, c = it - r * WORDS;
-    if (interior) return __ldg(reinterpret_cast<const uint32_t*>(img + (size_t)(y0 + r) * pitch + x0) + c);
-    const uint8_t* row = img + (size_t)reflect101(y0 + r, h) * pitch;
-    const int x = x0 + 4 * c;
-    return (uint32_t)row[reflect101(x, w)] | ((uint32_t)row[reflect101(x + 1, w)] << 8) |
-           ((uint32_t)row[reflect101(x + 2, w)] << 16) | ((uint32_t)row[reflect101(x + 3, w)] << 24);
-}
+// Tile staging.  A (ROWS x WORDS) tile whose top-left byte is image pixel (x0, y0), x0 % 4 == 0.
+// Interior tiles use aligned 32-bit loads held in registers until the warp may overwrite the
+// shared tile; tiles touching the border are rare and go through one out-of-line routine that
+// indexes with REFLECT_101 byte by byte (the pyramid apron of buildOpticalFlowPyramid).
 template <int ROWS, int WORDS>
 __device__ __forceinline__ bool tile_interior(const uint8_t* img, int pitch, int w, int h, int x0, int y0) {
     return x0 >= 0 && y0 >= 0 && (x0 + 4 * WORDS) <= w && (y0 + ROWS) <= h && ((pitch & 3) == 0) &&
            ((reinterpret_cast<uintptr_t>(img) & 3) == 0);
+}
+template <int WORDS>
+__device__ __forceinline__ uint32_t tile_word_fast(const uint8_t* __restrict__ img, int pitch, int x0, int y0, int it) {
+    const int r = it / WORDS, c = it - r * WORDS;
+    return __ldg(reinterpret_cast<const uint32_t*>(img + (size_t)(y0 + r) * pitch + x0) + c);
+}
+__device__ __noinline__ void tile_fill_border(uint32_t* s, const uint8_t* __restrict__ img, int pitch, int w, int h,
+                                              int x0, int y0, int words, int total, int lane) {
+#pragma unroll 1
+    for (int it = lane; it < total; it += 32) {
+        const int r = it / words, c = it - r * words;
+        const uint8_t* row = img + (size_t)reflect101(y0 + r, h) * pitch;
+        const int x = x0 + 4 * c;
+        s[it] = (uint32_t)row[reflect101(x, w)] | ((uint32_t)row[reflect101(x + 1, w)] << 8) |
+                ((uint32_t)row[reflect101(x + 2, w)] << 16) | ((uint32_t)row[reflect101(x + 3, w)] << 24);
+    }
 }
 
 __device__ __forceinline__ void bilinear_weights(float a, float b, int& wt, int& wb) {
@@ -129,7 +135,7 @@ __device__ __forceinline__ void run_sample(const uint32_t* __restrict__ top, con
 template <int MB>
 __global__ void __launch_bounds__(kLkWarps * 32, MB) k_lk_track(const TrackJobDev* __restrict__ jobs, LkParams P) {
     __shared__ __align__(16) uint32_t sT_all[kLkWarps][kTRows * kTWords];
-    __shared__ __align__(16) uint32_t sD_all[kLkWarps][kDRows * kDWords];
+    __shared__ __align__(16) uint32_t sD_all[kLkWarps][(kDRows + 2) * kDWords];
     __shared__ __align__(16) uint32_t sJ_all[kLkWarps][kJRows * kJWords];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const TrackJobDev& job = jobs[blockIdx.y];
@@ -155,7 +161,8 @@ __global__ void __launch_bounds__(kLkWarps * 32, MB) k_lk_track(const TrackJobDe
             if (real && 4 * seg + j < kWin) colmask |= 1u << (4 * k + j);
     }
 #define LK_OFF_T(k) ((offJ[k] / kJWords + 1) * kTWords + offJ[k] % kJWords)
-#define LK_OFF_D(k) ((offJ[k] / kJWords) * kDWords + 4 * (offJ[k] % kJWords))
+// padding runs (k == 3 on lanes 30, 31) read the two zero rows below the derivative grid
+#define LK_OFF_D(k) (((k) == 3 && lane >= 30) ? kDRows * kDWords : (offJ[k] / kJWords) * kDWords + 4 * (offJ[k] % kJWords))
 
     const float px0 = job.prev_xy[2 * pt], py0 = job.prev_xy[2 * pt + 1];
     const float half = (kWin - 1) * 0.5f;
@@ -189,68 +196,92 @@ __global__ void __launch_bounds__(kLkWarps * 32, MB) k_lk_track(const TrackJobDe
         bool tile_ok = false;
         {
             const bool intT = tile_interior<kTRows, kTWords>(imgI, pitchI, w, h, xT0, yT0);
-            uint32_t tw[6], jw[9];
-#pragma unroll
-            for (int i = 0; i < 6; ++i) tw[i] = tile_word<kTWords>(imgI, pitchI, w, h, xT0, yT0, intT, lane + 32 * i);
             const int inx = (int)floorf(nx), iny = (int)floorf(ny);
             const bool jin = !(inx < -kWin || inx >= w || iny < -kWin || iny >= h);
+            bool intJ = false;
             if (jin) {
                 tx0 = (inx - 4) & ~3; ty0 = iny - 5;
-                const bool intJ = tile_interior<kJRows, kJWords>(imgJ, pitchJ, w, h, tx0, ty0);
+                intJ = tile_interior<kJRows, kJWords>(imgJ, pitchJ, w, h, tx0, ty0);
+            }
+            uint32_t tw[6], jw[9];
+            if (intT) {
 #pragma unroll
-                for (int i = 0; i < 9; ++i) jw[i] = tile_word<kJWords>(imgJ, pitchJ, w, h, tx0, ty0, intJ, lane + 32 * i);
+                for (int i = 0; i < 6; ++i) tw[i] = tile_word_fast<kTWords>(imgI, pitchI, xT0, yT0, lane + 32 * i);
+            }
+            if (intJ) {
+#pragma unroll
+                for (int i = 0; i < 9; ++i) jw[i] = tile_word_fast<kJWords>(imgJ, pitchJ, tx0, ty0, lane + 32 * i);
             }
             __syncwarp();
+            if (intT) {
 #pragma unroll
-            for (int i = 0; i < 6; ++i) sT[lane + 32 * i] = tw[i];
-            if (jin) {
+                for (int i = 0; i < 6; ++i) sT[lane + 32 * i] = tw[i];
+            } else {
+                tile_fill_border(sT, imgI, pitchI, w, h, xT0, yT0, kTWords, kTRows * kTWords, lane);
+            }
+            if (intJ) {
 #pragma unroll
                 for (int i = 0; i < 9; ++i) sJ[lane + 32 * i] = jw[i];
-                tile_ok = true;
+            } else if (jin) {
+                tile_fill_border(sJ, imgJ, pitchJ, w, h, tx0, ty0, kJWords, kJRows * kJWords, lane);
             }
+            tile_ok = jin;
             __syncwarp();
         }
-        // ---- Scharr on the 22 x 22 grid (ipx + dx, ipy + dy): lane = (4-column run cr, row group g)
+        // ---- Scharr on the 22 x 22 grid (ipx + dx, ipy + dy): lane = (4-column run cr, row group g).
+        // Per tile row one dp4a gives the horizontal smoothing 3a+10b+3c and one the horizontal
+        // difference c-a of a column; the vertical halves are combined from a 3-row register window.
         {
-            const int cr = lane % 6, g = lane / 6;            // g 0..5 (g == 5: lanes 30, 31 idle)
-            const int r0 = g * 5, r1 = min(r0 + 5, kDRows);   // groups of 5 rows: 0-4 ... 15-19, 20-21 (g == 4 -> rows 20,21)
+            const int cr = lane % 6, g = lane / 6;            // g 0..4 work, lanes 30, 31 idle
             if (g < 5) {
+                const int r0 = g * 5, r1 = min(r0 + 5, kDRows);   // rows 0-4, 5-9, 10-14, 15-19, 20-21
                 const int b0 = oT - 1 + 4 * cr;               // tile byte of column (dx0 - 1), dx0 = 4 * cr
-                const int kw = b0 >> 2, s = b0 & 3;
-                int h0[4], h1[4], h2[4], d0[4], d1[4], d2[4];
-#define LK_ROW_HD(tr, H, Dd)                                                                        \
-                {                                                                                   \
-                    const uint32_t* q = sT + (tr) * kTWords + kw;                                   \
-                    const uint32_t w0 = q[0], w1 = q[1], w2 = (kw + 2 < kTWords) ? q[2] : 0u;       \
-                    _Pragma("unroll") for (int j = 0; j < 4; ++j) {                                 \
-                        const int t = s + j; /* bytes b0+j .. b0+j+3 = columns dx-1 .. dx+2 */      \
-                        const uint32_t x = t < 4 ? __funnelshift_rc(w0, w1, 8 * t) : __funnelshift_rc(w1, w2, 8 * (t - 4)); \
-                        H[j] = dp4a_us(x, 0x00030a03, 0);  /* 3 a + 10 b + 3 c */                   \
-                        Dd[j] = dp4a_us(x, 0x000100ff, 0); /* c - a */                              \
-                    }                                                                               \
+                const uint32_t* q = sT + r0 * kTWords + (b0 >> 2);
+                const int s8 = 8 * (b0 & 3);
+                uint32_t cm[4];                               // column validity (derivative apron is zero)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int dx = 4 * cr + j, gx = ipx + dx;
+                    cm[j] = (dx < kDRows && gx >= 0 && gx < w) ? 0xffffffffu : 0u;
                 }
-                LK_ROW_HD(r0, h0, d0)
-                LK_ROW_HD(r0 + 1, h1, d1)
+                int h0[4], h1[4], h2[4], d0[4], d1[4], d2[4];
+#define LK_ROW_HD(H, Dd)                                                                   \
+                {                                                                          \
+                    const uint32_t a0 = __funnelshift_rc(q[0], q[1], s8);                   \
+                    const uint32_t a1 = __funnelshift_rc(q[1], q[2], s8);                   \
+                    const uint32_t x1 = __funnelshift_r(a0, a1, 8), x2 = __funnelshift_r(a0, a1, 16), \
+                                   x3 = __funnelshift_r(a0, a1, 24);                        \
+                    H[0] = dp4a_us(a0, 0x00030a03, 0); Dd[0] = dp4a_us(a0, 0x000100ff, 0);  \
+                    H[1] = dp4a_us(x1, 0x00030a03, 0); Dd[1] = dp4a_us(x1, 0x000100ff, 0);  \
+                    H[2] = dp4a_us(x2, 0x00030a03, 0); Dd[2] = dp4a_us(x2, 0x000100ff, 0);  \
+                    H[3] = dp4a_us(x3, 0x00030a03, 0); Dd[3] = dp4a_us(x3, 0x000100ff, 0);  \
+                    q += kTWords;                                                           \
+                }
+                LK_ROW_HD(h0, d0)
+                LK_ROW_HD(h1, d1)
+                uint32_t* dst = sD + r0 * kDWords + 4 * cr;
+#pragma unroll 1
                 for (int dy = r0; dy < r1; ++dy) {
-                    LK_ROW_HD(dy + 2, h2, d2)
-                    const int gy = ipy + dy;
-                    const bool rowin = gy >= 0 && gy < h;
+                    LK_ROW_HD(h2, d2)
+                    const unsigned gy = (unsigned)(ipy + dy);
+                    const uint32_t rm = gy < (unsigned)h ? 0xffffffffu : 0u;
                     uint32_t o[4];
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
-                        const int dx = 4 * cr + j, gx = ipx + dx;
                         const int ix = 3 * (d0[j] + d2[j]) + 10 * d1[j];
                         const int iy = h2[j] - h0[j];
-                        const bool in = rowin && dx < kDRows && gx >= 0 && gx < w;   // derivative apron is zero
-                        o[j] = in ? (((uint32_t)ix & 0xffffu) | ((uint32_t)iy << 16)) : 0u;
+                        o[j] = __byte_perm((uint32_t)ix, (uint32_t)iy, 0x5410) & cm[j] & rm;   // (ix & 0xffff) | (iy << 16)
                         h0[j] = h1[j]; h1[j] = h2[j]; d0[j] = d1[j]; d1[j] = d2[j];
                     }
-                    *reinterpret_cast<uint4*>(sD + dy * kDWords + 4 * cr) = make_uint4(o[0], o[1], o[2], o[3]);
+                    *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
+                    dst += kDWords;
                 }
 #undef LK_ROW_HD
             }
-            // column 24 of every row is read by the last run's right tap: keep it zero
+            // column 24 of every row is read by the last run's right tap, row 22 by the two
+            // padding runs of lanes 30 / 31: keep them zero
             if (lane < kDRows) sD[lane * kDWords + 24] = 0u;
+            if (lane < kDWords) { sD[kDRows * kDWords + lane] = 0u; sD[(kDRows + 1) * kDWords + lane] = 0u; }
         }
         __syncwarp();
         // ---- template samples: I (only for sum I*Ix, sum I*Iy), Ix, Iy per owned pixel
@@ -278,10 +309,11 @@ __global__ void __launch_bounds__(kLkWarps * 32, MB) k_lk_track(const TrackJobDe
                 }
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    const bool real = (colmask >> (4 * k + j)) & 1u;
                     int ixv = (tx[j] * w00 + tx[j + 1] * w01 + bx[j] * w10 + bx[j + 1] * w11 + (1 << 13)) >> 14;
                     int iyv = (ty[j] * w00 + ty[j + 1] * w01 + by[j] * w10 + by[j + 1] * w11 + (1 << 13)) >> 14;
-                    if (!real) { ixv = 0; iyv = 0; }
+                    // window column 21 (padding) still sees derivative column 21 on its left tap;
+                    // columns 22, 23 and the padding runs only see zeros
+                    if (j == 1 && offJ[k] % kJWords == 5) { ixv = 0; iyv = 0; }
                     Ix[4 * k + j] = ixv; Iy[4 * k + j] = iyv;
                     sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
                     cI1 += iv[j] * ixv; cI2 += iv[j] * iyv;
@@ -305,13 +337,17 @@ __global__ void __launch_bounds__(kLkWarps * 32, MB) k_lk_track(const TrackJobDe
         auto ensure_tile = [&](int inx, int iny) {
             if (!tile_ok || inx < tx0 || inx + 25 > tx0 + 4 * kJWords || iny < ty0 || iny + 22 > ty0 + kJRows) {
                 tx0 = (inx - 4) & ~3; ty0 = iny - 5;
-                const bool intJ = tile_interior<kJRows, kJWords>(imgJ, pitchJ, w, h, tx0, ty0);
-                uint32_t jw[9];
+                if (tile_interior<kJRows, kJWords>(imgJ, pitchJ, w, h, tx0, ty0)) {
+                    uint32_t jw[9];
 #pragma unroll
-                for (int i = 0; i < 9; ++i) jw[i] = tile_word<kJWords>(imgJ, pitchJ, w, h, tx0, ty0, intJ, lane + 32 * i);
-                __syncwarp();
+                    for (int i = 0; i < 9; ++i) jw[i] = tile_word_fast<kJWords>(imgJ, pitchJ, tx0, ty0, lane + 32 * i);
+                    __syncwarp();
 #pragma unroll
-                for (int i = 0; i < 9; ++i) sJ[lane + 32 * i] = jw[i];
+                    for (int i = 0; i < 9; ++i) sJ[lane + 32 * i] = jw[i];
+                } else {
+                    __syncwarp();
+                    tile_fill_border(sJ, imgJ, pitchJ, w, h, tx0, ty0, kJWords, kJRows * kJWords, lane);
+                }
                 __syncwarp();
                 tile_ok = true;
             }

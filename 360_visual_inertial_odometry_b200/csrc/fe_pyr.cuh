@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(256) k_pyr_down(const PyrJob* __restrict__ job
 // halos, so a warp writes 120 output bytes per row (one 32-bit store per lane).
 // All arithmetic is exact: vertical sums <= 16*255, full sums <= 256*255 + 128 < 2^16, so
 // two columns share one 32-bit register without carries between the halves.
-constexpr int kPyrStripRows = 32;          // output rows per warp
+constexpr int kPyrStripRows = 32;          // output rows per warp (upper bound; halved while the grid underfills the GPU)
 constexpr int kPyrWarpCols = 240;          // input columns whose outputs one warp writes
 constexpr int kPyrFastThreads = 256;
 
@@ -122,8 +122,40 @@ __device__ __forceinline__ uint32_t pyr_v5(uint32_t a, uint32_t b, uint32_t c, u
     return (a + e) + 4u * (b + d) + 6u * c;
 }
 
+__device__ __forceinline__ PyrRow pyr_unpack(uint2 v) {
+    PyrRow r;
+    r.e0 = __byte_perm(v.x, 0u, 0x4240); r.o0 = __byte_perm(v.x, 0u, 0x4341);
+    r.e1 = __byte_perm(v.y, 0u, 0x4240); r.o1 = __byte_perm(v.y, 0u, 0x4341);
+    return r;
+}
+
+// horizontal 5-tap + rounding of one output row from the vertical sums of this lane and its neighbours
+__device__ __forceinline__ uint32_t pyr_hrow(const PyrRow& r0, const PyrRow& r1, const PyrRow& r2, const PyrRow& r3,
+                                             const PyrRow& r4, bool left_edge, bool right_edge) {
+    const uint32_t ve0 = pyr_v5(r0.e0, r1.e0, r2.e0, r3.e0, r4.e0);   // (V0,V2)
+    const uint32_t vo0 = pyr_v5(r0.o0, r1.o0, r2.o0, r3.o0, r4.o0);   // (V1,V3)
+    const uint32_t ve1 = pyr_v5(r0.e1, r1.e1, r2.e1, r3.e1, r4.e1);   // (V4,V6)
+    const uint32_t vo1 = pyr_v5(r0.o1, r1.o1, r2.o1, r3.o1, r4.o1);   // (V5,V7)
+    // neighbours: (V6,V7) of the lane to the left, V0 of the lane to the right
+    uint32_t lft = __shfl_up_sync(0xffffffffu, __byte_perm(ve1, vo1, 0x7632), 1);
+    uint32_t rgt = __shfl_down_sync(0xffffffffu, ve0, 1);
+    if (left_edge) lft = __byte_perm(ve0, vo0, 0x5432);    // reflect: V[-2] = V2, V[-1] = V1
+    if (right_edge) rgt = ve1 >> 16;                        // reflect: V[8] = V6
+    const uint32_t a01 = __byte_perm(lft, ve0, 0x5410);     // (V-2, V0)
+    const uint32_t b01 = __byte_perm(lft, vo0, 0x5432);     // (V-1, V1)
+    const uint32_t c01 = __byte_perm(ve0, ve1, 0x5432);     // (V2, V4)
+    const uint32_t b23 = __byte_perm(vo0, vo1, 0x5432);     // (V3, V5)
+    const uint32_t c23 = __byte_perm(ve1, rgt, 0x5432);     // (V6, V8)
+    const uint32_t p01 = (a01 + c01) + 4u * (b01 + vo0) + 6u * ve0 + 0x00800080u;
+    const uint32_t p23 = (c01 + c23) + 4u * (b23 + vo1) + 6u * ve1 + 0x00800080u;
+    return __byte_perm(p01, p23, 0x7531);
+}
+
+// strip_rows (even) output rows per warp; two output rows per loop trip with the four input
+// rows of the next trip already in flight (1 KB of loads per warp outstanding).
 __global__ void __launch_bounds__(kPyrFastThreads)
-k_pyr_down8(const PyrJob* __restrict__ jobs, int w, int h, int dw, int dh, int nwx, int nsy, int total_warps) {
+k_pyr_down8(const PyrJob* __restrict__ jobs, int w, int h, int dw, int dh, int nwx, int nsy, int total_warps,
+            int strip_rows) {
     const int gw = blockIdx.x * (kPyrFastThreads / 32) + (threadIdx.x >> 5);
     if (gw >= total_warps) return;
     const int lane = threadIdx.x & 31;
@@ -134,36 +166,24 @@ k_pyr_down8(const PyrJob* __restrict__ jobs, int w, int h, int dw, int dh, int n
     const bool left_edge = col0 == 0, right_edge = col0 + 8 == w;
     const bool writer = lane >= 1 && lane <= 30 && col0 >= 0 && col0 < w;
     const uint8_t* src = job.src + lcol;
-    const int y0 = sy * kPyrStripRows, y1 = min(y0 + kPyrStripRows, dh);
-    auto row_ptr = [&](int r) { return src + (size_t)reflect101(r, h) * job.spitch; };
-    PyrRow r0 = pyr_load_row(row_ptr(2 * y0 - 2)), r1 = pyr_load_row(row_ptr(2 * y0 - 1)), r2 = pyr_load_row(row_ptr(2 * y0));
-    PyrRow n3 = pyr_load_row(row_ptr(2 * y0 + 1)), n4 = pyr_load_row(row_ptr(2 * y0 + 2));
+    const int y0 = sy * strip_rows, y1 = min(y0 + strip_rows, dh);
+    auto load = [&](int r) { return __ldg(reinterpret_cast<const uint2*>(src + (size_t)reflect101(r, h) * job.spitch)); };
+    PyrRow r0 = pyr_unpack(load(2 * y0 - 2)), r1 = pyr_unpack(load(2 * y0 - 1)), r2 = pyr_unpack(load(2 * y0));
+    uint2 n3 = load(2 * y0 + 1), n4 = load(2 * y0 + 2), n5 = load(2 * y0 + 3), n6 = load(2 * y0 + 4);
     uint8_t* dst = job.dst + (size_t)y0 * job.dpitch + (col0 >> 1);
-    for (int y = y0; y < y1; ++y) {
-        const PyrRow r3 = n3, r4 = n4;
-        if (y + 1 < y1) {   // prefetch the next two rows while this one is reduced
-            n3 = pyr_load_row(row_ptr(2 * y + 3));
-            n4 = pyr_load_row(row_ptr(2 * y + 4));
+    for (int y = y0; y < y1; y += 2) {
+        const PyrRow r3 = pyr_unpack(n3), r4 = pyr_unpack(n4), r5 = pyr_unpack(n5), r6 = pyr_unpack(n6);
+        if (y + 2 < y1) {
+            n3 = load(2 * y + 5); n4 = load(2 * y + 6); n5 = load(2 * y + 7); n6 = load(2 * y + 8);
         }
-        const uint32_t ve0 = pyr_v5(r0.e0, r1.e0, r2.e0, r3.e0, r4.e0);   // (V0,V2)
-        const uint32_t vo0 = pyr_v5(r0.o0, r1.o0, r2.o0, r3.o0, r4.o0);   // (V1,V3)
-        const uint32_t ve1 = pyr_v5(r0.e1, r1.e1, r2.e1, r3.e1, r4.e1);   // (V4,V6)
-        const uint32_t vo1 = pyr_v5(r0.o1, r1.o1, r2.o1, r3.o1, r4.o1);   // (V5,V7)
-        // neighbours: (V6,V7) of the lane to the left, V0 of the lane to the right
-        uint32_t lft = __shfl_up_sync(0xffffffffu, __byte_perm(ve1, vo1, 0x7632), 1);
-        uint32_t rgt = __shfl_down_sync(0xffffffffu, ve0, 1);
-        if (left_edge) lft = __byte_perm(ve0, vo0, 0x5432);    // reflect: V[-2] = V2, V[-1] = V1
-        if (right_edge) rgt = ve1 >> 16;                        // reflect: V[8] = V6
-        const uint32_t a01 = __byte_perm(lft, ve0, 0x5410);     // (V-2, V0)
-        const uint32_t b01 = __byte_perm(lft, vo0, 0x5432);     // (V-1, V1)
-        const uint32_t c01 = __byte_perm(ve0, ve1, 0x5432);     // (V2, V4)
-        const uint32_t b23 = __byte_perm(vo0, vo1, 0x5432);     // (V3, V5)
-        const uint32_t c23 = __byte_perm(ve1, rgt, 0x5432);     // (V6, V8)
-        const uint32_t p01 = (a01 + c01) + 4u * (b01 + vo0) + 6u * ve0 + 0x00800080u;
-        const uint32_t p23 = (c01 + c23) + 4u * (b23 + vo1) + 6u * ve1 + 0x00800080u;
-        if (writer) *reinterpret_cast<uint32_t*>(dst) = __byte_perm(p01, p23, 0x7531);
-        dst += job.dpitch;
-        r0 = r2; r1 = r3; r2 = r4;
+        const uint32_t o0 = pyr_hrow(r0, r1, r2, r3, r4, left_edge, right_edge);
+        const uint32_t o1 = pyr_hrow(r2, r3, r4, r5, r6, left_edge, right_edge);
+        if (writer) {
+            *reinterpret_cast<uint32_t*>(dst) = o0;
+            if (y + 1 < y1) *reinterpret_cast<uint32_t*>(dst + job.dpitch) = o1;
+        }
+        dst += 2 * (size_t)job.dpitch;
+        r0 = r4; r1 = r5; r2 = r6;
     }
 }
 
