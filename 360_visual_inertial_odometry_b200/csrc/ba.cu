@@ -12,6 +12,7 @@
 #include <numeric>
 
 #include "ba_math.cuh"
+#include "ba_schur.cuh"
 #include "common.cuh"
 
 using namespace vio360;
@@ -51,6 +52,12 @@ struct vio360_ba {
     DevBuf d_r, d_Jp, d_Jl, d_partials, d_packed, d_blocks, d_chi2, d_flag;
     PinBuf pin;
     bool use_D = false;
+    // chunked (atomic-free) Schur path: see ba_schur.cuh
+    std::vector<int> h_pose;                 // landmark-major pose index of every observation
+    std::vector<SchurChunk> chunks;
+    std::vector<int> irregular, cov_ptr, cov_idx, free_pose;
+    DevBuf d_chunks, d_cov_ptr, d_cov_idx, d_free_pose, d_irregular, d_partS, d_partRhs;
+    bool chunks_dirty = true, smem_attr_set = false;
 };
 
 // ------------------------------------------------------------------------ kernels
@@ -101,6 +108,8 @@ __global__ void k_sum_partials(const double* __restrict__ partials, int n, doubl
         if (lane == 0) *out = s;
     }
 }
+
+#include "ba_schur_kernels.cuh"
 
 template <bool WANT_JAC>
 __global__ void __launch_bounds__(128) k_evaluate(BaDev d, bool apply_loss, double* __restrict__ r_out,
@@ -254,13 +263,15 @@ __global__ void __launch_bounds__(256) k_blocks_pose(BaDev d, bool apply_loss, b
 // the landmark's observations (broadcast by shuffle) to emit -Y_i W_k^T into the upper
 // block triangle of S.  Accumulation into S / rhs uses fp64 RED (order-insensitive to
 // ~1e-16); the tiled kernel below removes the atomics for the regular case.
-__global__ void __launch_bounds__(128) k_schur_warp(BaDev d, int lm_begin, int lm_end, bool apply_loss,
-                                                    double* __restrict__ S, int n, double* __restrict__ rhs,
-                                                    double* __restrict__ partials) {
+__global__ void __launch_bounds__(128) k_schur_warp(BaDev d, int lm_begin, int lm_end, const int* __restrict__ lm_list,
+                                                    bool apply_loss, double* __restrict__ S, int n,
+                                                    double* __restrict__ rhs, double* __restrict__ partials) {
+    // lm_list != nullptr: process landmarks lm_list[0 .. lm_end) (the ones the chunked kernel cannot take)
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    const int l = lm_begin + warp;
+    const bool valid = lm_list ? warp < lm_end : lm_begin + warp < lm_end;
+    const int l = !valid ? 0 : (lm_list ? lm_list[warp] : lm_begin + warp);
     double cost = 0.0;
-    if (l < lm_end) {
+    if (valid) {
         const int lo = d.lm_ptr[l], hi = d.lm_ptr[l + 1];
         const bool lfix = d.point_fixed[l] != 0;
         const double Pw[3] = {d.points[3 * (size_t)l], d.points[3 * (size_t)l + 1], d.points[3 * (size_t)l + 2]};
@@ -440,10 +451,67 @@ extern "C" void vio360_ba_destroy(vio360_ba* ba) {
     DevBuf* bufs[] = {&ba->d_u, &ba->d_v, &ba->d_pose, &ba->d_point, &ba->d_orig, &ba->d_outlier, &ba->d_lm_ptr,
                       &ba->d_pose_ptr, &ba->d_pose_order, &ba->d_Twb, &ba->d_Tcb, &ba->d_posebuf, &ba->d_pose_delta,
                       &ba->d_points, &ba->d_free_map, &ba->d_point_fixed, &ba->d_D, &ba->d_r, &ba->d_Jp, &ba->d_Jl,
-                      &ba->d_partials, &ba->d_packed, &ba->d_blocks, &ba->d_chi2, &ba->d_flag};
+                      &ba->d_partials, &ba->d_packed, &ba->d_blocks, &ba->d_chi2, &ba->d_flag,
+                      &ba->d_chunks, &ba->d_cov_ptr, &ba->d_cov_idx, &ba->d_free_pose, &ba->d_irregular, &ba->d_partS, &ba->d_partRhs};
     for (DevBuf* b : bufs) b->release();
     ba->pin.release();
     delete ba;
+}
+
+// Partition the shard's landmarks [lm_begin, lm_end) into chunks for k_schur_tile: contiguous
+// landmark ranges whose observing poses fit a window of kSWin consecutive poses.  Landmarks
+// that cannot (span too wide, or two observations from the same pose) go to the list handled
+// by k_schur_warp.  Also builds, per pose, the list of chunks covering it (k_schur_reduce).
+static void build_chunks(vio360_ba* ba) {
+    const int K = ba->K;
+    ba->chunks.clear(); ba->irregular.clear();
+    const int nlm = ba->lm_end - ba->lm_begin;
+    const int target = std::max(kSMaxLm, (nlm + 2 * ba->ctx->num_sms - 1) / std::max(1, 2 * ba->ctx->num_sms));
+    std::vector<int> seen(K, -1);
+    SchurChunk cur{ba->lm_begin, ba->lm_begin, 0, 0};
+    int cmin = K, cmax = -1;
+    auto close = [&](int end) {
+        cur.lm_end = end;
+        if (cur.lm_end > cur.lm_begin && cmax >= cmin) { cur.pbase = cmin; cur.span = cmax - cmin + 1; ba->chunks.push_back(cur); }
+        cur.lm_begin = end; cmin = K; cmax = -1;
+    };
+    for (int l = ba->lm_begin; l < ba->lm_end; ++l) {
+        const int lo = ba->lm_ptr[l], hi = ba->lm_ptr[l + 1];
+        if (hi == lo) continue;                       // unobserved landmark: contributes nothing
+        int pmin = K, pmax = -1;
+        bool dup = false;
+        for (int q = lo; q < hi; ++q) {
+            const int p = ba->h_pose[q];
+            if (seen[p] == l) dup = true;
+            seen[p] = l;
+            pmin = std::min(pmin, p); pmax = std::max(pmax, p);
+        }
+        if (dup || pmax - pmin + 1 > kSWin) {
+            close(l);
+            ba->irregular.push_back(l);
+            cur.lm_begin = l + 1;
+            continue;
+        }
+        const int nmin = std::min(cmin, pmin), nmax = std::max(cmax, pmax);
+        if (cmax >= cmin && (nmax - nmin + 1 > kSWin || l - cur.lm_begin >= target)) {
+            close(l);
+            cmin = pmin; cmax = pmax;
+        } else {
+            cmin = nmin; cmax = nmax;
+        }
+    }
+    close(ba->lm_end);
+    ba->cov_ptr.assign(K + 1, 0);
+    for (const SchurChunk& c : ba->chunks)
+        for (int p = c.pbase; p < c.pbase + c.span; ++p) ba->cov_ptr[p + 1]++;
+    for (int p = 0; p < K; ++p) ba->cov_ptr[p + 1] += ba->cov_ptr[p];
+    ba->cov_idx.assign(std::max(1, ba->cov_ptr[K]), 0);
+    std::vector<int> fill(ba->cov_ptr.begin(), ba->cov_ptr.end() - 1);
+    for (int c = 0; c < (int)ba->chunks.size(); ++c)
+        for (int p = ba->chunks[c].pbase; p < ba->chunks[c].pbase + ba->chunks[c].span; ++p) ba->cov_idx[fill[p]++] = c;
+    ba->free_pose.clear();
+    for (int k = 0; k < K; ++k) if (ba->free_map[k] >= 0) ba->free_pose.push_back(k);
+    ba->chunks_dirty = true;
 }
 
 static void compute_shard(vio360_ba* ba) {
@@ -463,6 +531,7 @@ static void compute_shard(vio360_ba* ba) {
     ba->lm_begin = std::min(cut(ba->shard_rank), M);
     ba->lm_end = std::min(cut(ba->shard_rank + 1), M);
     if (ba->lm_end < ba->lm_begin) ba->lm_end = ba->lm_begin;
+    build_chunks(ba);
 }
 
 extern "C" int vio360_ba_set_shard(vio360_ba* ba, int rank, int world) {
@@ -515,6 +584,7 @@ extern "C" int vio360_ba_set_structure(vio360_ba* ba, const int32_t* pose_idx, c
     for (int k = 0; k < K; ++k) if (!ba->pose_fixed[k]) ba->free_map[k] = ba->n_free++;
     memcpy(ba->Tcb, T_cb, sizeof(ba->Tcb));
     cam_const_init(ba->cam, cols, rows, info, T_cb, huber_delta);
+    ba->h_pose = s_pose;
     compute_shard(ba);
 
     cudaStream_t st = ctx->stream;
@@ -733,17 +803,68 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
         int rcD = vio360_ba_set_lm_diagonal(ba, lm_diag);
         if (rcD) return rcD;
     }
-    VIO_CUDA(ctx, cudaMemsetAsync(ba->d_packed.p, 0, packed * 8, st));
     double* dS = ba->d_packed.as<double>(); double* drhs = dS + (size_t)n * n; double* dcost = drhs + n;
-    const int nlm = ba->lm_end - ba->lm_begin;
-    const int nb = std::max(1, (nlm * 32 + 127) / 128);
-    VIO_CUDA(ctx, ba->d_partials.reserve((size_t)(nb + 1) * 8));
     BaDev d = make_dev(ba);
-    { KernelTimer kt_(ctx, "k_schur_warp");
-    k_schur_warp<<<nb, 128, 0, st>>>(d, ba->lm_begin, ba->lm_end, apply_loss != 0, dS, n, drhs, ba->d_partials.as<double>());
+    const bool use_tiles = getenv("VIO360_BA_ATOMIC") == nullptr;   // tuning / A-B switch: the general kernel only
+    const int nch = use_tiles ? (int)ba->chunks.size() : 0;
+    const int nirr = use_tiles ? (int)ba->irregular.size() : ba->lm_end - ba->lm_begin;
+    const int nb_irr = (nirr * 32 + 127) / 128;
+    VIO_CUDA(ctx, ba->d_partials.reserve((size_t)(nch + nb_irr + 2) * 8));
+    if (use_tiles) {
+        if (ba->chunks_dirty) {
+            VIO_CUDA(ctx, cudaStreamSynchronize(st));
+            const size_t nc = std::max<size_t>(1, ba->chunks.size());
+            VIO_CUDA(ctx, ba->d_chunks.reserve(nc * sizeof(SchurChunk)));
+            VIO_CUDA(ctx, ba->d_cov_ptr.reserve(ba->cov_ptr.size() * 4));
+            VIO_CUDA(ctx, ba->d_cov_idx.reserve(ba->cov_idx.size() * 4));
+            VIO_CUDA(ctx, ba->d_free_pose.reserve(std::max<size_t>(1, ba->free_pose.size()) * 4));
+            VIO_CUDA(ctx, ba->d_irregular.reserve(std::max<size_t>(1, ba->irregular.size()) * 4));
+            VIO_CUDA(ctx, ba->d_partS.reserve(nc * kST * kST * 8));
+            VIO_CUDA(ctx, ba->d_partRhs.reserve(nc * kST * 8));
+            if (!ba->chunks.empty()) VIO_CUDA(ctx, cudaMemcpy(ba->d_chunks.p, ba->chunks.data(), ba->chunks.size() * sizeof(SchurChunk), cudaMemcpyHostToDevice));
+            VIO_CUDA(ctx, cudaMemcpy(ba->d_cov_ptr.p, ba->cov_ptr.data(), ba->cov_ptr.size() * 4, cudaMemcpyHostToDevice));
+            VIO_CUDA(ctx, cudaMemcpy(ba->d_cov_idx.p, ba->cov_idx.data(), ba->cov_idx.size() * 4, cudaMemcpyHostToDevice));
+            if (!ba->free_pose.empty()) VIO_CUDA(ctx, cudaMemcpy(ba->d_free_pose.p, ba->free_pose.data(), ba->free_pose.size() * 4, cudaMemcpyHostToDevice));
+            if (!ba->irregular.empty()) VIO_CUDA(ctx, cudaMemcpy(ba->d_irregular.p, ba->irregular.data(), ba->irregular.size() * 4, cudaMemcpyHostToDevice));
+            ba->chunks_dirty = false;
+        }
+        if (!ba->smem_attr_set) {
+            VIO_CUDA(ctx, cudaFuncSetAttribute(k_schur_tile, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSchurSmemBytes));
+            ba->smem_attr_set = true;
+        }
+        if (nch > 0) {
+            { KernelTimer kt_(ctx, "k_schur_tile");
+            k_schur_tile<<<nch, kSThreads, kSchurSmemBytes, st>>>(d, ba->d_chunks.as<SchurChunk>(), apply_loss != 0, ba->d_partS.as<double>(),
+                                                                 ba->d_partRhs.as<double>(), ba->d_partials.as<double>());
+            }
+            VIO_LAUNCH_CHECK(ctx);
+        }
+        if (n > 0) {
+            const long long tot = (long long)n * n + n;
+            { KernelTimer kt_(ctx, "k_schur_reduce");
+            k_schur_reduce<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(dS, n, drhs, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
+                                                                        ba->d_chunks.as<SchurChunk>(), ba->d_cov_ptr.as<int>(),
+                                                                        ba->d_cov_idx.as<int>(), ba->d_free_pose.as<int>());
+            }
+            VIO_LAUNCH_CHECK(ctx);
+        }
+        if (nirr > 0) {
+            { KernelTimer kt_(ctx, "k_schur_warp");
+            k_schur_warp<<<nb_irr, 128, 0, st>>>(d, 0, nirr, ba->d_irregular.as<int>(), apply_loss != 0, dS, n, drhs,
+                                                 ba->d_partials.as<double>() + nch);
+            }
+            VIO_LAUNCH_CHECK(ctx);
+        }
+    } else {
+        VIO_CUDA(ctx, cudaMemsetAsync(ba->d_packed.p, 0, packed * 8, st));
+        if (nirr > 0) {
+            { KernelTimer kt_(ctx, "k_schur_warp");
+            k_schur_warp<<<nb_irr, 128, 0, st>>>(d, ba->lm_begin, ba->lm_end, nullptr, apply_loss != 0, dS, n, drhs, ba->d_partials.as<double>());
+            }
+            VIO_LAUNCH_CHECK(ctx);
+        }
     }
-    VIO_LAUNCH_CHECK(ctx);
-    int rc = sum_partials(ba, nb, dcost);
+    int rc = sum_partials(ba, nch + nb_irr, dcost);
     if (rc) return rc;
     if (n > 0) {
         { KernelTimer kt_(ctx, "k_finish_S");
