@@ -9,14 +9,20 @@
 // system with a std::mutex (:211,414,551), a CTA here owns a private 144 x 144 tile of S in
 // shared memory for its pose window:
 //
+// The CTA is warp-specialised.  Twelve producer warps own a dense (pose slot, landmark slot)
+// grid of 24 x 16 threads per batch of 16 landmarks:
 //   phase A  one thread per observation: residual, Jacobians F (2x6), E (2x3), Huber
-//   phase B  per landmark: E'E (+D^2), g = E'r by a segmented sum; Cholesky E'E = L L';
-//            L^-1 and (E'E)^-1 g
-//   phase C  per observation: F'F and F'(r - E (E'E)^-1 g) summed per pose through a slot
-//            table (no atomics), Z = (F'E) L^-T written to the operand stage
+//   phase B  per landmark: E'E (+D^2), g = E'r summed over the pose slots; Cholesky
+//            E'E = L L'; L^-1 and (E'E)^-1 g
+//   phase C  per observation: F'F and F'(r - E (E'E)^-1 g); the 16 landmark lanes of a pose
+//            slot are one half warp, so the per-pose sums are a shuffle reduce-scatter (no
+//            atomics, no shared memory); Z = (F'E) L^-T goes to one of two operand stages
+// while four consumer warps run
 //   phase D  S_tile -= Z Z'  on the FP64 tensor pipe (mma.sync m8n8k4.f64 = DMMA): the
 //            per-landmark 6x3 * 3x3 * 3x6 products of all pose pairs are one SYRK over the
-//            concatenated landmark columns
+//            concatenated landmark columns of the other stage.
+// Stages are handed over with named barriers (bar.arrive / bar.sync), so the latency-bound
+// evaluation and the pipe-bound SYRK overlap.
 //
 // Every chunk writes its tile to a private slab; k_schur_reduce sums the slabs that cover a
 // cell in a fixed order, so the result is deterministic.  Landmarks that do not fit a window
@@ -31,17 +37,19 @@ constexpr int kSWin = 24;                          // poses per chunk window
 constexpr int kST = 6 * kSWin;                     // 144 tile rows
 constexpr int kSNT = kST / 8;                      // 18 DMMA tiles per dimension
 constexpr int kSTiles = kSNT * (kSNT + 1) / 2;     // 171 stored (upper) tiles
-constexpr int kSThreads = 512;                     // observations per batch
-constexpr int kSWarps = kSThreads / 32;
-constexpr int kSMaxLm = 24;                        // landmarks per batch
-constexpr int kSZPitch = 84;                       // doubles per stage row: 3*kSMaxLm padded, == 4 (mod 16)
+constexpr int kSMaxLm = 16;                        // landmarks per batch
+constexpr int kSProd = kSWin * kSMaxLm;            // 384 producer threads: thread = (pose slot, landmark slot)
+constexpr int kSCons = 128;                        // 4 consumer warps issue the DMMA
+constexpr int kSThreads = kSProd + kSCons;         // 512
+constexpr int kSK = 3 * kSMaxLm;                   // 48 stage columns per batch (12 DMMA k-steps)
+constexpr int kSZPitch = 148;                      // doubles per stage column (>= kST, == 4 mod 16: conflict-free fragments)
 constexpr int kSRed = 9;                           // doubles per observation in the reduction scratch
 
 struct SchurChunk { int lm_begin, lm_end, pbase, span; };
 
 constexpr size_t kSchurSmemBytes =
-    sizeof(double) * ((size_t)kST * kSZPitch + (size_t)kSTiles * 64 + (size_t)kSWin * kPoseStride + (size_t)kSMaxLm * 9 + 32) +
-    sizeof(short) * (size_t)kSMaxLm * kSWin + sizeof(int) * 32;
+    sizeof(double) * (2 * (size_t)kSK * kSZPitch + (size_t)kSTiles * 64 + (size_t)kSWin * kPoseStride + (size_t)kSMaxLm * 9 + 32) +
+    sizeof(short) * (size_t)kSProd + sizeof(int) * 32;
 
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"

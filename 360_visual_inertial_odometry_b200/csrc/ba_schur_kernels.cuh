@@ -14,179 +14,198 @@ __device__ __forceinline__ void tri6(int t, int& a, int& b) {
     b = a + rem;
 }
 
+__device__ __forceinline__ void named_bar_sync(int id, int count) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+__device__ __forceinline__ void named_bar_arrive(int id, int count) {
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+constexpr int kBarProd = 1, kBarFull = 2, kBarEmpty = 4;   // ids: producers-only, full[2], empty[2]
+
 __global__ void __launch_bounds__(kSThreads, 1)
 k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, bool apply_loss, double* __restrict__ partS,
              double* __restrict__ partRhs, double* __restrict__ partCost) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    double* Z = reinterpret_cast<double*>(smem_raw);            // [kST][kSZPitch] operand stage
-    double* sRed = Z;                                           // alias: [kSThreads][kSRed] reduction scratch
-    double* St = Z + kST * kSZPitch;                            // [kSTiles][64] S tile, DMMA fragment order
+    double* Zst = reinterpret_cast<double*>(smem_raw);          // [2][kSK][kSZPitch] operand stages, Z^T: column-major in k
+    double* St = Zst + 2 * kSK * kSZPitch;                      // [kSTiles][64] S tile, DMMA fragment order
     double* sPose = St + kSTiles * 64;                          // [kSWin][kPoseStride]
     double* sLmk = sPose + kSWin * kPoseStride;                 // [kSMaxLm][9]: L^-1 (6), (E'E)^-1 g (3)
     double* sBlk = sLmk + kSMaxLm * 9;                          // [32] block-sum scratch
-    short* sOst = reinterpret_cast<short*>(sBlk + 32);          // [kSMaxLm][kSWin] thread that holds (landmark, pose)
-    int* sLmp = reinterpret_cast<int*>(sOst + kSMaxLm * kSWin); // [kSMaxLm + 1] lm_ptr of the batch
+    short* sOst = reinterpret_cast<short*>(sBlk + 32);          // [kSProd] observation (batch-relative) of slot (w, ls)
+    int* sLmp = reinterpret_cast<int*>(sOst + kSProd);          // [kSMaxLm + 1] lm_ptr of the batch
 
     const SchurChunk ch = chunks[blockIdx.x];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < kST * kSZPitch; i += kSThreads) Z[i] = 0.0;
     for (int i = tid; i < kSTiles * 64; i += kSThreads) St[i] = 0.0;
     for (int i = tid; i < ch.span * kPoseStride; i += kSThreads) sPose[i] = d.posebuf[(size_t)ch.pbase * kPoseStride + i];
-
-    // per-pose sums: thread (w, e) with w = tid / 9, e = tid % 9 owns entries 9*round + e of
-    // [F'F upper triangle (21) | F'(r - E ig) (6)] of pose slot w
-    double pacc[3] = {0.0, 0.0, 0.0};
+    __syncthreads();
+    const int nbatch = (ch.lm_end - ch.lm_begin + kSMaxLm - 1) / kSMaxLm;
+    double pacc0 = 0.0, pacc1 = 0.0;   // producer lane j of pose slot w: entries 2j, 2j+1 of [F'F tri (21) | F'(r - E ig) (6)]
     double cost = 0.0;
-    int cur = ch.lm_begin;
-    while (cur < ch.lm_end) {
-        __syncthreads();   // stage / tile free: previous batch's DMMA (or the initial zeroing) is done
-        if (tid <= kSMaxLm) sLmp[tid] = d.lm_ptr[min(cur + tid, ch.lm_end)];
-        for (int i = tid; i < kSMaxLm * kSWin; i += kSThreads) sOst[i] = -1;
-        __syncthreads();
-        const int o0 = sLmp[0];
-        int NB = 0;
-        while (NB < kSMaxLm && cur + NB < ch.lm_end && sLmp[NB + 1] - o0 <= kSThreads) ++NB;
-        const int nobs = sLmp[NB] - o0;
-        const int NBp = (NB + 3) & ~3;
-        // ---- phase A: evaluate one observation per thread
-        const bool act = tid < nobs;
-        int ls = 0, w = 0;
-        bool emit = false;     // free pose and free landmark: contributes to Z
-        bool pfree = false;
-        double r[2], F[12], E[6];
-        if (act) {
-            const int i = o0 + tid;
-            const int p = d.pose[i], l = d.point[i];
-            ls = l - cur; w = p - ch.pbase;
-            const double Pw[3] = {__ldg(d.points + 3 * (size_t)l), __ldg(d.points + 3 * (size_t)l + 1),
-                                  __ldg(d.points + 3 * (size_t)l + 2)};
-            cost += obs_evaluate<true>(sPose + kPoseStride * w, Pw, d.u[i], d.v[i], d.outlier[i] != 0, d.cam, apply_loss, r, F, E);
-            pfree = d.free_map[p] >= 0;
-            emit = pfree && d.point_fixed[l] == 0;
-            sOst[ls * kSWin + w] = (short)tid;
-            double* q = sRed + tid * kSRed;
-            q[0] = E[0] * E[0] + E[3] * E[3]; q[1] = E[0] * E[1] + E[3] * E[4]; q[2] = E[0] * E[2] + E[3] * E[5];
-            q[3] = E[1] * E[1] + E[4] * E[4]; q[4] = E[1] * E[2] + E[4] * E[5]; q[5] = E[2] * E[2] + E[5] * E[5];
-            q[6] = E[0] * r[0] + E[3] * r[1]; q[7] = E[1] * r[0] + E[4] * r[1]; q[8] = E[2] * r[0] + E[5] * r[1];
-        }
-        __syncthreads();
-        // ---- phase B: per-landmark sums, Cholesky, L^-1, (E'E)^-1 g
-        if (tid < NB * 9) {
-            const int bl = tid / 9, e = tid - bl * 9;
-            double s = 0.0;
-            for (int j = sLmp[bl] - o0; j < sLmp[bl + 1] - o0; ++j) s += sRed[j * kSRed + e];
-            sLmk[tid] = s;
-        }
-        __syncthreads();
-        if (tid < NB) {
-            const int l = cur + tid;
-            double* q = sLmk + tid * 9;
-            double h[6] = {q[0], q[1], q[2], q[3], q[4], q[5]};
-            const double g0 = q[6], g1 = q[7], g2 = q[8];
-            double li[6] = {0, 0, 0, 0, 0, 0}, ig[3] = {0, 0, 0};
-            if (d.point_fixed[l] == 0) {
-                if (d.D) {
-                    const double* Dl = d.D + 6 * (size_t)d.K + 3 * (size_t)l;
-                    h[0] += Dl[0] * Dl[0]; h[3] += Dl[1] * Dl[1]; h[5] += Dl[2] * Dl[2];
-                }
-                const double l00 = sqrt(h[0]);
-                const double l10 = h[1] / l00, l20 = h[2] / l00;
-                const double l11 = sqrt(h[3] - l10 * l10);
-                const double l21 = (h[4] - l20 * l10) / l11;
-                const double l22 = sqrt(h[5] - l20 * l20 - l21 * l21);
-                const double i00 = 1.0 / l00, i11 = 1.0 / l11, i22 = 1.0 / l22;
-                const double i10 = -l10 * i00 * i11;
-                const double i21 = -l21 * i11 * i22;
-                const double i20 = -(l20 * i00 + l21 * i10) * i22;
-                li[0] = i00; li[1] = i10; li[2] = i11; li[3] = i20; li[4] = i21; li[5] = i22;
-                bool ok = true;
-#pragma unroll
-                for (int j = 0; j < 6; ++j) ok = ok && isfinite(li[j]);
-                if (!ok) {   // rank-deficient landmark: not eliminated (as the general kernel)
-#pragma unroll
-                    for (int j = 0; j < 6; ++j) li[j] = 0.0;
-                }
-                // (E'E)^-1 g = L^-T (L^-1 g)
-                const double y0 = li[0] * g0, y1 = li[1] * g0 + li[2] * g1, y2 = li[3] * g0 + li[4] * g1 + li[5] * g2;
-                ig[0] = li[0] * y0 + li[1] * y1 + li[3] * y2;
-                ig[1] = li[2] * y1 + li[4] * y2;
-                ig[2] = li[5] * y2;
+
+    if (tid < kSProd) {
+        // ================= producers: thread = (pose slot w, landmark slot ls) =================
+        const int w = tid >> 4, ls = tid & 15;
+        for (int b = 0; b < nbatch; ++b) {
+            const int cur = ch.lm_begin + b * kSMaxLm;
+            const int NB = min(kSMaxLm, ch.lm_end - cur);
+            double* Zs = Zst + (b & 1) * kSK * kSZPitch;
+            double* sRed = Zs;                                  // alias: [kSProd][kSRed]
+            if (b >= 2) named_bar_sync(kBarEmpty + (b & 1), kSThreads);   // consumers are done with this stage
+            if (tid <= kSMaxLm) sLmp[tid] = d.lm_ptr[min(cur + tid, ch.lm_end)];
+            sOst[tid] = -1;
+            named_bar_sync(kBarProd, kSProd);
+            const int o0 = sLmp[0], nobs = sLmp[NB] - o0;       // <= kSProd: regular landmarks have <= kSWin observations
+            if (tid < nobs) {
+                const int i = o0 + tid;
+                sOst[(d.pose[i] - ch.pbase) * kSMaxLm + (d.point[i] - cur)] = (short)tid;
             }
+            named_bar_sync(kBarProd, kSProd);
+            // ---- phase A
+            const int oi = sOst[tid];
+            double r[2] = {0.0, 0.0}, F[12], E[6];
 #pragma unroll
-            for (int j = 0; j < 6; ++j) q[j] = li[j];
-            q[6] = ig[0]; q[7] = ig[1]; q[8] = ig[2];
-        }
-        __syncthreads();
-        // ---- phase C: per-pose sums of F'F and F'(r - E ig) in three rounds of nine entries
-        double li[6] = {0, 0, 0, 0, 0, 0};
-        double s0 = 0.0, s1 = 0.0;
-        if (act) {
-            const double* q = sLmk + ls * 9;
+            for (int j = 0; j < 12; ++j) F[j] = 0.0;
 #pragma unroll
-            for (int j = 0; j < 6; ++j) li[j] = q[j];
-            s0 = r[0] - (E[0] * q[6] + E[1] * q[7] + E[2] * q[8]);
-            s1 = r[1] - (E[3] * q[6] + E[4] * q[7] + E[5] * q[8]);
-        }
+            for (int j = 0; j < 6; ++j) E[j] = 0.0;
+            if (oi >= 0) {
+                const int i = o0 + oi;
+                const int p = ch.pbase + w, l = cur + ls;
+                const double Pw[3] = {__ldg(d.points + 3 * (size_t)l), __ldg(d.points + 3 * (size_t)l + 1),
+                                      __ldg(d.points + 3 * (size_t)l + 2)};
+                cost += obs_evaluate<true>(sPose + kPoseStride * w, Pw, d.u[i], d.v[i], d.outlier[i] != 0, d.cam, apply_loss, r, F, E);
+                if (d.free_map[p] < 0) {   // constant pose: no F block (its E block still enters E'E)
 #pragma unroll
-        for (int round = 0; round < 3; ++round) {
-            if (act) {
+                    for (int j = 0; j < 12; ++j) F[j] = 0.0;
+                }
+            }
+            {
                 double* q = sRed + tid * kSRed;
-#pragma unroll
-                for (int e = 0; e < 9; ++e) {
-                    const int t = 9 * round + e;   // compile-time after unrolling
-                    double v;
-                    if (t < 21) {
-                        int a = 0, rem = t;
-                        while (rem >= 6 - a) { rem -= 6 - a; ++a; }
-                        const int b = a + rem;
-                        v = F[a] * F[b] + F[6 + a] * F[6 + b];
-                    } else {
-                        v = F[t - 21] * s0 + F[6 + t - 21] * s1;
-                    }
-                    q[e] = pfree ? v : 0.0;
-                }
+                q[0] = E[0] * E[0] + E[3] * E[3]; q[1] = E[0] * E[1] + E[3] * E[4]; q[2] = E[0] * E[2] + E[3] * E[5];
+                q[3] = E[1] * E[1] + E[4] * E[4]; q[4] = E[1] * E[2] + E[4] * E[5]; q[5] = E[2] * E[2] + E[5] * E[5];
+                q[6] = E[0] * r[0] + E[3] * r[1]; q[7] = E[1] * r[0] + E[4] * r[1]; q[8] = E[2] * r[0] + E[5] * r[1];
             }
-            __syncthreads();
-            if (tid < kSWin * 9) {
-                const int pw = tid / 9, e = tid - pw * 9;
+            named_bar_sync(kBarProd, kSProd);
+            // ---- phase B: per-landmark sums over the pose slots, Cholesky, L^-1, (E'E)^-1 g
+            if (tid < kSMaxLm * 9) {
+                const int bl = tid / 9, e = tid - bl * 9;
                 double s = 0.0;
-                for (int bl = 0; bl < NB; ++bl) {
-                    const int src = sOst[bl * kSWin + pw];
-                    if (src >= 0) s += sRed[src * kSRed + e];
+#pragma unroll 4
+                for (int pw = 0; pw < kSWin; ++pw) s += sRed[(pw * kSMaxLm + bl) * kSRed + e];
+                sLmk[tid] = s;
+            }
+            named_bar_sync(kBarProd, kSProd);
+            if (tid < kSMaxLm) {
+                double* q = sLmk + tid * 9;
+                double li[6] = {0, 0, 0, 0, 0, 0}, ig[3] = {0, 0, 0};
+                if (tid < NB && d.point_fixed[cur + tid] == 0) {
+                    const int l = cur + tid;
+                    double h[6] = {q[0], q[1], q[2], q[3], q[4], q[5]};
+                    const double g0 = q[6], g1 = q[7], g2 = q[8];
+                    if (d.D) {
+                        const double* Dl = d.D + 6 * (size_t)d.K + 3 * (size_t)l;
+                        h[0] += Dl[0] * Dl[0]; h[3] += Dl[1] * Dl[1]; h[5] += Dl[2] * Dl[2];
+                    }
+                    const double l00 = sqrt(h[0]);
+                    const double l10 = h[1] / l00, l20 = h[2] / l00;
+                    const double l11 = sqrt(h[3] - l10 * l10);
+                    const double l21 = (h[4] - l20 * l10) / l11;
+                    const double l22 = sqrt(h[5] - l20 * l20 - l21 * l21);
+                    const double i00 = 1.0 / l00, i11 = 1.0 / l11, i22 = 1.0 / l22;
+                    const double i10 = -l10 * i00 * i11;
+                    const double i21 = -l21 * i11 * i22;
+                    const double i20 = -(l20 * i00 + l21 * i10) * i22;
+                    li[0] = i00; li[1] = i10; li[2] = i11; li[3] = i20; li[4] = i21; li[5] = i22;
+                    bool ok = true;
+#pragma unroll
+                    for (int j = 0; j < 6; ++j) ok = ok && isfinite(li[j]);
+                    if (!ok) {   // rank-deficient landmark: not eliminated (as the general kernel)
+#pragma unroll
+                        for (int j = 0; j < 6; ++j) li[j] = 0.0;
+                    }
+                    // (E'E)^-1 g = L^-T (L^-1 g)
+                    const double y0 = li[0] * g0, y1 = li[1] * g0 + li[2] * g1, y2 = li[3] * g0 + li[4] * g1 + li[5] * g2;
+                    ig[0] = li[0] * y0 + li[1] * y1 + li[3] * y2;
+                    ig[1] = li[2] * y1 + li[4] * y2;
+                    ig[2] = li[5] * y2;
                 }
-                pacc[round] += s;
-            }
-            __syncthreads();
-        }
-        // ---- operand stage: Z = (F'E) L^-T for every (pose slot, landmark) of the batch, zeros elsewhere
-        if (act) {
-            double* zr = Z + (6 * w) * kSZPitch + 3 * ls;
 #pragma unroll
-            for (int a = 0; a < 6; ++a) {
-                const double w0 = F[a] * E[0] + F[6 + a] * E[3];
-                const double w1 = F[a] * E[1] + F[6 + a] * E[4];
-                const double w2 = F[a] * E[2] + F[6 + a] * E[5];
-                zr[a * kSZPitch + 0] = emit ? w0 * li[0] : 0.0;
-                zr[a * kSZPitch + 1] = emit ? w0 * li[1] + w1 * li[2] : 0.0;
-                zr[a * kSZPitch + 2] = emit ? w0 * li[3] + w1 * li[4] + w2 * li[5] : 0.0;
+                for (int j = 0; j < 6; ++j) q[j] = li[j];
+                q[6] = ig[0]; q[7] = ig[1]; q[8] = ig[2];
             }
-        }
-        for (int t = tid; t < NBp * kSWin; t += kSThreads) {
-            const int bl = t / kSWin, pw = t - bl * kSWin;
-            if (bl >= NB || sOst[t] < 0) {
-                double* zr = Z + (6 * pw) * kSZPitch + 3 * bl;
+            named_bar_sync(kBarProd, kSProd);
+            // ---- phase C
+            const double* q = sLmk + ls * 9;
+            const double s0 = r[0] - (E[0] * q[6] + E[1] * q[7] + E[2] * q[8]);
+            const double s1 = r[1] - (E[3] * q[6] + E[4] * q[7] + E[5] * q[8]);
+            // per-pose sums over the 16 landmark lanes of this half warp: recursive-halving
+            // reduce-scatter of the 32 (27 used) entries; lane j ends with entries 2j, 2j+1
+            {
+                constexpr int TA[32] = {0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 4, 4, 5, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+                constexpr int TB[32] = {0, 1, 2, 3, 4, 5, 1, 2, 3, 4, 5, 2, 3, 4, 5, 3, 4, 5, 4, 5, 5, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+                double x[16];
+                const bool up8 = (lane & 8) != 0;
 #pragma unroll
-                for (int a = 0; a < 6; ++a) { zr[a * kSZPitch] = 0.0; zr[a * kSZPitch + 1] = 0.0; zr[a * kSZPitch + 2] = 0.0; }
+                for (int i = 0; i < 16; ++i) {
+                    double lo, hi;   // entries i and i + 16 of this thread (compile-time indices)
+                    lo = F[TA[i]] * F[TB[i]] + F[6 + TA[i]] * F[6 + TB[i]];
+                    if (i + 16 < 21) {
+                        hi = F[TA[i + 16]] * F[TB[i + 16]] + F[6 + TA[i + 16]] * F[6 + TB[i + 16]];
+                    } else if (i + 16 < 27) {
+                        hi = F[i + 16 - 21] * s0 + F[6 + i + 16 - 21] * s1;
+                    } else {
+                        hi = 0.0;
+                    }
+                    const double keep = up8 ? hi : lo, send = up8 ? lo : hi;
+                    x[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+                }
+#define SCHUR_RS_STEP(M, HALF)                                                                    \
+                {                                                                                 \
+                    const bool up = (lane & (M)) != 0;                                            \
+                    _Pragma("unroll") for (int i = 0; i < (HALF); ++i) {                          \
+                        const double keep = up ? x[i + (HALF)] : x[i], send = up ? x[i] : x[i + (HALF)]; \
+                        x[i] = keep + __shfl_xor_sync(0xffffffffu, send, (M));                    \
+                    }                                                                             \
+                }
+                SCHUR_RS_STEP(4, 8)
+                SCHUR_RS_STEP(2, 4)
+                SCHUR_RS_STEP(1, 2)
+#undef SCHUR_RS_STEP
+                pacc0 += x[0]; pacc1 += x[1];
             }
+            // ---- operand stage: Z = (F'E) L^-T (zero for empty slots, constant poses and constant landmarks)
+            {
+                double z[3][6];
+#pragma unroll
+                for (int a = 0; a < 6; ++a) {
+                    const double w0 = F[a] * E[0] + F[6 + a] * E[3];
+                    const double w1 = F[a] * E[1] + F[6 + a] * E[4];
+                    const double w2 = F[a] * E[2] + F[6 + a] * E[5];
+                    z[0][a] = w0 * q[0];
+                    z[1][a] = w0 * q[1] + w1 * q[2];
+                    z[2][a] = w0 * q[3] + w1 * q[4] + w2 * q[5];
+                }
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    double2* dst = reinterpret_cast<double2*>(Zs + (3 * ls + c) * kSZPitch + 6 * w);
+                    dst[0] = make_double2(z[c][0], z[c][1]);
+                    dst[1] = make_double2(z[c][2], z[c][3]);
+                    dst[2] = make_double2(z[c][4], z[c][5]);
+                }
+            }
+            __threadfence_block();
+            named_bar_arrive(kBarFull + (b & 1), kSThreads);
         }
-        __syncthreads();
-        // ---- phase D: S_tile -= Z Z' over the batch's 3*NBp columns, 16x16 blocks of the upper triangle
-        {
-            const int nb2 = (6 * ch.span + 15) >> 4;
-            const int nblk = nb2 * (nb2 + 1) / 2;
-            const int ksteps = (3 * NBp) >> 2;
-            const int fr = lane >> 2, fc = lane & 3;
-            for (int blk = warp; blk < nblk; blk += kSWarps) {
+    } else {
+        // ================= consumers: S_tile -= Z Z' over the stage's 48 columns =================
+        const int cw = warp - kSProd / 32;
+        const int nb2 = (6 * ch.span + 15) >> 4;
+        const int nblk = nb2 * (nb2 + 1) / 2;
+        const int fr = lane >> 2, fc = lane & 3;
+        for (int b = 0; b < nbatch; ++b) {
+            const double* Zs = Zst + (b & 1) * kSK * kSZPitch;
+            named_bar_sync(kBarFull + (b & 1), kSThreads);
+            for (int blk = cw; blk < nblk; blk += kSCons / 32) {
                 int bi = 0, rem = blk;
                 while (rem >= nb2 - bi) { rem -= nb2 - bi; ++bi; }
                 const int bj = bi + rem;
@@ -197,12 +216,12 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, bool apply_loss, do
                 double2* c10 = diag ? c00 : reinterpret_cast<double2*>(St + schur_tile_index(2 * bi + 1, 2 * bj) * 64) + lane;
                 double2 a00 = *c00, a01 = *c01, a11 = *c11, a10 = make_double2(0.0, 0.0);
                 if (!diag) a10 = *c10;
-                const double* za = Z + (16 * bi + fr) * kSZPitch + fc;
-                const double* zb = Z + (16 * bj + fr) * kSZPitch + fc;
-#pragma unroll 3
-                for (int ks = 0; ks < ksteps; ++ks) {
-                    const double x0 = -za[4 * ks], x1 = -za[8 * kSZPitch + 4 * ks];
-                    const double y0 = zb[4 * ks], y1 = zb[8 * kSZPitch + 4 * ks];
+                const double* za = Zs + fc * kSZPitch + 16 * bi + fr;
+                const double* zb = Zs + fc * kSZPitch + 16 * bj + fr;
+#pragma unroll 4
+                for (int ks = 0; ks < kSK / 4; ++ks) {
+                    const double x0 = -za[4 * ks * kSZPitch], x1 = -za[4 * ks * kSZPitch + 8];
+                    const double y0 = zb[4 * ks * kSZPitch], y1 = zb[4 * ks * kSZPitch + 8];
                     dmma884(a00.x, a00.y, x0, y0);
                     dmma884(a01.x, a01.y, x0, y1);
                     dmma884(a11.x, a11.y, x1, y1);
@@ -211,25 +230,29 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, bool apply_loss, do
                 *c00 = a00; *c01 = a01; *c11 = a11;
                 if (!diag) *c10 = a10;
             }
+            if (b + 2 < nbatch) {
+                __threadfence_block();
+                named_bar_arrive(kBarEmpty + (b & 1), kSThreads);
+            }
         }
-        cur += NB;
     }
     __syncthreads();
     // ---- fold the per-pose sums into the tile (diagonal pose blocks) and the chunk's rhs slab
     double* outRhs = partRhs + (size_t)blockIdx.x * kST;
-    if (tid < kSWin * 9) {
-        const int pw = tid / 9, e = tid - pw * 9;
+    if (tid < kSProd) {
+        const int pw = tid >> 4, j = tid & 15;
 #pragma unroll
-        for (int round = 0; round < 3; ++round) {
-            const int t = 9 * round + e;
+        for (int h = 0; h < 2; ++h) {
+            const int t = 2 * j + h;
+            const double v = h ? pacc1 : pacc0;
             if (t < 21) {
                 int a, b;
                 tri6(t, a, b);
                 const int R = 6 * pw + a, Cc = 6 * pw + b;
-                St[schur_elem_index(R, Cc)] += pacc[round];                       // R <= Cc: always a stored tile
-                if (a != b && (Cc >> 3) == (R >> 3)) St[schur_elem_index(Cc, R)] += pacc[round];   // mirror inside a diagonal tile
-            } else {
-                outRhs[6 * pw + (t - 21)] = pacc[round];
+                St[schur_elem_index(R, Cc)] += v;                                            // R <= Cc: always a stored tile
+                if (a != b && (Cc >> 3) == (R >> 3)) St[schur_elem_index(Cc, R)] += v;       // mirror inside a diagonal tile
+            } else if (t < 27) {
+                outRhs[6 * pw + (t - 21)] = v;
             }
         }
     }
@@ -240,7 +263,7 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, bool apply_loss, do
         const int nt = 2 * ((6 * ch.span + 15) >> 4);
         const int fr = lane >> 2, fc = lane & 3;
         for (int ti = 0; ti < nt; ++ti)
-            for (int tj = ti + warp; tj < nt; tj += kSWarps) {
+            for (int tj = ti + warp; tj < nt; tj += kSThreads / 32) {
                 const double2 v = *(reinterpret_cast<const double2*>(St + schur_tile_index(ti, tj) * 64) + lane);
                 *reinterpret_cast<double2*>(outS + (size_t)(8 * ti + fr) * kST + 8 * tj + 2 * fc) = v;
             }
@@ -250,7 +273,7 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, bool apply_loss, do
     if (lane == 0) sBlk[warp] = cost;
     __syncthreads();
     if (warp == 0) {
-        double t = lane < kSWarps ? sBlk[lane] : 0.0;
+        double t = lane < kSThreads / 32 ? sBlk[lane] : 0.0;
         t = warp_sum(t);
         if (lane == 0) partCost[blockIdx.x] = t;
     }
