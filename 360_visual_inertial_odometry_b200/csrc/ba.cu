@@ -55,9 +55,9 @@ struct vio360_ba {
     // chunked (atomic-free) Schur path: see ba_schur.cuh
     std::vector<int> h_pose;                 // landmark-major pose index of every observation
     std::vector<SchurChunk> chunks;
-    std::vector<int> irregular, cov_ptr, cov_idx, free_pose;
-    DevBuf d_chunks, d_cov_ptr, d_cov_idx, d_free_pose, d_irregular, d_partS, d_partRhs;
-    bool chunks_dirty = true, smem_attr_set = false;
+    std::vector<int> irregular, cov_ptr, cov_idx, free_pose, reach, slot_table;
+    DevBuf d_chunks, d_cov_ptr, d_cov_idx, d_free_pose, d_irregular, d_partS, d_partRhs, d_reach, d_slots;
+    bool chunks_dirty = true, smem_attr_set = false, chunk_error = false;
 };
 
 // ------------------------------------------------------------------------ kernels
@@ -452,7 +452,7 @@ extern "C" void vio360_ba_destroy(vio360_ba* ba) {
                       &ba->d_pose_ptr, &ba->d_pose_order, &ba->d_Twb, &ba->d_Tcb, &ba->d_posebuf, &ba->d_pose_delta,
                       &ba->d_points, &ba->d_free_map, &ba->d_point_fixed, &ba->d_D, &ba->d_r, &ba->d_Jp, &ba->d_Jl,
                       &ba->d_partials, &ba->d_packed, &ba->d_blocks, &ba->d_chi2, &ba->d_flag,
-                      &ba->d_chunks, &ba->d_cov_ptr, &ba->d_cov_idx, &ba->d_free_pose, &ba->d_irregular, &ba->d_partS, &ba->d_partRhs};
+                      &ba->d_chunks, &ba->d_cov_ptr, &ba->d_cov_idx, &ba->d_free_pose, &ba->d_irregular, &ba->d_partS, &ba->d_partRhs, &ba->d_reach, &ba->d_slots};
     for (DevBuf* b : bufs) b->release();
     ba->pin.release();
     delete ba;
@@ -468,7 +468,7 @@ static void build_chunks(vio360_ba* ba) {
     const int nlm = ba->lm_end - ba->lm_begin;
     const int target = std::max(kSMaxLm, (nlm + 2 * ba->ctx->num_sms - 1) / std::max(1, 2 * ba->ctx->num_sms));
     std::vector<int> seen(K, -1);
-    SchurChunk cur{ba->lm_begin, ba->lm_begin, 0, 0};
+    SchurChunk cur{ba->lm_begin, ba->lm_begin, 0, 0, 0, 0, 0, 0};
     int cmin = K, cmax = -1;
     auto close = [&](int end) {
         cur.lm_end = end;
@@ -509,6 +509,23 @@ static void build_chunks(vio360_ba* ba) {
     std::vector<int> fill(ba->cov_ptr.begin(), ba->cov_ptr.end() - 1);
     for (int c = 0; c < (int)ba->chunks.size(); ++c)
         for (int p = ba->chunks[c].pbase; p < ba->chunks[c].pbase + ba->chunks[c].span; ++p) ba->cov_idx[fill[p]++] = c;
+    // slot table: per batch of kSMaxLm landmarks, the observation held by thread (pose slot, landmark slot)
+    int nbatch_total = 0;
+    for (SchurChunk& c : ba->chunks) { c.batch0 = nbatch_total; nbatch_total += (c.lm_end - c.lm_begin + kSMaxLm - 1) / kSMaxLm; }
+    ba->slot_table.assign((size_t)std::max(1, nbatch_total) * kSProd, -1);
+    for (const SchurChunk& c : ba->chunks)
+        for (int l = c.lm_begin; l < c.lm_end; ++l) {
+            const int b = (l - c.lm_begin) / kSMaxLm, ls = (l - c.lm_begin) % kSMaxLm;
+            int* row = ba->slot_table.data() + (size_t)(c.batch0 + b) * kSProd;
+            for (int q = ba->lm_ptr[l]; q < ba->lm_ptr[l + 1]; ++q) {
+                const int pw = ba->h_pose[q] - c.pbase;
+                if (pw < 0 || pw >= c.span || row[pw * kSMaxLm + ls] != -1) { ba->chunk_error = true; continue; }
+                row[pw * kSMaxLm + ls] = q;
+            }
+        }
+    ba->reach.assign(K, -1);
+    for (const SchurChunk& c : ba->chunks)
+        for (int p = c.pbase; p < c.pbase + c.span; ++p) ba->reach[p] = std::max(ba->reach[p], c.pbase + c.span - 1);
     ba->free_pose.clear();
     for (int k = 0; k < K; ++k) if (ba->free_map[k] >= 0) ba->free_pose.push_back(k);
     ba->chunks_dirty = true;
@@ -805,6 +822,7 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
     }
     double* dS = ba->d_packed.as<double>(); double* drhs = dS + (size_t)n * n; double* dcost = drhs + n;
     BaDev d = make_dev(ba);
+    if (ba->chunk_error) return vio360_fail(ctx, VIO360_ERR_STATE, "internal: inconsistent chunk table");
     const bool use_tiles = getenv("VIO360_BA_ATOMIC") == nullptr;   // tuning / A-B switch: the general kernel only
     const int nch = use_tiles ? (int)ba->chunks.size() : 0;
     const int nirr = use_tiles ? (int)ba->irregular.size() : ba->lm_end - ba->lm_begin;
@@ -821,6 +839,10 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
             VIO_CUDA(ctx, ba->d_irregular.reserve(std::max<size_t>(1, ba->irregular.size()) * 4));
             VIO_CUDA(ctx, ba->d_partS.reserve(nc * kST * kST * 8));
             VIO_CUDA(ctx, ba->d_partRhs.reserve(nc * kST * 8));
+            VIO_CUDA(ctx, ba->d_reach.reserve(ba->reach.size() * 4));
+            VIO_CUDA(ctx, ba->d_slots.reserve(ba->slot_table.size() * 4));
+            VIO_CUDA(ctx, cudaMemcpy(ba->d_slots.p, ba->slot_table.data(), ba->slot_table.size() * 4, cudaMemcpyHostToDevice));
+            VIO_CUDA(ctx, cudaMemcpy(ba->d_reach.p, ba->reach.data(), ba->reach.size() * 4, cudaMemcpyHostToDevice));
             if (!ba->chunks.empty()) VIO_CUDA(ctx, cudaMemcpy(ba->d_chunks.p, ba->chunks.data(), ba->chunks.size() * sizeof(SchurChunk), cudaMemcpyHostToDevice));
             VIO_CUDA(ctx, cudaMemcpy(ba->d_cov_ptr.p, ba->cov_ptr.data(), ba->cov_ptr.size() * 4, cudaMemcpyHostToDevice));
             VIO_CUDA(ctx, cudaMemcpy(ba->d_cov_idx.p, ba->cov_idx.data(), ba->cov_idx.size() * 4, cudaMemcpyHostToDevice));
@@ -834,19 +856,34 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
         }
         if (nch > 0) {
             { KernelTimer kt_(ctx, "k_schur_tile");
-            k_schur_tile<<<nch, kSThreads, kSchurSmemBytes, st>>>(d, ba->d_chunks.as<SchurChunk>(), apply_loss != 0, ba->d_partS.as<double>(),
+            k_schur_tile<<<nch, kSThreads, kSchurSmemBytes, st>>>(d, ba->d_chunks.as<SchurChunk>(), ba->d_slots.as<int>(), apply_loss != 0, ba->d_partS.as<double>(),
                                                                  ba->d_partRhs.as<double>(), ba->d_partials.as<double>());
             }
             VIO_LAUNCH_CHECK(ctx);
         }
+        if (ctx->debug_sync) { fprintf(stderr, "schur: n=%d nch=%d nirr=%d K=%d cov=%zu\n", n, nch, nirr, ba->K, ba->cov_idx.size()); for (auto& c : ba->chunks) fprintf(stderr, "  chunk lm[%d,%d) pbase %d span %d batch0 %d\n", c.lm_begin, c.lm_end, c.pbase, c.span, c.batch0); }
+        const bool fused = nirr == 0 && n > 0;   // one pass: sum slabs, mirror, LM diagonal, cost
         if (n > 0) {
-            const long long tot = (long long)n * n + n;
+            const dim3 nblk(ba->n_free, ba->n_free);
+            const double* Dp = ba->use_D ? ba->d_D.as<double>() : nullptr;
             { KernelTimer kt_(ctx, "k_schur_reduce");
-            k_schur_reduce<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(dS, n, drhs, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
-                                                                        ba->d_chunks.as<SchurChunk>(), ba->d_cov_ptr.as<int>(),
-                                                                        ba->d_cov_idx.as<int>(), ba->d_free_pose.as<int>());
+            if (fused)
+                k_schur_reduce<true><<<nblk, 36 * kRedLanes, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
+                                                           ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),
+                                                           ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int>(), ba->d_reach.as<int>(),
+                                                           ba->d_free_pose.as<int>(), Dp, ba->shard_rank == 0);
+            else
+                k_schur_reduce<false><<<nblk, 36 * kRedLanes, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
+                                                            ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),
+                                                            ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int>(), ba->d_reach.as<int>(),
+                                                            ba->d_free_pose.as<int>(), Dp, false);
             }
             VIO_LAUNCH_CHECK(ctx);
+        }
+        if (fused) {
+            ba->has_reduced = true;
+            if (S || rhs || cost) return vio360_ba_fetch_reduced_system(ba, S, rhs, cost);
+            return VIO360_OK;   // asynchronous on the context's stream
         }
         if (nirr > 0) {
             { KernelTimer kt_(ctx, "k_schur_warp");

@@ -21,6 +21,17 @@
 namespace vio360 {
 
 constexpr double kPi = 3.14159265358979323846;
+constexpr double kInvPi = 0.31830988618379067154;
+constexpr double kInv2Pi = 0.15915494309189533577;
+
+// 1/sqrt(x): the device intrinsic is ~1 ulp; every use below is followed by a 1e-9 tolerance.
+VIO_HD double vio_rsqrt(double x) {
+#if defined(__CUDA_ARCH__)
+    return rsqrt(x);
+#else
+    return 1.0 / sqrt(x);
+#endif
+}
 constexpr int kPoseStride = 33;  // doubles per prepared pose: Rcw 9, tcw 3, Rbw 9, tbw 3, Mcp 9
 
 // ---------------------------------------------------------------- 3x3 helpers
@@ -210,24 +221,27 @@ VIO_HD void cam_const_init(CamConst& c, double cols, double rows, const double* 
 }
 
 // Pixel error of one observation: returns branch 0 ok / 1 tiny depth / 2 large error.
-struct ObsProj { double x, y, z, L, du, dv; int branch; };
+struct ObsProj { double x, y, z, L_sq, inv_L, du, dv; int branch; };
 
+// Divisions and square roots of Factors.cpp:369-419 are restated with one reciprocal square
+// root and multiplications (the FP64 pipe has no divider; a division costs ~17 DFMA).
 VIO_HD void obs_project(const double* pose, const double* Pw, double u_obs, double v_obs,
                         const CamConst& c, ObsProj& p) {
     const double* Rcw = pose; const double* tcw = pose + 9;
     p.x = Rcw[0] * Pw[0] + Rcw[1] * Pw[1] + Rcw[2] * Pw[2] + tcw[0];
     p.y = Rcw[3] * Pw[0] + Rcw[4] * Pw[1] + Rcw[5] * Pw[2] + tcw[1];
     p.z = Rcw[6] * Pw[0] + Rcw[7] * Pw[1] + Rcw[8] * Pw[2] + tcw[2];
-    p.L = sqrt(p.x * p.x + p.y * p.y + p.z * p.z);
-    p.branch = 0; p.du = 0.0; p.dv = 0.0;
-    if (p.L < 1e-10) { p.branch = 1; return; }
+    p.L_sq = p.x * p.x + p.y * p.y + p.z * p.z;
+    p.branch = 0; p.du = 0.0; p.dv = 0.0; p.inv_L = 0.0;
+    if (p.L_sq < 1e-20) { p.branch = 1; return; }          // L < 1e-10
+    p.inv_L = vio_rsqrt(p.L_sq);
     const double theta = atan2(p.x, p.z);
-    const double phi = -asin(p.y / p.L);
-    const double u = c.cols * (0.5 + theta / (2.0 * kPi));
-    const double v = c.rows * (0.5 - phi / kPi);
+    const double phi = -asin(p.y * p.inv_L);
+    const double u = c.cols * (0.5 + theta * kInv2Pi);
+    const double v = c.rows * (0.5 - phi * kInvPi);
     double du = u_obs - u;
-    if (du > c.cols / 2.0) du -= c.cols;
-    else if (du < -c.cols / 2.0) du += c.cols;
+    if (du > c.cols * 0.5) du -= c.cols;
+    else if (du < -c.cols * 0.5) du += c.cols;
     p.du = du; p.dv = v_obs - v;
     if (fabs(p.du) > 100.0 || fabs(p.dv) > 100.0) p.branch = 2;
 }
@@ -252,16 +266,18 @@ VIO_HD double obs_evaluate(const double* pose, const double* Pw, double u_obs, d
             r[1] = c.Lc[2] * p.du + c.Lc[3] * p.dv;
             if (WANT_JAC) {
                 const double xz_sq = p.x * p.x + p.z * p.z;
-                const double L_sq = p.L * p.L;
+                const double L_sq = p.L_sq;
                 if (xz_sq < 1e-10 || L_sq < 1e-10) zero_j = true;                // :466-476
                 else {
-                    const double xz_norm = sqrt(xz_sq);
+                    const double inv_xz = vio_rsqrt(xz_sq);
+                    const double xz_norm = xz_sq * inv_xz;
+                    const double inv_xz_sq = inv_xz * inv_xz, inv_L_sq = p.inv_L * p.inv_L;
+                    const double inv_den = inv_L_sq * inv_xz;                  // 1 / (L^2 * |xz|)
                     double Jp0[3], Jp1[3];
-                    Jp0[0] = -c.c2pi * p.z / xz_sq; Jp0[1] = 0.0; Jp0[2] = c.c2pi * p.x / xz_sq;
-                    const double den = L_sq * xz_norm;
-                    Jp1[0] = c.rpi * (p.x * p.y) / den;
-                    Jp1[1] = -c.rpi * xz_norm / L_sq;
-                    Jp1[2] = c.rpi * (p.y * p.z) / den;
+                    Jp0[0] = -c.c2pi * p.z * inv_xz_sq; Jp0[1] = 0.0; Jp0[2] = c.c2pi * p.x * inv_xz_sq;
+                    Jp1[0] = c.rpi * (p.x * p.y) * inv_den;
+                    Jp1[1] = -c.rpi * xz_norm * inv_L_sq;
+                    Jp1[2] = c.rpi * (p.y * p.z) * inv_den;
                     double Jw0[3], Jw1[3];
 #pragma unroll
                     for (int j = 0; j < 3; ++j) {
@@ -308,9 +324,9 @@ VIO_HD double obs_evaluate(const double* pose, const double* Pw, double u_obs, d
     if (!apply_loss || !(c.huber_a > 0.0)) return 0.5 * s;
     const double b = c.huber_a * c.huber_a;
     if (s > b) {
-        const double rt = sqrt(s);
+        const double rs = vio_rsqrt(s), rt = s * rs;
         const double rho0 = 2.0 * c.huber_a * rt - b;
-        const double rho1 = fmax(2.2250738585072014e-308, c.huber_a / rt);
+        const double rho1 = fmax(2.2250738585072014e-308, c.huber_a * rs);
         const double sc = sqrt(rho1);
         if (WANT_JAC && !zero_j) {
 #pragma unroll

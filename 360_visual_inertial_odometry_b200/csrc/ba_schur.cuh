@@ -45,11 +45,13 @@ constexpr int kSK = 3 * kSMaxLm;                   // 48 stage columns per batch
 constexpr int kSZPitch = 148;                      // doubles per stage column (>= kST, == 4 mod 16: conflict-free fragments)
 constexpr int kSRed = 9;                           // doubles per observation in the reduction scratch
 
-struct SchurChunk { int lm_begin, lm_end, pbase, span; };
+// batch0: first row of the slot table that belongs to this chunk (one row of kSProd observation
+// indices, -1 = empty, per batch of kSMaxLm landmarks; built on the host in ba.cu:build_chunks)
+struct SchurChunk { int lm_begin, lm_end, pbase, span, batch0, pad0, pad1, pad2; };
 
 constexpr size_t kSchurSmemBytes =
     sizeof(double) * (2 * (size_t)kSK * kSZPitch + (size_t)kSTiles * 64 + (size_t)kSWin * kPoseStride + (size_t)kSMaxLm * 9 + 32) +
-    sizeof(short) * (size_t)kSProd + sizeof(int) * 32;
+    sizeof(int) * 32;
 
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"

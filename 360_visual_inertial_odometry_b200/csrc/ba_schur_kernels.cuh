@@ -23,7 +23,7 @@ __device__ __forceinline__ void named_bar_arrive(int id, int count) {
 constexpr int kBarProd = 1, kBarFull = 2, kBarEmpty = 4;   // ids: producers-only, full[2], empty[2]
 
 __global__ void __launch_bounds__(kSThreads, 1)
-k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, bool apply_loss, double* __restrict__ partS,
+k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restrict__ slots, bool apply_loss, double* __restrict__ partS,
              double* __restrict__ partRhs, double* __restrict__ partCost) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* Zst = reinterpret_cast<double*>(smem_raw);          // [2][kSK][kSZPitch] operand stages, Z^T: column-major in k
@@ -31,9 +31,6 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, bool apply_loss, do
     double* sPose = St + kSTiles * 64;                          // [kSWin][kPoseStride]
     double* sLmk = sPose + kSWin * kPoseStride;                 // [kSMaxLm][9]: L^-1 (6), (E'E)^-1 g (3)
     double* sBlk = sLmk + kSMaxLm * 9;                          // [32] block-sum scratch
-    short* sOst = reinterpret_cast<short*>(sBlk + 32);          // [kSProd] observation (batch-relative) of slot (w, ls)
-    int* sLmp = reinterpret_cast<int*>(sOst + kSProd);          // [kSMaxLm + 1] lm_ptr of the batch
-
     const SchurChunk ch = chunks[blockIdx.x];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int i = tid; i < kSTiles * 64; i += kSThreads) St[i] = 0.0;
@@ -46,30 +43,24 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, bool apply_loss, do
     if (tid < kSProd) {
         // ================= producers: thread = (pose slot w, landmark slot ls) =================
         const int w = tid >> 4, ls = tid & 15;
+        const int* myslot = slots + (size_t)ch.batch0 * kSProd + tid;
+        int oi_next = nbatch > 0 ? __ldg(myslot) : -1;   // observation of slot (w, ls) in batch 0
         for (int b = 0; b < nbatch; ++b) {
             const int cur = ch.lm_begin + b * kSMaxLm;
             const int NB = min(kSMaxLm, ch.lm_end - cur);
             double* Zs = Zst + (b & 1) * kSK * kSZPitch;
             double* sRed = Zs;                                  // alias: [kSProd][kSRed]
+            const int oi = oi_next;
+            if (b + 1 < nbatch) oi_next = __ldg(myslot + (size_t)(b + 1) * kSProd);
             if (b >= 2) named_bar_sync(kBarEmpty + (b & 1), kSThreads);   // consumers are done with this stage
-            if (tid <= kSMaxLm) sLmp[tid] = d.lm_ptr[min(cur + tid, ch.lm_end)];
-            sOst[tid] = -1;
-            named_bar_sync(kBarProd, kSProd);
-            const int o0 = sLmp[0], nobs = sLmp[NB] - o0;       // <= kSProd: regular landmarks have <= kSWin observations
-            if (tid < nobs) {
-                const int i = o0 + tid;
-                sOst[(d.pose[i] - ch.pbase) * kSMaxLm + (d.point[i] - cur)] = (short)tid;
-            }
-            named_bar_sync(kBarProd, kSProd);
             // ---- phase A
-            const int oi = sOst[tid];
             double r[2] = {0.0, 0.0}, F[12], E[6];
 #pragma unroll
             for (int j = 0; j < 12; ++j) F[j] = 0.0;
 #pragma unroll
             for (int j = 0; j < 6; ++j) E[j] = 0.0;
             if (oi >= 0) {
-                const int i = o0 + oi;
+                const int i = oi;
                 const int p = ch.pbase + w, l = cur + ls;
                 const double Pw[3] = {__ldg(d.points + 3 * (size_t)l), __ldg(d.points + 3 * (size_t)l + 1),
                                       __ldg(d.points + 3 * (size_t)l + 2)};
@@ -86,52 +77,57 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, bool apply_loss, do
                 q[6] = E[0] * r[0] + E[3] * r[1]; q[7] = E[1] * r[0] + E[4] * r[1]; q[8] = E[2] * r[0] + E[5] * r[1];
             }
             named_bar_sync(kBarProd, kSProd);
-            // ---- phase B: per-landmark sums over the pose slots, Cholesky, L^-1, (E'E)^-1 g
-            if (tid < kSMaxLm * 9) {
-                const int bl = tid / 9, e = tid - bl * 9;
-                double s = 0.0;
-#pragma unroll 4
-                for (int pw = 0; pw < kSWin; ++pw) s += sRed[(pw * kSMaxLm + bl) * kSRed + e];
-                sLmk[tid] = s;
-            }
-            named_bar_sync(kBarProd, kSProd);
-            if (tid < kSMaxLm) {
-                double* q = sLmk + tid * 9;
-                double li[6] = {0, 0, 0, 0, 0, 0}, ig[3] = {0, 0, 0};
-                if (tid < NB && d.point_fixed[cur + tid] == 0) {
-                    const int l = cur + tid;
-                    double h[6] = {q[0], q[1], q[2], q[3], q[4], q[5]};
-                    const double g0 = q[6], g1 = q[7], g2 = q[8];
-                    if (d.D) {
-                        const double* Dl = d.D + 6 * (size_t)d.K + 3 * (size_t)l;
-                        h[0] += Dl[0] * Dl[0]; h[3] += Dl[1] * Dl[1]; h[5] += Dl[2] * Dl[2];
-                    }
-                    const double l00 = sqrt(h[0]);
-                    const double l10 = h[1] / l00, l20 = h[2] / l00;
-                    const double l11 = sqrt(h[3] - l10 * l10);
-                    const double l21 = (h[4] - l20 * l10) / l11;
-                    const double l22 = sqrt(h[5] - l20 * l20 - l21 * l21);
-                    const double i00 = 1.0 / l00, i11 = 1.0 / l11, i22 = 1.0 / l22;
-                    const double i10 = -l10 * i00 * i11;
-                    const double i21 = -l21 * i11 * i22;
-                    const double i20 = -(l20 * i00 + l21 * i10) * i22;
-                    li[0] = i00; li[1] = i10; li[2] = i11; li[3] = i20; li[4] = i21; li[5] = i22;
-                    bool ok = true;
+            // ---- phase B: per-landmark sums over the pose slots, Cholesky, L^-1, (E'E)^-1 g.
+            // thread (bl, e) = tid>>4, tid&15 sums entry e < 9 of landmark bl; the nine sums of a
+            // landmark sit in one half warp and are gathered by shuffles, lane e == 0 factorises.
+            if (tid < kSMaxLm * 16) {   // 8 whole warps
+                const int bl = tid >> 4, e = tid & 15;
+                double sum = 0.0;
+                if (e < 9) {
 #pragma unroll
-                    for (int j = 0; j < 6; ++j) ok = ok && isfinite(li[j]);
-                    if (!ok) {   // rank-deficient landmark: not eliminated (as the general kernel)
-#pragma unroll
-                        for (int j = 0; j < 6; ++j) li[j] = 0.0;
-                    }
-                    // (E'E)^-1 g = L^-T (L^-1 g)
-                    const double y0 = li[0] * g0, y1 = li[1] * g0 + li[2] * g1, y2 = li[3] * g0 + li[4] * g1 + li[5] * g2;
-                    ig[0] = li[0] * y0 + li[1] * y1 + li[3] * y2;
-                    ig[1] = li[2] * y1 + li[4] * y2;
-                    ig[2] = li[5] * y2;
+                    for (int pw = 0; pw < kSWin; ++pw) sum += sRed[(pw * kSMaxLm + bl) * kSRed + e];
                 }
+                const int base = lane & 16;
+                double hq[9];
 #pragma unroll
-                for (int j = 0; j < 6; ++j) q[j] = li[j];
-                q[6] = ig[0]; q[7] = ig[1]; q[8] = ig[2];
+                for (int j = 0; j < 9; ++j) hq[j] = __shfl_sync(0xffffffffu, sum, base + j);
+                if (e == 0) {
+                    double* q = sLmk + bl * 9;
+                    double li[6] = {0, 0, 0, 0, 0, 0}, ig[3] = {0, 0, 0};
+                    if (bl < NB && d.point_fixed[cur + bl] == 0) {
+                        const int l = cur + bl;
+                        if (d.D) {
+                            const double* Dl = d.D + 6 * (size_t)d.K + 3 * (size_t)l;
+                            hq[0] += Dl[0] * Dl[0]; hq[3] += Dl[1] * Dl[1]; hq[5] += Dl[2] * Dl[2];
+                        }
+                        // E'E = L L': only L^-1 is needed (reciprocal square roots, no divisions)
+                        const double i00 = vio_rsqrt(hq[0]);
+                        const double l10 = hq[1] * i00, l20 = hq[2] * i00;
+                        const double i11 = vio_rsqrt(hq[3] - l10 * l10);
+                        const double l21 = (hq[4] - l20 * l10) * i11;
+                        const double i22 = vio_rsqrt(hq[5] - l20 * l20 - l21 * l21);
+                        const double i10 = -l10 * i00 * i11;
+                        const double i21 = -l21 * i11 * i22;
+                        const double i20 = -(l20 * i00 + l21 * i10) * i22;
+                        li[0] = i00; li[1] = i10; li[2] = i11; li[3] = i20; li[4] = i21; li[5] = i22;
+                        bool ok = true;
+#pragma unroll
+                        for (int j = 0; j < 6; ++j) ok = ok && isfinite(li[j]);
+                        if (!ok) {   // rank-deficient landmark: not eliminated (as the general kernel)
+#pragma unroll
+                            for (int j = 0; j < 6; ++j) li[j] = 0.0;
+                        }
+                        // (E'E)^-1 g = L^-T (L^-1 g)
+                        const double g0 = hq[6], g1 = hq[7], g2 = hq[8];
+                        const double y0 = li[0] * g0, y1 = li[1] * g0 + li[2] * g1, y2 = li[3] * g0 + li[4] * g1 + li[5] * g2;
+                        ig[0] = li[0] * y0 + li[1] * y1 + li[3] * y2;
+                        ig[1] = li[2] * y1 + li[4] * y2;
+                        ig[2] = li[5] * y2;
+                    }
+#pragma unroll
+                    for (int j = 0; j < 6; ++j) q[j] = li[j];
+                    q[6] = ig[0]; q[7] = ig[1]; q[8] = ig[2];
+                }
             }
             named_bar_sync(kBarProd, kSProd);
             // ---- phase C
@@ -279,37 +275,63 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, bool apply_loss, do
     }
 }
 
-// Sums the chunk slabs into the upper block triangle of S (and rhs) in a fixed order.
-// cov_ptr / cov_idx: for every pose, the chunks whose window contains it.
-__global__ void __launch_bounds__(256)
-k_schur_reduce(double* __restrict__ S, int n, double* __restrict__ rhs, const double* __restrict__ partS,
-               const double* __restrict__ partRhs, const SchurChunk* __restrict__ chunks,
-               const int* __restrict__ cov_ptr, const int* __restrict__ cov_idx, const int* __restrict__ free_pose) {
-    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx < (long long)n * n) {
-        const int ri = (int)(idx / n), rj = (int)(idx - (long long)ri * n);
-        const int bi = ri / 6, bj = rj / 6;
-        if (bi < bj || (bi == bj && ri <= rj)) {
-            const int pi = free_pose[bi], pj = free_pose[bj];
-            const int a = ri - 6 * bi, b = rj - 6 * bj;
-            double s = 0.0;
-            for (int q = cov_ptr[pi]; q < cov_ptr[pi + 1]; ++q) {
-                const int c = cov_idx[q];
-                const SchurChunk ch = chunks[c];
-                if (pj >= ch.pbase && pj < ch.pbase + ch.span)
-                    s += partS[(size_t)c * kST * kST + (size_t)(6 * (pi - ch.pbase) + a) * kST + 6 * (pj - ch.pbase) + b];
-            }
-            S[idx] = s;
-        }
-    } else if (idx < (long long)n * n + n) {
-        const int ri = (int)(idx - (long long)n * n);
-        const int bi = ri / 6, pi = free_pose[bi], a = ri - 6 * bi;
-        double s = 0.0;
-        for (int q = cov_ptr[pi]; q < cov_ptr[pi + 1]; ++q) {
+// Sums the chunk slabs into S (and rhs, cost) in a fixed order: one CTA per pair of free poses
+// (bi <= bj), thread = (entry of the 6x6 block, one of kRedLanes strided walkers of the list of
+// chunks covering pose bi); the walkers' partial sums are combined in a fixed order.
+// cov_ptr / cov_idx: for every pose, the chunks whose window contains it; reach[p] = last pose
+// that shares a chunk with p.  FULL: also write the mirrored block, add the pose part of the LM
+// diagonal (levenberg_marquardt_strategy.cc:78-89) and sum the chunk costs, so that no further
+// pass over S is needed; !FULL: upper block triangle only (k_schur_warp then adds the landmarks
+// that fit no window and k_finish_S mirrors).
+constexpr int kRedLanes = 7;
+template <bool FULL>
+__global__ void __launch_bounds__(36 * kRedLanes)
+k_schur_reduce(double* __restrict__ S, int n, double* __restrict__ rhs, double* __restrict__ cost_out,
+               const double* __restrict__ partS, const double* __restrict__ partRhs, const double* __restrict__ partCost,
+               int nchunks, const SchurChunk* __restrict__ chunks, const int* __restrict__ cov_ptr,
+               const int* __restrict__ cov_idx, const int* __restrict__ reach, const int* __restrict__ free_pose,
+               const double* __restrict__ D, bool add_diag) {
+    const int bj = blockIdx.x, bi = blockIdx.y;
+    if (bi > bj) return;
+    __shared__ double part[kRedLanes][36];
+    const int t = threadIdx.x, e = t % 36, g = t / 36;
+    const int a = e / 6, b = e - 6 * a;
+    const int pi = free_pose[bi], pj = free_pose[bj];
+    const int q0 = cov_ptr[pi], q1 = cov_ptr[pi + 1];
+    double s = 0.0;
+    if (pj <= reach[pi] && (bi < bj || a <= b)) {
+        for (int q = q0 + g; q < q1; q += kRedLanes) {
             const int c = cov_idx[q];
-            s += partRhs[(size_t)c * kST + 6 * (pi - chunks[c].pbase) + a];
+            const int pbase = chunks[c].pbase, span = chunks[c].span;
+            if (pj < pbase + span)   // pj >= pi >= pbase
+                s += partS[(size_t)c * kST * kST + (size_t)(6 * (pi - pbase) + a) * kST + 6 * (pj - pbase) + b];
         }
-        rhs[ri] = s;
+    }
+    part[g][e] = s;
+    __syncthreads();
+    if (t < 36 && (bi < bj || a <= b)) {
+        double tot = part[0][e];
+#pragma unroll
+        for (int k = 1; k < kRedLanes; ++k) tot += part[k][e];
+        if (FULL && bi == bj && a == b && add_diag && D) { const double dd = D[6 * (size_t)pi + a]; tot += dd * dd; }
+        const size_t ri = 6 * (size_t)bi + a, rj = 6 * (size_t)bj + b;
+        S[ri * n + rj] = tot;
+        if (FULL && ri != rj) S[rj * n + ri] = tot;
+    }
+    if (bi == bj && t >= 36 && t < 42) {   // rhs of this pose
+        const int ar = t - 36;
+        double tot = 0.0;
+        for (int q = q0; q < q1; ++q) {
+            const int c = cov_idx[q];
+            tot += partRhs[(size_t)c * kST + 6 * (pi - chunks[c].pbase) + ar];
+        }
+        rhs[6 * bi + ar] = tot;
+    }
+    if (FULL && bi == 0 && bj == 0 && t >= 64 && t < 96) {   // cost: fixed-order sum of the chunk partials
+        double tot = 0.0;
+        for (int i = t - 64; i < nchunks; i += 32) tot += partCost[i];
+        tot = warp_sum(tot);
+        if (t == 64) *cost_out = tot;
     }
 }
 

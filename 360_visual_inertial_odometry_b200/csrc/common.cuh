@@ -29,6 +29,7 @@ struct vio360_ctx {
     size_t pinned_bytes = 0;
     // optional per-kernel CUDA-event timing (bench.py's roofline numbers)
     bool timing = false;
+    bool debug_sync = false;     // VIO360_DEBUG_SYNC=1: synchronise after every launch so a fault names its kernel
     struct TimedLaunch { const char* name; cudaEvent_t e0, e1; };
     std::vector<TimedLaunch> timed;
     std::vector<cudaEvent_t> event_pool;
@@ -70,6 +71,7 @@ inline int vio360_fail(vio360_ctx* ctx, int code, const char* fmt, ...) {
     do {                                                                                 \
         (ctx)->launches++;                                                               \
         cudaError_t e_ = cudaGetLastError();                                             \
+        if (e_ == cudaSuccess && (ctx)->debug_sync) e_ = cudaStreamSynchronize((ctx)->stream); \
         if (e_ != cudaSuccess)                                                           \
             return vio360_fail((ctx), VIO360_ERR_CUDA, "%s:%d kernel launch -> %s", __FILE__, \
                                __LINE__, cudaGetErrorString(e_));                        \

@@ -1,4 +1,6 @@
 // ctx.cu -- context lifetime, stream, launch accounting and the FMA-peak probe.
+#include <cstdlib>
+
 #include "common.cuh"
 
 static std::string g_create_error;
@@ -35,6 +37,7 @@ extern "C" int vio360_create(int device, vio360_ctx** out) {
         return VIO360_ERR_CUDA;
     }
     ctx->num_sms = ctx->prop.multiProcessorCount;
+    { const char* e = getenv("VIO360_DEBUG_SYNC"); ctx->debug_sync = e && e[0] == '1'; }
     *out = ctx;
     return VIO360_OK;
 }

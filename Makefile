@@ -3,7 +3,7 @@ NVCC ?= /usr/local/cuda/bin/nvcc
 PKG := 360_visual_inertial_odometry_b200
 CSRC := $(PKG)/csrc
 ARCH := -gencode arch=compute_100a,code=sm_100a
-NVFLAGS := $(ARCH) -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -Xcompiler -Wall -Xptxas -v
+NVFLAGS := $(ARCH) -O3 -lineinfo -std=c++17 -Xcompiler -fPIC -Xcompiler -Wall -Xptxas -v $(EXTRA_NVFLAGS)
 LIB := $(PKG)/libvio360_cuda.so
 OBJS := $(CSRC)/ctx.o $(CSRC)/ba.o $(CSRC)/fe.o
 
