@@ -119,7 +119,7 @@ extern "C" int vio360_fe_configure(vio360_ctx* ctx, int width, int height, int m
     VIO_CUDA(ctx, s->d_status.reserve(np)); VIO_CUDA(ctx, s->d_err.reserve(np * 4)); VIO_CUDA(ctx, s->d_keep.reserve(np));
     VIO_CUDA(ctx, s->h_pts_in.reserve(np * 8));
     VIO_CUDA(ctx, s->h_out.reserve(np * (8 + 1 + 4 + 1)));
-    if (const char* e = getenv("VIO360_LK_MB")) s->lk_mb = atoi(e) == 3 ? 3 : 2;
+    if (const char* e = getenv("VIO360_LK_MB")) s->lk_mb = atoi(e);
     s->configured = true;
     return VIO360_OK;
 }
@@ -300,10 +300,10 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
     VIO_CUDA(ctx, cudaMemcpyAsync(dj, hj, sizeof(TrackJobDev) * (size_t)n_jobs, cudaMemcpyHostToDevice, st));
     if (mem_space == VIO360_MEM_HOST)
         VIO_CUDA(ctx, cudaMemcpyAsync(s->d_pts_in.p, s->h_pts_in.p, off * 8, cudaMemcpyHostToDevice, st));
-    dim3 grid((max_n + kLkWarps - 1) / kLkWarps, n_jobs);
     { KernelTimer kt_(ctx, "k_lk_track");
-    if (s->lk_mb == 3) k_lk_track<3><<<grid, kLkWarps * 32, 0, st>>>(dj, lk_params(s));
-    else k_lk_track<2><<<grid, kLkWarps * 32, 0, st>>>(dj, lk_params(s));
+    if (s->lk_mb == 3) k_lk_track<7, 96><<<dim3((max_n + 6) / 7, n_jobs), 7 * 32, 0, st>>>(dj, lk_params(s));
+    else if (s->lk_mb == 4) k_lk_track<6, 80><<<dim3((max_n + 5) / 6, n_jobs), 6 * 32, 0, st>>>(dj, lk_params(s));
+    else k_lk_track<8, 128><<<dim3((max_n + 7) / 8, n_jobs), 8 * 32, 0, st>>>(dj, lk_params(s));
     }
     VIO_LAUNCH_CHECK(ctx);
     if ((rc = end_stage(ctx))) return rc;

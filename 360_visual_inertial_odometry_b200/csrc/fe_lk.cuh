@@ -56,7 +56,6 @@ constexpr int kRpl = 4;                           // runs per lane
 constexpr int kTRows = 24, kTWords = 8;           // template tile: 24 rows x 32 bytes
 constexpr int kDRows = 22, kDWords = 28;          // derivative grid: 22 (+2 zero) rows x 28 packed (ix | iy << 16)
 constexpr int kJRows = 32, kJWords = 9;           // search tile: 32 rows x 36 bytes
-constexpr int kLkWarps = 8;
 
 // exact 64-bit warp sum of 32-bit lane partials from two hardware integer reductions
 __device__ __forceinline__ long long warp_sum_i32(int v) {
@@ -97,6 +96,22 @@ __device__ __forceinline__ uint32_t tile_word_fast(const uint8_t* __restrict__ i
     const int r = it / WORDS, c = it - r * WORDS;
     return __ldg(reinterpret_cast<const uint32_t*>(img + (size_t)(y0 + r) * pitch + x0) + c);
 }
+// Asynchronous (LDGSTS) fill of an interior tile: no registers are held while the loads fly.
+template <int ROWS, int WORDS>
+__device__ __forceinline__ void tile_fill_async(uint32_t* s, const uint8_t* __restrict__ img, int pitch, int x0, int y0, int lane) {
+#pragma unroll
+    for (int i = 0; i < (ROWS * WORDS) / 32; ++i) {
+        const int it = lane + 32 * i, r = it / WORDS, c = it - r * WORDS;
+        const uint32_t dst = (uint32_t)__cvta_generic_to_shared(s + it);
+        const uint8_t* src = img + (size_t)(y0 + r) * pitch + x0 + 4 * c;
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
 __device__ __noinline__ void tile_fill_border(uint32_t* s, const uint8_t* __restrict__ img, int pitch, int w, int h,
                                               int x0, int y0, int words, int total, int lane) {
 #pragma unroll 1
@@ -131,9 +146,10 @@ __device__ __forceinline__ void run_sample(const uint32_t* __restrict__ top, con
     v[3] = dp2a_hi_su(wt, tb, dp2a_hi_su(wb, bb, 256)) >> 9;
 }
 
-// MB = resident CTAs per SM the register allocator targets (2 -> 128 registers, 3 -> 80)
-template <int MB>
-__global__ void __launch_bounds__(kLkWarps * 32, MB) k_lk_track(const TrackJobDev* __restrict__ jobs, LkParams P) {
+// kLkWarps features per CTA; REGS = register cap (8 warps x 128 regs -> 16 warps / SM,
+// 7 x 96 -> 21, 6 x 80 -> 24)
+template <int kLkWarps, int REGS>
+__global__ void __launch_bounds__(kLkWarps * 32) __maxnreg__(REGS) k_lk_track(const TrackJobDev* __restrict__ jobs, LkParams P) {
     __shared__ __align__(16) uint32_t sT_all[kLkWarps][kTRows * kTWords];
     __shared__ __align__(16) uint32_t sD_all[kLkWarps][(kDRows + 2) * kDWords];
     __shared__ __align__(16) uint32_t sJ_all[kLkWarps][kJRows * kJWords];
@@ -169,6 +185,7 @@ __global__ void __launch_bounds__(kLkWarps * 32, MB) k_lk_track(const TrackJobDe
     float outx = 0.f, outy = 0.f;   // nextPts[ptidx]
     int status = 1;
     float errv = 0.f;
+    bool pfT = false;   // the next level's template tile is already in flight into sT
 
     for (int level = P.nlevels - 1; level >= 0; --level) {
         const int w = P.w[level], h = P.h[level];
@@ -195,36 +212,26 @@ __global__ void __launch_bounds__(kLkWarps * 32, MB) k_lk_track(const TrackJobDe
         int tx0 = 0, ty0 = 0;
         bool tile_ok = false;
         {
-            const bool intT = tile_interior<kTRows, kTWords>(imgI, pitchI, w, h, xT0, yT0);
+            // template tile: prefetched during the previous level's iterations when interior
+            const bool haveT = pfT;
+            pfT = false;
             const int inx = (int)floorf(nx), iny = (int)floorf(ny);
             const bool jin = !(inx < -kWin || inx >= w || iny < -kWin || iny >= h);
-            bool intJ = false;
+            __syncwarp();   // every lane is done with the previous level's tiles
+            if (!haveT) {
+                if (tile_interior<kTRows, kTWords>(imgI, pitchI, w, h, xT0, yT0)) tile_fill_async<kTRows, kTWords>(sT, imgI, pitchI, xT0, yT0, lane);
+                else tile_fill_border(sT, imgI, pitchI, w, h, xT0, yT0, kTWords, kTRows * kTWords, lane);
+            }
+            // search tile: issued now, needed only after the Scharr / template phase
+            bool jAsync = false;
             if (jin) {
                 tx0 = (inx - 4) & ~3; ty0 = iny - 5;
-                intJ = tile_interior<kJRows, kJWords>(imgJ, pitchJ, w, h, tx0, ty0);
+                jAsync = tile_interior<kJRows, kJWords>(imgJ, pitchJ, w, h, tx0, ty0);
+                if (jAsync) tile_fill_async<kJRows, kJWords>(sJ, imgJ, pitchJ, tx0, ty0, lane);
+                else tile_fill_border(sJ, imgJ, pitchJ, w, h, tx0, ty0, kJWords, kJRows * kJWords, lane);
             }
-            uint32_t tw[6], jw[9];
-            if (intT) {
-#pragma unroll
-                for (int i = 0; i < 6; ++i) tw[i] = tile_word_fast<kTWords>(imgI, pitchI, xT0, yT0, lane + 32 * i);
-            }
-            if (intJ) {
-#pragma unroll
-                for (int i = 0; i < 9; ++i) jw[i] = tile_word_fast<kJWords>(imgJ, pitchJ, tx0, ty0, lane + 32 * i);
-            }
-            __syncwarp();
-            if (intT) {
-#pragma unroll
-                for (int i = 0; i < 6; ++i) sT[lane + 32 * i] = tw[i];
-            } else {
-                tile_fill_border(sT, imgI, pitchI, w, h, xT0, yT0, kTWords, kTRows * kTWords, lane);
-            }
-            if (intJ) {
-#pragma unroll
-                for (int i = 0; i < 9; ++i) sJ[lane + 32 * i] = jw[i];
-            } else if (jin) {
-                tile_fill_border(sJ, imgJ, pitchJ, w, h, tx0, ty0, kJWords, kJRows * kJWords, lane);
-            }
+            if (jAsync) cp_async_wait<1>();   // everything but the search tile (committed last) has landed
+            else cp_async_wait<0>();
             tile_ok = jin;
             __syncwarp();
         }
@@ -324,6 +331,22 @@ __global__ void __launch_bounds__(kLkWarps * 32, MB) k_lk_track(const TrackJobDe
         const float A11 = (float)warp_sum_i32(sA11) * FLT_SCALE;
         const float A12 = (float)warp_sum_i32(sA12) * FLT_SCALE;
         const float A22 = (float)warp_sum_i32(sA22) * FLT_SCALE;
+        // The template tile is dead from here on (the error epilogue re-reads it at level 0 only):
+        // start the next level's template tile, whose position is known, behind the iterations.
+        if (level > 0) {
+            const int ln = level - 1, wn = P.w[ln], hn = P.h[ln];
+            const float scn = (float)(1. / (1 << ln));
+            const int ipxn = (int)floorf(px0 * scn - half), ipyn = (int)floorf(py0 * scn - half);
+            if (!(ipxn < -kWin || ipxn >= wn || ipyn < -kWin || ipyn >= hn)) {
+                const int xTn = (ipxn - 1) & ~3, yTn = ipyn - 1;
+                if (tile_interior<kTRows, kTWords>(job.prev.p[ln], job.prev.pitch[ln], wn, hn, xTn, yTn)) {
+                    tile_fill_async<kTRows, kTWords>(sT, job.prev.p[ln], job.prev.pitch[ln], xTn, yTn, lane);
+                    pfT = true;
+                }
+            }
+        }
+        if (pfT) cp_async_wait<1>(); else cp_async_wait<0>();   // the search tile of this level has landed
+        __syncwarp();
         float D = A11 * A22 - A12 * A12;
         const float tt = A11 - A22;
         const float minEig = (A22 + A11 - sqrtf(tt * tt + 4.f * A12 * A12)) / (float)(2 * kWin * kWin);
