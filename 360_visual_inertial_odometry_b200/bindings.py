@@ -223,6 +223,25 @@ class Context:
                                              min_dist, _ptr(out), C.byref(n)))
         return out[:n.value].copy()
 
+    def fe_detect_batch(self, imgs, masks=None, max_corners=1000, quality=float(np.float32(0.01)),
+                        min_dist=float(np.float32(30.0)), out_cap=None):
+        """One vio360_fe_detect_batch call over independent images (host memory); list of (n, 2) arrays."""
+        nb = len(imgs)
+        imgs = [np.ascontiguousarray(i, np.uint8) for i in imgs]
+        masks = [None if m is None else np.ascontiguousarray(m, np.uint8) for m in (masks or [None] * nb)]
+        cap = max_corners if max_corners > 0 else (out_cap or imgs[0].size)
+        outs = [np.zeros((cap, 2), np.float32) for _ in range(nb)]
+        ns = np.zeros(nb, np.int32)
+        jobs = (DetectJob * nb)()
+        for b in range(nb):
+            j = jobs[b]
+            j.img, j.pitch, j.key = imgs[b].ctypes.data, imgs[b].strides[0], 0
+            j.mask = masks[b].ctypes.data if masks[b] is not None else None
+            j.mask_pitch = masks[b].strides[0] if masks[b] is not None else 0
+            j.out_xy, j.out_n = outs[b].ctypes.data, ns.ctypes.data + 4 * b
+        self.check(self.lib.vio360_fe_detect_batch(self.h, jobs, nb, max_corners, quality, min_dist, MEM_HOST))
+        return [outs[b][:ns[b]].copy() for b in range(nb)]
+
     def fe_detect_batch_raw(self, jobs, n_jobs, max_corners, quality, min_dist, mem_space):
         self.check(self.lib.vio360_fe_detect_batch(self.h, jobs, n_jobs, max_corners, quality, min_dist, mem_space))
 

@@ -46,7 +46,9 @@ struct vio360_fe_state {
     // detection pools
     DevBuf d_djobs, d_eig, d_mask, d_small, d_cand, d_cand_sorted, d_grid, d_cub, d_corners;
     PinBuf h_djobs, h_dout;
-    int det_batch_cap = 0, max_cand = 1 << 18;
+    int det_batch_cap = 0, max_cand = 1 << 17;   // initial candidate capacity per image (grown on demand)
+    size_t cand_cap = 0;
+    bool select_attr_set = false;
     int lk_mb = 2;               // occupancy variant of k_lk_track (tuning knob: VIO360_LK_MB)
     size_t cub_bytes = 0;
 };
@@ -120,6 +122,7 @@ extern "C" int vio360_fe_configure(vio360_ctx* ctx, int width, int height, int m
     VIO_CUDA(ctx, s->h_pts_in.reserve(np * 8));
     VIO_CUDA(ctx, s->h_out.reserve(np * (8 + 1 + 4 + 1)));
     if (const char* e = getenv("VIO360_LK_MB")) s->lk_mb = atoi(e);
+    if (const char* e = getenv("VIO360_DET_CAND")) s->max_cand = std::max(1, atoi(e));   // initial candidate capacity per image
     s->configured = true;
     return VIO360_OK;
 }
@@ -370,25 +373,34 @@ extern "C" int vio360_fe_pyramid(vio360_ctx* ctx, const uint8_t* img, size_t pit
 }
 
 // ---- detection -----------------------------------------------------------------------
+static int reserve_candidates(vio360_ctx* ctx, size_t cap) {
+    vio360_fe_state* s = ctx->fe;
+    if (cap <= s->cand_cap) return VIO360_OK;
+    VIO_CUDA(ctx, s->d_cand.reserve(cap * 8));
+    VIO_CUDA(ctx, s->d_cand_sorted.reserve(cap * 8));
+    size_t tb = 0;
+    cub::DeviceRadixSort::SortKeysDescending(nullptr, tb, (const unsigned long long*)nullptr, (unsigned long long*)nullptr, (int)cap);
+    s->cub_bytes = tb;
+    VIO_CUDA(ctx, s->d_cub.reserve(tb));
+    s->cand_cap = cap;
+    return VIO360_OK;
+}
+
 static int ensure_detect_pools(vio360_ctx* ctx, int n_jobs, int max_corners) {
     vio360_fe_state* s = ctx->fe;
     const size_t WH = (size_t)s->W * s->H;
     if (n_jobs > s->det_batch_cap) {
         VIO_CUDA(ctx, s->d_eig.reserve(WH * 4 * n_jobs));
-        VIO_CUDA(ctx, s->d_cand.reserve((size_t)s->max_cand * 8 * n_jobs));
-        VIO_CUDA(ctx, s->d_cand_sorted.reserve((size_t)s->max_cand * 8 * n_jobs));
-        VIO_CUDA(ctx, s->d_small.reserve(16 * (size_t)n_jobs));
+        VIO_CUDA(ctx, s->d_small.reserve(16 * (size_t)(n_jobs + 1)));
         VIO_CUDA(ctx, s->d_djobs.reserve(sizeof(DetectJobDev) * (size_t)n_jobs));
         VIO_CUDA(ctx, s->h_djobs.reserve(sizeof(DetectJobDev) * (size_t)n_jobs));
-        size_t tb = 0;
-        cub::DeviceRadixSort::SortKeysDescending(nullptr, tb, (const unsigned long long*)nullptr, (unsigned long long*)nullptr, s->max_cand);
-        s->cub_bytes = tb;
-        VIO_CUDA(ctx, s->d_cub.reserve(tb));
         s->det_batch_cap = n_jobs;
     }
-    const size_t cap = (size_t)(max_corners > 0 ? max_corners : s->max_cand);
+    int rc = reserve_candidates(ctx, (size_t)s->max_cand * n_jobs);
+    if (rc) return rc;
+    const size_t cap = (size_t)(max_corners > 0 ? max_corners : 0);
     VIO_CUDA(ctx, s->d_corners.reserve(cap * 8 * n_jobs));
-    VIO_CUDA(ctx, s->h_dout.reserve(cap * 8 * n_jobs + 16 * (size_t)n_jobs));
+    VIO_CUDA(ctx, s->h_dout.reserve(cap * 8 * n_jobs + 16 * (size_t)(n_jobs + 1)));
     return VIO360_OK;
 }
 
@@ -397,8 +409,19 @@ static DetectParams detect_params(const vio360_fe_state* s) {
     P.W = s->W; P.H = s->H;
     P.top_rows = (int)(s->H * s->polar_ratio);                    // Camera.cpp:104
     P.bottom_start = (int)(s->H * (1.0f - s->polar_ratio));       // Camera.cpp:105
-    P.margin = s->margin; P.max_cand = s->max_cand;
+    P.margin = s->margin;
+    P.idx_bits = 1;
+    while (((size_t)1 << P.idx_bits) < (size_t)s->W * s->H) ++P.idx_bits;
+    P.max_cand = (unsigned int)s->cand_cap;
     return P;
+}
+
+static void launch_min_eig(vio360_ctx* ctx, const DetectJobDev* dj, const DetectParams& P, int n_jobs, bool any_mask) {
+    const int nwx = (P.W + kEigWarpCols - 1) / kEigWarpCols;
+    const dim3 grid((nwx + kEigWarps - 1) / kEigWarps, n_jobs);
+    KernelTimer kt_(ctx, "k_min_eig");
+    if (any_mask) k_min_eig<true><<<grid, kEigWarps * 32, 0, ctx->stream>>>(dj, P, nwx);
+    else k_min_eig<false><<<grid, kEigWarps * 32, 0, ctx->stream>>>(dj, P, nwx);
 }
 
 extern "C" int vio360_fe_detect_batch(vio360_ctx* ctx, const vio360_detect_job* jobs, int n_jobs, int max_corners,
@@ -408,20 +431,27 @@ extern "C" int vio360_fe_detect_batch(vio360_ctx* ctx, const vio360_detect_job* 
     if (!s || !s->configured) return vio360_fail(ctx, VIO360_ERR_STATE, "fe_detect before fe_configure");
     if (!jobs || n_jobs < 0 || n_jobs > s->max_batch) return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_detect_batch: bad job count");
     if (n_jobs == 0) return VIO360_OK;
-    if (max_corners > s->max_cand) return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_detect_batch: max_corners too large");
+    const size_t WH = (size_t)s->W * s->H;
+    if (s->W < 3 || s->H < 3 || s->W > 65535 || s->H > 65535) return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_detect_batch: image size out of range");
+    if (max_corners > 0 && (size_t)max_corners > WH) max_corners = (int)WH;
     VIO_CUDA(ctx, cudaSetDevice(ctx->device));
     VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     int rc = ensure_detect_pools(ctx, n_jobs, max_corners);
     if (rc) return rc;
+    DetectParams P = detect_params(s);
+    if (32 + P.idx_bits > 63 || ((unsigned long long)(n_jobs - 1) >> (64 - 32 - P.idx_bits)) != 0)
+        return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_detect_batch: batch of %d images of %zu pixels does not fit the 64-bit sort key", n_jobs, WH);
     cudaStream_t st = ctx->stream;
-    const size_t WH = (size_t)s->W * s->H;
-    const size_t cap = (size_t)(max_corners > 0 ? max_corners : s->max_cand);
+    const size_t cap = (size_t)(max_corners > 0 ? max_corners : 0);
     const int cell = min_dist >= 1.0 ? (int)lrint(min_dist) : 1;
     const int gw = (s->W + cell - 1) / cell, gh = (s->H + cell - 1) / cell;
-    const size_t grid_ints = min_dist >= 1.0 ? (size_t)gw * gh * (1 + kCellCap) : 1;
-    VIO_CUDA(ctx, s->d_grid.reserve(grid_ints * 4 * n_jobs));
-    VIO_CUDA(ctx, cudaMemsetAsync(s->d_grid.p, 0, grid_ints * 4 * n_jobs, st));
-    VIO_CUDA(ctx, cudaMemsetAsync(s->d_small.p, 0, 16 * (size_t)n_jobs, st));
+    const size_t grid_bytes = min_dist >= 1.0 ? (size_t)gw * gh * sizeof(uint4) : 0;
+    const bool smem_grid = grid_bytes <= (size_t)200 * 1024;
+    if (!smem_grid) {
+        VIO_CUDA(ctx, s->d_grid.reserve(grid_bytes * n_jobs));
+        VIO_CUDA(ctx, cudaMemsetAsync(s->d_grid.p, 0, grid_bytes * n_jobs, st));
+    }
+    VIO_CUDA(ctx, cudaMemsetAsync(s->d_small.p, 0, 16 * (size_t)(n_jobs + 1), st));
     s->batch_tag++;
     bool any_mask = false;
     for (int b = 0; b < n_jobs; ++b) any_mask = any_mask || jobs[b].mask;
@@ -447,52 +477,79 @@ extern "C" int vio360_fe_detect_batch(vio360_ctx* ctx, const vio360_detect_job* 
         d.eig = s->d_eig.as<float>() + WH * b;
         unsigned int* small = s->d_small.as<unsigned int>() + 4 * b;
         d.max_bits = small; d.n_cand = small + 1; d.out_n = (int*)(small + 2);
-        d.cand = s->d_cand.as<unsigned long long>() + (size_t)s->max_cand * b;
-        d.grid = s->d_grid.as<int>() + grid_ints * b;
-        d.out_xy = mem_space == VIO360_MEM_DEVICE ? j.out_xy : s->d_corners.as<float>() + cap * 2 * b;
+        d.grid = smem_grid ? nullptr : (uint4*)(s->d_grid.as<uint8_t>() + grid_bytes * b);
+        d.out_xy = mem_space == VIO360_MEM_DEVICE ? j.out_xy : (max_corners > 0 ? s->d_corners.as<float>() + cap * 2 * b : nullptr);
     }
     VIO_CUDA(ctx, cudaMemcpyAsync(s->d_djobs.p, hj, sizeof(DetectJobDev) * (size_t)n_jobs, cudaMemcpyHostToDevice, st));
-    const DetectParams P = detect_params(s);
     const DetectJobDev* dj = s->d_djobs.as<DetectJobDev>();
-    { KernelTimer kt_(ctx, "k_min_eig");
-    k_min_eig<<<dim3((s->W + kEigCols - 1) / kEigCols, n_jobs), kEigThreads, 0, st>>>(dj, P);
-    }
+    unsigned int* d_total = s->d_small.as<unsigned int>() + 4 * n_jobs;
+    launch_min_eig(ctx, dj, P, n_jobs, any_mask);
     VIO_LAUNCH_CHECK(ctx);
-    { KernelTimer kt_(ctx, "k_candidates");
-    k_candidates<<<dim3((s->W - 2 + 31) / 32, (s->H - 2 + 7) / 8, n_jobs), 256, 0, st>>>(dj, P, quality);
+    // candidates of all images go to one buffer; the count comes back to size the sort.  A batch
+    // that overflows the buffer is redone with a larger one (nothing is ever dropped).
+    unsigned int total = 0;
+    for (;;) {
+        { KernelTimer kt_(ctx, "k_candidates");
+        k_candidates<<<dim3((s->W - 2 + kCandTX - 1) / kCandTX, (s->H - 2 + kCandTY - 1) / kCandTY, n_jobs), kCandTX, 0, st>>>(
+            dj, P, quality, s->d_cand.as<unsigned long long>(), d_total);
+        }
+        VIO_LAUNCH_CHECK(ctx);
+        VIO_CUDA(ctx, cudaMemcpyAsync(s->h_dout.p, d_total, 4, cudaMemcpyDeviceToHost, st));
+        VIO_CUDA(ctx, cudaStreamSynchronize(st));
+        total = *s->h_dout.as<unsigned int>();
+        if (total <= P.max_cand) break;
+        if ((rc = reserve_candidates(ctx, (size_t)total + total / 4))) return rc;
+        P.max_cand = (unsigned int)s->cand_cap;
+        VIO_CUDA(ctx, cudaMemset2DAsync(s->d_small.as<unsigned int>() + 1, 16, 0, 4, (size_t)n_jobs, st));   // n_cand of every image
+        VIO_CUDA(ctx, cudaMemsetAsync(d_total, 0, 4, st));
     }
-    VIO_LAUNCH_CHECK(ctx);
-    // sort each job's candidates by (value, raster index) descending; the count lives on the
-    // device, so sort the whole zero-padded buffer (zeros sort last)
-    VIO_CUDA(ctx, cudaMemcpyAsync(s->h_dout.p, s->d_small.p, 16 * (size_t)n_jobs, cudaMemcpyDeviceToHost, st));
-    VIO_CUDA(ctx, cudaStreamSynchronize(st));
-    const unsigned int* hs = s->h_dout.as<unsigned int>();
-    std::vector<int> ncand(n_jobs);
-    for (int b = 0; b < n_jobs; ++b) ncand[b] = (int)std::min<unsigned int>(hs[4 * b + 1], (unsigned int)s->max_cand);
-    for (int b = 0; b < n_jobs; ++b) {
-        if (ncand[b] == 0) continue;
+    const unsigned long long* sorted = s->d_cand.as<unsigned long long>();
+    if (total > 0) {
         size_t tb = s->cub_bytes;
-        unsigned long long* in = s->d_cand.as<unsigned long long>() + (size_t)s->max_cand * b;
-        unsigned long long* outk = s->d_cand_sorted.as<unsigned long long>() + (size_t)s->max_cand * b;
-        cudaError_t e = cub::DeviceRadixSort::SortKeysDescending(s->d_cub.p, tb, in, outk, ncand[b], 0, 64, st);
+        int end_bit = 32 + P.idx_bits;
+        for (int nb = n_jobs - 1; nb > 0; nb >>= 1) ++end_bit;
+        cudaError_t e = cub::DeviceRadixSort::SortKeysDescending(s->d_cub.p, tb, s->d_cand.as<unsigned long long>(),
+                                                                 s->d_cand_sorted.as<unsigned long long>(), (int)total, 0, end_bit, st);
         if (e != cudaSuccess) return vio360_fail(ctx, VIO360_ERR_CUDA, "cub sort: %s", cudaGetErrorString(e));
-        ctx->launches += 4;   // upsweep/scan/downsweep passes of the library sort (not our kernels)
-        hj[b].cand = outk;
+        ctx->launches += 4;   // histogram / scan / onesweep passes of the library sort (not our kernels)
+        sorted = s->d_cand_sorted.as<unsigned long long>();
     }
-    VIO_CUDA(ctx, cudaMemcpyAsync(s->d_djobs.p, hj, sizeof(DetectJobDev) * (size_t)n_jobs, cudaMemcpyHostToDevice, st));
+    if (max_corners <= 0 && mem_space == VIO360_MEM_HOST) VIO_CUDA(ctx, s->d_corners.reserve((size_t)total * 8 + 8));
+    float* pool_xy = s->d_corners.as<float>();
     { KernelTimer kt_(ctx, "k_select");
-    k_select<<<n_jobs, 32, 0, st>>>(dj, P, max_corners, min_dist);
+    if (smem_grid) {
+        if (!s->select_attr_set) {
+            VIO_CUDA(ctx, cudaFuncSetAttribute(k_select<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            s->select_attr_set = true;
+        }
+        k_select<true><<<n_jobs, 32, grid_bytes, st>>>(dj, P, n_jobs, sorted, max_corners, min_dist, pool_xy);
+    } else {
+        k_select<false><<<n_jobs, 32, 0, st>>>(dj, P, n_jobs, sorted, max_corners, min_dist, pool_xy);
+    }
     }
     VIO_LAUNCH_CHECK(ctx);
     if (mem_space == VIO360_MEM_HOST) {
         uint8_t* ho = s->h_dout.as<uint8_t>();
-        VIO_CUDA(ctx, cudaMemcpyAsync(ho, s->d_small.p, 16 * (size_t)n_jobs, cudaMemcpyDeviceToHost, st));
-        VIO_CUDA(ctx, cudaMemcpyAsync(ho + 16 * (size_t)n_jobs, s->d_corners.p, cap * 8 * n_jobs, cudaMemcpyDeviceToHost, st));
-        VIO_CUDA(ctx, cudaStreamSynchronize(st));
-        for (int b = 0; b < n_jobs; ++b) {
-            const int n = ((const int*)ho)[4 * b + 2];
-            *jobs[b].out_n = n;
-            if (n > 0) memcpy(jobs[b].out_xy, ho + 16 * (size_t)n_jobs + cap * 8 * b, (size_t)n * 8);
+        const size_t small_bytes = 16 * (size_t)(n_jobs + 1);
+        VIO_CUDA(ctx, cudaMemcpyAsync(ho, s->d_small.p, small_bytes, cudaMemcpyDeviceToHost, st));
+        if (max_corners > 0) {
+            VIO_CUDA(ctx, cudaMemcpyAsync(ho + small_bytes, s->d_corners.p, cap * 8 * n_jobs, cudaMemcpyDeviceToHost, st));
+            VIO_CUDA(ctx, cudaStreamSynchronize(st));
+            for (int b = 0; b < n_jobs; ++b) {
+                const int n = ((const int*)ho)[4 * b + 2];
+                *jobs[b].out_n = n;
+                if (n > 0) memcpy(jobs[b].out_xy, ho + small_bytes + cap * 8 * b, (size_t)n * 8);
+            }
+        } else {   // unlimited corner count: copy what each image produced
+            VIO_CUDA(ctx, cudaStreamSynchronize(st));
+            size_t begin = 0;   // segments follow the descending sort: last image first
+            for (int b = n_jobs - 1; b >= 0; --b) {
+                const int n = ((const int*)ho)[4 * b + 2];
+                *jobs[b].out_n = n;
+                if (n > 0) VIO_CUDA(ctx, cudaMemcpyAsync(jobs[b].out_xy, pool_xy + 2 * begin, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+                begin += ((const unsigned int*)ho)[4 * b + 1];
+            }
+            VIO_CUDA(ctx, cudaStreamSynchronize(st));
         }
     } else {
         VIO_CUDA(ctx, cudaMemcpyAsync(s->h_dout.p, s->d_small.p, 16 * (size_t)n_jobs, cudaMemcpyDeviceToHost, st));
@@ -531,9 +588,7 @@ extern "C" int vio360_fe_min_eigen_val(vio360_ctx* ctx, const uint8_t* img, size
     hj->eig = s->d_eig.as<float>();
     hj->max_bits = s->d_small.as<unsigned int>(); hj->n_cand = hj->max_bits + 1; hj->out_n = (int*)(hj->max_bits + 2);
     VIO_CUDA(ctx, cudaMemcpyAsync(s->d_djobs.p, hj, sizeof(DetectJobDev), cudaMemcpyHostToDevice, st));
-    { KernelTimer kt_(ctx, "k_min_eig");
-    k_min_eig<<<dim3((s->W + kEigCols - 1) / kEigCols, 1), kEigThreads, 0, st>>>(s->d_djobs.as<DetectJobDev>(), detect_params(s));
-    }
+    launch_min_eig(ctx, s->d_djobs.as<DetectJobDev>(), detect_params(s), 1, false);
     VIO_LAUNCH_CHECK(ctx);
     VIO_CUDA(ctx, cudaMemcpyAsync(out, s->d_eig.p, (size_t)s->W * s->H * 4, cudaMemcpyDeviceToHost, st));
     VIO_CUDA(ctx, cudaStreamSynchronize(st));

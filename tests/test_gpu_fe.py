@@ -116,6 +116,26 @@ def test_detect_vs_oracle(ctx, synthetic, size, seed):
     assert len(ctx.fe_detect(f0, np.zeros_like(mask), 1000)) == 0
 
 
+def test_detect_batch_and_grid_variants(ctx, synthetic, monkeypatch):
+    """One batched call over different images (single merged sort), odd image size (byte loads /
+    scalar stores), a small minDistance (cell grid in global memory), minDistance < 1 (no grid),
+    no corner limit, and a candidate buffer that starts too small and is regrown."""
+    W, H = 963, 481
+    frames = [synthetic.render_erp_frame(W, H, t, seed=21 + t, n_waves=40, sigma_omega=45.0) for t in range(3)]
+    mask = fo.base_mask(W, H)
+    occ = mask.copy()
+    occ[:, 300:500] = 0
+    monkeypatch.setenv("VIO360_DET_CAND", "64")
+    ctx.fe_configure(W, H, max_points=8, max_batch=4)
+    assert np.array_equal(ctx.fe_min_eigen_val(frames[0]), fo.min_eigen_val(frames[0]))
+    for md, mc in ((30.0, 1000), (3.0, 400), (0.5, 300), (12.0, 0)):
+        got = ctx.fe_detect_batch(frames, [None, occ, None], mc, min_dist=md)
+        for b in range(3):
+            ref = fo.good_features(frames[b], occ if b == 1 else mask, mc, min_dist=md)
+            assert np.array_equal(got[b], ref), (md, mc, b)
+            assert len(ref) > 20
+
+
 def test_full_size_properties_c2(ctx, synthetic):
     """BASELINE config 2 size: a frame tracked onto itself does not move; status all ones."""
     W, H = 3840, 1920
