@@ -304,9 +304,23 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
     if (mem_space == VIO360_MEM_HOST)
         VIO_CUDA(ctx, cudaMemcpyAsync(s->d_pts_in.p, s->h_pts_in.p, off * 8, cudaMemcpyHostToDevice, st));
     { KernelTimer kt_(ctx, "k_lk_track");
-    if (s->lk_mb == 3) k_lk_track<7, 96><<<dim3((max_n + 6) / 7, n_jobs), 7 * 32, 0, st>>>(dj, lk_params(s));
-    else if (s->lk_mb == 4) k_lk_track<6, 80><<<dim3((max_n + 5) / 6, n_jobs), 6 * 32, 0, st>>>(dj, lk_params(s));
-    else k_lk_track<8, 128><<<dim3((max_n + 7) / 8, n_jobs), 8 * 32, 0, st>>>(dj, lk_params(s));
+    {
+        const LkParams lp = lk_params(s);
+        auto launch = [&](auto kern, int warps) -> cudaError_t {
+            const size_t smem = (size_t)warps * kLkWarpWords * sizeof(uint32_t);
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return e;
+            kern<<<dim3((max_n + warps - 1) / warps, n_jobs), warps * 32, smem, st>>>(dj, lp);
+            return cudaSuccess;
+        };
+        cudaError_t e;
+        if (s->lk_mb == 3) e = launch(k_lk_track<7, 96>, 7);
+        else if (s->lk_mb == 4) e = launch(k_lk_track<6, 80>, 6);
+        else if (s->lk_mb == 5) e = launch(k_lk_track<6, 104>, 6);
+        else if (s->lk_mb == 6) e = launch(k_lk_track<9, 112>, 9);
+        else e = launch(k_lk_track<8, 128>, 8);
+        if (e != cudaSuccess) return vio360_fail(ctx, VIO360_ERR_CUDA, "k_lk_track: %s", cudaGetErrorString(e));
+    }
     }
     VIO_LAUNCH_CHECK(ctx);
     if ((rc = end_stage(ctx))) return rc;

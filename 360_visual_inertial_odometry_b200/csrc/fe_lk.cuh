@@ -54,8 +54,11 @@ constexpr int kRunsPerRow = 6;                    // 6 x 4 = 24 >= 21 columns
 constexpr int kRuns = kWin * kRunsPerRow;         // 126
 constexpr int kRpl = 4;                           // runs per lane
 constexpr int kTRows = 24, kTWords = 8;           // template tile: 24 rows x 32 bytes
-constexpr int kDRows = 22, kDWords = 28;          // derivative grid: 22 (+2 zero) rows x 28 packed (ix | iy << 16)
+constexpr int kDRows = 22, kDWords = 24;          // derivative grid: two planes (Ix, Iy) of 22 (+2 zero) rows x 24 ints; a run's
+                                                  // four values sit at word 4 * run, so 128-bit accesses are conflict free
+constexpr int kDPlane = (kDRows + 2) * kDWords;
 constexpr int kJRows = 32, kJWords = 9;           // search tile: 32 rows x 36 bytes
+constexpr int kLkWarpWords = kTRows * kTWords + 2 * kDPlane + kJRows * kJWords;   // shared words per feature (warp)
 
 // exact 64-bit warp sum of 32-bit lane partials from two hardware integer reductions
 __device__ __forceinline__ long long warp_sum_i32(int v) {
@@ -146,20 +149,37 @@ __device__ __forceinline__ void run_sample(const uint32_t* __restrict__ top, con
     v[3] = dp2a_hi_su(wt, tb, dp2a_hi_su(wb, bb, 256)) >> 9;
 }
 
+// Derivatives outside the image are zero (the zero apron of calcScharrDeriv's buffer); only
+// windows that leave the image need this pass.
+__device__ __noinline__ void deriv_zero_outside(int* sDx, int* sDy, int ipx, int ipy, int w, int h, int lane) {
+#pragma unroll 1
+    for (int i = lane; i < kDRows * kDRows; i += 32) {
+        const int dy = i / kDRows, dx = i - dy * kDRows;
+        const unsigned gx = (unsigned)(ipx + dx), gy = (unsigned)(ipy + dy);
+        if (gx >= (unsigned)w || gy >= (unsigned)h) { sDx[dy * kDWords + dx] = 0; sDy[dy * kDWords + dx] = 0; }
+    }
+}
+
 // kLkWarps features per CTA; REGS = register cap (8 warps x 128 regs -> 16 warps / SM,
 // 7 x 96 -> 21, 6 x 80 -> 24)
 template <int kLkWarps, int REGS>
 __global__ void __launch_bounds__(kLkWarps * 32) __maxnreg__(REGS) k_lk_track(const TrackJobDev* __restrict__ jobs, LkParams P) {
-    __shared__ __align__(16) uint32_t sT_all[kLkWarps][kTRows * kTWords];
-    __shared__ __align__(16) uint32_t sD_all[kLkWarps][(kDRows + 2) * kDWords];
-    __shared__ __align__(16) uint32_t sJ_all[kLkWarps][kJRows * kJWords];
+    extern __shared__ __align__(16) uint32_t lk_smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const TrackJobDev& job = jobs[blockIdx.y];
     const int pt = blockIdx.x * kLkWarps + warp;
     if (pt >= job.n) return;   // warp-uniform; only __syncwarp is used below
-    uint32_t* sT = sT_all[warp];
-    uint32_t* sD = sD_all[warp];
-    uint32_t* sJ = sJ_all[warp];
+    uint32_t* sT = lk_smem + warp * kLkWarpWords;
+    int* sDx = reinterpret_cast<int*>(sT + kTRows * kTWords);
+    int* sDy = sDx + kDPlane;
+    uint32_t* sJ = reinterpret_cast<uint32_t*>(sDy + kDPlane);
+    // Zero once what the Scharr stage never writes: columns 22, 23 of every row (the taps right of
+    // the window) and rows 22, 23 (read by the two padding runs of lanes 30 / 31).
+    if (lane < kDRows) {
+        *reinterpret_cast<int2*>(sDx + lane * kDWords + kDRows) = make_int2(0, 0);
+        *reinterpret_cast<int2*>(sDy + lane * kDWords + kDRows) = make_int2(0, 0);
+    }
+    for (int i = lane; i < 2 * kDWords; i += 32) { sDx[kDRows * kDWords + i] = 0; sDy[kDRows * kDWords + i] = 0; }
 
     // runs owned by this lane: window row wy, column segment seg (columns 4*seg .. 4*seg+3);
     // offJ = wy * kJWords + seg is the only per-run register kept across the level loop
@@ -241,17 +261,12 @@ __global__ void __launch_bounds__(kLkWarps * 32) __maxnreg__(REGS) k_lk_track(co
         {
             const int cr = lane % 6, g = lane / 6;            // g 0..4 work, lanes 30, 31 idle
             if (g < 5) {
-                const int r0 = g * 5, r1 = min(r0 + 5, kDRows);   // rows 0-4, 5-9, 10-14, 15-19, 20-21
+                const bool full = g < 4;                      // rows 0-4, 5-9, 10-14, 15-19; g == 4 has rows 20, 21 only
+                const int r0 = g * 5;
                 const int b0 = oT - 1 + 4 * cr;               // tile byte of column (dx0 - 1), dx0 = 4 * cr
                 const uint32_t* q = sT + r0 * kTWords + (b0 >> 2);
                 const int s8 = 8 * (b0 & 3);
-                uint32_t cm[4];                               // column validity (derivative apron is zero)
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int dx = 4 * cr + j, gx = ipx + dx;
-                    cm[j] = (dx < kDRows && gx >= 0 && gx < w) ? 0xffffffffu : 0u;
-                }
-                int h0[4], h1[4], h2[4], d0[4], d1[4], d2[4];
+                int hA[4], hB[4], hC[4], dA[4], dB[4], dC[4];
 #define LK_ROW_HD(H, Dd)                                                                   \
                 {                                                                          \
                     const uint32_t a0 = __funnelshift_rc(q[0], q[1], s8);                   \
@@ -264,33 +279,41 @@ __global__ void __launch_bounds__(kLkWarps * 32) __maxnreg__(REGS) k_lk_track(co
                     H[3] = dp4a_us(x3, 0x00030a03, 0); Dd[3] = dp4a_us(x3, 0x000100ff, 0);  \
                     q += kTWords;                                                           \
                 }
-                LK_ROW_HD(h0, d0)
-                LK_ROW_HD(h1, d1)
-                uint32_t* dst = sD + r0 * kDWords + 4 * cr;
-#pragma unroll 1
-                for (int dy = r0; dy < r1; ++dy) {
-                    LK_ROW_HD(h2, d2)
-                    const unsigned gy = (unsigned)(ipy + dy);
-                    const uint32_t rm = gy < (unsigned)h ? 0xffffffffu : 0u;
-                    uint32_t o[4];
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const int ix = 3 * (d0[j] + d2[j]) + 10 * d1[j];
-                        const int iy = h2[j] - h0[j];
-                        o[j] = __byte_perm((uint32_t)ix, (uint32_t)iy, 0x5410) & cm[j] & rm;   // (ix & 0xffff) | (iy << 16)
-                        h0[j] = h1[j]; h1[j] = h2[j]; d0[j] = d1[j]; d1[j] = d2[j];
-                    }
-                    *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[2], o[3]);
-                    dst += kDWords;
+                // output row (r0 + I) from the window (H0, D0), (H1, D1) and the freshly read row (H2, D2)
+#define LK_ROW_OUT(I, H0, D0, H1, D1, H2, D2)                                              \
+                if ((I) < 2 || full) {                                                     \
+                    LK_ROW_HD(H2, D2)                                                      \
+                    int ix[4], iy[4];                                                      \
+                    _Pragma("unroll") for (int j = 0; j < 4; ++j) {                        \
+                        ix[j] = 3 * (D0[j] + D2[j]) + 10 * D1[j];                           \
+                        iy[j] = H2[j] - H0[j];                                             \
+                    }                                                                      \
+                    int* ox = sDx + (r0 + (I)) * kDWords + 4 * cr;                         \
+                    int* oy = sDy + (r0 + (I)) * kDWords + 4 * cr;                         \
+                    if (cr < 5) {                                                          \
+                        *reinterpret_cast<int4*>(ox) = make_int4(ix[0], ix[1], ix[2], ix[3]); \
+                        *reinterpret_cast<int4*>(oy) = make_int4(iy[0], iy[1], iy[2], iy[3]); \
+                    } else {   /* columns 20, 21; 22 and 23 stay zero */                   \
+                        *reinterpret_cast<int2*>(ox) = make_int2(ix[0], ix[1]);            \
+                        *reinterpret_cast<int2*>(oy) = make_int2(iy[0], iy[1]);            \
+                    }                                                                      \
                 }
+                LK_ROW_HD(hA, dA)
+                LK_ROW_HD(hB, dB)
+                LK_ROW_OUT(0, hA, dA, hB, dB, hC, dC)
+                LK_ROW_OUT(1, hB, dB, hC, dC, hA, dA)
+                LK_ROW_OUT(2, hC, dC, hA, dA, hB, dB)
+                LK_ROW_OUT(3, hA, dA, hB, dB, hC, dC)
+                LK_ROW_OUT(4, hB, dB, hC, dC, hA, dA)
+#undef LK_ROW_OUT
 #undef LK_ROW_HD
             }
-            // column 24 of every row is read by the last run's right tap, row 22 by the two
-            // padding runs of lanes 30 / 31: keep them zero
-            if (lane < kDRows) sD[lane * kDWords + 24] = 0u;
-            if (lane < kDWords) { sD[kDRows * kDWords + lane] = 0u; sD[(kDRows + 1) * kDWords + lane] = 0u; }
         }
         __syncwarp();
+        if (ipx < 0 || ipy < 0 || ipx + kDRows > w || ipy + kDRows > h) {   // warp-uniform, rare
+            deriv_zero_outside(sDx, sDy, ipx, ipy, w, h, lane);
+            __syncwarp();
+        }
         // ---- template samples: I (only for sum I*Ix, sum I*Iy), Ix, Iy per owned pixel
         int wtI, wbI;   // template weights, kept for the error epilogue
         bilinear_weights(px - ipx, py - ipy, wtI, wbI);
@@ -304,16 +327,13 @@ __global__ void __launch_bounds__(kLkWarps * 32) __maxnreg__(REGS) k_lk_track(co
                 int iv[4];
                 run_sample(sT + LK_OFF_T(k) + kT, sT + LK_OFF_T(k) + kT + kTWords, sT8, wtI, wbI, iv);
                 const int oD = LK_OFF_D(k);
-                const uint4 da = *reinterpret_cast<const uint4*>(sD + oD);
-                const uint4 db = *reinterpret_cast<const uint4*>(sD + oD + kDWords);
-                const uint32_t dt[5] = {da.x, da.y, da.z, da.w, sD[oD + 4]};
-                const uint32_t dbt[5] = {db.x, db.y, db.z, db.w, sD[oD + kDWords + 4]};
-                int tx[5], ty[5], bx[5], by[5];
-#pragma unroll
-                for (int j = 0; j < 5; ++j) {
-                    tx[j] = (int)(short)(dt[j] & 0xffff); ty[j] = (int)dt[j] >> 16;
-                    bx[j] = (int)(short)(dbt[j] & 0xffff); by[j] = (int)dbt[j] >> 16;
-                }
+                const int4 xa = *reinterpret_cast<const int4*>(sDx + oD), xb = *reinterpret_cast<const int4*>(sDx + oD + kDWords);
+                const int4 ya = *reinterpret_cast<const int4*>(sDy + oD), yb = *reinterpret_cast<const int4*>(sDy + oD + kDWords);
+                // the fifth tap of a run in the last column segment would be column 24 = the next row's
+                // column 0; that tap belongs to padding pixel 23 and must read zero
+                const bool seg5 = offJ[k] % kJWords == 5;
+                const int tx[5] = {xa.x, xa.y, xa.z, xa.w, seg5 ? 0 : sDx[oD + 4]}, bx[5] = {xb.x, xb.y, xb.z, xb.w, seg5 ? 0 : sDx[oD + kDWords + 4]};
+                const int ty[5] = {ya.x, ya.y, ya.z, ya.w, seg5 ? 0 : sDy[oD + 4]}, by[5] = {yb.x, yb.y, yb.z, yb.w, seg5 ? 0 : sDy[oD + kDWords + 4]};
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     int ixv = (tx[j] * w00 + tx[j + 1] * w01 + bx[j] * w10 + bx[j + 1] * w11 + (1 << 13)) >> 14;
