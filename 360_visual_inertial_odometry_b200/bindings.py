@@ -20,6 +20,7 @@ EXPORTS = [
     "vio360_enable_kernel_timing", "vio360_kernel_time", "vio360_reset_kernel_times",
     "vio360_fe_configure", "vio360_fe_track", "vio360_fe_track_batch", "vio360_fe_detect",
     "vio360_fe_detect_batch", "vio360_fe_pyramid", "vio360_fe_min_eigen_val",
+    "vio360_fe_ransac_rotation", "vio360_fe_ransac_rotation_batch",
     "vio360_ba_create", "vio360_ba_destroy", "vio360_ba_set_structure", "vio360_ba_set_outliers",
     "vio360_ba_set_shard", "vio360_ba_set_parameters", "vio360_ba_evaluate",
     "vio360_ba_get_residuals_jacobians", "vio360_ba_normal_blocks", "vio360_ba_reduced_dim",
@@ -37,6 +38,11 @@ class TrackJob(C.Structure):
                 ("cur", C.c_void_p), ("cur_pitch", C.c_size_t), ("cur_key", C.c_uint64),
                 ("prev_xy", C.c_void_p), ("n", C.c_int),
                 ("cur_xy", C.c_void_p), ("status", C.c_void_p), ("err", C.c_void_p), ("keep", C.c_void_p)]
+
+
+class RansacJob(C.Structure):
+    _fields_ = [("prev_xy", C.c_void_p), ("cur_xy", C.c_void_p), ("n", C.c_int), ("samples", C.c_void_p),
+                ("inlier_mask", C.c_void_p), ("best_inliers", C.c_void_p), ("counts", C.c_void_p)]
 
 
 class DetectJob(C.Structure):
@@ -81,6 +87,9 @@ def load():
     lib.vio360_fe_track_batch.argtypes = [C.c_void_p, C.POINTER(TrackJob), C.c_int, C.c_int]
     lib.vio360_fe_detect.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p, C.c_size_t,
                                      C.c_int, C.c_double, C.c_double, C.c_void_p, C.POINTER(C.c_int)]
+    lib.vio360_fe_ransac_rotation.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_float,
+                                              C.c_void_p, C.c_void_p]
+    lib.vio360_fe_ransac_rotation_batch.argtypes = [C.c_void_p, C.POINTER(RansacJob), C.c_int, C.c_int, C.c_float, C.c_int]
     lib.vio360_fe_detect_batch.argtypes = [C.c_void_p, C.POINTER(DetectJob), C.c_int, C.c_int, C.c_double,
                                            C.c_double, C.c_int]
     lib.vio360_fe_pyramid.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.POINTER(C.c_void_p),
@@ -241,6 +250,32 @@ class Context:
             j.out_xy, j.out_n = outs[b].ctypes.data, ns.ctypes.data + 4 * b
         self.check(self.lib.vio360_fe_detect_batch(self.h, jobs, nb, max_corners, quality, min_dist, MEM_HOST))
         return [outs[b][:ns[b]].copy() for b in range(nb)]
+
+    def fe_ransac_rotation(self, prev_xy, cur_xy, samples, threshold_deg):
+        """FeatureTracker::RejectOutliersRotationRANSAC with an injected (iters, 3) sample list.
+        returns (best_inliers, mask, counts)."""
+        return self.fe_ransac_rotation_batch([(prev_xy, cur_xy, samples)], threshold_deg)[0]
+
+    def fe_ransac_rotation_batch(self, items, threshold_deg):
+        nb = len(items)
+        jobs = (RansacJob * nb)()
+        keep, outs = [], []
+        iters = None
+        for b, (prev_xy, cur_xy, samples) in enumerate(items):
+            prev_xy = np.ascontiguousarray(prev_xy, np.float32).reshape(-1, 2)
+            cur_xy = np.ascontiguousarray(cur_xy, np.float32).reshape(-1, 2)
+            samples = np.ascontiguousarray(samples, np.int32).reshape(-1, 3)
+            iters = samples.shape[0] if iters is None else iters
+            assert samples.shape[0] == iters
+            n = prev_xy.shape[0]
+            mask = np.zeros(n, np.uint8); best = np.zeros(1, np.int32); counts = np.zeros(max(iters, 1), np.int32)
+            keep.append((prev_xy, cur_xy, samples))
+            outs.append((best, mask, counts))
+            j = jobs[b]
+            j.prev_xy, j.cur_xy, j.n, j.samples = _ptr(prev_xy), _ptr(cur_xy), n, _ptr(samples)
+            j.inlier_mask, j.best_inliers, j.counts = _ptr(mask), best.ctypes.data, counts.ctypes.data
+        self.check(self.lib.vio360_fe_ransac_rotation_batch(self.h, jobs, nb, iters or 0, C.c_float(threshold_deg), MEM_HOST))
+        return [(int(b[0]), m, c[:iters]) for b, m, c in outs]
 
     def fe_detect_batch_raw(self, jobs, n_jobs, max_corners, quality, min_dist, mem_space):
         self.check(self.lib.vio360_fe_detect_batch(self.h, jobs, n_jobs, max_corners, quality, min_dist, mem_space))

@@ -55,8 +55,8 @@ struct vio360_ba {
     // chunked (atomic-free) Schur path: see ba_schur.cuh
     std::vector<int> h_pose;                 // landmark-major pose index of every observation
     std::vector<SchurChunk> chunks;
-    std::vector<int> irregular, cov_ptr, cov_idx, free_pose, reach, slot_table;
-    DevBuf d_chunks, d_cov_ptr, d_cov_idx, d_free_pose, d_irregular, d_partS, d_partRhs, d_reach, d_slots;
+    std::vector<int> irregular, cov_ptr, cov_idx, free_pose, reach, slot_table, batch_rng;
+    DevBuf d_chunks, d_cov_ptr, d_cov_idx, d_free_pose, d_irregular, d_partS, d_partRhs, d_reach, d_slots, d_batch_rng;
     bool chunks_dirty = true, smem_attr_set = false, chunk_error = false;
 };
 
@@ -452,7 +452,7 @@ extern "C" void vio360_ba_destroy(vio360_ba* ba) {
                       &ba->d_pose_ptr, &ba->d_pose_order, &ba->d_Twb, &ba->d_Tcb, &ba->d_posebuf, &ba->d_pose_delta,
                       &ba->d_points, &ba->d_free_map, &ba->d_point_fixed, &ba->d_D, &ba->d_r, &ba->d_Jp, &ba->d_Jl,
                       &ba->d_partials, &ba->d_packed, &ba->d_blocks, &ba->d_chi2, &ba->d_flag,
-                      &ba->d_chunks, &ba->d_cov_ptr, &ba->d_cov_idx, &ba->d_free_pose, &ba->d_irregular, &ba->d_partS, &ba->d_partRhs, &ba->d_reach, &ba->d_slots};
+                      &ba->d_chunks, &ba->d_cov_ptr, &ba->d_cov_idx, &ba->d_free_pose, &ba->d_irregular, &ba->d_partS, &ba->d_partRhs, &ba->d_reach, &ba->d_slots, &ba->d_batch_rng};
     for (DevBuf* b : bufs) b->release();
     ba->pin.release();
     delete ba;
@@ -513,6 +513,7 @@ static void build_chunks(vio360_ba* ba) {
     int nbatch_total = 0;
     for (SchurChunk& c : ba->chunks) { c.batch0 = nbatch_total; nbatch_total += (c.lm_end - c.lm_begin + kSMaxLm - 1) / kSMaxLm; }
     ba->slot_table.assign((size_t)std::max(1, nbatch_total) * kSProd, -1);
+    ba->batch_rng.assign((size_t)std::max(1, nbatch_total), 0xff);   // empty: lo = 255 > hi = 0
     for (const SchurChunk& c : ba->chunks)
         for (int l = c.lm_begin; l < c.lm_end; ++l) {
             const int b = (l - c.lm_begin) / kSMaxLm, ls = (l - c.lm_begin) % kSMaxLm;
@@ -521,6 +522,9 @@ static void build_chunks(vio360_ba* ba) {
                 const int pw = ba->h_pose[q] - c.pbase;
                 if (pw < 0 || pw >= c.span || row[pw * kSMaxLm + ls] != -1) { ba->chunk_error = true; continue; }
                 row[pw * kSMaxLm + ls] = q;
+                int& rg = ba->batch_rng[c.batch0 + b];   // used pose slots of the batch: lo | hi << 8
+                const int lo = std::min(rg & 0xff, pw), hi = std::max((rg >> 8) & 0xff, pw);
+                rg = lo | (hi << 8);
             }
         }
     ba->reach.assign(K, -1);
@@ -842,6 +846,8 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
             VIO_CUDA(ctx, ba->d_reach.reserve(ba->reach.size() * 4));
             VIO_CUDA(ctx, ba->d_slots.reserve(ba->slot_table.size() * 4));
             VIO_CUDA(ctx, cudaMemcpy(ba->d_slots.p, ba->slot_table.data(), ba->slot_table.size() * 4, cudaMemcpyHostToDevice));
+            VIO_CUDA(ctx, ba->d_batch_rng.reserve(ba->batch_rng.size() * 4));
+            VIO_CUDA(ctx, cudaMemcpy(ba->d_batch_rng.p, ba->batch_rng.data(), ba->batch_rng.size() * 4, cudaMemcpyHostToDevice));
             VIO_CUDA(ctx, cudaMemcpy(ba->d_reach.p, ba->reach.data(), ba->reach.size() * 4, cudaMemcpyHostToDevice));
             if (!ba->chunks.empty()) VIO_CUDA(ctx, cudaMemcpy(ba->d_chunks.p, ba->chunks.data(), ba->chunks.size() * sizeof(SchurChunk), cudaMemcpyHostToDevice));
             VIO_CUDA(ctx, cudaMemcpy(ba->d_cov_ptr.p, ba->cov_ptr.data(), ba->cov_ptr.size() * 4, cudaMemcpyHostToDevice));
@@ -856,7 +862,7 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
         }
         if (nch > 0) {
             { KernelTimer kt_(ctx, "k_schur_tile");
-            k_schur_tile<<<nch, kSThreads, kSchurSmemBytes, st>>>(d, ba->d_chunks.as<SchurChunk>(), ba->d_slots.as<int>(), apply_loss != 0, ba->d_partS.as<double>(),
+            k_schur_tile<<<nch, kSThreads, kSchurSmemBytes, st>>>(d, ba->d_chunks.as<SchurChunk>(), ba->d_slots.as<int>(), ba->d_batch_rng.as<int>(), apply_loss != 0, ba->d_partS.as<double>(),
                                                                  ba->d_partRhs.as<double>(), ba->d_partials.as<double>());
             }
             VIO_LAUNCH_CHECK(ctx);

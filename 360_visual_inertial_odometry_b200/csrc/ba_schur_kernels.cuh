@@ -23,7 +23,8 @@ __device__ __forceinline__ void named_bar_arrive(int id, int count) {
 constexpr int kBarProd = 1, kBarFull = 2, kBarEmpty = 4;   // ids: producers-only, full[2], empty[2]
 
 __global__ void __launch_bounds__(kSThreads, 1)
-k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restrict__ slots, bool apply_loss, double* __restrict__ partS,
+k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restrict__ slots, const int* __restrict__ batch_rng, bool apply_loss,
+             double* __restrict__ partS,
              double* __restrict__ partRhs, double* __restrict__ partCost) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* Zst = reinterpret_cast<double*>(smem_raw);          // [2][kSK][kSZPitch] operand stages, Z^T: column-major in k
@@ -195,17 +196,27 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
     } else {
         // ================= consumers: S_tile -= Z Z' over the stage's 48 columns =================
         const int cw = warp - kSProd / 32;
-        const int nb2 = (6 * ch.span + 15) >> 4;
-        const int nblk = nb2 * (nb2 + 1) / 2;
         const int fr = lane >> 2, fc = lane & 3;
+        int rng_next = nbatch > 0 ? __ldg(batch_rng + ch.batch0) : 0;
         for (int b = 0; b < nbatch; ++b) {
             const double* Zs = Zst + (b & 1) * kSK * kSZPitch;
+            // pose slots [wlo, whi] used by this batch: Z is zero outside, so only the 8x8 tiles
+            // tlo..thi of the window change (a band of ~degree poses inside the 24-pose window)
+            const int rng = rng_next;
+            if (b + 1 < nbatch) rng_next = __ldg(batch_rng + ch.batch0 + b + 1);
+            const int wlo = rng & 0xff, whi = (rng >> 8) & 0xff;
+            const int tlo = (6 * wlo) >> 3, thi = (6 * whi + 5) >> 3;
+            const int blo = tlo >> 1, nb2 = whi >= wlo ? (thi >> 1) - blo + 1 : 0;
+            const int nblk = nb2 * (nb2 + 1) / 2;
             named_bar_sync(kBarFull + (b & 1), kSThreads);
             for (int blk = cw; blk < nblk; blk += kSCons / 32) {
                 int bi = 0, rem = blk;
                 while (rem >= nb2 - bi) { rem -= nb2 - bi; ++bi; }
-                const int bj = bi + rem;
+                const int bj = blo + bi + rem;
+                bi += blo;
                 const bool diag = bi == bj;
+                const bool vr0 = 2 * bi >= tlo, vr1 = 2 * bi + 1 <= thi, vc0 = 2 * bj >= tlo, vc1 = 2 * bj + 1 <= thi;
+                const bool p00 = vr0 && vc0, p01 = vr0 && vc1, p11 = vr1 && vc1, p10 = !diag && vr1 && vc0;
                 double2* c00 = reinterpret_cast<double2*>(St + schur_tile_index(2 * bi, 2 * bj) * 64) + lane;
                 double2* c01 = reinterpret_cast<double2*>(St + schur_tile_index(2 * bi, 2 * bj + 1) * 64) + lane;
                 double2* c11 = reinterpret_cast<double2*>(St + schur_tile_index(2 * bi + 1, 2 * bj + 1) * 64) + lane;
@@ -218,10 +229,10 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
                 for (int ks = 0; ks < kSK / 4; ++ks) {
                     const double x0 = -za[4 * ks * kSZPitch], x1 = -za[4 * ks * kSZPitch + 8];
                     const double y0 = zb[4 * ks * kSZPitch], y1 = zb[4 * ks * kSZPitch + 8];
-                    dmma884(a00.x, a00.y, x0, y0);
-                    dmma884(a01.x, a01.y, x0, y1);
-                    dmma884(a11.x, a11.y, x1, y1);
-                    if (!diag) dmma884(a10.x, a10.y, x1, y0);
+                    if (p00) dmma884(a00.x, a00.y, x0, y0);
+                    if (p01) dmma884(a01.x, a01.y, x0, y1);
+                    if (p11) dmma884(a11.x, a11.y, x1, y1);
+                    if (p10) dmma884(a10.x, a10.y, x1, y0);
                 }
                 *c00 = a00; *c01 = a01; *c11 = a11;
                 if (!diag) *c10 = a10;

@@ -6,6 +6,7 @@
 
 #include "common.cuh"
 #include "fe_detect.cuh"
+#include "fe_ransac.cuh"
 #include "fe_lk.cuh"
 #include "fe_pyr.cuh"
 
@@ -46,6 +47,9 @@ struct vio360_fe_state {
     // detection pools
     DevBuf d_djobs, d_eig, d_mask, d_small, d_cand, d_cand_sorted, d_grid, d_cub, d_corners;
     PinBuf h_djobs, h_dout;
+    // rotation RANSAC pools
+    DevBuf d_ransac;
+    PinBuf h_ransac;
     int det_batch_cap = 0, max_cand = 1 << 17;   // initial candidate capacity per image (grown on demand)
     size_t cand_cap = 0;
     bool select_attr_set = false;
@@ -59,9 +63,9 @@ void vio360_fe_release(vio360_ctx* ctx) {
     for (auto& sl : s->slots) sl.mem.release();
     DevBuf* db[] = {&s->d_jobs, &s->d_pyrjobs, &s->d_pts_in, &s->d_pts_out, &s->d_status, &s->d_err, &s->d_keep,
                     &s->d_djobs, &s->d_eig, &s->d_mask, &s->d_small, &s->d_cand, &s->d_cand_sorted, &s->d_grid,
-                    &s->d_cub, &s->d_corners};
+                    &s->d_cub, &s->d_corners, &s->d_ransac};
     for (DevBuf* b : db) b->release();
-    PinBuf* pb[] = {&s->h_pts_in, &s->h_out, &s->h_djobs, &s->h_dout};
+    PinBuf* pb[] = {&s->h_pts_in, &s->h_out, &s->h_djobs, &s->h_dout, &s->h_ransac};
     for (PinBuf* b : pb) b->release();
     for (auto& sg : s->stage) { sg.jobs.release(); sg.pyrjobs.release(); if (sg.ev) cudaEventDestroy(sg.ev); }
     for (auto& d : s->d_jobs_ring) d.release();
@@ -607,4 +611,109 @@ extern "C" int vio360_fe_min_eigen_val(vio360_ctx* ctx, const uint8_t* img, size
     VIO_CUDA(ctx, cudaMemcpyAsync(out, s->d_eig.p, (size_t)s->W * s->H * 4, cudaMemcpyDeviceToHost, st));
     VIO_CUDA(ctx, cudaStreamSynchronize(st));
     return VIO360_OK;
+}
+
+// ---- rotation-only RANSAC -------------------------------------------
+extern "C" int vio360_fe_ransac_rotation_batch(vio360_ctx* ctx, const vio360_ransac_job* jobs, int n_jobs, int iters,
+                                               float threshold_deg, int mem_space) {
+    if (!ctx) return VIO360_ERR_INVALID;
+    vio360_fe_state* s = ctx->fe;
+    if (!s || !s->configured) return vio360_fail(ctx, VIO360_ERR_STATE, "fe_ransac before fe_configure");
+    if (!jobs || n_jobs < 0 || iters < 0) return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_ransac: bad arguments");
+    if (n_jobs == 0) return VIO360_OK;
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    VIO_CUDA(ctx, cudaStreamSynchronize(st));
+    // pool layout per job (4-byte units): [prev 2n | cur 2n | samples 3I | b1 3n | b2 3n | R 9I | counts I | best 2 | mask n bytes]
+    auto a4 = [](size_t v) { return (v + 3) / 4 * 4; };
+    size_t words = 0, hwords = 0;
+    int max_n = 0;
+    for (int b = 0; b < n_jobs; ++b) {
+        const vio360_ransac_job& j = jobs[b];
+        if (j.n < 0 || (j.n > 0 && (!j.prev_xy || !j.cur_xy || !j.inlier_mask)) || !j.best_inliers || (j.n >= 3 && iters > 0 && !j.samples))
+            return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_ransac: job %d invalid", b);
+        const size_t n = (size_t)j.n, I = (size_t)iters;
+        words += 4 * n + 3 * I + 6 * n + 9 * I + I + 4 + a4(n) / 4 + 8;
+        hwords += 4 * n + 3 * I + I + 4 + a4(n) / 4 + 8;
+        max_n = std::max(max_n, j.n);
+    }
+    VIO_CUDA(ctx, s->d_ransac.reserve(words * 4 + sizeof(RansacJobDev) * (size_t)n_jobs));
+    VIO_CUDA(ctx, s->h_ransac.reserve(hwords * 4 + sizeof(RansacJobDev) * (size_t)n_jobs));
+    RansacJobDev* hj = s->h_ransac.as<RansacJobDev>();
+    RansacJobDev* dj = s->d_ransac.as<RansacJobDev>();
+    uint32_t* dw = reinterpret_cast<uint32_t*>(dj + n_jobs);
+    uint32_t* hw = reinterpret_cast<uint32_t*>(hj + n_jobs);
+    struct Back { uint32_t* h_counts; uint32_t* h_best; uint8_t* h_mask; };
+    std::vector<Back> back(n_jobs);
+    for (int b = 0; b < n_jobs; ++b) {
+        const vio360_ransac_job& j = jobs[b];
+        const size_t n = (size_t)j.n, I = (size_t)iters;
+        RansacJobDev& d = hj[b];
+        d.n = j.n;
+        if (mem_space == VIO360_MEM_DEVICE) {
+            d.prev_xy = j.prev_xy; d.cur_xy = j.cur_xy; d.samples = j.samples; d.mask = j.inlier_mask;
+        } else {
+            memcpy(hw, j.prev_xy, n * 8); VIO_CUDA(ctx, cudaMemcpyAsync(dw, hw, n * 8, cudaMemcpyHostToDevice, st));
+            d.prev_xy = (const float*)dw; dw += 2 * n; hw += 2 * n;
+            memcpy(hw, j.cur_xy, n * 8); VIO_CUDA(ctx, cudaMemcpyAsync(dw, hw, n * 8, cudaMemcpyHostToDevice, st));
+            d.cur_xy = (const float*)dw; dw += 2 * n; hw += 2 * n;
+            if (j.n >= 3 && I) { memcpy(hw, j.samples, I * 12); VIO_CUDA(ctx, cudaMemcpyAsync(dw, hw, I * 12, cudaMemcpyHostToDevice, st)); }
+            d.samples = (const int*)dw; dw += 3 * I; hw += 3 * I;
+        }
+        d.b1 = (float*)dw; dw += 3 * n;
+        d.b2 = (float*)dw; dw += 3 * n;
+        d.R = (float*)dw; dw += 9 * I;
+        d.counts = (int*)dw; dw += I;
+        d.best = (int*)dw; dw += 4;
+        back[b].h_counts = hw; hw += I;
+        back[b].h_best = hw; hw += 4;
+        if (mem_space != VIO360_MEM_DEVICE) { d.mask = (uint8_t*)dw; dw += a4(n) / 4; }
+        back[b].h_mask = (uint8_t*)hw; hw += a4(n) / 4;
+        // validate the sample list here: an index outside [0, n) would read outside the bearings
+        if (mem_space != VIO360_MEM_DEVICE && j.n >= 3)
+            for (size_t q = 0; q < 3 * I; ++q)
+                if (j.samples[q] < 0 || j.samples[q] >= j.n) return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_ransac: job %d sample %zu out of range", b, q);
+    }
+    VIO_CUDA(ctx, cudaMemcpyAsync(dj, hj, sizeof(RansacJobDev) * (size_t)n_jobs, cudaMemcpyHostToDevice, st));
+    const float thr = (float)((double)threshold_deg * 3.14159265358979323846 / 180.0);   // FeatureTracker.cpp:305
+    if (max_n > 0) {
+        { KernelTimer kt_(ctx, "k_ransac_bearings");
+        k_ransac_bearings<<<dim3((max_n + 255) / 256, n_jobs), 256, 0, st>>>(dj, s->W, s->H);
+        }
+        VIO_LAUNCH_CHECK(ctx);
+        if (iters > 0) {
+            KernelTimer kt_(ctx, "k_ransac_hypotheses");
+            k_ransac_hypotheses<<<dim3((iters + kRansacWarps - 1) / kRansacWarps, n_jobs), kRansacWarps * 32, 0, st>>>(dj, iters, thr);
+        }
+        VIO_LAUNCH_CHECK(ctx);
+    }
+    { KernelTimer kt_(ctx, "k_ransac_pick");
+    k_ransac_pick<<<n_jobs, 256, 0, st>>>(dj, iters, thr);
+    }
+    VIO_LAUNCH_CHECK(ctx);
+    for (int b = 0; b < n_jobs; ++b) {
+        const vio360_ransac_job& j = jobs[b];
+        VIO_CUDA(ctx, cudaMemcpyAsync(back[b].h_best, hj[b].best, 8, cudaMemcpyDeviceToHost, st));
+        if (j.counts && iters > 0 && mem_space != VIO360_MEM_DEVICE) VIO_CUDA(ctx, cudaMemcpyAsync(back[b].h_counts, hj[b].counts, (size_t)iters * 4, cudaMemcpyDeviceToHost, st));
+        if (j.counts && iters > 0 && mem_space == VIO360_MEM_DEVICE) VIO_CUDA(ctx, cudaMemcpyAsync(j.counts, hj[b].counts, (size_t)iters * 4, cudaMemcpyDeviceToDevice, st));
+        if (mem_space != VIO360_MEM_DEVICE && j.n > 0) VIO_CUDA(ctx, cudaMemcpyAsync(back[b].h_mask, hj[b].mask, (size_t)j.n, cudaMemcpyDeviceToHost, st));
+    }
+    VIO_CUDA(ctx, cudaStreamSynchronize(st));
+    for (int b = 0; b < n_jobs; ++b) {
+        const vio360_ransac_job& j = jobs[b];
+        *j.best_inliers = (int)back[b].h_best[0];
+        if (mem_space != VIO360_MEM_DEVICE) {
+            if (j.n > 0) memcpy(j.inlier_mask, back[b].h_mask, (size_t)j.n);
+            if (j.counts && iters > 0) memcpy(j.counts, back[b].h_counts, (size_t)iters * 4);
+        }
+    }
+    return VIO360_OK;
+}
+
+extern "C" int vio360_fe_ransac_rotation(vio360_ctx* ctx, const float* prev_xy, const float* cur_xy, int n, const int32_t* samples,
+                                         int iters, float threshold_deg, uint8_t* inlier_mask, int* best_inliers) {
+    vio360_ransac_job j;
+    j.prev_xy = prev_xy; j.cur_xy = cur_xy; j.n = n; j.samples = samples; j.inlier_mask = inlier_mask; j.best_inliers = best_inliers;
+    j.counts = nullptr;
+    return vio360_fe_ransac_rotation_batch(ctx, &j, 1, iters, threshold_deg, VIO360_MEM_HOST);
 }

@@ -1,6 +1,8 @@
 // FeatureTrackerCuda.cpp -- see FeatureTrackerCuda.h.
 #include "FeatureTrackerCuda.h"
 
+#include <algorithm>
+#include <random>
 #include <stdexcept>
 
 namespace vio_360 {
@@ -70,6 +72,37 @@ int FeatureTrackerCuda::TrackOpticalFlow(const cv::Mat& prev_image, const cv::Ma
         if (status[i]) num_tracked++;
     m_num_tracked = num_tracked;
     return num_tracked;
+}
+
+int FeatureTrackerCuda::RejectOutliersRotationRANSAC(const std::vector<cv::Point2f>& prev_points,
+                                                     const std::vector<cv::Point2f>& curr_points,
+                                                     std::vector<uchar>& inlier_mask) {
+    const int n = (int)prev_points.size();
+    if (n < 3) {   // FeatureTracker.cpp:258-261
+        inlier_mask.resize(prev_points.size(), 1);
+        return n;
+    }
+    ensure_capacity(1);
+    // the draw of FeatureTracker.cpp:273-289
+    std::random_device rd;
+    std::mt19937 gen(m_ransac_seeded ? m_ransac_seed : rd());
+    std::uniform_int_distribution<> dis(0, n - 1);
+    std::vector<int32_t> samples((size_t)m_ransac_max_iterations * 3);
+    for (int iter = 0; iter < m_ransac_max_iterations; ++iter) {
+        int32_t* idx = samples.data() + 3 * (size_t)iter;
+        int have = 0;
+        while (have < 3) {
+            const int k = dis(gen);
+            if (std::find(idx, idx + have, k) == idx + have) idx[have++] = k;
+        }
+    }
+    inlier_mask.assign((size_t)n, 0);
+    int best_inliers = 0;
+    check(vio360_fe_ransac_rotation(m_ctx, reinterpret_cast<const float*>(prev_points.data()),
+                                    reinterpret_cast<const float*>(curr_points.data()), n, samples.data(),
+                                    m_ransac_max_iterations, m_ransac_threshold, inlier_mask.data(), &best_inliers),
+          "vio360_fe_ransac_rotation");
+    return best_inliers;
 }
 
 }  // namespace vio_360

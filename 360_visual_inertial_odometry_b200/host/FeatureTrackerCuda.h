@@ -44,6 +44,13 @@ public:
     int TrackOpticalFlow(const cv::Mat& prev_image, const cv::Mat& curr_image,
                          const std::vector<cv::Point2f>& prev_points, std::vector<cv::Point2f>& curr_points,
                          std::vector<uchar>& status);
+    // FeatureTracker.cpp:253-328.  The 3-point samples are drawn here exactly as the reference draws them
+    // (std::mt19937 over std::uniform_int_distribution, repeats redrawn, :273-289); hypotheses and inlier
+    // counting run on the device.  SetRansacSeed replaces the std::random_device seed (tests).
+    int RejectOutliersRotationRANSAC(const std::vector<cv::Point2f>& prev_points,
+                                     const std::vector<cv::Point2f>& curr_points, std::vector<uchar>& inlier_mask);
+    void SetRansacSeed(uint32_t seed) { m_ransac_seed = seed; m_ransac_seeded = true; }
+    void SetRansacParams(int max_iterations, float threshold_deg) { m_ransac_max_iterations = max_iterations; m_ransac_threshold = threshold_deg; }
     // The post filter of TrackFeatures (FeatureTracker.cpp:118-126) computed on the device
     // during the last TrackOpticalFlow call: status && !polar && !near-boundary.
     const std::vector<uchar>& LastKeepMask() const { return m_keep; }
@@ -67,6 +74,10 @@ private:
     int m_point_capacity = 0;
     uint64_t m_prev_key = 0, m_curr_key = 0;
     int m_num_tracked = 0, m_num_detected = 0;
+    int m_ransac_max_iterations = 1000;   // FeatureTracker.cpp:36
+    float m_ransac_threshold = 2.0f;      // degrees, FeatureTracker.cpp:37
+    uint32_t m_ransac_seed = 0;
+    bool m_ransac_seeded = false;
     std::vector<uchar> m_keep;
     void ensure_capacity(int n_points);
 };

@@ -200,3 +200,38 @@ def make_track_points(W, H, n, seed, seam_frac=0.05, margin=20):
         x[:ns] = np.where(side, rng.uniform(margin, 104, ns), rng.uniform(W - 104, W - margin, ns))
     pts = np.stack([x, y], axis=1)
     return (np.round(pts * 8.0) / 8.0).astype(np.float32)
+
+
+def make_rotation_tracks(W, H, n, seed, angle_deg=1.2, noise_px=0.3, outlier_frac=0.2):
+    """Tracked pairs under a pure camera rotation (what RejectOutliersRotationRANSAC models,
+    FeatureTracker.cpp:253-328) + pixel noise + gross outliers.  returns prev, cur (float32), is_outlier."""
+    rng = np.random.default_rng(seed)
+    prev = np.stack([rng.uniform(20, W - 20, n), rng.uniform(0.15 * H, 0.85 * H, n)], 1).astype(np.float32)
+    p = prev.astype(np.float64)
+    lon = (p[:, 0] / W - 0.5) * 2 * np.pi
+    lat = -(p[:, 1] / H - 0.5) * np.pi
+    b = np.stack([np.cos(lat) * np.sin(lon), -np.sin(lat), np.cos(lat) * np.cos(lon)], 1)
+    ax = np.array([0.2, 0.9, 0.1]); ax /= np.linalg.norm(ax)
+    K = np.array([[0, -ax[2], ax[1]], [ax[2], 0, -ax[0]], [-ax[1], ax[0], 0]])
+    a = np.deg2rad(angle_deg)
+    R = np.eye(3) + np.sin(a) * K + (1 - np.cos(a)) * K @ K
+    rb = b @ R.T
+    th = np.arctan2(rb[:, 0], rb[:, 2]); ph = -np.arcsin(rb[:, 1] / np.linalg.norm(rb, axis=1))
+    cur = np.stack([W * (0.5 + th / (2 * np.pi)), H * (0.5 - ph / np.pi)], 1) + rng.normal(0, noise_px, (n, 2))
+    out = rng.random(n) < outlier_frac
+    cur[out] += rng.normal(0, 40, (int(out.sum()), 2))
+    return prev, cur.astype(np.float32), out
+
+
+def draw_ransac_samples(n, iters, seed):
+    """iters x 3 distinct indices, drawn like FeatureTracker.cpp:283-289 (uniform, redraw on repeats)."""
+    rng = np.random.default_rng(seed)
+    out = np.zeros((iters, 3), np.int32)
+    for it in range(iters):
+        idx = []
+        while len(idx) < 3:
+            k = int(rng.integers(0, n))
+            if k not in idx:
+                idx.append(k)
+        out[it] = idx
+    return out

@@ -240,6 +240,7 @@ def run_ours(args):
     # ---- detection (reported separately)
     if not args.skip_detect:
         line["detect"] = bench_detect(ctx, b, torch, ring, B, world, device, barrier, stream)
+        line["ransac"] = bench_ransac(ctx, syn)
     # ---- BA factor evaluation
     if not args.skip_ba:
         line["ba"] = bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, args)
@@ -250,6 +251,33 @@ def run_ours(args):
         dist.destroy_process_group()
     if rank == 0:
         print(json.dumps(line))
+
+
+def bench_ransac(ctx, syn):
+    """rotation RANSAC, 1000 tracked points x 1000 hypotheses at 2 degrees (FeatureTracker.cpp:36-37),
+    16 frames per call through the host-memory C ABI (copies inside the timed region)."""
+    nb, n, iters = 16, 1000, 1000
+    items = []
+    for s in range(nb):
+        prev, cur, _ = syn.make_rotation_tracks(W, H, n, seed=500 + s)
+        items.append((prev, cur, syn.draw_ransac_samples(n, iters, seed=600 + s)))
+    for _ in range(3):
+        res = ctx.fe_ransac_rotation_batch(items, 2.0)
+    reps = 10
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        res = ctx.fe_ransac_rotation_batch(items, 2.0)
+    dt = (time.perf_counter() - t0) / reps
+    ctx.enable_kernel_timing(True); ctx.reset_kernel_times()
+    ctx.fe_ransac_rotation_batch(items, 2.0)
+    kern = {}
+    for name in ("k_ransac_bearings", "k_ransac_hypotheses", "k_ransac_pick"):
+        ms, cnt = ctx.kernel_time(name)
+        kern[name] = ms / max(cnt, 1)
+    ctx.enable_kernel_timing(False)
+    return {"metric": "rotation RANSAC frames/s (1000 points, 1000 hypotheses)", "value": nb / dt, "unit": "frames/s",
+            "frames_per_call": nb, "ms_per_call": dt * 1e3, "kernel_ms_per_launch": kern,
+            "inliers_first_frame": int(res[0][0])}
 
 
 def bench_detect(ctx, b, torch, ring, B, world, device, barrier, stream):

@@ -124,6 +124,31 @@ int vio360_fe_pyramid(vio360_ctx* ctx, const uint8_t* img, size_t pitch, int n_l
 /* cv::cornerMinEigenVal(img, dst, 3, 3) response map (float, W x H, dense pitch). */
 int vio360_fe_min_eigen_val(vio360_ctx* ctx, const uint8_t* img, size_t pitch, float* out);
 
+/* Rotation-only RANSAC outlier rejection on tracked features.
+ * Replaces FeatureTracker::RejectOutliersRotationRANSAC / EstimateRotation /
+ * ComputeRotationInliers (src/processing/FeatureTracker.cpp:253-379) with
+ * Camera::PixelToBearing / AngularDistance (src/database/Camera.cpp:22-47, 89-98).
+ * The reference draws its 3-point samples from std::random_device (:273-275); the draw stays
+ * on the host and is passed in: samples is iters x 3 distinct point indices per row.
+ * threshold_deg is m_ransac_threshold (degrees).  Outputs: inlier_mask[n] (0/1) and
+ * *best_inliers (the function's return value): n < 3 -> all ones, n; no hypothesis with an
+ * inlier -> all ones, 0.  counts (iters ints, optional) receives every hypothesis' inlier
+ * count, -1 where |det R - 1| > 0.1 rejected it (:300-302).                              */
+typedef struct vio360_ransac_job {
+    const float* prev_xy;
+    const float* cur_xy;
+    int n;
+    const int32_t* samples;
+    uint8_t* inlier_mask;
+    int* best_inliers;       /* host memory in both memory spaces */
+    int32_t* counts;         /* may be NULL */
+} vio360_ransac_job;
+int vio360_fe_ransac_rotation(vio360_ctx* ctx, const float* prev_xy, const float* cur_xy, int n,
+                              const int32_t* samples, int iters, float threshold_deg,
+                              uint8_t* inlier_mask, int* best_inliers);
+int vio360_fe_ransac_rotation_batch(vio360_ctx* ctx, const vio360_ransac_job* jobs, int n_jobs,
+                                    int iters, float threshold_deg, int mem_space);
+
 /* ------------------------------------------- path B: BA factor evaluation ---- */
 /* A window = what Optimizer::RunLocalBA / RunBA assemble (src/optimization/
  * Optimizer.cpp:741-840): K poses, M landmarks, O observations.                     */

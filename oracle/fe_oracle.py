@@ -115,6 +115,21 @@ def post_filter(xy, status, w, h, polar_thr=0.15, margin=20.0):
     return keep
 
 
+def ransac_rotation(prev_xy, cur_xy, w, h, samples, threshold_deg):
+    """FeatureTracker::RejectOutliersRotationRANSAC with an injected sample list (iters x 3).
+    returns (best_inliers, mask, counts, best_iter, errs)."""
+    prev_xy = np.ascontiguousarray(prev_xy, np.float32); cur_xy = np.ascontiguousarray(cur_xy, np.float32)
+    samples = np.ascontiguousarray(samples, np.int32).reshape(-1, 3)
+    n, iters = prev_xy.shape[0], samples.shape[0]
+    mask = np.zeros(n, np.uint8); counts = np.zeros(max(iters, 1), np.int32); errs = np.zeros(max(n, 1), np.float32)
+    bi = C.c_int(-1)
+    f = lib().vf_ransac_rotation
+    f.restype = C.c_int
+    best = f(_p(prev_xy, C.c_float), _p(cur_xy, C.c_float), n, w, h, _p(samples, C.c_int), iters,
+             C.c_float(threshold_deg), _p(mask, C.c_ubyte), _p(counts, C.c_int), C.byref(bi), _p(errs, C.c_float))
+    return best, mask, counts[:iters], bi.value, errs[:n]
+
+
 # ------------------------------------------------------------------ the real dependency
 def cv2_lk_track(prev, cur, pts):
     """cv::calcOpticalFlowPyrLK exactly as FeatureTracker.cpp:238-240 calls it."""

@@ -451,3 +451,139 @@ void vf_post_filter(const float* xy, const uint8_t* status, int n, int w, int h,
         keep[i] = (uint8_t)(status[i] && !polar && !nearb);
     }
 }
+
+/* ------------------------------------------------------------------ rotation RANSAC */
+#ifndef M_PI
+#define M_PI 3.14159265358979323846   /* -std=c11 hides the POSIX constant */
+#endif
+/* Camera.cpp:22-47 */
+static void pixel_to_bearing(float px, float py, int W, int H, float b[3]) {
+    const float u_norm = px / (float)W, v_norm = py / (float)H;
+    const float lon = (float)((double)((u_norm - 0.5f) * 2.0f) * M_PI);   /* float * double -> float */
+    const float lat = (float)((double)(-(v_norm - 0.5f)) * M_PI);
+    const float cos_lat = cosf(lat);
+    b[0] = cos_lat * sinf(lon);
+    b[1] = -sinf(lat);
+    b[2] = cos_lat * cosf(lon);
+    const float n2 = b[0] * b[0] + b[1] * b[1] + b[2] * b[2];          /* Eigen normalize() */
+    if (n2 > 0.f) { const float nn = sqrtf(n2); b[0] /= nn; b[1] /= nn; b[2] /= nn; }
+}
+
+static float det3f(const float A[9]) {
+    return A[0] * (A[4] * A[8] - A[5] * A[7]) - A[1] * (A[3] * A[8] - A[5] * A[6]) +
+           A[2] * (A[3] * A[7] - A[4] * A[6]);
+}
+
+/* U V^T of the SVD of the 3x3 M (row-major); V column 2 negated if det < 0 (FeatureTracker.cpp:345-349) */
+static void kabsch_rotation(const float M[9], float R[9]) {
+    float B[9], V[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+    memcpy(B, M, sizeof(B));
+    for (int sweep = 0; sweep < 30; ++sweep) {
+        float off = 0.f;
+        for (int p = 0; p < 2; ++p)
+            for (int q = p + 1; q < 3; ++q) {
+                float alpha = 0.f, beta = 0.f, gamma = 0.f;
+                for (int k = 0; k < 3; ++k) {
+                    alpha += B[k * 3 + p] * B[k * 3 + p];
+                    beta += B[k * 3 + q] * B[k * 3 + q];
+                    gamma += B[k * 3 + p] * B[k * 3 + q];
+                }
+                const float lim = sqrtf(alpha * beta);
+                if (gamma == 0.f || fabsf(gamma) <= 1e-9f * lim) continue;
+                const float rel = fabsf(gamma) / (lim > 0.f ? lim : 1.f);
+                if (rel > off) off = rel;
+                const float zeta = (beta - alpha) / (2.f * gamma);
+                const float t = (zeta >= 0.f ? 1.f : -1.f) / (fabsf(zeta) + sqrtf(1.f + zeta * zeta));
+                const float c = 1.f / sqrtf(1.f + t * t), s = c * t;
+                for (int k = 0; k < 3; ++k) {
+                    const float bp = B[k * 3 + p], bq = B[k * 3 + q];
+                    B[k * 3 + p] = c * bp - s * bq; B[k * 3 + q] = s * bp + c * bq;
+                    const float vp = V[k * 3 + p], vq = V[k * 3 + q];
+                    V[k * 3 + p] = c * vp - s * vq; V[k * 3 + q] = s * vp + c * vq;
+                }
+            }
+        if (off < 1e-7f) break;
+    }
+    float sv[3];
+    for (int j = 0; j < 3; ++j) sv[j] = sqrtf(B[j] * B[j] + B[3 + j] * B[3 + j] + B[6 + j] * B[6 + j]);
+    int ord[3] = {0, 1, 2};
+    for (int a = 0; a < 2; ++a)
+        for (int b = a + 1; b < 3; ++b)
+            if (sv[ord[b]] > sv[ord[a]]) { const int t = ord[a]; ord[a] = ord[b]; ord[b] = t; }
+    float U[9], Vs[9];
+    for (int j = 0; j < 3; ++j)
+        for (int k = 0; k < 3; ++k) {
+            U[k * 3 + j] = sv[ord[j]] > 0.f ? B[k * 3 + ord[j]] / sv[ord[j]] : 0.f;
+            Vs[k * 3 + j] = V[k * 3 + ord[j]];
+        }
+    if (!(sv[ord[2]] > 0.f) && sv[ord[1]] > 0.f) {
+        U[2] = U[3] * U[7] - U[6] * U[4];
+        U[5] = U[6] * U[1] - U[0] * U[7];
+        U[8] = U[0] * U[4] - U[3] * U[1];
+    }
+    for (int pass = 0; pass < 2; ++pass) {
+        for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j)
+                R[i * 3 + j] = U[i * 3] * Vs[j * 3] + U[i * 3 + 1] * Vs[j * 3 + 1] + U[i * 3 + 2] * Vs[j * 3 + 2];
+        if (pass == 1 || !(det3f(R) < 0.f)) break;
+        Vs[2] = -Vs[2]; Vs[5] = -Vs[5]; Vs[8] = -Vs[8];
+    }
+}
+
+/* Camera.cpp:89-98 after R * b1 (FeatureTracker.cpp:366-369) */
+static float rotated_angle(const float R[9], const float b1[3], const float b2[3]) {
+    const float rx = R[0] * b1[0] + R[1] * b1[1] + R[2] * b1[2];
+    const float ry = R[3] * b1[0] + R[4] * b1[1] + R[5] * b1[2];
+    const float rz = R[6] * b1[0] + R[7] * b1[1] + R[8] * b1[2];
+    float c = rx * b2[0] + ry * b2[1] + rz * b2[2];
+    c = fmaxf(-1.0f, fminf(1.0f, c));
+    return acosf(c);
+}
+
+int vf_ransac_rotation(const float* prev_xy, const float* cur_xy, int n, int W, int H,
+                       const int* samples, int iters, float threshold_deg, uint8_t* mask,
+                       int* counts, int* best_iter, float* errs) {
+    if (best_iter) *best_iter = -1;
+    if (n < 3) {                                                   /* :258-261 */
+        for (int i = 0; i < n; ++i) mask[i] = 1;
+        return n;
+    }
+    float* b1 = (float*)malloc(sizeof(float) * 3 * (size_t)n);
+    float* b2 = (float*)malloc(sizeof(float) * 3 * (size_t)n);
+    for (int i = 0; i < n; ++i) {
+        pixel_to_bearing(prev_xy[2 * i], prev_xy[2 * i + 1], W, H, b1 + 3 * i);
+        pixel_to_bearing(cur_xy[2 * i], cur_xy[2 * i + 1], W, H, b2 + 3 * i);
+    }
+    const float thr = (float)((double)threshold_deg * M_PI / 180.0);   /* :305 */
+    int best = 0, bi = -1;
+    float bestR[9] = {0};
+    for (int it = 0; it < iters; ++it) {
+        float Hm[9] = {0};
+        for (int s = 0; s < 3; ++s) {                              /* :335-338: H += b2 b1^T */
+            const float* a = b1 + 3 * samples[3 * it + s];
+            const float* b = b2 + 3 * samples[3 * it + s];
+            for (int i = 0; i < 3; ++i)
+                for (int j = 0; j < 3; ++j) Hm[i * 3 + j] += b[i] * a[j];
+        }
+        float R[9];
+        kabsch_rotation(Hm, R);
+        if (fabsf(det3f(R) - 1.0f) > 0.1f) { if (counts) counts[it] = -1; continue; }   /* :300-302 */
+        int cnt = 0;
+        for (int i = 0; i < n; ++i) cnt += rotated_angle(R, b1 + 3 * i, b2 + 3 * i) < thr;
+        if (counts) counts[it] = cnt;
+        if (cnt > best) { best = cnt; bi = it; memcpy(bestR, R, sizeof(R)); }   /* :314-317 */
+    }
+    if (bi < 0) {
+        for (int i = 0; i < n; ++i) mask[i] = 1;                   /* :321-322 */
+        if (errs) for (int i = 0; i < n; ++i) errs[i] = 0.f;
+    } else {
+        for (int i = 0; i < n; ++i) {
+            const float e = rotated_angle(bestR, b1 + 3 * i, b2 + 3 * i);
+            mask[i] = e < thr;
+            if (errs) errs[i] = e;
+        }
+    }
+    if (best_iter) *best_iter = bi;
+    free(b1); free(b2);
+    return best;
+}

@@ -194,7 +194,22 @@ static void test_fe() {
     EXPECT(worst < 0.05, "position mismatch %.4f", worst);
     std::vector<cv::Point2f> none, out; std::vector<uchar> st2;
     EXPECT(tracker.TrackOpticalFlow(m0, m1, none, out, st2) == 0 && out.empty() && st2.empty(), "empty input must be a no-op");
-    std::printf("  front-end: %d corners, %d tracked, |dxy| %.2e px\n", nref, ntr, worst);
+    // rotation RANSAC through the shim (same mt19937 draw as the reference, fixed seed): the tracked
+    // pairs of a small pure shift are nearly all consistent with one rotation
+    std::vector<cv::Point2f> gp, gc;
+    for (size_t i = 0; i < corners.size(); ++i)
+        if (status[i]) { gp.push_back(corners[i]); gc.push_back(cur[i]); }
+    std::vector<uchar> inl;
+    tracker.SetRansacSeed(1234u);
+    tracker.SetRansacParams(200, 2.0f);
+    const int nin = tracker.RejectOutliersRotationRANSAC(gp, gc, inl);
+    int msum = 0;
+    for (uchar m : inl) msum += m;
+    EXPECT(inl.size() == gp.size() && nin == msum && nin > (int)gp.size() * 8 / 10, "ransac inliers %d of %zu (mask %d)", nin, gp.size(), msum);
+    std::vector<cv::Point2f> two(gp.begin(), gp.begin() + 2), two_c(gc.begin(), gc.begin() + 2);
+    std::vector<uchar> inl2;
+    EXPECT(tracker.RejectOutliersRotationRANSAC(two, two_c, inl2) == 2 && inl2.size() == 2 && inl2[0] == 1 && inl2[1] == 1, "n < 3 keeps everything");
+    std::printf("  front-end: %d corners, %d tracked, |dxy| %.2e px, ransac %d/%zu inliers\n", nref, ntr, worst, nin, gp.size());
 }
 
 int main() {

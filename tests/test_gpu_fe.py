@@ -136,6 +136,34 @@ def test_detect_batch_and_grid_variants(ctx, synthetic, monkeypatch):
             assert len(ref) > 20
 
 
+def test_ransac_rotation_vs_oracle(ctx, synthetic):
+    """rotation RANSAC with an injected sample list.  fp32 trigonometry differs
+    by an ulp between libm and the device, so counts may differ on borderline points; the
+    tolerance is written out: <= 1 % of the points per hypothesis, and mask differences only
+    where the oracle's angular error is within 2e-4 rad of the threshold."""
+    W, H = 3840, 1920
+    ctx.fe_configure(W, H, max_points=8, max_batch=2)
+    for n, iters, thr_deg, seed in ((1000, 200, 1.0, 11), (300, 64, 0.1, 12)):
+        prev, cur, is_out = synthetic.make_rotation_tracks(W, H, n, seed=seed)
+        samples = synthetic.draw_ransac_samples(n, iters, seed=seed + 100)
+        best, mask, counts = ctx.fe_ransac_rotation(prev, cur, samples, thr_deg)
+        obest, omask, ocounts, obi, oerrs = fo.ransac_rotation(prev, cur, W, H, samples, thr_deg)
+        assert np.array_equal(counts < 0, ocounts < 0)
+        assert np.abs(counts - ocounts).max() <= max(2, 0.01 * n)
+        assert abs(best - obest) <= max(2, 0.01 * n) and mask.sum() == best == counts.max()
+        if int(np.argmax(counts)) == obi:
+            thr = np.float32(np.deg2rad(thr_deg))
+            diff = mask != omask
+            assert (np.abs(oerrs[diff] - thr) < 2e-4).all()
+    # batch of two + degenerate inputs (FeatureTracker.cpp:258-261)
+    p1, c1, _ = synthetic.make_rotation_tracks(W, H, 500, seed=21)
+    p2, c2, _ = synthetic.make_rotation_tracks(W, H, 2, seed=22)
+    s1 = synthetic.draw_ransac_samples(500, 50, seed=23)
+    (b1, m1, k1), (b2, m2, k2) = ctx.fe_ransac_rotation_batch([(p1, c1, s1), (p2, c2, np.zeros((50, 3), np.int32))], 1.0)
+    ob1 = fo.ransac_rotation(p1, c1, W, H, s1, 1.0)[0]
+    assert abs(b1 - ob1) <= 5 and b2 == 2 and m2.tolist() == [1, 1]
+
+
 def test_full_size_properties_c2(ctx, synthetic):
     """BASELINE config 2 size: a frame tracked onto itself does not move; status all ones."""
     W, H = 3840, 1920
