@@ -48,7 +48,8 @@ class RansacJob(C.Structure):
 class DetectJob(C.Structure):
     _fields_ = [("img", C.c_void_p), ("pitch", C.c_size_t), ("key", C.c_uint64),
                 ("mask", C.c_void_p), ("mask_pitch", C.c_size_t),
-                ("out_xy", C.c_void_p), ("out_n", C.c_void_p)]
+                ("out_xy", C.c_void_p), ("out_n", C.c_void_p),
+                ("occupied_xy", C.c_void_p), ("n_occupied", C.c_int), ("occupied_radius", C.c_int)]
 
 
 _lib = None
@@ -233,7 +234,7 @@ class Context:
         return out[:n.value].copy()
 
     def fe_detect_batch(self, imgs, masks=None, max_corners=1000, quality=float(np.float32(0.01)),
-                        min_dist=float(np.float32(30.0)), out_cap=None):
+                        min_dist=float(np.float32(30.0)), out_cap=None, occupied=None, occupied_radius=30):
         """One vio360_fe_detect_batch call over independent images (host memory); list of (n, 2) arrays."""
         nb = len(imgs)
         imgs = [np.ascontiguousarray(i, np.uint8) for i in imgs]
@@ -248,6 +249,10 @@ class Context:
             j.mask = masks[b].ctypes.data if masks[b] is not None else None
             j.mask_pitch = masks[b].strides[0] if masks[b] is not None else 0
             j.out_xy, j.out_n = outs[b].ctypes.data, ns.ctypes.data + 4 * b
+            if occupied is not None and occupied[b] is not None and len(occupied[b]):
+                occ = np.ascontiguousarray(occupied[b], np.float32).reshape(-1, 2)
+                imgs.append(occ)   # keep alive
+                j.occupied_xy, j.n_occupied, j.occupied_radius = occ.ctypes.data, occ.shape[0], occupied_radius
         self.check(self.lib.vio360_fe_detect_batch(self.h, jobs, nb, max_corners, quality, min_dist, MEM_HOST))
         return [outs[b][:ns[b]].copy() for b in range(nb)]
 

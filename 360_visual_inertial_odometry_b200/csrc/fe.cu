@@ -47,6 +47,8 @@ struct vio360_fe_state {
     // detection pools
     DevBuf d_djobs, d_eig, d_mask, d_small, d_cand, d_cand_sorted, d_grid, d_cub, d_corners;
     PinBuf h_djobs, h_dout;
+    DevBuf d_occ;
+    PinBuf h_occ;
     // rotation RANSAC pools
     DevBuf d_ransac;
     PinBuf h_ransac;
@@ -63,9 +65,9 @@ void vio360_fe_release(vio360_ctx* ctx) {
     for (auto& sl : s->slots) sl.mem.release();
     DevBuf* db[] = {&s->d_jobs, &s->d_pyrjobs, &s->d_pts_in, &s->d_pts_out, &s->d_status, &s->d_err, &s->d_keep,
                     &s->d_djobs, &s->d_eig, &s->d_mask, &s->d_small, &s->d_cand, &s->d_cand_sorted, &s->d_grid,
-                    &s->d_cub, &s->d_corners, &s->d_ransac};
+                    &s->d_cub, &s->d_corners, &s->d_ransac, &s->d_occ};
     for (DevBuf* b : db) b->release();
-    PinBuf* pb[] = {&s->h_pts_in, &s->h_out, &s->h_djobs, &s->h_dout, &s->h_ransac};
+    PinBuf* pb[] = {&s->h_pts_in, &s->h_out, &s->h_djobs, &s->h_dout, &s->h_ransac, &s->h_occ};
     for (PinBuf* b : pb) b->release();
     for (auto& sg : s->stage) { sg.jobs.release(); sg.pyrjobs.release(); if (sg.ev) cudaEventDestroy(sg.ev); }
     for (auto& d : s->d_jobs_ring) d.release();
@@ -434,6 +436,28 @@ static DetectParams detect_params(const vio360_fe_state* s) {
     return P;
 }
 
+// half-width per row offset of cv::circle(img, c, radius, color, -1): OpenCV's midpoint loop
+// (imgproc/src/drawing.cpp, Circle() with fill) draws rows c.y +- dy over [c.x - dx, c.x + dx] and
+// rows c.y +- dx over [c.x - dy, c.x + dy]
+static DiscTable disc_table(int radius) {
+    DiscTable T;
+    T.radius = radius;
+    for (int i = 0; i <= kMaxDiscRadius; ++i) T.hw[i] = -1;
+    int err = 0, dx = radius, dy = 0, plus = 1, minus = (radius << 1) - 1;
+    while (dx >= dy) {
+        T.hw[dy] = (signed char)std::max<int>(T.hw[dy], dx);
+        T.hw[dx] = (signed char)std::max<int>(T.hw[dx], dy);
+        dy++;
+        err += plus;
+        plus += 2;
+        const int mask = (err <= 0) - 1;
+        err -= minus & mask;
+        dx += mask;
+        minus -= mask & 2;
+    }
+    return T;
+}
+
 static void launch_min_eig(vio360_ctx* ctx, const DetectJobDev* dj, const DetectParams& P, int n_jobs, bool any_mask) {
     const int nwx = (P.W + kEigWarpCols - 1) / kEigWarpCols;
     const dim3 grid((nwx + kEigWarps - 1) / kEigWarps, n_jobs);
@@ -471,9 +495,31 @@ extern "C" int vio360_fe_detect_batch(vio360_ctx* ctx, const vio360_detect_job* 
     }
     VIO_CUDA(ctx, cudaMemsetAsync(s->d_small.p, 0, 16 * (size_t)(n_jobs + 1), st));
     s->batch_tag++;
-    bool any_mask = false;
-    for (int b = 0; b < n_jobs; ++b) any_mask = any_mask || jobs[b].mask;
-    if (any_mask && mem_space == VIO360_MEM_HOST) VIO_CUDA(ctx, s->d_mask.reserve(WH * n_jobs));
+    bool any_mask = false, any_occ = false;
+    int occ_radius = -1, max_occ = 0;
+    size_t occ_floats = 0;
+    for (int b = 0; b < n_jobs; ++b) {
+        const bool occ = jobs[b].occupied_xy && jobs[b].n_occupied > 0;
+        any_mask = any_mask || jobs[b].mask || occ;
+        if (!occ) continue;
+        if (jobs[b].occupied_radius < 0 || jobs[b].occupied_radius > kMaxDiscRadius || (occ_radius >= 0 && occ_radius != jobs[b].occupied_radius))
+            return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_detect_batch: occupied_radius must be one value in [0, %d] per batch", kMaxDiscRadius);
+        occ_radius = jobs[b].occupied_radius;
+        any_occ = true;
+        max_occ = std::max(max_occ, jobs[b].n_occupied);
+        occ_floats += 2 * (size_t)jobs[b].n_occupied;
+    }
+    // a device-side mask per image is needed when the mask comes from the host or discs are drawn into it
+    if (any_mask && (mem_space == VIO360_MEM_HOST || any_occ)) VIO_CUDA(ctx, s->d_mask.reserve(WH * n_jobs));
+    if (any_occ) {
+        VIO_CUDA(ctx, s->d_occ.reserve(occ_floats * 4 + (size_t)n_jobs * 16));
+        VIO_CUDA(ctx, s->h_occ.reserve(occ_floats * 4 + (size_t)n_jobs * 16));
+    }
+    // [pointers n_jobs x 8 | counts n_jobs x 4 | pad | points]
+    const float** h_occ_ptr = s->h_occ.as<const float*>();
+    int* h_occ_n = any_occ ? reinterpret_cast<int*>(h_occ_ptr + n_jobs) : nullptr;
+    float* h_occ_xy = any_occ ? reinterpret_cast<float*>(s->h_occ.as<uint8_t>() + (size_t)n_jobs * 16) : nullptr;
+    float* d_occ_xy = any_occ ? reinterpret_cast<float*>(s->d_occ.as<uint8_t>() + (size_t)n_jobs * 16) : nullptr;
     DetectJobDev* hj = s->h_djobs.as<DetectJobDev>();
     for (int b = 0; b < n_jobs; ++b) {
         const vio360_detect_job& j = jobs[b];
@@ -484,12 +530,25 @@ extern "C" int vio360_fe_detect_batch(vio360_ctx* ctx, const vio360_detect_job* 
         DetectJobDev& d = hj[b];
         d.img = s->slots[idx].p[0]; d.pitch = s->slots[idx].pitch[0];
         d.mask = nullptr; d.mask_pitch = 0;
-        if (j.mask) {
-            if (mem_space == VIO360_MEM_DEVICE) { d.mask = j.mask; d.mask_pitch = (int)j.mask_pitch; }
-            else {
+        const bool occ = j.occupied_xy && j.n_occupied > 0;
+        if (j.mask || occ) {
+            if (mem_space == VIO360_MEM_DEVICE && !occ) { d.mask = j.mask; d.mask_pitch = (int)j.mask_pitch; }
+            else {   // private copy: uploaded, or the caller's device mask / all-valid with discs drawn into it
                 uint8_t* dm = s->d_mask.as<uint8_t>() + WH * b;
-                VIO_CUDA(ctx, cudaMemcpy2DAsync(dm, s->W, j.mask, j.mask_pitch, s->W, s->H, cudaMemcpyHostToDevice, st));
+                if (j.mask) VIO_CUDA(ctx, cudaMemcpy2DAsync(dm, s->W, j.mask, j.mask_pitch, s->W, s->H,
+                                                           mem_space == VIO360_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, st));
+                else VIO_CUDA(ctx, cudaMemsetAsync(dm, 255, WH, st));
                 d.mask = dm; d.mask_pitch = s->W;
+            }
+        }
+        if (any_occ) {
+            h_occ_n[b] = occ ? j.n_occupied : 0;
+            h_occ_ptr[b] = nullptr;
+            if (occ && mem_space == VIO360_MEM_DEVICE) h_occ_ptr[b] = j.occupied_xy;
+            else if (occ) {
+                memcpy(h_occ_xy, j.occupied_xy, (size_t)j.n_occupied * 8);
+                h_occ_ptr[b] = d_occ_xy;
+                h_occ_xy += 2 * (size_t)j.n_occupied; d_occ_xy += 2 * (size_t)j.n_occupied;
             }
         }
         d.eig = s->d_eig.as<float>() + WH * b;
@@ -501,6 +560,14 @@ extern "C" int vio360_fe_detect_batch(vio360_ctx* ctx, const vio360_detect_job* 
     VIO_CUDA(ctx, cudaMemcpyAsync(s->d_djobs.p, hj, sizeof(DetectJobDev) * (size_t)n_jobs, cudaMemcpyHostToDevice, st));
     const DetectJobDev* dj = s->d_djobs.as<DetectJobDev>();
     unsigned int* d_total = s->d_small.as<unsigned int>() + 4 * n_jobs;
+    if (any_occ) {
+        VIO_CUDA(ctx, cudaMemcpyAsync(s->d_occ.p, s->h_occ.p, (size_t)n_jobs * 16 + (mem_space == VIO360_MEM_DEVICE ? 0 : occ_floats * 4), cudaMemcpyHostToDevice, st));
+        const DiscTable T = disc_table(occ_radius);
+        { KernelTimer kt_(ctx, "k_occupancy_discs");
+        k_occupancy_discs<<<dim3(max_occ, n_jobs), 2 * kMaxDiscRadius + 1, 0, st>>>(dj, s->d_occ.as<const float*>(), reinterpret_cast<const int*>(s->d_occ.as<const float*>() + n_jobs), s->W, s->H, T);
+        }
+        VIO_LAUNCH_CHECK(ctx);
+    }
     launch_min_eig(ctx, dj, P, n_jobs, any_mask);
     VIO_LAUNCH_CHECK(ctx);
     // candidates of all images go to one buffer; the count comes back to size the sort.  A batch
@@ -582,6 +649,7 @@ extern "C" int vio360_fe_detect(vio360_ctx* ctx, const uint8_t* img, size_t pitc
                                 int* out_n) {
     vio360_detect_job j;
     j.img = img; j.pitch = pitch; j.key = key; j.mask = mask; j.mask_pitch = mask_pitch; j.out_xy = out_xy; j.out_n = out_n;
+    j.occupied_xy = nullptr; j.n_occupied = 0; j.occupied_radius = 0;
     return vio360_fe_detect_batch(ctx, &j, 1, max_corners, quality, min_dist, VIO360_MEM_HOST);
 }
 

@@ -50,6 +50,24 @@ std::vector<cv::Point2f> FeatureTrackerCuda::DetectNewFeatures(const cv::Mat& im
     return corners;
 }
 
+std::vector<cv::Point2f> FeatureTrackerCuda::DetectNewFeatures(const cv::Mat& image, const std::vector<cv::Point2f>& occupied) {
+    ensure_capacity(1);
+    std::vector<cv::Point2f> corners((size_t)std::max(m_max_features, 1));
+    int n = 0;
+    vio360_detect_job job;
+    job.img = image.data; job.pitch = (size_t)image.step; job.key = m_curr_key;
+    job.mask = nullptr; job.mask_pitch = 0;
+    job.out_xy = reinterpret_cast<float*>(corners.data()); job.out_n = &n;
+    job.occupied_xy = occupied.empty() ? nullptr : reinterpret_cast<const float*>(occupied.data());
+    job.n_occupied = (int)occupied.size();
+    job.occupied_radius = static_cast<int>(m_min_distance);   // FeatureTracker.cpp:398
+    check(vio360_fe_detect_batch(m_ctx, &job, 1, m_max_features, (double)m_quality_level, (double)m_min_distance, VIO360_MEM_HOST),
+          "vio360_fe_detect_batch");
+    corners.resize((size_t)n);
+    m_num_detected = n;
+    return corners;
+}
+
 int FeatureTrackerCuda::TrackOpticalFlow(const cv::Mat& prev_image, const cv::Mat& curr_image,
                                          const std::vector<cv::Point2f>& prev_points,
                                          std::vector<cv::Point2f>& curr_points, std::vector<uchar>& status) {

@@ -40,6 +40,10 @@ public:
 
     // FeatureTracker.cpp:208-226
     std::vector<cv::Point2f> DetectNewFeatures(const cv::Mat& image, const cv::Mat& mask = cv::Mat());
+    // DetectNewFeatures(image, CreateFeatureMask(features)) (FeatureTracker.cpp:177-178, 386-402) without
+    // rasterising and uploading the mask: pass the pixel coordinates of the valid existing features; the
+    // discs cv::circle(mask, pt, int(min_distance), 0, -1) are applied on the device.
+    std::vector<cv::Point2f> DetectNewFeatures(const cv::Mat& image, const std::vector<cv::Point2f>& occupied);
     // FeatureTracker.cpp:228-251
     int TrackOpticalFlow(const cv::Mat& prev_image, const cv::Mat& curr_image,
                          const std::vector<cv::Point2f>& prev_points, std::vector<cv::Point2f>& curr_points,

@@ -105,6 +105,15 @@ typedef struct {
                                                NULL = base mask only                  */
     float* out_xy;   /* max_corners x 2 out, integer coordinates as float           */
     int* out_n;      /* out: corners found                                          */
+    /* Instead of rasterising and uploading the occupancy mask, a job may pass the positions
+     * of the existing valid features (n_occupied x 2 floats, same memory space as the image)
+     * and the disc radius static_cast<int>(m_min_distance), in [0, 64]: the device zeroes the
+     * pixels cv::circle(mask, pt, radius, 0, -1) would (FeatureTracker.cpp:397-398; centre
+     * rounded as cv::Point(pt), OpenCV's midpoint-circle fill) on top of `mask`, or of an
+     * all-valid mask when mask is NULL.  NULL = no discs.                              */
+    const float* occupied_xy;
+    int n_occupied;
+    int occupied_radius;
 } vio360_detect_job;
 
 /* Replaces FeatureTracker::DetectNewFeatures (src/processing/FeatureTracker.cpp:208-226,

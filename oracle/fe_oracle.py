@@ -115,6 +115,17 @@ def post_filter(xy, status, w, h, polar_thr=0.15, margin=20.0):
     return keep
 
 
+def feature_mask(mask, pts, radius):
+    """FeatureTracker::CreateFeatureMask: filled cv::circle discs zeroed in a copy of `mask`."""
+    out = np.ascontiguousarray(mask, np.uint8).copy()
+    pts = np.ascontiguousarray(pts, np.float32).reshape(-1, 2)
+    h, w = out.shape
+    f = lib().vf_feature_mask
+    f.restype = None
+    f(_p(out, C.c_ubyte), w, h, _p(pts, C.c_float), pts.shape[0], int(radius))
+    return out
+
+
 def ransac_rotation(prev_xy, cur_xy, w, h, samples, threshold_deg):
     """FeatureTracker::RejectOutliersRotationRANSAC with an injected sample list (iters x 3).
     returns (best_inliers, mask, counts, best_iter, errs)."""

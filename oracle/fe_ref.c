@@ -452,6 +452,34 @@ void vf_post_filter(const float* xy, const uint8_t* status, int n, int w, int h,
     }
 }
 
+/* ------------------------------------------------------------------ occupancy mask */
+static void hline0(uint8_t* mask, int w, int h, int y, int x0, int x1) {
+    if (y < 0 || y >= h) return;
+    if (x0 < 0) x0 = 0;
+    if (x1 > w - 1) x1 = w - 1;
+    for (int x = x0; x <= x1; ++x) mask[(size_t)y * w + x] = 0;
+}
+
+void vf_feature_mask(uint8_t* mask, int w, int h, const float* pts, int n, int radius) {
+    for (int i = 0; i < n; ++i) {
+        const int cx = (int)lrintf(pts[2 * i]), cy = (int)lrintf(pts[2 * i + 1]);   /* cvRound */
+        int err = 0, dx = radius, dy = 0, plus = 1, minus = (radius << 1) - 1;
+        while (dx >= dy) {
+            hline0(mask, w, h, cy - dy, cx - dx, cx + dx);
+            hline0(mask, w, h, cy + dy, cx - dx, cx + dx);
+            hline0(mask, w, h, cy - dx, cx - dy, cx + dy);
+            hline0(mask, w, h, cy + dx, cx - dy, cx + dy);
+            dy++;
+            err += plus;
+            plus += 2;
+            const int m = (err <= 0) - 1;
+            err -= minus & m;
+            dx += m;
+            minus -= m & 2;
+        }
+    }
+}
+
 /* ------------------------------------------------------------------ rotation RANSAC */
 #ifndef M_PI
 #define M_PI 3.14159265358979323846   /* -std=c11 hides the POSIX constant */

@@ -136,6 +136,29 @@ def test_detect_batch_and_grid_variants(ctx, synthetic, monkeypatch):
             assert len(ref) > 20
 
 
+def test_detect_with_occupied_features(ctx, synthetic):
+    """the occupancy mask of CreateFeatureMask (FeatureTracker.cpp:386-402) built on
+    the device from the feature positions equals detection with the rasterised cv::circle mask."""
+    W, H = 960, 480
+    f0 = synthetic.render_erp_frame(W, H, 0, seed=31, n_waves=48, sigma_omega=40.0)
+    f1 = synthetic.render_erp_frame(W, H, 1, seed=32, n_waves=48, sigma_omega=40.0)
+    ctx.fe_configure(W, H, max_points=8, max_batch=2)
+    base = fo.base_mask(W, H)
+    first = fo.good_features(f0, base, 120)
+    occ_pts = first[::2] + np.float32(0.5)              # half-integer centres round to even
+    occ_pts = np.concatenate([occ_pts, np.array([[3.0, 100.0], [W - 2.0, 300.0]], np.float32)])   # clipped discs
+    for r in (30, 7):
+        mask = fo.feature_mask(base, occ_pts, r)
+        ref0 = fo.good_features(f0, mask, 200)
+        ref1 = fo.good_features(f1, base, 200)
+        got = ctx.fe_detect_batch([f0, f1], None, 200, occupied=[occ_pts, None], occupied_radius=r)
+        assert np.array_equal(got[0], ref0) and np.array_equal(got[1], ref1) and len(ref0) > 20
+        # an explicit mask and discs together: discs are drawn on top of the caller's mask
+        extra = base.copy(); extra[:, 400:520] = 0
+        got = ctx.fe_detect_batch([f0], [extra], 200, occupied=[occ_pts], occupied_radius=r)
+        assert np.array_equal(got[0], fo.good_features(f0, fo.feature_mask(extra, occ_pts, r), 200))
+
+
 def test_ransac_rotation_vs_oracle(ctx, synthetic):
     """rotation RANSAC with an injected sample list.  fp32 trigonometry differs
     by an ulp between libm and the device, so counts may differ on borderline points; the

@@ -98,3 +98,19 @@ def test_gftt_vs_cv2_live(synthetic, size, seed):
     a = fo.cv2_good_features(f0, mask)
     b = fo.good_features(f0, mask)
     assert np.array_equal(a, b) and len(a) > 50
+
+
+def test_feature_mask_matches_cv2_circle():
+    """CreateFeatureMask (FeatureTracker.cpp:386-402): the restated midpoint-circle fill equals
+    cv2.circle(mask, (cvRound(x), cvRound(y)), r, 0, -1) including clipped and half-integer centres."""
+    cv2 = pytest.importorskip("cv2")
+    w, h = 321, 200
+    rng = np.random.default_rng(9)
+    pts = np.concatenate([rng.uniform(-20, [w + 20, h + 20], (60, 2)),
+                          np.array([[0.5, 0.5], [1.5, 2.5], [w - 1, h - 1], [10.5, 20.5], [160.49, 99.51]])]).astype(np.float32)
+    for r in (0, 1, 2, 7, 30, 64):
+        ref = np.full((h, w), 255, np.uint8)
+        for x, y in pts:
+            cv2.circle(ref, (int(np.rint(x)), int(np.rint(y))), r, 0, -1)
+        got = fo.feature_mask(np.full((h, w), 255, np.uint8), pts, r)
+        assert np.array_equal(got, ref), r
