@@ -575,8 +575,12 @@ extern "C" int vio360_fe_detect_batch(vio360_ctx* ctx, const vio360_detect_job* 
     unsigned int total = 0;
     for (;;) {
         { KernelTimer kt_(ctx, "k_candidates");
-        k_candidates<<<dim3((s->W - 2 + kCandTX - 1) / kCandTX, (s->H - 2 + kCandTY - 1) / kCandTY, n_jobs), kCandTX, 0, st>>>(
-            dj, P, quality, s->d_cand.as<unsigned long long>(), d_total);
+        if ((s->W & 3) == 0)
+            k_candidates4<<<dim3((s->W / 4 + kCand4Threads - 1) / kCand4Threads, (s->H - 2 + kCandTY - 1) / kCandTY, n_jobs), kCand4Threads, 0, st>>>(
+                dj, P, quality, s->d_cand.as<unsigned long long>(), d_total);
+        else
+            k_candidates<<<dim3((s->W - 2 + kCandTX - 1) / kCandTX, (s->H - 2 + kCandTY - 1) / kCandTY, n_jobs), kCandTX, 0, st>>>(
+                dj, P, quality, s->d_cand.as<unsigned long long>(), d_total);
         }
         VIO_LAUNCH_CHECK(ctx);
         VIO_CUDA(ctx, cudaMemcpyAsync(s->h_dout.p, d_total, 4, cudaMemcpyDeviceToHost, st));
