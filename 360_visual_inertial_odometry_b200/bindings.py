@@ -25,7 +25,7 @@ EXPORTS = [
     "vio360_ba_set_shard", "vio360_ba_set_parameters", "vio360_ba_evaluate",
     "vio360_ba_get_residuals_jacobians", "vio360_ba_normal_blocks", "vio360_ba_reduced_dim",
     "vio360_ba_build_reduced_system", "vio360_ba_set_lm_diagonal", "vio360_ba_reduced_system_dev", "vio360_ba_fetch_reduced_system",
-    "vio360_ba_column_sqnorm", "vio360_ba_chi2", "vio360_pnp_evaluate",
+    "vio360_ba_column_sqnorm", "vio360_ba_chi2", "vio360_ba_solve_reduced", "vio360_pnp_evaluate",
 ]
 
 
@@ -413,6 +413,12 @@ class BAWindow:
         S = np.zeros((n, n)); rhs = np.zeros(n); cost = C.c_double(0)
         self.ctx.check(self.lib.vio360_ba_fetch_reduced_system(self.h, _ptr(S), _ptr(rhs), C.byref(cost)))
         return S, rhs, cost.value
+
+    def solve_reduced(self, want_points=True):
+        """x of S x = rhs (K x 6, zeros for constant poses) and the back-substituted landmark step (M x 3)."""
+        dp = np.zeros((self.K, 6)); dl = np.zeros((self.M, 3)) if want_points else None
+        self.ctx.check(self.lib.vio360_ba_solve_reduced(self.h, _ptr(dp), _ptr(dl)))
+        return dp, dl
 
     def column_sqnorm(self, apply_loss=True):
         out = np.zeros(6 * self.K + 3 * self.M)

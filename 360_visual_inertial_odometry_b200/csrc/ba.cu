@@ -40,7 +40,9 @@ struct vio360_ba {
     vio360_ctx* ctx = nullptr;
     int K = 0, M = 0, O = 0;
     bool has_structure = false, has_params = false, has_eval = false, has_eval_jac = false;
-    bool has_reduced = false;
+    bool has_reduced = false, reduced_apply_loss = false, solve_dirty = true, chol_attr_set = false;
+    DevBuf d_chol, d_linv, d_x, d_dl, d_reachF;
+    PinBuf h_solve;
     int n_free = 0;
     int shard_rank = 0, shard_world = 1, lm_begin = 0, lm_end = 0;
     std::vector<int> lm_ptr, perm, free_map;
@@ -110,6 +112,7 @@ __global__ void k_sum_partials(const double* __restrict__ partials, int n, doubl
 }
 
 #include "ba_schur_kernels.cuh"
+#include "ba_solve.cuh"
 
 template <bool WANT_JAC>
 __global__ void __launch_bounds__(128) k_evaluate(BaDev d, bool apply_loss, double* __restrict__ r_out,
@@ -452,9 +455,11 @@ extern "C" void vio360_ba_destroy(vio360_ba* ba) {
                       &ba->d_pose_ptr, &ba->d_pose_order, &ba->d_Twb, &ba->d_Tcb, &ba->d_posebuf, &ba->d_pose_delta,
                       &ba->d_points, &ba->d_free_map, &ba->d_point_fixed, &ba->d_D, &ba->d_r, &ba->d_Jp, &ba->d_Jl,
                       &ba->d_partials, &ba->d_packed, &ba->d_blocks, &ba->d_chi2, &ba->d_flag,
-                      &ba->d_chunks, &ba->d_cov_ptr, &ba->d_cov_idx, &ba->d_free_pose, &ba->d_irregular, &ba->d_partS, &ba->d_partRhs, &ba->d_reach, &ba->d_slots, &ba->d_batch_rng};
+                      &ba->d_chunks, &ba->d_cov_ptr, &ba->d_cov_idx, &ba->d_free_pose, &ba->d_irregular, &ba->d_partS, &ba->d_partRhs, &ba->d_reach, &ba->d_slots, &ba->d_batch_rng,
+                      &ba->d_chol, &ba->d_linv, &ba->d_x, &ba->d_dl, &ba->d_reachF};
     for (DevBuf* b : bufs) b->release();
     ba->pin.release();
+    ba->h_solve.release();
     delete ba;
 }
 
@@ -636,7 +641,7 @@ extern "C" int vio360_ba_set_structure(vio360_ba* ba, const int32_t* pose_idx, c
     VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_free_map.p, ba->free_map.data(), (size_t)K * 4, cudaMemcpyHostToDevice, st));
     VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_point_fixed.p, ba->point_fixed.data(), (size_t)M, cudaMemcpyHostToDevice, st));
     VIO_CUDA(ctx, cudaStreamSynchronize(st));   // host vectors above go out of scope
-    ba->has_structure = true; ba->has_params = false; ba->has_eval = false; ba->has_reduced = false;
+    ba->has_structure = true; ba->has_params = false; ba->has_eval = false; ba->has_reduced = false; ba->solve_dirty = true;
     return VIO360_OK;
 }
 
@@ -887,7 +892,7 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
             VIO_LAUNCH_CHECK(ctx);
         }
         if (fused) {
-            ba->has_reduced = true;
+            ba->has_reduced = true; ba->reduced_apply_loss = apply_loss != 0;
             if (S || rhs || cost) return vio360_ba_fetch_reduced_system(ba, S, rhs, cost);
             return VIO360_OK;   // asynchronous on the context's stream
         }
@@ -916,7 +921,7 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
         }
         VIO_LAUNCH_CHECK(ctx);
     }
-    ba->has_reduced = true;
+    ba->has_reduced = true; ba->reduced_apply_loss = apply_loss != 0;
     if (S || rhs || cost) return vio360_ba_fetch_reduced_system(ba, S, rhs, cost);
     return VIO360_OK;   // asynchronous on the context's stream
 }
@@ -1085,5 +1090,86 @@ extern "C" int vio360_pnp_evaluate(vio360_ctx* ctx, int N, const double* obs_uv,
     }
     if (b) for (int a = 0; a < 6; ++a) b[a] = h28[21 + a];
     if (cost) *cost = h28[27];
+    return VIO360_OK;
+}
+
+// ---- solve the reduced system and back-substitute on the device ----
+extern "C" int vio360_ba_solve_reduced(vio360_ba* ba, double* delta_pose, double* delta_point) {
+    if (!ba) return VIO360_ERR_INVALID;
+    vio360_ctx* ctx = ba->ctx;
+    if (!ba->has_reduced) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_solve_reduced before ba_build_reduced_system");
+    if (!delta_pose) return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_solve_reduced: delta_pose is required");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const int nb = ba->n_free, K = ba->K, M = ba->M;
+    const size_t n = 6 * (size_t)nb;
+    const size_t panel_bytes = n > 6 ? (n - 6) * 6 * sizeof(double) : 0;
+    if (panel_bytes > (size_t)200 * 1024) return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_solve_reduced: %d free poses exceed the single-CTA solver (max 711)", nb);
+    VIO_CUDA(ctx, ba->h_solve.reserve((n + 3 * (size_t)M + 8) * 8));
+    double* hx = ba->h_solve.as<double>();
+    if (nb > 0) {
+        if (ba->solve_dirty) {
+            // envelope of S in free-pose index space: pose p shares a landmark with poses up to reach[p]
+            // (union over ALL landmarks, so it also covers the all-reduced system of a sharded window)
+            std::vector<int> rp(K);
+            for (int p = 0; p < K; ++p) rp[p] = p;
+            for (int l = 0; l < M; ++l) {
+                int pmax = -1;
+                for (int q = ba->lm_ptr[l]; q < ba->lm_ptr[l + 1]; ++q) pmax = std::max(pmax, ba->h_pose[q]);
+                for (int q = ba->lm_ptr[l]; q < ba->lm_ptr[l + 1]; ++q) rp[ba->h_pose[q]] = std::max(rp[ba->h_pose[q]], pmax);
+            }
+            std::vector<int> upto(K);   // number of free poses with index <= p
+            int cnt = 0;
+            for (int p = 0; p < K; ++p) { if (ba->free_map[p] >= 0) ++cnt; upto[p] = cnt; }
+            std::vector<int> reachF(nb);
+            int run = 0;
+            for (int p = 0; p < K; ++p) {
+                const int a = ba->free_map[p];
+                if (a < 0) continue;
+                run = std::max(run, std::max(a, upto[rp[p]] - 1));   // monotone: the factor's fill stays inside
+                reachF[a] = run;
+            }
+            VIO_CUDA(ctx, ba->d_reachF.reserve((size_t)nb * 4));
+            VIO_CUDA(ctx, cudaMemcpy(ba->d_reachF.p, reachF.data(), (size_t)nb * 4, cudaMemcpyHostToDevice));
+            ba->solve_dirty = false;
+        }
+        VIO_CUDA(ctx, ba->d_chol.reserve(n * n * 8));
+        VIO_CUDA(ctx, ba->d_linv.reserve((size_t)nb * 36 * 8));
+        VIO_CUDA(ctx, ba->d_x.reserve(n * 8 + 16));
+        const double* dS = ba->d_packed.as<double>();
+        VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_chol.p, dS, n * n * 8, cudaMemcpyDeviceToDevice, st));
+        VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_x.p, dS + n * n, n * 8, cudaMemcpyDeviceToDevice, st));
+        if (!ba->chol_attr_set) {
+            VIO_CUDA(ctx, cudaFuncSetAttribute(k_chol_skyline, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            ba->chol_attr_set = true;
+        }
+        int* d_status = reinterpret_cast<int*>(ba->d_x.as<double>() + n);
+        { KernelTimer kt_(ctx, "k_chol_skyline");
+        k_chol_skyline<<<1, kCholThreads, panel_bytes, st>>>(ba->d_chol.as<double>(), nb, ba->d_reachF.as<int>(), ba->d_linv.as<double>(),
+                                                            ba->d_x.as<double>(), d_status);
+        }
+        VIO_LAUNCH_CHECK(ctx);
+        VIO_CUDA(ctx, cudaMemcpyAsync(hx, ba->d_x.p, n * 8 + 8, cudaMemcpyDeviceToHost, st));
+    }
+    if (delta_point && M > 0) {
+        VIO_CUDA(ctx, ba->d_dl.reserve(3 * (size_t)M * 8));
+        VIO_CUDA(ctx, cudaMemsetAsync(ba->d_dl.p, 0, 3 * (size_t)M * 8, st));
+        const int nl = ba->lm_end - ba->lm_begin;
+        if (nl > 0) {
+            BaDev d = make_dev(ba);
+            KernelTimer kt_(ctx, "k_back_substitute");
+            k_back_substitute<<<(nl + 3) / 4, 128, 0, st>>>(d, ba->lm_begin, ba->lm_end, ba->reduced_apply_loss, ba->d_x.as<double>(), ba->d_dl.as<double>());
+        }
+        VIO_LAUNCH_CHECK(ctx);
+        VIO_CUDA(ctx, cudaMemcpyAsync(hx + n + 1, ba->d_dl.p, 3 * (size_t)M * 8, cudaMemcpyDeviceToHost, st));
+    }
+    VIO_CUDA(ctx, cudaStreamSynchronize(st));
+    if (nb > 0 && *reinterpret_cast<const int*>(hx + n) != 0)
+        return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_solve_reduced: the reduced system is not positive definite");
+    for (int p = 0; p < K; ++p) {
+        const int a = ba->free_map[p];
+        for (int k = 0; k < 6; ++k) delta_pose[6 * (size_t)p + k] = a >= 0 ? hx[6 * (size_t)a + k] : 0.0;
+    }
+    if (delta_point && M > 0) memcpy(delta_point, hx + n + 1, 3 * (size_t)M * 8);
     return VIO360_OK;
 }

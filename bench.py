@@ -387,6 +387,18 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
                "cost": cost, "S_trace": float(np.trace(S))}
         if out["roofline"]["achieved"]:
             out["roofline"]["frac"] = out["roofline"]["achieved"] / fp64_peak
+        if not sharded:
+            # reduced-system solve + landmark back substitution on the device
+            ba.solve_reduced(True)
+            ctx.enable_kernel_timing(True); ctx.reset_kernel_times()
+            t0 = time.perf_counter()
+            for _ in range(3):
+                ba.solve_reduced(True)
+            solve_s = (time.perf_counter() - t0) / 3
+            out["solve"] = {"ms_per_call_host_clock": solve_s * 1e3,
+                            "kernel_ms_per_launch": {k: ctx.kernel_time(k)[0] / max(ctx.kernel_time(k)[1], 1)
+                                                     for k in ("k_chol_skyline", "k_back_substitute")}}
+            ctx.enable_kernel_timing(False)
         ba.close()
         return out
 

@@ -228,6 +228,17 @@ int vio360_ba_fetch_reduced_system(vio360_ba* ba, double* S, double* rhs, double
 /* diag(J^T J) per parameter (6K + 3M), the input of the LM diagonal. */
 int vio360_ba_column_sqnorm(vio360_ba* ba, int apply_loss, double* out);
 
+/* consume the reduced system on the device.  Solves S x = rhs of the last
+ * vio360_ba_build_reduced_system by a block-envelope Cholesky (replaces the dense LLT of Ceres'
+ * DenseSchurComplementSolver::SolveReducedLinearSystem, schur_complement_solver.cc) and
+ * back-substitutes the landmarks, y_l = (E'E + D^2)^-1 (E'r - E'F x)
+ * (SchurEliminator::BackSubstitute, schur_eliminator_impl.h:310-380).  delta_pose is K x 6
+ * (zeros for constant poses), delta_point M x 3 or NULL (zeros for constant points and for
+ * landmarks outside this rank's shard).  Sign convention: exactly the x, y of S x = rhs as
+ * Ceres forms them (the caller negates as LevenbergMarquardtStrategy::ComputeStep does).
+ * With shards, all-reduce the packed system first; every rank then holds the same x.     */
+int vio360_ba_solve_reduced(vio360_ba* ba, double* delta_pose, double* delta_point);
+
 /* Replaces the per-factor BAFactor::compute_chi_square loop (Factors.cpp:544-612;
  * Optimizer.cpp:898-915): chi2 O (may be NULL), flag O = chi2 > thr (may be NULL).   */
 int vio360_ba_chi2(vio360_ba* ba, double thr, double* chi2, uint8_t* flag);

@@ -118,6 +118,35 @@ class Window:
                                  fm.ctypes.data_as(_ip))
         return S, rhs, fm
 
+    def solve_step(self, r, Jp, Jl, D, S, rhs, fm):
+        """Reduced-system solve + back substitution as Ceres does after Eliminate:
+        x = S^-1 rhs (DenseSchurComplementSolver::SolveReducedLinearSystem, schur_complement_solver.cc;
+        LAPACK here instead of Eigen LLT), then per landmark
+        y = (E'E + D^2)^-1 (E'r - E'F x)  (SchurEliminator::BackSubstitute, schur_eliminator_impl.h:310-380).
+        r/Jp/Jl are the loss-corrected rows; constant poses/points get zeros.  returns (dp K x 6, dl M x 3)."""
+        K, M, O = self.c.K, self.c.M, self.c.O
+        x = np.linalg.solve(S, rhs) if S.size else np.zeros(0)
+        dp = np.zeros((K, 6))
+        for p in range(K):
+            if fm[p] >= 0:
+                dp[p] = x[6 * fm[p]:6 * fm[p] + 6]
+        pose_idx = np.ctypeslib.as_array(self.c.pose_idx, (O,)); point_idx = np.ctypeslib.as_array(self.c.point_idx, (O,))
+        r = np.asarray(r).reshape(O, 2); Jp = np.asarray(Jp).reshape(O, 2, 6); Jl = np.asarray(Jl).reshape(O, 2, 3)
+        s = r - np.einsum("oij,oj->oi", Jp, dp[pose_idx])          # F x is zero for constant poses (dp = 0)
+        EtE = np.zeros((M, 3, 3)); g = np.zeros((M, 3))
+        np.add.at(EtE, point_idx, np.einsum("oki,okj->oij", Jl, Jl))
+        np.add.at(g, point_idx, np.einsum("oki,ok->oi", Jl, s))
+        dl = np.zeros((M, 3))
+        pf = self.keep["point_fixed"]
+        Dl = np.zeros((M, 3)) if D is None else np.asarray(D)[6 * K:].reshape(M, 3)
+        for l in range(M):
+            if pf is not None and pf[l]:
+                continue
+            A = EtE[l] + np.diag(Dl[l] ** 2)
+            if np.linalg.matrix_rank(A) == 3:
+                dl[l] = np.linalg.solve(A, g[l])
+        return dp, dl
+
     def lm_diagonal(self, Jp, Jl, radius=1e4):
         D = np.empty(6 * self.c.K + 3 * self.c.M)
         lib().vo_lm_diagonal(C.byref(self.c), _d(Jp), _d(Jl), C.c_double(radius), _d(D))

@@ -56,6 +56,29 @@ def _check_window(bindings, ctx, win, ref=None):
     return S, rhs
 
 
+def test_solve_reduced_and_back_substitution(bindings, ctx, synthetic):
+    """block-envelope Cholesky of S on the device + landmark back substitution
+    against LAPACK / numpy on the oracle's system.  A different factorisation order than Eigen's LLT,
+    so the tolerance is 1e-7 relative (cond(S) ~ 1e6 with the LM diagonal), written here."""
+    for win in (synthetic.make_ba_window(K=10, M=300, seed=20001),
+                synthetic.make_ba_window(K=40, M=1500, degree=8, seed=20002)):
+        W = ba_oracle.Window(win)
+        r, Jp, Jl, _ = W.evaluate(win["pose_delta"], win["points"])
+        D = W.lm_diagonal(Jp, Jl, 1e4)
+        S, rhs, fm = W.schur(r, Jp, Jl, D)
+        dp_ref, dl_ref = W.solve_step(r, Jp, Jl, D, S, rhs, fm)
+        ba = bindings.BAWindow(ctx, win)
+        ba.set_parameters(win["pose_delta"], win["points"])
+        ba.build_reduced_system(D, True, fetch=False)
+        dp, dl = ba.solve_reduced(True)
+        assert rel_err(dp, dp_ref) < 1e-7 and rel_err(dl, dl_ref) < 1e-7
+        assert not dp[win["pose_fixed"] != 0].any() and not dl[win["point_fixed"] != 0].any()
+        # the step reduces the linearised cost: |r - J d|^2 + |D d|^2 < |r|^2
+        dp2, _ = ba.solve_reduced(False)
+        assert np.array_equal(dp, dp2)
+        ba.close()
+
+
 def test_golden_window(bindings, ctx):
     g = np.load(GOLD)
     K, M, O, cols, rows, huber = g["scalars"]
