@@ -1103,8 +1103,8 @@ extern "C" int vio360_ba_solve_reduced(vio360_ba* ba, double* delta_pose, double
     cudaStream_t st = ctx->stream;
     const int nb = ba->n_free, K = ba->K, M = ba->M;
     const size_t n = 6 * (size_t)nb;
-    const size_t panel_bytes = n > 6 ? (n - 6) * 6 * sizeof(double) : 0;
-    if (panel_bytes > (size_t)200 * 1024) return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_solve_reduced: %d free poses exceed the single-CTA solver (max 711)", nb);
+    const size_t panel_bytes = n * 6 * sizeof(double);   // rows below the diagonal block + the rhs row
+    if (panel_bytes > (size_t)200 * 1024) return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_solve_reduced: %d free poses exceed the single-CTA solver (max 710)", nb);
     VIO_CUDA(ctx, ba->h_solve.reserve((n + 3 * (size_t)M + 8) * 8));
     double* hx = ba->h_solve.as<double>();
     if (nb > 0) {

@@ -17,28 +17,37 @@ namespace vio360 {
 
 constexpr int kCholThreads = 1024;
 
-// lower Cholesky of the 6x6 A (row-major, lower part read) and the inverse of the factor
+// lower Cholesky of the 6x6 A (row-major, lower part read) and the inverse of the factor;
+// division free: reciprocal square roots of the pivots
 __device__ __forceinline__ bool chol6_inv(const double* A, double* L, double* Li) {
     bool ok = true;
+    double inv[6];
 #pragma unroll
     for (int i = 0; i < 36; ++i) { L[i] = 0.0; Li[i] = 0.0; }
+#pragma unroll
     for (int j = 0; j < 6; ++j) {
         double d = A[j * 6 + j];
+#pragma unroll
         for (int k = 0; k < j; ++k) d -= L[j * 6 + k] * L[j * 6 + k];
         if (!(d > 0.0)) { ok = false; d = 1.0; }
-        const double ljj = sqrt(d);
-        L[j * 6 + j] = ljj;
+        inv[j] = vio_rsqrt(d);
+        L[j * 6 + j] = d * inv[j];
+#pragma unroll
         for (int i = j + 1; i < 6; ++i) {
             double s = A[i * 6 + j];
+#pragma unroll
             for (int k = 0; k < j; ++k) s -= L[i * 6 + k] * L[j * 6 + k];
-            L[i * 6 + j] = s / ljj;
+            L[i * 6 + j] = s * inv[j];
         }
     }
+#pragma unroll
     for (int c = 0; c < 6; ++c) {   // L * Li = I, column by column (forward substitution)
+#pragma unroll
         for (int i = c; i < 6; ++i) {
             double s = (i == c) ? 1.0 : 0.0;
+#pragma unroll
             for (int k = c; k < i; ++k) s -= L[i * 6 + k] * Li[k * 6 + c];
-            Li[i * 6 + c] = s / L[i * 6 + i];
+            Li[i * 6 + c] = s * inv[i];
         }
     }
     return ok;
@@ -46,17 +55,20 @@ __device__ __forceinline__ bool chol6_inv(const double* A, double* L, double* Li
 
 // A: n x n row-major work copy of S (lower triangle used and overwritten by the factor);
 // Linv: nb x 36 scratch; b: rhs in, solution out; status[0] = 0 ok / 1 not positive definite.
+// The right-hand side rides along as one more row below the matrix (row index n of the
+// augmented lower triangle), so the forward substitution happens inside the factorisation.
 __global__ void __launch_bounds__(kCholThreads) k_chol_skyline(double* __restrict__ A, int nb, const int* __restrict__ reach,
                                                                double* __restrict__ Linv, double* __restrict__ b, int* __restrict__ status) {
-    extern __shared__ double panel[];   // [(rows below the diagonal block) x 6] of the current column
+    extern __shared__ double panel[];   // [(rows below the diagonal block, + the rhs row) x 6] of the current column
     __shared__ double sD[36], sL[36], sLi[36], sy[6];
     __shared__ int sbad;
     const int tid = threadIdx.x, n = 6 * nb;
     if (tid == 0) sbad = 0;
     __syncthreads();
-    // ---- factorisation
+    // ---- factorisation (+ forward substitution of the rhs row)
     for (int j = 0; j < nb; ++j) {
         const int rj = reach[j], r = rj - j;   // block rows j+1 .. rj are inside the envelope
+        const int rows = 6 * r;
         if (tid < 36) sD[tid] = A[(size_t)(6 * j + tid / 6) * n + 6 * j + tid % 6];
         __syncthreads();
         if (tid == 0) { if (!chol6_inv(sD, sL, sLi)) sbad = 1; }
@@ -65,9 +77,9 @@ __global__ void __launch_bounds__(kCholThreads) k_chol_skyline(double* __restric
             A[(size_t)(6 * j + tid / 6) * n + 6 * j + tid % 6] = sL[tid];
             Linv[(size_t)j * 36 + tid] = sLi[tid];
         }
-        // L_ij = A_ij Ljj^-T, one thread per row of the column panel
-        for (int row = tid; row < 6 * r; row += kCholThreads) {
-            double* a = A + (size_t)(6 * (j + 1) + row) * n + 6 * j;
+        // L_ij = A_ij Ljj^-T, one thread per row of the column panel; row `rows` is the rhs: y_j = Ljj^-1 b_j
+        for (int row = tid; row <= rows; row += kCholThreads) {
+            double* a = row < rows ? A + (size_t)(6 * (j + 1) + row) * n + 6 * j : b + 6 * j;
             double v[6], o[6];
 #pragma unroll
             for (int k = 0; k < 6; ++k) v[k] = a[k];
@@ -82,36 +94,17 @@ __global__ void __launch_bounds__(kCholThreads) k_chol_skyline(double* __restric
             for (int c = 0; c < 6; ++c) { a[c] = o[c]; panel[row * 6 + c] = o[c]; }
         }
         __syncthreads();
-        // trailing update inside the envelope: A_ik -= L_ij L_kj^T for j < k <= i <= rj
-        const int rows = 6 * r;
-        for (int e = tid; e < rows * rows; e += kCholThreads) {
-            const int ri = e / rows, ck = e - ri * rows;
-            if (ck / 6 > ri / 6) continue;   // block upper part
-            const double* li = panel + ri * 6;
+        // trailing update inside the envelope: A_ik -= L_ij L_kj^T for j < k <= i <= rj, and the rhs row
+        for (int ck = tid & 127; ck < rows; ck += 128) {
             const double* lk = panel + ck * 6;
-            double s = 0.0;
-#pragma unroll
-            for (int q = 0; q < 6; ++q) s += li[q] * lk[q];
-            A[(size_t)(6 * (j + 1) + ri) * n + 6 * (j + 1) + ck] -= s;
-        }
-        __syncthreads();
-    }
-    // ---- forward substitution L y = b (column oriented)
-    for (int j = 0; j < nb; ++j) {
-        const int r = reach[j] - j;
-        if (tid < 6) {
-            double s = 0.0;
-            for (int k = 0; k <= tid; ++k) s += Linv[(size_t)j * 36 + tid * 6 + k] * b[6 * j + k];
-            sy[tid] = s;
-        }
-        __syncthreads();
-        if (tid < 6) b[6 * j + tid] = sy[tid];
-        for (int row = tid; row < 6 * r; row += kCholThreads) {
-            const double* a = A + (size_t)(6 * (j + 1) + row) * n + 6 * j;
-            double s = 0.0;
-#pragma unroll
-            for (int k = 0; k < 6; ++k) s += a[k] * sy[k];
-            b[6 * (j + 1) + row] -= s;
+            const double k0 = lk[0], k1 = lk[1], k2 = lk[2], k3 = lk[3], k4 = lk[4], k5 = lk[5];
+            const int first = (ck / 6) * 6;   // block lower part: rows of block ck/6 and below
+            for (int ri = first + (tid >> 7); ri <= rows; ri += kCholThreads / 128) {
+                const double* li = panel + ri * 6;
+                const double s = li[0] * k0 + li[1] * k1 + li[2] * k2 + li[3] * k3 + li[4] * k4 + li[5] * k5;
+                if (ri < rows) A[(size_t)(6 * (j + 1) + ri) * n + 6 * (j + 1) + ck] -= s;
+                else b[6 * (j + 1) + ck] -= s;
+            }
         }
         __syncthreads();
     }
@@ -138,11 +131,14 @@ __global__ void __launch_bounds__(kCholThreads) k_chol_skyline(double* __restric
                 for (int k = tid; k < 6; ++k) x += Linv[(size_t)j * 36 + k * 6 + tid] * s[k];
                 sy[tid] = x;
             }
+            __syncwarp();
+            if (tid < 6) b[6 * j + tid] = sy[tid];
+            __threadfence_block();
+            __syncwarp();
         }
-        __syncthreads();
-        if (tid < 6) b[6 * j + tid] = sy[tid];
-        __syncthreads();
+        // only warp 0 works in this phase; the other warps wait once at the end
     }
+    __syncthreads();
     if (tid == 0) status[0] = sbad;
 }
 

@@ -255,95 +255,155 @@ __global__ void __launch_bounds__(kLkWarps * 32) __maxnreg__(REGS) k_lk_track(co
             tile_ok = jin;
             __syncwarp();
         }
-        // ---- Scharr on the 22 x 22 grid (ipx + dx, ipy + dy): lane = (4-column run cr, row group g).
-        // Per tile row one dp4a gives the horizontal smoothing 3a+10b+3c and one the horizontal
-        // difference c-a of a column; the vertical halves are combined from a 3-row register window.
-        {
-            const int cr = lane % 6, g = lane / 6;            // g 0..4 work, lanes 30, 31 idle
-            if (g < 5) {
-                const bool full = g < 4;                      // rows 0-4, 5-9, 10-14, 15-19; g == 4 has rows 20, 21 only
-                const int r0 = g * 5;
-                const int b0 = oT - 1 + 4 * cr;               // tile byte of column (dx0 - 1), dx0 = 4 * cr
-                const uint32_t* q = sT + r0 * kTWords + (b0 >> 2);
-                const int s8 = 8 * (b0 & 3);
-                int hA[4], hB[4], hC[4], dA[4], dB[4], dC[4];
-#define LK_ROW_HD(H, Dd)                                                                   \
-                {                                                                          \
-                    const uint32_t a0 = __funnelshift_rc(q[0], q[1], s8);                   \
-                    const uint32_t a1 = __funnelshift_rc(q[1], q[2], s8);                   \
-                    const uint32_t x1 = __funnelshift_r(a0, a1, 8), x2 = __funnelshift_r(a0, a1, 16), \
-                                   x3 = __funnelshift_r(a0, a1, 24);                        \
-                    H[0] = dp4a_us(a0, 0x00030a03, 0); Dd[0] = dp4a_us(a0, 0x000100ff, 0);  \
-                    H[1] = dp4a_us(x1, 0x00030a03, 0); Dd[1] = dp4a_us(x1, 0x000100ff, 0);  \
-                    H[2] = dp4a_us(x2, 0x00030a03, 0); Dd[2] = dp4a_us(x2, 0x000100ff, 0);  \
-                    H[3] = dp4a_us(x3, 0x00030a03, 0); Dd[3] = dp4a_us(x3, 0x000100ff, 0);  \
-                    q += kTWords;                                                           \
-                }
-                // output row (r0 + I) from the window (H0, D0), (H1, D1) and the freshly read row (H2, D2)
-#define LK_ROW_OUT(I, H0, D0, H1, D1, H2, D2)                                              \
-                if ((I) < 2 || full) {                                                     \
-                    LK_ROW_HD(H2, D2)                                                      \
-                    int ix[4], iy[4];                                                      \
-                    _Pragma("unroll") for (int j = 0; j < 4; ++j) {                        \
-                        ix[j] = 3 * (D0[j] + D2[j]) + 10 * D1[j];                           \
-                        iy[j] = H2[j] - H0[j];                                             \
-                    }                                                                      \
-                    int* ox = sDx + (r0 + (I)) * kDWords + 4 * cr;                         \
-                    int* oy = sDy + (r0 + (I)) * kDWords + 4 * cr;                         \
-                    if (cr < 5) {                                                          \
-                        *reinterpret_cast<int4*>(ox) = make_int4(ix[0], ix[1], ix[2], ix[3]); \
-                        *reinterpret_cast<int4*>(oy) = make_int4(iy[0], iy[1], iy[2], iy[3]); \
-                    } else {   /* columns 20, 21; 22 and 23 stay zero */                   \
-                        *reinterpret_cast<int2*>(ox) = make_int2(ix[0], ix[1]);            \
-                        *reinterpret_cast<int2*>(oy) = make_int2(iy[0], iy[1]);            \
-                    }                                                                      \
-                }
-                LK_ROW_HD(hA, dA)
-                LK_ROW_HD(hB, dB)
-                LK_ROW_OUT(0, hA, dA, hB, dB, hC, dC)
-                LK_ROW_OUT(1, hB, dB, hC, dC, hA, dA)
-                LK_ROW_OUT(2, hC, dC, hA, dA, hB, dB)
-                LK_ROW_OUT(3, hA, dA, hB, dB, hC, dC)
-                LK_ROW_OUT(4, hB, dB, hC, dC, hA, dA)
-#undef LK_ROW_OUT
-#undef LK_ROW_HD
-            }
-        }
-        __syncwarp();
-        if (ipx < 0 || ipy < 0 || ipx + kDRows > w || ipy + kDRows > h) {   // warp-uniform, rare
-            deriv_zero_outside(sDx, sDy, ipx, ipy, w, h, lane);
-            __syncwarp();
-        }
-        // ---- template samples: I (only for sum I*Ix, sum I*Iy), Ix, Iy per owned pixel
         int wtI, wbI;   // template weights, kept for the error epilogue
         bilinear_weights(px - ipx, py - ipy, wtI, wbI);
-        const int w00 = (int)(short)(wtI & 0xffff), w01 = wtI >> 16, w10 = (int)(short)(wbI & 0xffff), w11 = wbI >> 16;
         int Ix[kRpl * 4], Iy[kRpl * 4];
         int sA11 = 0, sA12 = 0, sA22 = 0, cI1 = 0, cI2 = 0;
-        {
-            const int kT = oT >> 2, sT8 = 8 * (oT & 3);
+        // A window whose 22 x 22 derivative taps all lie inside the image (the usual case) needs no zero
+        // apron, and then interpolation and Scharr commute exactly: sum_k iw_k * Scharr(I)(p_k) ==
+        // Scharr(sum_k iw_k * I(. + k)) in integers (no intermediate rounding on either side).  So the
+        // bilinear sums Iw (23 bits) are formed once on a 23 x 23 grid, the template value is
+        // (Iw + 256) >> 9 and the derivatives are (Scharr(Iw) + 2^13) >> 14 -- one pass instead of a
+        // derivative grid plus a four-tap interpolation of each derivative.
+        const bool border_window = ipx < 0 || ipy < 0 || ipx + kDRows > w || ipy + kDRows > h;   // warp-uniform, rare
+        if (!border_window) {
+            int* G = sDx;   // [24 rows][24 cols]: G[r][c] = Iw at window offset (c - 1, r - 1)
+            {
+                const int cr = lane % 6, g = lane / 6;        // g 0..4 work, lanes 30, 31 idle
+                if (g < 5) {
+                    const bool full = g < 4;                  // grid rows 5g .. 5g+4; g == 4 has rows 20, 21, 22 only
+                    const int r0 = g * 5;
+                    const int b0 = oT - 1 + 4 * cr;           // tile byte of grid column 4 * cr
+                    const uint32_t* q = sT + r0 * kTWords + (b0 >> 2);
+                    const int s8 = 8 * (b0 & 3);
+                    uint32_t ta = __funnelshift_rc(q[0], q[1], s8), tb = __funnelshift_rc(q[0], q[1], s8 + 8);
+                    int* o = G + r0 * kDWords + 4 * cr;
+#pragma unroll
+                    for (int i = 0; i < 5; ++i) {
+                        if (i < 3 || full) {
+                            q += kTWords;
+                            const uint32_t ba = __funnelshift_rc(q[0], q[1], s8), bb = __funnelshift_rc(q[0], q[1], s8 + 8);
+                            *reinterpret_cast<int4*>(o) = make_int4(dp2a_lo_su(wtI, ta, dp2a_lo_su(wbI, ba, 0)), dp2a_lo_su(wtI, tb, dp2a_lo_su(wbI, bb, 0)),
+                                                                    dp2a_hi_su(wtI, ta, dp2a_hi_su(wbI, ba, 0)), dp2a_hi_su(wtI, tb, dp2a_hi_su(wbI, bb, 0)));
+                            o += kDWords;
+                            ta = ba; tb = bb;
+                        }
+                    }
+                }
+            }
+            __syncwarp();
 #pragma unroll
             for (int k = 0; k < kRpl; ++k) {
-                int iv[4];
-                run_sample(sT + LK_OFF_T(k) + kT, sT + LK_OFF_T(k) + kT + kTWords, sT8, wtI, wbI, iv);
-                const int oD = LK_OFF_D(k);
-                const int4 xa = *reinterpret_cast<const int4*>(sDx + oD), xb = *reinterpret_cast<const int4*>(sDx + oD + kDWords);
-                const int4 ya = *reinterpret_cast<const int4*>(sDy + oD), yb = *reinterpret_cast<const int4*>(sDy + oD + kDWords);
-                // the fifth tap of a run in the last column segment would be column 24 = the next row's
-                // column 0; that tap belongs to padding pixel 23 and must read zero
-                const bool seg5 = offJ[k] % kJWords == 5;
-                const int tx[5] = {xa.x, xa.y, xa.z, xa.w, seg5 ? 0 : sDx[oD + 4]}, bx[5] = {xb.x, xb.y, xb.z, xb.w, seg5 ? 0 : sDx[oD + kDWords + 4]};
-                const int ty[5] = {ya.x, ya.y, ya.z, ya.w, seg5 ? 0 : sDy[oD + 4]}, by[5] = {yb.x, yb.y, yb.z, yb.w, seg5 ? 0 : sDy[oD + kDWords + 4]};
+                // rows y-1, y, y+1 and columns x0-1 .. x0+4 of the window run (x0 = 4 * seg, y = wy)
+                const int* gp = G + (((k) == 3 && lane >= 30) ? 0 : (offJ[k] / kJWords) * kDWords + 4 * (offJ[k] % kJWords));
+                const int4 a4 = *reinterpret_cast<const int4*>(gp), b4 = *reinterpret_cast<const int4*>(gp + kDWords),
+                           c4 = *reinterpret_cast<const int4*>(gp + 2 * kDWords);
+                const int2 a2 = *reinterpret_cast<const int2*>(gp + 4), b2 = *reinterpret_cast<const int2*>(gp + kDWords + 4),
+                           c2 = *reinterpret_cast<const int2*>(gp + 2 * kDWords + 4);
+                const int A[6] = {a4.x, a4.y, a4.z, a4.w, a2.x, a2.y}, B[6] = {b4.x, b4.y, b4.z, b4.w, b2.x, b2.y},
+                          Cc[6] = {c4.x, c4.y, c4.z, c4.w, c2.x, c2.y};
+                int sv[6], dv[6];
+#pragma unroll
+                for (int c = 0; c < 6; ++c) { sv[c] = 3 * (A[c] + Cc[c]) + 10 * B[c]; dv[c] = Cc[c] - A[c]; }
+                const bool pad_run = k == 3 && lane >= 30, seg5 = offJ[k] % kJWords == 5;
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    int ixv = (tx[j] * w00 + tx[j + 1] * w01 + bx[j] * w10 + bx[j + 1] * w11 + (1 << 13)) >> 14;
-                    int iyv = (ty[j] * w00 + ty[j + 1] * w01 + by[j] * w10 + by[j + 1] * w11 + (1 << 13)) >> 14;
-                    // window column 21 (padding) still sees derivative column 21 on its left tap;
-                    // columns 22, 23 and the padding runs only see zeros
-                    if (j == 1 && offJ[k] % kJWords == 5) { ixv = 0; iyv = 0; }
+                    int ixv = (sv[j + 2] - sv[j] + (1 << 13)) >> 14;
+                    int iyv = (3 * (dv[j] + dv[j + 2]) + 10 * dv[j + 1] + (1 << 13)) >> 14;
+                    const int ival = (B[j + 1] + 256) >> 9;
+                    if (pad_run || (seg5 && j >= 1)) { ixv = 0; iyv = 0; }   // padding pixels (window columns 21..23)
                     Ix[4 * k + j] = ixv; Iy[4 * k + j] = iyv;
                     sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
-                    cI1 += iv[j] * ixv; cI2 += iv[j] * iyv;
+                    cI1 += ival * ixv; cI2 += ival * iyv;
+                }
+            }
+        } else {
+            // ---- Scharr on the 22 x 22 grid (ipx + dx, ipy + dy): lane = (4-column run cr, row group g).
+            // Per tile row one dp4a gives the horizontal smoothing 3a+10b+3c and one the horizontal
+            // difference c-a of a column; the vertical halves are combined from a 3-row register window.
+            {
+                const int cr = lane % 6, g = lane / 6;            // g 0..4 work, lanes 30, 31 idle
+                if (g < 5) {
+                    const bool full = g < 4;                      // rows 0-4, 5-9, 10-14, 15-19; g == 4 has rows 20, 21 only
+                    const int r0 = g * 5;
+                    const int b0 = oT - 1 + 4 * cr;               // tile byte of column (dx0 - 1), dx0 = 4 * cr
+                    const uint32_t* q = sT + r0 * kTWords + (b0 >> 2);
+                    const int s8 = 8 * (b0 & 3);
+                    int hA[4], hB[4], hC[4], dA[4], dB[4], dC[4];
+    #define LK_ROW_HD(H, Dd)                                                                   \
+                    {                                                                          \
+                        const uint32_t a0 = __funnelshift_rc(q[0], q[1], s8);                   \
+                        const uint32_t a1 = __funnelshift_rc(q[1], q[2], s8);                   \
+                        const uint32_t x1 = __funnelshift_r(a0, a1, 8), x2 = __funnelshift_r(a0, a1, 16), \
+                                       x3 = __funnelshift_r(a0, a1, 24);                        \
+                        H[0] = dp4a_us(a0, 0x00030a03, 0); Dd[0] = dp4a_us(a0, 0x000100ff, 0);  \
+                        H[1] = dp4a_us(x1, 0x00030a03, 0); Dd[1] = dp4a_us(x1, 0x000100ff, 0);  \
+                        H[2] = dp4a_us(x2, 0x00030a03, 0); Dd[2] = dp4a_us(x2, 0x000100ff, 0);  \
+                        H[3] = dp4a_us(x3, 0x00030a03, 0); Dd[3] = dp4a_us(x3, 0x000100ff, 0);  \
+                        q += kTWords;                                                           \
+                    }
+                    // output row (r0 + I) from the window (H0, D0), (H1, D1) and the freshly read row (H2, D2)
+    #define LK_ROW_OUT(I, H0, D0, H1, D1, H2, D2)                                              \
+                    if ((I) < 2 || full) {                                                     \
+                        LK_ROW_HD(H2, D2)                                                      \
+                        int ix[4], iy[4];                                                      \
+                        _Pragma("unroll") for (int j = 0; j < 4; ++j) {                        \
+                            ix[j] = 3 * (D0[j] + D2[j]) + 10 * D1[j];                           \
+                            iy[j] = H2[j] - H0[j];                                             \
+                        }                                                                      \
+                        int* ox = sDx + (r0 + (I)) * kDWords + 4 * cr;                         \
+                        int* oy = sDy + (r0 + (I)) * kDWords + 4 * cr;                         \
+                        if (cr < 5) {                                                          \
+                            *reinterpret_cast<int4*>(ox) = make_int4(ix[0], ix[1], ix[2], ix[3]); \
+                            *reinterpret_cast<int4*>(oy) = make_int4(iy[0], iy[1], iy[2], iy[3]); \
+                        } else {   /* columns 20, 21; 22 and 23 stay zero */                   \
+                            *reinterpret_cast<int2*>(ox) = make_int2(ix[0], ix[1]);            \
+                            *reinterpret_cast<int2*>(oy) = make_int2(iy[0], iy[1]);            \
+                        }                                                                      \
+                    }
+                    LK_ROW_HD(hA, dA)
+                    LK_ROW_HD(hB, dB)
+                    LK_ROW_OUT(0, hA, dA, hB, dB, hC, dC)
+                    LK_ROW_OUT(1, hB, dB, hC, dC, hA, dA)
+                    LK_ROW_OUT(2, hC, dC, hA, dA, hB, dB)
+                    LK_ROW_OUT(3, hA, dA, hB, dB, hC, dC)
+                    LK_ROW_OUT(4, hB, dB, hC, dC, hA, dA)
+    #undef LK_ROW_OUT
+    #undef LK_ROW_HD
+                }
+            }
+            __syncwarp();
+            if (ipx < 0 || ipy < 0 || ipx + kDRows > w || ipy + kDRows > h) {   // warp-uniform, rare
+                deriv_zero_outside(sDx, sDy, ipx, ipy, w, h, lane);
+                __syncwarp();
+            }
+            // ---- template samples: I (only for sum I*Ix, sum I*Iy), Ix, Iy per owned pixel
+            const int w00 = (int)(short)(wtI & 0xffff), w01 = wtI >> 16, w10 = (int)(short)(wbI & 0xffff), w11 = wbI >> 16;
+            {
+                const int kT = oT >> 2, sT8 = 8 * (oT & 3);
+    #pragma unroll
+                for (int k = 0; k < kRpl; ++k) {
+                    int iv[4];
+                    run_sample(sT + LK_OFF_T(k) + kT, sT + LK_OFF_T(k) + kT + kTWords, sT8, wtI, wbI, iv);
+                    const int oD = LK_OFF_D(k);
+                    const int4 xa = *reinterpret_cast<const int4*>(sDx + oD), xb = *reinterpret_cast<const int4*>(sDx + oD + kDWords);
+                    const int4 ya = *reinterpret_cast<const int4*>(sDy + oD), yb = *reinterpret_cast<const int4*>(sDy + oD + kDWords);
+                    // the fifth tap of a run in the last column segment would be column 24 = the next row's
+                    // column 0; that tap belongs to padding pixel 23 and must read zero
+                    const bool seg5 = offJ[k] % kJWords == 5;
+                    const int tx[5] = {xa.x, xa.y, xa.z, xa.w, seg5 ? 0 : sDx[oD + 4]}, bx[5] = {xb.x, xb.y, xb.z, xb.w, seg5 ? 0 : sDx[oD + kDWords + 4]};
+                    const int ty[5] = {ya.x, ya.y, ya.z, ya.w, seg5 ? 0 : sDy[oD + 4]}, by[5] = {yb.x, yb.y, yb.z, yb.w, seg5 ? 0 : sDy[oD + kDWords + 4]};
+    #pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        int ixv = (tx[j] * w00 + tx[j + 1] * w01 + bx[j] * w10 + bx[j + 1] * w11 + (1 << 13)) >> 14;
+                        int iyv = (ty[j] * w00 + ty[j + 1] * w01 + by[j] * w10 + by[j + 1] * w11 + (1 << 13)) >> 14;
+                        // window column 21 (padding) still sees derivative column 21 on its left tap;
+                        // columns 22, 23 and the padding runs only see zeros
+                        if (j == 1 && offJ[k] % kJWords == 5) { ixv = 0; iyv = 0; }
+                        Ix[4 * k + j] = ixv; Iy[4 * k + j] = iyv;
+                        sA11 += ixv * ixv; sA12 += ixv * iyv; sA22 += iyv * iyv;
+                        cI1 += iv[j] * ixv; cI2 += iv[j] * iyv;
+                    }
                 }
             }
         }

@@ -387,7 +387,7 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
                "cost": cost, "S_trace": float(np.trace(S))}
         if out["roofline"]["achieved"]:
             out["roofline"]["frac"] = out["roofline"]["achieved"] / fp64_peak
-        if not sharded:
+        if world == 1:
             # reduced-system solve + landmark back substitution on the device
             ba.solve_reduced(True)
             ctx.enable_kernel_timing(True); ctx.reset_kernel_times()
