@@ -69,6 +69,10 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.rows)}
 
 
+# dram bytes per launch of the default 64-frame workload, from the committed ncu capture
+NCU_TRAFFIC = {"k_lk_track": 597.177344e6 + 11.730688e6}
+
+
 def measured_peaks():
     try:
         p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -216,7 +220,8 @@ def run_ours(args):
     frame_bytes = (pyr_b + lk_b) * B
     step_ms = ms_total / args.steps
     roofline = {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / hbm_peak, "traffic": NCU_TRAFFIC.get(dominant) if B == 64 else None, "peak_source": peak_src,
+                "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full capture of this command (profiles/r01_ncu_frontend_late.txt); 32-byte sectors around 32/36-byte tile rows and search-tile refills explain the factor over the algorithmic bytes",
                 "algorithmic_bytes_per_launch": per_launch_bytes, "avg_launch_ms": dur_ms,
                 "kernel_share_of_step": {"k_lk_track": lk_ms / ms_total, "k_pyr_down": pyr_ms / ms_total},
                 "tracking_frame": {"algorithmic_bytes_per_step": frame_bytes,
