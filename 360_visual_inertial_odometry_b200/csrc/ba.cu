@@ -42,6 +42,7 @@ struct vio360_ba {
     bool has_structure = false, has_params = false, has_eval = false, has_eval_jac = false;
     bool has_reduced = false, reduced_apply_loss = false, solve_dirty = true, chol_attr_set = false;
     DevBuf d_chol, d_linv, d_x, d_dl, d_reachF;
+    int max_reach = 0;   // widest column of the envelope, in blocks
     PinBuf h_solve;
     int n_free = 0;
     int shard_rank = 0, shard_world = 1, lm_begin = 0, lm_end = 0;
@@ -1131,22 +1132,38 @@ extern "C" int vio360_ba_solve_reduced(vio360_ba* ba, double* delta_pose, double
             }
             VIO_CUDA(ctx, ba->d_reachF.reserve((size_t)nb * 4));
             VIO_CUDA(ctx, cudaMemcpy(ba->d_reachF.p, reachF.data(), (size_t)nb * 4, cudaMemcpyHostToDevice));
+            ba->max_reach = 0;
+            for (int a = 0; a < nb; ++a) ba->max_reach = std::max(ba->max_reach, reachF[a] - a);
             ba->solve_dirty = false;
         }
-        VIO_CUDA(ctx, ba->d_chol.reserve(n * n * 8));
         VIO_CUDA(ctx, ba->d_linv.reserve((size_t)nb * 36 * 8));
         VIO_CUDA(ctx, ba->d_x.reserve(n * 8 + 16));
         const double* dS = ba->d_packed.as<double>();
-        VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_chol.p, dS, n * n * 8, cudaMemcpyDeviceToDevice, st));
         VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_x.p, dS + n * n, n * 8, cudaMemcpyDeviceToDevice, st));
         if (!ba->chol_attr_set) {
             VIO_CUDA(ctx, cudaFuncSetAttribute(k_chol_skyline, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            VIO_CUDA(ctx, cudaFuncSetAttribute(k_chol_band, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
             ba->chol_attr_set = true;
         }
         int* d_status = reinterpret_cast<int*>(ba->d_x.as<double>() + n);
-        { KernelTimer kt_(ctx, "k_chol_skyline");
-        k_chol_skyline<<<1, kCholThreads, panel_bytes, st>>>(ba->d_chol.as<double>(), nb, ba->d_reachF.as<int>(), ba->d_linv.as<double>(),
-                                                            ba->d_x.as<double>(), d_status);
+        const size_t band_smem = ((size_t)kCholWb * kCholWb * 36 + ((kCholWb - 1) * 6 + 1) * 6 + n) * sizeof(double);
+        if (ba->max_reach < kCholWb && band_smem <= (size_t)220 * 1024) {
+            // banded window: trailing matrix in shared memory, S itself is only read
+            VIO_CUDA(ctx, ba->d_chol.reserve(((size_t)nb * (kCholWb - 1) * 36 + (size_t)nb * 42) * 8));
+            double* Lcol = ba->d_chol.as<double>();
+            { KernelTimer kt_(ctx, "k_chol_band");
+            k_chol_band<<<1, kCholThreads, band_smem, st>>>(dS, nb, ba->d_reachF.as<int>(), Lcol, Lcol + (size_t)nb * (kCholWb - 1) * 36,
+                                                           ba->d_x.as<double>(), d_status);
+            }
+            VIO_LAUNCH_CHECK(ctx);
+            KernelTimer kt_(ctx, "k_chol_band_back");
+            k_chol_band_back<<<1, 32, n * sizeof(double), st>>>(nb, ba->d_reachF.as<int>(), Lcol, Lcol + (size_t)nb * (kCholWb - 1) * 36, ba->d_x.as<double>());
+        } else {
+            VIO_CUDA(ctx, ba->d_chol.reserve(n * n * 8));
+            VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_chol.p, dS, n * n * 8, cudaMemcpyDeviceToDevice, st));
+            KernelTimer kt_(ctx, "k_chol_skyline");
+            k_chol_skyline<<<1, kCholThreads, panel_bytes, st>>>(ba->d_chol.as<double>(), nb, ba->d_reachF.as<int>(), ba->d_linv.as<double>(),
+                                                                ba->d_x.as<double>(), d_status);
         }
         VIO_LAUNCH_CHECK(ctx);
         VIO_CUDA(ctx, cudaMemcpyAsync(hx, ba->d_x.p, n * 8 + 8, cudaMemcpyDeviceToHost, st));

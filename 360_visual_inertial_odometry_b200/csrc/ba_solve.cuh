@@ -142,6 +142,204 @@ __global__ void __launch_bounds__(kCholThreads) k_chol_skyline(double* __restric
     if (tid == 0) status[0] = sbad;
 }
 
+// Banded fast path of the same factorisation: when no column reaches further than kCholWb - 1 block
+// rows (sliding windows: ~20), the active (kCholWb x kCholWb)-block part of the trailing matrix lives
+// in shared memory as a circular buffer (block (i, k) at slot (i mod Wb, k mod Wb)); a finished
+// column frees its slot for the block row that enters the window, fetched from the untouched S
+// while the column is being processed.  Three block barriers per column, no global round trips
+// on the dependent path.  L's columns are streamed out compactly for the backward substitution.
+constexpr int kCholWb = 24;
+
+__device__ __forceinline__ bool chol6_diag(const double* A, double* L, double* invd) {
+    bool ok = true;
+#pragma unroll
+    for (int i = 0; i < 36; ++i) L[i] = 0.0;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+        double d = A[j * 6 + j];
+#pragma unroll
+        for (int k = 0; k < j; ++k) d -= L[j * 6 + k] * L[j * 6 + k];
+        if (!(d > 0.0)) { ok = false; d = 1.0; }
+        const double iv = vio_rsqrt(d);
+        invd[j] = iv;
+        L[j * 6 + j] = d * iv;
+#pragma unroll
+        for (int i = j + 1; i < 6; ++i) {
+            double s = A[i * 6 + j];
+#pragma unroll
+            for (int k = 0; k < j; ++k) s -= L[i * 6 + k] * L[j * 6 + k];
+            L[i * 6 + j] = s * iv;
+        }
+    }
+    return ok;
+}
+
+// S: n x n row-major (read only); Lcol: nb x (Wb-1) x 36 (block rows below the diagonal of each
+// column); Ldiag: nb x 42 (L_jj, 6 reciprocal pivots); b: rhs in, x out.
+__global__ void __launch_bounds__(kCholThreads) k_chol_band(const double* __restrict__ S, int nb, const int* __restrict__ reach,
+                                                            double* __restrict__ Lcol, double* __restrict__ Ldiag, double* __restrict__ b,
+                                                            int* __restrict__ status) {
+    extern __shared__ double sm[];
+    double* Wsm = sm;                                         // [Wb][Wb][36]
+    double* panel = Wsm + kCholWb * kCholWb * 36;             // [(Wb-1)*6 + 1][6]
+    double* sb = panel + ((kCholWb - 1) * 6 + 1) * 6;         // [n]
+    __shared__ double sL[36], sInv[6];
+    __shared__ int sbad;
+    const int tid = threadIdx.x, n = 6 * nb;
+    auto slot = [&](int i, int k) { return Wsm + ((i % kCholWb) * kCholWb + (k % kCholWb)) * 36; };
+    if (tid == 0) sbad = 0;
+    for (int e = tid; e < n; e += kCholThreads) sb[e] = b[e];
+    {   // first window: lower triangle of block rows 0 .. min(Wb, nb) - 1
+        const int w0 = min(kCholWb, nb), wr = 6 * w0;
+        for (int e = tid; e < wr * wr; e += kCholThreads) {
+            const int row = e / wr, colm = e - row * wr;
+            if (colm / 6 > row / 6) continue;
+            slot(row / 6, colm / 6)[(row % 6) * 6 + colm % 6] = S[(size_t)row * n + colm];
+        }
+    }
+    __syncthreads();
+    // the block row that enters the window when column j leaves (row j + Wb, columns j+1 .. j+Wb) is
+    // fetched three columns ahead: one element per thread, three loads in flight
+    const int pa = tid / (6 * kCholWb), pc = tid - pa * (6 * kCholWb);   // row in block, column offset
+    auto fetch_row = [&](int j) -> double {
+        const int inew = j + kCholWb;
+        return (inew < nb && pa < 6) ? S[(size_t)(6 * inew + pa) * n + 6 * (j + 1) + pc] : 0.0;
+    };
+    double preA = fetch_row(0), preB = fetch_row(1), preC = fetch_row(2);
+    // Column j: [panel phase, all threads] barrier [trailing update on warps 1..31 | warp 0 updates the
+    // next diagonal block and factorises it] barrier -- the serial 6x6 pivot hides behind the update.
+    if (tid == 0) { if (!chol6_diag(slot(0, 0), sL, sInv)) sbad = 1; }
+    __syncthreads();
+#define CHOL_STEP(J, PRE)                                                                            \
+    if ((J) < nb) {                                                                                \
+        const int j = (J);                                                                         \
+        const int r = reach[j] - j, rows = 6 * r;                                                  \
+        if (tid < 36) Ldiag[(size_t)j * 42 + tid] = sL[tid];                                       \
+        if (tid < 6) Ldiag[(size_t)j * 42 + 36 + tid] = sInv[tid];                                 \
+        if (tid <= rows) {   /* panel row: x Ljj^T = v by substitution; row `rows` is the rhs */   \
+            const int bi = tid / 6, a = tid - bi * 6;                                              \
+            double* src = tid < rows ? slot(j + 1 + bi, j) + a * 6 : sb + 6 * j;                   \
+            double o[6];                                                                           \
+            _Pragma("unroll") for (int c = 0; c < 6; ++c) {                                        \
+                double v = src[c];                                                                 \
+                _Pragma("unroll") for (int k = 0; k < c; ++k) v -= o[k] * sL[c * 6 + k];           \
+                o[c] = v * sInv[c];                                                                \
+            }                                                                                      \
+            _Pragma("unroll") for (int c = 0; c < 6; ++c) panel[tid * 6 + c] = o[c];               \
+            if (tid < rows) {                                                                      \
+                _Pragma("unroll") for (int c = 0; c < 6; ++c) Lcol[((size_t)j * (kCholWb - 1) + bi) * 36 + a * 6 + c] = o[c]; \
+            } else {                                                                               \
+                _Pragma("unroll") for (int c = 0; c < 6; ++c) sb[6 * j + c] = o[c];                \
+            }                                                                                      \
+        }                                                                                          \
+        __syncthreads();                                                                           \
+        if (tid < 32) {   /* pivot warp: block (j+1, j+1) -= L L^T of the first panel block, then factorise */ \
+            if (j + 1 < nb) {                                                                      \
+                double* dblk = slot(j + 1, j + 1);                                                 \
+                if (rows >= 6) {                                                                   \
+                    for (int e = tid; e < 36; e += 32) {                                           \
+                        const double* li = panel + (e / 6) * 6;                                    \
+                        const double* lk = panel + (e % 6) * 6;                                    \
+                        dblk[e] -= li[0] * lk[0] + li[1] * lk[1] + li[2] * lk[2] + li[3] * lk[3] + li[4] * lk[4] + li[5] * lk[5]; \
+                    }                                                                              \
+                }                                                                                  \
+                __syncwarp();                                                                      \
+                if (tid == 0) { if (!chol6_diag(dblk, sL, sInv)) sbad = 1; }                       \
+            }                                                                                      \
+        } else {                                                                                   \
+            const int t2 = tid - 32;   /* 992 threads: column ck = t2 % 124, row phase t2 / 124 (8) */ \
+            for (int ck = t2 % 124; ck < rows; ck += 124) {                                        \
+                const double* lk = panel + ck * 6;                                                 \
+                const double k0 = lk[0], k1 = lk[1], k2 = lk[2], k3 = lk[3], k4 = lk[4], k5 = lk[5]; \
+                const int kb = ck / 6, kc = ck - kb * 6;                                           \
+                for (int ri = kb * 6 + t2 / 124; ri <= rows; ri += 8) {                            \
+                    if (ri < 6) continue;   /* block (j+1, j+1) belongs to the pivot warp */       \
+                    const double* li = panel + ri * 6;                                             \
+                    const double sdot = li[0] * k0 + li[1] * k1 + li[2] * k2 + li[3] * k3 + li[4] * k4 + li[5] * k5; \
+                    if (ri < rows) slot(j + 1 + ri / 6, j + 1 + kb)[(ri % 6) * 6 + kc] -= sdot;    \
+                    else sb[6 * (j + 1) + ck] -= sdot;                                             \
+                }                                                                                  \
+            }                                                                                      \
+        }                                                                                          \
+        if (j + kCholWb < nb && pa < 6) slot(j + kCholWb, j + 1 + pc / 6)[pa * 6 + pc % 6] = PRE;  /* row slot j mod Wb is free now */ \
+        PRE = fetch_row(j + 3);                                                                    \
+        __syncthreads();                                                                           \
+    }
+    for (int j3 = 0; j3 < nb; j3 += 3) {
+        CHOL_STEP(j3, preA)
+        CHOL_STEP(j3 + 1, preB)
+        CHOL_STEP(j3 + 2, preC)
+    }
+#undef CHOL_STEP
+    __syncthreads();
+    for (int e = tid; e < n; e += kCholThreads) b[e] = sb[e];
+    if (tid == 0) status[0] = sbad;
+}
+
+// Backward substitution L^T x = y for the banded factor: one warp, the next column's data is
+// fetched while the current one is reduced (the chain is nb dependent 6x6 solves).
+__global__ void __launch_bounds__(32) k_chol_band_back(int nb, const int* __restrict__ reach, const double* __restrict__ Lcol,
+                                                       const double* __restrict__ Ldiag, double* __restrict__ b) {
+    extern __shared__ double sx[];   // [n]
+    const int lane = threadIdx.x, n = 6 * nb;
+    for (int e = lane; e < n; e += 32) sx[e] = b[e];
+    __syncwarp();
+    constexpr int kRowsPerLane = ((kCholWb - 1) * 6 + 31) / 32;   // 5
+    double cur[kRowsPerLane][6], nxt[kRowsPerLane][6];
+    double dcur[2], dnxt[2];   // lanes 0..20 hold L_jj (36) and the reciprocal pivots (6): two doubles each
+    auto fetch = [&](int j, double (*dst)[6], double* dd) {
+        const int rows = 6 * (reach[j] - j);
+        const double* col = Lcol + (size_t)j * (kCholWb - 1) * 36;
+#pragma unroll
+        for (int q = 0; q < kRowsPerLane; ++q) {
+            const int row = lane + 32 * q;
+#pragma unroll
+            for (int c = 0; c < 6; ++c) dst[q][c] = row < rows ? col[row * 6 + c] : 0.0;
+        }
+        dd[0] = lane < 21 ? Ldiag[(size_t)j * 42 + 2 * lane] : 0.0;
+        dd[1] = lane < 21 ? Ldiag[(size_t)j * 42 + 2 * lane + 1] : 0.0;
+    };
+    if (nb > 0) fetch(nb - 1, cur, dcur);
+    for (int j = nb - 1; j >= 0; --j) {
+        if (j > 0) fetch(j - 1, nxt, dnxt);
+        const int rows = 6 * (reach[j] - j);
+        double acc[6] = {0, 0, 0, 0, 0, 0};
+#pragma unroll
+        for (int q = 0; q < kRowsPerLane; ++q) {
+            const int row = lane + 32 * q;
+            const double xv = row < rows ? sx[6 * (j + 1) + row] : 0.0;
+#pragma unroll
+            for (int c = 0; c < 6; ++c) acc[c] += cur[q][c] * xv;
+        }
+#pragma unroll
+        for (int c = 0; c < 6; ++c)
+#pragma unroll
+            for (int sft = 16; sft > 0; sft >>= 1) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], sft);
+        // x_c = (y_c - acc_c - sum_{k > c} L[k][c] x_k) / L[c][c], every lane redundantly (values via shuffles)
+        double x[6];
+#pragma unroll
+        for (int c = 5; c >= 0; --c) {
+            double v = sx[6 * j + c] - acc[c];
+#pragma unroll
+            for (int k = c + 1; k < 6; ++k) {
+                const int e = k * 6 + c;   // L[k][c] sits in lane e / 2, element e % 2
+                v -= __shfl_sync(0xffffffffu, dcur[e & 1], e >> 1) * x[k];
+            }
+            x[c] = v * __shfl_sync(0xffffffffu, dcur[(36 + c) & 1], (36 + c) >> 1);
+        }
+        __syncwarp();
+        if (lane < 6) sx[6 * j + lane] = x[lane];
+        __syncwarp();
+#pragma unroll
+        for (int q = 0; q < kRowsPerLane; ++q)
+#pragma unroll
+            for (int c = 0; c < 6; ++c) cur[q][c] = nxt[q][c];
+        dcur[0] = dnxt[0]; dcur[1] = dnxt[1];
+    }
+    __syncwarp();
+    for (int e = lane; e < n; e += 32) b[e] = sx[e];
+}
+
 // one warp per landmark of [lm_begin, lm_end): dl = (E'E + D^2)^-1 sum_i E_i'(r_i - F_i x_p(i))
 __global__ void __launch_bounds__(128) k_back_substitute(BaDev d, int lm_begin, int lm_end, bool apply_loss, const double* __restrict__ x,
                                                          double* __restrict__ dl) {

@@ -402,7 +402,7 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
             solve_s = (time.perf_counter() - t0) / 3
             out["solve"] = {"ms_per_call_host_clock": solve_s * 1e3,
                             "kernel_ms_per_launch": {k: ctx.kernel_time(k)[0] / max(ctx.kernel_time(k)[1], 1)
-                                                     for k in ("k_chol_skyline", "k_back_substitute")}}
+                                                     for k in ("k_chol_band", "k_chol_band_back", "k_chol_skyline", "k_back_substitute")}}
             ctx.enable_kernel_timing(False)
         ba.close()
         return out
