@@ -25,7 +25,7 @@ EXPORTS = [
     "vio360_ba_set_shard", "vio360_ba_set_parameters", "vio360_ba_evaluate",
     "vio360_ba_get_residuals_jacobians", "vio360_ba_normal_blocks", "vio360_ba_reduced_dim",
     "vio360_ba_build_reduced_system", "vio360_ba_set_lm_diagonal", "vio360_ba_reduced_system_dev", "vio360_ba_fetch_reduced_system",
-    "vio360_ba_column_sqnorm", "vio360_ba_chi2", "vio360_ba_solve_reduced", "vio360_pnp_evaluate",
+    "vio360_ba_column_sqnorm", "vio360_ba_chi2", "vio360_ba_solve_reduced", "vio360_pnp_evaluate", "vio360_triangulate",
 ]
 
 
@@ -113,6 +113,8 @@ def load():
     lib.vio360_ba_fetch_reduced_system.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]
     lib.vio360_ba_column_sqnorm.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
     lib.vio360_ba_chi2.argtypes = [C.c_void_p, C.c_double, C.c_void_p, C.c_void_p]
+    lib.vio360_triangulate.argtypes = [C.c_void_p] * 5 + [C.c_int, C.c_void_p, C.c_void_p]
+    lib.vio360_ba_solve_reduced.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     lib.vio360_pnp_evaluate.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 5 + [C.c_double, C.c_double, C.c_void_p,
                                                                                    C.c_double] + [C.c_void_p] * 8
     _lib = lib
@@ -255,6 +257,15 @@ class Context:
                 j.occupied_xy, j.n_occupied, j.occupied_radius = occ.ctypes.data, occ.shape[0], occupied_radius
         self.check(self.lib.vio360_fe_detect_batch(self.h, jobs, nb, max_corners, quality, min_dist, MEM_HOST))
         return [outs[b][:ns[b]].copy() for b in range(nb)]
+
+    def triangulate(self, b1, b2, T1w, T2w):
+        """Estimator::TriangulateSinglePoint for all matches of a keyframe pair: (points n x 3, valid n)."""
+        b1 = np.ascontiguousarray(b1, np.float32).reshape(-1, 3); b2 = np.ascontiguousarray(b2, np.float32).reshape(-1, 3)
+        T1 = np.ascontiguousarray(T1w, np.float32).reshape(16); T2 = np.ascontiguousarray(T2w, np.float32).reshape(16)
+        n = b1.shape[0]
+        pts = np.zeros((n, 3), np.float32); valid = np.zeros(n, np.uint8)
+        self.check(self.lib.vio360_triangulate(self.h, _ptr(b1), _ptr(b2), _ptr(T1), _ptr(T2), n, _ptr(pts), _ptr(valid)))
+        return pts, valid
 
     def fe_ransac_rotation(self, prev_xy, cur_xy, samples, threshold_deg):
         """FeatureTracker::RejectOutliersRotationRANSAC with an injected (iters, 3) sample list.

@@ -114,6 +114,7 @@ __global__ void k_sum_partials(const double* __restrict__ partials, int n, doubl
 
 #include "ba_schur_kernels.cuh"
 #include "ba_solve.cuh"
+#include "ba_triangulate.cuh"
 
 template <bool WANT_JAC>
 __global__ void __launch_bounds__(128) k_evaluate(BaDev d, bool apply_loss, double* __restrict__ r_out,
@@ -1188,5 +1189,37 @@ extern "C" int vio360_ba_solve_reduced(vio360_ba* ba, double* delta_pose, double
         for (int k = 0; k < 6; ++k) delta_pose[6 * (size_t)p + k] = a >= 0 ? hx[6 * (size_t)a + k] : 0.0;
     }
     if (delta_point && M > 0) memcpy(delta_point, hx + n + 1, 3 * (size_t)M * 8);
+    return VIO360_OK;
+}
+
+// ---- batched DLT triangulation (Estimator.cpp:1082-1139) ----
+extern "C" int vio360_triangulate(vio360_ctx* ctx, const float* bearing1, const float* bearing2, const float* T1w, const float* T2w, int n,
+                                  float* points, uint8_t* valid) {
+    if (!ctx) return VIO360_ERR_INVALID;
+    if (n < 0 || !T1w || !T2w || (n > 0 && (!bearing1 || !bearing2 || !points || !valid)))
+        return vio360_fail(ctx, VIO360_ERR_INVALID, "triangulate: bad arguments");
+    if (n == 0) return VIO360_OK;
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    DevBuf buf;
+    const size_t nf = 3 * (size_t)n;
+    VIO_CUDA(ctx, buf.reserve(nf * 4 * 3 + (size_t)n));
+    float* d_b1 = buf.as<float>(); float* d_b2 = d_b1 + nf; float* d_pts = d_b2 + nf;
+    unsigned char* d_valid = reinterpret_cast<unsigned char*>(d_pts + nf);
+    VIO_CUDA(ctx, cudaMemcpyAsync(d_b1, bearing1, nf * 4, cudaMemcpyHostToDevice, st));
+    VIO_CUDA(ctx, cudaMemcpyAsync(d_b2, bearing2, nf * 4, cudaMemcpyHostToDevice, st));
+    Mat4f A, B;
+    memcpy(A.m, T1w, sizeof(A.m)); memcpy(B.m, T2w, sizeof(B.m));
+    { KernelTimer kt_(ctx, "k_triangulate");
+    k_triangulate<<<(n + 127) / 128, 128, 0, st>>>(n, d_b1, d_b2, A, B, d_pts, d_valid);
+    }
+    ctx->launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { buf.release(); return vio360_fail(ctx, VIO360_ERR_CUDA, "k_triangulate: %s", cudaGetErrorString(e)); }
+    cudaMemcpyAsync(points, d_pts, nf * 4, cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(valid, d_valid, (size_t)n, cudaMemcpyDeviceToHost, st);
+    e = cudaStreamSynchronize(st);
+    buf.release();
+    if (e != cudaSuccess) return vio360_fail(ctx, VIO360_ERR_CUDA, "triangulate: %s", cudaGetErrorString(e));
     return VIO360_OK;
 }

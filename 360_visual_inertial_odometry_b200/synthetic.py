@@ -235,3 +235,24 @@ def draw_ransac_samples(n, iters, seed):
                 idx.append(k)
         out[it] = idx
     return out
+
+
+def make_triangulation_pairs(n, seed, baseline=0.5):
+    """Two camera poses `baseline` apart looking at n points 2-10 m away: unit bearings in both camera
+    frames and the world-to-camera transforms (row-major 4x4, float32), plus the true points."""
+    rng = np.random.default_rng(seed)
+    def rot(axis, ang):
+        axis = np.asarray(axis, np.float64) / np.linalg.norm(axis)
+        K = np.array([[0, -axis[2], axis[1]], [axis[2], 0, -axis[0]], [-axis[1], axis[0], 0]])
+        return np.eye(3) + np.sin(ang) * K + (1 - np.cos(ang)) * K @ K
+    R1, t1 = rot([0.1, 1.0, 0.2], 0.3), np.array([0.2, -0.1, 0.3])
+    R2, t2 = rot([0.3, 0.9, -0.1], 0.45), np.array([0.2 - baseline, 0.05, 0.25])
+    d = rng.normal(size=(n, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    P = d * rng.uniform(2.0, 10.0, (n, 1))
+    def to_cam(R, t): return P @ R.T + t
+    c1, c2 = to_cam(R1, t1), to_cam(R2, t2)
+    b1 = (c1 / np.linalg.norm(c1, axis=1, keepdims=True)).astype(np.float32)
+    b2 = (c2 / np.linalg.norm(c2, axis=1, keepdims=True)).astype(np.float32)
+    T1 = np.eye(4); T1[:3, :3] = R1; T1[:3, 3] = t1
+    T2 = np.eye(4); T2[:3, :3] = R2; T2[:3, 3] = t2
+    return b1, b2, T1.astype(np.float32), T2.astype(np.float32), P

@@ -255,6 +255,14 @@ int vio360_pnp_evaluate(vio360_ctx* ctx, int N, const double* obs_uv, const doub
                         const double* pose_delta, double* r, double* Jp, uint8_t* valid,
                         double* H, double* b, double* cost, double* chi2);
 
+/* batched DLT triangulation of the matches of one keyframe pair.  Replaces the
+ * per-match Estimator::TriangulateSinglePoint (src/processing/Estimator.cpp:1082-1139, called at :1218).
+ * bearing1/bearing2: n x 3 unit bearings in the two camera frames; T1w, T2w: 4 x 4 row-major
+ * world-to-camera transforms (Eigen::Matrix4f values); points: n x 3; valid[i] = the function's bool
+ * (|w| >= 1e-10 and finite coordinates), points of invalid matches are zero.  fp32 as the reference. */
+int vio360_triangulate(vio360_ctx* ctx, const float* bearing1, const float* bearing2, const float* T1w,
+                       const float* T2w, int n, float* points, uint8_t* valid);
+
 #ifdef __cplusplus
 }
 #endif

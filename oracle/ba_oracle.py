@@ -202,3 +202,17 @@ def so3_project(M):
     R = np.empty((3, 3)); Mc = np.ascontiguousarray(M, np.float64)
     lib().vo_so3_project(_d(Mc), _d(R))
     return R
+
+
+def triangulate(b1, b2, T1w, T2w):
+    """Estimator::TriangulateSinglePoint for n matches (fp32).  returns (points n x 3, valid n)."""
+    b1 = np.ascontiguousarray(b1, np.float32).reshape(-1, 3); b2 = np.ascontiguousarray(b2, np.float32).reshape(-1, 3)
+    T1 = np.ascontiguousarray(T1w, np.float32).reshape(16); T2 = np.ascontiguousarray(T2w, np.float32).reshape(16)
+    n = b1.shape[0]
+    pts = np.zeros((n, 3), np.float32); valid = np.zeros(n, np.uint8)
+    fp = C.POINTER(C.c_float)
+    f = lib().vo_triangulate
+    f.restype = None
+    f(b1.ctypes.data_as(fp), b2.ctypes.data_as(fp), T1.ctypes.data_as(fp), T2.ctypes.data_as(fp), n,
+      pts.ctypes.data_as(fp), valid.ctypes.data_as(_up))
+    return pts, valid

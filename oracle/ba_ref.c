@@ -851,3 +851,57 @@ void vo_window_chi2(const vo_window* w, const double* pose_delta, const double* 
         if (flag) flag[i] = (unsigned char)(c > thr);
     }
 }
+
+/* ------------------------------------------------------------------ DLT triangulation */
+void vo_triangulate(const float* b1, const float* b2, const float* T1, const float* T2, int n,
+                    float* points, unsigned char* valid) {
+    for (int i = 0; i < n; ++i) {
+        const float* u = b1 + 3 * i; const float* v = b2 + 3 * i;
+        float B[16], V[16];
+        for (int c = 0; c < 4; ++c) {                         /* Estimator.cpp:1098-1101 */
+            B[0 * 4 + c] = u[0] * T1[2 * 4 + c] - u[2] * T1[0 * 4 + c];
+            B[1 * 4 + c] = u[1] * T1[2 * 4 + c] - u[2] * T1[1 * 4 + c];
+            B[2 * 4 + c] = v[0] * T2[2 * 4 + c] - v[2] * T2[0 * 4 + c];
+            B[3 * 4 + c] = v[1] * T2[2 * 4 + c] - v[2] * T2[1 * 4 + c];
+        }
+        for (int k = 0; k < 16; ++k) V[k] = (k % 5 == 0) ? 1.f : 0.f;
+        for (int sweep = 0; sweep < 30; ++sweep) {
+            float off = 0.f;
+            for (int p = 0; p < 3; ++p)
+                for (int q = p + 1; q < 4; ++q) {
+                    float alpha = 0.f, beta = 0.f, gamma = 0.f;
+                    for (int k = 0; k < 4; ++k) {
+                        alpha += B[k * 4 + p] * B[k * 4 + p];
+                        beta += B[k * 4 + q] * B[k * 4 + q];
+                        gamma += B[k * 4 + p] * B[k * 4 + q];
+                    }
+                    const float lim = sqrtf(alpha * beta);
+                    if (gamma == 0.f || fabsf(gamma) <= 1e-9f * lim) continue;
+                    const float rel = fabsf(gamma) / (lim > 0.f ? lim : 1.f);
+                    if (rel > off) off = rel;
+                    const float zeta = (beta - alpha) / (2.f * gamma);
+                    const float t = (zeta >= 0.f ? 1.f : -1.f) / (fabsf(zeta) + sqrtf(1.f + zeta * zeta));
+                    const float c = 1.f / sqrtf(1.f + t * t), s = c * t;
+                    for (int k = 0; k < 4; ++k) {
+                        const float bp = B[k * 4 + p], bq = B[k * 4 + q];
+                        B[k * 4 + p] = c * bp - s * bq; B[k * 4 + q] = s * bp + c * bq;
+                        const float vp = V[k * 4 + p], vq = V[k * 4 + q];
+                        V[k * 4 + p] = c * vp - s * vq; V[k * 4 + q] = s * vp + c * vq;
+                    }
+                }
+            if (off < 1e-7f) break;
+        }
+        int best = 0;
+        float smin = FLT_MAX;
+        for (int j = 0; j < 4; ++j) {
+            const float sv = B[j] * B[j] + B[4 + j] * B[4 + j] + B[8 + j] * B[8 + j] + B[12 + j] * B[12 + j];
+            if (sv < smin) { smin = sv; best = j; }
+        }
+        const float h0 = V[best], h1 = V[4 + best], h2 = V[8 + best], h3 = V[12 + best];
+        int ok = !(fabsf(h3) < 1e-10f);                       /* :1108-1110 */
+        const float x = h0 / h3, y = h1 / h3, z = h2 / h3;    /* :1113 */
+        ok = ok && isfinite(x) && isfinite(y) && isfinite(z); /* :1119-1121 */
+        points[3 * i] = ok ? x : 0.f; points[3 * i + 1] = ok ? y : 0.f; points[3 * i + 2] = ok ? z : 0.f;
+        valid[i] = (unsigned char)ok;
+    }
+}

@@ -128,6 +128,12 @@ void vo_lm_diagonal(const vo_window* w, const double* Jp, const double* Jl,
 void vo_window_chi2(const vo_window* w, const double* pose_delta, const double* points,
                     double thr, double* chi2, unsigned char* flag);
 
+/* Estimator::TriangulateSinglePoint (src/processing/Estimator.cpp:1082-1139) for n matches of one
+ * keyframe pair, fp32.  T1w/T2w 4x4 row-major.  Eigen::JacobiSVD<Matrix4f> is restated by a one-sided
+ * Jacobi SVD (last right singular vector; unique up to sign).  valid[i] = the function's return.   */
+void vo_triangulate(const float* b1, const float* b2, const float* T1w, const float* T2w, int n,
+                    float* points, unsigned char* valid);
+
 #ifdef __cplusplus
 }
 #endif

@@ -61,7 +61,8 @@ def test_solve_reduced_and_back_substitution(bindings, ctx, synthetic):
     against LAPACK / numpy on the oracle's system.  A different factorisation order than Eigen's LLT,
     so the tolerance is 1e-7 relative (cond(S) ~ 1e6 with the LM diagonal), written here."""
     for win in (synthetic.make_ba_window(K=10, M=300, seed=20001),
-                synthetic.make_ba_window(K=40, M=1500, degree=8, seed=20002)):
+                synthetic.make_ba_window(K=40, M=1500, degree=8, seed=20002),
+                synthetic.make_ba_window(K=36, M=400, degree=30, seed=20003)):   # envelope wider than the shared-memory window
         W = ba_oracle.Window(win)
         r, Jp, Jl, _ = W.evaluate(win["pose_delta"], win["points"])
         D = W.lm_diagonal(Jp, Jl, 1e4)
@@ -77,6 +78,19 @@ def test_solve_reduced_and_back_substitution(bindings, ctx, synthetic):
         dp2, _ = ba.solve_reduced(False)
         assert np.array_equal(dp, dp2)
         ba.close()
+
+
+def test_triangulate_vs_oracle(ctx, synthetic):
+    """fp32 DLT triangulation; same algorithm as the oracle, different FMA contraction:
+    tolerance 2e-3 of the point's distance (fp32 with a 0.5 m baseline and up to 10 m depth)."""
+    b1, b2, T1, T2, P = synthetic.make_triangulation_pairs(1000, seed=6)
+    pts, valid = ctx.triangulate(b1, b2, T1, T2)
+    opts, ovalid = ba_oracle.triangulate(b1, b2, T1, T2)
+    assert np.array_equal(valid, ovalid) and valid.all()
+    scale = np.linalg.norm(opts, axis=1)
+    assert (np.linalg.norm(pts - opts, axis=1) / scale).max() < 2e-3
+    assert np.median(np.linalg.norm(pts - P, axis=1) / scale) < 1e-3
+    assert ctx.triangulate(b1[:0], b2[:0], T1, T2)[0].shape == (0, 3)
 
 
 def test_golden_window(bindings, ctx):
