@@ -43,6 +43,8 @@ struct vio360_ba {
     bool has_reduced = false, reduced_apply_loss = false, solve_dirty = true, chol_attr_set = false;
     DevBuf d_chol, d_linv, d_x, d_dl, d_reachF;
     int max_reach = 0;   // widest column of the envelope, in blocks
+    int red_band = 1;    // widest row of the chunk envelope in free-pose blocks (k_schur_reduce grid)
+    int band_zero_n = -1;   // S outside the envelope is known to be zero for this n (-1: not known)
     PinBuf h_solve;
     int n_free = 0;
     int shard_rank = 0, shard_world = 1, lm_begin = 0, lm_end = 0;
@@ -512,10 +514,14 @@ static void build_chunks(vio360_ba* ba) {
     for (const SchurChunk& c : ba->chunks)
         for (int p = c.pbase; p < c.pbase + c.span; ++p) ba->cov_ptr[p + 1]++;
     for (int p = 0; p < K; ++p) ba->cov_ptr[p + 1] += ba->cov_ptr[p];
-    ba->cov_idx.assign(std::max(1, ba->cov_ptr[K]), 0);
+    ba->cov_idx.assign(2 * (size_t)std::max(1, ba->cov_ptr[K]), 0);   // (chunk, pbase | span << 16) pairs
     std::vector<int> fill(ba->cov_ptr.begin(), ba->cov_ptr.end() - 1);
     for (int c = 0; c < (int)ba->chunks.size(); ++c)
-        for (int p = ba->chunks[c].pbase; p < ba->chunks[c].pbase + ba->chunks[c].span; ++p) ba->cov_idx[fill[p]++] = c;
+        for (int p = ba->chunks[c].pbase; p < ba->chunks[c].pbase + ba->chunks[c].span; ++p) {
+            ba->cov_idx[2 * (size_t)fill[p]] = c;
+            ba->cov_idx[2 * (size_t)fill[p] + 1] = ba->chunks[c].pbase | (ba->chunks[c].span << 16);
+            fill[p]++;
+        }
     // slot table: per batch of kSMaxLm landmarks, the observation held by thread (pose slot, landmark slot)
     int nbatch_total = 0;
     for (SchurChunk& c : ba->chunks) { c.batch0 = nbatch_total; nbatch_total += (c.lm_end - c.lm_begin + kSMaxLm - 1) / kSMaxLm; }
@@ -539,6 +545,13 @@ static void build_chunks(vio360_ba* ba) {
         for (int p = c.pbase; p < c.pbase + c.span; ++p) ba->reach[p] = std::max(ba->reach[p], c.pbase + c.span - 1);
     ba->free_pose.clear();
     for (int k = 0; k < K; ++k) if (ba->free_map[k] >= 0) ba->free_pose.push_back(k);
+    ba->red_band = 1;
+    for (int bi = 0, bj = 0; bi < (int)ba->free_pose.size(); ++bi) {   // reach is not monotone: scan per row
+        bj = bi;
+        while (bj + 1 < (int)ba->free_pose.size() && ba->free_pose[bj + 1] <= ba->reach[ba->free_pose[bi]]) ++bj;
+        ba->red_band = std::max(ba->red_band, bj - bi + 1);
+    }
+    ba->band_zero_n = -1;
     ba->chunks_dirty = true;
 }
 
@@ -825,7 +838,11 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
     const int n = 6 * ba->n_free;
     const size_t K = ba->K, M = ba->M;
     const size_t packed = (size_t)n * n + n + 1;
-    VIO_CUDA(ctx, ba->d_packed.reserve(packed * 8));
+    {
+        const void* before = ba->d_packed.p;
+        VIO_CUDA(ctx, ba->d_packed.reserve(packed * 8));
+        if (ba->d_packed.p != before) ba->band_zero_n = -1;
+    }
     cudaStream_t st = ctx->stream;
     if (lm_diag) {
         int rcD = vio360_ba_set_lm_diagonal(ba, lm_diag);
@@ -874,22 +891,40 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
             }
             VIO_LAUNCH_CHECK(ctx);
         }
-        if (ctx->debug_sync) { fprintf(stderr, "schur: n=%d nch=%d nirr=%d K=%d cov=%zu\n", n, nch, nirr, ba->K, ba->cov_idx.size()); for (auto& c : ba->chunks) fprintf(stderr, "  chunk lm[%d,%d) pbase %d span %d batch0 %d\n", c.lm_begin, c.lm_end, c.pbase, c.span, c.batch0); }
+        if (ctx->debug_sync) { fprintf(stderr, "schur: n=%d nch=%d nirr=%d K=%d cov=%zu\n", n, nch, nirr, ba->K, ba->cov_idx.size() / 2); for (auto& c : ba->chunks) fprintf(stderr, "  chunk lm[%d,%d) pbase %d span %d batch0 %d\n", c.lm_begin, c.lm_end, c.pbase, c.span, c.batch0); }
         const bool fused = nirr == 0 && n > 0;   // one pass: sum slabs, mirror, LM diagonal, cost
         if (n > 0) {
-            const dim3 nblk(ba->n_free, ba->n_free);
             const double* Dp = ba->use_D ? ba->d_D.as<double>() : nullptr;
-            { KernelTimer kt_(ctx, "k_schur_reduce");
-            if (fused)
-                k_schur_reduce<true><<<nblk, 36 * kRedLanes, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
+            if (fused) {
+                // only the block rows' envelope is summed; the rest of S is zeroed once per structure
+                // (nothing else writes there: the solver factors a copy, an allreduce adds zeros)
+                // (a sharded window is allreduced in place by the caller, which fills the other ranks' envelopes)
+                const bool band = ba->red_band < ba->n_free && ba->shard_world == 1;
+                if (band && ba->band_zero_n != n) {
+                    VIO_CUDA(ctx, cudaMemsetAsync(dS, 0, (size_t)n * n * 8, st));
+                    ba->band_zero_n = n;
+                }
+                const dim3 nblk(band ? ba->red_band : ba->n_free, ba->n_free);
+                KernelTimer kt_(ctx, "k_schur_reduce");
+                // few block pairs (a short window with many chunks per pose): more walkers per pair
+                if ((size_t)nblk.x * nblk.y >= 2000)
+                    k_schur_reduce<true, 7><<<nblk, 36 * 7, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
                                                            ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),
-                                                           ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int>(), ba->d_reach.as<int>(),
-                                                           ba->d_free_pose.as<int>(), Dp, ba->shard_rank == 0);
-            else
-                k_schur_reduce<false><<<nblk, 36 * kRedLanes, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
+                                                           ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int2>(), ba->d_reach.as<int>(),
+                                                           ba->d_free_pose.as<int>(), Dp, ba->shard_rank == 0, band);
+                else
+                    k_schur_reduce<true, 14><<<nblk, 36 * 14, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
+                                                           ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),
+                                                           ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int2>(), ba->d_reach.as<int>(),
+                                                           ba->d_free_pose.as<int>(), Dp, ba->shard_rank == 0, band);
+            } else {
+                ba->band_zero_n = -1;
+                const dim3 nblk(ba->n_free, ba->n_free);
+                KernelTimer kt_(ctx, "k_schur_reduce");
+                k_schur_reduce<false, 7><<<nblk, 36 * 7, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
                                                             ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),
-                                                            ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int>(), ba->d_reach.as<int>(),
-                                                            ba->d_free_pose.as<int>(), Dp, false);
+                                                            ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int2>(), ba->d_reach.as<int>(),
+                                                            ba->d_free_pose.as<int>(), Dp, false, false);
             }
             VIO_LAUNCH_CHECK(ctx);
         }
@@ -907,6 +942,7 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
         }
     } else {
         VIO_CUDA(ctx, cudaMemsetAsync(ba->d_packed.p, 0, packed * 8, st));
+        ba->band_zero_n = -1;
         if (nirr > 0) {
             { KernelTimer kt_(ctx, "k_schur_warp");
             k_schur_warp<<<nb_irr, 128, 0, st>>>(d, ba->lm_begin, ba->lm_end, nullptr, apply_loss != 0, dS, n, drhs, ba->d_partials.as<double>());

@@ -46,6 +46,16 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
         const int w = tid >> 4, ls = tid & 15;
         const int* myslot = slots + (size_t)ch.batch0 * kSProd + tid;
         int oi_next = nbatch > 0 ? __ldg(myslot) : -1;   // observation of slot (w, ls) in batch 0
+        const bool pose_const = w < ch.span ? d.free_map[ch.pbase + w] < 0 : true;
+        // observation data of the batch about to be evaluated: fetched one batch ahead (after
+        // phase A of the previous batch), so that no global-memory latency sits in phase A
+        double nu = 0.0, nv = 0.0, nP0 = 0.0, nP1 = 0.0, nP2 = 0.0;
+        bool nout = false;
+        if (oi_next >= 0) {
+            const size_t l = (size_t)(ch.lm_begin + ls);
+            nu = __ldg(d.u + oi_next); nv = __ldg(d.v + oi_next); nout = __ldg(d.outlier + oi_next) != 0;
+            nP0 = __ldg(d.points + 3 * l); nP1 = __ldg(d.points + 3 * l + 1); nP2 = __ldg(d.points + 3 * l + 2);
+        }
         for (int b = 0; b < nbatch; ++b) {
             const int cur = ch.lm_begin + b * kSMaxLm;
             const int NB = min(kSMaxLm, ch.lm_end - cur);
@@ -53,6 +63,16 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
             double* sRed = Zs;                                  // alias: [kSProd][kSRed]
             const int oi = oi_next;
             if (b + 1 < nbatch) oi_next = __ldg(myslot + (size_t)(b + 1) * kSProd);
+            // phase B inputs, one value per lane (e = 9: constant flag, 10..12: LM diagonal of the
+            // landmark), requested here and first used after phase A
+            double pre = 0.0;
+            if (tid < kSMaxLm * 16) {
+                const int bl = tid >> 4, e = tid & 15;
+                if (bl < NB) {
+                    if (e == 9) pre = __ldg(d.point_fixed + cur + bl) != 0 ? 1.0 : 0.0;
+                    else if (e >= 10 && e < 13 && d.D) pre = __ldg(d.D + 6 * (size_t)d.K + 3 * (size_t)(cur + bl) + (e - 10));
+                } else if (e == 9) pre = 1.0;
+            }
             if (b >= 2) named_bar_sync(kBarEmpty + (b & 1), kSThreads);   // consumers are done with this stage
             // ---- phase A
             double r[2] = {0.0, 0.0}, F[12], E[6];
@@ -61,15 +81,17 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
 #pragma unroll
             for (int j = 0; j < 6; ++j) E[j] = 0.0;
             if (oi >= 0) {
-                const int i = oi;
-                const int p = ch.pbase + w, l = cur + ls;
-                const double Pw[3] = {__ldg(d.points + 3 * (size_t)l), __ldg(d.points + 3 * (size_t)l + 1),
-                                      __ldg(d.points + 3 * (size_t)l + 2)};
-                cost += obs_evaluate<true>(sPose + kPoseStride * w, Pw, d.u[i], d.v[i], d.outlier[i] != 0, d.cam, apply_loss, r, F, E);
-                if (d.free_map[p] < 0) {   // constant pose: no F block (its E block still enters E'E)
+                const double Pw[3] = {nP0, nP1, nP2};
+                cost += obs_evaluate<true>(sPose + kPoseStride * w, Pw, nu, nv, nout, d.cam, apply_loss, r, F, E);
+                if (pose_const) {   // constant pose: no F block (its E block still enters E'E)
 #pragma unroll
                     for (int j = 0; j < 12; ++j) F[j] = 0.0;
                 }
+            }
+            if (b + 1 < nbatch && oi_next >= 0) {
+                const size_t l = (size_t)(cur + kSMaxLm + ls);
+                nu = __ldg(d.u + oi_next); nv = __ldg(d.v + oi_next); nout = __ldg(d.outlier + oi_next) != 0;
+                nP0 = __ldg(d.points + 3 * l); nP1 = __ldg(d.points + 3 * l + 1); nP2 = __ldg(d.points + 3 * l + 2);
             }
             {
                 double* q = sRed + tid * kSRed;
@@ -84,23 +106,24 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
             if (tid < kSMaxLm * 16) {   // 8 whole warps
                 const int bl = tid >> 4, e = tid & 15;
                 double sum = 0.0;
-                if (e < 9) {
+                if (e < 9) {   // four independent partial sums: a 6-deep instead of a 24-deep add chain
+                    double s4[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
-                    for (int pw = 0; pw < kSWin; ++pw) sum += sRed[(pw * kSMaxLm + bl) * kSRed + e];
+                    for (int pw = 0; pw < kSWin; ++pw) s4[pw & 3] += sRed[(pw * kSMaxLm + bl) * kSRed + e];
+                    sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
                 }
                 const int base = lane & 16;
                 double hq[9];
 #pragma unroll
                 for (int j = 0; j < 9; ++j) hq[j] = __shfl_sync(0xffffffffu, sum, base + j);
+                const double lm_const = __shfl_sync(0xffffffffu, pre, base + 9);
+                const double Dl0 = __shfl_sync(0xffffffffu, pre, base + 10), Dl1 = __shfl_sync(0xffffffffu, pre, base + 11),
+                             Dl2 = __shfl_sync(0xffffffffu, pre, base + 12);
                 if (e == 0) {
                     double* q = sLmk + bl * 9;
                     double li[6] = {0, 0, 0, 0, 0, 0}, ig[3] = {0, 0, 0};
-                    if (bl < NB && d.point_fixed[cur + bl] == 0) {
-                        const int l = cur + bl;
-                        if (d.D) {
-                            const double* Dl = d.D + 6 * (size_t)d.K + 3 * (size_t)l;
-                            hq[0] += Dl[0] * Dl[0]; hq[3] += Dl[1] * Dl[1]; hq[5] += Dl[2] * Dl[2];
-                        }
+                    if (lm_const == 0.0) {
+                        hq[0] += Dl0 * Dl0; hq[3] += Dl1 * Dl1; hq[5] += Dl2 * Dl2;   // zeros without an LM diagonal
                         // E'E = L L': only L^-1 is needed (reciprocal square roots, no divisions)
                         const double i00 = vio_rsqrt(hq[0]);
                         const double l10 = hq[1] * i00, l20 = hq[2] * i00;
@@ -215,8 +238,6 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
                 const int bj = blo + bi + rem;
                 bi += blo;
                 const bool diag = bi == bj;
-                const bool vr0 = 2 * bi >= tlo, vr1 = 2 * bi + 1 <= thi, vc0 = 2 * bj >= tlo, vc1 = 2 * bj + 1 <= thi;
-                const bool p00 = vr0 && vc0, p01 = vr0 && vc1, p11 = vr1 && vc1, p10 = !diag && vr1 && vc0;
                 double2* c00 = reinterpret_cast<double2*>(St + schur_tile_index(2 * bi, 2 * bj) * 64) + lane;
                 double2* c01 = reinterpret_cast<double2*>(St + schur_tile_index(2 * bi, 2 * bj + 1) * 64) + lane;
                 double2* c11 = reinterpret_cast<double2*>(St + schur_tile_index(2 * bi + 1, 2 * bj + 1) * 64) + lane;
@@ -225,14 +246,26 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
                 if (!diag) a10 = *c10;
                 const double* za = Zs + fc * kSZPitch + 16 * bi + fr;
                 const double* zb = Zs + fc * kSZPitch + 16 * bj + fr;
+                // two copies of the k loop: a predicated mma.sync costs a WARPSYNC + NOP pair each
+                if (diag) {
 #pragma unroll 4
-                for (int ks = 0; ks < kSK / 4; ++ks) {
-                    const double x0 = -za[4 * ks * kSZPitch], x1 = -za[4 * ks * kSZPitch + 8];
-                    const double y0 = zb[4 * ks * kSZPitch], y1 = zb[4 * ks * kSZPitch + 8];
-                    if (p00) dmma884(a00.x, a00.y, x0, y0);
-                    if (p01) dmma884(a01.x, a01.y, x0, y1);
-                    if (p11) dmma884(a11.x, a11.y, x1, y1);
-                    if (p10) dmma884(a10.x, a10.y, x1, y0);
+                    for (int ks = 0; ks < kSK / 4; ++ks) {
+                        const double x0 = -za[4 * ks * kSZPitch], x1 = -za[4 * ks * kSZPitch + 8];
+                        const double y0 = zb[4 * ks * kSZPitch], y1 = zb[4 * ks * kSZPitch + 8];
+                        dmma884(a00.x, a00.y, x0, y0);
+                        dmma884(a01.x, a01.y, x0, y1);
+                        dmma884(a11.x, a11.y, x1, y1);
+                    }
+                } else {
+#pragma unroll 4
+                    for (int ks = 0; ks < kSK / 4; ++ks) {
+                        const double x0 = -za[4 * ks * kSZPitch], x1 = -za[4 * ks * kSZPitch + 8];
+                        const double y0 = zb[4 * ks * kSZPitch], y1 = zb[4 * ks * kSZPitch + 8];
+                        dmma884(a00.x, a00.y, x0, y0);
+                        dmma884(a01.x, a01.y, x0, y1);
+                        dmma884(a11.x, a11.y, x1, y1);
+                        dmma884(a10.x, a10.y, x1, y0);
+                    }
                 }
                 *c00 = a00; *c01 = a01; *c11 = a11;
                 if (!diag) *c10 = a10;
@@ -294,31 +327,51 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
 // diagonal (levenberg_marquardt_strategy.cc:78-89) and sum the chunk costs, so that no further
 // pass over S is needed; !FULL: upper block triangle only (k_schur_warp then adds the landmarks
 // that fit no window and k_finish_S mirrors).
-constexpr int kRedLanes = 7;
-template <bool FULL>
+template <bool FULL, int kRedLanes>
 __global__ void __launch_bounds__(36 * kRedLanes)
 k_schur_reduce(double* __restrict__ S, int n, double* __restrict__ rhs, double* __restrict__ cost_out,
                const double* __restrict__ partS, const double* __restrict__ partRhs, const double* __restrict__ partCost,
                int nchunks, const SchurChunk* __restrict__ chunks, const int* __restrict__ cov_ptr,
-               const int* __restrict__ cov_idx, const int* __restrict__ reach, const int* __restrict__ free_pose,
-               const double* __restrict__ D, bool add_diag) {
-    const int bj = blockIdx.x, bi = blockIdx.y;
-    if (bi > bj) return;
+               const int2* __restrict__ cov_idx, const int* __restrict__ reach, const int* __restrict__ free_pose,
+               const double* __restrict__ D, bool add_diag, bool band_grid) {
+    // band_grid: blockIdx.x counts block columns from the diagonal (the host sized the grid to the
+    // widest row of the envelope and zeroed S outside it once per structure)
+    const int bi = blockIdx.y, bj = band_grid ? bi + blockIdx.x : blockIdx.x;
+    if (bi > bj || bj >= gridDim.y) return;
     __shared__ double part[kRedLanes][36];
+    __shared__ double partR[kRedLanes][6];
     const int t = threadIdx.x, e = t % 36, g = t / 36;
     const int a = e / 6, b = e - 6 * a;
     const int pi = free_pose[bi], pj = free_pose[bj];
     const int q0 = cov_ptr[pi], q1 = cov_ptr[pi + 1];
-    double s = 0.0;
-    if (pj <= reach[pi] && (bi < bj || a <= b)) {
-        for (int q = q0 + g; q < q1; q += kRedLanes) {
-            const int c = cov_idx[q];
-            const int pbase = chunks[c].pbase, span = chunks[c].span;
-            if (pj < pbase + span)   // pj >= pi >= pbase
-                s += partS[(size_t)c * kST * kST + (size_t)(6 * (pi - pbase) + a) * kST + 6 * (pj - pbase) + b];
+    const bool in_env = pj <= reach[pi] && (bi < bj || a <= b);
+    const bool do_rhs = bi == bj && e < 6;   // the walkers' first six threads also sum the pose's rhs entry e
+    double s = 0.0, sr = 0.0;
+    if (in_env || do_rhs) {
+        // four chunks per round: the (chunk, window) entries and the slab loads of a round are
+        // independent, so a walker pays two memory latencies per four chunks instead of per chunk
+        for (int q = q0 + g; q < q1; q += 4 * kRedLanes) {
+            int c[4];
+            int2 win[4];
+            double v[4], vr[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int2 ent = q + u * kRedLanes < q1 ? __ldg(cov_idx + q + u * kRedLanes) : make_int2(-1, 0);
+                c[u] = ent.x; win[u] = make_int2(ent.y & 0xffff, ent.y >> 16);   // (pbase, span)
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                v[u] = (in_env && c[u] >= 0 && pj < win[u].x + win[u].y)   // pj >= pi >= pbase
+                           ? partS[(size_t)c[u] * kST * kST + (size_t)(6 * (pi - win[u].x) + a) * kST + 6 * (pj - win[u].x) + b]
+                           : 0.0;
+                vr[u] = (do_rhs && c[u] >= 0) ? partRhs[(size_t)c[u] * kST + 6 * (pi - win[u].x) + e] : 0.0;
+            }
+            s += (v[0] + v[1]) + (v[2] + v[3]);
+            sr += (vr[0] + vr[1]) + (vr[2] + vr[3]);
         }
     }
     part[g][e] = s;
+    if (e < 6) partR[g][e] = sr;
     __syncthreads();
     if (t < 36 && (bi < bj || a <= b)) {
         double tot = part[0][e];
@@ -331,11 +384,9 @@ k_schur_reduce(double* __restrict__ S, int n, double* __restrict__ rhs, double* 
     }
     if (bi == bj && t >= 36 && t < 42) {   // rhs of this pose
         const int ar = t - 36;
-        double tot = 0.0;
-        for (int q = q0; q < q1; ++q) {
-            const int c = cov_idx[q];
-            tot += partRhs[(size_t)c * kST + 6 * (pi - chunks[c].pbase) + ar];
-        }
+        double tot = partR[0][ar];
+#pragma unroll
+        for (int k = 1; k < kRedLanes; ++k) tot += partR[k][ar];
         rhs[6 * bi + ar] = tot;
     }
     if (FULL && bi == 0 && bj == 0 && t >= 64 && t < 96) {   // cost: fixed-order sum of the chunk partials

@@ -404,6 +404,17 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
                             "kernel_ms_per_launch": {k: ctx.kernel_time(k)[0] / max(ctx.kernel_time(k)[1], 1)
                                                      for k in ("k_chol_band", "k_chol_band_back", "k_chol_skyline", "k_back_substitute")}}
             ctx.enable_kernel_timing(False)
+            # one whole LM linearisation on the device: parameters in, build + solve, (dx_pose, dx_landmark) back;
+            # the reduced system itself never crosses PCIe
+            t0 = time.perf_counter()
+            for _ in range(5):
+                ba.set_parameters(win["pose_delta"], win["points"])
+                ba.build_reduced_system(D, True, fetch=False)
+                ba.solve_reduced(True)
+            lm_s = (time.perf_counter() - t0) / 5
+            out["e2e_lm_step"] = {"ms_per_step_host_clock": lm_s * 1e3, "value": win["O"] / lm_s, "unit": "obs/s",
+                                  "h2d_bytes_per_step": int(8 * (6 * win["K"] + 3 * win["M"])),
+                                  "d2h_bytes_per_step": int(8 * (6 * win["K"] + 3 * win["M"]))}
         ba.close()
         return out
 

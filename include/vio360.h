@@ -220,7 +220,9 @@ int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_diag, int app
 /* Installs (or, with NULL, clears) the LM diagonal used by later build calls. */
 int vio360_ba_set_lm_diagonal(vio360_ba* ba, const double* lm_diag);
 /* Device view of the last reduced system as ONE packed buffer [S n*n | rhs n | cost 1]
- * so that a single ncclAllReduce(sum, double) combines the shards.  */
+ * so that a single ncclAllReduce(sum, double) combines the shards.
+ * Writable (in-place allreduce) only when a shard is set; without one treat it as
+ * read-only: the library keeps the zeros outside S's block envelope across builds. */
 int vio360_ba_reduced_system_dev(vio360_ba* ba, double** packed_dev, size_t* n_doubles);
 /* Copy the (possibly all-reduced) packed device buffer back to the host. */
 int vio360_ba_fetch_reduced_system(vio360_ba* ba, double* S, double* rhs, double* cost);

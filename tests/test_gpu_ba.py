@@ -170,6 +170,31 @@ def test_sharded_partials_sum_to_full_system(bindings, ctx, synthetic):
     ba.close()
 
 
+def test_rebuild_after_shard_and_parameter_changes(bindings, ctx, synthetic):
+    """The unsharded build only rewrites S inside its block envelope (zeros outside are kept from
+    the first build): rebuilding after a sharded build, and at new parameters, must still match."""
+    win = synthetic.make_ba_window(K=60, M=1500, degree=6, seed=91, mid_iteration=True)
+    ref = _oracle_all(win)
+    ba = bindings.BAWindow(ctx, win)
+    ba.set_parameters(win["pose_delta"], win["points"])
+    S, rhs, _ = ba.build_reduced_system(ref["D"], True)
+    assert rel_err(S, ref["S"]) < TOL and np.count_nonzero(ref["S"]) < 0.6 * S.size      # banded case
+    ba.set_shard(1, 2)
+    ba.build_reduced_system(ref["D"], True)               # fills a different envelope
+    ba.set_shard(0, 1)
+    S2, rhs2, _ = ba.build_reduced_system(ref["D"], True)
+    assert np.array_equal(S2, S) and np.array_equal(rhs2, rhs)
+    rng = np.random.default_rng(5)
+    win2 = dict(win, pose_delta=win["pose_delta"] + 1e-3 * rng.standard_normal(win["pose_delta"].shape),
+                points=win["points"] + 1e-3 * rng.standard_normal(win["points"].shape))
+    ref2 = _oracle_all(win2)
+    ba.set_parameters(win2["pose_delta"], win2["points"])
+    S3, rhs3, _ = ba.build_reduced_system(ref2["D"], True)
+    assert rel_err(S3, ref2["S"]) < TOL and rel_err(rhs3, ref2["rhs"]) < TOL
+    assert not S3[ref2["S"] == 0].any()                   # nothing stale outside the envelope
+    ba.close()
+
+
 def test_large_window_properties(bindings, ctx, synthetic):
     """BASELINE config 5 size (200 keyframes, 1M observations): size-independent checks --
     S symmetric PSD-ish, cost equals the evaluate() cost, linearity of the shard sum, and
