@@ -25,6 +25,7 @@ EXPORTS = [
     "vio360_ba_set_shard", "vio360_ba_set_parameters", "vio360_ba_evaluate",
     "vio360_ba_get_residuals_jacobians", "vio360_ba_normal_blocks", "vio360_ba_reduced_dim",
     "vio360_ba_build_reduced_system", "vio360_ba_set_lm_diagonal", "vio360_ba_reduced_system_dev", "vio360_ba_fetch_reduced_system",
+    "vio360_ba_reduced_band_dev", "vio360_ba_expand_band",
     "vio360_ba_column_sqnorm", "vio360_ba_chi2", "vio360_ba_solve_reduced", "vio360_pnp_evaluate", "vio360_triangulate",
 ]
 
@@ -110,6 +111,8 @@ def load():
                                                    C.POINTER(C.c_double)]
     lib.vio360_ba_set_lm_diagonal.argtypes = [C.c_void_p, C.c_void_p]
     lib.vio360_ba_reduced_system_dev.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
+    lib.vio360_ba_reduced_band_dev.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
+    lib.vio360_ba_expand_band.argtypes = [C.c_void_p]
     lib.vio360_ba_fetch_reduced_system.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]
     lib.vio360_ba_column_sqnorm.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
     lib.vio360_ba_chi2.argtypes = [C.c_void_p, C.c_double, C.c_void_p, C.c_void_p]
@@ -418,6 +421,17 @@ class BAWindow:
         p = C.c_void_p(); n = C.c_size_t(0)
         self.ctx.check(self.lib.vio360_ba_reduced_system_dev(self.h, C.byref(p), C.byref(n)))
         return p.value, n.value
+
+    def reduced_band_dev(self):
+        """(device pointer, doubles) of the block-band exchange buffer of a sharded build, or None when the
+        last build has none (not sharded / landmarks outside the chunk windows)."""
+        p = C.c_void_p(); n = C.c_size_t(0)
+        if self.lib.vio360_ba_reduced_band_dev(self.h, C.byref(p), C.byref(n)) != 0:
+            return None
+        return p.value, n.value
+
+    def expand_band(self):
+        self.ctx.check(self.lib.vio360_ba_expand_band(self.h))
 
     def fetch_reduced_system(self):
         n = self.reduced_dim

@@ -45,6 +45,9 @@ struct vio360_ba {
     int max_reach = 0;   // widest column of the envelope, in blocks
     int red_band = 1;    // widest row of the chunk envelope in free-pose blocks (k_schur_reduce grid)
     int band_zero_n = -1;   // S outside the envelope is known to be zero for this n (-1: not known)
+    DevBuf d_band;          // sharded builds: compact exchange buffer [n_free][band_w][36] | rhs | cost
+    int band_w = 0;         // block columns per row in d_band (0: the last build was dense)
+    bool dense_stale = false;   // d_packed has to be re-expanded from d_band before it is read
     PinBuf h_solve;
     int n_free = 0;
     int shard_rank = 0, shard_world = 1, lm_begin = 0, lm_end = 0;
@@ -460,7 +463,7 @@ extern "C" void vio360_ba_destroy(vio360_ba* ba) {
                       &ba->d_points, &ba->d_free_map, &ba->d_point_fixed, &ba->d_D, &ba->d_r, &ba->d_Jp, &ba->d_Jl,
                       &ba->d_partials, &ba->d_packed, &ba->d_blocks, &ba->d_chi2, &ba->d_flag,
                       &ba->d_chunks, &ba->d_cov_ptr, &ba->d_cov_idx, &ba->d_free_pose, &ba->d_irregular, &ba->d_partS, &ba->d_partRhs, &ba->d_reach, &ba->d_slots, &ba->d_batch_rng,
-                      &ba->d_chol, &ba->d_linv, &ba->d_x, &ba->d_dl, &ba->d_reachF};
+                      &ba->d_chol, &ba->d_linv, &ba->d_x, &ba->d_dl, &ba->d_reachF, &ba->d_band};
     for (DevBuf* b : bufs) b->release();
     ba->pin.release();
     ba->h_solve.release();
@@ -899,32 +902,48 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
                 // only the block rows' envelope is summed; the rest of S is zeroed once per structure
                 // (nothing else writes there: the solver factors a copy, an allreduce adds zeros)
                 // (a sharded window is allreduced in place by the caller, which fills the other ranks' envelopes)
-                const bool band = ba->red_band < ba->n_free && ba->shard_world == 1;
-                if (band && ba->band_zero_n != n) {
+                const bool sharded = ba->shard_world > 1;
+                const bool band = sharded || ba->red_band < ba->n_free;
+                double* outS = dS; double* outRhs = drhs; double* outCost = dcost;
+                int band_w = 0;
+                if (sharded) {
+                    // compact exchange buffer: chunk windows are kSWin poses wide on every rank, so block
+                    // row bi never reaches past bi + kSWin - 1 (every slot inside the grid is rewritten)
+                    band_w = std::min(ba->n_free, kSWin);
+                    const size_t nd = (size_t)ba->n_free * band_w * 36 + n + 1;
+                    if (ba->d_band.bytes < nd * 8) {
+                        VIO_CUDA(ctx, ba->d_band.reserve(nd * 8));
+                        VIO_CUDA(ctx, cudaMemsetAsync(ba->d_band.p, 0, nd * 8, st));   // slots past the last block column
+                    }
+                    outS = ba->d_band.as<double>(); outRhs = outS + (size_t)ba->n_free * band_w * 36; outCost = outRhs + n;
+                    ba->band_zero_n = -1;
+                } else if (band && ba->band_zero_n != n) {
                     VIO_CUDA(ctx, cudaMemsetAsync(dS, 0, (size_t)n * n * 8, st));
                     ba->band_zero_n = n;
                 }
-                const dim3 nblk(band ? ba->red_band : ba->n_free, ba->n_free);
+                ba->band_w = band_w; ba->dense_stale = sharded;
+                double* dS = outS; double* drhs = outRhs; double* dcost = outCost;   // shadow: the launches below write here
+                const dim3 nblk(sharded ? band_w : (band ? ba->red_band : ba->n_free), ba->n_free);
                 KernelTimer kt_(ctx, "k_schur_reduce");
                 // few block pairs (a short window with many chunks per pose): more walkers per pair
                 if ((size_t)nblk.x * nblk.y >= 2000)
                     k_schur_reduce<true, 7><<<nblk, 36 * 7, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
                                                            ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),
                                                            ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int2>(), ba->d_reach.as<int>(),
-                                                           ba->d_free_pose.as<int>(), Dp, ba->shard_rank == 0, band);
+                                                           ba->d_free_pose.as<int>(), Dp, ba->shard_rank == 0, band, band_w);
                 else
                     k_schur_reduce<true, 14><<<nblk, 36 * 14, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
                                                            ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),
                                                            ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int2>(), ba->d_reach.as<int>(),
-                                                           ba->d_free_pose.as<int>(), Dp, ba->shard_rank == 0, band);
+                                                           ba->d_free_pose.as<int>(), Dp, ba->shard_rank == 0, band, band_w);
             } else {
-                ba->band_zero_n = -1;
+                ba->band_zero_n = -1; ba->band_w = 0; ba->dense_stale = false;
                 const dim3 nblk(ba->n_free, ba->n_free);
                 KernelTimer kt_(ctx, "k_schur_reduce");
                 k_schur_reduce<false, 7><<<nblk, 36 * 7, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
                                                             ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),
                                                             ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int2>(), ba->d_reach.as<int>(),
-                                                            ba->d_free_pose.as<int>(), Dp, false, false);
+                                                            ba->d_free_pose.as<int>(), Dp, false, false, 0);
             }
             VIO_LAUNCH_CHECK(ctx);
         }
@@ -942,7 +961,7 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
         }
     } else {
         VIO_CUDA(ctx, cudaMemsetAsync(ba->d_packed.p, 0, packed * 8, st));
-        ba->band_zero_n = -1;
+        ba->band_zero_n = -1; ba->band_w = 0; ba->dense_stale = false;
         if (nirr > 0) {
             { KernelTimer kt_(ctx, "k_schur_warp");
             k_schur_warp<<<nb_irr, 128, 0, st>>>(d, ba->lm_begin, ba->lm_end, nullptr, apply_loss != 0, dS, n, drhs, ba->d_partials.as<double>());
@@ -964,9 +983,41 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
     return VIO360_OK;   // asynchronous on the context's stream
 }
 
+// Sharded builds leave their result in the compact band buffer; the dense [S | rhs | cost] view is
+// produced on first use (and again by vio360_ba_expand_band after the caller's allreduce).
+static int ensure_dense(vio360_ba* ba) {
+    if (!ba->dense_stale) return VIO360_OK;
+    vio360_ctx* ctx = ba->ctx;
+    const size_t n = 6 * (size_t)ba->n_free, total = n * n + n + 1;
+    { KernelTimer kt_(ctx, "k_expand_band");
+    k_expand_band<<<(unsigned)((total + 255) / 256), 256, 0, ctx->stream>>>(ba->d_band.as<double>(), ba->n_free, ba->band_w, ba->d_packed.as<double>());
+    }
+    VIO_LAUNCH_CHECK(ctx);
+    ba->dense_stale = false;
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_reduced_band_dev(vio360_ba* ba, double** band_dev, size_t* n_doubles) {
+    if (!ba || !band_dev || !n_doubles) return VIO360_ERR_INVALID;
+    if (!ba->has_reduced) return vio360_fail(ba->ctx, VIO360_ERR_STATE, "no reduced system built yet");
+    if (ba->band_w <= 0)
+        return vio360_fail(ba->ctx, VIO360_ERR_STATE, "the last build has no compact exchange buffer (no shard set, or landmarks outside the chunk windows): use vio360_ba_reduced_system_dev");
+    *band_dev = ba->d_band.as<double>();
+    *n_doubles = (size_t)ba->n_free * ba->band_w * 36 + 6 * (size_t)ba->n_free + 1;
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_expand_band(vio360_ba* ba) {
+    if (!ba) return VIO360_ERR_INVALID;
+    if (!ba->has_reduced || ba->band_w <= 0) return vio360_fail(ba->ctx, VIO360_ERR_STATE, "ba_expand_band: no compact exchange buffer");
+    ba->dense_stale = true;
+    return ensure_dense(ba);
+}
+
 extern "C" int vio360_ba_reduced_system_dev(vio360_ba* ba, double** packed_dev, size_t* n_doubles) {
     if (!ba || !packed_dev || !n_doubles) return VIO360_ERR_INVALID;
     if (!ba->has_reduced) return vio360_fail(ba->ctx, VIO360_ERR_STATE, "no reduced system built yet");
+    { int rcE = ensure_dense(ba); if (rcE) return rcE; }
     const size_t n = 6 * (size_t)ba->n_free;
     *packed_dev = ba->d_packed.as<double>();
     *n_doubles = n * n + n + 1;
@@ -977,6 +1028,7 @@ extern "C" int vio360_ba_fetch_reduced_system(vio360_ba* ba, double* S, double* 
     if (!ba) return VIO360_ERR_INVALID;
     vio360_ctx* ctx = ba->ctx;
     if (!ba->has_reduced) return vio360_fail(ctx, VIO360_ERR_STATE, "no reduced system built yet");
+    { int rcE = ensure_dense(ba); if (rcE) return rcE; }
     VIO_CUDA(ctx, cudaSetDevice(ctx->device));
     const size_t n = 6 * (size_t)ba->n_free;
     double* dS = ba->d_packed.as<double>();
@@ -1138,6 +1190,7 @@ extern "C" int vio360_ba_solve_reduced(vio360_ba* ba, double* delta_pose, double
     if (!ba->has_reduced) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_solve_reduced before ba_build_reduced_system");
     if (!delta_pose) return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_solve_reduced: delta_pose is required");
     VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    { int rcE = ensure_dense(ba); if (rcE) return rcE; }
     cudaStream_t st = ctx->stream;
     const int nb = ba->n_free, K = ba->K, M = ba->M;
     const size_t n = 6 * (size_t)nb;

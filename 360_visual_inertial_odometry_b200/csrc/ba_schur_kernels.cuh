@@ -319,6 +319,24 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
     }
 }
 
+// Dense S (both triangles) + rhs + cost from the compact band buffer [n_free][band_w][36 | rhs n | cost]
+__global__ void __launch_bounds__(256)
+k_expand_band(const double* __restrict__ band, int n_free, int band_w, double* __restrict__ packed) {
+    const int n = 6 * n_free;
+    const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t nn = (size_t)n * n;
+    if (idx < nn) {
+        const int i = (int)(idx / n), j = (int)(idx - (size_t)i * n);
+        const int bi = i / 6, bj = j / 6, a = i - 6 * bi, b = j - 6 * bj;
+        double v = 0.0;
+        if (bj >= bi) { if (bj - bi < band_w) v = band[((size_t)bi * band_w + (bj - bi)) * 36 + 6 * a + b]; }
+        else if (bi - bj < band_w) v = band[((size_t)bj * band_w + (bi - bj)) * 36 + 6 * b + a];
+        packed[idx] = v;
+    } else if (idx < nn + n + 1) {
+        packed[idx] = band[(size_t)n_free * band_w * 36 + (idx - nn)];
+    }
+}
+
 // Sums the chunk slabs into S (and rhs, cost) in a fixed order: one CTA per pair of free poses
 // (bi <= bj), thread = (entry of the 6x6 block, one of kRedLanes strided walkers of the list of
 // chunks covering pose bi); the walkers' partial sums are combined in a fixed order.
@@ -333,7 +351,7 @@ k_schur_reduce(double* __restrict__ S, int n, double* __restrict__ rhs, double* 
                const double* __restrict__ partS, const double* __restrict__ partRhs, const double* __restrict__ partCost,
                int nchunks, const SchurChunk* __restrict__ chunks, const int* __restrict__ cov_ptr,
                const int2* __restrict__ cov_idx, const int* __restrict__ reach, const int* __restrict__ free_pose,
-               const double* __restrict__ D, bool add_diag, bool band_grid) {
+               const double* __restrict__ D, bool add_diag, bool band_grid, int band_w) {
     // band_grid: blockIdx.x counts block columns from the diagonal (the host sized the grid to the
     // widest row of the envelope and zeroed S outside it once per structure)
     const int bi = blockIdx.y, bj = band_grid ? bi + blockIdx.x : blockIdx.x;
@@ -379,8 +397,15 @@ k_schur_reduce(double* __restrict__ S, int n, double* __restrict__ rhs, double* 
         for (int k = 1; k < kRedLanes; ++k) tot += part[k][e];
         if (FULL && bi == bj && a == b && add_diag && D) { const double dd = D[6 * (size_t)pi + a]; tot += dd * dd; }
         const size_t ri = 6 * (size_t)bi + a, rj = 6 * (size_t)bj + b;
-        S[ri * n + rj] = tot;
-        if (FULL && ri != rj) S[rj * n + ri] = tot;
+        if (FULL && band_w > 0) {
+            // compact exchange layout [block row bi][bj - bi < band_w][6 x 6] (vio360_ba_reduced_band_dev)
+            double* blk = S + ((size_t)bi * band_w + (bj - bi)) * 36;
+            blk[6 * a + b] = tot;
+            if (bi == bj && a != b) blk[6 * b + a] = tot;
+        } else {
+            S[ri * n + rj] = tot;
+            if (FULL && ri != rj) S[rj * n + ri] = tot;
+        }
     }
     if (bi == bj && t >= 36 && t < 42) {   // rhs of this pose
         const int ar = t - 36;

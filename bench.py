@@ -249,6 +249,9 @@ def run_ours(args):
     # ---- BA factor evaluation
     if not args.skip_ba:
         line["ba"] = bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, args)
+    # ---- configs[3]: 8K tracking, 64 sequences over the ranks (re-configures the front end: keep it last)
+    if not args.skip_c4:
+        line["tracking_c4"] = bench_c4(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, args)
     if rank == 0 and world == 1 and not args.skip_cpu:
         line["cpu_baseline"] = cpu_baseline_tracking(ring, pts_h, torch)
     if world > 1:
@@ -256,6 +259,71 @@ def run_ours(args):
         dist.destroy_process_group()
     if rank == 0:
         print(json.dumps(line))
+
+
+def bench_c4(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, args):
+    """BASELINE configs[3]: 7680x3840, 3000 features per frame, 64 independent sequences sharded over the
+    ranks (sequence s -> rank s mod world, no collective): strong scaling of one 64-frame step."""
+    W4, H4, N4, SEQ = 7680, 3840, 3000, 64
+    mine = [s for s in range(SEQ) if s % world == rank]
+    B4 = len(mine)
+    ctx.fe_configure(W4, H4, max_points=N4, max_batch=B4)
+    ring = [[], []]
+    for s in mine:
+        for t in (0, 1):
+            ring[t].append(syn.render_erp_frame(W4, H4, t, seed=360 + s, n_waves=24, sigma_omega=240.0, xp=torch, device=device))
+    pts_d = torch.from_numpy(np.stack([syn.make_track_points(W4, H4, N4, seed=3000 + s) for s in mine])).to(device)
+    out_xy = torch.zeros((B4, N4, 2), dtype=torch.float32, device=device)
+    out_st = torch.zeros((B4, N4), dtype=torch.uint8, device=device)
+    out_err = torch.zeros((B4, N4), dtype=torch.float32, device=device)
+    out_keep = torch.zeros((B4, N4), dtype=torch.uint8, device=device)
+    tables = []
+    for par in range(2):
+        jobs = (b.TrackJob * B4)()
+        for i in range(B4):
+            j = jobs[i]
+            j.prev, j.prev_pitch, j.cur, j.cur_pitch = ring[par][i].data_ptr(), W4, ring[1 - par][i].data_ptr(), W4
+            j.prev_xy, j.n = pts_d[i].data_ptr(), N4
+            j.cur_xy, j.status, j.err, j.keep = out_xy[i].data_ptr(), out_st[i].data_ptr(), out_err[i].data_ptr(), out_keep[i].data_ptr()
+        tables.append(jobs)
+
+    def step(i):
+        jobs = tables[i % 2]
+        for k in range(B4):
+            jobs[k].prev_key = (1 << 44) + i * B4 + k
+            jobs[k].cur_key = (1 << 44) + (i + 1) * B4 + k
+        ctx.fe_track_batch_raw(jobs, B4, b.MEM_DEVICE)
+
+    steps = max(2, min(args.steps, 6))
+    for i in range(3):
+        step(i)
+    barrier()
+    ctx.enable_kernel_timing(True); ctx.reset_kernel_times()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for i in range(3, 3 + steps):
+        step(i)
+    e1.record(stream)
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    lk_ms, lk_n = ctx.kernel_time("k_lk_track")
+    pyr_ms, _ = ctx.kernel_time("k_pyr_down")
+    ctx.enable_kernel_timing(False)
+    step_ms = float(ms.item()) / steps
+    frame_bytes = 1.640625 * W4 * H4 + N4 * 4 * 1013 + 21 * N4      # SURVEY 8-D tracking frame
+    hbm_peak = measured_peaks()[0]
+    fps = SEQ / (step_ms * 1e-3)
+    tracked = torch.tensor([int(out_st.sum().item())], dtype=torch.int64, device=device)
+    if world > 1:
+        dist.all_reduce(tracked)
+    return {"metric": "ERP frames/s @7680x3840, 3000 feats (64 sequences over all ranks)", "value": fps, "unit": "frames/s",
+            "scaling": "strong", "n_gpus": world, "sequences_per_gpu": B4, "steps": steps, "ms_per_step": step_ms,
+            "kernel_ms_per_launch": {"k_lk_track": lk_ms / max(lk_n, 1), "k_pyr_down_per_step": pyr_ms / steps},
+            "tracked_points_last_step": int(tracked.item()),
+            "roofline": {"bound": "hbm", "algorithmic_bytes_per_frame": frame_bytes, "achieved": fps / world * frame_bytes / 1e9,
+                         "peak": hbm_peak, "unit": "GB/s", "frac": fps / world * frame_bytes / 1e9 / hbm_peak}}
 
 
 def bench_ransac(ctx, syn):
@@ -343,7 +411,11 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
         ba.build_reduced_system(None, True, fetch=False)
         ptr, nd = ba.reduced_system_dev()
 
-        class _Buf:   # zero-copy torch view of the packed [S | rhs | cost] device buffer
+        band = ba.reduced_band_dev() if (sharded and world > 1) else None
+        if band is not None:      # block-band payload [blocks | rhs | cost] (1.4 MB instead of 11.4 MB at 200 keyframes)
+            ptr, nd = band
+
+        class _Buf:   # zero-copy torch view of the exchange buffer
             __cuda_array_interface__ = {"shape": (nd,), "typestr": "<f8", "data": (ptr, False), "version": 2}
         packed = torch.as_tensor(_Buf(), device=device)
 
@@ -351,7 +423,9 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
             ba.build_reduced_system(None, True, fetch=False)
             if sharded and world > 1:
                 with torch.cuda.stream(stream):
-                    dist.all_reduce(packed)     # one allreduce of [S | rhs | cost]
+                    dist.all_reduce(packed)     # one allreduce of the exchange buffer
+                if band is not None:
+                    ba.expand_band()            # dense [S | rhs | cost] for the solver, on the same stream
         for _ in range(warmup):
             step()
         barrier()
@@ -365,7 +439,7 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
         ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        ktimes = {name: ctx.kernel_time(name) for name in ("k_schur_tile", "k_schur_reduce", "k_schur_warp", "k_finish_S", "k_sum_partials")}
+        ktimes = {name: ctx.kernel_time(name) for name in ("k_schur_tile", "k_schur_reduce", "k_schur_warp", "k_finish_S", "k_sum_partials", "k_expand_band")}
         dom = max(ktimes, key=lambda k: ktimes[k][0])
         k_ms, k_n = ktimes[dom]
         ctx.enable_kernel_timing(False)
@@ -377,6 +451,8 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
             if sharded and world > 1:
                 with torch.cuda.stream(stream):
                     dist.all_reduce(packed)
+                if band is not None:
+                    ba.expand_band()
                 ba.fetch_reduced_system()
         barrier()
         e2e_s = (time.perf_counter() - t0) / max(2, steps // 2)
@@ -385,7 +461,7 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
         flops = 451.0 * win["O"] + float(np.sum(50 + 130 * deg + 216 * deg * (deg + 1) / 2))
         out = {"O": int(win["O"]), "K": int(win["K"]), "M": int(win["M"]), "ms_per_step": float(ms.item()) / steps,
                "value": win["O"] / (float(ms.item()) / steps * 1e-3), "e2e_value": win["O"] / e2e_s,
-               "algorithmic_flop_per_step": flops,
+               "algorithmic_flop_per_step": flops, "allreduce_doubles": int(nd) if (sharded and world > 1) else 0,
                "roofline": {"bound": "fp64", "kernel": dom, "achieved": flops / world / (k_ms / max(k_n, 1) * 1e-3) / 1e12 if k_ms > 0 else None,
                             "peak": fp64_peak, "unit": "TFLOP/s", "avg_launch_ms": k_ms / max(k_n, 1),
                             "kernel_ms_per_step": {k: v[0] / steps for k, v in ktimes.items() if v[1] > 0}},
@@ -535,6 +611,7 @@ def main():
     ap.add_argument("--skip-ba", action="store_true")
     ap.add_argument("--skip-detect", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--skip-c4", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else max(args.warmup, 1)
     if args.impl == "reference":

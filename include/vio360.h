@@ -224,6 +224,14 @@ int vio360_ba_set_lm_diagonal(vio360_ba* ba, const double* lm_diag);
  * Writable (in-place allreduce) only when a shard is set; without one treat it as
  * read-only: the library keeps the zeros outside S's block envelope across builds. */
 int vio360_ba_reduced_system_dev(vio360_ba* ba, double** packed_dev, size_t* n_doubles);
+/* Block-sparse exchange payload of a SHARDED build (SURVEY.md 8-E "block-sparse upper-triangular S"):
+ * [n_free block rows][w block columns from the diagonal][6 x 6 row-major] | rhs n | cost 1, with
+ * w = min(n_free, 24) identical on every rank (1.4 MB instead of 11.4 MB for 200 keyframes).
+ * Allreduce it in place (sum, double), then call vio360_ba_expand_band: the dense view, the fetch
+ * and the solver then see the summed system.  VIO360_ERR_STATE when the last build was not
+ * sharded or had landmarks outside the chunk windows (then allreduce the dense buffer instead). */
+int vio360_ba_reduced_band_dev(vio360_ba* ba, double** band_dev, size_t* n_doubles);
+int vio360_ba_expand_band(vio360_ba* ba);
 /* Copy the (possibly all-reduced) packed device buffer back to the host. */
 int vio360_ba_fetch_reduced_system(vio360_ba* ba, double* S, double* rhs, double* cost);
 

@@ -46,12 +46,17 @@ def _worker(rank, world, port, out):
     S, rhs, _ = W.schur(rs, Jps, Jls, Dr)
     packed = torch.from_numpy(np.concatenate([S.ravel(), rhs, [cs]]))
     dist.all_reduce(packed)              # the one collective of the path
+    # the same exchange with the block-band payload (vio360_ba_reduced_band_dev / vio360_ba_expand_band)
+    band = torch.from_numpy(sharding.band_pack(S, rhs, cs, band_w=8))
+    dist.all_reduce(band)
     if rank == 0:
         Sf, rhsf, _ = full.schur(r, Jp, Jl, D)
         n = Sf.shape[0]
         got = packed.numpy()
         rel = lambda a, b: float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
-        np.save(out, np.array([rel(got[:n * n], Sf.ravel()), rel(got[n * n:n * n + n], rhsf), abs(got[-1] - cost) / cost]))
+        Sb, rhsb, cb = sharding.band_expand(band.numpy(), n // 6, band_w=8)
+        np.save(out, np.array([rel(got[:n * n], Sf.ravel()), rel(got[n * n:n * n + n], rhsf), abs(got[-1] - cost) / cost,
+                               rel(Sb, Sf), rel(rhsb, rhsf), abs(cb - cost) / cost, band.numel() / packed.numel()]))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -77,3 +82,21 @@ def test_two_rank_schur_allreduce(tmp_path):
     mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
     res = np.load(out)
     assert res[0] < 1e-9 and res[1] < 1e-9 and res[2] < 1e-12
+    assert res[3] < 1e-9 and res[4] < 1e-9 and res[5] < 1e-12 and res[6] < 0.75      # band payload: same sums, fewer bytes
+
+
+def test_band_pack_expand_round_trip():
+    sys.path.insert(0, ROOT)
+    import importlib
+    sharding = importlib.import_module(PKG + ".sharding")
+    rng = np.random.default_rng(3)
+    for n_free in (1, 5, 24, 40):
+        w = min(n_free, sharding.BAND_BLOCKS)
+        A = rng.standard_normal((6 * n_free, 6 * n_free)); S = A + A.T
+        bi = np.arange(6 * n_free) // 6
+        S[np.abs(bi[:, None] - bi[None, :]) >= w] = 0.0
+        rhs = rng.standard_normal(6 * n_free)
+        buf = sharding.band_pack(S, rhs, 2.5)
+        assert buf.size == n_free * w * 36 + 6 * n_free + 1
+        S2, rhs2, c2 = sharding.band_expand(buf, n_free)
+        assert np.array_equal(S2, S) and np.array_equal(rhs2, rhs) and c2 == 2.5

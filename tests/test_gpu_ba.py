@@ -195,6 +195,49 @@ def test_rebuild_after_shard_and_parameter_changes(bindings, ctx, synthetic):
     ba.close()
 
 
+def test_band_exchange_buffer_sums_to_full_system(bindings, ctx, synthetic):
+    """The compact block-band payload of sharded builds: summing the ranks' band buffers
+    on the device and expanding gives the full reduced system, and the solver sees the sum."""
+    import torch
+    win = synthetic.make_ba_window(K=40, M=1500, degree=8, seed=78, mid_iteration=True)
+    ref = _oracle_all(win)
+    world = 3
+    bas = []
+    for rank in range(world):
+        ba = bindings.BAWindow(ctx, win)
+        ba.set_shard(rank, world)
+        ba.set_parameters(win["pose_delta"], win["points"])
+        ba.build_reduced_system(ref["D"], True, fetch=False)
+        bas.append(ba)
+    ctx.synchronize()
+    views = []
+    for ba in bas:
+        ptr, nd = ba.reduced_band_dev()
+        assert nd == ba.reduced_dim // 6 * min(ba.reduced_dim // 6, 24) * 36 + ba.reduced_dim + 1
+
+        class _Buf:
+            __cuda_array_interface__ = {"shape": (nd,), "typestr": "<f8", "data": (ptr, False), "version": 2}
+        views.append(torch.as_tensor(_Buf(), device="cuda:0"))
+    part0 = bas[0].fetch_reduced_system()                  # rank 0's partial through the lazy dense view
+    views[0] += views[1] + views[2]                        # what the allreduce does
+    torch.cuda.synchronize()
+    bas[0].expand_band()
+    S, rhs, cost = bas[0].fetch_reduced_system()
+    assert rel_err(S, ref["S"]) < TOL and rel_err(rhs, ref["rhs"]) < TOL and abs(cost - ref["cost"]) < TOL * ref["cost"]
+    assert np.array_equal(S, S.T) and not np.array_equal(part0[0], S)
+    dp, _ = bas[0].solve_reduced(False)
+    Wo = ba_oracle.Window(win)
+    So, rhso, fm = Wo.schur(ref["r"], ref["Jp"], ref["Jl"], ref["D"])
+    dp_ref, _ = Wo.solve_step(ref["r"], ref["Jp"], ref["Jl"], ref["D"], So, rhso, fm)
+    assert rel_err(dp, dp_ref) < 1e-7
+    # an unsharded build has no band buffer
+    bas[1].set_shard(0, 1)
+    bas[1].build_reduced_system(ref["D"], True, fetch=False)
+    assert bas[1].reduced_band_dev() is None
+    for ba in bas:
+        ba.close()
+
+
 def test_large_window_properties(bindings, ctx, synthetic):
     """BASELINE config 5 size (200 keyframes, 1M observations): size-independent checks --
     S symmetric PSD-ish, cost equals the evaluate() cost, linearity of the shard sum, and

@@ -203,3 +203,25 @@ def test_full_size_properties_c2(ctx, synthetic):
     assert np.array_equal(st, ost) and np.abs(xy - oxy)[ost == 1].max() < POS_TOL
     inner = (ost == 1) & (pts[:, 0] > 200) & (pts[:, 0] < W - 200)
     assert np.median(np.abs(xy[inner, 0] - pts[inner, 0] - 3.0)) < 0.05
+
+
+def test_full_size_properties_c4(ctx, synthetic):
+    """BASELINE config 4 size (7680x3840, 3000 features per frame): a two-sequence batch against the
+    oracle on a shifted frame pair, a frame tracked onto itself, and the detector on the 8K frame."""
+    W, H = 7680, 3840
+    f0 = synthetic.render_erp_frame(W, H, 0, seed=361, n_waves=16, sigma_omega=120.0)
+    f1 = np.roll(np.roll(f0, 2, axis=1), 1, axis=0)
+    pts = synthetic.make_track_points(W, H, 3000, seed=1001)
+    ctx.fe_configure(W, H, max_points=3000, max_batch=2)
+    out = ctx.fe_track_batch_host([(f0, f1, pts, 1, 2), (f0, f0, pts[:2500], 1, 1)])
+    oxy, ost, oerr, _ = fo.lk_track(f0, f1, pts)
+    xy, st, err, keep = out[0]
+    assert np.array_equal(st, ost) and np.abs(xy - oxy)[ost == 1].max() < POS_TOL
+    assert np.array_equal(keep, fo.post_filter(xy, st, W, H, 0.15, 20.0))
+    inner = (ost == 1) & (pts[:, 0] > 200) & (pts[:, 0] < W - 200)
+    assert np.median(np.abs(xy[inner, 0] - pts[inner, 0] - 2.0)) < 0.05
+    xy0, st0, err0, _ = out[1]
+    assert np.array_equal(st0, fo.lk_track(f0, f0, pts[:2500])[1])
+    assert np.abs(xy0 - pts[:2500])[st0 == 1].max() < 1e-3 and err0[st0 == 1].max() == 0.0
+    ocorners = fo.good_features(f0, fo.base_mask(W, H), 3000)
+    assert np.array_equal(ctx.fe_detect(f0, None, 3000), ocorners) and len(ocorners) > 1000
