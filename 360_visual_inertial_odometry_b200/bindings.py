@@ -13,6 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libvio360_cuda.so")
 
 MEM_HOST, MEM_DEVICE = 0, 1
+PEER_BLOB_BYTES = 128   # VIO360_PEER_BLOB_BYTES
 
 EXPORTS = [
     "vio360_version", "vio360_create", "vio360_destroy", "vio360_last_error", "vio360_synchronize",
@@ -26,6 +27,7 @@ EXPORTS = [
     "vio360_ba_get_residuals_jacobians", "vio360_ba_normal_blocks", "vio360_ba_reduced_dim",
     "vio360_ba_build_reduced_system", "vio360_ba_set_lm_diagonal", "vio360_ba_reduced_system_dev", "vio360_ba_fetch_reduced_system",
     "vio360_ba_reduced_band_dev", "vio360_ba_expand_band",
+    "vio360_ba_peer_export", "vio360_ba_peer_attach", "vio360_ba_peer_exchange", "vio360_ba_peer_detach",
     "vio360_ba_column_sqnorm", "vio360_ba_chi2", "vio360_ba_solve_reduced", "vio360_pnp_evaluate", "vio360_triangulate",
 ]
 
@@ -113,6 +115,10 @@ def load():
     lib.vio360_ba_reduced_system_dev.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
     lib.vio360_ba_reduced_band_dev.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
     lib.vio360_ba_expand_band.argtypes = [C.c_void_p]
+    lib.vio360_ba_peer_export.argtypes = [C.c_void_p, C.c_void_p]
+    lib.vio360_ba_peer_attach.argtypes = [C.c_void_p, C.c_void_p]
+    lib.vio360_ba_peer_exchange.argtypes = [C.c_void_p]
+    lib.vio360_ba_peer_detach.argtypes = [C.c_void_p]
     lib.vio360_ba_fetch_reduced_system.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]
     lib.vio360_ba_column_sqnorm.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
     lib.vio360_ba_chi2.argtypes = [C.c_void_p, C.c_double, C.c_void_p, C.c_void_p]
@@ -432,6 +438,24 @@ class BAWindow:
 
     def expand_band(self):
         self.ctx.check(self.lib.vio360_ba_expand_band(self.h))
+
+    def peer_export(self):
+        """This rank's exchange-buffer descriptor (bytes) for vio360_ba_peer_attach on every rank."""
+        blob = C.create_string_buffer(PEER_BLOB_BYTES)
+        self.ctx.check(self.lib.vio360_ba_peer_export(self.h, blob))
+        return blob.raw
+
+    def peer_attach(self, blobs):
+        """blobs: the world's descriptors in rank order (list of bytes)."""
+        raw = b"".join(blobs)
+        assert len(raw) % PEER_BLOB_BYTES == 0
+        self.ctx.check(self.lib.vio360_ba_peer_attach(self.h, C.c_char_p(raw)))
+
+    def peer_exchange(self):
+        self.ctx.check(self.lib.vio360_ba_peer_exchange(self.h))
+
+    def peer_detach(self):
+        self.ctx.check(self.lib.vio360_ba_peer_detach(self.h))
 
     def fetch_reduced_system(self):
         n = self.reduced_dim

@@ -8,10 +8,13 @@
 //   K10 k_chi2              chi-square classification
 // Observations are re-ordered landmark-major once, in set_structure, so that every
 // landmark is a contiguous segment; results are scattered back to the caller's order.
+#include <unistd.h>
+
 #include <algorithm>
 #include <numeric>
 
 #include "ba_math.cuh"
+#include "ba_peer.cuh"
 #include "ba_schur.cuh"
 #include "common.cuh"
 
@@ -66,7 +69,33 @@ struct vio360_ba {
     std::vector<int> irregular, cov_ptr, cov_idx, free_pose, reach, slot_table, batch_rng;
     DevBuf d_chunks, d_cov_ptr, d_cov_idx, d_free_pose, d_irregular, d_partS, d_partRhs, d_reach, d_slots, d_batch_rng;
     bool chunks_dirty = true, smem_attr_set = false, chunk_error = false;
+    // peer-memory exchange of the sharded reduced system (ba_peer.cuh)
+    struct Peer {
+        bool exported = false, attached = false;
+        DevBuf local;                    // [flags | band parity 0 | band parity 1]
+        void* base[kMaxPeers] = {};      // every rank's exchange buffer in this process' address space
+        bool ipc_open[kMaxPeers] = {};
+        int row_lo[kMaxPeers] = {}, row_hi[kMaxPeers] = {};
+        size_t nd = 0, nd_pad = 0;       // doubles per band buffer (payload / padded)
+        int n_free = 0, band_w = 0;
+        unsigned epoch = 0;              // exchanges completed (all ranks call in lock step)
+        int* h_err = nullptr;            // pinned: set by the kernel when a peer never announced
+        const void* zero_ptr = nullptr; int zero_n = -1;   // d_packed is known to be zero outside the band
+        int world = 0;
+    } peer;
+    int peer_world() const { return peer.world; }
 };
+
+static double* peer_band(vio360_ba* ba, int r, unsigned epoch) {
+    return reinterpret_cast<double*>(static_cast<char*>(ba->peer.base[r]) + kPeerHeaderBytes) + (size_t)(epoch & 1u) * ba->peer.nd_pad;
+}
+static void peer_release(vio360_ba* ba) {
+    auto& P = ba->peer;
+    for (int r = 0; r < kMaxPeers; ++r) { if (P.ipc_open[r] && P.base[r]) cudaIpcCloseMemHandle(P.base[r]); P.base[r] = nullptr; P.ipc_open[r] = false; }
+    P.local.release();
+    if (P.h_err) cudaFreeHost(P.h_err);
+    P.h_err = nullptr; P.exported = P.attached = false; P.epoch = 0; P.zero_n = -1;
+}
 
 // ------------------------------------------------------------------------ kernels
 __global__ void k_pose_prepare(int K, const double* __restrict__ Twb, const double* __restrict__ Tcb,
@@ -465,6 +494,7 @@ extern "C" void vio360_ba_destroy(vio360_ba* ba) {
                       &ba->d_chunks, &ba->d_cov_ptr, &ba->d_cov_idx, &ba->d_free_pose, &ba->d_irregular, &ba->d_partS, &ba->d_partRhs, &ba->d_reach, &ba->d_slots, &ba->d_batch_rng,
                       &ba->d_chol, &ba->d_linv, &ba->d_x, &ba->d_dl, &ba->d_reachF, &ba->d_band};
     for (DevBuf* b : bufs) b->release();
+    peer_release(ba);
     ba->pin.release();
     ba->h_solve.release();
     delete ba;
@@ -478,7 +508,12 @@ static void build_chunks(vio360_ba* ba) {
     const int K = ba->K;
     ba->chunks.clear(); ba->irregular.clear();
     const int nlm = ba->lm_end - ba->lm_begin;
-    const int target = std::max(kSMaxLm, (nlm + 2 * ba->ctx->num_sms - 1) / std::max(1, 2 * ba->ctx->num_sms));
+    // a chunk is a whole number of kSMaxLm-landmark batches (a partly filled batch costs a full one), sized so
+    // that the shard fills `waves` rounds of one CTA per SM (measured on the 1M-observation window: one round and
+    // two rounds tie on one GPU, one round wins on shards -- fewer slabs for k_schur_reduce, no short second round)
+    static const int waves = getenv("VIO360_BA_CHUNK_WAVES") ? std::max(1, atoi(getenv("VIO360_BA_CHUNK_WAVES"))) : 1;
+    const int nbatch_all = (nlm + kSMaxLm - 1) / kSMaxLm, slots = std::max(1, waves * ba->ctx->num_sms);
+    const int target = kSMaxLm * std::max(1, (nbatch_all + slots - 1) / slots);
     std::vector<int> seen(K, -1);
     SchurChunk cur{ba->lm_begin, ba->lm_begin, 0, 0, 0, 0, 0, 0};
     int cmin = K, cmax = -1;
@@ -859,6 +894,8 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
     const int nirr = use_tiles ? (int)ba->irregular.size() : ba->lm_end - ba->lm_begin;
     const int nb_irr = (nirr * 32 + 127) / 128;
     VIO_CUDA(ctx, ba->d_partials.reserve((size_t)(nch + nb_irr + 2) * 8));
+    if (ba->peer.attached && (nirr > 0 || !use_tiles || ba->shard_world != ba->peer_world()))
+        return vio360_fail(ctx, VIO360_ERR_STATE, "ba_build_reduced_system: a peer exchange is attached but this build cannot use the block band (landmarks outside the chunk windows, or the shard changed): vio360_ba_peer_detach first");
     if (use_tiles) {
         if (ba->chunks_dirty) {
             VIO_CUDA(ctx, cudaStreamSynchronize(st));
@@ -903,10 +940,22 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
                 // (nothing else writes there: the solver factors a copy, an allreduce adds zeros)
                 // (a sharded window is allreduced in place by the caller, which fills the other ranks' envelopes)
                 const bool sharded = ba->shard_world > 1;
+                const bool peer = sharded && ba->peer.attached;
                 const bool band = sharded || ba->red_band < ba->n_free;
                 double* outS = dS; double* outRhs = drhs; double* outCost = dcost;
-                int band_w = 0;
-                if (sharded) {
+                int band_w = 0, row0 = 0, nrows = ba->n_free;
+                if (peer) {
+                    // the band this rank announces in the next vio360_ba_peer_exchange; only the block rows its
+                    // landmarks touch are summed (the other ranks never read the rest), the LM diagonal is
+                    // added by the exchange kernel
+                    band_w = ba->peer.band_w;
+                    if (band_w != std::min(ba->n_free, kSWin) || ba->peer.n_free != ba->n_free)
+                        return vio360_fail(ctx, VIO360_ERR_STATE, "ba_build_reduced_system: the structure changed after vio360_ba_peer_export");
+                    outS = peer_band(ba, ba->shard_rank, ba->peer.epoch + 1);
+                    outRhs = outS + (size_t)ba->n_free * band_w * 36; outCost = outRhs + n;
+                    row0 = ba->peer.row_lo[ba->shard_rank]; nrows = ba->peer.row_hi[ba->shard_rank] - row0;
+                    ba->band_zero_n = -1;
+                } else if (sharded) {
                     // compact exchange buffer: chunk windows are kSWin poses wide on every rank, so block
                     // row bi never reaches past bi + kSWin - 1 (every slot inside the grid is rewritten)
                     band_w = std::min(ba->n_free, kSWin);
@@ -923,19 +972,22 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
                 }
                 ba->band_w = band_w; ba->dense_stale = sharded;
                 double* dS = outS; double* drhs = outRhs; double* dcost = outCost;   // shadow: the launches below write here
-                const dim3 nblk(sharded ? band_w : (band ? ba->red_band : ba->n_free), ba->n_free);
+                const dim3 nblk(sharded ? band_w : (band ? ba->red_band : ba->n_free), nrows);
+                const bool add_diag = ba->shard_rank == 0 && !peer;
+                if (nrows > 0) {
                 KernelTimer kt_(ctx, "k_schur_reduce");
                 // few block pairs (a short window with many chunks per pose): more walkers per pair
                 if ((size_t)nblk.x * nblk.y >= 2000)
                     k_schur_reduce<true, 7><<<nblk, 36 * 7, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
                                                            ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),
                                                            ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int2>(), ba->d_reach.as<int>(),
-                                                           ba->d_free_pose.as<int>(), Dp, ba->shard_rank == 0, band, band_w);
+                                                           ba->d_free_pose.as<int>(), Dp, add_diag, band, band_w, row0, ba->n_free);
                 else
                     k_schur_reduce<true, 14><<<nblk, 36 * 14, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
                                                            ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),
                                                            ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int2>(), ba->d_reach.as<int>(),
-                                                           ba->d_free_pose.as<int>(), Dp, ba->shard_rank == 0, band, band_w);
+                                                           ba->d_free_pose.as<int>(), Dp, add_diag, band, band_w, row0, ba->n_free);
+                }
             } else {
                 ba->band_zero_n = -1; ba->band_w = 0; ba->dense_stale = false;
                 const dim3 nblk(ba->n_free, ba->n_free);
@@ -943,7 +995,7 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
                 k_schur_reduce<false, 7><<<nblk, 36 * 7, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
                                                             ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),
                                                             ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int2>(), ba->d_reach.as<int>(),
-                                                            ba->d_free_pose.as<int>(), Dp, false, false, 0);
+                                                            ba->d_free_pose.as<int>(), Dp, false, false, 0, 0, ba->n_free);
             }
             VIO_LAUNCH_CHECK(ctx);
         }
@@ -988,6 +1040,8 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
 static int ensure_dense(vio360_ba* ba) {
     if (!ba->dense_stale) return VIO360_OK;
     vio360_ctx* ctx = ba->ctx;
+    if (ba->peer.attached)
+        return vio360_fail(ctx, VIO360_ERR_STATE, "the sharded build has not been exchanged yet: call vio360_ba_peer_exchange on every rank first");
     const size_t n = 6 * (size_t)ba->n_free, total = n * n + n + 1;
     { KernelTimer kt_(ctx, "k_expand_band");
     k_expand_band<<<(unsigned)((total + 255) / 256), 256, 0, ctx->stream>>>(ba->d_band.as<double>(), ba->n_free, ba->band_w, ba->d_packed.as<double>());
@@ -1000,6 +1054,8 @@ static int ensure_dense(vio360_ba* ba) {
 extern "C" int vio360_ba_reduced_band_dev(vio360_ba* ba, double** band_dev, size_t* n_doubles) {
     if (!ba || !band_dev || !n_doubles) return VIO360_ERR_INVALID;
     if (!ba->has_reduced) return vio360_fail(ba->ctx, VIO360_ERR_STATE, "no reduced system built yet");
+    if (ba->peer.attached)
+        return vio360_fail(ba->ctx, VIO360_ERR_STATE, "a peer exchange is attached: call vio360_ba_peer_exchange instead of all-reducing the band");
     if (ba->band_w <= 0)
         return vio360_fail(ba->ctx, VIO360_ERR_STATE, "the last build has no compact exchange buffer (no shard set, or landmarks outside the chunk windows): use vio360_ba_reduced_system_dev");
     *band_dev = ba->d_band.as<double>();
@@ -1012,6 +1068,134 @@ extern "C" int vio360_ba_expand_band(vio360_ba* ba) {
     if (!ba->has_reduced || ba->band_w <= 0) return vio360_fail(ba->ctx, VIO360_ERR_STATE, "ba_expand_band: no compact exchange buffer");
     ba->dense_stale = true;
     return ensure_dense(ba);
+}
+
+
+// ---- peer-memory exchange (ba_peer.cuh) --------------------------------------------------------
+struct PeerBlob {                 // what vio360_ba_peer_export hands to the other ranks (VIO360_PEER_BLOB_BYTES)
+    cudaIpcMemHandle_t ipc;       // 64 bytes
+    uint64_t base, nd;
+    int32_t pid, device, rank, world, n_free, band_w, row_lo, row_hi;
+    uint8_t pad[VIO360_PEER_BLOB_BYTES - 64 - 16 - 32];
+};
+static_assert(sizeof(PeerBlob) == VIO360_PEER_BLOB_BYTES, "peer blob layout");
+
+extern "C" int vio360_ba_peer_export(vio360_ba* ba, void* blob_out) {
+    if (!ba || !blob_out) return VIO360_ERR_INVALID;
+    vio360_ctx* ctx = ba->ctx;
+    if (!ba->has_structure) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_export before ba_set_structure");
+    if (ba->shard_world < 2 || ba->shard_world > kMaxPeers)
+        return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_export: needs a shard with 2..%d ranks (vio360_ba_set_shard)", kMaxPeers);
+    if (!ba->irregular.empty() || ba->chunk_error || ba->n_free <= 0)
+        return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_export: %zu landmarks of this shard fit no chunk window, so the build has no block band; allreduce the dense buffer instead", ba->irregular.size());
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    peer_release(ba);
+    auto& P = ba->peer;
+    P.world = ba->shard_world;
+    P.n_free = ba->n_free; P.band_w = std::min(ba->n_free, kSWin);
+    P.nd = (size_t)P.n_free * P.band_w * 36 + 6 * (size_t)P.n_free + 1;
+    P.nd_pad = (P.nd + 15) & ~(size_t)15;
+    const size_t bytes = kPeerHeaderBytes + 2 * P.nd_pad * 8;
+    VIO_CUDA(ctx, P.local.reserve(bytes));
+    VIO_CUDA(ctx, cudaMemset(P.local.p, 0, bytes));     // flags = epoch 0, bands zero (slots nobody writes stay zero)
+    VIO_CUDA(ctx, cudaHostAlloc((void**)&P.h_err, sizeof(int), cudaHostAllocMapped));
+    *P.h_err = 0;
+    // block rows (free-pose index) covered by this rank's chunks
+    int lo = P.n_free, hi = 0;
+    for (const SchurChunk& c : ba->chunks)
+        for (int p = c.pbase; p < c.pbase + c.span; ++p)
+            if (ba->free_map[p] >= 0) { lo = std::min(lo, ba->free_map[p]); hi = std::max(hi, ba->free_map[p] + 1); }
+    if (hi <= lo) lo = hi = 0;
+    PeerBlob b;
+    memset(&b, 0, sizeof(b));
+    VIO_CUDA(ctx, cudaIpcGetMemHandle(&b.ipc, P.local.p));
+    b.base = (uint64_t)reinterpret_cast<uintptr_t>(P.local.p); b.nd = P.nd;
+    b.pid = (int32_t)getpid(); b.device = ctx->device; b.rank = ba->shard_rank; b.world = ba->shard_world;
+    b.n_free = P.n_free; b.band_w = P.band_w; b.row_lo = lo; b.row_hi = hi;
+    memcpy(blob_out, &b, sizeof(b));
+    P.exported = true;
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_peer_attach(vio360_ba* ba, const void* blobs) {
+    if (!ba || !blobs) return VIO360_ERR_INVALID;
+    vio360_ctx* ctx = ba->ctx;
+    auto& P = ba->peer;
+    if (!P.exported) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_attach before ba_peer_export");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    const PeerBlob* B = static_cast<const PeerBlob*>(blobs);
+    for (int r = 0; r < P.world; ++r) {
+        PeerBlob b;
+        memcpy(&b, B + r, sizeof(b));
+        if (b.rank != r || b.world != P.world || b.n_free != P.n_free || b.band_w != P.band_w || b.nd != P.nd)
+            return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_peer_attach: blob %d does not describe rank %d of this window (rank %d world %d n_free %d band %d)",
+                               r, r, b.rank, b.world, b.n_free, b.band_w);
+        P.row_lo[r] = b.row_lo; P.row_hi[r] = b.row_hi;
+        if (r == ba->shard_rank) { P.base[r] = P.local.p; continue; }
+        if (b.pid == (int32_t)getpid()) {
+            // same process (one host thread per GPU): plain peer access
+            if (b.device != ctx->device) {
+                cudaError_t e = cudaDeviceEnablePeerAccess(b.device, 0);
+                if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+                else if (e != cudaSuccess) return vio360_fail(ctx, VIO360_ERR_CUDA, "ba_peer_attach: no peer access from device %d to %d: %s", ctx->device, b.device, cudaGetErrorString(e));
+            }
+            P.base[r] = reinterpret_cast<void*>(static_cast<uintptr_t>(b.base));
+        } else {
+            cudaError_t e = cudaIpcOpenMemHandle(&P.base[r], b.ipc, cudaIpcMemLazyEnablePeerAccess);
+            if (e != cudaSuccess) return vio360_fail(ctx, VIO360_ERR_CUDA, "ba_peer_attach: cudaIpcOpenMemHandle of rank %d: %s", r, cudaGetErrorString(e));
+            P.ipc_open[r] = true;
+        }
+    }
+    P.attached = true; P.epoch = 0; P.zero_n = -1;
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_peer_exchange(vio360_ba* ba) {
+    if (!ba) return VIO360_ERR_INVALID;
+    vio360_ctx* ctx = ba->ctx;
+    auto& P = ba->peer;
+    if (!P.attached) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_exchange before ba_peer_attach");
+    if (!ba->has_reduced || ba->band_w <= 0) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_exchange: no sharded build to exchange");
+    if (*P.h_err) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_exchange: an earlier exchange timed out waiting for a peer rank");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const int n = 6 * ba->n_free;
+    double* dS = ba->d_packed.as<double>();
+    if (P.zero_ptr != ba->d_packed.p || P.zero_n != n) {    // outside the band S is zero and stays zero
+        VIO_CUDA(ctx, cudaMemsetAsync(dS, 0, (size_t)n * n * 8, st));
+        P.zero_ptr = ba->d_packed.p; P.zero_n = n;
+    }
+    const unsigned epoch = ++P.epoch;
+    PeerView pv;
+    memset(&pv, 0, sizeof(pv));
+    pv.world = P.world; pv.rank = ba->shard_rank;
+    for (int r = 0; r < P.world; ++r) {
+        pv.band[r] = peer_band(ba, r, epoch);
+        pv.flags[r] = reinterpret_cast<unsigned*>(P.base[r]);
+        pv.row_lo[r] = P.row_lo[r]; pv.row_hi[r] = P.row_hi[r];
+    }
+    int* d_err = nullptr;
+    VIO_CUDA(ctx, cudaHostGetDevicePointer((void**)&d_err, P.h_err, 0));
+    const size_t total = P.nd;
+    // one element per thread where possible: a thread's peer loads are one NVLink round trip, so the kernel
+    // is a single latency deep when everything is in flight at once
+    const unsigned grid = (unsigned)std::min<size_t>((total + 255) / 256, (size_t)8 * ctx->num_sms);
+    { KernelTimer kt_(ctx, "k_band_exchange");
+    k_band_exchange<<<grid, 256, 0, st>>>(pv, epoch, ba->n_free, P.band_w, ba->d_free_pose.as<int>(),
+                                          ba->use_D ? ba->d_D.as<double>() : nullptr, dS, d_err);
+    }
+    VIO_LAUNCH_CHECK(ctx);
+    ba->dense_stale = false; ba->band_zero_n = -1;
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_peer_detach(vio360_ba* ba) {
+    if (!ba) return VIO360_ERR_INVALID;
+    cudaSetDevice(ba->ctx->device);
+    cudaStreamSynchronize(ba->ctx->stream);
+    peer_release(ba);
+    return VIO360_OK;
 }
 
 extern "C" int vio360_ba_reduced_system_dev(vio360_ba* ba, double** packed_dev, size_t* n_doubles) {
@@ -1036,6 +1220,8 @@ extern "C" int vio360_ba_fetch_reduced_system(vio360_ba* ba, double* S, double* 
     if (rhs && n) VIO_CUDA(ctx, cudaMemcpyAsync(rhs, dS + n * n, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
     if (cost) VIO_CUDA(ctx, cudaMemcpyAsync(cost, dS + n * n + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
     VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ba->peer.h_err && *ba->peer.h_err)
+        return vio360_fail(ctx, VIO360_ERR_STATE, "the peer exchange timed out waiting for another rank: the reduced system is incomplete");
     return VIO360_OK;
 }
 

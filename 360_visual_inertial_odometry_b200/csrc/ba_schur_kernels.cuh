@@ -351,11 +351,12 @@ k_schur_reduce(double* __restrict__ S, int n, double* __restrict__ rhs, double* 
                const double* __restrict__ partS, const double* __restrict__ partRhs, const double* __restrict__ partCost,
                int nchunks, const SchurChunk* __restrict__ chunks, const int* __restrict__ cov_ptr,
                const int2* __restrict__ cov_idx, const int* __restrict__ reach, const int* __restrict__ free_pose,
-               const double* __restrict__ D, bool add_diag, bool band_grid, int band_w) {
+               const double* __restrict__ D, bool add_diag, bool band_grid, int band_w, int row0, int n_free) {
     // band_grid: blockIdx.x counts block columns from the diagonal (the host sized the grid to the
-    // widest row of the envelope and zeroed S outside it once per structure)
-    const int bi = blockIdx.y, bj = band_grid ? bi + blockIdx.x : blockIdx.x;
-    if (bi > bj || bj >= gridDim.y) return;
+    // widest row of the envelope and zeroed S outside it once per structure).  row0: first block row
+    // of the grid (a rank of a peer-memory exchange sums only the rows its landmarks touch).
+    const int bi = blockIdx.y + row0, bj = band_grid ? bi + blockIdx.x : blockIdx.x;
+    if (bi > bj || bj >= n_free) return;
     __shared__ double part[kRedLanes][36];
     __shared__ double partR[kRedLanes][6];
     const int t = threadIdx.x, e = t % 36, g = t / 36;
@@ -414,7 +415,7 @@ k_schur_reduce(double* __restrict__ S, int n, double* __restrict__ rhs, double* 
         for (int k = 1; k < kRedLanes; ++k) tot += partR[k][ar];
         rhs[6 * bi + ar] = tot;
     }
-    if (FULL && bi == 0 && bj == 0 && t >= 64 && t < 96) {   // cost: fixed-order sum of the chunk partials
+    if (FULL && blockIdx.y == 0 && bi == bj && t >= 64 && t < 96) {   // cost: fixed-order sum of the chunk partials
         double tot = 0.0;
         for (int i = t - 64; i < nchunks; i += 32) tot += partCost[i];
         tot = warp_sum(tot);

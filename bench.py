@@ -400,7 +400,7 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
     res = {"metric": "BA factor evals (observations/s), fused residual+Jacobian+Huber+Schur blocks", "unit": "obs/s",
            "fp64_peak_tflops_measured": fp64_peak, "dtype": "f64"}
 
-    def run(win, steps, warmup, sharded):
+    def run(win, steps, warmup, sharded, exchange="nccl"):
         ba = b.BAWindow(ctx, win)
         if sharded:
             ba.set_shard(rank, world)
@@ -408,24 +408,38 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
         colsq = ba.column_sqnorm(True)
         D = np.sqrt(np.clip(colsq, 1e-6, 1e32) / 1e4)
         ba.set_lm_diagonal(D)
-        ba.build_reduced_system(None, True, fetch=False)
-        ptr, nd = ba.reduced_system_dev()
-
-        band = ba.reduced_band_dev() if (sharded and world > 1) else None
-        if band is not None:      # block-band payload [blocks | rhs | cost] (1.4 MB instead of 11.4 MB at 200 keyframes)
-            ptr, nd = band
-
-        class _Buf:   # zero-copy torch view of the exchange buffer
-            __cuda_array_interface__ = {"shape": (nd,), "typestr": "<f8", "data": (ptr, False), "version": 2}
-        packed = torch.as_tensor(_Buf(), device=device)
-
-        def step():
+        multi = sharded and world > 1
+        peer = multi and exchange == "peer"
+        if peer:
+            # SURVEY 8-E through peer memory: one kernel per rank pulls the covering bands over NVLink, sums, expands
+            blobs = [None] * world
+            dist.all_gather_object(blobs, ba.peer_export())
+            ba.peer_attach(blobs)
+            dist.barrier()
+            band, packed, nd = None, None, 0
+        else:
             ba.build_reduced_system(None, True, fetch=False)
-            if sharded and world > 1:
+            ptr, nd = ba.reduced_system_dev()
+            band = ba.reduced_band_dev() if multi else None
+            if band is not None:      # block-band payload [blocks | rhs | cost] (1.4 MB instead of 11.4 MB at 200 keyframes)
+                ptr, nd = band
+
+            class _Buf:   # zero-copy torch view of the exchange buffer
+                __cuda_array_interface__ = {"shape": (nd,), "typestr": "<f8", "data": (ptr, False), "version": 2}
+            packed = torch.as_tensor(_Buf(), device=device)
+
+        def exchange_step():
+            if peer:
+                ba.peer_exchange()
+            elif multi:
                 with torch.cuda.stream(stream):
                     dist.all_reduce(packed)     # one allreduce of the exchange buffer
                 if band is not None:
                     ba.expand_band()            # dense [S | rhs | cost] for the solver, on the same stream
+
+        def step():
+            ba.build_reduced_system(None, True, fetch=False)
+            exchange_step()
         for _ in range(warmup):
             step()
         barrier()
@@ -439,7 +453,7 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
         ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        ktimes = {name: ctx.kernel_time(name) for name in ("k_schur_tile", "k_schur_reduce", "k_schur_warp", "k_finish_S", "k_sum_partials", "k_expand_band")}
+        ktimes = {name: ctx.kernel_time(name) for name in ("k_schur_tile", "k_schur_reduce", "k_schur_warp", "k_finish_S", "k_sum_partials", "k_expand_band", "k_band_exchange")}
         dom = max(ktimes, key=lambda k: ktimes[k][0])
         k_ms, k_n = ktimes[dom]
         ctx.enable_kernel_timing(False)
@@ -447,12 +461,9 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
         t0 = time.perf_counter()
         for _ in range(max(2, steps // 2)):
             ba.set_parameters(win["pose_delta"], win["points"])
-            ba.build_reduced_system(D, True, fetch=not (sharded and world > 1))
-            if sharded and world > 1:
-                with torch.cuda.stream(stream):
-                    dist.all_reduce(packed)
-                if band is not None:
-                    ba.expand_band()
+            ba.build_reduced_system(D, True, fetch=not multi)
+            if multi:
+                exchange_step()
                 ba.fetch_reduced_system()
         barrier()
         e2e_s = (time.perf_counter() - t0) / max(2, steps // 2)
@@ -461,7 +472,9 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
         flops = 451.0 * win["O"] + float(np.sum(50 + 130 * deg + 216 * deg * (deg + 1) / 2))
         out = {"O": int(win["O"]), "K": int(win["K"]), "M": int(win["M"]), "ms_per_step": float(ms.item()) / steps,
                "value": win["O"] / (float(ms.item()) / steps * 1e-3), "e2e_value": win["O"] / e2e_s,
-               "algorithmic_flop_per_step": flops, "allreduce_doubles": int(nd) if (sharded and world > 1) else 0,
+               "algorithmic_flop_per_step": flops, "allreduce_doubles": int(nd) if (multi and not peer) else 0,
+               "exchange": ("peer memory (k_band_exchange: announce, pull covering bands over NVLink, rank-ordered sum, LM diagonal, dense expand in one kernel)"
+                            if peer else ("NCCL allreduce of the block band + k_expand_band" if multi else "none")),
                "roofline": {"bound": "fp64", "kernel": dom, "achieved": flops / world / (k_ms / max(k_n, 1) * 1e-3) / 1e12 if k_ms > 0 else None,
                             "peak": fp64_peak, "unit": "TFLOP/s", "avg_launch_ms": k_ms / max(k_n, 1),
                             "kernel_ms_per_step": {k: v[0] / steps for k, v in ktimes.items() if v[1] > 0}},
@@ -491,6 +504,9 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
             out["e2e_lm_step"] = {"ms_per_step_host_clock": lm_s * 1e3, "value": win["O"] / lm_s, "unit": "obs/s",
                                   "h2d_bytes_per_step": int(8 * (6 * win["K"] + 3 * win["M"])),
                                   "d2h_bytes_per_step": int(8 * (6 * win["K"] + 3 * win["M"]))}
+        if peer:
+            barrier()
+            ba.peer_detach()
         ba.close()
         return out
 
@@ -498,10 +514,16 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
         win3 = syn.make_ba_window(K=10, M=2000, seed=20000, mid_iteration=True)
         res["c3_local_window"] = run(win3, args.ba_steps * 4, 3, False)
     win5 = syn.make_ba_window(K=200, M=50000, degree=20, seed=1000000, mid_iteration=True, loop_radius=6.0)
-    r5 = run(win5, args.ba_steps, 3, True)
+    r5 = run(win5, args.ba_steps, 3, True, "peer")
+    if world > 1:
+        # the library-collective variant beside it (same shards, ncclAllReduce of the band + expand kernel)
+        rn = run(win5, args.ba_steps, 3, True, "nccl")
+        r5["nccl_variant"] = {k: rn[k] for k in ("ms_per_step", "value", "e2e_value", "allreduce_doubles", "exchange")}
+        r5["nccl_variant"]["kernel_ms_per_step"] = rn["roofline"]["kernel_ms_per_step"]
+        r5["nccl_variant"]["S_trace"] = rn["S_trace"]
     res["c5_large_window"] = r5
     res["value"] = r5["value"]; res["n_gpus"] = world
-    res["config"] = {"workload": "configs[4]: 200 keyframes, 1M observations, landmark-range sharding, NCCL allreduce of [S|rhs|cost]"}
+    res["config"] = {"workload": "configs[4]: 200 keyframes, 1M observations, landmark-range sharding, reduced-camera-system blocks summed over NVLink peer memory (NCCL allreduce variant reported beside it)"}
     if rank == 0 and world == 1 and not args.skip_cpu:
         res["cpu_baseline"] = cpu_baseline_ba(syn, win5)
     return res
@@ -607,7 +629,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=64, help="independent sequences (frame pairs) per GPU per step")
-    ap.add_argument("--ba-steps", type=int, default=5)
+    ap.add_argument("--ba-steps", type=int, default=20)
     ap.add_argument("--skip-ba", action="store_true")
     ap.add_argument("--skip-detect", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")

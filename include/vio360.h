@@ -232,6 +232,29 @@ int vio360_ba_reduced_system_dev(vio360_ba* ba, double** packed_dev, size_t* n_d
  * sharded or had landmarks outside the chunk windows (then allreduce the dense buffer instead). */
 int vio360_ba_reduced_band_dev(vio360_ba* ba, double** band_dev, size_t* n_doubles);
 int vio360_ba_expand_band(vio360_ba* ba);
+/* Peer-memory exchange of a sharded build over NVLink / NVSwitch: replaces the
+ * allreduce + vio360_ba_expand_band pair by ONE kernel per rank that announces its partial band,
+ * waits for the other ranks, pulls the bands covering each block straight out of their memory,
+ * sums them in rank order (bit-identical on all ranks), adds the pose part of the LM diagonal and
+ * writes the dense [S | rhs | cost].  No NCCL call, no staging copy.  There is no counterpart in
+ * the reference (single process, Ceres' mutex-guarded cells, schur_eliminator_impl.h:211).
+ *   1. after vio360_ba_set_structure + vio360_ba_set_shard(rank, world <= 8), every rank calls
+ *      vio360_ba_peer_export and hands its VIO360_PEER_BLOB_BYTES blob to all ranks (any transport:
+ *      MPI, torch.distributed all_gather, a socket; inside one process just an array);
+ *   2. every rank calls vio360_ba_peer_attach with the world's blobs in rank order (other processes'
+ *      buffers are mapped with cudaIpcOpenMemHandle, same-process ones by peer access), then the
+ *      caller synchronises the ranks once (all attached before the first exchange);
+ *   3. per LM iteration: vio360_ba_build_reduced_system(..., NULL, NULL, NULL) then
+ *      vio360_ba_peer_exchange, on every rank, the same number of times (collective semantics);
+ *      the dense view, the fetch and the solver then see the summed system.
+ * VIO360_ERR_STATE from export when landmarks of the shard fit no chunk window (allreduce the dense
+ * buffer instead).  A rank that never arrives makes the others fail after ~2 s (reported by the
+ * next fetch / exchange), it cannot hang the device.  Ranks must stay alive until all have detached. */
+#define VIO360_PEER_BLOB_BYTES 128
+int vio360_ba_peer_export(vio360_ba* ba, void* blob_out);
+int vio360_ba_peer_attach(vio360_ba* ba, const void* blobs);
+int vio360_ba_peer_exchange(vio360_ba* ba);
+int vio360_ba_peer_detach(vio360_ba* ba);
 /* Copy the (possibly all-reduced) packed device buffer back to the host. */
 int vio360_ba_fetch_reduced_system(vio360_ba* ba, double* S, double* rhs, double* cost);
 

@@ -238,6 +238,83 @@ def test_band_exchange_buffer_sums_to_full_system(bindings, ctx, synthetic):
         ba.close()
 
 
+def test_peer_exchange_same_process(bindings, synthetic):
+    """vio360_ba_peer_exchange (one kernel: announce, wait, pull the covering bands, sum in rank order,
+    LM diagonal, dense [S | rhs | cost]) with three ranks emulated by three contexts (= three streams) of one
+    process: every rank must end with the full reduced system, bit-identical across ranks, over several
+    epochs with changing parameters (the two band buffers alternate)."""
+    win = synthetic.make_ba_window(K=40, M=1500, degree=8, seed=78, mid_iteration=True)
+    ref = _oracle_all(win)
+    world = 3
+    ctxs = [bindings.Context(0) for _ in range(world)]
+    bas = []
+    for rank in range(world):
+        ba = bindings.BAWindow(ctxs[rank], win)
+        ba.set_shard(rank, world)
+        ba.set_parameters(win["pose_delta"], win["points"])
+        ba.set_lm_diagonal(ref["D"])
+        bas.append(ba)
+    blobs = [ba.peer_export() for ba in bas]
+    assert all(len(b) == bindings.PEER_BLOB_BYTES for b in blobs)
+    for ba in bas:
+        ba.peer_attach(blobs)
+    with pytest.raises(bindings.Vio360Error):
+        bas[0].peer_exchange()                      # nothing built yet
+    for epoch in range(3):
+        if epoch == 2:                              # a new linearisation point: the other parity buffer again
+            win2 = synthetic.make_ba_window(K=40, M=1500, degree=8, seed=78, mid_iteration=True)
+            rng = np.random.default_rng(5)
+            pd = win["pose_delta"] + 1e-3 * rng.standard_normal(win["pose_delta"].shape)
+            pd[win["pose_fixed"] != 0] = 0.0
+            win2["pose_delta"] = pd
+            ref = _oracle_all(win2)
+            for ba in bas:
+                ba.set_parameters(pd, win["points"])
+                ba.set_lm_diagonal(ref["D"])
+        for ba in bas:
+            ba.build_reduced_system(None, True, fetch=False)
+        with pytest.raises(bindings.Vio360Error):
+            bas[0].fetch_reduced_system()           # built but not exchanged: no silent partial result
+        assert bas[0].reduced_band_dev() is None    # the band must not be all-reduced behind the exchange
+        for ba in bas:
+            ba.peer_exchange()                      # asynchronous: the three kernels meet on the device
+        outs = [ba.fetch_reduced_system() for ba in bas]
+        S, rhs, cost = outs[0]
+        assert rel_err(S, ref["S"]) < TOL and rel_err(rhs, ref["rhs"]) < TOL and abs(cost - ref["cost"]) < TOL * ref["cost"]
+        assert np.array_equal(S, S.T)
+        for S2, rhs2, cost2 in outs[1:]:
+            assert np.array_equal(S2, S) and np.array_equal(rhs2, rhs) and cost2 == cost
+    dp, _ = bas[1].solve_reduced(False)
+    Wo = ba_oracle.Window(win2)
+    So, rhso, fm = Wo.schur(ref["r"], ref["Jp"], ref["Jl"], ref["D"])
+    dp_ref, _ = Wo.solve_step(ref["r"], ref["Jp"], ref["Jl"], ref["D"], So, rhso, fm)
+    assert rel_err(dp, dp_ref) < 1e-7
+    for ba in bas:
+        ba.peer_detach()
+    bas[0].build_reduced_system(None, True, fetch=False)      # back to the NCCL-style band
+    assert bas[0].reduced_band_dev() is not None
+    for ba in bas:
+        ba.close()
+    for c in ctxs:
+        c.close()
+
+
+def test_peer_exchange_two_processes():
+    """The same exchange across PROCESSES (one per GPU, cudaIpc handles gathered through torch.distributed),
+    checked against the NCCL allreduce of the band and the unsharded build; needs two GPUs."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    here = os.path.dirname(os.path.abspath(__file__))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29611", os.path.join(here, "dist_peer_worker.py")]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
+    assert "PEER_OK" in out.stdout
+
+
 def test_large_window_properties(bindings, ctx, synthetic):
     """BASELINE config 5 size (200 keyframes, 1M observations): size-independent checks --
     S symmetric PSD-ish, cost equals the evaluate() cost, linearity of the shard sum, and
