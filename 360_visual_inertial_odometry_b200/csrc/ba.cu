@@ -81,6 +81,7 @@ struct vio360_ba {
         unsigned epoch = 0;              // exchanges completed (all ranks call in lock step)
         int* h_err = nullptr;            // pinned: set by the kernel when a peer never announced
         const void* zero_ptr = nullptr; int zero_n = -1;   // d_packed is known to be zero outside the band
+        bool trace = false;                                 // VIO360_PEER_TRACE=1: device time stamps of the exchange kernel
         int world = 0;
     } peer;
     int peer_world() const { return peer.world; }
@@ -1148,6 +1149,7 @@ extern "C" int vio360_ba_peer_attach(vio360_ba* ba, const void* blobs) {
         }
     }
     P.attached = true; P.epoch = 0; P.zero_n = -1;
+    P.trace = getenv("VIO360_PEER_TRACE") != nullptr;
     return VIO360_OK;
 }
 
@@ -1177,13 +1179,15 @@ extern "C" int vio360_ba_peer_exchange(vio360_ba* ba) {
     }
     int* d_err = nullptr;
     VIO_CUDA(ctx, cudaHostGetDevicePointer((void**)&d_err, P.h_err, 0));
+    // trace words live behind the flags in the exchange header: [CTA 0 wait ns, CTA 0 total ns]
+    unsigned long long* d_trace = P.trace ? reinterpret_cast<unsigned long long*>(static_cast<char*>(P.local.p) + 512) : nullptr;
     const size_t total = P.nd;
     // one element per thread where possible: a thread's peer loads are one NVLink round trip, so the kernel
     // is a single latency deep when everything is in flight at once
     const unsigned grid = (unsigned)std::min<size_t>((total + 255) / 256, (size_t)8 * ctx->num_sms);
     { KernelTimer kt_(ctx, "k_band_exchange");
     k_band_exchange<<<grid, 256, 0, st>>>(pv, epoch, ba->n_free, P.band_w, ba->d_free_pose.as<int>(),
-                                          ba->use_D ? ba->d_D.as<double>() : nullptr, dS, d_err);
+                                          ba->use_D ? ba->d_D.as<double>() : nullptr, dS, d_err, d_trace);
     }
     VIO_LAUNCH_CHECK(ctx);
     ba->dense_stale = false; ba->band_zero_n = -1;
@@ -1194,6 +1198,13 @@ extern "C" int vio360_ba_peer_detach(vio360_ba* ba) {
     if (!ba) return VIO360_ERR_INVALID;
     cudaSetDevice(ba->ctx->device);
     cudaStreamSynchronize(ba->ctx->stream);
+    if (ba->peer.trace && ba->peer.attached && ba->peer.epoch > 1) {
+        unsigned long long h[4] = {0, 0, 0, 0};
+        cudaMemcpy(h, static_cast<char*>(ba->peer.local.p) + 512, sizeof(h), cudaMemcpyDeviceToHost);
+        const double ne = (double)ba->peer.epoch;
+        fprintf(stderr, "[vio360 peer trace] rank %d: %u exchanges, CTA 0 waited %.2f us and ran %.2f us per exchange\n",
+                ba->shard_rank, ba->peer.epoch, h[0] / ne * 1e-3, h[1] / ne * 1e-3);
+    }
     peer_release(ba);
     return VIO360_OK;
 }

@@ -440,21 +440,29 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
         def step():
             ba.build_reduced_system(None, True, fetch=False)
             exchange_step()
+        def timed(nsteps):
+            barrier()
+            e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(nsteps):
+                step()
+            e1.record(stream)
+            barrier()
+            t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return t
         for _ in range(warmup):
             step()
-        barrier()
+        ms = timed(steps)                          # the step as a caller runs it
         ctx.enable_kernel_timing(True); ctx.reset_kernel_times()
-        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        for _ in range(steps):
-            step()
-        e1.record(stream)
-        barrier()
-        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        ms_events = timed(steps)                   # again with an event pair around every kernel (per-kernel times; ~2 us each)
         ktimes = {name: ctx.kernel_time(name) for name in ("k_schur_tile", "k_schur_reduce", "k_schur_warp", "k_finish_S", "k_sum_partials", "k_expand_band", "k_band_exchange")}
-        dom = max(ktimes, key=lambda k: ktimes[k][0])
+        per_rank = None
+        if multi:   # every rank's kernel times: the exchange kernel's time includes waiting for the slowest rank
+            per_rank = [None] * world
+            dist.all_gather_object(per_rank, {k: round(v[0] / max(v[1], 1), 5) for k, v in ktimes.items() if v[1] > 0})
+        dom = max((k for k in ktimes if k != "k_band_exchange"), key=lambda k: ktimes[k][0])
         k_ms, k_n = ktimes[dom]
         ctx.enable_kernel_timing(False)
         # end to end: parameters from the host, reduced system back to the host
@@ -471,6 +479,7 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
         deg = np.bincount(win["point_idx"], minlength=win["M"]).astype(np.float64)
         flops = 451.0 * win["O"] + float(np.sum(50 + 130 * deg + 216 * deg * (deg + 1) / 2))
         out = {"O": int(win["O"]), "K": int(win["K"]), "M": int(win["M"]), "ms_per_step": float(ms.item()) / steps,
+               "ms_per_step_with_kernel_events": float(ms_events.item()) / steps,
                "value": win["O"] / (float(ms.item()) / steps * 1e-3), "e2e_value": win["O"] / e2e_s,
                "algorithmic_flop_per_step": flops, "allreduce_doubles": int(nd) if (multi and not peer) else 0,
                "exchange": ("peer memory (k_band_exchange: announce, pull covering bands over NVLink, rank-ordered sum, LM diagonal, dense expand in one kernel)"
@@ -481,6 +490,8 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
                "cost": cost, "S_trace": float(np.trace(S))}
         if out["roofline"]["achieved"]:
             out["roofline"]["frac"] = out["roofline"]["achieved"] / fp64_peak
+        if per_rank is not None:
+            out["kernel_ms_per_launch_by_rank"] = per_rank
         if world == 1:
             # reduced-system solve + landmark back substitution on the device
             ba.solve_reduced(True)
