@@ -4,6 +4,8 @@
 #include <algorithm>
 #include <cub/cub.cuh>
 
+#include <time.h>
+
 #include "common.cuh"
 #include "fe_detect.cuh"
 #include "fe_ransac.cuh"
@@ -56,6 +58,11 @@ struct vio360_fe_state {
     size_t cand_cap = 0;
     bool select_attr_set = false;
     int lk_mb = 2;               // occupancy variant of k_lk_track (tuning knob: VIO360_LK_MB)
+    // host-space batches: frames are uploaded on a second stream in groups of h2d_group jobs, and a group's
+    // pyramid + LK launches wait only for its own frames, so the kernels run behind the PCIe copies
+    cudaStream_t copy_stream = nullptr;
+    std::vector<cudaEvent_t> grp_ev;
+    int h2d_group = 4;           // VIO360_FE_H2D_GROUP (3840x1920 x 64 pairs: 4 -> 6959, 8 -> 6801, 16 -> 6823, off -> 6348 frames/s)
     size_t cub_bytes = 0;
 };
 
@@ -72,6 +79,8 @@ void vio360_fe_release(vio360_ctx* ctx) {
     for (auto& sg : s->stage) { sg.jobs.release(); sg.pyrjobs.release(); if (sg.ev) cudaEventDestroy(sg.ev); }
     for (auto& d : s->d_jobs_ring) d.release();
     for (auto& d : s->d_pyrjobs_ring) d.release();
+    for (cudaEvent_t e : s->grp_ev) cudaEventDestroy(e);
+    if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
     delete s;
     ctx->fe = nullptr;
 }
@@ -128,6 +137,8 @@ extern "C" int vio360_fe_configure(vio360_ctx* ctx, int width, int height, int m
     VIO_CUDA(ctx, s->h_pts_in.reserve(np * 8));
     VIO_CUDA(ctx, s->h_out.reserve(np * (8 + 1 + 4 + 1)));
     if (const char* e = getenv("VIO360_LK_MB")) s->lk_mb = atoi(e);
+    if (const char* e = getenv("VIO360_FE_H2D_GROUP")) s->h2d_group = std::max(1, atoi(e));
+    VIO_CUDA(ctx, cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
     if (const char* e = getenv("VIO360_DET_CAND")) s->max_cand = std::max(1, atoi(e));   // initial candidate capacity per image
     s->configured = true;
     return VIO360_OK;
@@ -176,7 +187,7 @@ static int acquire_slot(vio360_ctx* ctx, uint64_t key, bool* hit, int* out_idx) 
     return VIO360_OK;
 }
 
-static int load_frame(vio360_ctx* ctx, int slot, const uint8_t* img, size_t pitch, int mem_space) {
+static int load_frame(vio360_ctx* ctx, int slot, const uint8_t* img, size_t pitch, int mem_space, cudaStream_t h2d_stream = nullptr) {
     vio360_fe_state* s = ctx->fe;
     FeSlot& sl = s->slots[slot];
     if (mem_space == VIO360_MEM_DEVICE) {
@@ -186,27 +197,44 @@ static int load_frame(vio360_ctx* ctx, int slot, const uint8_t* img, size_t pitc
         }
         VIO_CUDA(ctx, cudaMemcpy2DAsync(sl.own[0], s->lpitch[0], img, pitch, s->W, s->H, cudaMemcpyDeviceToDevice, ctx->stream));
     } else {
-        VIO_CUDA(ctx, cudaMemcpy2DAsync(sl.own[0], s->lpitch[0], img, pitch, s->W, s->H, cudaMemcpyHostToDevice, ctx->stream));
+        cudaStream_t cs = h2d_stream ? h2d_stream : ctx->stream;
+        if (pitch == (size_t)s->W && s->lpitch[0] == s->W)     // contiguous on both sides: one linear DMA
+            VIO_CUDA(ctx, cudaMemcpyAsync(sl.own[0], img, (size_t)s->W * s->H, cudaMemcpyHostToDevice, cs));
+        else
+            VIO_CUDA(ctx, cudaMemcpy2DAsync(sl.own[0], s->lpitch[0], img, pitch, s->W, s->H, cudaMemcpyHostToDevice, cs));
     }
     sl.p[0] = sl.own[0]; sl.pitch[0] = s->lpitch[0];
     return VIO360_OK;
 }
 
-// build levels 1..L-1 for the listed slots, one launch per level for the whole batch
-static int build_pyramids(vio360_ctx* ctx, const std::vector<int>& todo) {
+// build levels 1..L-1 for the listed slots, one launch per level for the whole batch.
+// Three steps so that a caller can ship the descriptors of several groups in one copy BEFORE it queues bulk
+// uploads (host-to-device copies of all streams share the copy engine's queue in issue order):
+// stage_pyr_jobs fills the pinned table, upload_pyr_jobs copies a range, launch_pyramids launches.
+static void stage_pyr_jobs(vio360_ctx* ctx, const std::vector<int>& todo, size_t job_off) {
     vio360_fe_state* s = ctx->fe;
-    if (todo.empty() || s->nlevels <= 1) { for (int i : todo) s->slots[i].has_pyramid = true; return VIO360_OK; }
     const int nb = (int)todo.size();
-    PyrJob* hj = s->cur_stage->pyrjobs.as<PyrJob>();
-    PyrJob* dj = s->d_pyrjobs_ring[s->cur_stage_i].as<PyrJob>();
+    PyrJob* hj = s->cur_stage->pyrjobs.as<PyrJob>() + job_off;
     for (int l = 0; l + 1 < s->nlevels; ++l)
         for (int b = 0; b < nb; ++b) {
             FeSlot& sl = s->slots[todo[b]];
             PyrJob& j = hj[(size_t)l * nb + b];
             j.src = sl.p[l]; j.spitch = sl.pitch[l]; j.dst = sl.own[l + 1]; j.dpitch = s->lpitch[l + 1];
         }
-    const size_t bytes = sizeof(PyrJob) * (size_t)nb * (s->nlevels - 1);
-    VIO_CUDA(ctx, cudaMemcpyAsync(dj, hj, bytes, cudaMemcpyHostToDevice, ctx->stream));
+}
+static int upload_pyr_jobs(vio360_ctx* ctx, size_t job_off, size_t count) {
+    vio360_fe_state* s = ctx->fe;
+    if (count == 0) return VIO360_OK;
+    VIO_CUDA(ctx, cudaMemcpyAsync(s->d_pyrjobs_ring[s->cur_stage_i].as<PyrJob>() + job_off, s->cur_stage->pyrjobs.as<PyrJob>() + job_off,
+                                  sizeof(PyrJob) * count, cudaMemcpyHostToDevice, ctx->stream));
+    return VIO360_OK;
+}
+static int launch_pyramids(vio360_ctx* ctx, const std::vector<int>& todo, size_t job_off) {
+    vio360_fe_state* s = ctx->fe;
+    if (todo.empty() || s->nlevels <= 1) { for (int i : todo) s->slots[i].has_pyramid = true; return VIO360_OK; }
+    const int nb = (int)todo.size();
+    const PyrJob* hj = s->cur_stage->pyrjobs.as<PyrJob>() + job_off;    // job_off: several groups share one descriptor stage
+    PyrJob* dj = s->d_pyrjobs_ring[s->cur_stage_i].as<PyrJob>() + job_off;
     for (int l = 0; l + 1 < s->nlevels; ++l) {
         const int dw = s->lw[l + 1], dh = s->lh[l + 1];
         // fast path: 8-column lanes need w % 8 == 0 and 8-byte aligned source rows
@@ -236,6 +264,15 @@ static int build_pyramids(vio360_ctx* ctx, const std::vector<int>& todo) {
     for (int i : todo) s->slots[i].has_pyramid = true;
     return VIO360_OK;
 }
+static int build_pyramids(vio360_ctx* ctx, const std::vector<int>& todo) {
+    vio360_fe_state* s = ctx->fe;
+    if (!todo.empty() && s->nlevels > 1) {
+        stage_pyr_jobs(ctx, todo, 0);
+        int rc = upload_pyr_jobs(ctx, 0, todo.size() * (size_t)(s->nlevels - 1));
+        if (rc) return rc;
+    }
+    return launch_pyramids(ctx, todo, 0);
+}
 
 static void fill_levels(const vio360_fe_state* s, const FeSlot& sl, FrameLevels& f) {
     for (int l = 0; l < kMaxLevels; ++l) { f.p[l] = l < s->nlevels ? sl.p[l] : nullptr; f.pitch[l] = l < s->nlevels ? sl.pitch[l] : 0; }
@@ -261,8 +298,23 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
     if (mem_space == VIO360_MEM_HOST) VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     int rc0 = begin_stage(ctx);
     if (rc0) return rc0;
+    timespec ts_begin; clock_gettime(CLOCK_MONOTONIC, &ts_begin);
     s->batch_tag++;
-    std::vector<int> todo;
+    // host-space batches are cut into groups of h2d_group jobs: a group's frames are uploaded on the copy
+    // stream, its pyramid and LK launches wait only for those copies (device-space batches are one group)
+    static const bool force_piped = getenv("VIO360_FE_H2D_FORCE") != nullptr;   // A/B probe: copy stream even for one group
+    const bool piped = mem_space == VIO360_MEM_HOST && (n_jobs > s->h2d_group || force_piped);
+    const int gsize = piped ? s->h2d_group : n_jobs, ngroups = (n_jobs + gsize - 1) / gsize;
+    std::vector<std::vector<int>> todo(ngroups);
+    std::vector<int> queued;
+    struct Upload { int slot, group; const uint8_t* img; size_t pitch; };
+    std::vector<Upload> uploads;
+    if (piped)
+        while ((int)s->grp_ev.size() < ngroups) {
+            cudaEvent_t e;
+            VIO_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            s->grp_ev.push_back(e);
+        }
     TrackJobDev* hj = s->cur_stage->jobs.as<TrackJobDev>();
     TrackJobDev* dj = s->d_jobs_ring[s->cur_stage_i].as<TrackJobDev>();
     int max_n = 0;
@@ -278,14 +330,21 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
         const size_t pitches[2] = {j.prev_pitch, j.cur_pitch};
         const uint64_t keys[2] = {j.prev_key, j.cur_key};
         int idx[2];
+        const int g = b / gsize;
         for (int f = 0; f < 2; ++f) {
             int rc = acquire_slot(ctx, keys[f], &hit, &idx[f]);
             if (rc) return rc;
             if (!hit) {
-                rc = load_frame(ctx, idx[f], imgs[f], pitches[f], mem_space);
-                if (rc) return rc;
+                if (mem_space == VIO360_MEM_DEVICE) {       // alias (or device copy) now: the level table below needs it
+                    rc = load_frame(ctx, idx[f], imgs[f], pitches[f], mem_space);
+                    if (rc) return rc;
+                } else {
+                    uploads.push_back({idx[f], g, imgs[f], pitches[f]});   // queued after the descriptor copies
+                }
             }
-            if (!s->slots[idx[f]].has_pyramid && std::find(todo.begin(), todo.end(), idx[f]) == todo.end()) todo.push_back(idx[f]);
+            if (!s->slots[idx[f]].has_pyramid && std::find(queued.begin(), queued.end(), idx[f]) == queued.end()) {
+                queued.push_back(idx[f]); todo[g].push_back(idx[f]);
+            }
         }
         sp = idx[0]; sc = idx[1];
         TrackJobDev& d = hj[b];
@@ -302,21 +361,44 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
         off += (size_t)j.n;
         max_n = std::max(max_n, j.n);
     }
-    int rc = build_pyramids(ctx, todo);
-    if (rc) return rc;
-    if (max_n == 0) return end_stage(ctx);
     cudaStream_t st = ctx->stream;
-    VIO_CUDA(ctx, cudaMemcpyAsync(dj, hj, sizeof(TrackJobDev) * (size_t)n_jobs, cudaMemcpyHostToDevice, st));
-    if (mem_space == VIO360_MEM_HOST)
-        VIO_CUDA(ctx, cudaMemcpyAsync(s->d_pts_in.p, s->h_pts_in.p, off * 8, cudaMemcpyHostToDevice, st));
-    { KernelTimer kt_(ctx, "k_lk_track");
+    int rc = VIO360_OK;
+    static const bool fe_trace = getenv("VIO360_FE_TRACE") != nullptr;
+    auto now_us = []() { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3; };
+    const double t_copies = fe_trace ? now_us() : 0.0;
+    if (max_n > 0) {
+        VIO_CUDA(ctx, cudaMemcpyAsync(dj, hj, sizeof(TrackJobDev) * (size_t)n_jobs, cudaMemcpyHostToDevice, st));
+        if (mem_space == VIO360_MEM_HOST)
+            VIO_CUDA(ctx, cudaMemcpyAsync(s->d_pts_in.p, s->h_pts_in.p, off * 8, cudaMemcpyHostToDevice, st));
+    }
+    // descriptors first, bulk frame uploads second: host-to-device copies of both streams are served in issue
+    // order, so a descriptor copy queued behind the frames would hold every kernel back until the last frame
+    const size_t per = (size_t)std::max(0, s->nlevels - 1);
+    size_t pyr_off = 0;
+    for (int g = 0; g < ngroups; ++g) { stage_pyr_jobs(ctx, todo[g], pyr_off); pyr_off += todo[g].size() * per; }
+    if ((rc = upload_pyr_jobs(ctx, 0, pyr_off))) return rc;
     {
-        const LkParams lp = lk_params(s);
+        size_t u = 0;
+        for (int g = 0; g < ngroups; ++g) {
+            for (; u < uploads.size() && uploads[u].group == g; ++u)
+                if ((rc = load_frame(ctx, uploads[u].slot, uploads[u].img, uploads[u].pitch, mem_space, piped ? s->copy_stream : nullptr))) return rc;
+            if (piped) VIO_CUDA(ctx, cudaEventRecord(s->grp_ev[g], s->copy_stream));
+        }
+    }
+    const LkParams lp = lk_params(s);
+    pyr_off = 0;
+    for (int g = 0; g < ngroups; ++g) {
+        const int j0 = g * gsize, nj = std::min(gsize, n_jobs - j0);
+        if (piped) VIO_CUDA(ctx, cudaStreamWaitEvent(st, s->grp_ev[g], 0));
+        if ((rc = launch_pyramids(ctx, todo[g], pyr_off))) return rc;
+        pyr_off += todo[g].size() * per;
+        if (max_n == 0) continue;
+        { KernelTimer kt_(ctx, "k_lk_track");
         auto launch = [&](auto kern, int warps) -> cudaError_t {
             const size_t smem = (size_t)warps * kLkWarpWords * sizeof(uint32_t);
             cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
             if (e != cudaSuccess) return e;
-            kern<<<dim3((max_n + warps - 1) / warps, n_jobs), warps * 32, smem, st>>>(dj, lp);
+            kern<<<dim3((max_n + warps - 1) / warps, nj), warps * 32, smem, st>>>(dj + j0, lp);
             return cudaSuccess;
         };
         cudaError_t e;
@@ -326,10 +408,15 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
         else if (s->lk_mb == 6) e = launch(k_lk_track<9, 112>, 9);
         else e = launch(k_lk_track<8, 128>, 8);
         if (e != cudaSuccess) return vio360_fail(ctx, VIO360_ERR_CUDA, "k_lk_track: %s", cudaGetErrorString(e));
+        }
+        VIO_LAUNCH_CHECK(ctx);
     }
+    if (max_n == 0) {
+        if (mem_space == VIO360_MEM_HOST) VIO_CUDA(ctx, cudaStreamSynchronize(st));   // the caller's frames are free again
+        return end_stage(ctx);
     }
-    VIO_LAUNCH_CHECK(ctx);
     if ((rc = end_stage(ctx))) return rc;
+    const double t_kernels = fe_trace ? now_us() : 0.0;
     if (mem_space == VIO360_MEM_HOST) {
         // one pinned block: [xy off*8 | err off*4 | status off | keep off]
         uint8_t* ho = s->h_out.as<uint8_t>();
@@ -338,6 +425,8 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
         VIO_CUDA(ctx, cudaMemcpyAsync(ho + off * 12, s->d_status.p, off, cudaMemcpyDeviceToHost, st));
         VIO_CUDA(ctx, cudaMemcpyAsync(ho + off * 13, s->d_keep.p, off, cudaMemcpyDeviceToHost, st));
         VIO_CUDA(ctx, cudaStreamSynchronize(st));
+        if (fe_trace) fprintf(stderr, "[vio360 fe trace] %d jobs: copies enqueued in %.0f us, kernels in %.0f us, stream idle %.0f us later\n",
+                              n_jobs, t_copies - (ts_begin.tv_sec * 1e6 + ts_begin.tv_nsec * 1e-3), t_kernels - t_copies, now_us() - t_kernels);
         size_t o = 0;
         for (int b = 0; b < n_jobs; ++b) {
             const vio360_track_job& j = jobs[b];

@@ -95,6 +95,38 @@ def test_track_batch_cache_and_keep(ctx, synthetic):
     assert nt == 0 and len(st) == 0
 
 
+def test_track_batch_host_upload_groups(ctx, synthetic, monkeypatch):
+    """Host-space batches larger than the upload group are cut into groups whose frames travel on a copy stream
+    while the previous group's kernels run: the results must be the ones of the same jobs issued one by one, also
+    when a frame uploaded for one group is the cached previous frame of a job in a later group, and for ragged
+    and empty jobs."""
+    W, H = 640, 320
+    frames = [synthetic.render_erp_frame(W, H, t, seed=33, n_waves=32, sigma_omega=40.0) for t in range(12)]
+    pts = synthetic.make_track_points(W, H, 200, seed=7)
+    monkeypatch.setenv("VIO360_FE_H2D_GROUP", "3")
+    ctx.fe_configure(W, H, max_points=256, max_batch=16)
+    monkeypatch.delenv("VIO360_FE_H2D_GROUP")
+    ns = [200, 150, 0, 77, 200, 1, 200, 33, 200, 120, 64]
+    # a chain: job i tracks frame i -> i + 1; keys make frame i + 1 of job i the cached prev of job i + 1 (next group or same)
+    pairs = [(frames[i], frames[i + 1], pts[:ns[i]], 500 + i, 501 + i) for i in range(11)]
+    l0 = ctx.launch_count
+    outs = ctx.fe_track_batch_host(pairs)
+    assert ctx.launch_count - l0 == 4 * (3 + 1)          # four groups: three pyramid levels + one LK launch each
+    ctx.fe_configure(W, H, max_points=256, max_batch=16)
+    for i, (xy, st, err, keep) in enumerate(outs):
+        if ns[i] == 0:
+            continue
+        (xy1, st1, err1, keep1), = ctx.fe_track_batch_host([(frames[i], frames[i + 1], pts[:ns[i]], 0, 0)])
+        assert np.array_equal(xy, xy1) and np.array_equal(st, st1) and np.array_equal(err, err1) and np.array_equal(keep, keep1)
+    oxy, ost, _, _ = fo.lk_track(frames[4], frames[5], pts[:ns[4]])
+    assert np.array_equal(outs[4][1], ost) and np.abs(outs[4][0] - oxy)[ost == 1].max() < POS_TOL
+    # unkeyed host frames in a grouped batch (every frame uploaded, nothing cached)
+    ctx.fe_configure(W, H, max_points=256, max_batch=16)
+    outs2 = ctx.fe_track_batch_host([(frames[i], frames[i + 1], pts[:ns[i]], 0, 0) for i in range(11)])
+    for a, b2 in zip(outs, outs2):
+        assert np.array_equal(a[0], b2[0]) and np.array_equal(a[1], b2[1])
+
+
 @pytest.mark.parametrize("size,seed", [((960, 480), 3), ((1920, 960), 4), ((3840, 1920), 5)])
 def test_detect_vs_oracle(ctx, synthetic, size, seed):
     W, H = size
