@@ -21,7 +21,7 @@ EXPORTS = [
     "vio360_enable_kernel_timing", "vio360_kernel_time", "vio360_reset_kernel_times",
     "vio360_fe_configure", "vio360_fe_track", "vio360_fe_track_batch", "vio360_fe_detect",
     "vio360_fe_detect_batch", "vio360_fe_pyramid", "vio360_fe_min_eigen_val",
-    "vio360_fe_ransac_rotation", "vio360_fe_ransac_rotation_batch",
+    "vio360_fe_ransac_rotation", "vio360_fe_ransac_rotation_batch", "vio360_fe_cluster_filter", "vio360_fe_grid_cap",
     "vio360_ba_create", "vio360_ba_destroy", "vio360_ba_set_structure", "vio360_ba_set_outliers",
     "vio360_ba_set_shard", "vio360_ba_set_parameters", "vio360_ba_evaluate",
     "vio360_ba_get_residuals_jacobians", "vio360_ba_normal_blocks", "vio360_ba_reduced_dim",
@@ -99,6 +99,8 @@ def load():
     lib.vio360_fe_pyramid.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.POINTER(C.c_void_p),
                                       C.POINTER(C.c_size_t)]
     lib.vio360_fe_min_eigen_val.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    lib.vio360_fe_cluster_filter.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 6 + [C.c_float, C.c_void_p, C.c_int]
+    lib.vio360_fe_grid_cap.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 7 + [C.c_void_p, C.c_int]
     lib.vio360_ba_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
     lib.vio360_ba_set_structure.argtypes = [C.c_void_p] + [C.c_void_p] * 6 + [C.c_double, C.c_double, C.c_void_p,
                                                                                C.c_double, C.c_void_p, C.c_void_p]
@@ -230,6 +232,31 @@ class Context:
 
     def fe_track_batch_raw(self, jobs, n_jobs, mem_space):
         self.check(self.lib.vio360_fe_track_batch(self.h, jobs, n_jobs, mem_space))
+
+    def _grid_pack(self, frames, track=None):
+        nf = len(frames)
+        ns = np.array([len(f) for f in frames], np.int32)
+        stride = max(int(ns.max()) if nf else 0, 1)
+        xy = np.zeros((nf, stride, 2), np.float32); tr = np.zeros((nf, stride), np.int32)
+        for f in range(nf):
+            xy[f, :ns[f]] = np.asarray(frames[f], np.float32).reshape(-1, 2)
+            if track is not None:
+                tr[f, :ns[f]] = np.asarray(track[f], np.int32)
+        return nf, ns, stride, xy, tr, np.zeros((nf, stride), np.uint8)
+
+    def fe_cluster_filter(self, frames, width, height, cols=20, rows=10, std_ratio=0.25):
+        """FeatureTracker::RemoveClusteredFeatures over a list of per-frame (n, 2) point arrays -> list of keep masks."""
+        nf, ns, stride, xy, _, keep = self._grid_pack(frames)
+        self.check(self.lib.vio360_fe_cluster_filter(self.h, _ptr(xy), _ptr(ns), nf, stride, width, height, cols, rows,
+                                                     std_ratio, _ptr(keep), MEM_HOST))
+        return [keep[f, :ns[f]].copy() for f in range(nf)]
+
+    def fe_grid_cap(self, frames, track, width, height, cols=20, rows=10, max_per_cell=4):
+        """Frame::LimitFeaturesPerGrid over a list of per-frame point arrays and track counts -> list of keep masks."""
+        nf, ns, stride, xy, tr, keep = self._grid_pack(frames, track)
+        self.check(self.lib.vio360_fe_grid_cap(self.h, _ptr(xy), _ptr(tr), _ptr(ns), nf, stride, width, height, cols, rows,
+                                               max_per_cell, _ptr(keep), MEM_HOST))
+        return [keep[f, :ns[f]].copy() for f in range(nf)]
 
     def fe_detect(self, img, mask=None, max_corners=1000, quality=float(np.float32(0.01)),
                   min_dist=float(np.float32(30.0)), key=0):

@@ -8,6 +8,7 @@
 
 #include "common.cuh"
 #include "fe_detect.cuh"
+#include "fe_grid.cuh"
 #include "fe_ransac.cuh"
 #include "fe_lk.cuh"
 #include "fe_pyr.cuh"
@@ -877,4 +878,79 @@ extern "C" int vio360_fe_ransac_rotation(vio360_ctx* ctx, const float* prev_xy, 
     j.prev_xy = prev_xy; j.cur_xy = cur_xy; j.n = n; j.samples = samples; j.inlier_mask = inlier_mask; j.best_inliers = best_inliers;
     j.counts = nullptr;
     return vio360_fe_ransac_rotation_batch(ctx, &j, 1, iters, threshold_deg, VIO360_MEM_HOST);
+}
+
+// ---- feature-list filters between tracking and detection -------------------------
+// mode 0: RemoveClusteredFeatures, mode 1: LimitFeaturesPerGrid.  Frames are rows of `stride` features.
+static int grid_filter(vio360_ctx* ctx, int mode, const float* xy, const int32_t* track, const int* n, int n_frames, int stride,
+                       int width, int height, int cols, int rows, float std_ratio, int max_per_cell, uint8_t* keep, int mem_space) {
+    if (!ctx) return VIO360_ERR_INVALID;
+    vio360_fe_state* s = ctx->fe;
+    if (!s || !s->configured) return vio360_fail(ctx, VIO360_ERR_STATE, "fe grid filter before fe_configure");
+    if (!xy || !n || !keep || n_frames < 0 || stride < 0 || width <= 0 || height <= 0 || cols <= 0 || rows <= 0 || (mode == 1 && (!track || max_per_cell < 0)))
+        return vio360_fail(ctx, VIO360_ERR_INVALID, "fe grid filter: bad arguments");
+    if ((size_t)cols * rows >= 0xffff) return vio360_fail(ctx, VIO360_ERR_INVALID, "fe grid filter: more than 65534 cells");
+    if (n_frames == 0) return VIO360_OK;
+    int max_n = 0;
+    for (int f = 0; f < n_frames; ++f) {
+        if (n[f] < 0 || n[f] > stride || n[f] > kGridMaxPoints) return vio360_fail(ctx, VIO360_ERR_INVALID, "fe grid filter: frame %d has %d features (stride %d, max %d)", f, n[f], stride, kGridMaxPoints);
+        max_n = std::max(max_n, n[f]);
+    }
+    if (max_n == 0) return VIO360_OK;
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    VIO_CUDA(ctx, cudaStreamSynchronize(st));          // the pinned pool below may still be in flight
+    const size_t tot = (size_t)n_frames * stride;
+    const bool host = mem_space == VIO360_MEM_HOST;
+    // pool: [jobs | xy 2*tot floats | track tot ints | keep tot bytes] (the last three only for host-space calls)
+    const size_t job_bytes = (sizeof(GridJobDev) * (size_t)n_frames + 15) & ~(size_t)15;
+    const size_t bytes = job_bytes + (host ? tot * 8 + tot * 4 + ((tot + 15) & ~(size_t)15) : 0);
+    VIO_CUDA(ctx, s->d_ransac.reserve(bytes));
+    VIO_CUDA(ctx, s->h_ransac.reserve(bytes));
+    uint8_t* hp = s->h_ransac.as<uint8_t>();
+    uint8_t* dp = s->d_ransac.as<uint8_t>();
+    GridJobDev* hj = reinterpret_cast<GridJobDev*>(hp);
+    const float* dxy = xy; const int32_t* dtr = track; uint8_t* dkeep = keep;
+    if (host) {
+        memcpy(hp + job_bytes, xy, tot * 8);
+        if (track) memcpy(hp + job_bytes + tot * 8, track, tot * 4);
+        dxy = reinterpret_cast<const float*>(dp + job_bytes);
+        dtr = reinterpret_cast<const int32_t*>(dp + job_bytes + tot * 8);
+        dkeep = dp + job_bytes + tot * 12;
+    }
+    for (int f = 0; f < n_frames; ++f) {
+        hj[f].xy = dxy + 2 * (size_t)f * stride; hj[f].track = dtr ? dtr + (size_t)f * stride : nullptr;
+        hj[f].keep = dkeep + (size_t)f * stride; hj[f].n = n[f];
+    }
+    VIO_CUDA(ctx, cudaMemcpyAsync(dp, hp, host ? job_bytes + tot * 12 : job_bytes, cudaMemcpyHostToDevice, st));
+    const int np = (max_n + 1) & ~1;
+    if (mode == 0) {
+        const size_t smem = (size_t)np * 2 + (size_t)cols * rows;
+        if (smem > 200 * 1024) return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_cluster_filter: grid too large");
+        VIO_CUDA(ctx, cudaFuncSetAttribute(k_cluster_filter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(smem, 48 * 1024)));
+        KernelTimer kt_(ctx, "k_cluster_filter");
+        k_cluster_filter<<<n_frames, kGridThreads, smem, st>>>(reinterpret_cast<const GridJobDev*>(dp), width, height, cols, rows, std_ratio);
+    } else {
+        const size_t smem = (size_t)np * 2 + (size_t)max_n * 4;
+        VIO_CUDA(ctx, cudaFuncSetAttribute(k_grid_cap, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(smem, 48 * 1024)));
+        KernelTimer kt_(ctx, "k_grid_cap");
+        k_grid_cap<<<n_frames, kGridThreads, smem, st>>>(reinterpret_cast<const GridJobDev*>(dp), width, height, cols, rows, max_per_cell);
+    }
+    VIO_LAUNCH_CHECK(ctx);
+    if (host) {
+        VIO_CUDA(ctx, cudaMemcpyAsync(hp + job_bytes + tot * 12, dp + job_bytes + tot * 12, tot, cudaMemcpyDeviceToHost, st));
+        VIO_CUDA(ctx, cudaStreamSynchronize(st));
+        for (int f = 0; f < n_frames; ++f) memcpy(keep + (size_t)f * stride, hp + job_bytes + tot * 12 + (size_t)f * stride, (size_t)n[f]);
+    }
+    return VIO360_OK;
+}
+
+extern "C" int vio360_fe_cluster_filter(vio360_ctx* ctx, const float* xy, const int* n, int n_frames, int stride, int width, int height,
+                                        int grid_cols, int grid_rows, float std_ratio, uint8_t* keep, int mem_space) {
+    return grid_filter(ctx, 0, xy, nullptr, n, n_frames, stride, width, height, grid_cols, grid_rows, std_ratio, 0, keep, mem_space);
+}
+
+extern "C" int vio360_fe_grid_cap(vio360_ctx* ctx, const float* xy, const int32_t* track_count, const int* n, int n_frames, int stride,
+                                  int width, int height, int grid_cols, int grid_rows, int max_per_cell, uint8_t* keep, int mem_space) {
+    return grid_filter(ctx, 1, xy, track_count, n, n_frames, stride, width, height, grid_cols, grid_rows, 0.f, max_per_cell, keep, mem_space);
 }

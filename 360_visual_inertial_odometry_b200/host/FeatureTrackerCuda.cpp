@@ -123,4 +123,25 @@ int FeatureTrackerCuda::RejectOutliersRotationRANSAC(const std::vector<cv::Point
     return best_inliers;
 }
 
+std::vector<uchar> FeatureTrackerCuda::RemoveClusteredFeatures(const std::vector<cv::Point2f>& points, float clustered_std_ratio,
+                                                               int grid_cols, int grid_rows) {
+    std::vector<uchar> keep(points.size(), 1);
+    if (points.empty()) return keep;
+    const int n = (int)points.size();
+    check(vio360_fe_cluster_filter(m_ctx, reinterpret_cast<const float*>(points.data()), &n, 1, n, m_width, m_height, grid_cols,
+                                   grid_rows, clustered_std_ratio, keep.data(), VIO360_MEM_HOST), "vio360_fe_cluster_filter");
+    return keep;
+}
+
+std::vector<uchar> FeatureTrackerCuda::LimitFeaturesPerGrid(const std::vector<cv::Point2f>& points, const std::vector<int>& track_counts,
+                                                            int max_features_per_grid, int grid_cols, int grid_rows) {
+    if (track_counts.size() != points.size()) throw std::runtime_error("LimitFeaturesPerGrid: one track count per point");
+    std::vector<uchar> keep(points.size(), 0);
+    if (points.empty()) return keep;
+    const int n = (int)points.size();
+    check(vio360_fe_grid_cap(m_ctx, reinterpret_cast<const float*>(points.data()), track_counts.data(), &n, 1, n, m_width, m_height,
+                             grid_cols, grid_rows, max_features_per_grid, keep.data(), VIO360_MEM_HOST), "vio360_fe_grid_cap");
+    return keep;
+}
+
 }  // namespace vio_360

@@ -55,6 +55,15 @@ public:
                                      const std::vector<cv::Point2f>& curr_points, std::vector<uchar>& inlier_mask);
     void SetRansacSeed(uint32_t seed) { m_ransac_seed = seed; m_ransac_seeded = true; }
     void SetRansacParams(int max_iterations, float threshold_deg) { m_ransac_max_iterations = max_iterations; m_ransac_threshold = threshold_deg; }
+    // FeatureTracker::RemoveClusteredFeatures (FeatureTracker.cpp:404-497) over the features' pixel coordinates:
+    // keep[i] == 0 for features of clustered grid cells (the caller erases them from the Frame in order).
+    // Grid and ratio default to the reference's (FeatureTracker.cpp:39-40, default_config.yaml:54).
+    std::vector<uchar> RemoveClusteredFeatures(const std::vector<cv::Point2f>& points, float clustered_std_ratio = 0.25f,
+                                               int grid_cols = 20, int grid_rows = 10);
+    // Frame::AssignFeaturesToGrid + Frame::LimitFeaturesPerGrid (Frame.cpp:108-202): keep[i] == 1 for the features that
+    // survive the per-cell cap (highest track counts first, ties in feature order).
+    std::vector<uchar> LimitFeaturesPerGrid(const std::vector<cv::Point2f>& points, const std::vector<int>& track_counts,
+                                            int max_features_per_grid = 4, int grid_cols = 20, int grid_rows = 10);
     // The post filter of TrackFeatures (FeatureTracker.cpp:118-126) computed on the device
     // during the last TrackOpticalFlow call: status && !polar && !near-boundary.
     const std::vector<uchar>& LastKeepMask() const { return m_keep; }

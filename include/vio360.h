@@ -158,6 +158,27 @@ int vio360_fe_ransac_rotation(vio360_ctx* ctx, const float* prev_xy, const float
 int vio360_fe_ransac_rotation_batch(vio360_ctx* ctx, const vio360_ransac_job* jobs, int n_jobs,
                                     int iters, float threshold_deg, int mem_space);
 
+/* the feature-list filters FeatureTracker::TrackFeatures runs between tracking and
+ * detection, on the device so that the point list can stay there.  Frames are rows of `stride`
+ * features (xy: n_frames x stride x 2 floats, keep: n_frames x stride bytes, n[f] <= stride, host
+ * array in both memory spaces); keep[i] = 1 for features the reference keeps, in its order.
+ *  - vio360_fe_cluster_filter replaces FeatureTracker::RemoveClusteredFeatures
+ *    (src/processing/FeatureTracker.cpp:404-497): grid cells (grid_cols x grid_rows over width x height,
+ *    :420-436) holding >= 4 features whose positional standard deviation (float, summed in feature
+ *    order, :459-476) is below std_ratio * cell diagonal lose all their features; frames with fewer
+ *    than 4 features are left alone (:411).
+ *  - vio360_fe_grid_cap replaces Frame::AssignFeaturesToGrid + Frame::LimitFeaturesPerGrid
+ *    (src/database/Frame.cpp:108-202): features outside the image are dropped (:125-128); a cell keeps
+ *    its max_per_cell features with the highest track_count; ties keep feature order (std::sort of a
+ *    cell of <= 16 indices is libstdc++'s stable insertion sort; for larger cells with ties the
+ *    reference's pick is implementation-defined and this call stays with feature order).          */
+int vio360_fe_cluster_filter(vio360_ctx* ctx, const float* xy, const int* n, int n_frames, int stride,
+                             int width, int height, int grid_cols, int grid_rows, float std_ratio,
+                             uint8_t* keep, int mem_space);
+int vio360_fe_grid_cap(vio360_ctx* ctx, const float* xy, const int32_t* track_count, const int* n,
+                       int n_frames, int stride, int width, int height, int grid_cols, int grid_rows,
+                       int max_per_cell, uint8_t* keep, int mem_space);
+
 /* ------------------------------------------- path B: BA factor evaluation ---- */
 /* A window = what Optimizer::RunLocalBA / RunBA assemble (src/optimization/
  * Optimizer.cpp:741-840): K poses, M landmarks, O observations.                     */

@@ -141,6 +141,26 @@ def ransac_rotation(prev_xy, cur_xy, w, h, samples, threshold_deg):
     return best, mask, counts[:iters], bi.value, errs[:n]
 
 
+def cluster_filter(xy, w, h, cols=20, rows=10, std_ratio=0.25):
+    """FeatureTracker::RemoveClusteredFeatures -> keep mask."""
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    keep = np.zeros(max(xy.shape[0], 1), np.uint8)
+    f = lib().vf_cluster_filter
+    f.restype = None
+    f(_p(xy, C.c_float), xy.shape[0], w, h, cols, rows, C.c_float(std_ratio), _p(keep, C.c_ubyte))
+    return keep[:xy.shape[0]]
+
+
+def grid_cap(xy, track, w, h, cols=20, rows=10, max_per_cell=4):
+    """Frame::AssignFeaturesToGrid + LimitFeaturesPerGrid -> keep mask."""
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2); track = np.ascontiguousarray(track, np.int32)
+    keep = np.zeros(max(xy.shape[0], 1), np.uint8)
+    f = lib().vf_grid_cap
+    f.restype = None
+    f(_p(xy, C.c_float), _p(track, C.c_int), xy.shape[0], w, h, cols, rows, max_per_cell, _p(keep, C.c_ubyte))
+    return keep[:xy.shape[0]]
+
+
 # ------------------------------------------------------------------ the real dependency
 def cv2_lk_track(prev, cur, pts):
     """cv::calcOpticalFlowPyrLK exactly as FeatureTracker.cpp:238-240 calls it."""

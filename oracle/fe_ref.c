@@ -615,3 +615,80 @@ int vf_ransac_rotation(const float* prev_xy, const float* cur_xy, int n, int W, 
     free(b1); free(b2);
     return best;
 }
+
+/* ---- feature-list filters (FeatureTracker.cpp:404-497, Frame.cpp:108-202) ---------------------- */
+static int vf_cell_index(float x, float y, float cw, float ch, int cols, int rows) {
+    int col = (int)(x / cw), row = (int)(y / ch);        /* :435-436 / Frame.cpp:131-132 */
+    if (col > cols - 1) col = cols - 1;
+    if (row > rows - 1) row = rows - 1;
+    if (col < 0) col = 0;                                 /* the reference would index out of bounds */
+    if (row < 0) row = 0;
+    return row * cols + col;
+}
+
+void vf_cluster_filter(const float* xy, int n, int w, int h, int cols, int rows, float std_ratio, uint8_t* keep) {
+    for (int i = 0; i < n; ++i) keep[i] = 1;
+    if (n < 4) return;                                    /* :411 */
+    const float cw = (float)w / cols, ch = (float)h / rows;
+    const float diag = sqrtf(cw * cw + ch * ch);
+    const float thr = diag * std_ratio;
+    const int ncell = cols * rows;
+    int* cell = (int*)malloc(sizeof(int) * (size_t)n);
+    uint8_t* clustered = (uint8_t*)calloc((size_t)ncell, 1);
+    for (int i = 0; i < n; ++i) cell[i] = vf_cell_index(xy[2 * i], xy[2 * i + 1], cw, ch, cols, rows);
+    for (int c = 0; c < ncell; ++c) {
+        int cnt = 0;
+        float mx = 0.f, my = 0.f;
+        for (int i = 0; i < n; ++i) if (cell[i] == c) { mx += xy[2 * i]; my += xy[2 * i + 1]; ++cnt; }
+        if (cnt < 4) continue;                            /* :447 */
+        mx /= (float)cnt; my /= (float)cnt;
+        float var = 0.f;
+        for (int i = 0; i < n; ++i)
+            if (cell[i] == c) { const float dx = xy[2 * i] - mx, dy = xy[2 * i + 1] - my; var += (dx * dx + dy * dy); }
+        var /= (float)cnt;
+        if (sqrtf(var) < thr) clustered[c] = 1;           /* :472-474 */
+    }
+    for (int i = 0; i < n; ++i) if (clustered[cell[i]]) keep[i] = 0;
+    free(cell); free(clustered);
+}
+
+void vf_grid_cap(const float* xy, const int* track, int n, int w, int h, int cols, int rows, int max_per_cell, uint8_t* keep) {
+    const float cw = (float)w / cols, ch = (float)h / rows;
+    const int ncell = cols * rows;
+    int* count = (int*)calloc((size_t)ncell + 1, sizeof(int));
+    int* cell = (int*)malloc(sizeof(int) * (size_t)(n > 0 ? n : 1));
+    for (int i = 0; i < n; ++i) {
+        const float x = xy[2 * i], y = xy[2 * i + 1];
+        keep[i] = 0;
+        cell[i] = -1;
+        if (x < 0 || x >= w || y < 0 || y >= h) continue;  /* Frame.cpp:125-128 */
+        cell[i] = vf_cell_index(x, y, cw, ch, cols, rows);
+        count[cell[i] + 1]++;
+    }
+    for (int c = 0; c < ncell; ++c) count[c + 1] += count[c];
+    int* list = (int*)malloc(sizeof(int) * (size_t)(n > 0 ? n : 1));
+    int* fill = (int*)malloc(sizeof(int) * (size_t)ncell);
+    for (int c = 0; c < ncell; ++c) fill[c] = count[c];
+    for (int i = 0; i < n; ++i) if (cell[i] >= 0) list[fill[cell[i]]++] = i;   /* push_back in feature order */
+    for (int c = 0; c < ncell; ++c) {
+        int* v = list + count[c];
+        int sz = count[c + 1] - count[c];
+        if (sz > max_per_cell) {
+            /* std::sort(cell, comp = track[a] > track[b]) as libstdc++'s __insertion_sort */
+            for (int i = 1; i < sz; ++i) {
+                const int val = v[i];
+                if (track[val] > track[v[0]]) {
+                    for (int k = i; k > 0; --k) v[k] = v[k - 1];
+                    v[0] = val;
+                } else {
+                    int k = i;
+                    while (track[val] > track[v[k - 1]]) { v[k] = v[k - 1]; --k; }
+                    v[k] = val;
+                }
+            }
+            sz = max_per_cell;                              /* cell.resize */
+        }
+        for (int k = 0; k < sz; ++k) keep[v[k]] = 1;
+    }
+    free(count); free(cell); free(list); free(fill);
+}

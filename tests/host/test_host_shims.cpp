@@ -209,7 +209,23 @@ static void test_fe() {
     std::vector<cv::Point2f> two(gp.begin(), gp.begin() + 2), two_c(gc.begin(), gc.begin() + 2);
     std::vector<uchar> inl2;
     EXPECT(tracker.RejectOutliersRotationRANSAC(two, two_c, inl2) == 2 && inl2.size() == 2 && inl2[0] == 1 && inl2[1] == 1, "n < 3 keeps everything");
-    std::printf("  front-end: %d corners, %d tracked, |dxy| %.2e px, ransac %d/%zu inliers\n", nref, ntr, worst, nin, gp.size());
+    // feature-list filters through the shim against the oracle (tracked points + a tight artificial cluster)
+    std::vector<cv::Point2f> fl(gc);
+    for (int i = 0; i < 6; ++i) fl.push_back(cv::Point2f(300.f + 0.5f * i, 200.f + 0.25f * i));
+    std::vector<int> tc(fl.size());
+    for (size_t i = 0; i < fl.size(); ++i) tc[i] = 1 + (int)((i * 7u) % 5u);
+    const std::vector<uchar> kc = tracker.RemoveClusteredFeatures(fl), kg = tracker.LimitFeaturesPerGrid(fl, tc, 2);
+    std::vector<unsigned char> okc(fl.size()), okg(fl.size());
+    vf_cluster_filter(reinterpret_cast<const float*>(fl.data()), (int)fl.size(), W, H, 20, 10, 0.25f, okc.data());
+    vf_grid_cap(reinterpret_cast<const float*>(fl.data()), tc.data(), (int)fl.size(), W, H, 20, 10, 2, okg.data());
+    int nclu = 0, ncap = 0;
+    for (size_t i = 0; i < fl.size(); ++i) {
+        EXPECT(kc[i] == okc[i], "cluster filter %zu", i);
+        EXPECT(kg[i] == okg[i], "grid cap %zu", i);
+        nclu += !kc[i]; ncap += !kg[i];
+    }
+    EXPECT(nclu >= 6 && ncap > 0, "filters removed %d / %d features", nclu, ncap);
+    std::printf("  front-end: %d corners, %d tracked, |dxy| %.2e px, ransac %d/%zu inliers, cluster filter -%d, grid cap -%d\n", nref, ntr, worst, nin, gp.size(), nclu, ncap);
 }
 
 int main() {

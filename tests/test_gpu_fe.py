@@ -95,6 +95,30 @@ def test_track_batch_cache_and_keep(ctx, synthetic):
     assert nt == 0 and len(st) == 0
 
 
+def test_cluster_filter_and_grid_cap_vs_oracle(ctx):
+    """RemoveClusteredFeatures and LimitFeaturesPerGrid on the device, bit exact against the
+    oracle over ragged multi-frame batches (an empty frame, a frame with fewer than four features, ties, points
+    outside the image, the reference's grid 20 x 10 with caps 4 (FeatureTracker.cpp:41) and 10 (default_config.yaml:16))."""
+    from test_grid_cpu import make_features
+    W, H = 3840, 1920
+    ctx.fe_configure(W, H, max_points=3000, max_batch=2)
+    sizes = [1000, 0, 3, 3000, 257, 4]
+    frames, tracks = [], []
+    for f, n in enumerate(sizes):
+        xy, tr = make_features(n, W, H, 40 + f) if n else (np.zeros((0, 2), np.float32), np.zeros(0, np.int32))
+        frames.append(xy); tracks.append(tr)
+    for ratio in (0.15, 0.25):
+        got = ctx.fe_cluster_filter(frames, W, H, 20, 10, ratio)
+        for f in range(len(sizes)):
+            assert np.array_equal(got[f], fo.cluster_filter(frames[f], W, H, 20, 10, ratio)), (f, ratio)
+    assert any((g == 0).any() for g in got)
+    for cap in (4, 10, 1):
+        got = ctx.fe_grid_cap(frames, tracks, W, H, 20, 10, cap)
+        for f in range(len(sizes)):
+            assert np.array_equal(got[f], fo.grid_cap(frames[f], tracks[f], W, H, 20, 10, cap)), (f, cap)
+    assert any((g == 0).any() for g in got)
+
+
 def test_track_batch_host_upload_groups(ctx, synthetic, monkeypatch):
     """Host-space batches larger than the upload group are cut into groups whose frames travel on a copy stream
     while the previous group's kernels run: the results must be the ones of the same jobs issued one by one, also
