@@ -14,6 +14,8 @@ def make_features(n, w, h, seed, clusters=3, outside=0.03):
     rng = np.random.default_rng(seed)
     pts = rng.uniform([0, 0], [w, h], (n, 2))
     per = max(4, n // 20)
+    if clusters * per > n:
+        clusters = 0
     for c in range(clusters):
         ctr = rng.uniform([0.1 * w, 0.1 * h], [0.9 * w, 0.9 * h])
         pts[c * per:(c + 1) * per] = ctr + rng.normal(0, 2.0 + 6.0 * c, (per, 2))
