@@ -83,6 +83,7 @@ struct vio360_ba {
         const void* zero_ptr = nullptr; int zero_n = -1;   // d_packed is known to be zero outside the band
         bool trace = false;                                 // VIO360_PEER_TRACE=1: device time stamps of the exchange kernel
         int world = 0;
+        unsigned band_epoch = 0;         // epoch the last build wrote its band for
     } peer;
     int peer_world() const { return peer.world; }
 };
@@ -975,6 +976,7 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
                 double* dS = outS; double* drhs = outRhs; double* dcost = outCost;   // shadow: the launches below write here
                 const dim3 nblk(sharded ? band_w : (band ? ba->red_band : ba->n_free), nrows);
                 const bool add_diag = ba->shard_rank == 0 && !peer;
+                if (peer) ba->peer.band_epoch = ba->peer.epoch + 1;
                 if (nrows > 0) {
                 KernelTimer kt_(ctx, "k_schur_reduce");
                 // few block pairs (a short window with many chunks per pose): more walkers per pair
@@ -1160,6 +1162,7 @@ extern "C" int vio360_ba_peer_exchange(vio360_ba* ba) {
     if (!P.attached) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_exchange before ba_peer_attach");
     if (!ba->has_reduced || ba->band_w <= 0) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_exchange: no sharded build to exchange");
     if (*P.h_err) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_exchange: an earlier exchange timed out waiting for a peer rank");
+    if (P.band_epoch != P.epoch + 1) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_exchange: no vio360_ba_build_reduced_system since the last exchange");
     VIO_CUDA(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
     const int n = 6 * ba->n_free;

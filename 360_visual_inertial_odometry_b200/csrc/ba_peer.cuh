@@ -48,33 +48,11 @@ __device__ __forceinline__ void st_release_sys_u32(unsigned* p, unsigned v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-__global__ void __launch_bounds__(256)
-k_band_exchange(const PeerView pv, const unsigned epoch, const int n_free, const int band_w,
-                const int* __restrict__ free_pose, const double* __restrict__ D,
-                double* __restrict__ packed, int* __restrict__ err_flag, unsigned long long* __restrict__ trace) {
-    unsigned long long t_start = 0;
-    if (trace && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
-    // announce: this rank's band of `epoch` was completed by the previous kernel on this stream
-    if (blockIdx.x == 0 && threadIdx.x < pv.world) {
-        __threadfence_system();
-        st_release_sys_u32(pv.flags[threadIdx.x] + pv.rank, epoch);
-    }
-    // wait for every rank's announcement (flags of this rank are local memory: the poll stays on this GPU)
-    if (threadIdx.x < pv.world) {
-        const unsigned* f = pv.flags[pv.rank] + threadIdx.x;
-        const long long t0 = clock64();
-        // (measured on 4 B200: acquire polls by one thread per peer beat relaxed polls + one fence per CTA, 13 vs 28 us)
-        while ((int)(ld_acquire_sys_u32(f) - epoch) < 0) {
-            if (clock64() - t0 > kPeerTimeoutCycles) { *err_flag = 1; break; }
-        }
-    }
-    __syncthreads();
-    if (trace && threadIdx.x == 0) {   // VIO360_PEER_TRACE: ns CTA 0 spent waiting / in total, summed over exchanges
-        unsigned long long t;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-        if (blockIdx.x == 0) trace[0] += t - t_start;
-    }
-
+// Every thread pulls its elements of the band from the ranks whose rows cover them, sums in rank order, adds the
+// LM diagonal and writes the dense mirrored [S | rhs | cost] (grid-stride over the band).
+__device__ __forceinline__ void band_pull_sum_expand(const PeerView& pv, const int n_free, const int band_w,
+                                                     const int* __restrict__ free_pose, const double* __restrict__ D,
+                                                     double* __restrict__ packed) {
     const int n = 6 * n_free;
     const size_t nS = (size_t)n_free * band_w * 36, total = nS + n + 1;
     for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
@@ -109,6 +87,36 @@ k_band_exchange(const PeerView pv, const unsigned epoch, const int n_free, const
             packed[(size_t)n * n + (idx - nS)] = s;
         }
     }
+}
+
+__global__ void __launch_bounds__(256)
+k_band_exchange(const PeerView pv, const unsigned epoch, const int n_free, const int band_w,
+                const int* __restrict__ free_pose, const double* __restrict__ D,
+                double* __restrict__ packed, int* __restrict__ err_flag, unsigned long long* __restrict__ trace) {
+    unsigned long long t_start = 0;
+    if (trace && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
+    // announce: this rank's band of `epoch` was completed by the previous kernel on this stream
+    if (blockIdx.x == 0 && threadIdx.x < pv.world) {
+        __threadfence_system();
+        st_release_sys_u32(pv.flags[threadIdx.x] + pv.rank, epoch);
+    }
+    // wait for every rank's announcement (flags of this rank are local memory: the poll stays on this GPU)
+    if (threadIdx.x < pv.world) {
+        const unsigned* f = pv.flags[pv.rank] + threadIdx.x;
+        const long long t0 = clock64();
+        // (measured on 4 B200: acquire polls by one thread per peer beat relaxed polls + one fence per CTA, 13 vs 28 us)
+        while ((int)(ld_acquire_sys_u32(f) - epoch) < 0) {
+            if (clock64() - t0 > kPeerTimeoutCycles) { *err_flag = 1; break; }
+        }
+    }
+    __syncthreads();
+    if (trace && threadIdx.x == 0) {   // VIO360_PEER_TRACE: ns CTA 0 spent waiting / in total, summed over exchanges
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (blockIdx.x == 0) trace[0] += t - t_start;
+    }
+
+    band_pull_sum_expand(pv, n_free, band_w, free_pose, D, packed);
     if (trace) {
         __syncthreads();
         if (threadIdx.x == 0) {

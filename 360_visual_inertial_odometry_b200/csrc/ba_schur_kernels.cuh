@@ -345,26 +345,24 @@ k_expand_band(const double* __restrict__ band, int n_free, int band_w, double* _
 // diagonal (levenberg_marquardt_strategy.cc:78-89) and sum the chunk costs, so that no further
 // pass over S is needed; !FULL: upper block triangle only (k_schur_warp then adds the landmarks
 // that fit no window and k_finish_S mirrors).
+// One block pair (bi <= bj) of the slab sum; called by every thread of the CTA (threads beyond 36 * kRedLanes idle
+// through the loads).  first: this CTA also sums the chunk costs.  part / partR: shared scratch.
 template <bool FULL, int kRedLanes>
-__global__ void __launch_bounds__(36 * kRedLanes)
-k_schur_reduce(double* __restrict__ S, int n, double* __restrict__ rhs, double* __restrict__ cost_out,
-               const double* __restrict__ partS, const double* __restrict__ partRhs, const double* __restrict__ partCost,
-               int nchunks, const SchurChunk* __restrict__ chunks, const int* __restrict__ cov_ptr,
-               const int2* __restrict__ cov_idx, const int* __restrict__ reach, const int* __restrict__ free_pose,
-               const double* __restrict__ D, bool add_diag, bool band_grid, int band_w, int row0, int n_free) {
-    // band_grid: blockIdx.x counts block columns from the diagonal (the host sized the grid to the
-    // widest row of the envelope and zeroed S outside it once per structure).  row0: first block row
-    // of the grid (a rank of a peer-memory exchange sums only the rows its landmarks touch).
-    const int bi = blockIdx.y + row0, bj = band_grid ? bi + blockIdx.x : blockIdx.x;
-    if (bi > bj || bj >= n_free) return;
-    __shared__ double part[kRedLanes][36];
-    __shared__ double partR[kRedLanes][6];
+__device__ __forceinline__ void schur_reduce_block(const int bi, const int bj, const bool first, double* __restrict__ S, int n,
+                                                   double* __restrict__ rhs, double* __restrict__ cost_out,
+                                                   const double* __restrict__ partS, const double* __restrict__ partRhs,
+                                                   const double* __restrict__ partCost, int nchunks,
+                                                   const int* __restrict__ cov_ptr, const int2* __restrict__ cov_idx,
+                                                   const int* __restrict__ reach, const int* __restrict__ free_pose,
+                                                   const double* __restrict__ D, bool add_diag, int band_w,
+                                                   double (*part)[36], double (*partR)[6]) {
     const int t = threadIdx.x, e = t % 36, g = t / 36;
     const int a = e / 6, b = e - 6 * a;
     const int pi = free_pose[bi], pj = free_pose[bj];
     const int q0 = cov_ptr[pi], q1 = cov_ptr[pi + 1];
-    const bool in_env = pj <= reach[pi] && (bi < bj || a <= b);
-    const bool do_rhs = bi == bj && e < 6;   // the walkers' first six threads also sum the pose's rhs entry e
+    const bool walker = g < kRedLanes;
+    const bool in_env = walker && pj <= reach[pi] && (bi < bj || a <= b);
+    const bool do_rhs = walker && bi == bj && e < 6;   // the walkers' first six threads also sum the pose's rhs entry e
     double s = 0.0, sr = 0.0;
     if (in_env || do_rhs) {
         // four chunks per round: the (chunk, window) entries and the slab loads of a round are
@@ -389,8 +387,10 @@ k_schur_reduce(double* __restrict__ S, int n, double* __restrict__ rhs, double* 
             sr += (vr[0] + vr[1]) + (vr[2] + vr[3]);
         }
     }
-    part[g][e] = s;
-    if (e < 6) partR[g][e] = sr;
+    if (walker) {
+        part[g][e] = s;
+        if (e < 6) partR[g][e] = sr;
+    }
     __syncthreads();
     if (t < 36 && (bi < bj || a <= b)) {
         double tot = part[0][e];
@@ -415,12 +415,30 @@ k_schur_reduce(double* __restrict__ S, int n, double* __restrict__ rhs, double* 
         for (int k = 1; k < kRedLanes; ++k) tot += partR[k][ar];
         rhs[6 * bi + ar] = tot;
     }
-    if (FULL && blockIdx.y == 0 && bi == bj && t >= 64 && t < 96) {   // cost: fixed-order sum of the chunk partials
+    if (FULL && first && t >= 64 && t < 96) {   // cost: fixed-order sum of the chunk partials
         double tot = 0.0;
         for (int i = t - 64; i < nchunks; i += 32) tot += partCost[i];
         tot = warp_sum(tot);
         if (t == 64) *cost_out = tot;
     }
+}
+
+template <bool FULL, int kRedLanes>
+__global__ void __launch_bounds__(36 * kRedLanes)
+k_schur_reduce(double* __restrict__ S, int n, double* __restrict__ rhs, double* __restrict__ cost_out,
+               const double* __restrict__ partS, const double* __restrict__ partRhs, const double* __restrict__ partCost,
+               int nchunks, const SchurChunk* __restrict__ chunks, const int* __restrict__ cov_ptr,
+               const int2* __restrict__ cov_idx, const int* __restrict__ reach, const int* __restrict__ free_pose,
+               const double* __restrict__ D, bool add_diag, bool band_grid, int band_w, int row0, int n_free) {
+    // band_grid: blockIdx.x counts block columns from the diagonal (the host sized the grid to the
+    // widest row of the envelope and zeroed S outside it once per structure).  row0: first block row
+    // of the grid (a rank of a peer-memory exchange sums only the rows its landmarks touch).
+    const int bi = blockIdx.y + row0, bj = band_grid ? bi + blockIdx.x : blockIdx.x;
+    if (bi > bj || bj >= n_free) return;
+    __shared__ double part[kRedLanes][36];
+    __shared__ double partR[kRedLanes][6];
+    schur_reduce_block<FULL, kRedLanes>(bi, bj, blockIdx.y == 0 && bi == bj, S, n, rhs, cost_out, partS, partRhs, partCost, nchunks,
+                                        cov_ptr, cov_idx, reach, free_pose, D, add_diag, band_w, part, partR);
 }
 
 }  // namespace vio360

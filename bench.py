@@ -70,7 +70,7 @@ class ClockSampler(threading.Thread):
 
 
 # dram bytes per launch of the default 64-frame workload, from the committed ncu capture
-NCU_TRAFFIC = {"k_lk_track": 597.177344e6 + 11.730688e6}
+NCU_TRAFFIC = {"k_lk_track": 597.195776e6 + 8.958464e6}
 
 
 def measured_peaks():
@@ -214,7 +214,12 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_value = B * e2e_steps * world / float(e2e_s.item())
-    e2e_status_equal = bool((hst.to(device) == out_st).all().item()) if (args.warmup + args.steps - (2 + e2e_steps)) % 2 == 0 else None
+    # same frame pair as the last device-resident step (one more untimed call when the ring parity differs):
+    # the status bytes of the host-buffer path must equal the device path's
+    last_host, last_dev = 1 + e2e_steps, args.warmup + args.steps - 1
+    if last_host % 2 != last_dev % 2:
+        host_step(last_host + 1)
+    e2e_status_equal = bool((hst.to(device) == out_st).all().item())
 
     # ---- roofline of the dominant kernel
     hbm_peak, peak_src = measured_peaks()
@@ -229,7 +234,7 @@ def run_ours(args):
     step_ms = ms_total / args.steps
     roofline = {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                 "frac": achieved / hbm_peak, "traffic": NCU_TRAFFIC.get(dominant) if B == 64 else None, "peak_source": peak_src,
-                "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full capture of this command (profiles/r01_ncu_frontend_late.txt); 32-byte sectors around 32/36-byte tile rows and search-tile refills explain the factor over the algorithmic bytes",
+                "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full capture of this command (profiles/r01_ncu_final.txt); 32-byte sectors around 32/36-byte tile rows and search-tile refills explain the factor over the algorithmic bytes",
                 "algorithmic_bytes_per_launch": per_launch_bytes, "avg_launch_ms": dur_ms,
                 "kernel_share_of_step": {"k_lk_track": lk_ms / ms_total, "k_pyr_down": pyr_ms / ms_total},
                 "tracking_frame": {"algorithmic_bytes_per_step": frame_bytes,

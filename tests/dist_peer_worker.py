@@ -52,9 +52,8 @@ def main():
         assert rel(S1, S0) < 1e-11 and rel(rhs1, rhs0) < 1e-11 and abs(cost1 - cost0) < 1e-11 * cost0
         del packed
         # peer-memory path
-        blob = ba.peer_export()
         blobs = [None] * world
-        dist.all_gather_object(blobs, blob)
+        dist.all_gather_object(blobs, ba.peer_export())
         ba.peer_attach(blobs)
         dist.barrier()
         for it in range(4):

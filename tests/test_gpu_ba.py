@@ -276,8 +276,13 @@ def test_peer_exchange_same_process(bindings, synthetic):
         with pytest.raises(bindings.Vio360Error):
             bas[0].fetch_reduced_system()           # built but not exchanged: no silent partial result
         assert bas[0].reduced_band_dev() is None    # the band must not be all-reduced behind the exchange
+        for c in ctxs:
+            c.synchronize()                         # ranks sharing ONE device: the exchange kernels wait for each other and
+                                                    # must not hold SM slots another rank's tile kernel still needs
         for ba in bas:
             ba.peer_exchange()                      # asynchronous: the three kernels meet on the device
+        with pytest.raises(bindings.Vio360Error):
+            bas[0].peer_exchange()                  # a second exchange without a new build
         outs = [ba.fetch_reduced_system() for ba in bas]
         S, rhs, cost = outs[0]
         assert rel_err(S, ref["S"]) < TOL and rel_err(rhs, ref["rhs"]) < TOL and abs(cost - ref["cost"]) < TOL * ref["cost"]

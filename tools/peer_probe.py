@@ -1,4 +1,4 @@
-"""tools/peer_probe.py -- latency of vio360_ba_peer_exchange alone (no build in between), developer probe.
+"""tools/peer_probe.py -- per-kernel times of build + vio360_ba_peer_exchange in an LM loop on every rank, developer probe
 usage: python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P tools/peer_probe.py"""
 import importlib
 import os
@@ -31,16 +31,6 @@ def main():
     ba.peer_attach(blobs)
     dist.barrier()
     ba.build_reduced_system(None, True, fetch=False)
-    for reps in (1, 50, 50):
-        ba.peer_exchange()
-        ctx.synchronize(); dist.barrier(); torch.cuda.synchronize()
-        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        for _ in range(reps):
-            ba.peer_exchange()
-        e1.record(stream)
-        ctx.synchronize()
-        print("rank %d: %d back-to-back exchanges, %.2f us each" % (rank, reps, e0.elapsed_time(e1) * 1e3 / reps), flush=True)
     # skew probe: build + exchange, events around each part
     ctx.enable_kernel_timing(True); ctx.reset_kernel_times()
     for _ in range(30):
