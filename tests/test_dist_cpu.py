@@ -47,8 +47,27 @@ def _worker(rank, world, port, out):
     packed = torch.from_numpy(np.concatenate([S.ravel(), rhs, [cs]]))
     dist.all_reduce(packed)              # the one collective of the path
     # the same exchange with the block-band payload (vio360_ba_reduced_band_dev / vio360_ba_expand_band)
-    band = torch.from_numpy(sharding.band_pack(S, rhs, cs, band_w=8))
+    band_part = sharding.band_pack(S, rhs, cs, band_w=8)
+    band = torch.from_numpy(band_part.copy())
     dist.all_reduce(band)
+    # the peer-memory exchange (vio360_ba_peer_exchange) stated in numpy: every rank publishes the block rows its
+    # landmarks touch, pulls a row only from the ranks covering it and sums in rank order; no rank adds the pose
+    # diagonal to its partial, the exchange adds it once
+    fm = W.schur(rs, Jps, Jls, Dr)[2]                  # pose -> reduced block index, -1 for constant poses
+    rows_mine = sharding.peer_rows(win["pose_idx"], win["point_idx"], fm, lo, hi)
+    Sn, rhsn, _ = W.schur(rs, Jps, Jls, np.concatenate([np.zeros(6 * win["K"]), D[6 * win["K"]:]]))
+    mine = sharding.band_pack(Sn, rhsn, cs, band_w=8)
+    n_free = Sn.shape[0] // 6
+    outside = np.ones(n_free, bool); outside[rows_mine[0]:rows_mine[1]] = False
+    assert not mine[:n_free * 8 * 36].reshape(n_free, -1)[outside].any()      # nothing outside the published rows
+    gathered = [None] * world
+    dist.all_gather_object(gathered, (mine, rows_mine))
+    pose_diag = D[:6 * win["K"]].reshape(-1, 6)[fm >= 0].ravel()
+    Sp, rhsp, cp = sharding.peer_exchange_sum([g[0] for g in gathered], [g[1] for g in gathered], n_free, 8, pose_diag)
+    digest = torch.tensor([float(Sp.sum()), float(rhsp.sum()), cp], dtype=torch.float64)
+    digests = [torch.zeros_like(digest) for _ in range(world)]
+    dist.all_gather(digests, digest)
+    assert all(torch.equal(d_, digests[0]) for d_ in digests)                 # bit-identical on every rank
     if rank == 0:
         Sf, rhsf, _ = full.schur(r, Jp, Jl, D)
         n = Sf.shape[0]
@@ -56,7 +75,9 @@ def _worker(rank, world, port, out):
         rel = lambda a, b: float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
         Sb, rhsb, cb = sharding.band_expand(band.numpy(), n // 6, band_w=8)
         np.save(out, np.array([rel(got[:n * n], Sf.ravel()), rel(got[n * n:n * n + n], rhsf), abs(got[-1] - cost) / cost,
-                               rel(Sb, Sf), rel(rhsb, rhsf), abs(cb - cost) / cost, band.numel() / packed.numel()]))
+                               rel(Sb, Sf), rel(rhsb, rhsf), abs(cb - cost) / cost, band.numel() / packed.numel(),
+                               rel(Sp, Sf), rel(rhsp, rhsf), abs(cp - cost) / cost,
+                               float(sum(g[1][1] - g[1][0] for g in gathered)) / (world * n_free)]))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -83,6 +104,8 @@ def test_two_rank_schur_allreduce(tmp_path):
     res = np.load(out)
     assert res[0] < 1e-9 and res[1] < 1e-9 and res[2] < 1e-12
     assert res[3] < 1e-9 and res[4] < 1e-9 and res[5] < 1e-12 and res[6] < 0.75      # band payload: same sums, fewer bytes
+    assert res[7] < 1e-9 and res[8] < 1e-9 and res[9] < 1e-12                        # peer exchange: same system
+    assert res[10] <= 1.0                                                            # rows pulled per rank / all rows
 
 
 def test_band_pack_expand_round_trip():
