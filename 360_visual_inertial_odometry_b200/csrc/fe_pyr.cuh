@@ -151,8 +151,9 @@ __device__ __forceinline__ uint32_t pyr_hrow(const PyrRow& r0, const PyrRow& r1,
     return __byte_perm(p01, p23, 0x7531);
 }
 
-// strip_rows (even) output rows per warp; two output rows per loop trip with the four input
-// rows of the next trip already in flight (1 KB of loads per warp outstanding).
+// strip_rows (a multiple of 4) output rows per warp; four output rows per loop trip with the eight input
+// rows of the next trip already in flight (2 KB of loads per warp outstanding: at ~24 resident warps per SM
+// that is the ~35 KB per SM HBM3e needs in flight; with 1 KB the kernel stalled at 4.0 TB/s).
 __global__ void __launch_bounds__(kPyrFastThreads)
 k_pyr_down8(const PyrJob* __restrict__ jobs, int w, int h, int dw, int dh, int nwx, int nsy, int total_warps,
             int strip_rows) {
@@ -169,21 +170,30 @@ k_pyr_down8(const PyrJob* __restrict__ jobs, int w, int h, int dw, int dh, int n
     const int y0 = sy * strip_rows, y1 = min(y0 + strip_rows, dh);
     auto load = [&](int r) { return __ldg(reinterpret_cast<const uint2*>(src + (size_t)reflect101(r, h) * job.spitch)); };
     PyrRow r0 = pyr_unpack(load(2 * y0 - 2)), r1 = pyr_unpack(load(2 * y0 - 1)), r2 = pyr_unpack(load(2 * y0));
-    uint2 n3 = load(2 * y0 + 1), n4 = load(2 * y0 + 2), n5 = load(2 * y0 + 3), n6 = load(2 * y0 + 4);
+    uint2 n[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) n[i] = load(2 * y0 + 1 + i);
     uint8_t* dst = job.dst + (size_t)y0 * job.dpitch + (col0 >> 1);
-    for (int y = y0; y < y1; y += 2) {
-        const PyrRow r3 = pyr_unpack(n3), r4 = pyr_unpack(n4), r5 = pyr_unpack(n5), r6 = pyr_unpack(n6);
-        if (y + 2 < y1) {
-            n3 = load(2 * y + 5); n4 = load(2 * y + 6); n5 = load(2 * y + 7); n6 = load(2 * y + 8);
+    for (int y = y0; y < y1; y += 4) {
+        PyrRow q[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) q[i] = pyr_unpack(n[i]);
+        if (y + 4 < y1) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) n[i] = load(2 * y + 9 + i);
         }
-        const uint32_t o0 = pyr_hrow(r0, r1, r2, r3, r4, left_edge, right_edge);
-        const uint32_t o1 = pyr_hrow(r2, r3, r4, r5, r6, left_edge, right_edge);
+        const uint32_t o0 = pyr_hrow(r0, r1, r2, q[0], q[1], left_edge, right_edge);
+        const uint32_t o1 = pyr_hrow(r2, q[0], q[1], q[2], q[3], left_edge, right_edge);
+        const uint32_t o2 = pyr_hrow(q[1], q[2], q[3], q[4], q[5], left_edge, right_edge);
+        const uint32_t o3 = pyr_hrow(q[3], q[4], q[5], q[6], q[7], left_edge, right_edge);
         if (writer) {
             *reinterpret_cast<uint32_t*>(dst) = o0;
             if (y + 1 < y1) *reinterpret_cast<uint32_t*>(dst + job.dpitch) = o1;
+            if (y + 2 < y1) *reinterpret_cast<uint32_t*>(dst + 2 * (size_t)job.dpitch) = o2;
+            if (y + 3 < y1) *reinterpret_cast<uint32_t*>(dst + 3 * (size_t)job.dpitch) = o3;
         }
-        dst += 2 * (size_t)job.dpitch;
-        r0 = r4; r1 = r5; r2 = r6;
+        dst += 4 * (size_t)job.dpitch;
+        r0 = q[5]; r1 = q[6]; r2 = q[7];
     }
 }
 
