@@ -372,6 +372,8 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
         if (mem_space == VIO360_MEM_HOST)
             VIO_CUDA(ctx, cudaMemcpyAsync(s->d_pts_in.p, s->h_pts_in.p, off * 8, cudaMemcpyHostToDevice, st));
     }
+    // an error return below must not leave uploads of the caller's frames in flight on the copy stream
+    struct CopyGuard { cudaStream_t st; bool armed; ~CopyGuard() { if (armed) cudaStreamSynchronize(st); } } copy_guard{s->copy_stream, piped};
     // descriptors first, bulk frame uploads second: host-to-device copies of both streams are served in issue
     // order, so a descriptor copy queued behind the frames would hold every kernel back until the last frame
     const size_t per = (size_t)std::max(0, s->nlevels - 1);
@@ -426,6 +428,7 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
         VIO_CUDA(ctx, cudaMemcpyAsync(ho + off * 12, s->d_status.p, off, cudaMemcpyDeviceToHost, st));
         VIO_CUDA(ctx, cudaMemcpyAsync(ho + off * 13, s->d_keep.p, off, cudaMemcpyDeviceToHost, st));
         VIO_CUDA(ctx, cudaStreamSynchronize(st));
+        copy_guard.armed = false;      // the main stream waited for every upload group
         if (fe_trace) fprintf(stderr, "[vio360 fe trace] %d jobs: copies enqueued in %.0f us, kernels in %.0f us, stream idle %.0f us later\n",
                               n_jobs, t_copies - (ts_begin.tv_sec * 1e6 + ts_begin.tv_nsec * 1e-3), t_kernels - t_copies, now_us() - t_kernels);
         size_t o = 0;
