@@ -979,17 +979,24 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
                 if (peer) ba->peer.band_epoch = ba->peer.epoch + 1;
                 if (nrows > 0) {
                 KernelTimer kt_(ctx, "k_schur_reduce");
-                // few block pairs (a short window with many chunks per pose): more walkers per pair
-                if ((size_t)nblk.x * nblk.y >= 2000)
-                    k_schur_reduce<true, 7><<<nblk, 36 * 7, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
-                                                           ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),
-                                                           ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int2>(), ba->d_reach.as<int>(),
-                                                           ba->d_free_pose.as<int>(), Dp, add_diag, band, band_w, row0, ba->n_free);
-                else
-                    k_schur_reduce<true, 14><<<nblk, 36 * 14, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
-                                                           ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),
-                                                           ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int2>(), ba->d_reach.as<int>(),
-                                                           ba->d_free_pose.as<int>(), Dp, add_diag, band, band_w, row0, ba->n_free);
+                // walkers per block pair: enough for one round of four chunks each over the longest per-pose chunk list
+                // (few block pairs, i.e. a short window with many chunks per pose: more walkers per pair)
+                int max_cov = 0;
+                for (int p = 0; p < ba->K; ++p) max_cov = std::max(max_cov, ba->cov_ptr[p + 1] - ba->cov_ptr[p]);
+                static const int force_lanes = getenv("VIO360_BA_RED_LANES") ? atoi(getenv("VIO360_BA_RED_LANES")) : 0;
+                int lanes = (size_t)nblk.x * nblk.y >= 2000 ? 7 : 14;
+                if ((size_t)nblk.x * nblk.y >= 2000 && max_cov <= 20) lanes = 5;
+                if (force_lanes) lanes = force_lanes;
+#define VIO_REDUCE_LAUNCH(L)                                                                                                   \
+                k_schur_reduce<true, L><<<nblk, 36 * L, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(), \
+                                                           ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),  \
+                                                           ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int2>(), ba->d_reach.as<int>(), \
+                                                           ba->d_free_pose.as<int>(), Dp, add_diag, band, band_w, row0, ba->n_free)
+                if (lanes <= 3) VIO_REDUCE_LAUNCH(3);
+                else if (lanes <= 5) VIO_REDUCE_LAUNCH(5);
+                else if (lanes <= 7) VIO_REDUCE_LAUNCH(7);
+                else VIO_REDUCE_LAUNCH(14);
+#undef VIO_REDUCE_LAUNCH
                 }
             } else {
                 ba->band_zero_n = -1; ba->band_w = 0; ba->dense_stale = false;
