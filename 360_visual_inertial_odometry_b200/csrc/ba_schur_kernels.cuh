@@ -297,16 +297,21 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
         }
     }
     __syncthreads();
-    // ---- tile -> slab (dense kST x kST, upper 8x8 tiles of the chunk's span only)
+    // ---- tile -> slab, upper 8x8 tiles of the chunk's span only.  The slab is pose-block major
+    // [pose slot i][pose slot j][6 x 6] so that k_schur_reduce reads a block as 288 contiguous bytes; a lane's
+    // two columns (even, odd) always fall into the same 6-wide block.
     {
         double* outS = partS + (size_t)blockIdx.x * kST * kST;
         const int nt = 2 * ((6 * ch.span + 15) >> 4);
         const int fr = lane >> 2, fc = lane & 3;
-        for (int ti = 0; ti < nt; ++ti)
+        for (int ti = 0; ti < nt; ++ti) {
+            const int R = 8 * ti + fr, rb = R / 6, ra = R - 6 * rb;
             for (int tj = ti + warp; tj < nt; tj += kSThreads / 32) {
                 const double2 v = *(reinterpret_cast<const double2*>(St + schur_tile_index(ti, tj) * 64) + lane);
-                *reinterpret_cast<double2*>(outS + (size_t)(8 * ti + fr) * kST + 8 * tj + 2 * fc) = v;
+                const int C = 8 * tj + 2 * fc, cb = C / 6, ca = C - 6 * cb;
+                *reinterpret_cast<double2*>(outS + (size_t)(rb * kSWin + cb) * 36 + ra * 6 + ca) = v;
             }
+        }
     }
     // ---- cost of the chunk
     cost = warp_sum(cost);
@@ -379,7 +384,7 @@ __device__ __forceinline__ void schur_reduce_block(const int bi, const int bj, c
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 v[u] = (in_env && c[u] >= 0 && pj < win[u].x + win[u].y)   // pj >= pi >= pbase
-                           ? partS[(size_t)c[u] * kST * kST + (size_t)(6 * (pi - win[u].x) + a) * kST + 6 * (pj - win[u].x) + b]
+                           ? partS[(size_t)c[u] * kST * kST + (size_t)((pi - win[u].x) * kSWin + (pj - win[u].x)) * 36 + e]   // pose-block major slab
                            : 0.0;
                 vr[u] = (do_rhs && c[u] >= 0) ? partRhs[(size_t)c[u] * kST + 6 * (pi - win[u].x) + e] : 0.0;
             }
