@@ -304,6 +304,44 @@ def test_peer_exchange_same_process(bindings, synthetic):
         c.close()
 
 
+def test_peer_exchange_two_devices_one_process(bindings, synthetic):
+    """One process driving two GPUs (the reference is a single process): the ranks' buffers are mapped by plain peer
+    access (cudaDeviceEnablePeerAccess) instead of cudaIpc handles; needs two GPUs."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    win = synthetic.make_ba_window(K=60, M=3000, degree=10, seed=91, mid_iteration=True)
+    ref = _oracle_all(win)
+    ctxs = [bindings.Context(0), bindings.Context(1)]
+    bas = []
+    for rank in range(2):
+        ba = bindings.BAWindow(ctxs[rank], win)
+        ba.set_shard(rank, 2)
+        ba.set_parameters(win["pose_delta"], win["points"])
+        ba.set_lm_diagonal(ref["D"])
+        bas.append(ba)
+    blobs = [ba.peer_export() for ba in bas]
+    for ba in bas:
+        ba.peer_attach(blobs)
+    for _ in range(3):
+        for ba in bas:
+            ba.build_reduced_system(None, True, fetch=False)
+        for ba in bas:
+            ba.peer_exchange()
+    outs = [ba.fetch_reduced_system() for ba in bas]
+    S, rhs, cost = outs[0]
+    assert rel_err(S, ref["S"]) < TOL and rel_err(rhs, ref["rhs"]) < TOL and abs(cost - ref["cost"]) < TOL * ref["cost"]
+    assert np.array_equal(outs[1][0], S) and np.array_equal(outs[1][1], rhs) and outs[1][2] == cost
+    for c in ctxs:
+        c.synchronize()
+    for ba in bas:
+        ba.peer_detach()
+    for ba in bas:
+        ba.close()
+    for c in ctxs:
+        c.close()
+
+
 def test_peer_exchange_two_processes():
     """The same exchange across PROCESSES (one per GPU, cudaIpc handles gathered through torch.distributed),
     checked against the NCCL allreduce of the band and the unsharded build; needs two GPUs."""
