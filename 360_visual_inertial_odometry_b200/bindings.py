@@ -23,7 +23,7 @@ EXPORTS = [
     "vio360_fe_detect_batch", "vio360_fe_pyramid", "vio360_fe_min_eigen_val",
     "vio360_fe_ransac_rotation", "vio360_fe_ransac_rotation_batch", "vio360_fe_cluster_filter", "vio360_fe_grid_cap",
     "vio360_ba_create", "vio360_ba_destroy", "vio360_ba_set_structure", "vio360_ba_set_outliers",
-    "vio360_ba_set_shard", "vio360_ba_set_parameters", "vio360_ba_evaluate",
+    "vio360_ba_set_shard", "vio360_ba_set_parameters", "vio360_ba_evaluate", "vio360_ba_evaluate_f32",
     "vio360_ba_get_residuals_jacobians", "vio360_ba_normal_blocks", "vio360_ba_reduced_dim",
     "vio360_ba_build_reduced_system", "vio360_ba_set_lm_diagonal", "vio360_ba_reduced_system_dev", "vio360_ba_fetch_reduced_system",
     "vio360_ba_reduced_band_dev", "vio360_ba_expand_band",
@@ -108,6 +108,7 @@ def load():
     lib.vio360_ba_set_shard.argtypes = [C.c_void_p, C.c_int, C.c_int]
     lib.vio360_ba_set_parameters.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     lib.vio360_ba_evaluate.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double)]
+    lib.vio360_ba_evaluate_f32.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double)]
     lib.vio360_ba_get_residuals_jacobians.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.vio360_ba_normal_blocks.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 5
     lib.vio360_ba_reduced_dim.argtypes = [C.c_void_p]
@@ -414,9 +415,10 @@ class BAWindow:
         pd = np.ascontiguousarray(pose_delta, np.float64); pts = np.ascontiguousarray(points, np.float64)
         self.ctx.check(self.lib.vio360_ba_set_parameters(self.h, _ptr(pd), _ptr(pts)))
 
-    def evaluate(self, want_jacobians=True, apply_loss=True, fetch=True):
+    def evaluate(self, want_jacobians=True, apply_loss=True, fetch=True, f32=False):
         cost = C.c_double(0)
-        self.ctx.check(self.lib.vio360_ba_evaluate(self.h, int(want_jacobians), int(apply_loss), C.byref(cost)))
+        fn = self.lib.vio360_ba_evaluate_f32 if f32 else self.lib.vio360_ba_evaluate
+        self.ctx.check(fn(self.h, int(want_jacobians), int(apply_loss), C.byref(cost)))
         if not fetch:
             return cost.value
         r = np.zeros((self.O, 2)); Jp = np.zeros((self.O, 2, 6)) if want_jacobians else None

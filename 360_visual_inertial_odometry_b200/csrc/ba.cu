@@ -179,6 +179,36 @@ __global__ void __launch_bounds__(128) k_evaluate(BaDev d, bool apply_loss, doub
     block_sum_to(cost, partials);
 }
 
+// Optional fp32 mode of the factor evaluation (north star: "1e-4 in an optional fp32 mode"): the same math with
+// T = float on the FP32 pipe; prepared poses, points and observations are rounded to float on load, results are
+// widened to the double buffers Ceres reads.  The cost partials are summed in double.
+template <bool WANT_JAC>
+__global__ void __launch_bounds__(128) k_evaluate_f32(BaDev d, bool apply_loss, double* __restrict__ r_out,
+                                                      double* __restrict__ Jp_out, double* __restrict__ Jl_out,
+                                                      double* __restrict__ partials) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    double cost = 0.0;
+    if (i < d.O) {
+        const int p = d.pose[i], l = d.point[i];
+        float pose[kPoseStride];
+#pragma unroll
+        for (int j = 0; j < kPoseStride; ++j) pose[j] = (float)__ldg(d.posebuf + kPoseStride * (size_t)p + j);
+        const float Pw[3] = {(float)__ldg(d.points + 3 * (size_t)l), (float)__ldg(d.points + 3 * (size_t)l + 1),
+                             (float)__ldg(d.points + 3 * (size_t)l + 2)};
+        float r[2], F[12], E[6];
+        cost = (double)obs_evaluate<WANT_JAC>(pose, Pw, (float)d.u[i], (float)d.v[i], d.outlier[i] != 0, d.cam, apply_loss, r, F, E);
+        const size_t o = (size_t)d.orig[i];
+        r_out[2 * o] = r[0]; r_out[2 * o + 1] = r[1];
+        if (WANT_JAC) {
+#pragma unroll
+            for (int j = 0; j < 12; ++j) Jp_out[12 * o + j] = F[j];
+#pragma unroll
+            for (int j = 0; j < 6; ++j) Jl_out[6 * o + j] = E[j];
+        }
+    }
+    block_sum_to(cost, partials);
+}
+
 __global__ void __launch_bounds__(128) k_chi2(BaDev d, double thr, double* __restrict__ chi2,
                                               unsigned char* __restrict__ flag) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -744,7 +774,14 @@ static int sum_partials(vio360_ba* ba, int nblocks, double* dev_out) {
     return VIO360_OK;
 }
 
+static int ba_evaluate_impl(vio360_ba* ba, int want_jacobians, int apply_loss, double* cost, bool f32);
 extern "C" int vio360_ba_evaluate(vio360_ba* ba, int want_jacobians, int apply_loss, double* cost) {
+    return ba_evaluate_impl(ba, want_jacobians, apply_loss, cost, false);
+}
+extern "C" int vio360_ba_evaluate_f32(vio360_ba* ba, int want_jacobians, int apply_loss, double* cost) {
+    return ba_evaluate_impl(ba, want_jacobians, apply_loss, cost, true);
+}
+static int ba_evaluate_impl(vio360_ba* ba, int want_jacobians, int apply_loss, double* cost, bool f32) {
     if (!ba) return VIO360_ERR_INVALID;
     vio360_ctx* ctx = ba->ctx;
     if (!ba->has_params) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_evaluate before ba_set_parameters");
@@ -756,7 +793,15 @@ extern "C" int vio360_ba_evaluate(vio360_ba* ba, int want_jacobians, int apply_l
     const int nb = std::max(1, (O + 127) / 128);
     VIO_CUDA(ctx, ba->d_partials.reserve((size_t)(nb + 1) * 8));
     BaDev d = make_dev(ba);
-    if (want_jacobians)
+    if (f32) {
+        KernelTimer kt_(ctx, "k_evaluate_f32");
+        if (want_jacobians)
+            k_evaluate_f32<true><<<nb, 128, 0, ctx->stream>>>(d, apply_loss != 0, ba->d_r.as<double>(), ba->d_Jp.as<double>(),
+                                                             ba->d_Jl.as<double>(), ba->d_partials.as<double>());
+        else
+            k_evaluate_f32<false><<<nb, 128, 0, ctx->stream>>>(d, apply_loss != 0, ba->d_r.as<double>(), nullptr, nullptr,
+                                                              ba->d_partials.as<double>());
+    } else if (want_jacobians)
         { KernelTimer kt_(ctx, "k_evaluate");
         k_evaluate<true><<<nb, 128, 0, ctx->stream>>>(d, apply_loss != 0, ba->d_r.as<double>(), ba->d_Jp.as<double>(),
                                                      ba->d_Jl.as<double>(), ba->d_partials.as<double>());

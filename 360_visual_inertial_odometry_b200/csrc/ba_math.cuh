@@ -220,81 +220,105 @@ VIO_HD void cam_const_init(CamConst& c, double cols, double rows, const double* 
     c.huber_a = huber_a;
 }
 
+// Scalar-type helpers: the per-observation math below is written once for T = double (the parity path) and
+// T = float (the optional fp32 mode of the north star, tolerance 1e-4).
+VIO_HD float vio_rsqrt(float x) {
+#ifdef __CUDA_ARCH__
+    return rsqrtf(x);
+#else
+    return 1.0f / sqrtf(x);
+#endif
+}
+VIO_HD double m_atan2(double y, double x) { return atan2(y, x); }
+VIO_HD float m_atan2(float y, float x) { return atan2f(y, x); }
+VIO_HD double m_asin(double x) { return asin(x); }
+VIO_HD float m_asin(float x) { return asinf(x); }
+VIO_HD double m_sqrt(double x) { return sqrt(x); }
+VIO_HD float m_sqrt(float x) { return sqrtf(x); }
+VIO_HD double m_abs(double x) { return fabs(x); }
+VIO_HD float m_abs(float x) { return fabsf(x); }
+VIO_HD double m_tiny(double) { return 2.2250738585072014e-308; }   // std::numeric_limits<T>::min()
+VIO_HD float m_tiny(float) { return 1.17549435e-38f; }
+
 // Pixel error of one observation: returns branch 0 ok / 1 tiny depth / 2 large error.
-struct ObsProj { double x, y, z, L_sq, inv_L, du, dv; int branch; };
+template <typename T>
+struct ObsProjT { T x, y, z, L_sq, inv_L, du, dv; int branch; };
+using ObsProj = ObsProjT<double>;
 
 // Divisions and square roots of Factors.cpp:369-419 are restated with one reciprocal square
 // root and multiplications (the FP64 pipe has no divider; a division costs ~17 DFMA).
-VIO_HD void obs_project(const double* pose, const double* Pw, double u_obs, double v_obs,
-                        const CamConst& c, ObsProj& p) {
-    const double* Rcw = pose; const double* tcw = pose + 9;
+template <typename T>
+VIO_HD void obs_project(const T* pose, const T* Pw, T u_obs, T v_obs, const CamConst& c, ObsProjT<T>& p) {
+    const T* Rcw = pose; const T* tcw = pose + 9;
+    const T cols = (T)c.cols, rows = (T)c.rows;
     p.x = Rcw[0] * Pw[0] + Rcw[1] * Pw[1] + Rcw[2] * Pw[2] + tcw[0];
     p.y = Rcw[3] * Pw[0] + Rcw[4] * Pw[1] + Rcw[5] * Pw[2] + tcw[1];
     p.z = Rcw[6] * Pw[0] + Rcw[7] * Pw[1] + Rcw[8] * Pw[2] + tcw[2];
     p.L_sq = p.x * p.x + p.y * p.y + p.z * p.z;
-    p.branch = 0; p.du = 0.0; p.dv = 0.0; p.inv_L = 0.0;
-    if (p.L_sq < 1e-20) { p.branch = 1; return; }          // L < 1e-10
+    p.branch = 0; p.du = T(0); p.dv = T(0); p.inv_L = T(0);
+    if (p.L_sq < T(1e-20)) { p.branch = 1; return; }          // L < 1e-10
     p.inv_L = vio_rsqrt(p.L_sq);
-    const double theta = atan2(p.x, p.z);
-    const double phi = -asin(p.y * p.inv_L);
-    const double u = c.cols * (0.5 + theta * kInv2Pi);
-    const double v = c.rows * (0.5 - phi * kInvPi);
-    double du = u_obs - u;
-    if (du > c.cols * 0.5) du -= c.cols;
-    else if (du < -c.cols * 0.5) du += c.cols;
+    const T theta = m_atan2(p.x, p.z);
+    const T phi = -m_asin(p.y * p.inv_L);
+    const T u = cols * (T(0.5) + theta * (T)kInv2Pi);
+    const T v = rows * (T(0.5) - phi * (T)kInvPi);
+    T du = u_obs - u;
+    if (du > cols * T(0.5)) du -= cols;
+    else if (du < -cols * T(0.5)) du += cols;
     p.du = du; p.dv = v_obs - v;
-    if (fabs(p.du) > 100.0 || fabs(p.dv) > 100.0) p.branch = 2;
+    if (m_abs(p.du) > T(100) || m_abs(p.dv) > T(100)) p.branch = 2;
 }
 
 // BAFactor::Evaluate for one observation with a prepared pose, followed by the Huber
 // correction.  F = d r / d pose (2x6 row-major), E = d r / d point (2x3 row-major).
 // returns the block's cost 0.5 * rho(s).
-template <bool WANT_JAC>
-VIO_HD double obs_evaluate(const double* pose, const double* Pw, double u_obs, double v_obs,
-                           bool outlier, const CamConst& c, bool apply_loss, double* r,
-                           double* F, double* E) {
+template <bool WANT_JAC, typename T>
+VIO_HD T obs_evaluate(const T* pose, const T* Pw, T u_obs, T v_obs, bool outlier, const CamConst& c, bool apply_loss,
+                      T* r, T* F, T* E) {
     bool zero_j = false;
+    const T Lc0 = (T)c.Lc[0], Lc1 = (T)c.Lc[1], Lc2 = (T)c.Lc[2], Lc3 = (T)c.Lc[3];
     if (outlier) {                       // Factors.cpp:330-344
-        r[0] = 640.0; r[1] = 480.0; zero_j = true;
+        r[0] = T(640); r[1] = T(480); zero_j = true;
     } else {
-        ObsProj p;
+        ObsProjT<T> p;
         obs_project(pose, Pw, u_obs, v_obs, c, p);
-        if (p.branch == 1) { r[0] = 640.0; r[1] = 360.0; zero_j = true; }        // :378-394
-        else if (p.branch == 2) { r[0] = 100.0; r[1] = 100.0; zero_j = true; }   // :427-441
+        if (p.branch == 1) { r[0] = T(640); r[1] = T(360); zero_j = true; }        // :378-394
+        else if (p.branch == 2) { r[0] = T(100); r[1] = T(100); zero_j = true; }   // :427-441
         else {
-            r[0] = c.Lc[0] * p.du + c.Lc[1] * p.dv;
-            r[1] = c.Lc[2] * p.du + c.Lc[3] * p.dv;
+            r[0] = Lc0 * p.du + Lc1 * p.dv;
+            r[1] = Lc2 * p.du + Lc3 * p.dv;
             if (WANT_JAC) {
-                const double xz_sq = p.x * p.x + p.z * p.z;
-                const double L_sq = p.L_sq;
-                if (xz_sq < 1e-10 || L_sq < 1e-10) zero_j = true;                // :466-476
+                const T xz_sq = p.x * p.x + p.z * p.z;
+                const T L_sq = p.L_sq;
+                if (xz_sq < T(1e-10) || L_sq < T(1e-10)) zero_j = true;                // :466-476
                 else {
-                    const double inv_xz = vio_rsqrt(xz_sq);
-                    const double xz_norm = xz_sq * inv_xz;
-                    const double inv_xz_sq = inv_xz * inv_xz, inv_L_sq = p.inv_L * p.inv_L;
-                    const double inv_den = inv_L_sq * inv_xz;                  // 1 / (L^2 * |xz|)
-                    double Jp0[3], Jp1[3];
-                    Jp0[0] = -c.c2pi * p.z * inv_xz_sq; Jp0[1] = 0.0; Jp0[2] = c.c2pi * p.x * inv_xz_sq;
-                    Jp1[0] = c.rpi * (p.x * p.y) * inv_den;
-                    Jp1[1] = -c.rpi * xz_norm * inv_L_sq;
-                    Jp1[2] = c.rpi * (p.y * p.z) * inv_den;
-                    double Jw0[3], Jw1[3];
+                    const T c2pi = (T)c.c2pi, rpi = (T)c.rpi;
+                    const T inv_xz = vio_rsqrt(xz_sq);
+                    const T xz_norm = xz_sq * inv_xz;
+                    const T inv_xz_sq = inv_xz * inv_xz, inv_L_sq = p.inv_L * p.inv_L;
+                    const T inv_den = inv_L_sq * inv_xz;                  // 1 / (L^2 * |xz|)
+                    T Jp0[3], Jp1[3];
+                    Jp0[0] = -c2pi * p.z * inv_xz_sq; Jp0[1] = T(0); Jp0[2] = c2pi * p.x * inv_xz_sq;
+                    Jp1[0] = rpi * (p.x * p.y) * inv_den;
+                    Jp1[1] = -rpi * xz_norm * inv_L_sq;
+                    Jp1[2] = rpi * (p.y * p.z) * inv_den;
+                    T Jw0[3], Jw1[3];
 #pragma unroll
                     for (int j = 0; j < 3; ++j) {
-                        Jw0[j] = c.Lc[0] * Jp0[j] + c.Lc[1] * Jp1[j];
-                        Jw1[j] = c.Lc[2] * Jp0[j] + c.Lc[3] * Jp1[j];
+                        Jw0[j] = Lc0 * Jp0[j] + Lc1 * Jp1[j];
+                        Jw1[j] = Lc2 * Jp0[j] + Lc3 * Jp1[j];
                     }
-                    const double* Rbw = pose + 12; const double* tbw = pose + 21;
-                    const double* Mcp = pose + 24;
-                    const double Pb0 = Rbw[0] * Pw[0] + Rbw[1] * Pw[1] + Rbw[2] * Pw[2] + tbw[0];
-                    const double Pb1 = Rbw[3] * Pw[0] + Rbw[4] * Pw[1] + Rbw[5] * Pw[2] + tbw[1];
-                    const double Pb2 = Rbw[6] * Pw[0] + Rbw[7] * Pw[1] + Rbw[8] * Pw[2] + tbw[2];
+                    const T* Rbw = pose + 12; const T* tbw = pose + 21;
+                    const T* Mcp = pose + 24;
+                    const T Pb0 = Rbw[0] * Pw[0] + Rbw[1] * Pw[1] + Rbw[2] * Pw[2] + tbw[0];
+                    const T Pb1 = Rbw[3] * Pw[0] + Rbw[4] * Pw[1] + Rbw[5] * Pw[2] + tbw[1];
+                    const T Pb2 = Rbw[6] * Pw[0] + Rbw[7] * Pw[1] + Rbw[8] * Pw[2] + tbw[2];
                     // A = Jw * Rcb ; translation block = -A ; rotation block rows = a x Pb
-                    double A0[3], A1[3];
+                    T A0[3], A1[3];
 #pragma unroll
                     for (int j = 0; j < 3; ++j) {
-                        A0[j] = Jw0[0] * c.Rcb[j] + Jw0[1] * c.Rcb[3 + j] + Jw0[2] * c.Rcb[6 + j];
-                        A1[j] = Jw1[0] * c.Rcb[j] + Jw1[1] * c.Rcb[3 + j] + Jw1[2] * c.Rcb[6 + j];
+                        A0[j] = Jw0[0] * (T)c.Rcb[j] + Jw0[1] * (T)c.Rcb[3 + j] + Jw0[2] * (T)c.Rcb[6 + j];
+                        A1[j] = Jw1[0] * (T)c.Rcb[j] + Jw1[1] * (T)c.Rcb[3 + j] + Jw1[2] * (T)c.Rcb[6 + j];
                     }
                     F[0] = -A0[0]; F[1] = -A0[1]; F[2] = -A0[2];
                     F[3] = A0[1] * Pb2 - A0[2] * Pb1;
@@ -315,19 +339,21 @@ VIO_HD double obs_evaluate(const double* pose, const double* Pw, double u_obs, d
     }
     if (WANT_JAC && zero_j) {
 #pragma unroll
-        for (int j = 0; j < 12; ++j) F[j] = 0.0;
+        for (int j = 0; j < 12; ++j) F[j] = T(0);
 #pragma unroll
-        for (int j = 0; j < 6; ++j) E[j] = 0.0;
+        for (int j = 0; j < 6; ++j) E[j] = T(0);
     }
     // ResidualBlock::Evaluate tail: cost + Corrector (rho'' <= 0 for Huber)
-    const double s = r[0] * r[0] + r[1] * r[1];
-    if (!apply_loss || !(c.huber_a > 0.0)) return 0.5 * s;
-    const double b = c.huber_a * c.huber_a;
+    const T s = r[0] * r[0] + r[1] * r[1];
+    const T ha = (T)c.huber_a;
+    if (!apply_loss || !(c.huber_a > 0.0)) return T(0.5) * s;
+    const T b = ha * ha;
     if (s > b) {
-        const double rs = vio_rsqrt(s), rt = s * rs;
-        const double rho0 = 2.0 * c.huber_a * rt - b;
-        const double rho1 = fmax(2.2250738585072014e-308, c.huber_a * rs);
-        const double sc = sqrt(rho1);
+        const T rs = vio_rsqrt(s), rt = s * rs;
+        const T rho0 = T(2) * ha * rt - b;
+        const T rho1c = ha * rs;
+        const T rho1 = rho1c > m_tiny(T(0)) ? rho1c : m_tiny(T(0));
+        const T sc = m_sqrt(rho1);
         if (WANT_JAC && !zero_j) {
 #pragma unroll
             for (int j = 0; j < 12; ++j) F[j] *= sc;
@@ -335,9 +361,9 @@ VIO_HD double obs_evaluate(const double* pose, const double* Pw, double u_obs, d
             for (int j = 0; j < 6; ++j) E[j] *= sc;
         }
         r[0] *= sc; r[1] *= sc;
-        return 0.5 * rho0;
+        return T(0.5) * rho0;
     }
-    return 0.5 * s;
+    return T(0.5) * s;
 }
 
 // BAFactor::compute_chi_square (Factors.cpp:544-612) with a prepared pose.

@@ -214,6 +214,10 @@ int vio360_ba_set_parameters(vio360_ba* ba, const double* pose_delta, const doub
  * (program_evaluator.h:187-258; Factors.cpp:327-542) incl. HuberLoss + Corrector
  * (residual_block.cc:161-195) when apply_loss != 0.  *cost = sum of 0.5*rho(s).      */
 int vio360_ba_evaluate(vio360_ba* ba, int want_jacobians, int apply_loss, double* cost);
+/* The optional fp32 mode of the north star: the same per-observation math (Factors.cpp:327-542 with the
+ * Huber correction) evaluated in float on the FP32 pipe from the fp64 prepared poses; results are stored
+ * as double and read with vio360_ba_get_residuals_jacobians.  Parity bar 1e-4 relative (max-norm). */
+int vio360_ba_evaluate_f32(vio360_ba* ba, int want_jacobians, int apply_loss, double* cost);
 /* Copy out the last evaluate(): r O x 2, Jp O x 12 (2x6 row-major), Jl O x 6 (2x3
  * row-major), in the caller's observation order.  Any pointer may be NULL.          */
 int vio360_ba_get_residuals_jacobians(vio360_ba* ba, double* r, double* Jp, double* Jl);

@@ -29,6 +29,26 @@ double emu_evaluate(int O, const int* pose_idx, const int* point_idx, const doub
     return cost;
 }
 
+// the fp32 mode (k_evaluate_f32): poses, points and observations rounded to float, float math, widened results
+double emu_evaluate_f32(int O, const int* pose_idx, const int* point_idx, const double* u, const double* v,
+                        const unsigned char* outlier, const double* posebuf, const double* points, double cols,
+                        double rows, const double* info, const double* Tcb, double huber_a, int apply_loss,
+                        double* r, double* Jp, double* Jl) {
+    CamConst cam;
+    cam_const_init(cam, cols, rows, info, Tcb, huber_a);
+    double cost = 0.0;
+    for (int i = 0; i < O; ++i) {
+        float pose[kPoseStride], Pw[3], rf[2], F[12], E[6];
+        for (int j = 0; j < kPoseStride; ++j) pose[j] = (float)posebuf[kPoseStride * pose_idx[i] + j];
+        for (int j = 0; j < 3; ++j) Pw[j] = (float)points[3 * point_idx[i] + j];
+        cost += (double)obs_evaluate<true>(pose, Pw, (float)u[i], (float)v[i], outlier && outlier[i], cam, apply_loss != 0, rf, F, E);
+        r[2 * i] = rf[0]; r[2 * i + 1] = rf[1];
+        for (int j = 0; j < 12; ++j) Jp[12 * i + j] = F[j];
+        for (int j = 0; j < 6; ++j) Jl[6 * i + j] = E[j];
+    }
+    return cost;
+}
+
 void emu_so3_project(const double* M, double* R) { so3_project(M, R); }
 void emu_inv_spd3(const double* m6, double* inv6) { inv_spd3(m6, inv6); }
 }

@@ -103,6 +103,29 @@ def test_golden_window(bindings, ctx):
     _check_window(bindings, ctx, win, ref)
 
 
+def test_evaluate_fp32_mode(bindings, ctx, synthetic):
+    """The optional fp32 mode of the factor evaluation (north star: 1e-4 relative): k_evaluate_f32 against the fp64
+    oracle on the local window, at the linearisation point and mid-iteration, with and without the loss."""
+    for mid in (False, True):
+        win = synthetic.make_ba_window(K=10, M=2000, seed=20000, mid_iteration=mid)
+        Wo = ba_oracle.Window(win)
+        ba = bindings.BAWindow(ctx, win)
+        ba.set_parameters(win["pose_delta"], win["points"])
+        for loss in (True, False):
+            r0, Jp0, Jl0, cost0 = Wo.evaluate(win["pose_delta"], win["points"], apply_loss=loss)
+            r, Jp, Jl, cost = ba.evaluate(True, loss, f32=True)
+            O = len(r0)
+            same = (np.abs(Jp0).reshape(O, -1).max(axis=1) == 0) == (np.abs(Jp).reshape(O, -1).max(axis=1) == 0)
+            assert same.mean() > 0.999          # a float-rounded projection may cross the 100 px clamp the other way
+            assert rel_err(r[same], r0[same]) < 1e-4 and rel_err(Jp[same], Jp0[same]) < 1e-4 and rel_err(Jl[same], Jl0[same]) < 1e-4
+            if same.all():
+                assert abs(cost - cost0) < 1e-4 * cost0
+            assert not np.array_equal(r, r0)    # it ran in float
+            r64, _, _, _ = ba.evaluate(True, loss)          # the fp64 path is untouched by the mode
+            assert rel_err(r64, r0) < TOL
+        ba.close()
+
+
 def test_local_window_c3(bindings, ctx, synthetic):
     """BASELINE config 3: 10 keyframes, ~20k observations, mid-iteration state."""
     win = synthetic.make_ba_window(K=10, M=2000, seed=20000, mid_iteration=True)

@@ -217,3 +217,19 @@ def test_device_arithmetic_on_host(win, emu_lib):
     c0, _ = W.chi2(win["pose_delta"], win["points"])
     assert rel_err(r, r0) < 1e-12 and rel_err(Jp, Jp0) < 1e-12 and rel_err(Jl, Jl0) < 1e-12
     assert abs(cost - cost0) < 1e-12 * cost0 and rel_err(chi2, c0) < 1e-12
+    # the optional fp32 mode (vio360_ba_evaluate_f32): same math in float, north-star bar 1e-4 relative
+    r32 = np.zeros((O, 2)); Jp32 = np.zeros((O, 2, 6)); Jl32 = np.zeros((O, 2, 3))
+    emu_lib.emu_evaluate_f32.restype = C.c_double
+    cost32 = emu_lib.emu_evaluate_f32(O, win["pose_idx"].ctypes.data_as(ip), win["point_idx"].ctypes.data_as(ip),
+                                      win["obs_u"].ctypes.data_as(dp), win["obs_v"].ctypes.data_as(dp),
+                                      win["outlier"].ctypes.data_as(up), posebuf.ctypes.data_as(dp), pts.ctypes.data_as(dp),
+                                      C.c_double(win["cols"]), C.c_double(win["rows"]), info.ctypes.data_as(dp),
+                                      Tcb.ctypes.data_as(dp), C.c_double(win["huber_a"]), 1, r32.ctypes.data_as(dp),
+                                      Jp32.ctypes.data_as(dp), Jl32.ctypes.data_as(dp))
+    special = np.abs(Jp0).reshape(O, -1).max(axis=1) == 0
+    # a float-rounded observation can cross the 100 px clamp the other way: compare the rows both precisions treat alike
+    same = special == (np.abs(Jp32).reshape(O, -1).max(axis=1) == 0)
+    assert same.mean() > 0.999
+    assert rel_err(r32[same], r0[same]) < 1e-4 and rel_err(Jp32[same], Jp0[same]) < 1e-4 and rel_err(Jl32[same], Jl0[same]) < 1e-4
+    assert abs(cost32 - cost0) < 1e-4 * cost0
+    assert not np.array_equal(r32[~special], r0[~special])          # it really ran in float
