@@ -84,6 +84,9 @@ struct vio360_ba {
         bool trace = false;                                 // VIO360_PEER_TRACE=1: device time stamps of the exchange kernel
         int world = 0;
         unsigned band_epoch = 0;         // epoch the last build wrote its band for
+        bool stale = false;              // set_structure / set_shard ran after the export: row ranges, band width and
+                                         // chunk coverage the peers hold are those of the OLD structure
+        int same_device = 1;             // ranks of the world that share this rank's device (tests, MPS)
     } peer;
     int peer_world() const { return peer.world; }
 };
@@ -96,7 +99,7 @@ static void peer_release(vio360_ba* ba) {
     for (int r = 0; r < kMaxPeers; ++r) { if (P.ipc_open[r] && P.base[r]) cudaIpcCloseMemHandle(P.base[r]); P.base[r] = nullptr; P.ipc_open[r] = false; }
     P.local.release();
     if (P.h_err) cudaFreeHost(P.h_err);
-    P.h_err = nullptr; P.exported = P.attached = false; P.epoch = 0; P.zero_n = -1;
+    P.h_err = nullptr; P.exported = P.attached = false; P.epoch = 0; P.zero_n = -1; P.stale = false; P.same_device = 1;
 }
 
 // ------------------------------------------------------------------------ kernels
@@ -649,6 +652,7 @@ extern "C" int vio360_ba_set_shard(vio360_ba* ba, int rank, int world) {
     if (!ba) return VIO360_ERR_INVALID;
     if (world < 1 || rank < 0 || rank >= world) return vio360_fail(ba->ctx, VIO360_ERR_INVALID, "ba_set_shard: bad rank/world");
     ba->shard_rank = rank; ba->shard_world = world;
+    if (ba->peer.exported) ba->peer.stale = true;   // the peers hold the old shard's row ranges: detach + export again
     if (ba->has_structure) compute_shard(ba);
     return VIO360_OK;
 }
@@ -696,6 +700,7 @@ extern "C" int vio360_ba_set_structure(vio360_ba* ba, const int32_t* pose_idx, c
     memcpy(ba->Tcb, T_cb, sizeof(ba->Tcb));
     cam_const_init(ba->cam, cols, rows, info, T_cb, huber_delta);
     ba->h_pose = s_pose;
+    if (ba->peer.exported) ba->peer.stale = true;   // the exported row ranges / band width describe the old structure
     compute_shard(ba);
 
     cudaStream_t st = ctx->stream;
@@ -936,11 +941,14 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
     double* dS = ba->d_packed.as<double>(); double* drhs = dS + (size_t)n * n; double* dcost = drhs + n;
     BaDev d = make_dev(ba);
     if (ba->chunk_error) return vio360_fail(ctx, VIO360_ERR_STATE, "internal: inconsistent chunk table");
-    const bool use_tiles = getenv("VIO360_BA_ATOMIC") == nullptr;   // tuning / A-B switch: the general kernel only
+    static const bool force_atomic = getenv("VIO360_BA_ATOMIC") != nullptr;   // tuning / A-B switch, read once per process
+    const bool use_tiles = !force_atomic;
     const int nch = use_tiles ? (int)ba->chunks.size() : 0;
     const int nirr = use_tiles ? (int)ba->irregular.size() : ba->lm_end - ba->lm_begin;
     const int nb_irr = (nirr * 32 + 127) / 128;
     VIO_CUDA(ctx, ba->d_partials.reserve((size_t)(nch + nb_irr + 2) * 8));
+    if (ba->peer.attached && ba->peer.stale)
+        return vio360_fail(ctx, VIO360_ERR_STATE, "ba_build_reduced_system: vio360_ba_set_structure / vio360_ba_set_shard ran after vio360_ba_peer_export; the peers hold the old row ranges: vio360_ba_peer_detach, then export and attach again on every rank");
     if (ba->peer.attached && (nirr > 0 || !use_tiles || ba->shard_world != ba->peer_world()))
         return vio360_fail(ctx, VIO360_ERR_STATE, "ba_build_reduced_system: a peer exchange is attached but this build cannot use the block band (landmarks outside the chunk windows, or the shard changed): vio360_ba_peer_detach first");
     if (use_tiles) {
@@ -1178,7 +1186,9 @@ extern "C" int vio360_ba_peer_attach(vio360_ba* ba, const void* blobs) {
     vio360_ctx* ctx = ba->ctx;
     auto& P = ba->peer;
     if (!P.exported) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_attach before ba_peer_export");
+    if (P.stale) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_attach: the structure or shard changed after vio360_ba_peer_export: export again");
     VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    P.same_device = 0;
     const PeerBlob* B = static_cast<const PeerBlob*>(blobs);
     for (int r = 0; r < P.world; ++r) {
         PeerBlob b;
@@ -1187,6 +1197,7 @@ extern "C" int vio360_ba_peer_attach(vio360_ba* ba, const void* blobs) {
             return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_peer_attach: blob %d does not describe rank %d of this window (rank %d world %d n_free %d band %d)",
                                r, r, b.rank, b.world, b.n_free, b.band_w);
         P.row_lo[r] = b.row_lo; P.row_hi[r] = b.row_hi;
+        if (b.device == ctx->device) P.same_device++;   // (device ordinals; CUDA_VISIBLE_DEVICES-remapped processes count as distinct)
         if (r == ba->shard_rank) { P.base[r] = P.local.p; continue; }
         if (b.pid == (int32_t)getpid()) {
             // same process (one host thread per GPU): plain peer access
@@ -1212,6 +1223,7 @@ extern "C" int vio360_ba_peer_exchange(vio360_ba* ba) {
     vio360_ctx* ctx = ba->ctx;
     auto& P = ba->peer;
     if (!P.attached) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_exchange before ba_peer_attach");
+    if (P.stale) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_exchange: the structure or shard changed after vio360_ba_peer_export (detach, export and attach again)");
     if (!ba->has_reduced || ba->band_w <= 0) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_exchange: no sharded build to exchange");
     if (*P.h_err) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_exchange: an earlier exchange timed out waiting for a peer rank");
     if (P.band_epoch != P.epoch + 1) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_exchange: no vio360_ba_build_reduced_system since the last exchange");
@@ -1239,7 +1251,10 @@ extern "C" int vio360_ba_peer_exchange(vio360_ba* ba) {
     const size_t total = P.nd;
     // one element per thread where possible: a thread's peer loads are one NVLink round trip, so the kernel
     // is a single latency deep when everything is in flight at once
-    const unsigned grid = (unsigned)std::min<size_t>((total + 255) / 256, (size_t)8 * ctx->num_sms);
+    // Every CTA polls the arrival flags, so all CTAs of all ranks that share a device must be resident together
+    // (a rank whose CTA 0 cannot get an SM slot never announces): cap the grid at this rank's share of the
+    // 8 x 256-thread CTAs per SM.
+    const unsigned grid = (unsigned)std::min<size_t>((total + 255) / 256, std::max<size_t>(1, (size_t)8 * ctx->num_sms / std::max(1, P.same_device)));
     { KernelTimer kt_(ctx, "k_band_exchange");
     k_band_exchange<<<grid, 256, 0, st>>>(pv, epoch, ba->n_free, P.band_w, ba->d_free_pose.as<int>(),
                                           ba->use_D ? ba->d_D.as<double>() : nullptr, dS, d_err, d_trace);

@@ -20,6 +20,8 @@ struct FeSlot {
     uint64_t last_use = 0;
     uint64_t batch_tag = 0;      // slot is pinned by the batch with this tag
     bool has_pyramid = false;
+    bool loaded = false;         // level 0 has been aliased / its upload has been enqueued
+    uint64_t pending_tag = 0;    // batch whose upload list holds this slot's frame (not enqueued yet)
     DevBuf mem;                  // levels 0..L-1 (level 0 unused when aliased)
     uint8_t* own[kMaxLevels] = {};
     const uint8_t* p[kMaxLevels] = {};
@@ -168,7 +170,11 @@ static int acquire_slot(vio360_ctx* ctx, uint64_t key, bool* hit, int* out_idx) 
         if (it != s->by_key.end()) {
             FeSlot& sl = s->slots[it->second];
             sl.last_use = ++s->clock; sl.batch_tag = s->batch_tag;
-            *hit = true; *out_idx = it->second;
+            // a slot whose frame never got as far as the copy queue (an earlier call failed between acquiring
+            // the slot and enqueuing the upload) holds stale pixels: treat the hit as a miss
+            *hit = sl.loaded || sl.pending_tag == s->batch_tag;
+            if (!*hit) { sl.has_pyramid = false; sl.p[0] = sl.own[0]; sl.pitch[0] = s->lpitch[0]; }
+            *out_idx = it->second;
             return VIO360_OK;
         }
     }
@@ -182,6 +188,7 @@ static int acquire_slot(vio360_ctx* ctx, uint64_t key, bool* hit, int* out_idx) 
     FeSlot& sl = s->slots[best];
     if (sl.key != 0) s->by_key.erase(sl.key);
     sl.key = key; sl.last_use = ++s->clock; sl.batch_tag = s->batch_tag; sl.has_pyramid = false;
+    sl.loaded = false; sl.pending_tag = 0;
     sl.p[0] = sl.own[0]; sl.pitch[0] = s->lpitch[0];
     if (key != 0) s->by_key[key] = best;
     *out_idx = best;
@@ -191,6 +198,7 @@ static int acquire_slot(vio360_ctx* ctx, uint64_t key, bool* hit, int* out_idx) 
 static int load_frame(vio360_ctx* ctx, int slot, const uint8_t* img, size_t pitch, int mem_space, cudaStream_t h2d_stream = nullptr) {
     vio360_fe_state* s = ctx->fe;
     FeSlot& sl = s->slots[slot];
+    sl.loaded = true;
     if (mem_space == VIO360_MEM_DEVICE) {
         if ((reinterpret_cast<uintptr_t>(img) & 3) == 0 && (pitch & 3) == 0) {
             sl.p[0] = img; sl.pitch[0] = (int)pitch;   // alias: no copy of level 0
@@ -320,12 +328,16 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
     TrackJobDev* dj = s->d_jobs_ring[s->cur_stage_i].as<TrackJobDev>();
     int max_n = 0;
     size_t off = 0;
+    // every job is validated before the first cache slot is taken: a rejected batch leaves the cache untouched
     for (int b = 0; b < n_jobs; ++b) {
         const vio360_track_job& j = jobs[b];
         if (j.n < 0 || j.n > s->max_points) return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_track_batch: job %d has %d points (max %d)", b, j.n, s->max_points);
         if (!j.prev || !j.cur || (j.n > 0 && (!j.prev_xy || !j.cur_xy || !j.status)))
             return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_track_batch: job %d has a null pointer", b);
         if (j.prev_pitch < (size_t)s->W || j.cur_pitch < (size_t)s->W) return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_track_batch: pitch < width");
+    }
+    for (int b = 0; b < n_jobs; ++b) {
+        const vio360_track_job& j = jobs[b];
         int sp, sc; bool hit;
         const uint8_t* imgs[2] = {j.prev, j.cur};
         const size_t pitches[2] = {j.prev_pitch, j.cur_pitch};
@@ -341,7 +353,15 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
                     if (rc) return rc;
                 } else {
                     uploads.push_back({idx[f], g, imgs[f], pitches[f]});   // queued after the descriptor copies
+                    s->slots[idx[f]].pending_tag = s->batch_tag;
                 }
+            } else if (mem_space == VIO360_MEM_DEVICE && s->slots[idx[f]].p[0] != s->slots[idx[f]].own[0]) {
+                // level 0 of a device-space frame is ALIASED, never copied: a keyed hit re-uses the cached levels
+                // 1..L-1 but reads level 0 through the pointer of THIS call (the caller may have moved the frame;
+                // see the lifetime rule in vio360.h)
+                if ((reinterpret_cast<uintptr_t>(imgs[f]) & 3) == 0 && (pitches[f] & 3) == 0) {
+                    s->slots[idx[f]].p[0] = imgs[f]; s->slots[idx[f]].pitch[0] = (int)pitches[f];
+                } else if ((rc = load_frame(ctx, idx[f], imgs[f], pitches[f], mem_space))) return rc;
             }
             if (!s->slots[idx[f]].has_pyramid && std::find(queued.begin(), queued.end(), idx[f]) == queued.end()) {
                 queued.push_back(idx[f]); todo[g].push_back(idx[f]);

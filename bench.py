@@ -69,8 +69,22 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.rows)}
 
 
-# dram bytes per launch of the default 64-frame workload, from the committed ncu capture
-NCU_TRAFFIC = {"k_lk_track": 597.195776e6 + 8.958464e6}
+def ncu_traffic(kernel, batch):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full`
+    capture (profiles/ncu_traffic.json, written by tools/ncu_summary.py --traffic).  Only reported when the
+    capture was taken on this workload AND on this version of the kernel source (sha1 of the .cuh), else None:
+    a profiler figure cannot be measured inside a timed run, so it is tied to what it was measured on."""
+    import hashlib
+    try:
+        rec = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))[kernel]
+        src = os.path.join(ROOT, PKG, "csrc", rec["source"])
+        sha = hashlib.sha1(open(src, "rb").read()).hexdigest()
+        wl = rec["workload"]
+        if sha != rec["source_sha1"] or (wl["W"], wl["H"], wl["batch"], wl["points"]) != (W, H, batch, NFEAT):
+            return None, "stale: capture %s was taken on another kernel version or workload" % rec.get("capture")
+        return float(rec["bytes_per_launch"]), "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full, %s" % rec["capture"]
+    except Exception as e:   # no capture committed
+        return None, "no capture (%s)" % type(e).__name__
 
 
 def measured_peaks():
@@ -152,7 +166,6 @@ def run_ours(args):
     for i in range(args.warmup):
         dev_step(i)
     barrier()
-    ctx.enable_kernel_timing(True); ctx.reset_kernel_times()
     l0 = ctx.launch_count
     sampler = ClockSampler(local_rank); sampler.start()
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
@@ -166,6 +179,16 @@ def run_ours(args):
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_total = float(ms.item())
     launches = ctx.launch_count - l0
+    # second pass over the same K steps with a CUDA event pair around every kernel launch (on the context's
+    # stream): the per-kernel durations of the roofline object.  Kept out of the headline region above.
+    ctx.enable_kernel_timing(True); ctx.reset_kernel_times()
+    k0 = torch.cuda.Event(enable_timing=True); k1 = torch.cuda.Event(enable_timing=True)
+    k0.record(stream)
+    for i in range(args.warmup + args.steps, args.warmup + 2 * args.steps):
+        dev_step(i)
+    k1.record(stream)
+    barrier()
+    ms_events_total = k0.elapsed_time(k1)
     lk_ms, lk_n = ctx.kernel_time("k_lk_track")
     pyr_ms, pyr_n = ctx.kernel_time("k_pyr_down")
     ctx.enable_kernel_timing(False)
@@ -173,7 +196,7 @@ def run_ours(args):
     # the timed region is ~10 ms, shorter than one nvidia-smi query: keep the same steps running for ~1.5 s more so
     # that the sampler sees clocks and throttle reasons UNDER THIS LOAD (reported beside `value`, not part of it)
     s0 = torch.cuda.Event(enable_timing=True); s1 = torch.cuda.Event(enable_timing=True)
-    sus_steps, t_sus, i_sus = 0, time.perf_counter(), args.warmup + args.steps
+    sus_steps, t_sus, i_sus = 0, time.perf_counter(), args.warmup + 2 * args.steps
     s0.record(stream)
     while time.perf_counter() - t_sus < 1.5:
         for _ in range(50):
@@ -188,7 +211,7 @@ def run_ours(args):
     value = frames / (ms_total * 1e-3)
 
     # ---- end to end through the C ABI with pinned HOST buffers
-    e2e_steps = max(2, min(args.steps, 6))
+    e2e_steps = max(20, args.steps)
     hring = [[torch.empty((H, W), dtype=torch.uint8).pin_memory() for _ in range(B)] for _ in range(2)]
     for t in range(2):
         for s in range(B):
@@ -245,11 +268,12 @@ def run_ours(args):
     achieved = per_launch_bytes / (dur_ms * 1e-3) / 1e9
     frame_bytes = (pyr_b + lk_b) * B
     step_ms = ms_total / args.steps
+    traffic, traffic_src = ncu_traffic(dominant, B)
     roofline = {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                "frac": achieved / hbm_peak, "traffic": NCU_TRAFFIC.get(dominant) if B == 64 else None, "peak_source": peak_src,
-                "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full capture of this command (profiles/r01_ncu_final.txt); 32-byte sectors around 32/36-byte tile rows and search-tile refills explain the factor over the algorithmic bytes",
+                "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src, "traffic_source": traffic_src,
                 "algorithmic_bytes_per_launch": per_launch_bytes, "avg_launch_ms": dur_ms,
-                "kernel_share_of_step": {"k_lk_track": lk_ms / ms_total, "k_pyr_down": pyr_ms / ms_total},
+                "kernel_share_of_step": {"k_lk_track": lk_ms / ms_events_total, "k_pyr_down": pyr_ms / ms_events_total},
+                "kernel_timing": "CUDA event pair around every launch on the context's stream, in a second pass over the same %d steps (%.4f ms/step with the event pairs, %.4f without)" % (args.steps, ms_events_total / args.steps, ms_total / args.steps),
                 "tracking_frame": {"algorithmic_bytes_per_step": frame_bytes,
                                    "achieved_gbs": frame_bytes / (step_ms * 1e-3) / 1e9,
                                    "frac": frame_bytes / (step_ms * 1e-3) / 1e9 / hbm_peak},
@@ -281,7 +305,21 @@ def run_ours(args):
     if not args.skip_c4:
         line["tracking_c4"] = bench_c4(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, args)
     if rank == 0 and world == 1 and not args.skip_cpu:
-        line["cpu_baseline"] = cpu_baseline_tracking(ring, pts_h, torch)
+        # parity on the benchmark's own inputs: the frame pairs the CPU leg runs, once more through the CUDA path
+        ctx.fe_configure(W, H, max_points=NFEAT, max_batch=B)
+        jobs = dev_jobs[0]                       # prev = frame t, cur = frame t + 1 of every sequence
+        for s in range(B):
+            jobs[s].prev_key = 0; jobs[s].cur_key = 0
+        ctx.fe_track_batch_raw(jobs, B, b.MEM_DEVICE)
+        ctx.synchronize()
+        gpu_out = (out_xy.cpu().numpy(), out_st.cpu().numpy(), out_err.cpu().numpy())
+        line["cpu_baseline"], line["parity"] = cpu_baseline_tracking(ring, pts_h, torch, gpu_out)
+        if "detect" in line:
+            cb, par = cpu_baseline_detect(ring, line["detect"].pop("_corners"))
+            line["detect"]["cpu_baseline"] = cb
+            line["parity"]["gftt_vs_cv2"] = par
+    if "detect" in line:
+        line["detect"].pop("_corners", None)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -382,7 +420,7 @@ def bench_ransac(ctx, syn):
 
 
 def bench_detect(ctx, b, torch, ring, B, world, device, barrier, stream):
-    nb = min(B, 16)
+    nb = min(B, 64)
     out_xy = torch.zeros((nb, 1000, 2), dtype=torch.float32, device=device)
     out_n = (C.c_int * nb)()
 
@@ -415,7 +453,9 @@ def bench_detect(ctx, b, torch, ring, B, world, device, barrier, stream):
     ctx.enable_kernel_timing(False)
     fps = nb / dt
     alg_bytes = float(W * H + 1000 * 8)   # SURVEY 8-D K4+K5: image in, corners out; the response map is internal
-    return {"metric": "ERP detection frames/s @3840x1920 (goodFeaturesToTrack, 1000 corners)", "value": fps * world,
+    corners = [out_xy[s, :out_n[s]].cpu().numpy() for s in range(min(nb, 2))]
+    return {"_corners": corners,
+            "metric": "ERP detection frames/s @3840x1920 (goodFeaturesToTrack, 1000 corners)", "value": fps * world,
             "unit": "frames/s", "frames_per_step_per_gpu": nb, "corners_first_frame": int(out_n[0]),
             "ms_per_step": dt * 1e3, "kernel_ms_per_launch": kern, "k_min_eig_ms_per_launch": kern["k_min_eig"],
             "timing": "host clock around the C-ABI call (it ends with a stream synchronize); includes one library radix sort and a 4-byte count read-back",
@@ -520,6 +560,23 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
             out["roofline"]["frac"] = out["roofline"]["achieved"] / fp64_peak
         if per_rank is not None:
             out["kernel_ms_per_launch_by_rank"] = per_rank
+        if multi:
+            # cross-device correctness carried by the scaling run itself: EVERY rank fetches the exchanged system
+            # and compares it with its own unsharded build of the same window (max-norm relative error)
+            step(); ctx.synchronize()
+            S_x, rhs_x, cost_x = ba.fetch_reduced_system()
+            full = b.BAWindow(ctx, win)
+            full.set_parameters(win["pose_delta"], win["points"])
+            full.set_lm_diagonal(D)
+            S_f, rhs_f, cost_f = full.build_reduced_system(None, True)
+            full.close()
+            mine = {"rank": rank, "S": float(np.max(np.abs(S_x - S_f)) / np.max(np.abs(S_f))),
+                    "rhs": float(np.max(np.abs(rhs_x - rhs_f)) / np.max(np.abs(rhs_f))),
+                    "cost": float(abs(cost_x - cost_f) / abs(cost_f))}
+            allp = [None] * world
+            dist.all_gather_object(allp, mine)
+            out["exchange_parity"] = {"per_rank": allp, "max": max(max(a["S"], a["rhs"], a["cost"]) for a in allp),
+                                      "tolerance": 1e-9, "what": "max-norm relative error of the exchanged [S | rhs | cost] on each rank against that rank's own unsharded build"}
         if world == 1:
             # reduced-system solve + landmark back substitution on the device
             ba.solve_reduced(True)
@@ -569,23 +626,66 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
 
 
 # ===================================================================== CPU baselines
-def cpu_baseline_tracking(ring, pts_h, torch, max_pairs=24, budget_s=25.0):
+def cpu_baseline_tracking(ring, pts_h, torch, gpu_out=None, max_pairs=24, budget_s=20.0):
     """cv2.calcOpticalFlowPyrLK = the reference's own CPU implementation of the path
-    (FeatureTracker.cpp:238-240), exact arguments, all host threads."""
+    (FeatureTracker.cpp:238-240), exact arguments, all host threads (and once more on one thread).  The outputs
+    of the first calls are kept and compared with the CUDA path's on the same frame pairs -> `parity`."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import cv2
     import fe_oracle
     n = min(len(ring[0]), 4)
     pairs = [(ring[0][s].cpu().numpy(), ring[1][s].cpu().numpy(), pts_h[s]) for s in range(n)]
-    for p in pairs[:2]:
-        fe_oracle.cv2_lk_track(*p)
+    cv_out = [fe_oracle.cv2_lk_track(*p) for p in pairs]
     t0 = time.perf_counter(); done = 0
     while done < max_pairs and time.perf_counter() - t0 < budget_s:
         fe_oracle.cv2_lk_track(*pairs[done % n]); done += 1
     dt = time.perf_counter() - t0
-    return {"value": done / dt, "unit": "frames/s", "cores": int(cv2.getNumThreads()), "kind": "reference",
+    cv2.setNumThreads(1)
+    t1 = time.perf_counter(); done1 = 0
+    while done1 < 8 and time.perf_counter() - t1 < 8.0:
+        fe_oracle.cv2_lk_track(*pairs[done1 % n]); done1 += 1
+    dt1 = time.perf_counter() - t1
+    cv2.setNumThreads(-1)
+    base = {"value": done / dt, "unit": "frames/s", "cores": int(cv2.getNumThreads()), "kind": "reference",
             "sample": "%d calls of cv2.calcOpticalFlowPyrLK %s (both pyramids rebuilt per call, as the reference does) on the same synthetic frames" % (done, cv2.__version__),
-            "host_cpus": os.cpu_count()}
+            "host_cpus": os.cpu_count(), "single_thread_value": done1 / dt1}
+    parity = None
+    if gpu_out is not None:
+        gxy, gst, gerr = gpu_out
+        mism, maxd, maxe, ntr, moved = 0, 0.0, 0.0, 0, []
+        for s, (cxy, cst, cerr) in enumerate(cv_out):
+            mism += int((gst[s] != cst).sum())
+            ok = (cst == 1) & (gst[s] == 1)
+            ntr += int(ok.sum())
+            if ok.any():
+                maxd = max(maxd, float(np.abs(gxy[s] - cxy)[ok].max()))
+                maxe = max(maxe, float(np.abs(gerr[s] - cerr)[ok].max()))
+                moved.append(float(np.median(np.linalg.norm(cxy - pts_h[s], axis=1)[ok])))
+        parity = {"lk_vs_cv2": {"pairs": n, "points": int(n * pts_h.shape[1]), "frames": "consecutive rendered frames t=0,1 at %dx%d (the timed inputs)" % (W, H),
+                                "status_mismatches": mism, "status_equal": mism == 0, "tracked_both": ntr,
+                                "max_abs_dxy_px": maxd, "tolerance_px": 0.05, "within_tolerance": maxd < 0.05,
+                                "max_abs_derr": maxe, "median_motion_px": float(np.median(moved)) if moved else None}}
+    return base, parity
+
+
+def cpu_baseline_detect(ring, gpu_corners):
+    """cv2.goodFeaturesToTrack with the reference's arguments (FeatureTracker.cpp:212-223) on the frames
+    bench_detect ran: timing (all host threads) and corner-by-corner comparison with the CUDA path."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import cv2
+    import fe_oracle
+    frames = [ring[0][s].cpu().numpy() for s in range(len(gpu_corners))]
+    mask = fe_oracle.base_mask(W, H)
+    cv_c = [fe_oracle.cv2_good_features(f, mask, 1000) for f in frames]
+    t0 = time.perf_counter(); done = 0
+    while done < 6 and time.perf_counter() - t0 < 10.0:
+        fe_oracle.cv2_good_features(frames[done % len(frames)], mask, 1000); done += 1
+    dt = time.perf_counter() - t0
+    eq = [bool(np.array_equal(a, c)) for a, c in zip(gpu_corners, cv_c)]
+    base = {"value": done / dt, "unit": "frames/s", "cores": int(cv2.getNumThreads()), "kind": "reference",
+            "sample": "%d calls of cv2.goodFeaturesToTrack %s (1000, 0.01, 30, polar & boundary mask, block 3) on the benchmark frames" % (done, cv2.__version__)}
+    par = {"frames": len(frames), "corners": [int(len(c)) for c in cv_c], "corners_identical": all(eq)}
+    return base, par
 
 
 def cpu_baseline_ba(syn, win5):

@@ -94,7 +94,12 @@ int vio360_fe_track(vio360_ctx* ctx, const uint8_t* prev, size_t prev_pitch,
                     uint8_t* status, float* err, int* n_tracked);
 /* Batched form for independent frame pairs (BASELINE config 4: one job per sequence).
  * mem_space says where ALL pointers inside the jobs live (the job array itself is
- * host memory).  Device-space images need 4-byte aligned base and pitch.             */
+ * host memory).  Lifetime of device-space frames: a frame whose base and pitch are
+ * 4-byte aligned is NOT copied -- level 0 is read through the pointer passed to THIS
+ * call (also on a keyed cache hit, which only re-uses levels 1..L-1), so the buffer must
+ * stay valid and unchanged until the call's kernels have run (vio360_synchronize), and a
+ * key must always name the same pixels.  Unaligned device frames and host frames are
+ * copied.  All jobs are validated before the cache is touched.                        */
 int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jobs, int n_jobs,
                           int mem_space);
 

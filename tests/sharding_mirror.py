@@ -1,7 +1,7 @@
 """Host-side mirror of the landmark sharding rule of libvio360_cuda.so (csrc/ba.cu:
 compute_shard): each rank owns a contiguous landmark range, ranges balanced by
 sum(d^2 + 4 d) over the landmarks' degrees d.  Used by the CPU-only
-multi-process tests and by bench.py to report the shard sizes; the product path computes the
+multi-process tests (it lives under tests/, not in the product package); the product path computes the
 same cuts in C++."""
 import numpy as np
 

@@ -23,10 +23,10 @@ def _worker(rank, world, port, out):
     import importlib
     import torch
     import torch.distributed as dist
-    sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "oracle")); sys.path.insert(0, os.path.join(ROOT, "tests"))
     import ba_oracle
     syn = importlib.import_module(PKG + ".synthetic")
-    sharding = importlib.import_module(PKG + ".sharding")
+    import sharding_mirror as sharding
     os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     win = syn.make_ba_window(K=14, M=240, degree=6, seed=123, mid_iteration=True)
@@ -85,7 +85,7 @@ def _worker(rank, world, port, out):
 def test_landmark_shards_cover_and_balance():
     sys.path.insert(0, ROOT)
     import importlib
-    sharding = importlib.import_module(PKG + ".sharding")
+    import sharding_mirror as sharding
     rng = np.random.default_rng(0)
     point_idx = np.repeat(np.arange(1000), rng.integers(0, 25, 1000))
     for world in (1, 2, 4, 8):
@@ -111,7 +111,7 @@ def test_two_rank_schur_allreduce(tmp_path):
 def test_band_pack_expand_round_trip():
     sys.path.insert(0, ROOT)
     import importlib
-    sharding = importlib.import_module(PKG + ".sharding")
+    import sharding_mirror as sharding
     rng = np.random.default_rng(3)
     for n_free in (1, 5, 24, 40):
         w = min(n_free, sharding.BAND_BLOCKS)

@@ -281,3 +281,84 @@ def test_full_size_properties_c4(ctx, synthetic):
     assert np.abs(xy0 - pts[:2500])[st0 == 1].max() < 1e-3 and err0[st0 == 1].max() == 0.0
     ocorners = fo.good_features(f0, fo.base_mask(W, H), 3000)
     assert np.array_equal(ctx.fe_detect(f0, None, 3000), ocorners) and len(ocorners) > 1000
+
+
+def _render_pair(synthetic, W, H, seed, sigma, n_waves=24, dt=1):
+    """consecutive rendered frames of the moving camera (camera_pose: translation + yaw + pitch), on the GPU"""
+    import torch
+    f0 = synthetic.render_erp_frame(W, H, 0, seed=seed, n_waves=n_waves, sigma_omega=sigma, xp=torch, device="cuda").cpu().numpy()
+    f1 = synthetic.render_erp_frame(W, H, dt, seed=seed, n_waves=n_waves, sigma_omega=sigma, xp=torch, device="cuda").cpu().numpy()
+    return f0, f1
+
+
+@pytest.mark.parametrize("size,n,seed,sigma", [((3840, 1920), 1000, 360, 120.0), ((7680, 3840), 3000, 361, 240.0)])
+def test_track_and_detect_vs_cv2_live_full_size(ctx, synthetic, size, n, seed, sigma):
+    """the CUDA path against cv2 ITSELF (the dependency the reference calls,
+    FeatureTracker.cpp:222-223, 238-240) at BASELINE configs 2 and 4, on CONSECUTIVE RENDERED frames of the
+    moving camera (not np.roll shifts): status bytes equal, positions within 0.05 px, corners identical."""
+    cv2 = pytest.importorskip("cv2")
+    W, H = size
+    f0, f1 = _render_pair(synthetic, W, H, seed, sigma)
+    pts = synthetic.make_track_points(W, H, n, seed=1000 + seed)
+    ctx.fe_configure(W, H, max_points=n, max_batch=1)
+    xy, st, err, nt = ctx.fe_track(f0, f1, pts)
+    cxy, cst, cerr = fo.cv2_lk_track(f0, f1, pts)
+    assert np.array_equal(st, cst), "status differs on %d of %d points" % (int((st != cst).sum()), n)
+    ok = cst == 1
+    assert ok.sum() > 0.8 * n
+    assert np.abs(xy - cxy)[ok].max() < POS_TOL
+    assert np.abs(err - cerr)[ok].max() < 0.05
+    moved = np.linalg.norm(cxy - pts, axis=1)[ok]
+    assert np.median(moved) > 0.5           # real sub-pixel motion, not a frame tracked onto itself
+    # detection: cv2.goodFeaturesToTrack with the reference's arguments and its polar & boundary mask
+    mask = fo.base_mask(W, H)
+    cc = fo.cv2_good_features(f0, mask, n)
+    got = ctx.fe_detect(f0, None, n)
+    assert np.array_equal(got, cc) and len(cc) > 0.5 * n
+    # re-detection as TrackFeatures does it: discs of radius min_distance at the tracked features
+    occ = xy[ok][: n // 2]
+    m2 = fo.feature_mask(mask, occ, 30)
+    cc2 = fo.cv2_good_features(f0, m2, n)
+    got2 = ctx.fe_detect_batch([f0], None, n, occupied=[occ], occupied_radius=30)[0]
+    assert np.array_equal(got2, cc2)
+
+
+def test_device_frames_alias_lifetime_and_failed_batch(ctx, synthetic, bindings):
+    """(1) level 0 of a keyed device-space frame is aliased -- a cache hit must read it through the
+    pointer of the CURRENT call, not the one remembered from the call that built the pyramid; (2) a batch
+    rejected at validation (or failing before its uploads are enqueued) must not leave cache slots that a
+    retry with the same keys takes for loaded frames."""
+    import torch
+    W, H, n = 640, 320, 200
+    frames = [synthetic.render_erp_frame(W, H, t, seed=44, n_waves=32, sigma_omega=40.0) for t in range(3)]
+    pts = synthetic.make_track_points(W, H, n, seed=5)
+    ctx.fe_configure(W, H, max_points=n, max_batch=2)
+    dev = [torch.from_numpy(f).cuda() for f in frames]
+    dpts = torch.from_numpy(pts).cuda()
+    oxy = torch.zeros((n, 2), dtype=torch.float32, device="cuda"); ost = torch.zeros(n, dtype=torch.uint8, device="cuda")
+
+    def run(prev, cur, kp, kc):
+        jobs = (bindings.TrackJob * 1)()
+        j = jobs[0]
+        j.prev, j.prev_pitch, j.prev_key, j.cur, j.cur_pitch, j.cur_key = prev.data_ptr(), W, kp, cur.data_ptr(), W, kc
+        j.prev_xy, j.n, j.cur_xy, j.status, j.err, j.keep = dpts.data_ptr(), n, oxy.data_ptr(), ost.data_ptr(), None, None
+        ctx.fe_track_batch_raw(jobs, 1, bindings.MEM_DEVICE)
+        ctx.synchronize()
+        return oxy.cpu().numpy().copy(), ost.cpu().numpy().copy()
+
+    run(dev[0], dev[1], 9001, 9002)                      # builds and caches the pyramid of frame 1 under key 9002
+    moved = dev[1].clone()                               # the caller moves frame 1 and recycles the old buffer
+    dev[1].fill_(0)
+    xy, st = run(moved, dev[2], 9002, 9003)              # cache hit on 9002: level 0 must come from `moved`
+    rxy, rst, _, _ = fo.lk_track(frames[1], frames[2], pts)
+    assert np.array_equal(st, rst) and np.abs(xy - rxy)[rst == 1].max() < POS_TOL
+
+    # (2) host-space batch whose second job is invalid: nothing may be cached under keys 7001 / 7002
+    ctx.fe_configure(W, H, max_points=n, max_batch=2)
+    ctx.fe_track(frames[2], frames[0], pts, 0, 0)        # fill the slot pool with other pixels
+    bad = np.zeros((n + 1, 2), np.float32)
+    with pytest.raises(bindings.Vio360Error):
+        ctx.fe_track_batch_host([(frames[0], frames[1], pts, 7001, 7002), (frames[1], frames[2], bad, 7002, 7003)])
+    (xy, st, err, keep), = ctx.fe_track_batch_host([(frames[0], frames[1], pts, 7001, 7002)])
+    rxy, rst, _, _ = fo.lk_track(frames[0], frames[1], pts)
+    assert np.array_equal(st, rst) and np.abs(xy - rxy)[rst == 1].max() < POS_TOL

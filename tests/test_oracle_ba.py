@@ -233,3 +233,116 @@ def test_device_arithmetic_on_host(win, emu_lib):
     assert rel_err(r32[same], r0[same]) < 1e-4 and rel_err(Jp32[same], Jp0[same]) < 1e-4 and rel_err(Jl32[same], Jl0[same]) < 1e-4
     assert abs(cost32 - cost0) < 1e-4 * cost0
     assert not np.array_equal(r32[~special], r0[~special])          # it really ran in float
+
+
+def _mp_polar(mp, M):
+    """SO3d(R) (LieUtils.cpp:275-288) at 50 digits: U V^T of the SVD, third column of U negated when det < 0."""
+    U, S, Vt = mp.svd_r(M)
+    R = U * Vt
+    if mp.det(R) < 0:
+        for i in range(3):
+            U[i, 2] = -U[i, 2]
+        R = U * Vt
+    return R
+
+
+def _mp_hat(mp, w):
+    return mp.matrix([[0, -w[2], w[1]], [w[2], 0, -w[0]], [-w[1], w[0], 0]])
+
+
+def _mp_ba_factor(mp, win, i, xi, pt):
+    """Independent 50-digit transcription of BAFactor::Evaluate (Factors.cpp:349-534) with the pose chain of
+    LieUtils.cpp:203-219, 275-333 / LieUtils.h:207-283 -- written from the reference source, not from
+    oracle/ba_ref.c or its numpy mirror.  Returns (r, J_pose 2x6, J_point 2x3) or None on a special branch."""
+    f = lambda a: mp.mpf(float(a))
+    k = win["pose_idx"][i]
+    T0 = win["Twb_init"][k]
+    R0 = _mp_polar(mp, mp.matrix([[f(T0[a, b]) for b in range(3)] for a in range(3)]))      # SE3d(m_T_wb_init)
+    t0 = mp.matrix([f(T0[a, 3]) for a in range(3)])
+    rho = mp.matrix([f(x) for x in xi[:3]]); phi = mp.matrix([f(x) for x in xi[3:]])
+    th = mp.sqrt(sum(p * p for p in phi))
+    I3 = mp.eye(3)
+    if th < mp.mpf("1e-10"):                                                               # LieUtils.cpp:206-209, 316-318
+        Rd = _mp_polar(mp, I3 + _mp_hat(mp, phi)); td = rho
+    else:
+        Kh = _mp_hat(mp, phi / th)
+        Rd = _mp_polar(mp, I3 + mp.sin(th) * Kh + (1 - mp.cos(th)) * Kh * Kh)              # :211-218
+        P = _mp_hat(mp, phi)
+        V = I3 + (1 - mp.cos(th)) / th ** 2 * P + (th - mp.sin(th)) / th ** 3 * P * P       # :320-329
+        td = V * rho
+    Rwb = _mp_polar(mp, R0 * Rd); twb = t0 + R0 * td                                         # LieUtils.h:268-271
+    Rbw = _mp_polar(mp, Rwb.T); tbw = Rbw * (-twb)                                           # :279-283
+    Tcb = win["Tcb"]
+    Rcb_raw = mp.matrix([[f(Tcb[a, b]) for b in range(3)] for a in range(3)])
+    Rcb = _mp_polar(mp, Rcb_raw); tcb = mp.matrix([f(Tcb[a, 3]) for a in range(3)])         # SE3d Tcb(m_Tcb)
+    Rcw = _mp_polar(mp, Rcb * Rbw); tcw = tcb + Rcb * tbw                                    # Tcb * Tbw
+    Pw = mp.matrix([f(x) for x in pt])
+    Pc = Rcw * Pw + tcw
+    x, y, z = Pc[0], Pc[1], Pc[2]
+    L = mp.sqrt(x * x + y * y + z * z)
+    if L < mp.mpf("1e-10"):
+        return None
+    cols, rows = f(win["cols"]), f(win["rows"])
+    u = cols * (mp.mpf(0.5) + mp.atan2(x, z) / (2 * mp.pi))
+    v = rows * (mp.mpf(0.5) + mp.asin(y / L) / mp.pi)                                      # phi = -asin(y/L); v = rows(0.5 - phi/pi)
+    du = f(win["obs_u"][i]) - u; dv = f(win["obs_v"][i]) - v
+    if du > cols / 2: du -= cols
+    elif du < -cols / 2: du += cols
+    if abs(du) > 100 or abs(dv) > 100:
+        return None
+    info = np.asarray(win["info"], np.float64).reshape(2, 2)
+    Lc = mp.cholesky(mp.matrix([[f(info[a, b]) for b in range(2)] for a in range(2)]))      # Eigen::LLT matrixL()
+    r = Lc * mp.matrix([du, dv])
+    xz2 = x * x + z * z; L2 = L * L; xz = mp.sqrt(xz2)
+    if xz2 < mp.mpf("1e-10") or L2 < mp.mpf("1e-10"):
+        return None
+    Jc = mp.matrix([[-cols / (2 * mp.pi) * z / xz2, 0, cols / (2 * mp.pi) * x / xz2],       # Factors.cpp:486-492
+                    [rows / mp.pi * (x * y) / (L2 * xz), -rows / mp.pi * xz / L2, rows / mp.pi * (y * z) / (L2 * xz)]])
+    Jw = Lc * Jc
+    Pb = Rbw * Pw + tbw                                                                     # :503
+    Jcp = mp.zeros(3, 6)
+    Jrot = Rcb_raw * _mp_hat(mp, Pb)                                                        # :509 (raw m_Tcb block)
+    for a in range(3):
+        for b in range(3):
+            Jcp[a, b] = -Rcb_raw[a, b]                                                      # :506
+            Jcp[a, 3 + b] = Jrot[a, b]
+    return r, Jw * Jcp, Jw * (Rcb_raw * Rbw)                                               # :517, :527-530
+
+
+def test_jacobians_closed_form_mpmath(win, synthetic):
+    """the 1e-9 bar on J_pose / J_point anchored independently of the numpy mirror --
+    oracle Jacobians against a 50-digit mpmath transcription of Factors.cpp:349-534 + the LieUtils pose chain
+    (polar factor from mp.svd_r), on >= 100 factors whose T_wb_init went through fp32 (Optimizer.cpp:777) at
+    a mid-iteration delta, plus factors at delta = 0 and a small-angle delta."""
+    mp = pytest.importorskip("mpmath")
+    mp.mp.dps = 50
+    rng = np.random.default_rng(11)
+    wins = [(win, win["pose_delta"]), (win, np.zeros_like(win["pose_delta"])),
+            (win, np.tile(np.array([1e-3, -2e-3, 5e-4, 3e-12, -2e-12, 1e-12]), (win["K"], 1)))]
+    big = synthetic.make_ba_window(K=12, M=60, degree=6, seed=77, mid_iteration=True, loop_radius=3.0)
+    wins.append((big, big["pose_delta"]))
+    checked = 0
+    worst = 0.0
+    for w, deltas in wins:
+        n = 60 if w is win and deltas is win["pose_delta"] else 25
+        for i in rng.choice(w["O"], n, replace=False):
+            k = w["pose_idx"][i]
+            pt = w["points"][w["point_idx"][i]]
+            ref = _mp_ba_factor(mp, w, i, deltas[k], pt)
+            fct = ba_oracle.make_factor((w["obs_u"][i], w["obs_v"][i]), w["cols"], w["rows"], w["Tcb"],
+                                        w["Twb_init"][k], w["info"])
+            ok, r, Jp, Jl = ba_oracle.ba_evaluate(fct, deltas[k], pt)
+            if ref is None:
+                assert not Jp.any() and not Jl.any()
+                continue
+            rm, Jpm, Jlm = ref
+            Jp_ref = np.array([[float(Jpm[a, b]) for b in range(6)] for a in range(2)])
+            Jl_ref = np.array([[float(Jlm[a, b]) for b in range(3)] for a in range(2)])
+            r_ref = np.array([float(rm[0]), float(rm[1])])
+            assert np.abs(r - r_ref).max() < 1e-9                      # pixels of magnitude ~1e3: absolute bar
+            ep = rel_err(Jp, Jp_ref); el = rel_err(Jl, Jl_ref)
+            worst = max(worst, ep, el)
+            assert ep < 1e-9 and el < 1e-9, (i, ep, el)
+            checked += 1
+    assert checked >= 100, checked
+    assert worst < 1e-10        # observed ~1e-13; the bar itself is 1e-9
