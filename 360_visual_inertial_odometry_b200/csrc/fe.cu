@@ -2,7 +2,6 @@
 // Compiled with --fmad=false (see fe_lk.cuh / fe_detect.cuh); explicit fmaf() calls mark
 // the places where OpenCV's dispatched code fuses.
 #include <algorithm>
-#include <cub/cub.cuh>
 
 #include <time.h>
 
@@ -20,6 +19,7 @@ struct FeSlot {
     uint64_t last_use = 0;
     uint64_t batch_tag = 0;      // slot is pinned by the batch with this tag
     bool has_pyramid = false;
+    bool reserved = false;       // owned by a vio360_seq: never evicted by the keyed cache
     bool loaded = false;         // level 0 has been aliased / its upload has been enqueued
     uint64_t pending_tag = 0;    // batch whose upload list holds this slot's frame (not enqueued yet)
     DevBuf mem;                  // levels 0..L-1 (level 0 unused when aliased)
@@ -50,7 +50,7 @@ struct vio360_fe_state {
     Stage* cur_stage = nullptr;
     int cur_stage_i = 0;
     // detection pools
-    DevBuf d_djobs, d_eig, d_mask, d_small, d_cand, d_cand_sorted, d_grid, d_cub, d_corners;
+    DevBuf d_djobs, d_eig, d_mask, d_small, d_cand, d_grid, d_corners;
     PinBuf h_djobs, h_dout;
     DevBuf d_occ;
     PinBuf h_occ;
@@ -59,14 +59,12 @@ struct vio360_fe_state {
     PinBuf h_ransac;
     int det_batch_cap = 0, max_cand = 1 << 17;   // initial candidate capacity per image (grown on demand)
     size_t cand_cap = 0;
-    bool select_attr_set = false;
     int lk_mb = 2;               // occupancy variant of k_lk_track (tuning knob: VIO360_LK_MB)
     // host-space batches: frames are uploaded on a second stream in groups of h2d_group jobs, and a group's
     // pyramid + LK launches wait only for its own frames, so the kernels run behind the PCIe copies
     cudaStream_t copy_stream = nullptr;
     std::vector<cudaEvent_t> grp_ev;
     int h2d_group = 4;           // VIO360_FE_H2D_GROUP (3840x1920 x 64 pairs: 4 -> 6959, 8 -> 6801, 16 -> 6823, off -> 6348 frames/s)
-    size_t cub_bytes = 0;
 };
 
 void vio360_fe_release(vio360_ctx* ctx) {
@@ -74,8 +72,8 @@ void vio360_fe_release(vio360_ctx* ctx) {
     if (!s) return;
     for (auto& sl : s->slots) sl.mem.release();
     DevBuf* db[] = {&s->d_jobs, &s->d_pyrjobs, &s->d_pts_in, &s->d_pts_out, &s->d_status, &s->d_err, &s->d_keep,
-                    &s->d_djobs, &s->d_eig, &s->d_mask, &s->d_small, &s->d_cand, &s->d_cand_sorted, &s->d_grid,
-                    &s->d_cub, &s->d_corners, &s->d_ransac, &s->d_occ};
+                    &s->d_djobs, &s->d_eig, &s->d_mask, &s->d_small, &s->d_cand, &s->d_grid,
+                    &s->d_corners, &s->d_ransac, &s->d_occ};
     for (DevBuf* b : db) b->release();
     PinBuf* pb[] = {&s->h_pts_in, &s->h_out, &s->h_djobs, &s->h_dout, &s->h_ransac, &s->h_occ};
     for (PinBuf* b : pb) b->release();
@@ -181,7 +179,7 @@ static int acquire_slot(vio360_ctx* ctx, uint64_t key, bool* hit, int* out_idx) 
     int best = -1;
     for (int i = 0; i < (int)s->slots.size(); ++i) {
         const FeSlot& sl = s->slots[i];
-        if (sl.batch_tag == s->batch_tag) continue;   // in use by this batch
+        if (sl.batch_tag == s->batch_tag || sl.reserved) continue;   // in use by this batch / owned by a sequence
         if (best < 0 || sl.last_use < s->slots[best].last_use) best = i;
     }
     if (best < 0) return vio360_fail(ctx, VIO360_ERR_STATE, "pyramid cache exhausted (batch larger than max_batch?)");
@@ -370,7 +368,7 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
         sp = idx[0]; sc = idx[1];
         TrackJobDev& d = hj[b];
         fill_levels(s, s->slots[sp], d.prev); fill_levels(s, s->slots[sc], d.cur);
-        d.n = j.n;
+        d.n = j.n; d.n_ptr = nullptr;
         if (mem_space == VIO360_MEM_DEVICE) {
             d.prev_xy = j.prev_xy; d.cur_xy = j.cur_xy; d.status = j.status; d.err = j.err; d.keep = j.keep;
         } else {
@@ -506,16 +504,12 @@ extern "C" int vio360_fe_pyramid(vio360_ctx* ctx, const uint8_t* img, size_t pit
 }
 
 // ---- detection -----------------------------------------------------------------------
-static int reserve_candidates(vio360_ctx* ctx, size_t cap) {
+// candidate segments: max_cand keys per image, det_cand_jobs images
+static int reserve_candidates(vio360_ctx* ctx, size_t per_image, int n_jobs) {
     vio360_fe_state* s = ctx->fe;
-    if (cap <= s->cand_cap) return VIO360_OK;
-    VIO_CUDA(ctx, s->d_cand.reserve(cap * 8));
-    VIO_CUDA(ctx, s->d_cand_sorted.reserve(cap * 8));
-    size_t tb = 0;
-    cub::DeviceRadixSort::SortKeysDescending(nullptr, tb, (const unsigned long long*)nullptr, (unsigned long long*)nullptr, (int)cap);
-    s->cub_bytes = tb;
-    VIO_CUDA(ctx, s->d_cub.reserve(tb));
-    s->cand_cap = cap;
+    s->max_cand = (int)std::max<size_t>(per_image, (size_t)s->max_cand);
+    const size_t cap = (size_t)s->max_cand * n_jobs;
+    if (cap > s->cand_cap) { VIO_CUDA(ctx, s->d_cand.reserve(cap * 8)); s->cand_cap = cap; }
     return VIO360_OK;
 }
 
@@ -529,7 +523,7 @@ static int ensure_detect_pools(vio360_ctx* ctx, int n_jobs, int max_corners) {
         VIO_CUDA(ctx, s->h_djobs.reserve(sizeof(DetectJobDev) * (size_t)n_jobs));
         s->det_batch_cap = n_jobs;
     }
-    int rc = reserve_candidates(ctx, (size_t)s->max_cand * n_jobs);
+    int rc = reserve_candidates(ctx, (size_t)s->max_cand, n_jobs);
     if (rc) return rc;
     const size_t cap = (size_t)(max_corners > 0 ? max_corners : 0);
     VIO_CUDA(ctx, s->d_corners.reserve(cap * 8 * n_jobs));
@@ -545,7 +539,7 @@ static DetectParams detect_params(const vio360_fe_state* s) {
     P.margin = s->margin;
     P.idx_bits = 1;
     while (((size_t)1 << P.idx_bits) < (size_t)s->W * s->H) ++P.idx_bits;
-    P.max_cand = (unsigned int)s->cand_cap;
+    P.max_cand = (unsigned int)s->max_cand;
     return P;
 }
 
@@ -579,6 +573,39 @@ static void launch_min_eig(vio360_ctx* ctx, const DetectJobDev* dj, const Detect
     else k_min_eig<false><<<grid, kEigWarps * 32, 0, ctx->stream>>>(dj, P, nwx);
 }
 
+// K4 + K5 for a batch whose job table is already on the device: response map, candidates, lazy sort + greedy filter.
+static int launch_detect_pipeline(vio360_ctx* ctx, const DetectJobDev* dj, const DetectParams& P, int n_jobs, bool any_mask, int max_corners,
+                                  double quality, double min_dist, bool smem_grid, size_t grid_bytes) {
+    vio360_fe_state* s = ctx->fe;
+    cudaStream_t st = ctx->stream;
+    launch_min_eig(ctx, dj, P, n_jobs, any_mask);
+    VIO_LAUNCH_CHECK(ctx);
+    { KernelTimer kt_(ctx, "k_candidates");
+    if ((s->W & 3) == 0)
+        k_candidates4<<<dim3((s->W / 4 + kCand4Threads - 1) / kCand4Threads, (s->H - 2 + kCandTY - 1) / kCandTY, n_jobs), kCand4Threads, 0, st>>>(dj, P, quality);
+    else
+        k_candidates<<<dim3((s->W - 2 + kCandTX - 1) / kCandTX, (s->H - 2 + kCandTY - 1) / kCandTY, n_jobs), kCandTX, 0, st>>>(dj, P, quality);
+    }
+    VIO_LAUNCH_CHECK(ctx);
+    // shared memory: the cell grid (when it fits) + one tranche of keys, a power of two
+    const size_t budget = (size_t)200 * 1024 - (smem_grid ? grid_bytes : 0);
+    int tranche = kSelMaxTranche;
+    while (tranche > 1024 && (size_t)tranche * 8 > budget) tranche >>= 1;
+    const size_t smem = (smem_grid ? grid_bytes : 0) + (size_t)tranche * 8;
+    float* pool_xy = s->d_corners.as<float>();
+    { KernelTimer kt_(ctx, "k_sort_select");
+    if (smem_grid) {
+        VIO_CUDA(ctx, cudaFuncSetAttribute(k_sort_select<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        k_sort_select<true><<<n_jobs, kSelThreads, smem, st>>>(dj, P, max_corners, min_dist, tranche, pool_xy);
+    } else {
+        VIO_CUDA(ctx, cudaFuncSetAttribute(k_sort_select<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+        k_sort_select<false><<<n_jobs, kSelThreads, smem, st>>>(dj, P, max_corners, min_dist, tranche, pool_xy);
+    }
+    }
+    VIO_LAUNCH_CHECK(ctx);
+    return VIO360_OK;
+}
+
 extern "C" int vio360_fe_detect_batch(vio360_ctx* ctx, const vio360_detect_job* jobs, int n_jobs, int max_corners,
                                       double quality, double min_dist, int mem_space) {
     if (!ctx) return VIO360_ERR_INVALID;
@@ -594,19 +621,16 @@ extern "C" int vio360_fe_detect_batch(vio360_ctx* ctx, const vio360_detect_job* 
     int rc = ensure_detect_pools(ctx, n_jobs, max_corners);
     if (rc) return rc;
     DetectParams P = detect_params(s);
-    if (32 + P.idx_bits > 63 || ((unsigned long long)(n_jobs - 1) >> (64 - 32 - P.idx_bits)) != 0)
-        return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_detect_batch: batch of %d images of %zu pixels does not fit the 64-bit sort key", n_jobs, WH);
     cudaStream_t st = ctx->stream;
     const size_t cap = (size_t)(max_corners > 0 ? max_corners : 0);
     const int cell = min_dist >= 1.0 ? (int)lrint(min_dist) : 1;
     const int gw = (s->W + cell - 1) / cell, gh = (s->H + cell - 1) / cell;
     const size_t grid_bytes = min_dist >= 1.0 ? (size_t)gw * gh * sizeof(uint4) : 0;
-    const bool smem_grid = grid_bytes <= (size_t)200 * 1024;
+    const bool smem_grid = grid_bytes + 8 * 1024 <= (size_t)200 * 1024;   // the cell grid and at least a 1024-key tranche
     if (!smem_grid) {
         VIO_CUDA(ctx, s->d_grid.reserve(grid_bytes * n_jobs));
         VIO_CUDA(ctx, cudaMemsetAsync(s->d_grid.p, 0, grid_bytes * n_jobs, st));
     }
-    VIO_CUDA(ctx, cudaMemsetAsync(s->d_small.p, 0, 16 * (size_t)(n_jobs + 1), st));
     s->batch_tag++;
     bool any_mask = false, any_occ = false;
     int occ_radius = -1, max_occ = 0;
@@ -667,96 +691,57 @@ extern "C" int vio360_fe_detect_batch(vio360_ctx* ctx, const vio360_detect_job* 
         d.eig = s->d_eig.as<float>() + WH * b;
         unsigned int* small = s->d_small.as<unsigned int>() + 4 * b;
         d.max_bits = small; d.n_cand = small + 1; d.out_n = (int*)(small + 2);
+        d.max_corners_dev = nullptr;
         d.grid = smem_grid ? nullptr : (uint4*)(s->d_grid.as<uint8_t>() + grid_bytes * b);
         d.out_xy = mem_space == VIO360_MEM_DEVICE ? j.out_xy : (max_corners > 0 ? s->d_corners.as<float>() + cap * 2 * b : nullptr);
     }
-    VIO_CUDA(ctx, cudaMemcpyAsync(s->d_djobs.p, hj, sizeof(DetectJobDev) * (size_t)n_jobs, cudaMemcpyHostToDevice, st));
     const DetectJobDev* dj = s->d_djobs.as<DetectJobDev>();
-    unsigned int* d_total = s->d_small.as<unsigned int>() + 4 * n_jobs;
+    if (max_corners <= 0 && mem_space == VIO360_MEM_HOST) VIO_CUDA(ctx, s->d_corners.reserve((size_t)s->max_cand * 8 * n_jobs));
     if (any_occ) {
         VIO_CUDA(ctx, cudaMemcpyAsync(s->d_occ.p, s->h_occ.p, (size_t)n_jobs * 16 + (mem_space == VIO360_MEM_DEVICE ? 0 : occ_floats * 4), cudaMemcpyHostToDevice, st));
-        const DiscTable T = disc_table(occ_radius);
-        { KernelTimer kt_(ctx, "k_occupancy_discs");
-        k_occupancy_discs<<<dim3(max_occ, n_jobs), 2 * kMaxDiscRadius + 1, 0, st>>>(dj, s->d_occ.as<const float*>(), reinterpret_cast<const int*>(s->d_occ.as<const float*>() + n_jobs), s->W, s->H, T);
-        }
-        VIO_LAUNCH_CHECK(ctx);
     }
-    launch_min_eig(ctx, dj, P, n_jobs, any_mask);
-    VIO_LAUNCH_CHECK(ctx);
-    // candidates of all images go to one buffer; the count comes back to size the sort.  A batch
-    // that overflows the buffer is redone with a larger one (nothing is ever dropped).
-    unsigned int total = 0;
+    bool discs_drawn = false;
+    // One pass = response map, candidates into per-image segments, per-image lazy sort + greedy filter: no
+    // library kernel and no read-back in between.  The pass is repeated only when an image had more candidates
+    // than its segment holds (seen in the counts that come back with the results; nothing is ever dropped).
     for (;;) {
-        { KernelTimer kt_(ctx, "k_candidates");
-        if ((s->W & 3) == 0)
-            k_candidates4<<<dim3((s->W / 4 + kCand4Threads - 1) / kCand4Threads, (s->H - 2 + kCandTY - 1) / kCandTY, n_jobs), kCand4Threads, 0, st>>>(
-                dj, P, quality, s->d_cand.as<unsigned long long>(), d_total);
-        else
-            k_candidates<<<dim3((s->W - 2 + kCandTX - 1) / kCandTX, (s->H - 2 + kCandTY - 1) / kCandTY, n_jobs), kCandTX, 0, st>>>(
-                dj, P, quality, s->d_cand.as<unsigned long long>(), d_total);
+        for (int b = 0; b < n_jobs; ++b) hj[b].cand = s->d_cand.as<unsigned long long>() + (size_t)s->max_cand * b;
+        VIO_CUDA(ctx, cudaMemcpyAsync(s->d_djobs.p, hj, sizeof(DetectJobDev) * (size_t)n_jobs, cudaMemcpyHostToDevice, st));
+        VIO_CUDA(ctx, cudaMemsetAsync(s->d_small.p, 0, 16 * (size_t)(n_jobs + 1), st));
+        if (!smem_grid) VIO_CUDA(ctx, cudaMemsetAsync(s->d_grid.p, 0, grid_bytes * n_jobs, st));
+        if (any_occ && !discs_drawn) {
+            const DiscTable T = disc_table(occ_radius);
+            { KernelTimer kt_(ctx, "k_occupancy_discs");
+            k_occupancy_discs<<<dim3(max_occ, n_jobs), 2 * kMaxDiscRadius + 1, 0, st>>>(dj, s->d_occ.as<const float*>(), reinterpret_cast<const int*>(s->d_occ.as<const float*>() + n_jobs), s->W, s->H, T);
+            }
+            VIO_LAUNCH_CHECK(ctx);
+            discs_drawn = true;
         }
-        VIO_LAUNCH_CHECK(ctx);
-        VIO_CUDA(ctx, cudaMemcpyAsync(s->h_dout.p, d_total, 4, cudaMemcpyDeviceToHost, st));
-        VIO_CUDA(ctx, cudaStreamSynchronize(st));
-        total = *s->h_dout.as<unsigned int>();
-        if (total <= P.max_cand) break;
-        if ((rc = reserve_candidates(ctx, (size_t)total + total / 4))) return rc;
-        P.max_cand = (unsigned int)s->cand_cap;
-        VIO_CUDA(ctx, cudaMemset2DAsync(s->d_small.as<unsigned int>() + 1, 16, 0, 4, (size_t)n_jobs, st));   // n_cand of every image
-        VIO_CUDA(ctx, cudaMemsetAsync(d_total, 0, 4, st));
-    }
-    const unsigned long long* sorted = s->d_cand.as<unsigned long long>();
-    if (total > 0) {
-        size_t tb = s->cub_bytes;
-        int end_bit = 32 + P.idx_bits;
-        for (int nb = n_jobs - 1; nb > 0; nb >>= 1) ++end_bit;
-        cudaError_t e = cub::DeviceRadixSort::SortKeysDescending(s->d_cub.p, tb, s->d_cand.as<unsigned long long>(),
-                                                                 s->d_cand_sorted.as<unsigned long long>(), (int)total, 0, end_bit, st);
-        if (e != cudaSuccess) return vio360_fail(ctx, VIO360_ERR_CUDA, "cub sort: %s", cudaGetErrorString(e));
-        ctx->launches += 4;   // histogram / scan / onesweep passes of the library sort (not our kernels)
-        sorted = s->d_cand_sorted.as<unsigned long long>();
-    }
-    if (max_corners <= 0 && mem_space == VIO360_MEM_HOST) VIO_CUDA(ctx, s->d_corners.reserve((size_t)total * 8 + 8));
-    float* pool_xy = s->d_corners.as<float>();
-    { KernelTimer kt_(ctx, "k_select");
-    if (smem_grid) {
-        if (!s->select_attr_set) {
-            VIO_CUDA(ctx, cudaFuncSetAttribute(k_select<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-            s->select_attr_set = true;
-        }
-        k_select<true><<<n_jobs, 32, grid_bytes, st>>>(dj, P, n_jobs, sorted, max_corners, min_dist, pool_xy);
-    } else {
-        k_select<false><<<n_jobs, 32, 0, st>>>(dj, P, n_jobs, sorted, max_corners, min_dist, pool_xy);
-    }
-    }
-    VIO_LAUNCH_CHECK(ctx);
-    if (mem_space == VIO360_MEM_HOST) {
+        P.max_cand = (unsigned int)s->max_cand;
+        if ((rc = launch_detect_pipeline(ctx, dj, P, n_jobs, any_mask, max_corners, quality, min_dist, smem_grid, grid_bytes))) return rc;
         uint8_t* ho = s->h_dout.as<uint8_t>();
         const size_t small_bytes = 16 * (size_t)(n_jobs + 1);
         VIO_CUDA(ctx, cudaMemcpyAsync(ho, s->d_small.p, small_bytes, cudaMemcpyDeviceToHost, st));
-        if (max_corners > 0) {
+        if (mem_space == VIO360_MEM_HOST && max_corners > 0)
             VIO_CUDA(ctx, cudaMemcpyAsync(ho + small_bytes, s->d_corners.p, cap * 8 * n_jobs, cudaMemcpyDeviceToHost, st));
-            VIO_CUDA(ctx, cudaStreamSynchronize(st));
-            for (int b = 0; b < n_jobs; ++b) {
-                const int n = ((const int*)ho)[4 * b + 2];
-                *jobs[b].out_n = n;
-                if (n > 0) memcpy(jobs[b].out_xy, ho + small_bytes + cap * 8 * b, (size_t)n * 8);
-            }
-        } else {   // unlimited corner count: copy what each image produced
-            VIO_CUDA(ctx, cudaStreamSynchronize(st));
-            size_t begin = 0;   // segments follow the descending sort: last image first
-            for (int b = n_jobs - 1; b >= 0; --b) {
-                const int n = ((const int*)ho)[4 * b + 2];
-                *jobs[b].out_n = n;
-                if (n > 0) VIO_CUDA(ctx, cudaMemcpyAsync(jobs[b].out_xy, pool_xy + 2 * begin, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
-                begin += ((const unsigned int*)ho)[4 * b + 1];
-            }
-            VIO_CUDA(ctx, cudaStreamSynchronize(st));
-        }
-    } else {
-        VIO_CUDA(ctx, cudaMemcpyAsync(s->h_dout.p, s->d_small.p, 16 * (size_t)n_jobs, cudaMemcpyDeviceToHost, st));
         VIO_CUDA(ctx, cudaStreamSynchronize(st));
-        for (int b = 0; b < n_jobs; ++b) *jobs[b].out_n = ((const int*)s->h_dout.p)[4 * b + 2];
+        unsigned int worst = 0;
+        for (int b = 0; b < n_jobs; ++b) worst = std::max(worst, ((const unsigned int*)ho)[4 * b + 1]);
+        if (worst <= (unsigned int)s->max_cand) break;
+        if ((rc = reserve_candidates(ctx, (size_t)worst + worst / 4, n_jobs))) return rc;
+        if (max_corners <= 0 && mem_space == VIO360_MEM_HOST) VIO_CUDA(ctx, s->d_corners.reserve((size_t)s->max_cand * 8 * n_jobs));
+    }
+    {
+        const uint8_t* ho = s->h_dout.as<uint8_t>();
+        const size_t small_bytes = 16 * (size_t)(n_jobs + 1);
+        for (int b = 0; b < n_jobs; ++b) {
+            const int n = ((const int*)ho)[4 * b + 2];
+            *jobs[b].out_n = n;
+            if (mem_space != VIO360_MEM_HOST || n <= 0) continue;
+            if (max_corners > 0) memcpy(jobs[b].out_xy, ho + small_bytes + cap * 8 * b, (size_t)n * 8);
+            else VIO_CUDA(ctx, cudaMemcpyAsync(jobs[b].out_xy, s->d_corners.as<float>() + 2 * (size_t)s->max_cand * b, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+        }
+        if (mem_space == VIO360_MEM_HOST && max_corners <= 0) VIO_CUDA(ctx, cudaStreamSynchronize(st));
     }
     return VIO360_OK;
 }
@@ -834,7 +819,7 @@ extern "C" int vio360_fe_ransac_rotation_batch(vio360_ctx* ctx, const vio360_ran
         const vio360_ransac_job& j = jobs[b];
         const size_t n = (size_t)j.n, I = (size_t)iters;
         RansacJobDev& d = hj[b];
-        d.n = j.n;
+        d.n = j.n; d.n_ptr = nullptr;
         if (mem_space == VIO360_MEM_DEVICE) {
             d.prev_xy = j.prev_xy; d.cur_xy = j.cur_xy; d.samples = j.samples; d.mask = j.inlier_mask;
         } else {

@@ -39,6 +39,7 @@ struct TrackJobDev {
     float* err;    // may be null
     uint8_t* keep; // may be null
     int n;
+    const int* n_ptr;   // when set, the point count is read from device memory (per-frame chain, fe_seq.cuh) and n is ignored
 };
 
 struct LkParams {
@@ -168,7 +169,7 @@ __global__ void __launch_bounds__(kLkWarps * 32) __maxnreg__(REGS) k_lk_track(co
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const TrackJobDev& job = jobs[blockIdx.y];
     const int pt = blockIdx.x * kLkWarps + warp;
-    if (pt >= job.n) return;   // warp-uniform; only __syncwarp is used below
+    if (pt >= (job.n_ptr ? *job.n_ptr : job.n)) return;   // warp-uniform; only __syncwarp is used below
     uint32_t* sT = lk_smem + warp * kLkWarpWords;
     int* sDx = reinterpret_cast<int*>(sT + kTRows * kTWords);
     int* sDy = sDx + kDPlane;

@@ -184,6 +184,45 @@ int vio360_fe_grid_cap(vio360_ctx* ctx, const float* xy, const int32_t* track_co
                        int n_frames, int stride, int width, int height, int grid_cols, int grid_rows,
                        int max_per_cell, uint8_t* keep, int mem_space);
 
+/* SURVEY 8-F rank 2, complete: one call per frame that replaces FeatureTracker::TrackFeatures
+ * (src/processing/FeatureTracker.cpp:61-206) for a whole sequence, with the feature list RESIDENT ON THE DEVICE
+ * between the stages and between the frames:
+ *   TrackOpticalFlow (:110) -> post filter (:118-126) -> RejectOutliersRotationRANSAC (:131) -> a Feature per
+ *   inlier with its id carried and track_count + 1 (:139-163) -> RemoveClusteredFeatures (:168) ->
+ *   Frame::AssignFeaturesToGrid + LimitFeaturesPerGrid (:171-172; Frame.cpp:108-202) -> if count < max_features:
+ *   DetectNewFeatures(image, CreateFeatureMask(features)) (:176-199), new ids from m_next_feature_id, grid cap again.
+ * The first frame of a sequence (no previous frame, :68-92) is the same chain on an empty list.
+ * Only the new frame goes in and only the final feature list comes out; no intermediate count or list
+ * visits the host.  The shared_ptr<Feature> observation bookkeeping stays with the caller (ids are returned).
+ *
+ * The reference seeds its RANSAC from std::random_device (:273-274).  Here the caller passes
+ * ransac_iterations x 3 random 32-bit words per frame; a word r selects index (r * n) >> 32 among the n
+ * filtered points, and an index equal to an earlier one of its triple moves to (index + 1) % n.           */
+typedef struct vio360_seq vio360_seq;
+typedef struct {
+    int max_features; float min_distance; float quality_level;   /* FeatureTracker ctor (Estimator.cpp:47-53)            */
+    int grid_cols, grid_rows, max_features_per_grid;             /* Frame::SetGridParameters (Estimator.cpp:572-576)      */
+    int remove_clustered; float clustered_std_ratio;             /* ConfigUtils visualization_highlight_clustered_grid,
+                                                                    visualization_clustered_std_ratio (FeatureTracker.cpp:407-423) */
+    int ransac_iterations; float ransac_threshold_deg;           /* FeatureTracker.cpp:36-37 (1000, 2.0)                  */
+} vio360_seq_config;
+/* vio360_fe_configure must have been called; a later vio360_fe_configure invalidates the sequence. */
+int vio360_seq_create(vio360_ctx* ctx, const vio360_seq_config* cfg, vio360_seq** out);
+void vio360_seq_destroy(vio360_seq* seq);
+int vio360_seq_reset(vio360_seq* seq);          /* forget the features and the previous frame; ids restart at 0 */
+int vio360_seq_capacity(const vio360_seq* seq);  /* entries the output arrays of a frame job must hold (2 * max_features) */
+typedef struct {
+    vio360_seq* seq;
+    const uint8_t* image; size_t pitch;   /* the new frame (CV_8UC1).  Device-space frames with 4-byte aligned base and
+                                             pitch are aliased, not copied: they must stay valid and unchanged until the
+                                             NEXT frame of the sequence has been processed (it is that call's previous frame) */
+    const uint32_t* ransac_words;         /* ransac_iterations x 3                                                       */
+    int32_t* ids; float* xy; int32_t* track_count;   /* out: the frame's features in the reference's order (capacity entries) */
+    int* n_features; int* n_tracked; int* n_detected; /* out, HOST memory in both spaces: list length, m_num_tracked, m_num_detected */
+} vio360_frame_job;
+/* One frame of each of n_jobs independent sequences (BASELINE config 4: one job per sequence). */
+int vio360_fe_track_frame_batch(vio360_ctx* ctx, const vio360_frame_job* jobs, int n_jobs, int mem_space);
+
 /* ------------------------------------------- path B: BA factor evaluation ---- */
 /* A window = what Optimizer::RunLocalBA / RunBA assemble (src/optimization/
  * Optimizer.cpp:741-840): K poses, M landmarks, O observations.                     */
