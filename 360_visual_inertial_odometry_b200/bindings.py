@@ -22,6 +22,7 @@ EXPORTS = [
     "vio360_fe_configure", "vio360_fe_track", "vio360_fe_track_batch", "vio360_fe_detect",
     "vio360_fe_detect_batch", "vio360_fe_pyramid", "vio360_fe_min_eigen_val",
     "vio360_fe_ransac_rotation", "vio360_fe_ransac_rotation_batch", "vio360_fe_cluster_filter", "vio360_fe_grid_cap",
+    "vio360_seq_create", "vio360_seq_destroy", "vio360_seq_reset", "vio360_seq_capacity", "vio360_fe_track_frame_batch",
     "vio360_ba_create", "vio360_ba_destroy", "vio360_ba_set_structure", "vio360_ba_set_outliers",
     "vio360_ba_set_shard", "vio360_ba_set_parameters", "vio360_ba_evaluate", "vio360_ba_evaluate_f32",
     "vio360_ba_get_residuals_jacobians", "vio360_ba_normal_blocks", "vio360_ba_reduced_dim",
@@ -53,6 +54,19 @@ class DetectJob(C.Structure):
                 ("mask", C.c_void_p), ("mask_pitch", C.c_size_t),
                 ("out_xy", C.c_void_p), ("out_n", C.c_void_p),
                 ("occupied_xy", C.c_void_p), ("n_occupied", C.c_int), ("occupied_radius", C.c_int)]
+
+
+class SeqConfig(C.Structure):
+    _fields_ = [("max_features", C.c_int), ("min_distance", C.c_float), ("quality_level", C.c_float),
+                ("grid_cols", C.c_int), ("grid_rows", C.c_int), ("max_features_per_grid", C.c_int),
+                ("remove_clustered", C.c_int), ("clustered_std_ratio", C.c_float),
+                ("ransac_iterations", C.c_int), ("ransac_threshold_deg", C.c_float)]
+
+
+class FrameJob(C.Structure):
+    _fields_ = [("seq", C.c_void_p), ("image", C.c_void_p), ("pitch", C.c_size_t), ("ransac_words", C.c_void_p),
+                ("ids", C.c_void_p), ("xy", C.c_void_p), ("track_count", C.c_void_p),
+                ("n_features", C.c_void_p), ("n_tracked", C.c_void_p), ("n_detected", C.c_void_p)]
 
 
 _lib = None
@@ -101,6 +115,12 @@ def load():
     lib.vio360_fe_min_eigen_val.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
     lib.vio360_fe_cluster_filter.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 6 + [C.c_float, C.c_void_p, C.c_int]
     lib.vio360_fe_grid_cap.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 7 + [C.c_void_p, C.c_int]
+    lib.vio360_seq_create.argtypes = [C.c_void_p, C.POINTER(SeqConfig), C.POINTER(C.c_void_p)]
+    lib.vio360_seq_destroy.restype = None
+    lib.vio360_seq_destroy.argtypes = [C.c_void_p]
+    lib.vio360_seq_reset.argtypes = [C.c_void_p]
+    lib.vio360_seq_capacity.argtypes = [C.c_void_p]
+    lib.vio360_fe_track_frame_batch.argtypes = [C.c_void_p, C.POINTER(FrameJob), C.c_int, C.c_int]
     lib.vio360_ba_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
     lib.vio360_ba_set_structure.argtypes = [C.c_void_p] + [C.c_void_p] * 6 + [C.c_double, C.c_double, C.c_void_p,
                                                                                C.c_double, C.c_void_p, C.c_void_p]
@@ -230,6 +250,43 @@ class Context:
             j.keep = keep.ctypes.data if want_keep else None
         self.check(self.lib.vio360_fe_track_batch(self.h, jobs, len(pairs), MEM_HOST))
         return outs
+
+    # ---- device-resident per-frame chain (FeatureTracker::TrackFeatures, FeatureTracker.cpp:61-206)
+    def seq_create(self, max_features=1000, min_distance=30.0, quality=0.01, grid_cols=20, grid_rows=10, max_per_cell=10,
+                   remove_clustered=True, std_ratio=0.25, ransac_iters=1000, ransac_thr_deg=2.0):
+        cfg = SeqConfig(max_features, min_distance, quality, grid_cols, grid_rows, max_per_cell, int(remove_clustered),
+                        std_ratio, ransac_iters, ransac_thr_deg)
+        h = C.c_void_p()
+        self.check(self.lib.vio360_seq_create(self.h, C.byref(cfg), C.byref(h)))
+        return h
+
+    def seq_destroy(self, seq):
+        self.lib.vio360_seq_destroy(seq)
+
+    def seq_reset(self, seq):
+        self.check(self.lib.vio360_seq_reset(seq))
+
+    def fe_track_frame_batch(self, seqs, images, words):
+        """one frame for each sequence (host arrays) -> list of (ids, xy, track_count, n_tracked, n_detected)"""
+        nj = len(seqs)
+        jobs = (FrameJob * nj)()
+        keep, outs = [], []
+        for b in range(nj):
+            cap = self.lib.vio360_seq_capacity(seqs[b])
+            img = np.ascontiguousarray(images[b], np.uint8)
+            w = np.ascontiguousarray(words[b], np.uint32)
+            ids = np.zeros(cap, np.int32); xy = np.zeros((cap, 2), np.float32); tc = np.zeros(cap, np.int32)
+            cnt = (C.c_int * 3)()
+            keep.append((img, w, cnt)); outs.append((ids, xy, tc, cnt))
+            j = jobs[b]
+            j.seq, j.image, j.pitch, j.ransac_words = seqs[b], img.ctypes.data, img.strides[0], w.ctypes.data
+            j.ids, j.xy, j.track_count = ids.ctypes.data, xy.ctypes.data, tc.ctypes.data
+            j.n_features, j.n_tracked, j.n_detected = C.addressof(cnt), C.addressof(cnt) + 4, C.addressof(cnt) + 8
+        self.check(self.lib.vio360_fe_track_frame_batch(self.h, jobs, nj, MEM_HOST))
+        return [(ids[:cnt[0]].copy(), xy[:cnt[0]].copy(), tc[:cnt[0]].copy(), cnt[1], cnt[2]) for ids, xy, tc, cnt in outs]
+
+    def fe_track_frame_batch_raw(self, jobs, n_jobs, mem_space):
+        self.check(self.lib.vio360_fe_track_frame_batch(self.h, jobs, n_jobs, mem_space))
 
     def fe_track_batch_raw(self, jobs, n_jobs, mem_space):
         self.check(self.lib.vio360_fe_track_batch(self.h, jobs, n_jobs, mem_space))

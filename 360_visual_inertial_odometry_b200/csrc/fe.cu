@@ -11,8 +11,11 @@
 #include "fe_ransac.cuh"
 #include "fe_lk.cuh"
 #include "fe_pyr.cuh"
+#include "fe_seq.cuh"
 
 using namespace vio360;
+
+static uint64_t g_fe_generation = 0;   // bumped by every vio360_fe_configure: sequences of an older state are invalid
 
 struct FeSlot {
     uint64_t key = 0;
@@ -30,6 +33,9 @@ struct FeSlot {
 
 struct vio360_fe_state {
     bool configured = false;
+    uint64_t generation = 0;
+    DevBuf d_seq;                // per-call tables of the per-frame chain (fe_seq_host.inc)
+    PinBuf h_seq;
     int W = 0, H = 0, nlevels = 0, win = 21, max_iters = 30;
     double eps2 = 0, min_eig = 0;
     float polar_ratio = 0.15f;
@@ -71,6 +77,7 @@ void vio360_fe_release(vio360_ctx* ctx) {
     vio360_fe_state* s = ctx->fe;
     if (!s) return;
     for (auto& sl : s->slots) sl.mem.release();
+    s->d_seq.release(); s->h_seq.release();
     DevBuf* db[] = {&s->d_jobs, &s->d_pyrjobs, &s->d_pts_in, &s->d_pts_out, &s->d_status, &s->d_err, &s->d_keep,
                     &s->d_djobs, &s->d_eig, &s->d_mask, &s->d_small, &s->d_cand, &s->d_grid,
                     &s->d_corners, &s->d_ransac, &s->d_occ};
@@ -100,6 +107,7 @@ extern "C" int vio360_fe_configure(vio360_ctx* ctx, int width, int height, int m
     vio360_fe_release(ctx);
     vio360_fe_state* s = new vio360_fe_state();
     ctx->fe = s;
+    s->generation = ++g_fe_generation;
     s->W = width; s->H = height; s->win = win;
     // calcOpticalFlowPyrLK: maxCount clamped to [0,100], epsilon to [0,10] then squared
     s->max_iters = std::min(std::max(max_iters, 0), 100);
@@ -294,6 +302,30 @@ static LkParams lk_params(const vio360_fe_state* s) {
     return P;
 }
 
+// one LK launch for nj jobs of up to max_n points each
+static int launch_lk(vio360_ctx* ctx, const TrackJobDev* dj, int nj, int max_n, const LkParams& lp) {
+    vio360_fe_state* s = ctx->fe;
+    cudaStream_t st = ctx->stream;
+    { KernelTimer kt_(ctx, "k_lk_track");
+    auto launch = [&](auto kern, int warps) -> cudaError_t {
+        const size_t smem = (size_t)warps * kLkWarpWords * sizeof(uint32_t);
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        kern<<<dim3((max_n + warps - 1) / warps, nj), warps * 32, smem, st>>>(dj, lp);
+        return cudaSuccess;
+    };
+    cudaError_t e;
+    if (s->lk_mb == 3) e = launch(k_lk_track<7, 96>, 7);
+    else if (s->lk_mb == 4) e = launch(k_lk_track<6, 80>, 6);
+    else if (s->lk_mb == 5) e = launch(k_lk_track<6, 104>, 6);
+    else if (s->lk_mb == 6) e = launch(k_lk_track<9, 112>, 9);
+    else e = launch(k_lk_track<8, 128>, 8);
+    if (e != cudaSuccess) return vio360_fail(ctx, VIO360_ERR_CUDA, "k_lk_track: %s", cudaGetErrorString(e));
+    }
+    VIO_LAUNCH_CHECK(ctx);
+    return VIO360_OK;
+}
+
 extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jobs, int n_jobs, int mem_space) {
     if (!ctx) return VIO360_ERR_INVALID;
     vio360_fe_state* s = ctx->fe;
@@ -414,23 +446,7 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
         if ((rc = launch_pyramids(ctx, todo[g], pyr_off))) return rc;
         pyr_off += todo[g].size() * per;
         if (max_n == 0) continue;
-        { KernelTimer kt_(ctx, "k_lk_track");
-        auto launch = [&](auto kern, int warps) -> cudaError_t {
-            const size_t smem = (size_t)warps * kLkWarpWords * sizeof(uint32_t);
-            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            if (e != cudaSuccess) return e;
-            kern<<<dim3((max_n + warps - 1) / warps, nj), warps * 32, smem, st>>>(dj + j0, lp);
-            return cudaSuccess;
-        };
-        cudaError_t e;
-        if (s->lk_mb == 3) e = launch(k_lk_track<7, 96>, 7);
-        else if (s->lk_mb == 4) e = launch(k_lk_track<6, 80>, 6);
-        else if (s->lk_mb == 5) e = launch(k_lk_track<6, 104>, 6);
-        else if (s->lk_mb == 6) e = launch(k_lk_track<9, 112>, 9);
-        else e = launch(k_lk_track<8, 128>, 8);
-        if (e != cudaSuccess) return vio360_fail(ctx, VIO360_ERR_CUDA, "k_lk_track: %s", cudaGetErrorString(e));
-        }
-        VIO_LAUNCH_CHECK(ctx);
+        if ((rc = launch_lk(ctx, dj + j0, nj, max_n, lp))) return rc;
     }
     if (max_n == 0) {
         if (mem_space == VIO360_MEM_HOST) VIO_CUDA(ctx, cudaStreamSynchronize(st));   // the caller's frames are free again
@@ -819,7 +835,7 @@ extern "C" int vio360_fe_ransac_rotation_batch(vio360_ctx* ctx, const vio360_ran
         const vio360_ransac_job& j = jobs[b];
         const size_t n = (size_t)j.n, I = (size_t)iters;
         RansacJobDev& d = hj[b];
-        d.n = j.n; d.n_ptr = nullptr;
+        d.n = j.n;
         if (mem_space == VIO360_MEM_DEVICE) {
             d.prev_xy = j.prev_xy; d.cur_xy = j.cur_xy; d.samples = j.samples; d.mask = j.inlier_mask;
         } else {
@@ -962,3 +978,5 @@ extern "C" int vio360_fe_grid_cap(vio360_ctx* ctx, const float* xy, const int32_
                                   int width, int height, int grid_cols, int grid_rows, int max_per_cell, uint8_t* keep, int mem_space) {
     return grid_filter(ctx, 1, xy, track_count, n, n_frames, stride, width, height, grid_cols, grid_rows, 0.f, max_per_cell, keep, mem_space);
 }
+
+#include "fe_seq_host.inc"

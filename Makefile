@@ -15,7 +15,7 @@ $(CSRC)/ba.o: $(CSRC)/ba.cu $(CSRC)/ba_peer.cuh $(CSRC)/ba_math.cuh $(CSRC)/ba_s
 	$(NVCC) $(NVFLAGS) -c $< -o $@
 # --fmad=false: float expressions must round like OpenCV's non-FMA baseline code; the
 # places where OpenCV's dispatched code does fuse are explicit fmaf() calls.
-$(CSRC)/fe.o: $(CSRC)/fe.cu $(CSRC)/fe_grid.cuh $(CSRC)/fe_pyr.cuh $(CSRC)/fe_lk.cuh $(CSRC)/fe_detect.cuh $(CSRC)/fe_ransac.cuh $(CSRC)/common.cuh include/vio360.h
+$(CSRC)/fe.o: $(CSRC)/fe.cu $(CSRC)/fe_seq.cuh $(CSRC)/fe_seq_host.inc $(CSRC)/fe_grid.cuh $(CSRC)/fe_pyr.cuh $(CSRC)/fe_lk.cuh $(CSRC)/fe_detect.cuh $(CSRC)/fe_ransac.cuh $(CSRC)/common.cuh include/vio360.h
 	$(NVCC) $(NVFLAGS) --fmad=false -c $< -o $@
 
 $(LIB): $(OBJS)

@@ -172,9 +172,95 @@ def cv2_lk_track(prev, cur, pts):
     return nxt.reshape(-1, 2), st.reshape(-1), err.reshape(-1)
 
 
-def cv2_good_features(img, mask=None, max_corners=1000):
+def cv2_good_features(img, mask=None, max_corners=1000, quality=GFTT_QUALITY, min_dist=GFTT_MIN_DIST):
     """cv::goodFeaturesToTrack exactly as FeatureTracker.cpp:222-223 calls it."""
     import cv2
-    c = cv2.goodFeaturesToTrack(img, max_corners, GFTT_QUALITY, GFTT_MIN_DIST, mask=mask,
+    c = cv2.goodFeaturesToTrack(img, max_corners, quality, min_dist, mask=mask,
                                 blockSize=3, useHarrisDetector=False, k=0.04)
     return np.zeros((0, 2), np.float32) if c is None else c.reshape(-1, 2)
+
+
+# ------------------------------------------------------------------ the per-frame chain
+def ransac_samples_from_words(words, n):
+    """The sample rule of vio360_fe_track_frame_batch (include/vio360.h): word r -> (r * n) >> 32, an index
+    equal to an earlier one of its triple moves to (index + 1) % n.  The reference draws from
+    std::random_device (FeatureTracker.cpp:273-289): any three distinct uniform indices are a faithful run."""
+    words = np.ascontiguousarray(words, np.uint32).reshape(-1, 3)
+    out = np.zeros(words.shape, np.int32)
+    for it in range(words.shape[0]):
+        idx = []
+        for s in range(3):
+            v = (int(words[it, s]) * n) >> 32
+            while v in idx:
+                v = (v + 1) % n
+            idx.append(v)
+        out[it] = idx
+    return out
+
+
+class SequenceTracker:
+    """FeatureTracker::TrackFeatures (FeatureTracker.cpp:61-206) frame after frame, on the CPU: cv2 for the two
+    OpenCV calls (or oracle/fe_ref.c with use_cv2=False), fe_ref.c for the reference's own list logic.
+    State = what Frame / Feature carry between frames: ids, pixel coordinates, track counts."""
+
+    def __init__(self, w, h, max_features=1000, min_distance=30.0, quality=0.01, grid_cols=20, grid_rows=10,
+                 max_per_cell=10, remove_clustered=True, std_ratio=0.25, ransac_thr_deg=2.0, use_cv2=True,
+                 polar_ratio=0.15, margin=20):
+        self.w, self.h = w, h
+        self.max_features, self.min_distance, self.quality = max_features, float(np.float32(min_distance)), float(np.float32(quality))
+        self.grid = (grid_cols, grid_rows, max_per_cell)
+        self.remove_clustered, self.std_ratio, self.ransac_thr_deg = remove_clustered, std_ratio, ransac_thr_deg
+        self.use_cv2, self.polar_ratio, self.margin = use_cv2, polar_ratio, margin
+        self.base = base_mask(w, h, polar_ratio, margin)
+        self.polar = base_mask(w, h, polar_ratio, 0)              # Camera::CreatePolarMask: rows only
+        self.ids = np.zeros(0, np.int32); self.xy = np.zeros((0, 2), np.float32); self.tc = np.zeros(0, np.int32)
+        self.next_id = 0
+        self.prev = None
+
+    def _detect(self, img, mask):
+        if self.use_cv2:
+            return cv2_good_features(img, mask, self.max_features, self.quality, self.min_distance).astype(np.float32)
+        return good_features(img, mask, self.max_features, self.quality, self.min_distance)
+
+    def _grid_cap(self):
+        keep = grid_cap(self.xy, self.tc, self.w, self.h, *self.grid) if len(self.xy) else np.zeros(0, np.uint8)
+        k = keep.astype(bool)
+        self.ids, self.xy, self.tc = self.ids[k], self.xy[k], self.tc[k]
+
+    def step(self, img, words):
+        """returns (n_tracked, n_detected); the frame's features are self.ids / self.xy / self.tc"""
+        n_tracked = 0
+        if self.prev is not None and len(self.xy):
+            if self.use_cv2:
+                cur, st, _ = cv2_lk_track(self.prev, img, self.xy)
+            else:
+                cur, st, _, _ = lk_track(self.prev, img, self.xy)
+            keep = post_filter(cur, st, self.w, self.h, self.polar_ratio, float(self.margin)).astype(bool)   # :118-126
+            gp, gc, gi = self.xy[keep], cur[keep], np.nonzero(keep)[0]
+            if len(gc) >= 3:                                                                              # :131
+                samples = ransac_samples_from_words(words, len(gc))
+                _, mask, _, _, _ = ransac_rotation(gp, gc, self.w, self.h, samples, self.ransac_thr_deg)
+            else:
+                mask = np.ones(len(gc), np.uint8)
+            m = mask.astype(bool)
+            self.ids, self.xy, self.tc = self.ids[gi[m]], gc[m].copy(), self.tc[gi[m]] + 1               # :139-163
+            n_tracked = len(self.ids)
+            if self.remove_clustered and len(self.xy) >= 4:                                               # :168
+                k = cluster_filter(self.xy, self.w, self.h, self.grid[0], self.grid[1], self.std_ratio).astype(bool)
+                self.ids, self.xy, self.tc = self.ids[k], self.xy[k], self.tc[k]
+            self._grid_cap()                                                                               # :171-172
+        else:
+            self.ids = np.zeros(0, np.int32); self.xy = np.zeros((0, 2), np.float32); self.tc = np.zeros(0, np.int32)
+        n_detected = 0
+        if len(self.ids) < self.max_features:                                                              # :176
+            # CreateFeatureMask starts from the POLAR mask (:389); DetectNewFeatures ands it with polar & boundary (:212-219)
+            mask = feature_mask(self.polar, self.xy, int(self.min_distance)) & self.base
+            new = self._detect(img, mask)
+            n_detected = len(new)
+            self.ids = np.concatenate([self.ids, self.next_id + np.arange(n_detected, dtype=np.int32)])
+            self.xy = np.concatenate([self.xy, new.reshape(-1, 2)]).astype(np.float32)
+            self.tc = np.concatenate([self.tc, np.zeros(n_detected, np.int32)])
+            self.next_id += n_detected
+            self._grid_cap()                                                                               # :199-200
+        self.prev = img
+        return n_tracked, n_detected

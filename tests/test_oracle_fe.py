@@ -113,3 +113,30 @@ def test_feature_mask_matches_cv2_circle():
             cv2.circle(ref, (int(np.rint(x)), int(np.rint(y))), r, 0, -1)
         got = fo.feature_mask(np.full((h, w), 255, np.uint8), pts, r)
         assert np.array_equal(got, ref), r
+
+
+def test_sequence_chain_cv2_vs_restatement(synthetic):
+    """The CPU statement of FeatureTracker::TrackFeatures (fe_oracle.SequenceTracker) gives the same per-frame feature
+    ids / track counts whether the two OpenCV calls are cv2 itself or oracle/fe_ref.c (positions within 0.05 px),
+    and it behaves like a tracker: ids persist, track counts grow, lost features are replenished."""
+    W, H, T = 640, 320, 6
+    frames = [synthetic.render_erp_frame(W, H, t, seed=11, n_waves=24, sigma_omega=40.0) for t in range(T)]
+    rng = np.random.default_rng(5)
+    kw = dict(max_features=200, min_distance=12.0, grid_cols=20, grid_rows=10, max_per_cell=4, std_ratio=0.15, ransac_thr_deg=1.0)
+    a = fo.SequenceTracker(W, H, use_cv2=True, **kw); b = fo.SequenceTracker(W, H, use_cv2=False, **kw)
+    seen_old = False
+    for t in range(T):
+        words = rng.integers(0, 2 ** 32, (64, 3), dtype=np.uint64).astype(np.uint32)
+        ra = a.step(frames[t], words); rb = b.step(frames[t], words)
+        assert ra == rb and np.array_equal(a.ids, b.ids) and np.array_equal(a.tc, b.tc)
+        assert np.abs(a.xy - b.xy).max() < POS_TOL
+        b.xy = a.xy.copy()                       # keep the two chains on identical inputs
+        if t == 0:
+            assert ra[0] == 0 and ra[1] > 50 and (a.tc == 0).all()
+        else:
+            assert ra[0] > 20 and a.tc.max() == t
+            seen_old = seen_old or (a.ids[a.tc == t] < 200).any()
+        assert len(np.unique(a.ids)) == len(a.ids)
+    assert seen_old
+    s = fo.ransac_samples_from_words(np.array([[0, 0, 0], [2 ** 32 - 1, 2 ** 32 - 1, 0], [2 ** 31, 2 ** 31, 2 ** 31]], np.uint32), 5)
+    assert s.tolist() == [[0, 1, 2], [4, 0, 1], [2, 3, 4]]
