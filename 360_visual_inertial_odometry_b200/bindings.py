@@ -28,6 +28,7 @@ EXPORTS = [
     "vio360_ba_get_residuals_jacobians", "vio360_ba_normal_blocks", "vio360_ba_reduced_dim",
     "vio360_ba_build_reduced_system", "vio360_ba_set_lm_diagonal", "vio360_ba_reduced_system_dev", "vio360_ba_fetch_reduced_system",
     "vio360_ba_reduced_band_dev", "vio360_ba_expand_band",
+    "vio360_lm_default_options", "vio360_ba_lm_solve",
     "vio360_ba_peer_export", "vio360_ba_peer_attach", "vio360_ba_peer_exchange", "vio360_ba_peer_detach",
     "vio360_ba_column_sqnorm", "vio360_ba_chi2", "vio360_ba_solve_reduced", "vio360_pnp_evaluate", "vio360_triangulate",
 ]
@@ -54,6 +55,20 @@ class DetectJob(C.Structure):
                 ("mask", C.c_void_p), ("mask_pitch", C.c_size_t),
                 ("out_xy", C.c_void_p), ("out_n", C.c_void_p),
                 ("occupied_xy", C.c_void_p), ("n_occupied", C.c_int), ("occupied_radius", C.c_int)]
+
+
+class LmOptions(C.Structure):
+    _fields_ = [("max_num_iterations", C.c_int), ("initial_trust_region_radius", C.c_double), ("max_trust_region_radius", C.c_double),
+                ("min_trust_region_radius", C.c_double), ("min_relative_decrease", C.c_double), ("min_lm_diagonal", C.c_double),
+                ("max_lm_diagonal", C.c_double), ("function_tolerance", C.c_double), ("gradient_tolerance", C.c_double),
+                ("parameter_tolerance", C.c_double), ("jacobi_scaling", C.c_int), ("max_num_consecutive_invalid_steps", C.c_int),
+                ("apply_loss", C.c_int)]
+
+
+class LmSummary(C.Structure):
+    _fields_ = [("iterations", C.c_int), ("num_successful_steps", C.c_int), ("num_unsuccessful_steps", C.c_int), ("termination", C.c_int),
+                ("initial_cost", C.c_double), ("final_cost", C.c_double), ("final_radius", C.c_double),
+                ("final_gradient_max_norm", C.c_double), ("n_trace", C.c_int)]
 
 
 class SeqConfig(C.Structure):
@@ -147,6 +162,8 @@ def load():
     lib.vio360_ba_chi2.argtypes = [C.c_void_p, C.c_double, C.c_void_p, C.c_void_p]
     lib.vio360_triangulate.argtypes = [C.c_void_p] * 5 + [C.c_int, C.c_void_p, C.c_void_p]
     lib.vio360_ba_solve_reduced.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.vio360_lm_default_options.argtypes = [C.POINTER(LmOptions)]
+    lib.vio360_ba_lm_solve.argtypes = [C.c_void_p, C.POINTER(LmOptions), C.c_void_p, C.c_void_p, C.POINTER(LmSummary), C.c_void_p, C.c_int]
     lib.vio360_pnp_evaluate.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 5 + [C.c_double, C.c_double, C.c_void_p,
                                                                                    C.c_double] + [C.c_void_p] * 8
     _lib = lib
@@ -554,6 +571,19 @@ class BAWindow:
         dp = np.zeros((self.K, 6)); dl = np.zeros((self.M, 3)) if want_points else None
         self.ctx.check(self.lib.vio360_ba_solve_reduced(self.h, _ptr(dp), _ptr(dl)))
         return dp, dl
+
+    def lm_solve(self, pose_delta, points, **overrides):
+        """vio360_ba_lm_solve: returns (pose_delta K x 6, points M x 3, summary dict, trace n x 8)."""
+        opt = LmOptions()
+        self.ctx.check(self.lib.vio360_lm_default_options(C.byref(opt)))
+        for k, v in overrides.items():
+            setattr(opt, k, v)
+        pd = np.array(pose_delta, np.float64).reshape(self.K, 6).copy(); pts = np.array(points, np.float64).reshape(self.M, 3).copy()
+        cap = opt.max_num_iterations + 2
+        trace = np.zeros((cap, 8)); sm = LmSummary()
+        self.ctx.check(self.lib.vio360_ba_lm_solve(self.h, C.byref(opt), _ptr(pd), _ptr(pts), C.byref(sm), _ptr(trace), cap))
+        summary = {f: getattr(sm, f) for f, _ in LmSummary._fields_}
+        return pd, pts, summary, trace[:sm.n_trace].copy()
 
     def column_sqnorm(self, apply_loss=True):
         out = np.zeros(6 * self.K + 3 * self.M)

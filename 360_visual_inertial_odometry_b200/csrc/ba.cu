@@ -63,6 +63,9 @@ struct vio360_ba {
     DevBuf d_r, d_Jp, d_Jl, d_partials, d_packed, d_blocks, d_chi2, d_flag;
     PinBuf pin;
     bool use_D = false;
+    // device LM loop (ba_lm.cuh): candidate point, step, per-parameter vectors, state
+    DevBuf d_cand_pose_delta, d_cand_points, d_cand_posebuf, d_step, d_colsq, d_scale, d_lm_state, d_lm_part;
+    PinBuf h_lm;
     // chunked (atomic-free) Schur path: see ba_schur.cuh
     std::vector<int> h_pose;                 // landmark-major pose index of every observation
     std::vector<SchurChunk> chunks;
@@ -154,6 +157,7 @@ __global__ void k_sum_partials(const double* __restrict__ partials, int n, doubl
 #include "ba_schur_kernels.cuh"
 #include "ba_solve.cuh"
 #include "ba_triangulate.cuh"
+#include "ba_lm.cuh"
 
 template <bool WANT_JAC>
 __global__ void __launch_bounds__(128) k_evaluate(BaDev d, bool apply_loss, double* __restrict__ r_out,
@@ -527,11 +531,14 @@ extern "C" void vio360_ba_destroy(vio360_ba* ba) {
                       &ba->d_points, &ba->d_free_map, &ba->d_point_fixed, &ba->d_D, &ba->d_r, &ba->d_Jp, &ba->d_Jl,
                       &ba->d_partials, &ba->d_packed, &ba->d_blocks, &ba->d_chi2, &ba->d_flag,
                       &ba->d_chunks, &ba->d_cov_ptr, &ba->d_cov_idx, &ba->d_free_pose, &ba->d_irregular, &ba->d_partS, &ba->d_partRhs, &ba->d_reach, &ba->d_slots, &ba->d_batch_rng,
-                      &ba->d_chol, &ba->d_linv, &ba->d_x, &ba->d_dl, &ba->d_reachF, &ba->d_band};
+                      &ba->d_chol, &ba->d_linv, &ba->d_x, &ba->d_dl, &ba->d_reachF, &ba->d_band,
+                      &ba->d_cand_pose_delta, &ba->d_cand_points, &ba->d_cand_posebuf, &ba->d_step, &ba->d_colsq, &ba->d_scale,
+                      &ba->d_lm_state, &ba->d_lm_part};
     for (DevBuf* b : bufs) b->release();
     peer_release(ba);
     ba->pin.release();
     ba->h_solve.release();
+    ba->h_lm.release();
     delete ba;
 }
 
@@ -1451,20 +1458,18 @@ extern "C" int vio360_pnp_evaluate(vio360_ctx* ctx, int N, const double* obs_uv,
 }
 
 // ---- solve the reduced system and back-substitute on the device ----
-extern "C" int vio360_ba_solve_reduced(vio360_ba* ba, double* delta_pose, double* delta_point) {
-    if (!ba) return VIO360_ERR_INVALID;
+// Device part of the solve: x (6 n_free, free-pose order) in d_x, the factorisation status behind it, and, when
+// want_points, the back-substituted landmark step in d_dl.  Nothing is copied to the host.
+static int solve_reduced_dev(vio360_ba* ba, bool want_points) {
     vio360_ctx* ctx = ba->ctx;
-    if (!ba->has_reduced) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_solve_reduced before ba_build_reduced_system");
-    if (!delta_pose) return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_solve_reduced: delta_pose is required");
-    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
     { int rcE = ensure_dense(ba); if (rcE) return rcE; }
     cudaStream_t st = ctx->stream;
     const int nb = ba->n_free, K = ba->K, M = ba->M;
     const size_t n = 6 * (size_t)nb;
     const size_t panel_bytes = n * 6 * sizeof(double);   // rows below the diagonal block + the rhs row
     if (panel_bytes > (size_t)200 * 1024) return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_solve_reduced: %d free poses exceed the single-CTA solver (max 710)", nb);
-    VIO_CUDA(ctx, ba->h_solve.reserve((n + 3 * (size_t)M + 8) * 8));
-    double* hx = ba->h_solve.as<double>();
+    VIO_CUDA(ctx, ba->d_x.reserve(n * 8 + 16));
+    if (nb == 0) VIO_CUDA(ctx, cudaMemsetAsync(ba->d_x.p, 0, 16, st));
     if (nb > 0) {
         if (ba->solve_dirty) {
             // envelope of S in free-pose index space: pose p shares a landmark with poses up to reach[p]
@@ -1523,9 +1528,8 @@ extern "C" int vio360_ba_solve_reduced(vio360_ba* ba, double* delta_pose, double
                                                                 ba->d_x.as<double>(), d_status);
         }
         VIO_LAUNCH_CHECK(ctx);
-        VIO_CUDA(ctx, cudaMemcpyAsync(hx, ba->d_x.p, n * 8 + 8, cudaMemcpyDeviceToHost, st));
     }
-    if (delta_point && M > 0) {
+    if (want_points && M > 0) {
         VIO_CUDA(ctx, ba->d_dl.reserve(3 * (size_t)M * 8));
         VIO_CUDA(ctx, cudaMemsetAsync(ba->d_dl.p, 0, 3 * (size_t)M * 8, st));
         const int nl = ba->lm_end - ba->lm_begin;
@@ -1535,8 +1539,24 @@ extern "C" int vio360_ba_solve_reduced(vio360_ba* ba, double* delta_pose, double
             k_back_substitute<<<(nl + 3) / 4, 128, 0, st>>>(d, ba->lm_begin, ba->lm_end, ba->reduced_apply_loss, ba->d_x.as<double>(), ba->d_dl.as<double>());
         }
         VIO_LAUNCH_CHECK(ctx);
-        VIO_CUDA(ctx, cudaMemcpyAsync(hx + n + 1, ba->d_dl.p, 3 * (size_t)M * 8, cudaMemcpyDeviceToHost, st));
     }
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_solve_reduced(vio360_ba* ba, double* delta_pose, double* delta_point) {
+    if (!ba) return VIO360_ERR_INVALID;
+    vio360_ctx* ctx = ba->ctx;
+    if (!ba->has_reduced) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_solve_reduced before ba_build_reduced_system");
+    if (!delta_pose) return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_solve_reduced: delta_pose is required");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const int nb = ba->n_free, K = ba->K, M = ba->M;
+    const size_t n = 6 * (size_t)nb;
+    VIO_CUDA(ctx, ba->h_solve.reserve((n + 3 * (size_t)M + 8) * 8));
+    double* hx = ba->h_solve.as<double>();
+    { int rcS = solve_reduced_dev(ba, delta_point != nullptr); if (rcS) return rcS; }
+    if (nb > 0) VIO_CUDA(ctx, cudaMemcpyAsync(hx, ba->d_x.p, n * 8 + 8, cudaMemcpyDeviceToHost, st));
+    if (delta_point && M > 0) VIO_CUDA(ctx, cudaMemcpyAsync(hx + n + 1, ba->d_dl.p, 3 * (size_t)M * 8, cudaMemcpyDeviceToHost, st));
     VIO_CUDA(ctx, cudaStreamSynchronize(st));
     if (nb > 0 && *reinterpret_cast<const int*>(hx + n) != 0)
         return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_solve_reduced: the reduced system is not positive definite");
@@ -1545,6 +1565,167 @@ extern "C" int vio360_ba_solve_reduced(vio360_ba* ba, double* delta_pose, double
         for (int k = 0; k < 6; ++k) delta_pose[6 * (size_t)p + k] = a >= 0 ? hx[6 * (size_t)a + k] : 0.0;
     }
     if (delta_point && M > 0) memcpy(delta_point, hx + n + 1, 3 * (size_t)M * 8);
+    return VIO360_OK;
+}
+
+// ---- the LM iteration of ceres::Solve on the device-built reduced system ----
+extern "C" int vio360_lm_default_options(vio360_lm_options* o) {
+    if (!o) return VIO360_ERR_INVALID;
+    o->max_num_iterations = 50;                 // Optimizer.cpp:76 (options.max_num_iterations)
+    o->initial_trust_region_radius = 1e4;       // ceres::Solver::Options defaults (include/ceres/solver.h)
+    o->max_trust_region_radius = 1e16;
+    o->min_trust_region_radius = 1e-32;
+    o->min_relative_decrease = 1e-3;
+    o->min_lm_diagonal = 1e-6;
+    o->max_lm_diagonal = 1e32;
+    o->function_tolerance = 1e-6;
+    o->gradient_tolerance = 1e-10;
+    o->parameter_tolerance = 1e-8;
+    o->jacobi_scaling = 1;
+    o->max_num_consecutive_invalid_steps = 5;
+    o->apply_loss = 1;
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_lm_solve(vio360_ba* ba, const vio360_lm_options* opt, double* pose_delta, double* points,
+                                  vio360_lm_summary* summary, double* trace, int trace_capacity) {
+    if (!ba) return VIO360_ERR_INVALID;
+    vio360_ctx* ctx = ba->ctx;
+    if (!ba->has_structure) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_lm_solve before ba_set_structure");
+    if (!opt || !pose_delta || !points || !summary) return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_lm_solve: null argument");
+    if (ba->shard_world > 1) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_lm_solve runs on an unsharded window (vio360_ba_set_shard(0, 1))");
+    if (!ba->irregular.empty()) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_lm_solve: %zu landmarks fit no chunk window", ba->irregular.size());
+    int rc = vio360_ba_set_parameters(ba, pose_delta, points);     // x0 to the device, pose chain at x0
+    if (rc) return rc;
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const int K = ba->K, M = ba->M, O = ba->O, nvar = 6 * K + 3 * M;
+    const size_t Ks = (size_t)K, Ms = (size_t)M;
+    VIO_CUDA(ctx, ba->d_cand_pose_delta.reserve(Ks * 6 * 8)); VIO_CUDA(ctx, ba->d_cand_points.reserve(Ms * 3 * 8));
+    VIO_CUDA(ctx, ba->d_cand_posebuf.reserve(Ks * kPoseStride * 8));
+    VIO_CUDA(ctx, ba->d_step.reserve((size_t)nvar * 8)); VIO_CUDA(ctx, ba->d_colsq.reserve((size_t)nvar * 8));
+    VIO_CUDA(ctx, ba->d_scale.reserve((size_t)nvar * 8)); VIO_CUDA(ctx, ba->d_lm_state.reserve(2 * sizeof(LmState)));
+    const int nbo = std::max(1, (O + 127) / 128), nbc = std::min(64, std::max(1, (nvar + kLmRedThreads - 1) / kLmRedThreads));
+    VIO_CUDA(ctx, ba->d_lm_part.reserve((size_t)(2 * nbo + nbc + 8) * 8));
+    VIO_CUDA(ctx, ba->h_lm.reserve(sizeof(LmState)));
+    VIO_CUDA(ctx, ba->d_x.reserve(6 * (size_t)std::max(ba->n_free, 1) * 8 + 16));
+    double* part_step = ba->d_lm_part.as<double>(); double* part_model = part_step + nbc; double* part_cost = part_model + nbo;
+    LmState* d_state = ba->d_lm_state.as<LmState>();
+    LmState* h_state = ba->h_lm.as<LmState>();
+    LmOptionsDev od;
+    od.min_diag = opt->min_lm_diagonal; od.max_diag = opt->max_lm_diagonal; od.max_radius = opt->max_trust_region_radius;
+    od.min_radius = opt->min_trust_region_radius; od.min_relative_decrease = opt->min_relative_decrease;
+    od.function_tolerance = opt->function_tolerance; od.gradient_tolerance = opt->gradient_tolerance;
+    od.parameter_tolerance = opt->parameter_tolerance; od.jacobi_scaling = opt->jacobi_scaling;
+    od.max_invalid = opt->max_num_consecutive_invalid_steps;
+    const bool loss = opt->apply_loss != 0;
+    auto read_state = [&]() -> int {
+        VIO_CUDA(ctx, cudaMemcpyAsync(h_state, d_state, sizeof(LmState), cudaMemcpyDeviceToHost, st));
+        VIO_CUDA(ctx, cudaStreamSynchronize(st));
+        return VIO360_OK;
+    };
+    // iteration 0 (IterationZero, trust_region_minimizer.cc:181-224): cost at x0
+    LmState init;
+    memset(&init, 0, sizeof(init));
+    init.radius = opt->initial_trust_region_radius; init.decrease_factor = 2.0; init.step_successful = 1; init.step_valid = 1; init.relinearize = 1;
+    {
+        BaDev d = make_dev(ba);
+        KernelTimer kt_(ctx, "k_lm_cost");
+        k_lm_cost<<<nbo, 128, 0, st>>>(d, loss, part_cost);
+    }
+    VIO_LAUNCH_CHECK(ctx);
+    std::vector<double> h_part((size_t)nbo);
+    VIO_CUDA(ctx, cudaMemcpyAsync(h_part.data(), part_cost, (size_t)nbo * 8, cudaMemcpyDeviceToHost, st));
+    VIO_CUDA(ctx, cudaStreamSynchronize(st));
+    {   // the initial cost only enters comparisons with tolerances 1e-3 / 1e-6: summed on the host in index order
+        double c0 = 0.0;
+        for (int i = 0; i < nbo; ++i) c0 += h_part[i];
+        init.x_cost = c0;
+    }
+    VIO_CUDA(ctx, cudaMemcpyAsync(d_state, &init, sizeof(LmState), cudaMemcpyHostToDevice, st));
+    VIO_CUDA(ctx, cudaStreamSynchronize(st));      // `init` is a stack object
+    memset(summary, 0, sizeof(*summary));
+    summary->initial_cost = init.x_cost;
+    int n_trace = 0;
+    auto push_trace = [&](const LmState& s, double cost) {
+        if (!trace || n_trace >= trace_capacity) return;
+        double* t = trace + 8 * (size_t)n_trace++;
+        t[0] = cost; t[1] = s.cost_change; t[2] = s.gradient_max_norm; t[3] = s.step_norm; t[4] = s.relative_decrease;
+        t[5] = s.radius; t[6] = (double)(s.step_valid ? (s.step_successful ? 1 : 0) : -1); t[7] = s.model_cost_change;
+    };
+    bool first = true, relinearize = true;
+    int termination = 0;
+    LmState last = init;
+    for (;;) {
+        if (relinearize) {
+            // Evaluator::Evaluate with Jacobian at x: the Gauss-Newton blocks give the squared column norms and J'r
+            rc = run_blocks(ba, loss ? 1 : 0);
+            if (rc) return rc;
+            const double* Hpp = ba->d_blocks.as<double>(); const double* bp = Hpp + Ks * 36; const double* Hll = bp + Ks * 6; const double* bl = Hll + Ms * 9;
+            { KernelTimer kt_(ctx, "k_lm_linearized");
+            k_lm_linearized<<<1, kLmRedThreads, 0, st>>>(K, M, Hpp, bp, Hll, bl, ba->d_free_map.as<int>(), ba->d_point_fixed.as<unsigned char>(),
+                                                       ba->d_pose_delta.as<double>(), ba->d_points.as<double>(), ba->d_colsq.as<double>(),
+                                                       ba->d_scale.as<double>(), first ? 1 : 0, od.jacobi_scaling, d_state);
+            }
+            VIO_LAUNCH_CHECK(ctx);
+            if ((rc = read_state())) return rc;
+            last = *h_state;
+            if (first) push_trace(last, last.x_cost);
+            first = false; relinearize = false;
+            if (last.gradient_max_norm <= od.gradient_tolerance) { termination = 1; break; }   // GradientToleranceReached (:674-692)
+            if (last.termination != 0) { termination = last.termination; break; }
+        }
+        // ---- ComputeTrustRegionStep: LM diagonal, fused build of the reduced system, Cholesky, back substitution
+        { KernelTimer kt_(ctx, "k_lm_diagonal");
+        k_lm_diagonal<<<(nvar + 255) / 256, 256, 0, st>>>(nvar, ba->d_colsq.as<double>(), ba->d_scale.as<double>(), d_state, od.min_diag, od.max_diag, ba->d_D.as<double>());
+        }
+        VIO_LAUNCH_CHECK(ctx);
+        ba->use_D = true;
+        if ((rc = vio360_ba_build_reduced_system(ba, nullptr, loss ? 1 : 0, nullptr, nullptr, nullptr))) return rc;
+        if ((rc = solve_reduced_dev(ba, true))) return rc;
+        const int* d_status = reinterpret_cast<const int*>(ba->d_x.as<double>() + 6 * (size_t)ba->n_free);
+        { KernelTimer kt_(ctx, "k_lm_candidate");
+        k_lm_candidate<<<nbc, kLmRedThreads, 0, st>>>(K, M, ba->d_free_map.as<int>(), ba->d_point_fixed.as<unsigned char>(), ba->d_x.as<double>(),
+                                                     ba->d_dl.as<double>(), ba->d_pose_delta.as<double>(), ba->d_points.as<double>(), ba->d_step.as<double>(),
+                                                     ba->d_cand_pose_delta.as<double>(), ba->d_cand_points.as<double>(), part_step);
+        }
+        VIO_LAUNCH_CHECK(ctx);
+        k_pose_prepare<<<(K + 63) / 64, 64, 0, st>>>(K, ba->d_Twb.as<double>(), ba->d_Tcb.as<double>(), ba->d_cand_pose_delta.as<double>(), ba->d_cand_posebuf.as<double>());
+        VIO_LAUNCH_CHECK(ctx);
+        BaDev d = make_dev(ba);
+        { KernelTimer kt_(ctx, "k_lm_model_change");
+        k_lm_model_change<<<nbo, 128, 0, st>>>(d, loss, ba->d_step.as<double>(), part_model);
+        }
+        VIO_LAUNCH_CHECK(ctx);
+        BaDev dc = d;
+        dc.posebuf = ba->d_cand_posebuf.as<double>(); dc.points = ba->d_cand_points.as<double>();
+        { KernelTimer kt_(ctx, "k_lm_cost");
+        k_lm_cost<<<nbo, 128, 0, st>>>(dc, loss, part_cost);
+        }
+        VIO_LAUNCH_CHECK(ctx);
+        { KernelTimer kt_(ctx, "k_lm_decide");
+        k_lm_decide<<<1, kLmRedThreads, 0, st>>>(part_step, nbc, part_model, nbo, part_cost, nbo, d_status, od, opt->max_num_iterations, d_state, d_state + 1);
+        }
+        VIO_LAUNCH_CHECK(ctx);
+        if ((rc = read_state())) return rc;
+        last = *h_state;
+        push_trace(last, last.step_successful ? last.x_cost : last.candidate_cost);
+        if (last.step_successful) {   // x = candidate_x (HandleSuccessfulStep): swap the current and candidate buffers
+            std::swap(ba->d_pose_delta, ba->d_cand_pose_delta); std::swap(ba->d_points, ba->d_cand_points); std::swap(ba->d_posebuf, ba->d_cand_posebuf);
+            relinearize = true;
+        }
+        if (last.termination != 0) { termination = last.termination; break; }
+    }
+    // the reduced system / evaluation caches belong to an earlier point
+    ba->has_eval = false; ba->has_reduced = false; ba->has_params = true;
+    VIO_CUDA(ctx, cudaMemcpyAsync(pose_delta, ba->d_pose_delta.p, Ks * 6 * 8, cudaMemcpyDeviceToHost, st));
+    VIO_CUDA(ctx, cudaMemcpyAsync(points, ba->d_points.p, Ms * 3 * 8, cudaMemcpyDeviceToHost, st));
+    VIO_CUDA(ctx, cudaStreamSynchronize(st));
+    summary->iterations = last.iteration; summary->num_successful_steps = last.num_successful + 1;   // iteration 0 counts (Ceres)
+    summary->num_unsuccessful_steps = last.num_unsuccessful; summary->termination = termination;
+    summary->final_cost = last.x_cost; summary->final_radius = last.radius; summary->final_gradient_max_norm = last.gradient_max_norm;
+    summary->n_trace = n_trace;
+    if (termination == -1) return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_lm_solve: %d consecutive invalid steps (the reduced system is not positive definite or the model does not decrease)", last.num_invalid);
     return VIO360_OK;
 }
 

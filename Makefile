@@ -11,7 +11,7 @@ all: $(LIB) oracle host hosttest
 
 $(CSRC)/ctx.o: $(CSRC)/ctx.cu $(CSRC)/common.cuh include/vio360.h
 	$(NVCC) $(NVFLAGS) -c $< -o $@
-$(CSRC)/ba.o: $(CSRC)/ba.cu $(CSRC)/ba_peer.cuh $(CSRC)/ba_math.cuh $(CSRC)/ba_schur.cuh $(CSRC)/ba_schur_kernels.cuh $(CSRC)/ba_solve.cuh $(CSRC)/ba_triangulate.cuh $(CSRC)/common.cuh include/vio360.h
+$(CSRC)/ba.o: $(CSRC)/ba.cu $(CSRC)/ba_peer.cuh $(CSRC)/ba_math.cuh $(CSRC)/ba_schur.cuh $(CSRC)/ba_schur_kernels.cuh $(CSRC)/ba_solve.cuh $(CSRC)/ba_lm.cuh $(CSRC)/ba_triangulate.cuh $(CSRC)/common.cuh include/vio360.h
 	$(NVCC) $(NVFLAGS) -c $< -o $@
 # --fmad=false: float expressions must round like OpenCV's non-FMA baseline code; the
 # places where OpenCV's dispatched code does fuse are explicit fmaf() calls.

@@ -341,6 +341,39 @@ int vio360_ba_column_sqnorm(vio360_ba* ba, int apply_loss, double* out);
  * With shards, all-reduce the packed system first; every rank then holds the same x.     */
 int vio360_ba_solve_reduced(vio360_ba* ba, double* delta_pose, double* delta_point);
 
+/* the whole Levenberg-Marquardt solve of Optimizer::RunLocalBA / RunBA
+ * (src/optimization/Optimizer.cpp:883-886: ceres::Solve with LEVENBERG_MARQUARDT, SPARSE_SCHUR, max 50
+ * iterations, HuberLoss) as ONE call on the device-resident window: per iteration the Jacobi-scaled LM diagonal
+ * (levenberg_marquardt_strategy.cc:78-89; trust_region_minimizer.cc:262-276), the fused build of the reduced
+ * camera system, its Cholesky solve and the landmark back substitution (schur_eliminator_impl.h:310-380), the
+ * step -y (:103-123), the model cost change (trust_region_minimizer.cc:430-441), the candidate cost, the
+ * parameter / function tolerance tests (:717-761), step acceptance and the radius update
+ * (:767-829; levenberg_marquardt_strategy.cc:148-161), gradient / radius / iteration termination (:302-356).
+ * Parameters, Jacobian blocks and systems never leave the device; one 128-byte state record per iteration does.
+ * Options mirror ceres::Solver::Options (include/ceres/solver.h defaults; vio360_lm_default_options fills them with
+ * what Optimizer::SetupSolverOptions leaves in place, Optimizer.cpp:73-81).  pose_delta (K x 6) and points (M x 3)
+ * are the start on entry and the solution on return.  trace (optional) receives 8 doubles per iteration, iteration
+ * 0 first: cost, cost_change, |gradient|_max, |step|, relative_decrease, radius, accepted (1 / 0 / -1 invalid),
+ * model_cost_change.  Follow with vio360_ba_chi2 for the outlier pass of Optimizer.cpp:898-915.                   */
+typedef struct {
+    int max_num_iterations;
+    double initial_trust_region_radius, max_trust_region_radius, min_trust_region_radius;
+    double min_relative_decrease, min_lm_diagonal, max_lm_diagonal;
+    double function_tolerance, gradient_tolerance, parameter_tolerance;
+    int jacobi_scaling, max_num_consecutive_invalid_steps;
+    int apply_loss;              /* HuberLoss as installed by vio360_ba_set_structure (Optimizer.cpp:835) */
+} vio360_lm_options;
+typedef struct {
+    int iterations, num_successful_steps, num_unsuccessful_steps;
+    int termination;             /* 1 gradient tolerance, 2 function tolerance, 3 parameter tolerance, 4 minimum trust
+                                    region radius (all four: ceres CONVERGENCE), 5 max iterations (NO_CONVERGENCE), -1 failure */
+    double initial_cost, final_cost, final_radius, final_gradient_max_norm;
+    int n_trace;
+} vio360_lm_summary;
+int vio360_lm_default_options(vio360_lm_options* opt);
+int vio360_ba_lm_solve(vio360_ba* ba, const vio360_lm_options* opt, double* pose_delta, double* points,
+                       vio360_lm_summary* summary, double* trace, int trace_capacity);
+
 /* Replaces the per-factor BAFactor::compute_chi_square loop (Factors.cpp:544-612;
  * Optimizer.cpp:898-915): chi2 O (may be NULL), flag O = chi2 > thr (may be NULL).   */
 int vio360_ba_chi2(vio360_ba* ba, double thr, double* chi2, uint8_t* flag);

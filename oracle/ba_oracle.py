@@ -152,6 +152,94 @@ class Window:
         lib().vo_lm_diagonal(C.byref(self.c), _d(Jp), _d(Jl), C.c_double(radius), _d(D))
         return D
 
+    def lm_solve(self, pose_delta, points, max_num_iterations=50, initial_radius=1e4, max_radius=1e16, min_radius=1e-32,
+                 min_relative_decrease=1e-3, min_diag=1e-6, max_diag=1e32, function_tolerance=1e-6,
+                 gradient_tolerance=1e-10, parameter_tolerance=1e-8, jacobi_scaling=True, max_invalid=5, apply_loss=True):
+        """ceres::Solve as Optimizer::RunLocalBA configures it (Optimizer.cpp:73-81, 883-886), restated:
+        TrustRegionMinimizer::Minimize (trust_region_minimizer.cc:67-139) with LevenbergMarquardtStrategy
+        (levenberg_marquardt_strategy.cc:66-161), monotonic steps (trust_region_step_evaluator.cc:52-67), Jacobi
+        scaling (trust_region_minimizer.cc:262-276), SPARSE_SCHUR = vo_schur_eliminate + LAPACK + BackSubstitute.
+        Parameter blocks are plain vectors (no LocalParameterization is attached, Optimizer.cpp:771-773).
+        returns (pose_delta, points, summary dict, trace list of per-iteration tuples)."""
+        K, M, O = self.c.K, self.c.M, self.c.O
+        x_p = np.array(pose_delta, np.float64).reshape(K, 6).copy(); x_l = np.array(points, np.float64).reshape(M, 3).copy()
+        pose_idx = np.ctypeslib.as_array(self.c.pose_idx, (O,)); point_idx = np.ctypeslib.as_array(self.c.point_idx, (O,))
+        free_p = self.keep["pose_fixed"] == 0; free_l = self.keep["point_fixed"] == 0
+
+        def linearize(xp, xl):
+            r, Jp, Jl, cost = self.evaluate(xp, xl, apply_loss=apply_loss)
+            cp = np.zeros((K, 6)); cl = np.zeros((M, 3)); gp = np.zeros((K, 6)); gl = np.zeros((M, 3))
+            np.add.at(cp, pose_idx, np.einsum("oia,oia->oa", Jp, Jp)); np.add.at(cl, point_idx, np.einsum("oia,oia->oa", Jl, Jl))
+            np.add.at(gp, pose_idx, np.einsum("oia,oi->oa", Jp, r)); np.add.at(gl, point_idx, np.einsum("oia,oi->oa", Jl, r))
+            cp[~free_p] = 0; cl[~free_l] = 0
+            gmax = max(np.abs(gp[free_p]).max() if free_p.any() else 0.0, np.abs(gl[free_l]).max() if free_l.any() else 0.0)
+            xnorm = np.sqrt((xp[free_p] ** 2).sum() + (xl[free_l] ** 2).sum())
+            return r, Jp, Jl, cost, np.concatenate([cp.reshape(-1), cl.reshape(-1)]), gmax, xnorm
+
+        r, Jp, Jl, x_cost, colsq, gmax, xnorm = linearize(x_p, x_l)
+        scale = 1.0 / (1.0 + np.sqrt(colsq)) if jacobi_scaling else np.ones_like(colsq)
+        radius, decrease = initial_radius, 2.0
+        it = n_ok = n_bad = n_invalid = 0
+        termination = 0
+        trace = [(x_cost, 0.0, gmax, 0.0, 0.0, radius, 1, 0.0)]
+        initial_cost = x_cost
+        n_ok = 1
+        if gmax <= gradient_tolerance:
+            termination = 1
+        while termination == 0:
+            it += 1
+            D = np.sqrt(np.clip(colsq * scale * scale, min_diag, max_diag) / radius) / scale
+            S, rhs, fm = self.schur(r, Jp, Jl, D)
+            try:
+                np.linalg.cholesky(S)
+                dp, dl = self.solve_step(r, Jp, Jl, D, S, rhs, fm)
+                solver_ok = True
+            except np.linalg.LinAlgError:
+                dp = np.zeros((K, 6)); dl = np.zeros((M, 3)); solver_ok = False
+            sp, sl = -dp, -dl
+            sp[~free_p] = 0; sl[~free_l] = 0
+            Jd = np.einsum("oia,oa->oi", Jp, sp[pose_idx]) + np.einsum("oia,oa->oi", Jl, sl[point_idx])
+            model = float(-(Jd * (r + 0.5 * Jd)).sum())
+            step_norm = float(np.sqrt((sp ** 2).sum() + (sl ** 2).sum()))
+            valid = solver_ok and model > 0.0
+            accepted, rel, cost_change, cand_cost = 0, 0.0, 0.0, 0.0
+            if not valid:
+                n_invalid += 1; n_bad += 1
+                if n_invalid >= max_invalid:
+                    termination = -1
+                else:
+                    radius /= decrease; decrease *= 2.0
+                accepted = -1
+            else:
+                n_invalid = 0
+                cand_cost = self.evaluate(x_p + sp, x_l + sl, apply_loss=apply_loss, outputs=False)
+                cost_change = x_cost - cand_cost
+                if step_norm <= parameter_tolerance * (xnorm + parameter_tolerance):
+                    termination = 3
+                elif abs(cost_change) <= function_tolerance * x_cost:
+                    termination = 2
+                else:
+                    rel = cost_change / model
+                    if rel > min_relative_decrease:
+                        accepted = 1; n_ok += 1
+                        x_p = x_p + sp; x_l = x_l + sl
+                        r, Jp, Jl, x_cost, colsq, gmax, xnorm = linearize(x_p, x_l)
+                        radius = min(max_radius, radius / max(1.0 / 3.0, 1.0 - (2.0 * rel - 1.0) ** 3)); decrease = 2.0
+                    else:
+                        n_bad += 1
+                        radius /= decrease; decrease *= 2.0
+            trace.append((x_cost if accepted == 1 else cand_cost, cost_change, gmax, step_norm, rel, radius, accepted, model))
+            if termination == 0:
+                if it >= max_num_iterations:
+                    termination = 5
+                elif accepted == 1 and gmax <= gradient_tolerance:
+                    termination = 1
+                elif radius <= min_radius:
+                    termination = 4
+        summary = dict(iterations=it, num_successful_steps=n_ok, num_unsuccessful_steps=n_bad, termination=termination,
+                       initial_cost=initial_cost, final_cost=x_cost, final_radius=radius, final_gradient_max_norm=gmax)
+        return x_p, x_l, summary, trace
+
     def chi2(self, pose_delta, points, thr=5.991):
         O = self.c.O
         pd = np.ascontiguousarray(pose_delta, np.float64); pts = np.ascontiguousarray(points, np.float64)

@@ -440,3 +440,61 @@ def test_pnp(bindings, ctx, synthetic):
         assert np.allclose(out["r"][i], rr, rtol=TOL, atol=TOL * 100) and rel_err(out["Jp"][i], JJ) < TOL or not JJ.any()
         H += JJ.T @ JJ; b += JJ.T @ rr
     assert rel_err(out["H"], H) < TOL and rel_err(out["b"], b) < TOL and abs(out["cost"] - cost) < TOL * cost
+
+
+@pytest.mark.parametrize("K,M,degree,seed", [(10, 2000, None, 20000), (40, 4000, 12, 777)])
+def test_lm_solve_vs_oracle(bindings, ctx, synthetic, K, M, degree, seed):
+    """SURVEY 8-F rank 3 / 7.3-8: the device LM loop (vio360_ba_lm_solve) against the restated ceres::Solve of
+    Optimizer::RunLocalBA (oracle Window.lm_solve: TrustRegionMinimizer + LevenbergMarquardtStrategy + Jacobi
+    scaling + Schur + LAPACK) on config C3 and on a 40-keyframe co-visibility window: the same accept / reject
+    sequence, the same termination, per-iteration cost and radius, final cost to 1e-9 and final parameters to
+    1e-7 (relative to the largest parameter), then the chi-square outlier pass of Optimizer.cpp:898-915."""
+    win = synthetic.make_ba_window(K=K, M=M, degree=degree, seed=seed, mid_iteration=True, loop_radius=1.0 if degree is None else 4.0)
+    W = ba_oracle.Window(win)
+    xp, xl, sm, tr = W.lm_solve(win["pose_delta"], win["points"])
+    ba = bindings.BAWindow(ctx, win)
+    gp, gl, gs, gt = ba.lm_solve(win["pose_delta"], win["points"])
+    tr = np.array(tr)
+    assert gs["termination"] == sm["termination"] and gs["iterations"] == sm["iterations"]
+    assert gs["num_successful_steps"] == sm["num_successful_steps"] and gs["num_unsuccessful_steps"] == sm["num_unsuccessful_steps"]
+    assert len(gt) == len(tr) and np.array_equal(gt[:, 6], tr[:, 6])                      # accept / reject / invalid sequence
+    assert np.allclose(gt[:, 0], tr[:, 0], rtol=1e-9) and np.allclose(gt[:, 5], tr[:, 5], rtol=1e-6)   # cost, radius
+    assert abs(gs["final_cost"] - sm["final_cost"]) < 1e-9 * sm["final_cost"]
+    assert abs(gs["initial_cost"] - sm["initial_cost"]) < 1e-9 * sm["initial_cost"]
+    assert sm["final_cost"] < 0.6 * sm["initial_cost"] and sm["iterations"] >= 3
+    scale_p = max(np.abs(xp).max(), 1e-3); scale_l = np.abs(xl).max()
+    assert np.abs(gp - xp).max() / scale_p < 1e-7 and np.abs(gl - xl).max() / scale_l < 1e-7
+    assert not gp[0].any()                                                                # pose 0 is constant
+    fixed = win["point_fixed"] != 0
+    assert np.array_equal(gl[fixed], win["points"][fixed])
+    # the window object now sits at the solution: the chi-square pass of Optimizer.cpp:898-915 on the device
+    chi2, flag = ba.chi2(5.991)
+    c2, f2 = W.chi2(xp, xl, 5.991)
+    band = np.abs(c2 - 5.991) > 1e-5
+    assert np.allclose(chi2, c2, rtol=1e-6, atol=1e-7) and np.array_equal(flag[band], f2[band])
+    # options: no Jacobi scaling, a small radius and two iterations -> max-iterations termination, same trace
+    xp2, xl2, sm2, tr2 = W.lm_solve(win["pose_delta"], win["points"], max_num_iterations=2, initial_radius=10.0, jacobi_scaling=False)
+    gp2, gl2, gs2, gt2 = ba.lm_solve(win["pose_delta"], win["points"], max_num_iterations=2, initial_trust_region_radius=10.0, jacobi_scaling=0)
+    assert gs2["termination"] == sm2["termination"] == 5 and np.array_equal(gt2[:, 6], np.array(tr2)[:, 6])
+    assert np.abs(gp2 - xp2).max() / scale_p < 1e-8 and abs(gs2["final_cost"] - sm2["final_cost"]) < 1e-9 * sm2["final_cost"]
+    ba.close()
+
+
+def test_lm_solve_rejected_steps(bindings, ctx, synthetic):
+    """A start far from the optimum, no loss function and a huge initial radius: the 100-pixel clamp of
+    BAFactor::Evaluate (Factors.cpp:424-441) makes the model over-predict, steps are REJECTED and the radius shrinks by
+    2, 4, 8, ... (levenberg_marquardt_strategy.cc:156-160) until one is accepted again -- the same sequence on both sides."""
+    win = synthetic.make_ba_window(K=10, M=600, seed=5, mid_iteration=True)
+    rng = np.random.default_rng(1)
+    pd = win["pose_delta"] + rng.normal(0, 0.05, win["pose_delta"].shape); pd[0] = 0
+    W = ba_oracle.Window(win)
+    xp, xl, sm, tr = W.lm_solve(pd, win["points"], initial_radius=1e10, apply_loss=False, max_num_iterations=15)
+    tr = np.array(tr)
+    assert (tr[:, 6] == 0).sum() >= 3 and (tr[1:, 6] == 1).sum() >= 3
+    ba = bindings.BAWindow(ctx, win)
+    gp, gl, gs, gt = ba.lm_solve(pd, win["points"], initial_trust_region_radius=1e10, apply_loss=0, max_num_iterations=15)
+    assert np.array_equal(gt[:, 6], tr[:, 6]) and gs["termination"] == sm["termination"] and gs["iterations"] == sm["iterations"]
+    assert np.allclose(gt[:, 5], tr[:, 5], rtol=1e-6) and np.allclose(gt[:, 0], tr[:, 0], rtol=1e-8)
+    assert abs(gs["final_cost"] - sm["final_cost"]) < 1e-8 * sm["final_cost"]
+    assert np.abs(gp - xp).max() < 1e-6 * max(np.abs(xp).max(), 1e-3) and np.abs(gl - xl).max() < 1e-6 * np.abs(xl).max()
+    ba.close()
