@@ -1729,6 +1729,30 @@ extern "C" int vio360_ba_lm_solve(vio360_ba* ba, const vio360_lm_options* opt, d
     return VIO360_OK;
 }
 
+// y += J x at the current parameters (see k_jacobian_right_multiply): what a ceres::internal::SparseMatrix standing for
+// the device-resident Jacobian answers to RightMultiply (host/ceres_adapters).
+extern "C" int vio360_ba_jacobian_right_multiply(vio360_ba* ba, int apply_loss, const double* x, double* y) {
+    if (!ba || !x || !y) return VIO360_ERR_INVALID;
+    vio360_ctx* ctx = ba->ctx;
+    if (!ba->has_params) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_jacobian_right_multiply before ba_set_parameters");
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t nv = 6 * (size_t)ba->K + 3 * (size_t)ba->M, O = (size_t)ba->O;
+    if (O == 0) return VIO360_OK;
+    cudaStream_t st = ctx->stream;
+    VIO_CUDA(ctx, cudaStreamSynchronize(st));
+    VIO_CUDA(ctx, ba->d_step.reserve(nv * 8)); VIO_CUDA(ctx, ba->d_r.reserve(O * 16));
+    VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_step.p, x, nv * 8, cudaMemcpyHostToDevice, st));
+    VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_r.p, y, O * 16, cudaMemcpyHostToDevice, st));
+    ba->has_eval = false;   // d_r is borrowed
+    { KernelTimer kt_(ctx, "k_jacobian_right_multiply");
+    k_jacobian_right_multiply<<<(int)((O + 127) / 128), 128, 0, st>>>(make_dev(ba), apply_loss != 0, ba->d_step.as<double>(), ba->d_r.as<double>());
+    }
+    VIO_LAUNCH_CHECK(ctx);
+    VIO_CUDA(ctx, cudaMemcpyAsync(y, ba->d_r.p, O * 16, cudaMemcpyDeviceToHost, st));
+    VIO_CUDA(ctx, cudaStreamSynchronize(st));
+    return VIO360_OK;
+}
+
 // ---- batched DLT triangulation (Estimator.cpp:1082-1139) ----
 extern "C" int vio360_triangulate(vio360_ctx* ctx, const float* bearing1, const float* bearing2, const float* T1w, const float* T2w, int n,
                                   float* points, uint8_t* valid) {

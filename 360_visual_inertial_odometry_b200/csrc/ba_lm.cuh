@@ -157,6 +157,31 @@ __global__ void __launch_bounds__(128) k_lm_model_change(BaDev d, bool apply_los
     block_sum_to(acc, partials);
 }
 
+// y += J x for the Ceres SparseMatrix adapter (LinearOperator::RightMultiply; used by the trust-region loop for the
+// model cost change): x is 6K + 3M (constant blocks ignored), y is O x 2 in the caller's observation order.
+__global__ void __launch_bounds__(128) k_jacobian_right_multiply(BaDev d, bool apply_loss, const double* __restrict__ x, double* __restrict__ y) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= d.O) return;
+    const int p = d.pose[i], l = d.point[i];
+    double pose[kPoseStride];
+#pragma unroll
+    for (int j = 0; j < kPoseStride; ++j) pose[j] = __ldg(d.posebuf + kPoseStride * (size_t)p + j);
+    const double Pw[3] = {__ldg(d.points + 3 * (size_t)l), __ldg(d.points + 3 * (size_t)l + 1), __ldg(d.points + 3 * (size_t)l + 2)};
+    double r[2], F[12], E[6];
+    obs_evaluate<true>(pose, Pw, d.u[i], d.v[i], d.outlier[i] != 0, d.cam, apply_loss, r, F, E);
+    double m0 = 0.0, m1 = 0.0;
+    if (d.free_map[p] >= 0) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) { m0 += F[k] * x[6 * (size_t)p + k]; m1 += F[6 + k] * x[6 * (size_t)p + k]; }
+    }
+    if (d.point_fixed[l] == 0) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { m0 += E[k] * x[6 * (size_t)d.K + 3 * (size_t)l + k]; m1 += E[3 + k] * x[6 * (size_t)d.K + 3 * (size_t)l + k]; }
+    }
+    const size_t o = (size_t)d.orig[i];
+    y[2 * o] += m0; y[2 * o + 1] += m1;
+}
+
 // cost of the candidate point (Evaluator::Evaluate with residuals / jacobian null): partial sums per CTA
 __global__ void __launch_bounds__(128) k_lm_cost(BaDev d, bool apply_loss, double* __restrict__ partials) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;

@@ -21,10 +21,46 @@ FeatureTrackerCuda::FeatureTrackerCuda(int width, int height, int max_features, 
     ensure_capacity(max_features > 0 ? max_features : 1);
 }
 
-FeatureTrackerCuda::~FeatureTrackerCuda() { vio360_destroy(m_ctx); }
+FeatureTrackerCuda::~FeatureTrackerCuda() {
+    if (m_seq) vio360_seq_destroy(m_seq);
+    delete m_seq_rng;
+    vio360_destroy(m_ctx);
+}
+
+void FeatureTrackerCuda::ResetSequence() {
+    if (m_seq) { vio360_seq_destroy(m_seq); m_seq = nullptr; }
+}
+
+void FeatureTrackerCuda::TrackFeatures(const cv::Mat& image, FrameFeatures& out) {
+    if (image.empty() || image.cols != m_width || image.rows != m_height)
+        throw std::runtime_error("FeatureTrackerCuda::TrackFeatures: image must be 8-bit single channel of the configured size");
+    ensure_capacity(2 * std::max(m_max_features, 1));      // may re-configure: only before the sequence exists
+    if (!m_seq) {
+        vio360_seq_config cfg;
+        cfg.max_features = m_max_features; cfg.min_distance = m_min_distance; cfg.quality_level = m_quality_level;
+        cfg.grid_cols = m_grid_cols; cfg.grid_rows = m_grid_rows; cfg.max_features_per_grid = m_grid_cap;
+        cfg.remove_clustered = m_cluster ? 1 : 0; cfg.clustered_std_ratio = m_cluster_ratio;
+        cfg.ransac_iterations = m_ransac_max_iterations; cfg.ransac_threshold_deg = m_ransac_threshold;
+        check(vio360_seq_create(m_ctx, &cfg, &m_seq), "vio360_seq_create");
+    }
+    if (!m_seq_rng) { std::random_device rd; m_seq_rng = new std::mt19937(m_ransac_seeded ? m_ransac_seed : rd()); }   // FeatureTracker.cpp:273-274
+    std::vector<uint32_t> words((size_t)std::max(m_ransac_max_iterations, 1) * 3);
+    for (uint32_t& w : words) w = (uint32_t)(*m_seq_rng)();
+    const int cap = vio360_seq_capacity(m_seq);
+    out.ids.resize((size_t)cap); out.points.resize((size_t)cap); out.track_counts.resize((size_t)cap);
+    int n = 0;
+    vio360_frame_job job;
+    job.seq = m_seq; job.image = image.data; job.pitch = (size_t)image.step; job.ransac_words = words.data();
+    job.ids = out.ids.data(); job.xy = reinterpret_cast<float*>(out.points.data()); job.track_count = out.track_counts.data();
+    job.n_features = &n; job.n_tracked = &out.num_tracked; job.n_detected = &out.num_detected;
+    check(vio360_fe_track_frame_batch(m_ctx, &job, 1, VIO360_MEM_HOST), "vio360_fe_track_frame_batch");
+    out.ids.resize((size_t)n); out.points.resize((size_t)n); out.track_counts.resize((size_t)n);
+    m_num_tracked = out.num_tracked; m_num_detected = out.num_detected;
+}
 
 void FeatureTrackerCuda::ensure_capacity(int n_points) {
     if (n_points <= m_point_capacity) return;
+    ResetSequence();                 // vio360_fe_configure invalidates the device-resident sequence
     m_point_capacity = n_points;
     // FeatureTracker.cpp:33-35: window 21x21, maxLevel 3, TermCriteria(EPS|COUNT, 30, 0.01f); the float
     // epsilon widens to double and doubles as minEigThreshold (:240).  Polar ratio 0.15 (Camera.h:76,84).

@@ -15,6 +15,7 @@
 
 #include <cstdint>
 #include <memory>
+#include <random>
 #include <string>
 #include <vector>
 
@@ -64,6 +65,24 @@ public:
     // survive the per-cell cap (highest track counts first, ties in feature order).
     std::vector<uchar> LimitFeaturesPerGrid(const std::vector<cv::Point2f>& points, const std::vector<int>& track_counts,
                                             int max_features_per_grid = 4, int grid_cols = 20, int grid_rows = 10);
+    // FeatureTracker::TrackFeatures (FeatureTracker.cpp:61-206) for the consecutive frames of one sequence as ONE
+    // device-resident call per frame (vio360_fe_track_frame_batch): tracking, post filter, rotation RANSAC, clustered
+    // cell removal, grid cap, re-detection under the occupancy mask, second grid cap.  The feature list lives on
+    // the device between the frames; what comes back is what Frame::GetFeatures() would hold: ids (carried from the
+    // previous frame or fresh from m_next_feature_id), pixel coordinates, track counts, in the reference's order.
+    // The shared_ptr<Feature> / observation bookkeeping (:139-163) stays with the caller.  The first call (or the
+    // first after ResetSequence) is the "no previous frame" branch (:68-92).
+    struct FrameFeatures {
+        std::vector<int> ids; std::vector<cv::Point2f> points; std::vector<int> track_counts;
+        int num_tracked = 0, num_detected = 0;
+    };
+    void TrackFeatures(const cv::Mat& image, FrameFeatures& out);
+    void ResetSequence();
+    // Frame::SetGridParameters (Estimator.cpp:572-576) and the ConfigUtils switches RemoveClusteredFeatures reads
+    // (FeatureTracker.cpp:407-423); call before the first TrackFeatures.  Defaults: default_config.yaml.
+    void SetGridParameters(int grid_cols, int grid_rows, int max_features_per_grid) { m_grid_cols = grid_cols; m_grid_rows = grid_rows; m_grid_cap = max_features_per_grid; ResetSequence(); }
+    void SetClusterRemoval(bool enabled, float std_ratio) { m_cluster = enabled; m_cluster_ratio = std_ratio; ResetSequence(); }
+
     // The post filter of TrackFeatures (FeatureTracker.cpp:118-126) computed on the device
     // during the last TrackOpticalFlow call: status && !polar && !near-boundary.
     const std::vector<uchar>& LastKeepMask() const { return m_keep; }
@@ -92,6 +111,10 @@ private:
     uint32_t m_ransac_seed = 0;
     bool m_ransac_seeded = false;
     std::vector<uchar> m_keep;
+    vio360_seq* m_seq = nullptr;
+    int m_grid_cols = 20, m_grid_rows = 10, m_grid_cap = 10;   // default_config.yaml:14-16
+    bool m_cluster = true; float m_cluster_ratio = 0.25f;      // default_config.yaml:52-54
+    std::mt19937* m_seq_rng = nullptr;
     void ensure_capacity(int n_points);
 };
 

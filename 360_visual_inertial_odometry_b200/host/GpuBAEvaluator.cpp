@@ -80,6 +80,8 @@ void GpuBAEvaluator::PrepareForEvaluation(bool evaluate_jacobians, bool new_eval
                                             evaluate_jacobians ? m_Jl.data() : nullptr),
           "vio360_ba_get_residuals_jacobians");
     m_have_jacobians = evaluate_jacobians;
+    m_eval_pose = m_params_pose; m_eval_point = m_params_point;
+    m_eval_valid = true;
 }
 
 int GpuBAEvaluator::ReducedDim() const { return vio360_ba_reduced_dim(m_ba); }
@@ -95,12 +97,40 @@ void GpuBAEvaluator::ComputeChiSquare(double threshold, std::vector<double>& chi
     chi2.resize((size_t)NumFactors()); outlier_flags.resize((size_t)NumFactors());
     check(vio360_ba_chi2(m_ba, threshold, chi2.data(), outlier_flags.data()), "vio360_ba_chi2");
     m_chi2 = chi2;
+    m_chi2_pose = m_params_pose; m_chi2_point = m_params_point;
+}
+
+vio360_lm_summary GpuBAEvaluator::SolveLM(const vio360_lm_options* opt) {
+    if (!m_finalized) throw std::runtime_error("GpuBAEvaluator::SolveLM before Finalize");
+    vio360_lm_options def;
+    if (!opt) { check(vio360_lm_default_options(&def), "vio360_lm_default_options"); opt = &def; }
+    for (size_t k = 0; k < m_pose_ptrs.size(); ++k) std::memcpy(&m_params_pose[6 * k], m_pose_ptrs[k], 6 * sizeof(double));
+    for (size_t j = 0; j < m_point_ptrs.size(); ++j) std::memcpy(&m_params_point[3 * j], m_point_ptrs[j], 3 * sizeof(double));
+    if (m_outliers_dirty) { check(vio360_ba_set_outliers(m_ba, m_outlier.data()), "vio360_ba_set_outliers"); m_outliers_dirty = false; }
+    vio360_lm_summary sm;
+    check(vio360_ba_lm_solve(m_ba, opt, m_params_pose.data(), m_params_point.data(), &sm, nullptr, 0), "vio360_ba_lm_solve");
+    // ceres::Solve leaves the solution in the user's parameter blocks (constant blocks unchanged: their step is zero)
+    for (size_t k = 0; k < m_pose_ptrs.size(); ++k) std::memcpy(m_pose_ptrs[k], &m_params_pose[6 * k], 6 * sizeof(double));
+    for (size_t j = 0; j < m_point_ptrs.size(); ++j) std::memcpy(m_point_ptrs[j], &m_params_point[3 * j], 3 * sizeof(double));
+    m_have_jacobians = false;   // cached r / J belong to an earlier point
+    m_r.assign(m_r.size(), 0.0);
+    m_eval_valid = false;
+    return sm;
 }
 
 // ------------------------------------------------------------------ the per-block facade
-bool GpuBackedBAFactor::Evaluate(double const* const* /*parameters*/, double* residuals, double** jacobians) const {
+// The rows served are those of the point the last PrepareForEvaluation uploaded.  Ceres passes pointers into ITS state
+// vector (ResidualBlock::Evaluate, residual_block.cc:81-88), so the check is by value: a caller that evaluates the factor
+// at another point (Problem::Evaluate elsewhere, a gradient checker, the reference's post-solve loops with explicit
+// pointers, Optimizer.cpp:220,432,662,906) gets an exception instead of stale numbers.
+bool GpuBackedBAFactor::Evaluate(double const* const* parameters, double* residuals, double** jacobians) const {
     const GpuBAEvaluator& e = *m_owner;
     const size_t i = (size_t)m_index;
+    if (!e.m_eval_valid) throw std::runtime_error("GpuBackedBAFactor::Evaluate: no evaluation point uploaded (register the GpuBAEvaluator as Problem::Options::evaluation_callback)");
+    if (parameters && parameters[0] && parameters[1] &&
+        (std::memcmp(parameters[0], &e.m_eval_pose[6 * (size_t)e.m_pose_idx[i]], 6 * sizeof(double)) != 0 ||
+         std::memcmp(parameters[1], &e.m_eval_point[3 * (size_t)e.m_point_idx[i]], 3 * sizeof(double)) != 0))
+        throw std::runtime_error("GpuBackedBAFactor::Evaluate: called at a point other than the one GpuBAEvaluator::PrepareForEvaluation uploaded");
     residuals[0] = e.m_r[2 * i]; residuals[1] = e.m_r[2 * i + 1];
     if (jacobians) {
         if (jacobians[0]) std::memcpy(jacobians[0], &e.m_Jp[12 * i], 12 * sizeof(double));
@@ -109,10 +139,16 @@ bool GpuBackedBAFactor::Evaluate(double const* const* /*parameters*/, double* re
     return true;   // BAFactor::Evaluate returns true on every branch (Factors.cpp:327-542)
 }
 
-double GpuBackedBAFactor::compute_chi_square(double const* const* /*parameters*/) const {
+double GpuBackedBAFactor::compute_chi_square(double const* const* parameters) const {
     // served from the batch computed by GpuBAEvaluator::ComputeChiSquare (one kernel for all factors)
-    if (m_owner->m_chi2.size() != (size_t)m_owner->NumFactors())
+    const GpuBAEvaluator& e = *m_owner;
+    const size_t i = (size_t)m_index;
+    if (e.m_chi2.size() != (size_t)e.NumFactors())
         throw std::runtime_error("GpuBackedBAFactor::compute_chi_square: call GpuBAEvaluator::ComputeChiSquare first");
+    if (parameters && parameters[0] && parameters[1] &&
+        (std::memcmp(parameters[0], &e.m_chi2_pose[6 * (size_t)e.m_pose_idx[i]], 6 * sizeof(double)) != 0 ||
+         std::memcmp(parameters[1], &e.m_chi2_point[3 * (size_t)e.m_point_idx[i]], 3 * sizeof(double)) != 0))
+        throw std::runtime_error("GpuBackedBAFactor::compute_chi_square: the parameters differ from the point GpuBAEvaluator::ComputeChiSquare used");
     return m_owner->m_chi2[(size_t)m_index];
 }
 

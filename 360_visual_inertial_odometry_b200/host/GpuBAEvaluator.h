@@ -94,6 +94,12 @@ public:
     void BuildReducedSystem(const double* lm_diag, double* S, double* rhs, double* cost);
     // per-factor chi-square at the current parameter values (Optimizer.cpp:898-915)
     void ComputeChiSquare(double threshold, std::vector<double>& chi2, std::vector<uint8_t>& outlier_flags);
+    // Drop-in for `ceres::Solve(options, &problem, &summary)` at Optimizer.cpp:883-886 when the window's factors are
+    // all BAFactors: the Levenberg-Marquardt iteration Ceres would run (trust_region_minimizer.cc,
+    // levenberg_marquardt_strategy.cc, SPARSE_SCHUR) executed on the device by vio360_ba_lm_solve, starting at the
+    // values in the user's parameter blocks and writing the solution back into them.  opt == nullptr: the options
+    // Optimizer::SetupSolverOptions leaves in place (vio360_lm_default_options).
+    vio360_lm_summary SolveLM(const vio360_lm_options* opt = nullptr);
 
     int NumFactors() const { return (int)m_pose_idx.size(); }
 
@@ -108,9 +114,11 @@ private:
     std::vector<double> m_Twb_init, m_obs_u, m_obs_v;
     std::vector<int32_t> m_pose_idx, m_point_idx;
     std::vector<uint8_t> m_pose_fixed, m_point_fixed, m_outlier;
-    bool m_outliers_dirty = false, m_have_jacobians = false, m_finalized = false;
+    bool m_outliers_dirty = false, m_have_jacobians = false, m_finalized = false, m_eval_valid = false;
     std::vector<double> m_params_pose, m_params_point;   // gathered evaluation point
     std::vector<double> m_r, m_Jp, m_Jl, m_chi2;          // results served to the factors
+    std::vector<double> m_chi2_pose, m_chi2_point;        // the point m_chi2 was computed at
+    std::vector<double> m_eval_pose, m_eval_point;        // the point m_r / m_Jp / m_Jl were computed at
     std::vector<uint8_t> m_flags;
 };
 

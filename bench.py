@@ -298,6 +298,7 @@ def run_ours(args):
     if not args.skip_detect:
         line["detect"] = bench_detect(ctx, b, torch, ring, B, world, device, barrier, stream)
         line["ransac"] = bench_ransac(ctx, syn)
+        line["sequence_chain"] = bench_sequence(ctx, b, syn, torch, device, barrier, args, rank)
     # ---- BA factor evaluation
     if not args.skip_ba:
         line["ba"] = bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, args)
@@ -390,6 +391,86 @@ def bench_c4(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
             "tracked_points_last_step": int(tracked.item()),
             "roofline": {"bound": "hbm", "algorithmic_bytes_per_frame": frame_bytes, "achieved": fps / world * frame_bytes / 1e9,
                          "peak": hbm_peak, "unit": "GB/s", "frac": fps / world * frame_bytes / 1e9 / hbm_peak}}
+
+
+def bench_sequence(ctx, b, syn, torch, device, barrier, args, rank):
+    """BASELINE configs[0], headless: FeatureTracker::TrackFeatures (FeatureTracker.cpp:61-206) frame after frame at 1920x960 with
+    default_config.yaml's detector settings, as ONE device-resident call per frame and batch of sequences
+    (vio360_fe_track_frame_batch: track -> post filter -> rotation RANSAC -> cluster removal -> grid cap -> masked
+    re-detection -> grid cap), host frames in, final feature lists out.  Beside it the same chain on the host cores:
+    cv2 for the two OpenCV calls + the C restatement of the reference's list logic."""
+    Ws, Hs, S, T = 1920, 960, 16, 10
+    ctx.fe_configure(Ws, Hs, max_points=2000, max_batch=S)
+    frames = [[syn.render_erp_frame(Ws, Hs, t, seed=360 + rank * S + q, n_waves=24, sigma_omega=60.0, xp=torch, device=device) for t in range(T)]
+              for q in range(S)]
+    hframes = [[f.cpu().pin_memory() for f in fs] for fs in frames]
+    rng = np.random.default_rng(42)
+    words = torch.from_numpy(rng.integers(0, 2 ** 32, (T, S, 1000, 3), dtype=np.uint64).astype(np.uint32).view(np.int32)).pin_memory()
+    cfg = dict(max_features=1000, min_distance=30.0, quality=0.01, grid_cols=20, grid_rows=10, max_per_cell=10,
+               remove_clustered=True, std_ratio=0.25, ransac_iters=1000, ransac_thr_deg=2.0)
+    cap = 2000
+    ids = torch.zeros((S, cap), dtype=torch.int32).pin_memory(); xy = torch.zeros((S, cap, 2), dtype=torch.float32).pin_memory()
+    tc = torch.zeros((S, cap), dtype=torch.int32).pin_memory()
+    cnt = (C.c_int * (3 * S))()
+    out = {}
+    for space, name in ((b.MEM_HOST, "host_frames"), (b.MEM_DEVICE, "device_frames")):
+        seqs = [ctx.seq_create(**cfg) for _ in range(S)]
+        if space == b.MEM_DEVICE:
+            d_ids = torch.zeros((S, cap), dtype=torch.int32, device=device); d_xy = torch.zeros((S, cap, 2), dtype=torch.float32, device=device)
+            d_tc = torch.zeros((S, cap), dtype=torch.int32, device=device); d_words = words.to(device)
+        jobs = (b.FrameJob * S)()
+
+        def step(t):
+            for q in range(S):
+                j = jobs[q]
+                j.seq = seqs[q]; j.pitch = Ws
+                if space == b.MEM_HOST:
+                    j.image, j.ransac_words = hframes[q][t].data_ptr(), words[t, q].data_ptr()
+                    j.ids, j.xy, j.track_count = ids[q].data_ptr(), xy[q].data_ptr(), tc[q].data_ptr()
+                else:
+                    j.image, j.ransac_words = frames[q][t].data_ptr(), d_words[t, q].data_ptr()
+                    j.ids, j.xy, j.track_count = d_ids[q].data_ptr(), d_xy[q].data_ptr(), d_tc[q].data_ptr()
+                j.n_features, j.n_tracked, j.n_detected = C.addressof(cnt) + 12 * q, C.addressof(cnt) + 12 * q + 4, C.addressof(cnt) + 12 * q + 8
+            ctx.fe_track_frame_batch_raw(jobs, S, space)
+
+        step(0); step(1)
+        barrier()
+        l0 = ctx.launch_count
+        t0 = time.perf_counter()
+        for t in range(2, T):
+            step(t)
+        barrier()
+        dt = time.perf_counter() - t0
+        n_feat = [cnt[3 * q] for q in range(S)]; n_trk = [cnt[3 * q + 1] for q in range(S)]
+        out[name] = {"value": S * (T - 2) / dt, "unit": "frames/s", "ms_per_frame_batch": dt / (T - 2) * 1e3, "sequences": S,
+                     "frames_timed": T - 2, "gpu_launches_per_call": (ctx.launch_count - l0) / (T - 2),
+                     "features_last_frame_mean": float(np.mean(n_feat)), "tracked_last_frame_mean": float(np.mean(n_trk))}
+        if space == b.MEM_HOST:
+            last = (ids[0, :cnt[0]].numpy().copy(), xy[0, :cnt[0]].numpy().copy(), tc[0, :cnt[0]].numpy().copy())
+            out[name]["h2d_bytes_per_call"] = S * (Ws * Hs + 12000); out[name]["d2h_bytes_per_call"] = S * (16 * cap + 80)
+        for h in seqs:
+            ctx.seq_destroy(h)
+    res = {"metric": "TrackFeatures chain frames/s @1920x960 (configs[0] headless): track + filter + RANSAC + cluster + grid cap + re-detect",
+           "value": out["host_frames"]["value"], "unit": "frames/s", **out}
+    if rank == 0 and not args.skip_cpu:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import fe_oracle
+        ref = fe_oracle.SequenceTracker(Ws, Hs, max_features=1000, min_distance=30.0, quality=0.01, max_per_cell=10, use_cv2=True)
+        f0 = [hframes[0][t].numpy() for t in range(T)]
+        w0 = words[:, 0].numpy().view(np.uint32)
+        ref.step(f0[0], w0[0]); ref.step(f0[1], w0[1])
+        t0 = time.perf_counter()
+        for t in range(2, T):
+            ref.step(f0[t], w0[t])
+        dtc = time.perf_counter() - t0
+        import cv2
+        res["cpu_baseline"] = {"value": (T - 2) / dtc, "unit": "frames/s", "cores": int(cv2.getNumThreads()), "kind": "reference",
+                               "sample": "%d frames of one sequence: cv2.calcOpticalFlowPyrLK + cv2.goodFeaturesToTrack %s with the reference's arguments, the reference's list logic restated in C (oracle/fe_ref.c)" % (T - 2, cv2.__version__)}
+        gi, gx, gt = last
+        res["parity"] = {"sequence": 0, "frame": T - 1, "ids_equal": bool(np.array_equal(gi, ref.ids)), "track_counts_equal": bool(np.array_equal(gt, ref.tc)),
+                         "max_abs_dxy_px": float(np.abs(gx - ref.xy).max()) if gx.shape == ref.xy.shape and len(gx) else None,
+                         "features": int(len(gi)), "tolerance_px": 0.05}
+    return res
 
 
 def bench_ransac(ctx, syn):
@@ -600,6 +681,27 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
             out["e2e_lm_step"] = {"ms_per_step_host_clock": lm_s * 1e3, "value": win["O"] / lm_s, "unit": "obs/s",
                                   "h2d_bytes_per_step": int(8 * (6 * win["K"] + 3 * win["M"])),
                                   "d2h_bytes_per_step": int(8 * (6 * win["K"] + 3 * win["M"]))}
+            # the whole ceres::Solve of Optimizer::RunLocalBA as one device-resident call (vio360_ba_lm_solve)
+            ba.lm_solve(win["pose_delta"], win["points"])
+            t0 = time.perf_counter()
+            gp, gl, sm, tr = ba.lm_solve(win["pose_delta"], win["points"])
+            lm_total = time.perf_counter() - t0
+            evals = (sm["iterations"] + sm["num_successful_steps"]) * win["O"]      # one candidate cost per iteration + one linearisation per accepted step
+            out["e2e_lm_solve"] = {"ms_host_clock": lm_total * 1e3, "iterations": sm["iterations"], "successful_steps": sm["num_successful_steps"],
+                                   "termination": sm["termination"], "initial_cost": sm["initial_cost"], "final_cost": sm["final_cost"],
+                                   "ms_per_iteration": lm_total * 1e3 / max(sm["iterations"], 1), "factor_evals_per_s": evals / lm_total,
+                                   "h2d_bytes": int(8 * (6 * win["K"] + 3 * win["M"])), "d2h_bytes": int(8 * (6 * win["K"] + 3 * win["M"]) + 128 * (sm["iterations"] + sm["num_successful_steps"]))}
+            if rank == 0 and not args.skip_cpu and win["O"] <= 50000:
+                # the restated ceres::Solve on the host (oracle, numpy + C): same iteration count, accept/reject sequence and final cost
+                sys.path.insert(0, os.path.join(ROOT, "oracle"))
+                import ba_oracle
+                t0 = time.perf_counter()
+                xp, xl, osm, otr = ba_oracle.Window(win).lm_solve(win["pose_delta"], win["points"])
+                o_s = time.perf_counter() - t0
+                out["e2e_lm_solve"]["oracle"] = {"ms": o_s * 1e3, "kind": "port (numpy + C restatement, 1 thread)", "iterations": osm["iterations"], "final_cost": osm["final_cost"],
+                                                 "same_accept_reject_sequence": bool(len(tr) == len(otr) and all(int(a[6]) == int(b_[6]) for a, b_ in zip(tr, otr))),
+                                                 "final_cost_rel_diff": abs(sm["final_cost"] - osm["final_cost"]) / osm["final_cost"],
+                                                 "max_param_diff": float(max(np.abs(gp - xp).max(), np.abs(gl - xl).max()))}
         if peer:
             barrier()
             ba.peer_detach()

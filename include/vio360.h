@@ -374,6 +374,12 @@ int vio360_lm_default_options(vio360_lm_options* opt);
 int vio360_ba_lm_solve(vio360_ba* ba, const vio360_lm_options* opt, double* pose_delta, double* points,
                        vio360_lm_summary* summary, double* trace, int trace_capacity);
 
+/* y += J x at the current parameters, J = the (loss-corrected when apply_loss) Jacobian of all residual blocks with the
+ * columns of constant blocks removed: x is 6K + 3M (pose part first), y is O x 2 in the caller's observation order.
+ * LinearOperator::RightMultiply (internal/ceres/linear_operator.h:46) for the SparseMatrix stand-in of
+ * host/ceres_adapters -- the Jacobian itself is never materialised.                                            */
+int vio360_ba_jacobian_right_multiply(vio360_ba* ba, int apply_loss, const double* x, double* y);
+
 /* Replaces the per-factor BAFactor::compute_chi_square loop (Factors.cpp:544-612;
  * Optimizer.cpp:898-915): chi2 O (may be NULL), flag O = chi2 > thr (may be NULL).   */
 int vio360_ba_chi2(vio360_ba* ba, double thr, double* chi2, uint8_t* flag);

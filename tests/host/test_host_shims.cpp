@@ -5,6 +5,8 @@
 //     correction applied by the caller (residual_block.cc:161-195)
 //   * FeatureTracker::DetectNewFeatures / TrackOpticalFlow on cv::Mat-shaped inputs
 // and compares with the oracle.  Prints HOST_SHIM_TEST PASS on success.
+#include <array>
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -154,6 +156,32 @@ static void test_ba() {
             ++checked;
         }
     EXPECT(checked == n_out && n_out > 0, "outlier count %d %d", checked, n_out);
+    // a factor evaluated at a point other than the uploaded one must not serve stale rows
+    {
+        double moved[6]; std::memcpy(moved, pose_params[fp[1]].data(), 48); moved[0] += 1e-3;
+        const double* params[2] = {moved, point_params[fl[1]].data()};
+        double rr[2]; bool threw = false;
+        try { factors[1]->Evaluate(params, rr, nullptr); } catch (const std::runtime_error&) { threw = true; }
+        EXPECT(threw, "Evaluate at a stale point must throw");
+    }
+    // ceres::Solve replacement (Optimizer.cpp:883-886): the device LM loop from the user's parameter blocks, back into them
+    {
+        const std::vector<double> p0_before = pose_params[0];
+        const std::vector<double> fixed_pt_before = point_params[0];
+        const vio360_lm_summary sm = ev.SolveLM();
+        EXPECT(sm.termination >= 1 && sm.termination <= 5, "LM termination %d", sm.termination);
+        EXPECT(sm.iterations >= 2 && sm.final_cost < 0.9 * sm.initial_cost, "LM did not reduce the cost: %.6g -> %.6g", sm.initial_cost, sm.final_cost);
+        EXPECT(pose_params[0] == p0_before && point_params[0] == fixed_pt_before, "constant blocks moved");
+        for (int k = 0; k < K; ++k) std::memcpy(&pd[6 * k], pose_params[k].data(), 48);
+        for (int j = 0; j < M; ++j) std::memcpy(&pts[3 * j], point_params[j].data(), 24);
+        std::vector<unsigned char> outl(O, 0);
+        for (int i = 0; i < O; ++i) outl[i] = factors[i]->is_outlier() ? 1 : 0;
+        w.outlier = outl.data();
+        double cost_sol = 0;
+        vo_window_evaluate(&w, pd.data(), pts.data(), 1, nullptr, nullptr, nullptr, &cost_sol, 2);
+        EXPECT(std::fabs(cost_sol - sm.final_cost) < 1e-9 * cost_sol, "LM final cost %.17g vs oracle cost at the returned point %.17g", sm.final_cost, cost_sol);
+        std::printf("  LM: %d iterations, cost %.6g -> %.6g, termination %d\n", sm.iterations, sm.initial_cost, sm.final_cost, sm.termination);
+    }
     for (auto* f : factors) delete f;   // (a ceres::Problem would own them)
     std::printf("  BA seam: %d factors, |dr| %.2e, |dJ| %.2e, %d chi2 outliers\n", O, worst_r, worst_J, n_out);
 }
@@ -225,6 +253,21 @@ static void test_fe() {
         nclu += !kc[i]; ncap += !kg[i];
     }
     EXPECT(nclu >= 6 && ncap > 0, "filters removed %d / %d features", nclu, ncap);
+    // the whole TrackFeatures chain as one device-resident call per frame: first frame = detection + grid cap,
+    // second frame = tracked features keep their ids and gain a track count, new ones fill the gaps
+    vio_360::FeatureTrackerCuda seqtr(&cam, 300, 30.0f, 0.01f, 20, 0);
+    seqtr.SetRansacSeed(99u);
+    seqtr.SetRansacParams(100, 2.0f);
+    vio_360::FeatureTrackerCuda::FrameFeatures fa, fb;
+    seqtr.TrackFeatures(m0, fa);
+    EXPECT(fa.num_tracked == 0 && fa.num_detected == nref && !fa.ids.empty() && fa.ids.size() <= (size_t)nref, "first frame: %d detected, %zu kept", fa.num_detected, fa.ids.size());
+    for (size_t i = 0; i < fa.ids.size(); ++i) EXPECT(fa.track_counts[i] == 0, "fresh feature with a track count");
+    seqtr.TrackFeatures(m1, fb);
+    int carried = 0;
+    for (size_t i = 0; i < fb.ids.size(); ++i)
+        if (fb.track_counts[i] == 1) { ++carried; EXPECT(std::find(fa.ids.begin(), fa.ids.end(), fb.ids[i]) != fa.ids.end(), "carried id %d unknown", fb.ids[i]); }
+        else EXPECT(fb.track_counts[i] == 0 && fb.ids[i] >= nref, "new feature id %d", fb.ids[i]);
+    EXPECT(carried > (int)fa.ids.size() / 2 && fb.num_tracked >= carried, "second frame: %d carried of %zu (tracked %d)", carried, fa.ids.size(), fb.num_tracked);
     std::printf("  front-end: %d corners, %d tracked, |dxy| %.2e px, ransac %d/%zu inliers, cluster filter -%d, grid cap -%d\n", nref, ntr, worst, nin, gp.size(), nclu, ncap);
 }
 
