@@ -28,7 +28,7 @@ EXPORTS = [
     "vio360_ba_get_residuals_jacobians", "vio360_ba_normal_blocks", "vio360_ba_reduced_dim",
     "vio360_ba_build_reduced_system", "vio360_ba_set_lm_diagonal", "vio360_ba_reduced_system_dev", "vio360_ba_fetch_reduced_system",
     "vio360_ba_reduced_band_dev", "vio360_ba_expand_band",
-    "vio360_lm_default_options", "vio360_ba_lm_solve", "vio360_ba_jacobian_right_multiply",
+    "vio360_ba_set_eval_precision", "vio360_lm_default_options", "vio360_ba_lm_solve", "vio360_ba_jacobian_right_multiply",
     "vio360_ba_peer_export", "vio360_ba_peer_attach", "vio360_ba_peer_exchange", "vio360_ba_peer_detach",
     "vio360_ba_column_sqnorm", "vio360_ba_chi2", "vio360_ba_solve_reduced", "vio360_pnp_evaluate", "vio360_triangulate",
 ]
@@ -162,6 +162,7 @@ def load():
     lib.vio360_ba_chi2.argtypes = [C.c_void_p, C.c_double, C.c_void_p, C.c_void_p]
     lib.vio360_triangulate.argtypes = [C.c_void_p] * 5 + [C.c_int, C.c_void_p, C.c_void_p]
     lib.vio360_ba_solve_reduced.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.vio360_ba_set_eval_precision.argtypes = [C.c_void_p, C.c_int]
     lib.vio360_ba_jacobian_right_multiply.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
     lib.vio360_lm_default_options.argtypes = [C.POINTER(LmOptions)]
     lib.vio360_ba_lm_solve.argtypes = [C.c_void_p, C.POINTER(LmOptions), C.c_void_p, C.c_void_p, C.POINTER(LmSummary), C.c_void_p, C.c_int]
@@ -572,6 +573,9 @@ class BAWindow:
         dp = np.zeros((self.K, 6)); dl = np.zeros((self.M, 3)) if want_points else None
         self.ctx.check(self.lib.vio360_ba_solve_reduced(self.h, _ptr(dp), _ptr(dl)))
         return dp, dl
+
+    def set_eval_precision(self, fp32):
+        self.ctx.check(self.lib.vio360_ba_set_eval_precision(self.h, int(bool(fp32))))
 
     def jacobian_right_multiply(self, x, apply_loss=True):
         x = np.ascontiguousarray(x, np.float64).reshape(-1)

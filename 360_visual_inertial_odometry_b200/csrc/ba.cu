@@ -63,6 +63,7 @@ struct vio360_ba {
     DevBuf d_r, d_Jp, d_Jl, d_partials, d_packed, d_blocks, d_chi2, d_flag;
     PinBuf pin;
     bool use_D = false;
+    bool eval_f32 = false;       // vio360_ba_set_eval_precision: per-observation math of the fused build / blocks in float
     // device LM loop (ba_lm.cuh): candidate point, step, per-parameter vectors, state
     DevBuf d_cand_pose_delta, d_cand_points, d_cand_posebuf, d_step, d_colsq, d_scale, d_lm_state, d_lm_part;
     PinBuf h_lm;
@@ -237,7 +238,28 @@ __device__ __forceinline__ void load_pose(const BaDev& d, int p, double* pose) {
     for (int j = 0; j < kPoseStride; ++j) pose[j] = __ldg(d.posebuf + kPoseStride * (size_t)p + j);
 }
 
+// Per-observation evaluation in the precision PT (double: parity path; float: optional fp32 mode, results widened).
+template <typename PT>
+__device__ __forceinline__ void eval_obs_as(const double* pose, const double* Pw, double u, double v, bool outl, const CamConst& cam,
+                                            bool apply_loss, double* r, double* F, double* E) {
+    if (sizeof(PT) == 4) {
+        float pf[kPoseStride], rf[2], Ff[12], Ef[6];
+#pragma unroll
+        for (int j = 0; j < kPoseStride; ++j) pf[j] = (float)pose[j];
+        const float Pwf[3] = {(float)Pw[0], (float)Pw[1], (float)Pw[2]};
+        obs_evaluate<true>(pf, Pwf, (float)u, (float)v, outl, cam, apply_loss, rf, Ff, Ef);
+        r[0] = rf[0]; r[1] = rf[1];
+#pragma unroll
+        for (int j = 0; j < 12; ++j) F[j] = Ff[j];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) E[j] = Ef[j];
+    } else {
+        obs_evaluate<true>(pose, Pw, u, v, outl, cam, apply_loss, r, F, E);
+    }
+}
+
 // K8a: one warp per landmark: Hll (3x3), bl (3) by warp reduction; Hpl per observation.
+template <typename PT>
 __global__ void __launch_bounds__(128) k_blocks_landmark(BaDev d, bool apply_loss, double* __restrict__ Hll,
                                                          double* __restrict__ bl, double* __restrict__ Hpl) {
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
@@ -252,7 +274,7 @@ __global__ void __launch_bounds__(128) k_blocks_landmark(BaDev d, bool apply_los
             const int pk = d.pose[i];
             double pose[kPoseStride], r[2], F[12], E[6];
             load_pose(d, pk, pose);
-            obs_evaluate<true>(pose, Pw, d.u[i], d.v[i], d.outlier[i] != 0, d.cam, apply_loss, r, F, E);
+            eval_obs_as<PT>(pose, Pw, d.u[i], d.v[i], d.outlier[i] != 0, d.cam, apply_loss, r, F, E);
             const bool pfix = d.free_map[pk] < 0;
             if (!lfix) {
                 h[0] += E[0] * E[0] + E[3] * E[3]; h[1] += E[0] * E[1] + E[3] * E[4];
@@ -287,6 +309,7 @@ __global__ void __launch_bounds__(128) k_blocks_landmark(BaDev d, bool apply_los
 
 // K8b: one block per pose: Hpp (6x6), bp (6) by a segmented block reduction over the
 // pose's observations (no atomics, fixed summation order).
+template <typename PT>
 __global__ void __launch_bounds__(256) k_blocks_pose(BaDev d, bool apply_loss, bool skip_fixed_points_never,
                                                      double* __restrict__ Hpp, double* __restrict__ bp) {
     const int k = blockIdx.x;
@@ -302,7 +325,7 @@ __global__ void __launch_bounds__(256) k_blocks_pose(BaDev d, bool apply_loss, b
             const int l = d.point[i];
             const double Pw[3] = {d.points[3 * (size_t)l], d.points[3 * (size_t)l + 1], d.points[3 * (size_t)l + 2]};
             double r[2], F[12], E[6];
-            obs_evaluate<true>(pose, Pw, d.u[i], d.v[i], d.outlier[i] != 0, d.cam, apply_loss, r, F, E);
+            eval_obs_as<PT>(pose, Pw, d.u[i], d.v[i], d.outlier[i] != 0, d.cam, apply_loss, r, F, E);
             int t = 0;
 #pragma unroll
             for (int a = 0; a < 6; ++a)
@@ -859,11 +882,13 @@ static int run_blocks(vio360_ba* ba, int apply_loss) {
     double* bl = Hll + M * 9; double* Hpl = bl + M * 3;
     BaDev d = make_dev(ba);
     { KernelTimer kt_(ctx, "k_blocks_landmark");
-    k_blocks_landmark<<<(int)((M * 32 + 127) / 128), 128, 0, ctx->stream>>>(d, apply_loss != 0, Hll, bl, Hpl);
+    if (ba->eval_f32) k_blocks_landmark<float><<<(int)((M * 32 + 127) / 128), 128, 0, ctx->stream>>>(d, apply_loss != 0, Hll, bl, Hpl);
+    else k_blocks_landmark<double><<<(int)((M * 32 + 127) / 128), 128, 0, ctx->stream>>>(d, apply_loss != 0, Hll, bl, Hpl);
     }
     VIO_LAUNCH_CHECK(ctx);
     { KernelTimer kt_(ctx, "k_blocks_pose");
-    k_blocks_pose<<<(int)K, 256, 0, ctx->stream>>>(d, apply_loss != 0, false, Hpp, bp);
+    if (ba->eval_f32) k_blocks_pose<float><<<(int)K, 256, 0, ctx->stream>>>(d, apply_loss != 0, false, Hpp, bp);
+    else k_blocks_pose<double><<<(int)K, 256, 0, ctx->stream>>>(d, apply_loss != 0, false, Hpp, bp);
     }
     VIO_LAUNCH_CHECK(ctx);
     return VIO360_OK;
@@ -905,6 +930,13 @@ extern "C" int vio360_ba_column_sqnorm(vio360_ba* ba, int apply_loss, double* ou
     VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     for (size_t k = 0; k < K; ++k) for (int a = 0; a < 6; ++a) out[6 * k + a] = hpp[36 * k + 7 * a];
     for (size_t l = 0; l < M; ++l) for (int a = 0; a < 3; ++a) out[6 * K + 3 * l + a] = hll[9 * l + 4 * a];
+    return VIO360_OK;
+}
+
+extern "C" int vio360_ba_set_eval_precision(vio360_ba* ba, int fp32) {
+    if (!ba) return VIO360_ERR_INVALID;
+    ba->eval_f32 = fp32 != 0;
+    ba->has_reduced = false;
     return VIO360_OK;
 }
 
@@ -983,13 +1015,18 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
             ba->chunks_dirty = false;
         }
         if (!ba->smem_attr_set) {
-            VIO_CUDA(ctx, cudaFuncSetAttribute(k_schur_tile, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSchurSmemBytes));
+            VIO_CUDA(ctx, cudaFuncSetAttribute(k_schur_tile<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSchurSmemBytes));
+            VIO_CUDA(ctx, cudaFuncSetAttribute(k_schur_tile<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSchurSmemBytes));
             ba->smem_attr_set = true;
         }
         if (nch > 0) {
-            { KernelTimer kt_(ctx, "k_schur_tile");
-            k_schur_tile<<<nch, kSThreads, kSchurSmemBytes, st>>>(d, ba->d_chunks.as<SchurChunk>(), ba->d_slots.as<int>(), ba->d_batch_rng.as<int>(), apply_loss != 0, ba->d_partS.as<double>(),
-                                                                 ba->d_partRhs.as<double>(), ba->d_partials.as<double>());
+            { KernelTimer kt_(ctx, ba->eval_f32 ? "k_schur_tile_f32" : "k_schur_tile");
+            if (ba->eval_f32)
+                k_schur_tile<float><<<nch, kSThreads, kSchurSmemBytes, st>>>(d, ba->d_chunks.as<SchurChunk>(), ba->d_slots.as<int>(), ba->d_batch_rng.as<int>(), apply_loss != 0,
+                                                                           ba->d_partS.as<double>(), ba->d_partRhs.as<double>(), ba->d_partials.as<double>());
+            else
+                k_schur_tile<double><<<nch, kSThreads, kSchurSmemBytes, st>>>(d, ba->d_chunks.as<SchurChunk>(), ba->d_slots.as<int>(), ba->d_batch_rng.as<int>(), apply_loss != 0,
+                                                                            ba->d_partS.as<double>(), ba->d_partRhs.as<double>(), ba->d_partials.as<double>());
             }
             VIO_LAUNCH_CHECK(ctx);
         }

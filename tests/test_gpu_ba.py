@@ -498,3 +498,33 @@ def test_lm_solve_rejected_steps(bindings, ctx, synthetic):
     assert abs(gs["final_cost"] - sm["final_cost"]) < 1e-8 * sm["final_cost"]
     assert np.abs(gp - xp).max() < 1e-6 * max(np.abs(xp).max(), 1e-3) and np.abs(gl - xl).max() < 1e-6 * np.abs(xl).max()
     ba.close()
+
+
+def test_fused_paths_fp32_mode(bindings, ctx, synthetic):
+    """The north star's optional fp32 mode on the FUSED paths (vio360_ba_set_eval_precision): per-observation math in
+    float, sums / Cholesky / Schur products in double.  Hessian blocks within 1e-4 (max-norm relative) of the fp64
+    oracle; the reduced system, whose Schur complement amplifies the Jacobian rounding by the conditioning of E'E,
+    within 1e-3; and it is really a different evaluation (not bit-equal to the fp64 build)."""
+    win = synthetic.make_ba_window(K=10, M=2000, seed=20000, mid_iteration=True)
+    ref = _oracle_all(win)
+    ba = bindings.BAWindow(ctx, win)
+    ba.set_parameters(win["pose_delta"], win["points"])
+    S64, rhs64, c64 = ba.build_reduced_system(ref["D"], True)
+    ba.set_eval_precision(True)
+    Hpp, bp, Hll, bl, Hpl = ba.normal_blocks(True)
+    oHpp, obp, oHll, obl, oHpl = ref["blocks"]
+    assert rel_err(Hpp, oHpp) < 1e-4 and rel_err(bp, obp) < 1e-4 and rel_err(Hll, oHll) < 1e-4 and rel_err(bl, obl) < 1e-4
+    assert rel_err(Hpl, oHpl) < 1e-4
+    S32, rhs32, c32 = ba.build_reduced_system(ref["D"], True)
+    assert rel_err(S32, ref["S"]) < 1e-3 and rel_err(rhs32, ref["rhs"]) < 1e-3 and abs(c32 - ref["cost"]) < 1e-4 * ref["cost"]
+    assert not np.array_equal(S32, S64)
+    ba.set_eval_precision(False)
+    S64b, _, _ = ba.build_reduced_system(ref["D"], True)
+    assert np.array_equal(S64b, S64)
+    # the LM loop in fp32 evaluation mode lands at the same minimum (cost within 1e-4)
+    W = ba_oracle.Window(win)
+    xp, xl, sm, tr = W.lm_solve(win["pose_delta"], win["points"])
+    ba.set_eval_precision(True)
+    gp, gl, gs, gt = ba.lm_solve(win["pose_delta"], win["points"])
+    assert abs(gs["final_cost"] - sm["final_cost"]) < 1e-3 * sm["final_cost"]
+    ba.close()
