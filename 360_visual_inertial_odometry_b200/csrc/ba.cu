@@ -81,6 +81,7 @@ struct vio360_ba {
         bool ipc_open[kMaxPeers] = {};
         int row_lo[kMaxPeers] = {}, row_hi[kMaxPeers] = {};
         size_t nd = 0, nd_pad = 0;       // doubles per band buffer (payload / padded)
+        size_t header_bytes = 0;         // trace words + row flags [kMaxPeers][n_free] + row counters [n_free]
         int n_free = 0, band_w = 0;
         unsigned epoch = 0;              // exchanges completed (all ranks call in lock step)
         int* h_err = nullptr;            // pinned: set by the kernel when a peer never announced
@@ -88,6 +89,7 @@ struct vio360_ba {
         bool trace = false;                                 // VIO360_PEER_TRACE=1: device time stamps of the exchange kernel
         int world = 0;
         unsigned band_epoch = 0;         // epoch the last build wrote its band for
+        unsigned builds = 0;             // sharded builds since the export (the reduce's row counters count over all of them)
         bool stale = false;              // set_structure / set_shard ran after the export: row ranges, band width and
                                          // chunk coverage the peers hold are those of the OLD structure
         int same_device = 1;             // ranks of the world that share this rank's device (tests, MPS)
@@ -96,14 +98,17 @@ struct vio360_ba {
 };
 
 static double* peer_band(vio360_ba* ba, int r, unsigned epoch) {
-    return reinterpret_cast<double*>(static_cast<char*>(ba->peer.base[r]) + kPeerHeaderBytes) + (size_t)(epoch & 1u) * ba->peer.nd_pad;
+    return reinterpret_cast<double*>(static_cast<char*>(ba->peer.base[r]) + ba->peer.header_bytes) + (size_t)(epoch & 1u) * ba->peer.nd_pad;
+}
+static unsigned* peer_row_flags(vio360_ba* ba, int r) {     // rank r's row-flag array [src rank][n_free]
+    return reinterpret_cast<unsigned*>(static_cast<char*>(ba->peer.base[r]) + kPeerHeaderBytes);
 }
 static void peer_release(vio360_ba* ba) {
     auto& P = ba->peer;
     for (int r = 0; r < kMaxPeers; ++r) { if (P.ipc_open[r] && P.base[r]) cudaIpcCloseMemHandle(P.base[r]); P.base[r] = nullptr; P.ipc_open[r] = false; }
     P.local.release();
     if (P.h_err) cudaFreeHost(P.h_err);
-    P.h_err = nullptr; P.exported = P.attached = false; P.epoch = 0; P.zero_n = -1; P.stale = false; P.same_device = 1;
+    P.h_err = nullptr; P.exported = P.attached = false; P.epoch = 0; P.zero_n = -1; P.stale = false; P.same_device = 1; P.builds = 0;
 }
 
 // ------------------------------------------------------------------------ kernels
@@ -1074,6 +1079,14 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
                 const dim3 nblk(sharded ? band_w : (band ? ba->red_band : ba->n_free), nrows);
                 const bool add_diag = ba->shard_rank == 0 && !peer;
                 if (peer) ba->peer.band_epoch = ba->peer.epoch + 1;
+                PeerPublish pub;
+                memset(&pub, 0, sizeof(pub));
+                if (peer) {   // the reduce releases finished block rows to every rank (ba_peer.cuh)
+                    pub.world = ba->peer.world; pub.rank = ba->shard_rank; pub.n_free = ba->n_free; pub.band_w = band_w;
+                    pub.epoch = ba->peer.epoch + 1; pub.builds = nrows > 0 ? ++ba->peer.builds : ba->peer.builds;
+                    for (int r = 0; r < ba->peer.world; ++r) pub.row_flags[r] = peer_row_flags(ba, r);
+                    pub.row_count = peer_row_flags(ba, ba->shard_rank) + (size_t)kMaxPeers * ba->n_free;
+                }
                 if (nrows > 0) {
                 KernelTimer kt_(ctx, "k_schur_reduce");
                 // walkers per block pair: enough for one round of four chunks each over the longest per-pose chunk list
@@ -1088,7 +1101,7 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
                 k_schur_reduce<true, L><<<nblk, 36 * L, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(), \
                                                            ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),  \
                                                            ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int2>(), ba->d_reach.as<int>(), \
-                                                           ba->d_free_pose.as<int>(), Dp, add_diag, band, band_w, row0, ba->n_free)
+                                                           ba->d_free_pose.as<int>(), Dp, add_diag, band, band_w, row0, ba->n_free, pub)
                 if (lanes <= 3) VIO_REDUCE_LAUNCH(3);
                 else if (lanes <= 5) VIO_REDUCE_LAUNCH(5);
                 else if (lanes <= 7) VIO_REDUCE_LAUNCH(7);
@@ -1102,7 +1115,7 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
                 k_schur_reduce<false, 7><<<nblk, 36 * 7, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
                                                             ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),
                                                             ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int2>(), ba->d_reach.as<int>(),
-                                                            ba->d_free_pose.as<int>(), Dp, false, false, 0, 0, ba->n_free);
+                                                            ba->d_free_pose.as<int>(), Dp, false, false, 0, 0, ba->n_free, PeerPublish{});
             }
             VIO_LAUNCH_CHECK(ctx);
         }
@@ -1203,7 +1216,8 @@ extern "C" int vio360_ba_peer_export(vio360_ba* ba, void* blob_out) {
     P.n_free = ba->n_free; P.band_w = std::min(ba->n_free, kSWin);
     P.nd = (size_t)P.n_free * P.band_w * 36 + 6 * (size_t)P.n_free + 1;
     P.nd_pad = (P.nd + 15) & ~(size_t)15;
-    const size_t bytes = kPeerHeaderBytes + 2 * P.nd_pad * 8;
+    P.header_bytes = (kPeerHeaderBytes + (size_t)(kMaxPeers + 1) * P.n_free * 4 + 127) & ~(size_t)127;
+    const size_t bytes = P.header_bytes + 2 * P.nd_pad * 8;
     VIO_CUDA(ctx, P.local.reserve(bytes));
     VIO_CUDA(ctx, cudaMemset(P.local.p, 0, bytes));     // flags = epoch 0, bands zero (slots nobody writes stay zero)
     VIO_CUDA(ctx, cudaHostAlloc((void**)&P.h_err, sizeof(int), cudaHostAllocMapped));
@@ -1285,9 +1299,9 @@ extern "C" int vio360_ba_peer_exchange(vio360_ba* ba) {
     pv.world = P.world; pv.rank = ba->shard_rank;
     for (int r = 0; r < P.world; ++r) {
         pv.band[r] = peer_band(ba, r, epoch);
-        pv.flags[r] = reinterpret_cast<unsigned*>(P.base[r]);
         pv.row_lo[r] = P.row_lo[r]; pv.row_hi[r] = P.row_hi[r];
     }
+    pv.row_flags = peer_row_flags(ba, ba->shard_rank);
     int* d_err = nullptr;
     VIO_CUDA(ctx, cudaHostGetDevicePointer((void**)&d_err, P.h_err, 0));
     // trace words live behind the flags in the exchange header: [CTA 0 wait ns, CTA 0 total ns]
@@ -1299,8 +1313,8 @@ extern "C" int vio360_ba_peer_exchange(vio360_ba* ba) {
     // (a rank whose CTA 0 cannot get an SM slot never announces): cap the grid at this rank's share of the
     // 8 x 256-thread CTAs per SM.
     const unsigned grid = (unsigned)std::min<size_t>((total + 255) / 256, std::max<size_t>(1, (size_t)8 * ctx->num_sms / std::max(1, P.same_device)));
-    { KernelTimer kt_(ctx, "k_band_exchange");
-    k_band_exchange<<<grid, 256, 0, st>>>(pv, epoch, ba->n_free, P.band_w, ba->d_free_pose.as<int>(),
+    { KernelTimer kt_(ctx, "k_band_pull");
+    k_band_pull<<<grid, 256, 0, st>>>(pv, epoch, ba->n_free, P.band_w, ba->d_free_pose.as<int>(),
                                           ba->use_D ? ba->d_D.as<double>() : nullptr, dS, d_err, d_trace);
     }
     VIO_LAUNCH_CHECK(ctx);

@@ -454,7 +454,7 @@ k_schur_reduce(double* __restrict__ S, int n, double* __restrict__ rhs, double* 
                const double* __restrict__ partS, const double* __restrict__ partRhs, const double* __restrict__ partCost,
                int nchunks, const SchurChunk* __restrict__ chunks, const int* __restrict__ cov_ptr,
                const int2* __restrict__ cov_idx, const int* __restrict__ reach, const int* __restrict__ free_pose,
-               const double* __restrict__ D, bool add_diag, bool band_grid, int band_w, int row0, int n_free) {
+               const double* __restrict__ D, bool add_diag, bool band_grid, int band_w, int row0, int n_free, const PeerPublish pub) {
     // band_grid: blockIdx.x counts block columns from the diagonal (the host sized the grid to the
     // widest row of the envelope and zeroed S outside it once per structure).  row0: first block row
     // of the grid (a rank of a peer-memory exchange sums only the rows its landmarks touch).
@@ -464,6 +464,7 @@ k_schur_reduce(double* __restrict__ S, int n, double* __restrict__ rhs, double* 
     __shared__ double partR[kRedLanes][6];
     schur_reduce_block<FULL, kRedLanes>(bi, bj, blockIdx.y == 0 && bi == bj, S, n, rhs, cost_out, partS, partRhs, partCost, nchunks,
                                         cov_ptr, cov_idx, reach, free_pose, D, add_diag, band_w, part, partR);
+    peer_publish_block(pub, bi);   // multi-GPU: release the block row to the other ranks once its last block is stored (ba_peer.cuh)
 }
 
 }  // namespace vio360

@@ -72,7 +72,7 @@ def peer_rows(pose_idx, point_idx, free_map, lm_begin, lm_end):
 
 
 def peer_exchange_sum(bands, rows, n_free, band_w=None, pose_diag=None):
-    """numpy statement of k_band_exchange (csrc/ba_peer.cuh): every element of the band is the sum, in rank order,
+    """numpy statement of k_band_pull (csrc/ba_peer.cuh): every element of the band is the sum, in rank order,
     of the partial bands of the ranks whose row range covers its block row (rhs entries: the pose's row; the cost:
     every rank); the pose part of the LM diagonal (squared, pose_diag: 6 n_free) is added on the diagonal; the
     result is expanded to the dense symmetric system.  bands: list of band_pack() buffers, rows: list of (lo, hi)."""
