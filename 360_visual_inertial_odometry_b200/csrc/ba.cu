@@ -1086,6 +1086,8 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
                     pub.epoch = ba->peer.epoch + 1; pub.builds = nrows > 0 ? ++ba->peer.builds : ba->peer.builds;
                     for (int r = 0; r < ba->peer.world; ++r) pub.row_flags[r] = peer_row_flags(ba, r);
                     pub.row_count = peer_row_flags(ba, ba->shard_rank) + (size_t)kMaxPeers * ba->n_free;
+                    static const int pub_mode = getenv("VIO360_PEER_PUBLISH") ? atoi(getenv("VIO360_PEER_PUBLISH")) : 1;
+                    pub.mode = pub_mode; pub.row_lo = row0; pub.row_hi = row0 + nrows;
                 }
                 if (nrows > 0) {
                 KernelTimer kt_(ctx, "k_schur_reduce");
@@ -1216,7 +1218,7 @@ extern "C" int vio360_ba_peer_export(vio360_ba* ba, void* blob_out) {
     P.n_free = ba->n_free; P.band_w = std::min(ba->n_free, kSWin);
     P.nd = (size_t)P.n_free * P.band_w * 36 + 6 * (size_t)P.n_free + 1;
     P.nd_pad = (P.nd + 15) & ~(size_t)15;
-    P.header_bytes = (kPeerHeaderBytes + (size_t)(kMaxPeers + 1) * P.n_free * 4 + 127) & ~(size_t)127;
+    P.header_bytes = (kPeerHeaderBytes + ((size_t)(kMaxPeers + 1) * P.n_free + 4) * 4 + 127) & ~(size_t)127;   // row flags, row counters, rows-done counter
     const size_t bytes = P.header_bytes + 2 * P.nd_pad * 8;
     VIO_CUDA(ctx, P.local.reserve(bytes));
     VIO_CUDA(ctx, cudaMemset(P.local.p, 0, bytes));     // flags = epoch 0, bands zero (slots nobody writes stay zero)

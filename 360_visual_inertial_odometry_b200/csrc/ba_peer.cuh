@@ -48,23 +48,10 @@ struct PeerPublish {
     int world, rank, n_free, band_w;
     unsigned epoch;                  // 0: not a peer build
     unsigned builds;                 // peer builds of this rank so far, this one included (row_count counts over all of them)
+    int mode;                        // 0: st.release.sys per rank and row; 1: one fence.sys, then relaxed stores (default);
+                                     // 2: one release per BUILD (the CTA that completes the last row releases every row)
+    int row_lo, row_hi;              // this rank's block rows
 };
-
-// called by every thread of a reduce CTA after it stored block (bi, .) of the band
-__device__ __forceinline__ void peer_publish_block(const PeerPublish& pub, int bi) {
-    if (pub.epoch == 0u) return;
-    __syncthreads();                                       // the CTA's stores are done
-    if (threadIdx.x == 0) {
-        __threadfence();
-        const unsigned per_row = (unsigned)min(pub.band_w, pub.n_free - bi);
-        const unsigned old = atomicAdd(pub.row_count + bi, 1u);
-        if (old + 1u == pub.builds * per_row) {             // this CTA completed the row: release it to every rank
-            __threadfence_system();
-            for (int r = 0; r < pub.world; ++r)
-                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(pub.row_flags[r] + (size_t)pub.rank * pub.n_free + bi), "r"(pub.epoch) : "memory");
-        }
-    }
-}
 
 __device__ __forceinline__ double ld_peer_f64(const double* p) {
     double v;
@@ -76,8 +63,40 @@ __device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ void st_release_sys_u32(unsigned* p, unsigned v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+__device__ __forceinline__ void st_relaxed_sys_u32(unsigned* p, unsigned v) {
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// called by every thread of a reduce CTA after it stored block (bi, .) of the band
+__device__ __forceinline__ void peer_publish_block(const PeerPublish& pub, int bi) {
+    if (pub.epoch == 0u) return;
+    __syncthreads();                                       // the CTA's stores are done
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned per_row = (unsigned)min(pub.band_w, pub.n_free - bi);
+        const unsigned old = atomicAdd(pub.row_count + bi, 1u);
+        if (old + 1u != pub.builds * per_row) return;      // not the CTA that completed the row
+        if (pub.mode == 2) {
+            // rank-level release: count completed rows in the slot behind the row counters
+            const unsigned nrows = (unsigned)(pub.row_hi - pub.row_lo);
+            __threadfence();
+            const unsigned done = atomicAdd(pub.row_count + pub.n_free, 1u);
+            if (done + 1u != pub.builds * nrows) return;
+            __threadfence_system();
+            for (int r = 0; r < pub.world; ++r)
+                for (int row = pub.row_lo; row < pub.row_hi; ++row)
+                    st_relaxed_sys_u32(pub.row_flags[r] + (size_t)pub.rank * pub.n_free + row, pub.epoch);
+            return;
+        }
+        if (pub.mode == 1) {
+            __threadfence_system();                        // the row's blocks (all CTAs: their fences precede their counts) are visible system wide
+            for (int r = 0; r < pub.world; ++r) st_relaxed_sys_u32(pub.row_flags[r] + (size_t)pub.rank * pub.n_free + bi, pub.epoch);
+            return;
+        }
+        __threadfence_system();
+        for (int r = 0; r < pub.world; ++r)
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(pub.row_flags[r] + (size_t)pub.rank * pub.n_free + bi), "r"(pub.epoch) : "memory");
+    }
 }
 
 // Every thread pulls its elements of the band from the ranks whose rows cover them, sums in rank order, adds the

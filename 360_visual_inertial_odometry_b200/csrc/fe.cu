@@ -69,6 +69,7 @@ struct vio360_fe_state {
     // host-space batches: frames are uploaded on a second stream in groups of h2d_group jobs, and a group's
     // pyramid + LK launches wait only for its own frames, so the kernels run behind the PCIe copies
     cudaStream_t copy_stream = nullptr;
+    cudaStream_t pyr_stream = nullptr;   // device-space batches: pyramids of the next group beside the LK kernel of this one
     std::vector<cudaEvent_t> grp_ev;
     int h2d_group = 4;           // VIO360_FE_H2D_GROUP (3840x1920 x 64 pairs: 4 -> 6959, 8 -> 6801, 16 -> 6823, off -> 6348 frames/s)
 };
@@ -89,6 +90,7 @@ void vio360_fe_release(vio360_ctx* ctx) {
     for (auto& d : s->d_pyrjobs_ring) d.release();
     for (cudaEvent_t e : s->grp_ev) cudaEventDestroy(e);
     if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
+    if (s->pyr_stream) cudaStreamDestroy(s->pyr_stream);
     delete s;
     ctx->fe = nullptr;
 }
@@ -148,6 +150,11 @@ extern "C" int vio360_fe_configure(vio360_ctx* ctx, int width, int height, int m
     if (const char* e = getenv("VIO360_LK_MB")) s->lk_mb = atoi(e);
     if (const char* e = getenv("VIO360_FE_H2D_GROUP")) s->h2d_group = std::max(1, atoi(e));
     VIO_CUDA(ctx, cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
+    {
+        int lo = 0, hi = 0;
+        VIO_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        VIO_CUDA(ctx, cudaStreamCreateWithPriority(&s->pyr_stream, cudaStreamNonBlocking, hi));   // short kernels: let them in first
+    }
     if (const char* e = getenv("VIO360_DET_CAND")) s->max_cand = std::max(1, atoi(e));   // initial candidate capacity per image
     s->configured = true;
     return VIO360_OK;
@@ -244,8 +251,9 @@ static int upload_pyr_jobs(vio360_ctx* ctx, size_t job_off, size_t count) {
                                   sizeof(PyrJob) * count, cudaMemcpyHostToDevice, ctx->stream));
     return VIO360_OK;
 }
-static int launch_pyramids(vio360_ctx* ctx, const std::vector<int>& todo, size_t job_off) {
+static int launch_pyramids(vio360_ctx* ctx, const std::vector<int>& todo, size_t job_off, cudaStream_t on = nullptr) {
     vio360_fe_state* s = ctx->fe;
+    const cudaStream_t pst = on ? on : ctx->stream;
     if (todo.empty() || s->nlevels <= 1) { for (int i : todo) s->slots[i].has_pyramid = true; return VIO360_OK; }
     const int nb = (int)todo.size();
     const PyrJob* hj = s->cur_stage->pyrjobs.as<PyrJob>() + job_off;    // job_off: several groups share one descriptor stage
@@ -266,12 +274,12 @@ static int launch_pyramids(vio360_ctx* ctx, const std::vector<int>& todo, size_t
             while (strip > 4 && (long long)nwx * ((dh + strip - 1) / strip) * nb < 24ll * ctx->num_sms) strip >>= 1;
             const int nsy = (dh + strip - 1) / strip, total = nwx * nsy * nb;
             { KernelTimer kt_(ctx, "k_pyr_down");
-            k_pyr_down8<<<(total + wpb - 1) / wpb, kPyrFastThreads, 0, ctx->stream>>>(dj + (size_t)l * nb, s->lw[l], s->lh[l], dw, dh, nwx, nsy, total, strip);
+            k_pyr_down8<<<(total + wpb - 1) / wpb, kPyrFastThreads, 0, pst>>>(dj + (size_t)l * nb, s->lw[l], s->lh[l], dw, dh, nwx, nsy, total, strip);
             }
         } else {
             dim3 grid((dw + kPyrTW - 1) / kPyrTW, (dh + kPyrTH - 1) / kPyrTH, nb);
             { KernelTimer kt_(ctx, "k_pyr_down");
-            k_pyr_down<<<grid, 256, 0, ctx->stream>>>(dj + (size_t)l * nb, s->lw[l], s->lh[l], dw, dh);
+            k_pyr_down<<<grid, 256, 0, pst>>>(dj + (size_t)l * nb, s->lw[l], s->lh[l], dw, dh);
             }
         }
         VIO_LAUNCH_CHECK(ctx);
@@ -343,13 +351,20 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
     // stream, its pyramid and LK launches wait only for those copies (device-space batches are one group)
     static const bool force_piped = getenv("VIO360_FE_H2D_FORCE") != nullptr;   // A/B probe: copy stream even for one group
     const bool piped = mem_space == VIO360_MEM_HOST && (n_jobs > s->h2d_group || force_piped);
-    const int gsize = piped ? s->h2d_group : n_jobs, ngroups = (n_jobs + gsize - 1) / gsize;
+    // device-space batches: the pyramids of all groups run back to back on a second (high priority) stream and a
+    // group's LK launch waits only for its own pyramids, so the HBM-bound pyramid kernels of group g + 1 share the
+    // machine with the issue-bound LK kernel of group g.  Off while per-kernel event timing is on (the event pairs
+    // live on the main stream) and for small batches.
+    static const bool no_overlap = getenv("VIO360_FE_NO_OVERLAP") != nullptr;
+    static const int dev_groups = getenv("VIO360_FE_DEV_GROUPS") ? std::max(1, atoi(getenv("VIO360_FE_DEV_GROUPS"))) : 4;
+    const bool dev_piped = mem_space == VIO360_MEM_DEVICE && n_jobs >= 2 * dev_groups && dev_groups > 1 && !ctx->timing && !no_overlap;
+    const int gsize = piped ? s->h2d_group : (dev_piped ? (n_jobs + dev_groups - 1) / dev_groups : n_jobs), ngroups = (n_jobs + gsize - 1) / gsize;
     std::vector<std::vector<int>> todo(ngroups);
     std::vector<int> queued;
     struct Upload { int slot, group; const uint8_t* img; size_t pitch; };
     std::vector<Upload> uploads;
-    if (piped)
-        while ((int)s->grp_ev.size() < ngroups) {
+    if (piped || dev_piped)
+        while ((int)s->grp_ev.size() < ngroups + 1) {
             cudaEvent_t e;
             VIO_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
             s->grp_ev.push_back(e);
@@ -440,10 +455,22 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
     }
     const LkParams lp = lk_params(s);
     pyr_off = 0;
+    if (dev_piped) {
+        // the side stream starts after everything already queued on the main stream (descriptor copies of this call,
+        // the previous call's LK kernels, which may still read the slots this call rebuilds)
+        VIO_CUDA(ctx, cudaEventRecord(s->grp_ev[ngroups], st));
+        VIO_CUDA(ctx, cudaStreamWaitEvent(s->pyr_stream, s->grp_ev[ngroups], 0));
+        size_t po = 0;
+        for (int g = 0; g < ngroups; ++g) {
+            if ((rc = launch_pyramids(ctx, todo[g], po, s->pyr_stream))) return rc;
+            po += todo[g].size() * per;
+            VIO_CUDA(ctx, cudaEventRecord(s->grp_ev[g], s->pyr_stream));
+        }
+    }
     for (int g = 0; g < ngroups; ++g) {
         const int j0 = g * gsize, nj = std::min(gsize, n_jobs - j0);
-        if (piped) VIO_CUDA(ctx, cudaStreamWaitEvent(st, s->grp_ev[g], 0));
-        if ((rc = launch_pyramids(ctx, todo[g], pyr_off))) return rc;
+        if (piped || dev_piped) VIO_CUDA(ctx, cudaStreamWaitEvent(st, s->grp_ev[g], 0));
+        if (!dev_piped && (rc = launch_pyramids(ctx, todo[g], pyr_off))) return rc;
         pyr_off += todo[g].size() * per;
         if (max_n == 0) continue;
         if ((rc = launch_lk(ctx, dj + j0, nj, max_n, lp))) return rc;
