@@ -351,12 +351,14 @@ extern "C" int vio360_fe_track_batch(vio360_ctx* ctx, const vio360_track_job* jo
     // stream, its pyramid and LK launches wait only for those copies (device-space batches are one group)
     static const bool force_piped = getenv("VIO360_FE_H2D_FORCE") != nullptr;   // A/B probe: copy stream even for one group
     const bool piped = mem_space == VIO360_MEM_HOST && (n_jobs > s->h2d_group || force_piped);
-    // device-space batches: the pyramids of all groups run back to back on a second (high priority) stream and a
-    // group's LK launch waits only for its own pyramids, so the HBM-bound pyramid kernels of group g + 1 share the
-    // machine with the issue-bound LK kernel of group g.  Off while per-kernel event timing is on (the event pairs
-    // live on the main stream) and for small batches.
+    // device-space batches, OPT-IN (VIO360_FE_DEV_GROUPS=4): the pyramids of all groups run back to back on a second
+    // (high priority) stream and a group's LK launch waits only for its own pyramids, so the HBM-bound pyramid
+    // kernels of group g + 1 share the machine with the issue-bound LK kernel of group g.  Measured on B200 (64 x
+    // 3840x1920, profiles/r02_bench_run6*.json): 1.027 ms per step against 0.950 ms with one group -- the LK
+    // kernel holds every register of the SMs (2 CTAs x 256 threads x 128), so the pyramid CTAs only displace LK
+    // CTAs, and four LK launches pay four tails.  Kept for other shapes; off by default.
     static const bool no_overlap = getenv("VIO360_FE_NO_OVERLAP") != nullptr;
-    static const int dev_groups = getenv("VIO360_FE_DEV_GROUPS") ? std::max(1, atoi(getenv("VIO360_FE_DEV_GROUPS"))) : 4;
+    static const int dev_groups = getenv("VIO360_FE_DEV_GROUPS") ? std::max(1, atoi(getenv("VIO360_FE_DEV_GROUPS"))) : 1;
     const bool dev_piped = mem_space == VIO360_MEM_DEVICE && n_jobs >= 2 * dev_groups && dev_groups > 1 && !ctx->timing && !no_overlap;
     const int gsize = piped ? s->h2d_group : (dev_piped ? (n_jobs + dev_groups - 1) / dev_groups : n_jobs), ngroups = (n_jobs + gsize - 1) / gsize;
     std::vector<std::vector<int>> todo(ngroups);
