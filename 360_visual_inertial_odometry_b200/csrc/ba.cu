@@ -70,8 +70,10 @@ struct vio360_ba {
     // chunked (atomic-free) Schur path: see ba_schur.cuh
     std::vector<int> h_pose;                 // landmark-major pose index of every observation
     std::vector<SchurChunk> chunks;
-    std::vector<int> irregular, cov_ptr, cov_idx, free_pose, reach, slot_table, batch_rng;
-    DevBuf d_chunks, d_cov_ptr, d_cov_idx, d_free_pose, d_irregular, d_partS, d_partRhs, d_reach, d_slots, d_batch_rng;
+    std::vector<int> irregular, wide, cov_ptr, cov_idx, free_pose, reach, slot_table, batch_rng, batch_lm;
+    int n_regular_chunks = 0;
+    int band_blocks = kSWin;   // block columns of S's band over ALL landmarks of the window (identical on every rank)
+    DevBuf d_chunks, d_cov_ptr, d_cov_idx, d_free_pose, d_irregular, d_partS, d_partRhs, d_reach, d_slots, d_batch_rng, d_batch_lm, d_wide, d_wide_inv;
     bool chunks_dirty = true, smem_attr_set = false, chunk_error = false;
     // peer-memory exchange of the sharded reduced system (ba_peer.cuh)
     struct Peer {
@@ -160,6 +162,26 @@ __global__ void k_sum_partials(const double* __restrict__ partials, int n, doubl
     }
 }
 
+// Per-observation evaluation in the precision PT (double: parity path; float: optional fp32 mode, results widened).
+template <typename PT>
+__device__ __forceinline__ void eval_obs_as(const double* pose, const double* Pw, double u, double v, bool outl, const CamConst& cam,
+                                            bool apply_loss, double* r, double* F, double* E) {
+    if (sizeof(PT) == 4) {
+        float pf[kPoseStride], rf[2], Ff[12], Ef[6];
+#pragma unroll
+        for (int j = 0; j < kPoseStride; ++j) pf[j] = (float)pose[j];
+        const float Pwf[3] = {(float)Pw[0], (float)Pw[1], (float)Pw[2]};
+        obs_evaluate<true>(pf, Pwf, (float)u, (float)v, outl, cam, apply_loss, rf, Ff, Ef);
+        r[0] = rf[0]; r[1] = rf[1];
+#pragma unroll
+        for (int j = 0; j < 12; ++j) F[j] = Ff[j];
+#pragma unroll
+        for (int j = 0; j < 6; ++j) E[j] = Ef[j];
+    } else {
+        obs_evaluate<true>(pose, Pw, u, v, outl, cam, apply_loss, r, F, E);
+    }
+}
+
 #include "ba_schur_kernels.cuh"
 #include "ba_solve.cuh"
 #include "ba_triangulate.cuh"
@@ -241,26 +263,6 @@ __global__ void __launch_bounds__(128) k_chi2(BaDev d, double thr, double* __res
 __device__ __forceinline__ void load_pose(const BaDev& d, int p, double* pose) {
 #pragma unroll
     for (int j = 0; j < kPoseStride; ++j) pose[j] = __ldg(d.posebuf + kPoseStride * (size_t)p + j);
-}
-
-// Per-observation evaluation in the precision PT (double: parity path; float: optional fp32 mode, results widened).
-template <typename PT>
-__device__ __forceinline__ void eval_obs_as(const double* pose, const double* Pw, double u, double v, bool outl, const CamConst& cam,
-                                            bool apply_loss, double* r, double* F, double* E) {
-    if (sizeof(PT) == 4) {
-        float pf[kPoseStride], rf[2], Ff[12], Ef[6];
-#pragma unroll
-        for (int j = 0; j < kPoseStride; ++j) pf[j] = (float)pose[j];
-        const float Pwf[3] = {(float)Pw[0], (float)Pw[1], (float)Pw[2]};
-        obs_evaluate<true>(pf, Pwf, (float)u, (float)v, outl, cam, apply_loss, rf, Ff, Ef);
-        r[0] = rf[0]; r[1] = rf[1];
-#pragma unroll
-        for (int j = 0; j < 12; ++j) F[j] = Ff[j];
-#pragma unroll
-        for (int j = 0; j < 6; ++j) E[j] = Ef[j];
-    } else {
-        obs_evaluate<true>(pose, Pw, u, v, outl, cam, apply_loss, r, F, E);
-    }
 }
 
 // K8a: one warp per landmark: Hll (3x3), bl (3) by warp reduction; Hpl per observation.
@@ -559,6 +561,7 @@ extern "C" void vio360_ba_destroy(vio360_ba* ba) {
                       &ba->d_points, &ba->d_free_map, &ba->d_point_fixed, &ba->d_D, &ba->d_r, &ba->d_Jp, &ba->d_Jl,
                       &ba->d_partials, &ba->d_packed, &ba->d_blocks, &ba->d_chi2, &ba->d_flag,
                       &ba->d_chunks, &ba->d_cov_ptr, &ba->d_cov_idx, &ba->d_free_pose, &ba->d_irregular, &ba->d_partS, &ba->d_partRhs, &ba->d_reach, &ba->d_slots, &ba->d_batch_rng,
+                      &ba->d_batch_lm, &ba->d_wide, &ba->d_wide_inv,
                       &ba->d_chol, &ba->d_linv, &ba->d_x, &ba->d_dl, &ba->d_reachF, &ba->d_band,
                       &ba->d_cand_pose_delta, &ba->d_cand_points, &ba->d_cand_posebuf, &ba->d_step, &ba->d_colsq, &ba->d_scale,
                       &ba->d_lm_state, &ba->d_lm_part};
@@ -570,13 +573,19 @@ extern "C" void vio360_ba_destroy(vio360_ba* ba) {
     delete ba;
 }
 
-// Partition the shard's landmarks [lm_begin, lm_end) into chunks for k_schur_tile: contiguous
-// landmark ranges whose observing poses fit a window of kSWin consecutive poses.  Landmarks
-// that cannot (span too wide, or two observations from the same pose) go to the list handled
-// by k_schur_warp.  Also builds, per pose, the list of chunks covering it (k_schur_reduce).
+// Partition the shard's landmarks [lm_begin, lm_end) into chunks for k_schur_tile.
+//  * regular landmarks (observing poses within kSWin consecutive poses): contiguous landmark ranges whose poses
+//    fit one window of kSWin poses -- one CTA per chunk, everything about a landmark happens inside it;
+//  * WIDE landmarks (span > kSWin, e.g. a loop closure): poses are cut into groups of kSGrp = kSWin / 2; a landmark
+//    joins one job per pair (a <= b) of groups it is seen from.  A job's CTA holds group a in pose slots 0..11 and
+//    group b in slots 12..23, gets (E'E + D^2)^-1 of the whole landmark from k_wide_prepare (pass 1) and contributes
+//    the S blocks of pose pairs (a, b) only (a == b: also F'F, F'r and the cost of the observations of group a);
+//  * landmarks with two observations from one pose (never produced by the reference) stay with k_schur_warp.
+// Also builds, per pose, the list of chunk slabs covering its block row (k_schur_reduce).
 static void build_chunks(vio360_ba* ba) {
     const int K = ba->K;
-    ba->chunks.clear(); ba->irregular.clear();
+    ba->chunks.clear(); ba->irregular.clear(); ba->wide.clear();
+    std::vector<int> chunk_lms;                       // landmark ids of all chunks, batch-padded (-1)
     const int nlm = ba->lm_end - ba->lm_begin;
     // a chunk is a whole number of kSMaxLm-landmark batches (a partly filled batch costs a full one), sized so
     // that the shard fills `waves` rounds of one CTA per SM (measured on the 1M-observation window: one round and
@@ -585,12 +594,19 @@ static void build_chunks(vio360_ba* ba) {
     const int nbatch_all = (nlm + kSMaxLm - 1) / kSMaxLm, slots = std::max(1, waves * ba->ctx->num_sms);
     const int target = kSMaxLm * std::max(1, (nbatch_all + slots - 1) / slots);
     std::vector<int> seen(K, -1);
-    SchurChunk cur{ba->lm_begin, ba->lm_begin, 0, 0, 0, 0, 0, 0};
+    int nbatch_total = 0;
+    auto push_chunk = [&](const std::vector<int>& lms, int pbase, int span, int pbaseB, int spanB, int flags) {
+        SchurChunk c{0, (int)lms.size(), pbase, span, nbatch_total, pbaseB, spanB, flags};
+        const int nb = ((int)lms.size() + kSMaxLm - 1) / kSMaxLm;
+        for (int i = 0; i < nb * kSMaxLm; ++i) chunk_lms.push_back(i < (int)lms.size() ? lms[i] : -1);
+        nbatch_total += nb;
+        ba->chunks.push_back(c);
+    };
+    std::vector<int> cur;
     int cmin = K, cmax = -1;
-    auto close = [&](int end) {
-        cur.lm_end = end;
-        if (cur.lm_end > cur.lm_begin && cmax >= cmin) { cur.pbase = cmin; cur.span = cmax - cmin + 1; ba->chunks.push_back(cur); }
-        cur.lm_begin = end; cmin = K; cmax = -1;
+    auto close = [&]() {
+        if (!cur.empty() && cmax >= cmin) push_chunk(cur, cmin, cmax - cmin + 1, 0, 0, 0);
+        cur.clear(); cmin = K; cmax = -1;
     };
     for (int l = ba->lm_begin; l < ba->lm_end; ++l) {
         const int lo = ba->lm_ptr[l], hi = ba->lm_ptr[l + 1];
@@ -603,54 +619,90 @@ static void build_chunks(vio360_ba* ba) {
             seen[p] = l;
             pmin = std::min(pmin, p); pmax = std::max(pmax, p);
         }
-        if (dup || pmax - pmin + 1 > kSWin) {
-            close(l);
-            ba->irregular.push_back(l);
-            cur.lm_begin = l + 1;
-            continue;
-        }
+        if (dup) { ba->irregular.push_back(l); continue; }
+        if (pmax - pmin + 1 > kSWin) { ba->wide.push_back(l); continue; }
         const int nmin = std::min(cmin, pmin), nmax = std::max(cmax, pmax);
-        if (cmax >= cmin && (nmax - nmin + 1 > kSWin || l - cur.lm_begin >= target)) {
-            close(l);
+        if (cmax >= cmin && (nmax - nmin + 1 > kSWin || (int)cur.size() >= target)) {
+            close();
             cmin = pmin; cmax = pmax;
         } else {
             cmin = nmin; cmax = nmax;
         }
+        cur.push_back(l);
     }
-    close(ba->lm_end);
-    ba->cov_ptr.assign(K + 1, 0);
-    for (const SchurChunk& c : ba->chunks)
-        for (int p = c.pbase; p < c.pbase + c.span; ++p) ba->cov_ptr[p + 1]++;
-    for (int p = 0; p < K; ++p) ba->cov_ptr[p + 1] += ba->cov_ptr[p];
-    ba->cov_idx.assign(2 * (size_t)std::max(1, ba->cov_ptr[K]), 0);   // (chunk, pbase | span << 16) pairs
-    std::vector<int> fill(ba->cov_ptr.begin(), ba->cov_ptr.end() - 1);
-    for (int c = 0; c < (int)ba->chunks.size(); ++c)
-        for (int p = ba->chunks[c].pbase; p < ba->chunks[c].pbase + ba->chunks[c].span; ++p) {
-            ba->cov_idx[2 * (size_t)fill[p]] = c;
-            ba->cov_idx[2 * (size_t)fill[p] + 1] = ba->chunks[c].pbase | (ba->chunks[c].span << 16);
-            fill[p]++;
+    close();
+    ba->n_regular_chunks = (int)ba->chunks.size();
+    // ---- jobs of the wide landmarks: (group a, group b) -> landmarks seen from both
+    if (!ba->wide.empty()) {
+        const int ngrp = (K + kSGrp - 1) / kSGrp;
+        std::vector<std::vector<int>> job((size_t)ngrp * ngrp);
+        std::vector<int> grp;
+        for (int l : ba->wide) {
+            grp.clear();
+            for (int q = ba->lm_ptr[l]; q < ba->lm_ptr[l + 1]; ++q) grp.push_back(ba->h_pose[q] / kSGrp);
+            std::sort(grp.begin(), grp.end());
+            grp.erase(std::unique(grp.begin(), grp.end()), grp.end());
+            for (size_t i = 0; i < grp.size(); ++i)
+                for (size_t j = i; j < grp.size(); ++j) job[(size_t)grp[i] * ngrp + grp[j]].push_back(l);
         }
-    // slot table: per batch of kSMaxLm landmarks, the observation held by thread (pose slot, landmark slot)
-    int nbatch_total = 0;
-    for (SchurChunk& c : ba->chunks) { c.batch0 = nbatch_total; nbatch_total += (c.lm_end - c.lm_begin + kSMaxLm - 1) / kSMaxLm; }
+        size_t wide_batches = 0;
+        for (const auto& v : job) wide_batches += (v.size() + kSMaxLm - 1) / kSMaxLm;
+        const int wtarget = kSMaxLm * (int)std::max<size_t>(1, (wide_batches + slots - 1) / slots);
+        std::vector<int> part;
+        for (int a = 0; a < ngrp; ++a)
+            for (int b2 = a; b2 < ngrp; ++b2) {
+                const std::vector<int>& v = job[(size_t)a * ngrp + b2];
+                for (size_t i0 = 0; i0 < v.size(); i0 += (size_t)wtarget) {
+                    part.assign(v.begin() + i0, v.begin() + std::min(v.size(), i0 + (size_t)wtarget));
+                    const int pa = a * kSGrp, sa = std::min(kSGrp, K - pa), pb = b2 * kSGrp, sb = std::min(kSGrp, K - pb);
+                    if (a == b2) push_chunk(part, pa, sa, 0, 0, kChunkWide);
+                    else push_chunk(part, pa, sa, pb, sb, kChunkWide | kChunkCross);
+                }
+            }
+    }
+    // ---- per pose: the slabs covering its block row.  entry = {chunk, slot of the pose, first column pose |
+    // columns << 16, slot of the first column}: the slab holds block (pose, q) for first <= q < first + columns
+    ba->cov_ptr.assign(K + 1, 0);
+    auto for_rows = [&](auto&& fn) {
+        for (int c = 0; c < (int)ba->chunks.size(); ++c) {
+            const SchurChunk& ch = ba->chunks[c];
+            if (ch.flags & kChunkCross) { for (int p = ch.pbase; p < ch.pbase + ch.span; ++p) fn(c, p, p - ch.pbase, ch.pbaseB, ch.spanB, kSGrp); }
+            else { for (int p = ch.pbase; p < ch.pbase + ch.span; ++p) fn(c, p, p - ch.pbase, ch.pbase, ch.span, 0); }
+        }
+    };
+    for_rows([&](int, int p, int, int, int, int) { ba->cov_ptr[p + 1]++; });
+    for (int p = 0; p < K; ++p) ba->cov_ptr[p + 1] += ba->cov_ptr[p];
+    ba->cov_idx.assign(4 * (size_t)std::max(1, ba->cov_ptr[K]), 0);
+    std::vector<int> fill(ba->cov_ptr.begin(), ba->cov_ptr.end() - 1);
+    ba->reach.assign(K, -1);
+    for_rows([&](int c, int p, int slot, int first, int cols, int slot0) {
+        int* e = ba->cov_idx.data() + 4 * (size_t)fill[p]++;
+        e[0] = c; e[1] = slot; e[2] = first | (cols << 16); e[3] = slot0;
+        ba->reach[p] = std::max(ba->reach[p], first + cols - 1);
+    });
+    // ---- slot table: per batch of kSMaxLm landmarks, the observation held by thread (pose slot, landmark slot)
+    ba->batch_lm = chunk_lms;
+    if (ba->batch_lm.empty()) ba->batch_lm.assign(kSMaxLm, -1);
     ba->slot_table.assign((size_t)std::max(1, nbatch_total) * kSProd, -1);
     ba->batch_rng.assign((size_t)std::max(1, nbatch_total), 0xff);   // empty: lo = 255 > hi = 0
     for (const SchurChunk& c : ba->chunks)
-        for (int l = c.lm_begin; l < c.lm_end; ++l) {
-            const int b = (l - c.lm_begin) / kSMaxLm, ls = (l - c.lm_begin) % kSMaxLm;
+        for (int i = 0; i < c.lm_end; ++i) {
+            const int b = i / kSMaxLm, ls = i % kSMaxLm;
+            const int l = ba->batch_lm[(size_t)(c.batch0 + b) * kSMaxLm + ls];
             int* row = ba->slot_table.data() + (size_t)(c.batch0 + b) * kSProd;
             for (int q = ba->lm_ptr[l]; q < ba->lm_ptr[l + 1]; ++q) {
-                const int pw = ba->h_pose[q] - c.pbase;
-                if (pw < 0 || pw >= c.span || row[pw * kSMaxLm + ls] != -1) { ba->chunk_error = true; continue; }
+                const int p = ba->h_pose[q];
+                int pw = -1;
+                if (p >= c.pbase && p < c.pbase + c.span) pw = p - c.pbase;
+                else if ((c.flags & kChunkCross) && p >= c.pbaseB && p < c.pbaseB + c.spanB) pw = kSGrp + p - c.pbaseB;
+                if (pw < 0) { if (!(c.flags & kChunkWide)) ba->chunk_error = true; continue; }   // a wide landmark's other groups
+                if (row[pw * kSMaxLm + ls] != -1) { ba->chunk_error = true; continue; }
                 row[pw * kSMaxLm + ls] = q;
                 int& rg = ba->batch_rng[c.batch0 + b];   // used pose slots of the batch: lo | hi << 8
                 const int lo = std::min(rg & 0xff, pw), hi = std::max((rg >> 8) & 0xff, pw);
                 rg = lo | (hi << 8);
             }
         }
-    ba->reach.assign(K, -1);
-    for (const SchurChunk& c : ba->chunks)
-        for (int p = c.pbase; p < c.pbase + c.span; ++p) ba->reach[p] = std::max(ba->reach[p], c.pbase + c.span - 1);
     ba->free_pose.clear();
     for (int k = 0; k < K; ++k) if (ba->free_map[k] >= 0) ba->free_pose.push_back(k);
     ba->red_band = 1;
@@ -736,6 +788,19 @@ extern "C" int vio360_ba_set_structure(vio360_ba* ba, const int32_t* pose_idx, c
     cam_const_init(ba->cam, cols, rows, info, T_cb, huber_delta);
     ba->h_pose = s_pose;
     if (ba->peer.exported) ba->peer.stale = true;   // the exported row ranges / band width describe the old structure
+    {   // block columns of the band of S over ALL landmarks (every rank computes the same number): at least kSWin, the
+        // chunk window, and as wide as the widest landmark's span of free poses
+        int wmax = 1;
+        for (int l = 0; l < M; ++l) {
+            int fmin = K, fmax = -1;
+            for (int q = ba->lm_ptr[l]; q < ba->lm_ptr[l + 1]; ++q) {
+                const int f = ba->free_map[s_pose[q]];
+                if (f >= 0) { fmin = std::min(fmin, f); fmax = std::max(fmax, f); }
+            }
+            if (fmax >= fmin) wmax = std::max(wmax, fmax - fmin + 1);
+        }
+        ba->band_blocks = std::max(kSWin, wmax);
+    }
     compute_shard(ba);
 
     cudaStream_t st = ctx->stream;
@@ -1011,6 +1076,13 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
             VIO_CUDA(ctx, cudaMemcpy(ba->d_slots.p, ba->slot_table.data(), ba->slot_table.size() * 4, cudaMemcpyHostToDevice));
             VIO_CUDA(ctx, ba->d_batch_rng.reserve(ba->batch_rng.size() * 4));
             VIO_CUDA(ctx, cudaMemcpy(ba->d_batch_rng.p, ba->batch_rng.data(), ba->batch_rng.size() * 4, cudaMemcpyHostToDevice));
+            VIO_CUDA(ctx, ba->d_batch_lm.reserve(ba->batch_lm.size() * 4));
+            VIO_CUDA(ctx, cudaMemcpy(ba->d_batch_lm.p, ba->batch_lm.data(), ba->batch_lm.size() * 4, cudaMemcpyHostToDevice));
+            VIO_CUDA(ctx, ba->d_wide.reserve(std::max<size_t>(1, ba->wide.size()) * 4));
+            if (!ba->wide.empty()) {
+                VIO_CUDA(ctx, cudaMemcpy(ba->d_wide.p, ba->wide.data(), ba->wide.size() * 4, cudaMemcpyHostToDevice));
+                VIO_CUDA(ctx, ba->d_wide_inv.reserve((size_t)ba->M * 9 * 8));
+            }
             VIO_CUDA(ctx, cudaMemcpy(ba->d_reach.p, ba->reach.data(), ba->reach.size() * 4, cudaMemcpyHostToDevice));
             if (!ba->chunks.empty()) VIO_CUDA(ctx, cudaMemcpy(ba->d_chunks.p, ba->chunks.data(), ba->chunks.size() * sizeof(SchurChunk), cudaMemcpyHostToDevice));
             VIO_CUDA(ctx, cudaMemcpy(ba->d_cov_ptr.p, ba->cov_ptr.data(), ba->cov_ptr.size() * 4, cudaMemcpyHostToDevice));
@@ -1024,18 +1096,27 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
             VIO_CUDA(ctx, cudaFuncSetAttribute(k_schur_tile<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSchurSmemBytes));
             ba->smem_attr_set = true;
         }
+        if (nch > 0 && !ba->wide.empty()) {   // pass 1 of the wide landmarks: (E'E + D^2)^-1 over all their observations
+            const int nw = (int)ba->wide.size();
+            KernelTimer kt_(ctx, "k_wide_prepare");
+            if (ba->eval_f32) k_wide_prepare<float><<<(nw * 32 + 127) / 128, 128, 0, st>>>(d, ba->d_wide.as<int>(), nw, apply_loss != 0, ba->d_wide_inv.as<double>());
+            else k_wide_prepare<double><<<(nw * 32 + 127) / 128, 128, 0, st>>>(d, ba->d_wide.as<int>(), nw, apply_loss != 0, ba->d_wide_inv.as<double>());
+        }
+        if (nch > 0 && !ba->wide.empty()) VIO_LAUNCH_CHECK(ctx);
         if (nch > 0) {
             { KernelTimer kt_(ctx, ba->eval_f32 ? "k_schur_tile_f32" : "k_schur_tile");
             if (ba->eval_f32)
-                k_schur_tile<float><<<nch, kSThreads, kSchurSmemBytes, st>>>(d, ba->d_chunks.as<SchurChunk>(), ba->d_slots.as<int>(), ba->d_batch_rng.as<int>(), apply_loss != 0,
+                k_schur_tile<float><<<nch, kSThreads, kSchurSmemBytes, st>>>(d, ba->d_chunks.as<SchurChunk>(), ba->d_slots.as<int>(), ba->d_batch_rng.as<int>(),
+                                                                           ba->d_batch_lm.as<int>(), ba->d_wide_inv.as<double>(), apply_loss != 0,
                                                                            ba->d_partS.as<double>(), ba->d_partRhs.as<double>(), ba->d_partials.as<double>());
             else
-                k_schur_tile<double><<<nch, kSThreads, kSchurSmemBytes, st>>>(d, ba->d_chunks.as<SchurChunk>(), ba->d_slots.as<int>(), ba->d_batch_rng.as<int>(), apply_loss != 0,
+                k_schur_tile<double><<<nch, kSThreads, kSchurSmemBytes, st>>>(d, ba->d_chunks.as<SchurChunk>(), ba->d_slots.as<int>(), ba->d_batch_rng.as<int>(),
+                                                                            ba->d_batch_lm.as<int>(), ba->d_wide_inv.as<double>(), apply_loss != 0,
                                                                             ba->d_partS.as<double>(), ba->d_partRhs.as<double>(), ba->d_partials.as<double>());
             }
             VIO_LAUNCH_CHECK(ctx);
         }
-        if (ctx->debug_sync) { fprintf(stderr, "schur: n=%d nch=%d nirr=%d K=%d cov=%zu\n", n, nch, nirr, ba->K, ba->cov_idx.size() / 2); for (auto& c : ba->chunks) fprintf(stderr, "  chunk lm[%d,%d) pbase %d span %d batch0 %d\n", c.lm_begin, c.lm_end, c.pbase, c.span, c.batch0); }
+        if (ctx->debug_sync) { fprintf(stderr, "schur: n=%d nch=%d (regular %d) wide=%zu nirr=%d K=%d cov=%zu\n", n, nch, ba->n_regular_chunks, ba->wide.size(), nirr, ba->K, ba->cov_idx.size() / 4); for (auto& c : ba->chunks) fprintf(stderr, "  chunk %d landmarks, poses %d+%d | %d+%d, flags %d, batch0 %d\n", c.lm_end, c.pbase, c.span, c.pbaseB, c.spanB, c.flags, c.batch0); }
         const bool fused = nirr == 0 && n > 0;   // one pass: sum slabs, mirror, LM diagonal, cost
         if (n > 0) {
             const double* Dp = ba->use_D ? ba->d_D.as<double>() : nullptr;
@@ -1053,7 +1134,7 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
                     // landmarks touch are summed (the other ranks never read the rest), the LM diagonal is
                     // added by the exchange kernel
                     band_w = ba->peer.band_w;
-                    if (band_w != std::min(ba->n_free, kSWin) || ba->peer.n_free != ba->n_free)
+                    if (band_w != std::min(ba->n_free, ba->band_blocks) || ba->peer.n_free != ba->n_free)
                         return vio360_fail(ctx, VIO360_ERR_STATE, "ba_build_reduced_system: the structure changed after vio360_ba_peer_export");
                     outS = peer_band(ba, ba->shard_rank, ba->peer.epoch + 1);
                     outRhs = outS + (size_t)ba->n_free * band_w * 36; outCost = outRhs + n;
@@ -1062,7 +1143,7 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
                 } else if (sharded) {
                     // compact exchange buffer: chunk windows are kSWin poses wide on every rank, so block
                     // row bi never reaches past bi + kSWin - 1 (every slot inside the grid is rewritten)
-                    band_w = std::min(ba->n_free, kSWin);
+                    band_w = std::min(ba->n_free, ba->band_blocks);
                     const size_t nd = (size_t)ba->n_free * band_w * 36 + n + 1;
                     if (ba->d_band.bytes < nd * 8) {
                         VIO_CUDA(ctx, ba->d_band.reserve(nd * 8));
@@ -1102,7 +1183,7 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
 #define VIO_REDUCE_LAUNCH(L)                                                                                                   \
                 k_schur_reduce<true, L><<<nblk, 36 * L, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(), \
                                                            ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),  \
-                                                           ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int2>(), ba->d_reach.as<int>(), \
+                                                           ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int4>(), ba->d_reach.as<int>(), \
                                                            ba->d_free_pose.as<int>(), Dp, add_diag, band, band_w, row0, ba->n_free, pub)
                 if (lanes <= 3) VIO_REDUCE_LAUNCH(3);
                 else if (lanes <= 5) VIO_REDUCE_LAUNCH(5);
@@ -1116,7 +1197,7 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
                 KernelTimer kt_(ctx, "k_schur_reduce");
                 k_schur_reduce<false, 7><<<nblk, 36 * 7, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(),
                                                             ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),
-                                                            ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int2>(), ba->d_reach.as<int>(),
+                                                            ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int4>(), ba->d_reach.as<int>(),
                                                             ba->d_free_pose.as<int>(), Dp, false, false, 0, 0, ba->n_free, PeerPublish{});
             }
             VIO_LAUNCH_CHECK(ctx);
@@ -1209,13 +1290,13 @@ extern "C" int vio360_ba_peer_export(vio360_ba* ba, void* blob_out) {
     if (ba->shard_world < 2 || ba->shard_world > kMaxPeers)
         return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_export: needs a shard with 2..%d ranks (vio360_ba_set_shard)", kMaxPeers);
     if (!ba->irregular.empty() || ba->chunk_error || ba->n_free <= 0)
-        return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_export: %zu landmarks of this shard fit no chunk window, so the build has no block band; allreduce the dense buffer instead", ba->irregular.size());
+        return vio360_fail(ctx, VIO360_ERR_STATE, "ba_peer_export: %zu landmarks of this shard are observed twice from one pose (the reference never builds such a window), so the build has no block band; allreduce the dense buffer instead", ba->irregular.size());
     VIO_CUDA(ctx, cudaSetDevice(ctx->device));
     VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     peer_release(ba);
     auto& P = ba->peer;
     P.world = ba->shard_world;
-    P.n_free = ba->n_free; P.band_w = std::min(ba->n_free, kSWin);
+    P.n_free = ba->n_free; P.band_w = std::min(ba->n_free, ba->band_blocks);
     P.nd = (size_t)P.n_free * P.band_w * 36 + 6 * (size_t)P.n_free + 1;
     P.nd_pad = (P.nd + 15) & ~(size_t)15;
     P.header_bytes = (kPeerHeaderBytes + ((size_t)(kMaxPeers + 1) * P.n_free + 4) * 4 + 127) & ~(size_t)127;   // row flags, row counters, rows-done counter
@@ -1647,7 +1728,7 @@ extern "C" int vio360_ba_lm_solve(vio360_ba* ba, const vio360_lm_options* opt, d
     if (!ba->has_structure) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_lm_solve before ba_set_structure");
     if (!opt || !pose_delta || !points || !summary) return vio360_fail(ctx, VIO360_ERR_INVALID, "ba_lm_solve: null argument");
     if (ba->shard_world > 1) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_lm_solve runs on an unsharded window (vio360_ba_set_shard(0, 1))");
-    if (!ba->irregular.empty()) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_lm_solve: %zu landmarks fit no chunk window", ba->irregular.size());
+    if (!ba->irregular.empty()) return vio360_fail(ctx, VIO360_ERR_STATE, "ba_lm_solve: %zu landmarks are observed twice from one pose", ba->irregular.size());
     int rc = vio360_ba_set_parameters(ba, pose_delta, points);     // x0 to the device, pose chain at x0
     if (rc) return rc;
     VIO_CUDA(ctx, cudaSetDevice(ctx->device));

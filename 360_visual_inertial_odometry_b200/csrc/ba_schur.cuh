@@ -45,9 +45,15 @@ constexpr int kSK = 3 * kSMaxLm;                   // 48 stage columns per batch
 constexpr int kSZPitch = 148;                      // doubles per stage column (>= kST, == 4 mod 16: conflict-free fragments)
 constexpr int kSRed = 9;                           // doubles per observation in the reduction scratch
 
-// batch0: first row of the slot table that belongs to this chunk (one row of kSProd observation
-// indices, -1 = empty, per batch of kSMaxLm landmarks; built on the host in ba.cu:build_chunks)
-struct SchurChunk { int lm_begin, lm_end, pbase, span, batch0, pad0, pad1, pad2; };
+constexpr int kSGrp = kSWin / 2;                   // poses per group of a wide landmark's jobs
+constexpr int kChunkWide = 1;                      // flags: (E'E + D^2)^-1 of the landmarks comes from k_wide_prepare
+constexpr int kChunkCross = 2;                     //        two pose groups; only the blocks between them are this chunk's
+
+// lm_begin .. lm_end: positions in the chunk's landmark list (batch_lm[(batch0 + b) * kSMaxLm + ls] = landmark id, -1
+// = empty slot); batch0: first row of the slot table that belongs to this chunk (one row of kSProd observation
+// indices, -1 = empty, per batch of kSMaxLm landmarks; built on the host in ba.cu:build_chunks).  pose slots
+// 0 .. span-1 hold poses pbase ..; for a cross chunk slots kSGrp .. kSGrp+spanB-1 hold poses pbaseB ..
+struct SchurChunk { int lm_begin, lm_end, pbase, span, batch0, pbaseB, spanB, flags; };
 
 constexpr size_t kSchurSmemBytes =
     sizeof(double) * (2 * (size_t)kSK * kSZPitch + (size_t)kSTiles * 64 + (size_t)kSWin * kPoseStride + (size_t)kSMaxLm * 9 + 32) +

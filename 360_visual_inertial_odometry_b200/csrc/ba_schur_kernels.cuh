@@ -27,7 +27,8 @@ constexpr int kBarProd = 1, kBarFull = 2, kBarEmpty = 4;   // ids: producers-onl
 // results are widened and phases B / C / D (sums, 3x3 Cholesky, F'F, Z, the SYRK) stay in double.
 template <typename PT>
 __global__ void __launch_bounds__(kSThreads, 1)
-k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restrict__ slots, const int* __restrict__ batch_rng, bool apply_loss,
+k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restrict__ slots, const int* __restrict__ batch_rng,
+             const int* __restrict__ batch_lm, const double* __restrict__ wide_inv, bool apply_loss,
              double* __restrict__ partS,
              double* __restrict__ partRhs, double* __restrict__ partCost) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -45,6 +46,12 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
         sPose[i] = v;
         if (sizeof(PT) == 4) sPoseF[i] = (float)v;
     }
+    for (int i = tid; i < ch.spanB * kPoseStride; i += kSThreads) {   // second pose group of a cross chunk: slots kSGrp ..
+        const double v = d.posebuf[(size_t)ch.pbaseB * kPoseStride + i];
+        sPose[kSGrp * kPoseStride + i] = v;
+        if (sizeof(PT) == 4) sPoseF[kSGrp * kPoseStride + i] = (float)v;
+    }
+    const bool wide = (ch.flags & kChunkWide) != 0, cross = (ch.flags & kChunkCross) != 0;
     __syncthreads();
     const int nbatch = (ch.lm_end - ch.lm_begin + kSMaxLm - 1) / kSMaxLm;
     double pacc0 = 0.0, pacc1 = 0.0;   // producer lane j of pose slot w: entries 2j, 2j+1 of [F'F tri (21) | F'(r - E ig) (6)]
@@ -54,14 +61,17 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
         // ================= producers: thread = (pose slot w, landmark slot ls) =================
         const int w = tid >> 4, ls = tid & 15;
         const int* myslot = slots + (size_t)ch.batch0 * kSProd + tid;
+        const int* mylm = batch_lm + (size_t)ch.batch0 * kSMaxLm;    // landmark ids of the chunk's batches
         int oi_next = nbatch > 0 ? __ldg(myslot) : -1;   // observation of slot (w, ls) in batch 0
-        const bool pose_const = w < ch.span ? d.free_map[ch.pbase + w] < 0 : true;
+        bool pose_const = true;
+        if (w < ch.span) pose_const = d.free_map[ch.pbase + w] < 0;
+        else if (w >= kSGrp && w - kSGrp < ch.spanB) pose_const = d.free_map[ch.pbaseB + w - kSGrp] < 0;
         // observation data of the batch about to be evaluated: fetched one batch ahead (after
         // phase A of the previous batch), so that no global-memory latency sits in phase A
         double nu = 0.0, nv = 0.0, nP0 = 0.0, nP1 = 0.0, nP2 = 0.0;
         bool nout = false;
         if (oi_next >= 0) {
-            const size_t l = (size_t)(ch.lm_begin + ls);
+            const size_t l = (size_t)__ldg(mylm + ls);
             nu = __ldg(d.u + oi_next); nv = __ldg(d.v + oi_next); nout = __ldg(d.outlier + oi_next) != 0;
             nP0 = __ldg(d.points + 3 * l); nP1 = __ldg(d.points + 3 * l + 1); nP2 = __ldg(d.points + 3 * l + 2);
         }
@@ -78,8 +88,10 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
             if (tid < kSMaxLm * 16) {
                 const int bl = tid >> 4, e = tid & 15;
                 if (bl < NB) {
-                    if (e == 9) pre = __ldg(d.point_fixed + cur + bl) != 0 ? 1.0 : 0.0;
-                    else if (e >= 10 && e < 13 && d.D) pre = __ldg(d.D + 6 * (size_t)d.K + 3 * (size_t)(cur + bl) + (e - 10));
+                    const int lid = __ldg(mylm + (size_t)b * kSMaxLm + bl);
+                    if (wide) { if (e < 9) pre = __ldg(wide_inv + 9 * (size_t)lid + e); }   // L^-1 (6), (E'E + D^2)^-1 g (3) of the WHOLE landmark
+                    else if (e == 9) pre = __ldg(d.point_fixed + lid) != 0 ? 1.0 : 0.0;
+                    else if (e >= 10 && e < 13 && d.D) pre = __ldg(d.D + 6 * (size_t)d.K + 3 * (size_t)lid + (e - 10));
                 } else if (e == 9) pre = 1.0;
             }
             if (b >= 2) named_bar_sync(kBarEmpty + (b & 1), kSThreads);   // consumers are done with this stage
@@ -109,7 +121,7 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
                 }
             }
             if (b + 1 < nbatch && oi_next >= 0) {
-                const size_t l = (size_t)(cur + kSMaxLm + ls);
+                const size_t l = (size_t)__ldg(mylm + (size_t)(b + 1) * kSMaxLm + ls);
                 nu = __ldg(d.u + oi_next); nv = __ldg(d.v + oi_next); nout = __ldg(d.outlier + oi_next) != 0;
                 nP0 = __ldg(d.points + 3 * l); nP1 = __ldg(d.points + 3 * l + 1); nP2 = __ldg(d.points + 3 * l + 2);
             }
@@ -123,7 +135,10 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
             // ---- phase B: per-landmark sums over the pose slots, Cholesky, L^-1, (E'E)^-1 g.
             // thread (bl, e) = tid>>4, tid&15 sums entry e < 9 of landmark bl; the nine sums of a
             // landmark sit in one half warp and are gathered by shuffles, lane e == 0 factorises.
-            if (tid < kSMaxLm * 16) {   // 8 whole warps
+            if (wide) {
+                // pass 1 (k_wide_prepare) factorised E'E + D^2 over ALL observations of the landmark: lanes e < 9 hold it
+                if (tid < kSMaxLm * 16 && (tid & 15) < 9) sLmk[(tid >> 4) * 9 + (tid & 15)] = pre;
+            } else if (tid < kSMaxLm * 16) {   // 8 whole warps
                 const int bl = tid >> 4, e = tid & 15;
                 double sum = 0.0;
                 if (e < 9) {   // four independent partial sums: a 6-deep instead of a 24-deep add chain
@@ -211,7 +226,7 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
                 SCHUR_RS_STEP(2, 4)
                 SCHUR_RS_STEP(1, 2)
 #undef SCHUR_RS_STEP
-                pacc0 += x[0]; pacc1 += x[1];
+                if (!cross) { pacc0 += x[0]; pacc1 += x[1]; }   // a cross chunk owns no diagonal block, rhs entry or cost
             }
             // ---- operand stage: Z = (F'E) L^-T (zero for empty slots, constant poses and constant landmarks)
             {
@@ -322,7 +337,7 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
     // two columns (even, odd) always fall into the same 6-wide block.
     {
         double* outS = partS + (size_t)blockIdx.x * kST * kST;
-        const int nt = 2 * ((6 * ch.span + 15) >> 4);
+        const int nt = cross ? kSNT : 2 * ((6 * ch.span + 15) >> 4);
         const int fr = lane >> 2, fc = lane & 3;
         for (int ti = 0; ti < nt; ++ti) {
             const int R = 8 * ti + fr, rb = R / 6, ra = R - 6 * rb;
@@ -334,6 +349,7 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
         }
     }
     // ---- cost of the chunk
+    if (cross) cost = 0.0;
     cost = warp_sum(cost);
     if (lane == 0) sBlk[warp] = cost;
     __syncthreads();
@@ -377,7 +393,7 @@ __device__ __forceinline__ void schur_reduce_block(const int bi, const int bj, c
                                                    double* __restrict__ rhs, double* __restrict__ cost_out,
                                                    const double* __restrict__ partS, const double* __restrict__ partRhs,
                                                    const double* __restrict__ partCost, int nchunks,
-                                                   const int* __restrict__ cov_ptr, const int2* __restrict__ cov_idx,
+                                                   const int* __restrict__ cov_ptr, const int4* __restrict__ cov_idx,
                                                    const int* __restrict__ reach, const int* __restrict__ free_pose,
                                                    const double* __restrict__ D, bool add_diag, int band_w,
                                                    double (*part)[36], double (*partR)[6]) {
@@ -393,20 +409,17 @@ __device__ __forceinline__ void schur_reduce_block(const int bi, const int bj, c
         // four chunks per round: the (chunk, window) entries and the slab loads of a round are
         // independent, so a walker pays two memory latencies per four chunks instead of per chunk
         for (int q = q0 + g; q < q1; q += 4 * kRedLanes) {
-            int c[4];
-            int2 win[4];
+            int4 ent[4];   // {chunk, slot of pose pi, first column pose | columns << 16, slot of the first column}
             double v[4], vr[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const int2 ent = q + u * kRedLanes < q1 ? __ldg(cov_idx + q + u * kRedLanes) : make_int2(-1, 0);
-                c[u] = ent.x; win[u] = make_int2(ent.y & 0xffff, ent.y >> 16);   // (pbase, span)
-            }
+            for (int u = 0; u < 4; ++u) ent[u] = q + u * kRedLanes < q1 ? __ldg(cov_idx + q + u * kRedLanes) : make_int4(-1, 0, 0, 0);
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-                v[u] = (in_env && c[u] >= 0 && pj < win[u].x + win[u].y)   // pj >= pi >= pbase
-                           ? partS[(size_t)c[u] * kST * kST + (size_t)((pi - win[u].x) * kSWin + (pj - win[u].x)) * 36 + e]   // pose-block major slab
+                const int first = ent[u].z & 0xffff, cols = ent[u].z >> 16;
+                v[u] = (in_env && ent[u].x >= 0 && pj >= first && pj < first + cols)
+                           ? partS[(size_t)ent[u].x * kST * kST + (size_t)(ent[u].y * kSWin + (ent[u].w + pj - first)) * 36 + e]   // pose-block major slab
                            : 0.0;
-                vr[u] = (do_rhs && c[u] >= 0) ? partRhs[(size_t)c[u] * kST + 6 * (pi - win[u].x) + e] : 0.0;
+                vr[u] = (do_rhs && ent[u].x >= 0) ? partRhs[(size_t)ent[u].x * kST + 6 * ent[u].y + e] : 0.0;
             }
             s += (v[0] + v[1]) + (v[2] + v[3]);
             sr += (vr[0] + vr[1]) + (vr[2] + vr[3]);
@@ -448,12 +461,68 @@ __device__ __forceinline__ void schur_reduce_block(const int bi, const int bj, c
     }
 }
 
+// Pass 1 for WIDE landmarks (observing poses span more than kSWin): one warp per landmark sums E'E (+ D^2) and E'r over
+// ALL its observations, factorises E'E = L L' and leaves L^-1 (6) and (E'E)^-1 g (3) for the chunk kernel, whose
+// jobs each see only two pose groups of the landmark.  Same arithmetic as phase B of k_schur_tile.
+template <typename PT>
+__global__ void __launch_bounds__(128) k_wide_prepare(BaDev d, const int* __restrict__ wide, int n_wide, bool apply_loss, double* __restrict__ wide_inv) {
+    const int wi = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (wi >= n_wide) return;
+    const int l = wide[wi];
+    const double Pw[3] = {d.points[3 * (size_t)l], d.points[3 * (size_t)l + 1], d.points[3 * (size_t)l + 2]};
+    double hq[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    for (int q = d.lm_ptr[l] + lane; q < d.lm_ptr[l + 1]; q += 32) {
+        double r[2], F[12], E[6], pose[kPoseStride];
+        const int p = d.pose[q];
+#pragma unroll
+        for (int j = 0; j < kPoseStride; ++j) pose[j] = __ldg(d.posebuf + kPoseStride * (size_t)p + j);
+        eval_obs_as<PT>(pose, Pw, d.u[q], d.v[q], d.outlier[q] != 0, d.cam, apply_loss, r, F, E);
+        hq[0] += E[0] * E[0] + E[3] * E[3]; hq[1] += E[0] * E[1] + E[3] * E[4]; hq[2] += E[0] * E[2] + E[3] * E[5];
+        hq[3] += E[1] * E[1] + E[4] * E[4]; hq[4] += E[1] * E[2] + E[4] * E[5]; hq[5] += E[2] * E[2] + E[5] * E[5];
+        hq[6] += E[0] * r[0] + E[3] * r[1]; hq[7] += E[1] * r[0] + E[4] * r[1]; hq[8] += E[2] * r[0] + E[5] * r[1];
+    }
+#pragma unroll
+    for (int j = 0; j < 9; ++j) hq[j] = warp_sum(hq[j]);
+    if (lane != 0) return;
+    double li[6] = {0, 0, 0, 0, 0, 0}, ig[3] = {0, 0, 0};
+    if (d.point_fixed[l] == 0) {
+        if (d.D) {
+            const double* Dl = d.D + 6 * (size_t)d.K + 3 * (size_t)l;
+            hq[0] += Dl[0] * Dl[0]; hq[3] += Dl[1] * Dl[1]; hq[5] += Dl[2] * Dl[2];
+        }
+        const double i00 = vio_rsqrt(hq[0]);
+        const double l10 = hq[1] * i00, l20 = hq[2] * i00;
+        const double i11 = vio_rsqrt(hq[3] - l10 * l10);
+        const double l21 = (hq[4] - l20 * l10) * i11;
+        const double i22 = vio_rsqrt(hq[5] - l20 * l20 - l21 * l21);
+        const double i10 = -l10 * i00 * i11;
+        const double i21 = -l21 * i11 * i22;
+        const double i20 = -(l20 * i00 + l21 * i10) * i22;
+        li[0] = i00; li[1] = i10; li[2] = i11; li[3] = i20; li[4] = i21; li[5] = i22;
+        bool ok = true;
+#pragma unroll
+        for (int j = 0; j < 6; ++j) ok = ok && isfinite(li[j]);
+        if (!ok) {
+#pragma unroll
+            for (int j = 0; j < 6; ++j) li[j] = 0.0;
+        }
+        const double y0 = li[0] * hq[6], y1 = li[1] * hq[6] + li[2] * hq[7], y2 = li[3] * hq[6] + li[4] * hq[7] + li[5] * hq[8];
+        ig[0] = li[0] * y0 + li[1] * y1 + li[3] * y2;
+        ig[1] = li[2] * y1 + li[4] * y2;
+        ig[2] = li[5] * y2;
+    }
+    double* q = wide_inv + 9 * (size_t)l;
+#pragma unroll
+    for (int j = 0; j < 6; ++j) q[j] = li[j];
+    q[6] = ig[0]; q[7] = ig[1]; q[8] = ig[2];
+}
+
 template <bool FULL, int kRedLanes>
 __global__ void __launch_bounds__(36 * kRedLanes)
 k_schur_reduce(double* __restrict__ S, int n, double* __restrict__ rhs, double* __restrict__ cost_out,
                const double* __restrict__ partS, const double* __restrict__ partRhs, const double* __restrict__ partCost,
                int nchunks, const SchurChunk* __restrict__ chunks, const int* __restrict__ cov_ptr,
-               const int2* __restrict__ cov_idx, const int* __restrict__ reach, const int* __restrict__ free_pose,
+               const int4* __restrict__ cov_idx, const int* __restrict__ reach, const int* __restrict__ free_pose,
                const double* __restrict__ D, bool add_diag, bool band_grid, int band_w, int row0, int n_free, const PeerPublish pub) {
     // band_grid: blockIdx.x counts block columns from the diagonal (the host sized the grid to the
     // widest row of the envelope and zeroed S outside it once per structure).  row0: first block row

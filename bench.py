@@ -606,7 +606,7 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
         ms = timed(steps)                          # the step as a caller runs it
         ctx.enable_kernel_timing(True); ctx.reset_kernel_times()
         ms_events = timed(steps)                   # again with an event pair around every kernel (per-kernel times; ~2 us each)
-        ktimes = {name: ctx.kernel_time(name) for name in ("k_schur_tile", "k_schur_reduce", "k_schur_warp", "k_finish_S", "k_sum_partials", "k_expand_band", "k_band_pull")}
+        ktimes = {name: ctx.kernel_time(name) for name in ("k_wide_prepare", "k_schur_tile", "k_schur_reduce", "k_schur_warp", "k_finish_S", "k_sum_partials", "k_expand_band", "k_band_pull")}
         per_rank = None
         if multi:   # every rank's kernel times: the exchange kernel's time includes waiting for the slowest rank
             per_rank = [None] * world
@@ -742,6 +742,10 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
         r5["nccl_variant"]["kernel_ms_per_step"] = rn["roofline"]["kernel_ms_per_step"]
         r5["nccl_variant"]["S_trace"] = rn["S_trace"]
     res["c5_large_window"] = r5
+    # SURVEY 8-D / 8-E dense variant: 20 000 landmarks of degree 50 (the Schur-dominated regime).  Every landmark spans
+    # more than the 24-pose chunk window: pass 1 (k_wide_prepare) + group-pair jobs of the same chunk kernel, no atomics
+    wind = syn.make_ba_window(K=200, M=20000, degree=50, seed=1000001, mid_iteration=True, loop_radius=6.0)
+    res["dense_window_degree50"] = run(wind, max(2, args.ba_steps // 2), 2, True, "peer")
     res["value"] = r5["value"]; res["n_gpus"] = world
     res["config"] = {"workload": "configs[4]: 200 keyframes, 1M observations, landmark-range sharding, reduced-camera-system blocks summed over NVLink peer memory (NCCL allreduce variant reported beside it)"}
     if rank == 0 and world == 1 and not args.skip_cpu:

@@ -157,6 +157,65 @@ def test_high_degree_landmarks(bindings, ctx, synthetic):
     _check_window(bindings, ctx, win)
 
 
+def test_wide_landmarks_without_atomics(bindings, ctx, synthetic):
+    """landmarks whose observing poses span more than the 24-pose chunk window (a loop closure, a
+    degree-50 landmark) are eliminated by the chunk kernel too -- pass 1 (k_wide_prepare) factorises E'E over all their
+    observations, group-pair jobs contribute the blocks -- so the fp64-atomic kernel k_schur_warp is not launched, the
+    build is deterministic (bit-identical when repeated) and still within 1e-9 of the oracle; mixed with regular
+    landmarks, constant points, constant poses, outlier flags, with and without the LM diagonal."""
+    rng = np.random.default_rng(4)
+    # (a) every landmark wide: degree 50 on 120 poses; (b) a regular band plus loop closures
+    wa = synthetic.make_ba_window(K=120, M=300, degree=50, seed=31, mid_iteration=True, loop_radius=5.0)
+    wb = synthetic.make_ba_window(K=60, M=400, degree=8, seed=32, mid_iteration=True, loop_radius=4.0)
+    # loop closure: 40 landmarks of the first poses are also seen from the last ones
+    import ba_ref_np
+    extra_p, extra_l, extra_u, extra_v = [], [], [], []
+    for l in range(0, 40):
+        for p in (55, 57, 59):     # the loop closes: pose 59 stands next to pose 0
+            Rcw, tcw, _, _ = ba_ref_np.pose_chain(wb["Twb_init"][p], wb["Tcb"], wb["pose_delta"][p])
+            u, v = synthetic.erp_project((Rcw @ wb["points"][l] + tcw)[None, :], wb["cols"], wb["rows"])
+            u, v = float(u[0]) + rng.normal(), float(v[0]) + rng.normal()
+            if 20 < u < wb["cols"] - 20 and 20 < v < wb["rows"] - 20:
+                extra_p.append(p); extra_l.append(l); extra_u.append(np.float64(np.float32(u))); extra_v.append(np.float64(np.float32(v)))
+    assert len(extra_p) > 60
+    wb = dict(wb)
+    wb["pose_idx"] = np.concatenate([wb["pose_idx"], np.array(extra_p, np.int32)]); wb["point_idx"] = np.concatenate([wb["point_idx"], np.array(extra_l, np.int32)])
+    wb["obs_u"] = np.concatenate([wb["obs_u"], np.array(extra_u)]); wb["obs_v"] = np.concatenate([wb["obs_v"], np.array(extra_v)])
+    wb["outlier"] = np.concatenate([wb["outlier"], np.zeros(len(extra_p), np.uint8)]); wb["O"] = len(wb["obs_u"])
+    wb["pose_fixed"] = wb["pose_fixed"].copy(); wb["pose_fixed"][30] = 1
+    for win in (wa, wb):
+        ref = _oracle_all(win)
+        ba = bindings.BAWindow(ctx, win)
+        ba.set_parameters(win["pose_delta"], win["points"])
+        ctx.enable_kernel_timing(True); ctx.reset_kernel_times()
+        S, rhs, cost = ba.build_reduced_system(ref["D"], True)
+        S2, rhs2, cost2 = ba.build_reduced_system(ref["D"], True)
+        assert ctx.kernel_time("k_schur_warp")[1] == 0 and ctx.kernel_time("k_wide_prepare")[1] == 2
+        ctx.enable_kernel_timing(False)
+        assert rel_err(S, ref["S"]) < TOL and rel_err(rhs, ref["rhs"]) < TOL and abs(cost - ref["cost"]) < TOL * ref["cost"]
+        assert np.array_equal(S, S2) and np.array_equal(rhs, rhs2) and cost == cost2          # no atomics: bit-identical
+        assert np.array_equal(S, S.T)
+        ba.set_lm_diagonal(None)
+        S0, rhs0, _ = ba.build_reduced_system(None, True)                                       # without an LM diagonal
+        W = ba_oracle.Window(win)
+        So, rhso, _ = W.schur(ref["r"], ref["Jp"], ref["Jl"], None)
+        # without the diagonal a constant-free landmark seen from few poses can be ill conditioned: compare on the scale of S
+        assert rel_err(S0, So) < 1e-8 and rel_err(rhs0, rhso) < 1e-8
+        # solve + back substitution through the general envelope factorisation
+        ba.build_reduced_system(ref["D"], True)
+        dp, dl = ba.solve_reduced(True)
+        odp, odl = W.solve_step(ref["r"], ref["Jp"], ref["Jl"], ref["D"], ref["S"], ref["rhs"], W.schur(ref["r"], ref["Jp"], ref["Jl"], ref["D"])[2])
+        assert rel_err(dp, odp) < 1e-7 and rel_err(dl, odl) < 1e-7
+        # sharded: the partial systems of three ranks sum to the full one (wide landmarks in every shard)
+        Ssum = np.zeros_like(S); rsum = np.zeros_like(rhs)
+        for rnk in range(3):
+            ba.set_shard(rnk, 3)
+            Sp, rp, _ = ba.build_reduced_system(ref["D"], True)
+            Ssum += Sp; rsum += rp
+        assert rel_err(Ssum, ref["S"]) < TOL and rel_err(rsum, ref["rhs"]) < TOL
+        ba.close()
+
+
 def test_outlier_flags_and_reuse(bindings, ctx, synthetic):
     win = synthetic.make_ba_window(K=6, M=150, seed=3, mid_iteration=True)
     ba = bindings.BAWindow(ctx, win)
