@@ -272,6 +272,9 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
                 while (rem >= nb2 - bi) { rem -= nb2 - bi; ++bi; }
                 const int bj = blo + bi + rem;
                 bi += blo;
+                // a cross chunk owns only the blocks between its two pose groups: 16-row blocks 0..4 hold group A
+                // (rows < 72), blocks 4..8 group B
+                if (cross && (bi > (6 * kSGrp - 1) / 16 || bj < (6 * kSGrp) / 16)) continue;
                 const bool diag = bi == bj;
                 double2* c00 = reinterpret_cast<double2*>(St + schur_tile_index(2 * bi, 2 * bj) * 64) + lane;
                 double2* c01 = reinterpret_cast<double2*>(St + schur_tile_index(2 * bi, 2 * bj + 1) * 64) + lane;
