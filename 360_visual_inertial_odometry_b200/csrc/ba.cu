@@ -102,6 +102,14 @@ struct vio360_ba {
 static double* peer_band(vio360_ba* ba, int r, unsigned epoch) {
     return reinterpret_cast<double*>(static_cast<char*>(ba->peer.base[r]) + ba->peer.header_bytes) + (size_t)(epoch & 1u) * ba->peer.nd_pad;
 }
+// How a rank's band reaches the peers (VIO360_PEER_PUBLISH).  0 / 1 / 2: k_schur_reduce counts finished blocks and
+// releases rows (0, 1) or the whole band (2) as they complete -- measured on 2 B200 (profiles/r02_peer_publish_modes.txt):
+// the per-CTA barrier + fence + atomic costs the reduce 13-40 us and buys nothing while the ranks run in lock step.
+// 3 (default): the reduce is untouched and CTA 0 of the pull kernel announces.
+static int peer_publish_mode() {
+    static const int m = getenv("VIO360_PEER_PUBLISH") ? atoi(getenv("VIO360_PEER_PUBLISH")) : 3;
+    return m;
+}
 static unsigned* peer_row_flags(vio360_ba* ba, int r) {     // rank r's row-flag array [src rank][n_free]
     return reinterpret_cast<unsigned*>(static_cast<char*>(ba->peer.base[r]) + kPeerHeaderBytes);
 }
@@ -1167,8 +1175,8 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
                     pub.epoch = ba->peer.epoch + 1; pub.builds = nrows > 0 ? ++ba->peer.builds : ba->peer.builds;
                     for (int r = 0; r < ba->peer.world; ++r) pub.row_flags[r] = peer_row_flags(ba, r);
                     pub.row_count = peer_row_flags(ba, ba->shard_rank) + (size_t)kMaxPeers * ba->n_free;
-                    static const int pub_mode = getenv("VIO360_PEER_PUBLISH") ? atoi(getenv("VIO360_PEER_PUBLISH")) : 1;
-                    pub.mode = pub_mode; pub.row_lo = row0; pub.row_hi = row0 + nrows;
+                    pub.mode = peer_publish_mode(); pub.row_lo = row0; pub.row_hi = row0 + nrows;
+                    if (pub.mode == 3) pub.epoch = 0;   // default: the reduce does not publish, the pull kernel's first CTA announces
                 }
                 if (nrows > 0) {
                 KernelTimer kt_(ctx, "k_schur_reduce");
@@ -1385,6 +1393,8 @@ extern "C" int vio360_ba_peer_exchange(vio360_ba* ba) {
         pv.row_lo[r] = P.row_lo[r]; pv.row_hi[r] = P.row_hi[r];
     }
     pv.row_flags = peer_row_flags(ba, ba->shard_rank);
+    if (peer_publish_mode() == 3)
+        for (int r = 0; r < P.world; ++r) pv.announce[r] = peer_row_flags(ba, r) + (size_t)ba->shard_rank * ba->n_free + P.row_lo[ba->shard_rank];
     int* d_err = nullptr;
     VIO_CUDA(ctx, cudaHostGetDevicePointer((void**)&d_err, P.h_err, 0));
     // trace words live behind the flags in the exchange header: [CTA 0 wait ns, CTA 0 total ns]

@@ -39,6 +39,7 @@ struct PeerView {
     const unsigned* row_flags;       // THIS rank's row flags [src rank][n_free]: last epoch rank src released row r for
     int row_lo[kMaxPeers], row_hi[kMaxPeers];   // block rows (free-pose index) a rank's band covers
     int world, rank;
+    unsigned* announce[kMaxPeers];   // mode 3: every rank's flag word of THIS rank (row_flags[r] + rank * n_free + row_lo[rank]); null otherwise
 };
 
 // what the producer side (k_schur_reduce) needs to release finished block rows to every rank
@@ -161,13 +162,25 @@ k_band_pull(const PeerView pv, const unsigned epoch, const int n_free, const int
         if (ra < 0 || rb < 0 || rb < ra) need_all = true;          // the cost element (or the S / rhs boundary): every rank's first row
         else { r_first = ra; r_last = rb; }
     }
+    // mode 3 (default): the band of this rank was completed by the previous kernel on this stream (k_schur_reduce runs
+    // without any publishing code); CTA 0, the first to be scheduled, announces it to every rank, and a rank's rows are
+    // all released by that one flag.  Only CTA 0 of a rank has to run for the others to proceed.
+    const bool rank_level = pv.announce[0] != nullptr;
+    if (rank_level && blockIdx.x == 0 && threadIdx.x < pv.world) {
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(pv.announce[threadIdx.x]), "r"(epoch) : "memory");
+    }
     // thread (p, k): rank p, k-th row of this CTA's row range (ranges are short: 256 elements are < 1 row)
     {
         const long long t0 = clock64();
-        const int nrows = need_all ? n_free : r_last - r_first + 1;
+        const int nrows = rank_level ? 1 : (need_all ? n_free : r_last - r_first + 1);
         for (int q = threadIdx.x; q < nrows * pv.world; q += blockDim.x) {
-            const int p = q / nrows, row = (need_all ? 0 : r_first) + (q - p * nrows);
-            if (row < pv.row_lo[p] || row >= pv.row_hi[p]) continue;
+            const int p = q / nrows;
+            int row = (need_all ? 0 : r_first) + (q - p * nrows);
+            if (rank_level) {
+                if (pv.row_hi[p] <= pv.row_lo[p] || (!need_all && (r_last < pv.row_lo[p] || r_first >= pv.row_hi[p]))) continue;   // this CTA reads nothing of rank p
+                row = pv.row_lo[p];
+            } else if (row < pv.row_lo[p] || row >= pv.row_hi[p]) continue;
             const unsigned* f = pv.row_flags + (size_t)p * n_free + row;
             while ((int)(ld_acquire_sys_u32(f) - epoch) < 0) {
                 if (clock64() - t0 > kPeerTimeoutCycles) { *err_flag = 1; break; }
