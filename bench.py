@@ -839,9 +839,41 @@ def cpu_baseline_ba(syn, win5):
         r, Jp, Jl, _ = Wo.evaluate(sub["pose_delta"], sub["points"], nthreads=nthreads, hoisted=True)
         Wo.schur(r, Jp, Jl, D)
     dth = (time.perf_counter() - t0) / 3
-    return {"value": sub["O"] / dt, "unit": "obs/s", "cores": nthreads, "kind": "port",
+    base = {"value": sub["O"] / dt, "unit": "obs/s", "cores": nthreads, "kind": "port",
             "sample": "%d observations (first %d landmarks of the 1M window), per-factor 6-SVD pose chain as the reference executes it + Huber + Schur elimination (C restatement, Schur single-threaded)" % (sub["O"], sub_M),
             "hoisted_pose_chain_value": sub["O"] / dth}
+    # All host cores, evaluation AND elimination threaded: the landmark range is cut into one contiguous part per
+    # core, every part evaluates its factors and eliminates its landmarks into a private S / rhs (what Ceres'
+    # SchurEliminator does per thread with its chunk loop, schur_eliminator_impl.h:190-262), then the parts are added.
+    from concurrent.futures import ThreadPoolExecutor
+    ncores = os.cpu_count() or 1
+    bounds = np.linspace(0, sub_M, ncores + 1).astype(np.int64)
+    parts = []
+    for c in range(ncores):
+        lo, hi = int(bounds[c]), int(bounds[c + 1])
+        k = (sub["point_idx"] >= lo) & (sub["point_idx"] < hi)
+        w = dict(sub, M=hi - lo, O=int(k.sum()), pose_idx=np.ascontiguousarray(sub["pose_idx"][k]),
+                 point_idx=np.ascontiguousarray(sub["point_idx"][k] - lo), obs_u=np.ascontiguousarray(sub["obs_u"][k]),
+                 obs_v=np.ascontiguousarray(sub["obs_v"][k]), outlier=np.ascontiguousarray(sub["outlier"][k]),
+                 points=np.ascontiguousarray(sub["points"][lo:hi]), point_fixed=np.ascontiguousarray(sub["point_fixed"][lo:hi]))
+        Wc = ba_oracle.Window(w)
+        rc, Jpc, Jlc, _ = Wc.evaluate(w["pose_delta"], w["points"])
+        parts.append((Wc, w, Wc.lm_diagonal(Jpc, Jlc)))
+
+    def one(p):
+        Wc, w, Dc = p
+        rc, Jpc, Jlc, _ = Wc.evaluate(w["pose_delta"], w["points"], nthreads=1)
+        return Wc.schur(rc, Jpc, Jlc, Dc)[:2]
+    with ThreadPoolExecutor(ncores) as ex:
+        list(ex.map(one, parts))
+        t0 = time.perf_counter(); reps = 0
+        while reps < 20 and time.perf_counter() - t0 < 10.0:
+            res = list(ex.map(one, parts))
+            S = sum(x[0] for x in res); rhs = sum(x[1] for x in res); reps += 1
+        dta = (time.perf_counter() - t0) / reps
+    base.update(all_cores_value=sub["O"] / dta, all_cores=ncores,
+                all_cores_note="same sample, one landmark range per host core (evaluation + elimination + the sum of the per-core systems)")
+    return base
 
 
 # ================================================================= reference arm

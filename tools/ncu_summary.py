@@ -33,5 +33,35 @@ def main(path):
         print()
 
 
+def to_bytes(value, unit):
+    mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    return float(value.replace(",", "")) * mult[unit]
+
+
+def traffic(path, kernel, source, capture, w, h, batch, points, out):
+    """ncu_summary.py raw.csv --traffic <kernel> <source under csrc/> <capture name> W H batch points out.json:
+    records dram__bytes_read.sum + dram__bytes_write.sum of the kernel's captured launch, tied to the sha1 of the
+    kernel's source file and to the workload, in the file bench.py's ncu_traffic() reads."""
+    import hashlib
+    import json
+    import os
+    rows = list(csv.reader(open(path)))
+    hdr, units = rows[0], rows[1]
+    ki = hdr.index("Kernel Name")
+    r = [x for x in rows[2:] if kernel in x[ki]][0]
+    ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+    total = to_bytes(r[ir], units[ir]) + to_bytes(r[iw], units[iw])
+    root = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
+    src = os.path.join(root, "360_visual_inertial_odometry_b200", "csrc", source)
+    rec = json.load(open(out)) if os.path.exists(out) else {}
+    rec[kernel] = {"bytes_per_launch": total, "source": source, "source_sha1": hashlib.sha1(open(src, "rb").read()).hexdigest(),
+                   "capture": capture, "workload": {"W": int(w), "H": int(h), "batch": int(batch), "points": int(points)}}
+    json.dump(rec, open(out, "w"), indent=1, sort_keys=True)
+    print(kernel, total, "bytes per launch ->", out)
+
+
 if __name__ == "__main__":
-    main(sys.argv[1])
+    if len(sys.argv) > 2 and sys.argv[2] == "--traffic":
+        traffic(sys.argv[1], *sys.argv[3:])
+    else:
+        main(sys.argv[1])
