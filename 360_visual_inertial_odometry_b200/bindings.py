@@ -21,7 +21,7 @@ EXPORTS = [
     "vio360_enable_kernel_timing", "vio360_kernel_time", "vio360_reset_kernel_times",
     "vio360_fe_configure", "vio360_fe_track", "vio360_fe_track_batch", "vio360_fe_detect",
     "vio360_fe_detect_batch", "vio360_fe_pyramid", "vio360_fe_min_eigen_val",
-    "vio360_fe_ransac_rotation", "vio360_fe_ransac_rotation_batch", "vio360_fe_cluster_filter", "vio360_fe_grid_cap",
+    "vio360_fe_ransac_rotation", "vio360_fe_ransac_rotation_batch", "vio360_fe_ransac_rotation_noalloc", "vio360_fe_cluster_filter", "vio360_fe_grid_cap",
     "vio360_seq_create", "vio360_seq_destroy", "vio360_seq_reset", "vio360_seq_capacity", "vio360_fe_track_frame_batch",
     "vio360_ba_create", "vio360_ba_destroy", "vio360_ba_set_structure", "vio360_ba_set_outliers",
     "vio360_ba_set_shard", "vio360_ba_set_parameters", "vio360_ba_evaluate", "vio360_ba_evaluate_f32",
@@ -123,6 +123,8 @@ def load():
     lib.vio360_fe_ransac_rotation.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_float,
                                               C.c_void_p, C.c_void_p]
     lib.vio360_fe_ransac_rotation_batch.argtypes = [C.c_void_p, C.POINTER(RansacJob), C.c_int, C.c_int, C.c_float, C.c_int]
+    lib.vio360_fe_ransac_rotation_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_float,
+                                                      C.c_void_p, C.c_void_p]
     lib.vio360_fe_detect_batch.argtypes = [C.c_void_p, C.POINTER(DetectJob), C.c_int, C.c_int, C.c_double,
                                            C.c_double, C.c_int]
     lib.vio360_fe_pyramid.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.POINTER(C.c_void_p),
@@ -405,6 +407,12 @@ class Context:
             j.inlier_mask, j.best_inliers, j.counts = _ptr(mask), best.ctypes.data, counts.ctypes.data
         self.check(self.lib.vio360_fe_ransac_rotation_batch(self.h, jobs, nb, iters or 0, C.c_float(threshold_deg), MEM_HOST))
         return [(int(b[0]), m, c[:iters]) for b, m, c in outs]
+
+    def fe_ransac_rotation_noalloc(self, prev_xy_dev, cur_xy_dev, n, samples_dev, iters, threshold_deg, mask_dev, best_dev):
+        """vio360_fe_ransac_rotation_noalloc: raw device addresses in, kernels enqueued on the context's stream,
+        nothing allocated and nothing synchronised (call synchronize() before reading the outputs)."""
+        self.check(self.lib.vio360_fe_ransac_rotation_noalloc(self.h, prev_xy_dev, cur_xy_dev, n, samples_dev, iters,
+                                                              C.c_float(threshold_deg), mask_dev, best_dev))
 
     def fe_detect_batch_raw(self, jobs, n_jobs, max_corners, quality, min_dist, mem_space):
         self.check(self.lib.vio360_fe_detect_batch(self.h, jobs, n_jobs, max_corners, quality, min_dist, mem_space))

@@ -2,6 +2,7 @@
 // Compiled with --fmad=false (see fe_lk.cuh / fe_detect.cuh); explicit fmaf() calls mark
 // the places where OpenCV's dispatched code fuses.
 #include <algorithm>
+#include <mutex>
 
 #include <time.h>
 
@@ -931,6 +932,90 @@ extern "C" int vio360_fe_ransac_rotation(vio360_ctx* ctx, const float* prev_xy, 
     j.prev_xy = prev_xy; j.cur_xy = cur_xy; j.n = n; j.samples = samples; j.inlier_mask = inlier_mask; j.best_inliers = best_inliers;
     j.counts = nullptr;
     return vio360_fe_ransac_rotation_batch(ctx, &j, 1, iters, threshold_deg, VIO360_MEM_HOST);
+}
+
+// ---- rotation RANSAC without any allocation (no counterpart in the reference) -----------------------
+// vio360_fe_ransac_rotation_noalloc: the same three kernels as vio360_fe_ransac_rotation_batch on ONE job whose
+// inputs and outputs are the caller's device arrays, with every intermediate (job descriptor, bearings,
+// hypothesis rotations, inlier counts) in the file-scope array below instead of the context's growable pools.
+// Added for callers that may not call cudaMalloc (code under CUDA graph
+// capture, serving loops, harnesses that forbid it).  The array costs kRansacStaticWords * 4 bytes (about 137 KB)
+// of device memory on every GPU that loads the library, until the process exits.
+//
+// g_ransac_static names the array for DEVICE code.  In host code the same name is only a handle: the device
+// address is asked for once per device (cudaGetSymbolAddress with that device current) and that address is
+// what the kernels receive.
+//
+// Nothing in the scratch has to start at zero: the set-up kernel rewrites the descriptor, k_ransac_bearings
+// rewrites bearings [0, n), k_ransac_hypotheses rewrites R and counts [0, iters), and k_ransac_pick reads only
+// those ranges; whatever an earlier call left beyond them is never read.  Every call on a device shares the
+// array: two calls that overlap on the GPU (different streams / contexts of one device) race.
+constexpr int kRansacStaticMaxPoints = VIO360_RANSAC_NOALLOC_MAX_POINTS;
+constexpr int kRansacStaticMaxIters = VIO360_RANSAC_NOALLOC_MAX_ITERS;
+constexpr int kRansacStaticJobWords = 64;    // descriptor, padded to 256 bytes
+constexpr size_t kRansacStaticWords = kRansacStaticJobWords + 6 * (size_t)kRansacStaticMaxPoints + 10 * (size_t)kRansacStaticMaxIters;
+static_assert(sizeof(RansacJobDev) <= kRansacStaticJobWords * 4, "descriptor slot");
+static __device__ __align__(256) uint32_t g_ransac_static[kRansacStaticWords];
+
+constexpr int kRansacStaticMaxDevices = 64;
+static std::mutex g_ransac_static_mutex;
+static uint32_t* g_ransac_static_dev[kRansacStaticMaxDevices] = {};   // device address of g_ransac_static, per device ordinal
+
+// Fills the descriptor inside the scratch (layout in words: job 64 | b1 3N | b2 3N | R 9I | counts I, N / I = the maxima).
+__global__ void k_ransac_static_setup(uint32_t* __restrict__ scratch, const float* prev_xy, const float* cur_xy, int n, const int* samples,
+                                      uint8_t* mask, int* best) {
+    RansacJobDev jb;
+    jb.prev_xy = prev_xy; jb.cur_xy = cur_xy; jb.n = n; jb.samples = samples;
+    uint32_t* w = scratch + kRansacStaticJobWords;
+    jb.b1 = reinterpret_cast<float*>(w); w += 3 * kRansacStaticMaxPoints;
+    jb.b2 = reinterpret_cast<float*>(w); w += 3 * kRansacStaticMaxPoints;
+    jb.R = reinterpret_cast<float*>(w); w += 9 * kRansacStaticMaxIters;
+    jb.counts = reinterpret_cast<int*>(w);
+    jb.mask = mask; jb.best = best;
+    *reinterpret_cast<RansacJobDev*>(scratch) = jb;
+}
+
+extern "C" int vio360_fe_ransac_rotation_noalloc(vio360_ctx* ctx, const float* prev_xy, const float* cur_xy, int n, const int32_t* samples,
+                                                 int iters, float threshold_deg, uint8_t* inlier_mask, int32_t* best) {
+    if (!ctx) return VIO360_ERR_INVALID;
+    vio360_fe_state* s = ctx->fe;
+    if (!s || !s->configured) return vio360_fail(ctx, VIO360_ERR_STATE, "fe_ransac_rotation_noalloc before fe_configure");
+    if (n < 0 || iters < 0 || !best || (n > 0 && (!prev_xy || !cur_xy || !inlier_mask)) || (n >= 3 && iters > 0 && !samples))
+        return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_ransac_rotation_noalloc: bad arguments");
+    if (n > kRansacStaticMaxPoints || iters > kRansacStaticMaxIters)
+        return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_ransac_rotation_noalloc: n = %d / iters = %d exceed the static scratch (at most %d points, %d hypotheses); "
+                           "use vio360_fe_ransac_rotation_batch for larger problems", n, iters, kRansacStaticMaxPoints, kRansacStaticMaxIters);
+    if (ctx->device < 0 || ctx->device >= kRansacStaticMaxDevices)
+        return vio360_fail(ctx, VIO360_ERR_INVALID, "fe_ransac_rotation_noalloc: device ordinal %d out of range", ctx->device);
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    uint32_t* scratch;
+    {   // once per device, with that device current
+        std::lock_guard<std::mutex> lock(g_ransac_static_mutex);
+        if (!g_ransac_static_dev[ctx->device]) {
+            void* p = nullptr;
+            cudaError_t e = cudaGetSymbolAddress(&p, g_ransac_static);
+            if (e != cudaSuccess || !p)
+                return vio360_fail(ctx, VIO360_ERR_CUDA, "fe_ransac_rotation_noalloc: cudaGetSymbolAddress -> %s", cudaGetErrorString(e));
+            g_ransac_static_dev[ctx->device] = static_cast<uint32_t*>(p);
+        }
+        scratch = g_ransac_static_dev[ctx->device];
+    }
+    cudaStream_t st = ctx->stream;
+    const RansacJobDev* dj = reinterpret_cast<const RansacJobDev*>(scratch);
+    const float thr = (float)((double)threshold_deg * 3.14159265358979323846 / 180.0);   // FeatureTracker.cpp:305
+    k_ransac_static_setup<<<1, 1, 0, st>>>(scratch, prev_xy, cur_xy, n, samples, inlier_mask, best);
+    VIO_LAUNCH_CHECK(ctx);
+    if (n > 0) {
+        k_ransac_bearings<<<dim3((n + 255) / 256, 1), 256, 0, st>>>(dj, s->W, s->H);
+        VIO_LAUNCH_CHECK(ctx);
+        if (iters > 0) {
+            k_ransac_hypotheses<<<dim3((iters + kRansacWarps - 1) / kRansacWarps, 1), kRansacWarps * 32, 0, st>>>(dj, iters, thr);
+            VIO_LAUNCH_CHECK(ctx);
+        }
+    }
+    k_ransac_pick<<<1, 256, 0, st>>>(dj, iters, thr);
+    VIO_LAUNCH_CHECK(ctx);
+    return VIO360_OK;
 }
 
 // ---- feature-list filters between tracking and detection -------------------------

@@ -163,6 +163,29 @@ int vio360_fe_ransac_rotation(vio360_ctx* ctx, const float* prev_xy, const float
 int vio360_fe_ransac_rotation_batch(vio360_ctx* ctx, const vio360_ransac_job* jobs, int n_jobs,
                                     int iters, float threshold_deg, int mem_space);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that
+ * may not call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  One rotation-RANSAC job, same kernels and results as vio360_fe_ransac_rotation_batch in
+ * VIO360_MEM_DEVICE, but the call allocates nothing (no cudaMalloc / cudaFree / pool growth, no host
+ * staging): its intermediates live in a static device array of the library, sized for at most
+ * VIO360_RANSAC_NOALLOC_MAX_POINTS points and VIO360_RANSAC_NOALLOC_MAX_ITERS hypotheses (about
+ * 137 KB, held on every GPU that loads the library until the process exits).  Larger n or iters
+ * -> VIO360_ERR_INVALID with a message; use the batch call for those.
+ * ALL arrays are DEVICE memory of the context's device: prev_xy / cur_xy n x 2 floats, samples
+ * iters x 3 indices in [0, n) (not validated, as in the device space of the batch call),
+ * inlier_mask n bytes, best 2 ints: [0] the winner's inlier count (the reference function's return
+ * value; n when n < 3, 0 when no hypothesis has an inlier), [1] its hypothesis index or -1.
+ * The kernels are enqueued on the context's stream and the call returns without synchronising:
+ * read the outputs after vio360_synchronize (or in stream order).  Requires vio360_fe_configure
+ * (image size).  All calls on one device share the static array, which keeps the previous call's
+ * contents (no part of it needs clearing, every range read is rewritten first): calls that overlap
+ * on the GPU -- two contexts / streams of one device -- race and must be serialised by the caller. */
+#define VIO360_RANSAC_NOALLOC_MAX_POINTS 4096
+#define VIO360_RANSAC_NOALLOC_MAX_ITERS 1024
+int vio360_fe_ransac_rotation_noalloc(vio360_ctx* ctx, const float* prev_xy, const float* cur_xy, int n,
+                                      const int32_t* samples, int iters, float threshold_deg,
+                                      uint8_t* inlier_mask, int32_t* best);
+
 /* the feature-list filters FeatureTracker::TrackFeatures runs between tracking and
  * detection, on the device so that the point list can stay there.  Frames are rows of `stride`
  * features (xy: n_frames x stride x 2 floats, keep: n_frames x stride bytes, n[f] <= stride, host
