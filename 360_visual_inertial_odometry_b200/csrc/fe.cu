@@ -48,6 +48,7 @@ struct vio360_fe_state {
     uint64_t clock = 0, batch_tag = 0;
     // tracking pools
     DevBuf d_jobs, d_pyrjobs, d_pts_in, d_pts_out, d_status, d_err, d_keep;
+    DevBuf d_lk_queue;           // k_lk_track's work counter {next item, finished warps}; zero between launches
     PinBuf h_pts_in, h_out;
     // ring of pinned descriptor staging so that device-space calls never wait for the stream
     struct Stage { PinBuf jobs, pyrjobs; cudaEvent_t ev = nullptr; bool used = false; };
@@ -82,7 +83,7 @@ void vio360_fe_release(vio360_ctx* ctx) {
     s->d_seq.release(); s->h_seq.release();
     DevBuf* db[] = {&s->d_jobs, &s->d_pyrjobs, &s->d_pts_in, &s->d_pts_out, &s->d_status, &s->d_err, &s->d_keep,
                     &s->d_djobs, &s->d_eig, &s->d_mask, &s->d_small, &s->d_cand, &s->d_grid,
-                    &s->d_corners, &s->d_ransac, &s->d_occ};
+                    &s->d_corners, &s->d_ransac, &s->d_occ, &s->d_lk_queue};
     for (DevBuf* b : db) b->release();
     PinBuf* pb[] = {&s->h_pts_in, &s->h_out, &s->h_djobs, &s->h_dout, &s->h_ransac, &s->h_occ};
     for (PinBuf* b : pb) b->release();
@@ -148,6 +149,8 @@ extern "C" int vio360_fe_configure(vio360_ctx* ctx, int width, int height, int m
     VIO_CUDA(ctx, s->d_status.reserve(np)); VIO_CUDA(ctx, s->d_err.reserve(np * 4)); VIO_CUDA(ctx, s->d_keep.reserve(np));
     VIO_CUDA(ctx, s->h_pts_in.reserve(np * 8));
     VIO_CUDA(ctx, s->h_out.reserve(np * (8 + 1 + 4 + 1)));
+    VIO_CUDA(ctx, s->d_lk_queue.reserve(256));
+    VIO_CUDA(ctx, cudaMemsetAsync(s->d_lk_queue.p, 0, 256, ctx->stream));
     if (const char* e = getenv("VIO360_LK_MB")) s->lk_mb = atoi(e);
     if (const char* e = getenv("VIO360_FE_H2D_GROUP")) s->h2d_group = std::max(1, atoi(e));
     VIO_CUDA(ctx, cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
@@ -316,19 +319,44 @@ static int launch_lk(vio360_ctx* ctx, const TrackJobDev* dj, int nj, int max_n, 
     vio360_fe_state* s = ctx->fe;
     cudaStream_t st = ctx->stream;
     { KernelTimer kt_(ctx, "k_lk_track");
+    const int n_items = max_n * nj;
+    unsigned* queue = s->d_lk_queue.as<unsigned>();
     auto launch = [&](auto kern, int warps) -> cudaError_t {
         const size_t smem = (size_t)warps * kLkWarpWords * sizeof(uint32_t);
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        kern<<<dim3((max_n + warps - 1) / warps, nj), warps * 32, smem, st>>>(dj, lp);
+        static const int carve = getenv("VIO360_LK_CARVE") ? atoi(getenv("VIO360_LK_CARVE")) : -1;   // percent of the 228 KB; -1: the driver's choice
+        if (carve >= 0) {
+            e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            if (e != cudaSuccess) return e;
+        }
+        kern<<<dim3((max_n + warps - 1) / warps, nj), warps * 32, smem, st>>>(dj, lp, max_n, n_items, queue);
+        return cudaSuccess;
+    };
+    // persistent form: as many CTAs as the device holds at once (warps_per_sm warps per SM), never more than the work
+    auto launch_persist = [&](auto kern, int warps, int warps_per_sm) -> cudaError_t {
+        const size_t smem = (size_t)warps * kLkWarpWords * sizeof(uint32_t);
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        const int ctas = std::min((n_items + warps - 1) / warps, ctx->num_sms * (warps_per_sm / warps));
+        kern<<<dim3(ctas, 1), warps * 32, smem, st>>>(dj, lp, max_n, n_items, queue);
         return cudaSuccess;
     };
     cudaError_t e;
-    if (s->lk_mb == 3) e = launch(k_lk_track<7, 96>, 7);
-    else if (s->lk_mb == 4) e = launch(k_lk_track<6, 80>, 6);
-    else if (s->lk_mb == 5) e = launch(k_lk_track<6, 104>, 6);
-    else if (s->lk_mb == 6) e = launch(k_lk_track<9, 112>, 9);
-    else e = launch(k_lk_track<8, 128>, 8);
+    switch (s->lk_mb) {   // tuning knob VIO360_LK_MB; the measured variants are listed in DESIGN.md section 8
+        case 3: e = launch(k_lk_track<7, 96, false>, 7); break;    // 3 CTAs / SM: 1.16 ms per step against 0.93 (spills)
+        case 4: e = launch(k_lk_track<6, 80, false>, 6); break;    // 4 CTAs / SM: 1.02 ms per step
+        case 7: e = launch(k_lk_track<4, 128, false>, 4); break;
+        case 8: e = launch(k_lk_track<2, 128, false>, 2); break;
+        case 10: e = launch(k_lk_track<8, 128, false>, 8); break;   // round 1's shape: 0.726-0.744 ms
+        case 11: e = launch_persist(k_lk_track<4, 128, true>, 4, 16); break;
+        case 12: e = launch_persist(k_lk_track<1, 128, true>, 1, 16); break;
+        case 18: e = launch_persist(k_lk_track<8, 128, true>, 8, 16); break;
+        // One-warp CTAs: a slot is refilled as soon as its feature is done (8-warp CTAs idle a quarter of the warp
+        // slots waiting for their slowest feature).  64 x 1000 features at 3840x1920: 0.686 ms; persistent work-queue
+        // forms 0.73-0.83 ms (the queue state costs registers, which spills), 4-warp CTAs 0.712, 2-warp 0.783.
+        default: e = launch(k_lk_track<1, 128, false>, 1); break;
+    }
     if (e != cudaSuccess) return vio360_fail(ctx, VIO360_ERR_CUDA, "k_lk_track: %s", cudaGetErrorString(e));
     }
     VIO_LAUNCH_CHECK(ctx);

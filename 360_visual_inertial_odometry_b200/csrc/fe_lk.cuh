@@ -161,27 +161,23 @@ __device__ __noinline__ void deriv_zero_outside(int* sDx, int* sDy, int ipx, int
     }
 }
 
-// kLkWarps features per CTA; REGS = register cap (8 warps x 128 regs -> 16 warps / SM,
-// 7 x 96 -> 21, 6 x 80 -> 24)
-template <int kLkWarps, int REGS>
-__global__ void __launch_bounds__(kLkWarps * 32) __maxnreg__(REGS) k_lk_track(const TrackJobDev* __restrict__ jobs, LkParams P) {
+// kLkWarps warps per CTA; REGS = register cap (8 warps x 128 regs -> 16 warps / SM, 7 x 96 -> 21, 6 x 80 -> 24).
+// PERSIST = false: warp w of CTA (x, y) tracks feature x * kLkWarps + w of job y and exits.  The iteration count of
+// a feature is data dependent (13 on average, 30 at most per level), and a CTA keeps its registers and shared memory
+// until its slowest warp is done: with 8-warp CTAs a quarter of the warp slots of an SM idle (ncu: 11.9 of 16 warps
+// active).  PERSIST = true: the grid is exactly the warps that fit the device, and every warp takes the next feature
+// of the batch from a device counter until none is left, so a slot is never empty before the batch ends.  Work item
+// i = (job i / max_n, feature i % max_n); consecutive items are consecutive features of one frame (L2 locality).
+// `queue`: [0] next item, [1] warps that have finished; the last warp to finish resets both for the next launch.
+template <int kLkWarps, int REGS, bool PERSIST>
+__global__ void __launch_bounds__(kLkWarps * 32) __maxnreg__(REGS) k_lk_track(const TrackJobDev* __restrict__ jobs, LkParams P, int max_n, int n_items,
+                                                                            unsigned* __restrict__ queue) {
     extern __shared__ __align__(16) uint32_t lk_smem[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const TrackJobDev& job = jobs[blockIdx.y];
-    const int pt = blockIdx.x * kLkWarps + warp;
-    if (pt >= (job.n_ptr ? *job.n_ptr : job.n)) return;   // warp-uniform; only __syncwarp is used below
     uint32_t* sT = lk_smem + warp * kLkWarpWords;
     int* sDx = reinterpret_cast<int*>(sT + kTRows * kTWords);
     int* sDy = sDx + kDPlane;
     uint32_t* sJ = reinterpret_cast<uint32_t*>(sDy + kDPlane);
-    // Zero once what the Scharr stage never writes: columns 22, 23 of every row (the taps right of
-    // the window) and rows 22, 23 (read by the two padding runs of lanes 30 / 31).
-    if (lane < kDRows) {
-        *reinterpret_cast<int2*>(sDx + lane * kDWords + kDRows) = make_int2(0, 0);
-        *reinterpret_cast<int2*>(sDy + lane * kDWords + kDRows) = make_int2(0, 0);
-    }
-    for (int i = lane; i < 2 * kDWords; i += 32) { sDx[kDRows * kDWords + i] = 0; sDy[kDRows * kDWords + i] = 0; }
-
     // runs owned by this lane: window row wy, column segment seg (columns 4*seg .. 4*seg+3);
     // offJ = wy * kJWords + seg is the only per-run register kept across the level loop
     int offJ[kRpl];
@@ -197,6 +193,23 @@ __global__ void __launch_bounds__(kLkWarps * 32) __maxnreg__(REGS) k_lk_track(co
         for (int j = 0; j < 4; ++j)
             if (real && 4 * seg + j < kWin) colmask |= 1u << (4 * k + j);
     }
+  for (;;) {
+    int job_idx, pt;
+    if (PERSIST) {
+        unsigned item = 0;
+        if (lane == 0) item = atomicAdd(queue, 1u);
+        item = __shfl_sync(0xffffffffu, item, 0);
+        if (item >= (unsigned)n_items) break;
+        job_idx = (int)(item / (unsigned)max_n); pt = (int)(item - (unsigned)job_idx * (unsigned)max_n);
+    } else {
+        job_idx = blockIdx.y; pt = blockIdx.x * (int)(blockDim.x >> 5) + warp;   // launched with <= kLkWarps warps per CTA
+    }
+    const TrackJobDev& job = jobs[job_idx];
+    if (pt >= (job.n_ptr ? *job.n_ptr : job.n)) {   // warp-uniform; only __syncwarp is used below
+        if (PERSIST) continue;
+        return;
+    }
+
 #define LK_OFF_T(k) ((offJ[k] / kJWords + 1) * kTWords + offJ[k] % kJWords)
 // padding runs (k == 3 on lanes 30, 31) read the two zero rows below the derivative grid
 #define LK_OFF_D(k) (((k) == 3 && lane >= 30) ? kDRows * kDWords : (offJ[k] / kJWords) * kDWords + 4 * (offJ[k] % kJWords))
@@ -319,6 +332,14 @@ __global__ void __launch_bounds__(kLkWarps * 32) __maxnreg__(REGS) k_lk_track(co
                 }
             }
         } else {
+            // Zero what the Scharr stage below never writes: columns 22, 23 of every row (the taps right of the
+            // window) and rows 22, 23 (read by the two padding runs of lanes 30 / 31).  Done per border window
+            // (rare) and not once per warp: the interior path uses the same words as its 24 x 24 grid.
+            if (lane < kDRows) {
+                *reinterpret_cast<int2*>(sDx + lane * kDWords + kDRows) = make_int2(0, 0);
+                *reinterpret_cast<int2*>(sDy + lane * kDWords + kDRows) = make_int2(0, 0);
+            }
+            for (int i = lane; i < 2 * kDWords; i += 32) { sDx[kDRows * kDWords + i] = 0; sDy[kDRows * kDWords + i] = 0; }
             // ---- Scharr on the 22 x 22 grid (ipx + dx, ipy + dy): lane = (4-column run cr, row group g).
             // Per tile row one dp4a gives the horizontal smoothing 3a+10b+3c and one the horizontal
             // difference c-a of a column; the vertical halves are combined from a 3-row register window.
@@ -527,6 +548,14 @@ __global__ void __launch_bounds__(kLkWarps * 32) __maxnreg__(REGS) k_lk_track(co
             const bool nearb = (outx < P.margin) || (outx > W0 - P.margin) || (outy < P.margin) || (outy > H0 - P.margin);
             job.keep[pt] = (uint8_t)(status && !polar && !nearb);
         }
+    }
+    if (!PERSIST) break;
+    __syncwarp();   // the next feature's tiles overwrite this one's
+  }
+    if (PERSIST && lane == 0) {
+        __threadfence();
+        const unsigned total = gridDim.x * kLkWarps;
+        if (atomicAdd(queue + 1, 1u) == total - 1) { queue[0] = 0; queue[1] = 0; __threadfence(); }
     }
 }
 
