@@ -17,7 +17,7 @@ PEER_BLOB_BYTES = 128   # VIO360_PEER_BLOB_BYTES
 
 EXPORTS = [
     "vio360_version", "vio360_create", "vio360_destroy", "vio360_last_error", "vio360_synchronize",
-    "vio360_stream", "vio360_launch_count", "vio360_probe_fma_peak",
+    "vio360_stream", "vio360_launch_count", "vio360_probe_fma_peak", "vio360_host_register", "vio360_host_unregister",
     "vio360_enable_kernel_timing", "vio360_kernel_time", "vio360_reset_kernel_times",
     "vio360_fe_configure", "vio360_fe_track", "vio360_fe_track_batch", "vio360_fe_detect",
     "vio360_fe_detect_batch", "vio360_fe_pyramid", "vio360_fe_min_eigen_val",
@@ -109,6 +109,8 @@ def load():
     lib.vio360_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
     lib.vio360_synchronize.argtypes = [C.c_void_p]
     lib.vio360_probe_fma_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    lib.vio360_host_register.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+    lib.vio360_host_unregister.argtypes = [C.c_void_p, C.c_void_p]
     lib.vio360_enable_kernel_timing.argtypes = [C.c_void_p, C.c_int]
     lib.vio360_kernel_time.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]
     lib.vio360_reset_kernel_times.argtypes = [C.c_void_p]
@@ -204,6 +206,13 @@ class Context:
             self.close()
         except Exception:
             pass
+
+    def host_register(self, arr):
+        """page-locks a numpy array's buffer in place (vio360_host_register); keep the array alive until host_unregister"""
+        self.check(self.lib.vio360_host_register(self.h, arr.ctypes.data, arr.nbytes))
+
+    def host_unregister(self, arr):
+        self.check(self.lib.vio360_host_unregister(self.h, arr.ctypes.data))
 
     def synchronize(self):
         self.check(self.lib.vio360_synchronize(self.h))

@@ -8,6 +8,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -34,6 +35,12 @@ struct vio360_ctx {
     std::vector<TimedLaunch> timed;
     std::vector<cudaEvent_t> event_pool;
     std::unordered_map<std::string, std::pair<double, long long>> kernel_ms;   // name -> (total ms, launches)
+    // Host ranges page-locked through vio360_host_register: begin -> end of the WHOLE pages inside the caller's range
+    // (never widened: the pages at both ends may be shared with a neighbouring allocation).  A copy must lie inside
+    // one registration or outside all of them (the runtime rejects a copy that straddles a boundary), so host frame
+    // copies are cut at these boundaries (vio360_h2d_linear).
+    std::map<uintptr_t, uintptr_t> registered;
+    std::unordered_map<uintptr_t, uintptr_t> registered_by_ptr;   // caller's pointer -> begin of its registration
 };
 
 // Brackets one kernel launch with events on the context's stream when timing is on.
@@ -108,3 +115,30 @@ struct PinBuf {
 };
 
 void vio360_fe_release(vio360_ctx* ctx);  // fe.cu
+
+// Host-to-device copy of `bytes` contiguous bytes, cut at the boundaries of the registered host ranges so that every
+// piece lies inside one registration (DMA straight from the caller's pages) or in pageable memory (the short fringes).
+inline cudaError_t vio360_h2d_linear(vio360_ctx* ctx, void* dst, const void* src, size_t bytes, cudaStream_t st) {
+    uintptr_t p = reinterpret_cast<uintptr_t>(src);
+    const uintptr_t end = p + bytes;
+    uint8_t* d = static_cast<uint8_t*>(dst);
+    if (!ctx->registered.empty()) {
+        auto it = ctx->registered.upper_bound(p);
+        if (it != ctx->registered.begin()) { auto pr = std::prev(it); if (pr->second > p) it = pr; }
+        for (; it != ctx->registered.end() && it->first < end && p < end; ++it) {
+            const uintptr_t a = it->first > p ? it->first : p, e = it->second < end ? it->second : end;
+            if (a > p) {   // pageable piece in front of this registration
+                cudaError_t rc = cudaMemcpyAsync(d, reinterpret_cast<const void*>(p), a - p, cudaMemcpyHostToDevice, st);
+                if (rc != cudaSuccess) return rc;
+                d += a - p; p = a;
+            }
+            if (e > p) {
+                cudaError_t rc = cudaMemcpyAsync(d, reinterpret_cast<const void*>(p), e - p, cudaMemcpyHostToDevice, st);
+                if (rc != cudaSuccess) return rc;
+                d += e - p; p = e;
+            }
+        }
+    }
+    if (p < end) return cudaMemcpyAsync(d, reinterpret_cast<const void*>(p), end - p, cudaMemcpyHostToDevice, st);
+    return cudaSuccess;
+}

@@ -50,6 +50,7 @@ extern "C" void vio360_destroy(vio360_ctx* ctx) {
     for (auto& t : ctx->timed) { cudaEventDestroy(t.e0); cudaEventDestroy(t.e1); }
     for (auto e : ctx->event_pool) cudaEventDestroy(e);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    for (auto& r : ctx->registered) cudaHostUnregister(reinterpret_cast<void*>(r.first));   // ranges the caller forgot
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -98,6 +99,40 @@ extern "C" int vio360_reset_kernel_times(vio360_ctx* ctx) {
     int rc = drain_timed(ctx);
     if (rc) return rc;
     ctx->kernel_ms.clear();
+    return VIO360_OK;
+}
+
+// Page-locks the whole pages INSIDE a caller-owned host range, so that later copies from it run at the PCIe rate.
+// The range is not widened: its first and last page may be shared with neighbouring heap allocations, and a page can
+// be registered only once.  The frame copies are cut at the registration's boundaries (vio360_h2d_linear).
+extern "C" int vio360_host_register(vio360_ctx* ctx, const void* ptr, size_t bytes) {
+    if (!ctx || !ptr || bytes == 0) return ctx ? vio360_fail(ctx, VIO360_ERR_INVALID, "host_register: bad arguments") : VIO360_ERR_INVALID;
+    const uintptr_t key = reinterpret_cast<uintptr_t>(ptr);
+    if (ctx->registered_by_ptr.count(key)) return VIO360_OK;   // already registered through this context
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    const uintptr_t page = 4096, a = (key + page - 1) & ~(page - 1), e = (key + bytes) & ~(page - 1);
+    if (e <= a) return vio360_fail(ctx, VIO360_ERR_INVALID, "host_register(%p, %zu): the range holds no whole page", ptr, bytes);
+    cudaError_t rc = cudaHostRegister(reinterpret_cast<void*>(a), (size_t)(e - a), cudaHostRegisterPortable);
+    if (rc != cudaSuccess) {
+        cudaGetLastError();
+        return vio360_fail(ctx, VIO360_ERR_CUDA, "host_register(%p, %zu): %s%s", ptr, bytes, cudaGetErrorString(rc),
+                           rc == cudaErrorHostMemoryAlreadyRegistered ? " (the range overlaps memory that is already page-locked)" : "");
+    }
+    ctx->registered[a] = e;
+    ctx->registered_by_ptr[key] = a;
+    return VIO360_OK;
+}
+extern "C" int vio360_host_unregister(vio360_ctx* ctx, const void* ptr) {
+    if (!ctx || !ptr) return VIO360_ERR_INVALID;
+    auto it = ctx->registered_by_ptr.find(reinterpret_cast<uintptr_t>(ptr));
+    if (it == ctx->registered_by_ptr.end()) return vio360_fail(ctx, VIO360_ERR_INVALID, "host_unregister(%p): not registered through this context", ptr);
+    VIO_CUDA(ctx, cudaSetDevice(ctx->device));
+    VIO_CUDA(ctx, cudaDeviceSynchronize());   // no copy from the range may still be in flight (frames travel on a second stream)
+    const uintptr_t a = it->second;
+    cudaError_t rc = cudaHostUnregister(reinterpret_cast<void*>(a));
+    ctx->registered.erase(a);
+    ctx->registered_by_ptr.erase(it);
+    if (rc != cudaSuccess) { cudaGetLastError(); return vio360_fail(ctx, VIO360_ERR_CUDA, "host_unregister: %s", cudaGetErrorString(rc)); }
     return VIO360_OK;
 }
 

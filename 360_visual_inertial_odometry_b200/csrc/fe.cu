@@ -224,10 +224,24 @@ static int load_frame(vio360_ctx* ctx, int slot, const uint8_t* img, size_t pitc
         VIO_CUDA(ctx, cudaMemcpy2DAsync(sl.own[0], s->lpitch[0], img, pitch, s->W, s->H, cudaMemcpyDeviceToDevice, ctx->stream));
     } else {
         cudaStream_t cs = h2d_stream ? h2d_stream : ctx->stream;
-        if (pitch == (size_t)s->W && s->lpitch[0] == s->W)     // contiguous on both sides: one linear DMA
-            VIO_CUDA(ctx, cudaMemcpyAsync(sl.own[0], img, (size_t)s->W * s->H, cudaMemcpyHostToDevice, cs));
-        else
+        if (pitch == (size_t)s->W && s->lpitch[0] == s->W) {   // contiguous on both sides: one linear DMA (cut at registration boundaries)
+            VIO_CUDA(ctx, vio360_h2d_linear(ctx, sl.own[0], img, (size_t)s->W * s->H, cs));
+        } else if (ctx->registered.empty()) {
             VIO_CUDA(ctx, cudaMemcpy2DAsync(sl.own[0], s->lpitch[0], img, pitch, s->W, s->H, cudaMemcpyHostToDevice, cs));
+        } else {
+            // a pitched view: one 2-D copy when its byte span lies inside one registration or outside all of them, else row by row
+            const uintptr_t p0 = reinterpret_cast<uintptr_t>(img), p1 = p0 + (size_t)(s->H - 1) * pitch + (size_t)s->W;
+            auto it = ctx->registered.upper_bound(p0);
+            bool one_piece;
+            if (it != ctx->registered.begin() && std::prev(it)->second > p0) one_piece = std::prev(it)->second >= p1;   // starts inside a registration
+            else one_piece = it == ctx->registered.end() || it->first >= p1;                                        // starts in pageable memory
+            if (one_piece) {
+                VIO_CUDA(ctx, cudaMemcpy2DAsync(sl.own[0], s->lpitch[0], img, pitch, s->W, s->H, cudaMemcpyHostToDevice, cs));
+            } else {
+                for (int y = 0; y < s->H; ++y)
+                    VIO_CUDA(ctx, vio360_h2d_linear(ctx, sl.own[0] + (size_t)y * s->lpitch[0], img + (size_t)y * pitch, (size_t)s->W, cs));
+            }
+        }
     }
     sl.p[0] = sl.own[0]; sl.pitch[0] = s->lpitch[0];
     return VIO360_OK;

@@ -27,6 +27,37 @@ FeatureTrackerCuda::~FeatureTrackerCuda() {
     vio360_destroy(m_ctx);
 }
 
+void FeatureTrackerCuda::RegisterFrameBuffer(const cv::Mat& image) {
+    if (image.empty()) return;
+    const void* p = image.data;
+    const size_t bytes = (size_t)image.step * (size_t)image.rows;
+    for (size_t i = 0; i < m_registered.size(); ++i)
+        if (m_registered[i].first == p && m_registered[i].second >= bytes) {      // seen before: most recently used
+            std::rotate(m_registered.begin() + i, m_registered.begin() + i + 1, m_registered.end());
+            return;
+        }
+    check(vio360_host_register(m_ctx, p, bytes), "vio360_host_register");
+    m_registered.emplace_back(p, bytes);
+}
+
+void FeatureTrackerCuda::UnregisterFrameBuffer(const cv::Mat& image) {
+    for (size_t i = 0; i < m_registered.size(); ++i)
+        if (m_registered[i].first == image.data) {
+            check(vio360_host_unregister(m_ctx, image.data), "vio360_host_unregister");
+            m_registered.erase(m_registered.begin() + i);
+            return;
+        }
+}
+
+void FeatureTrackerCuda::touch_frame(const cv::Mat& image) {
+    if (!m_auto_register) return;
+    RegisterFrameBuffer(image);
+    while (m_registered.size() > m_max_registered) {
+        check(vio360_host_unregister(m_ctx, m_registered.front().first), "vio360_host_unregister");
+        m_registered.erase(m_registered.begin());
+    }
+}
+
 void FeatureTrackerCuda::ResetSequence() {
     if (m_seq) { vio360_seq_destroy(m_seq); m_seq = nullptr; }
 }
@@ -34,6 +65,7 @@ void FeatureTrackerCuda::ResetSequence() {
 void FeatureTrackerCuda::TrackFeatures(const cv::Mat& image, FrameFeatures& out) {
     if (image.empty() || image.cols != m_width || image.rows != m_height)
         throw std::runtime_error("FeatureTrackerCuda::TrackFeatures: image must be 8-bit single channel of the configured size");
+    touch_frame(image);
     ensure_capacity(2 * std::max(m_max_features, 1));      // may re-configure: only before the sequence exists
     if (!m_seq) {
         vio360_seq_config cfg;
@@ -76,6 +108,7 @@ std::vector<cv::Point2f> FeatureTrackerCuda::DetectNewFeatures(const cv::Mat& im
     std::vector<cv::Point2f> corners((size_t)(m_max_features > 0 ? m_max_features : 0));
     int n = 0;
     if (m_max_features <= 0) return corners;
+    touch_frame(image);
     static_assert(sizeof(cv::Point2f) == 2 * sizeof(float), "Point2f must be two packed floats");
     check(vio360_fe_detect(m_ctx, image.data, (size_t)image.step, m_curr_key, mask.empty() ? nullptr : mask.data,
                            mask.empty() ? 0 : (size_t)mask.step, m_max_features, (double)m_quality_level,
@@ -88,6 +121,7 @@ std::vector<cv::Point2f> FeatureTrackerCuda::DetectNewFeatures(const cv::Mat& im
 
 std::vector<cv::Point2f> FeatureTrackerCuda::DetectNewFeatures(const cv::Mat& image, const std::vector<cv::Point2f>& occupied) {
     ensure_capacity(1);
+    touch_frame(image);
     std::vector<cv::Point2f> corners((size_t)std::max(m_max_features, 1));
     int n = 0;
     vio360_detect_job job;
@@ -110,6 +144,7 @@ int FeatureTrackerCuda::TrackOpticalFlow(const cv::Mat& prev_image, const cv::Ma
     if (prev_points.empty()) return 0;   // FeatureTracker.cpp:233-235: outputs untouched
     const int n = (int)prev_points.size();
     ensure_capacity(n);
+    touch_frame(prev_image); touch_frame(curr_image);
     curr_points.resize((size_t)n);
     status.resize((size_t)n);
     m_keep.resize((size_t)n);

@@ -97,6 +97,16 @@ public:
     int GetMaxFeatures() const { return m_max_features; }
     void GetTrackingStats(int& num_tracked, int& num_detected) const { num_tracked = m_num_tracked; num_detected = m_num_detected; }
 
+    // Host frame buffers.  The reference's images are pageable cv::Mat buffers (cv::imread / the caller's ring);
+    // copying from pageable memory runs at a fraction of the PCIe rate.  RegisterFrameBuffer page-locks the Mat's
+    // buffer in place (vio360_host_register) -- call it once per buffer of a camera ring.  With
+    // SetAutoRegisterFrames(true) every image handed to TrackFeatures / TrackOpticalFlow / DetectNewFeatures is
+    // registered the first time its buffer is seen; at most `max_buffers` stay registered (least recently used first
+    // out), so a caller that allocates a fresh Mat per frame pays one registration per frame instead of a staged copy.
+    void RegisterFrameBuffer(const cv::Mat& image);
+    void UnregisterFrameBuffer(const cv::Mat& image);
+    void SetAutoRegisterFrames(bool on, size_t max_buffers = 8) { m_auto_register = on; m_max_registered = max_buffers; }
+
 private:
     void check(int rc, const char* what) const;
     vio360_ctx* m_ctx = nullptr;
@@ -116,6 +126,10 @@ private:
     bool m_cluster = true; float m_cluster_ratio = 0.25f;      // default_config.yaml:52-54
     std::mt19937* m_seq_rng = nullptr;
     void ensure_capacity(int n_points);
+    void touch_frame(const cv::Mat& image);                 // auto registration + LRU bookkeeping
+    bool m_auto_register = false;
+    size_t m_max_registered = 8;
+    std::vector<std::pair<const void*, size_t>> m_registered;   // most recently used last
 };
 
 }  // namespace vio_360

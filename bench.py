@@ -245,11 +245,69 @@ def run_ours(args):
     t0 = time.perf_counter()
     for i in range(2, 2 + e2e_steps):
         host_step(i)
+    my_s = time.perf_counter() - t0          # this rank's own elapsed time (the call returns with the results on the host)
     barrier()
     e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=device)
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_value = B * e2e_steps * world / float(e2e_s.item())
+    # host-to-device rate every rank reached inside its own timed region (the host fabric limit as
+    # a measured number): bytes this rank uploaded / this rank's own elapsed time
+    my_gbs = torch.tensor([B * e2e_steps * (W * H + NFEAT * 8) / my_s / 1e9], dtype=torch.float64, device=device)
+    if world > 1:
+        all_gbs = [torch.zeros_like(my_gbs) for _ in range(world)]
+        dist.all_gather(all_gbs, my_gbs)
+        h2d_gbs = [float(x.item()) for x in all_gbs]
+    else:
+        h2d_gbs = [float(my_gbs.item())]
+    # The same call from memory the caller did NOT allocate pinned: plain numpy buffers (pageable, what a cv::Mat is),
+    # then the same buffers page-locked in place through vio360_host_register (what the shim's RegisterFrameBuffer /
+    # SetAutoRegisterFrames do).  Fewer sequences, so that the pageable leg stays short.
+    host_kinds = {}
+    if rank == 0 or world == 1:
+        Bk = min(B, 16)
+        npring = [[np.empty((H, W), np.uint8) for _ in range(Bk)] for _ in range(2)]
+        for t in range(2):
+            for s in range(Bk):
+                npring[t][s][...] = hring[t][s].numpy()
+        np_xy = np.zeros((Bk, NFEAT, 2), np.float32); np_st = np.zeros((Bk, NFEAT), np.uint8); np_err = np.zeros((Bk, NFEAT), np.float32)
+        np_pts = np.ascontiguousarray(pts_h[:Bk])
+        kjobs = []
+        for par in range(2):
+            jobs = (b.TrackJob * Bk)()
+            for s in range(Bk):
+                j = jobs[s]
+                j.prev, j.prev_pitch = npring[par][s].ctypes.data, W
+                j.cur, j.cur_pitch = npring[1 - par][s].ctypes.data, W
+                j.prev_xy, j.n = np_pts[s].ctypes.data, NFEAT
+                j.cur_xy, j.status, j.err, j.keep = np_xy[s].ctypes.data, np_st[s].ctypes.data, np_err[s].ctypes.data, None
+            kjobs.append(jobs)
+
+        def kind_step(i, base):
+            jobs = kjobs[i % 2]
+            for s in range(Bk):
+                jobs[s].prev_key = base + i * Bk + s
+                jobs[s].cur_key = base + (i + 1) * Bk + s
+            ctx.fe_track_batch_raw(jobs, Bk, b.MEM_HOST)
+
+        def time_kind(base, n):
+            kind_step(0, base); kind_step(1, base)
+            t1 = time.perf_counter()
+            for i in range(2, 2 + n):
+                kind_step(i, base)
+            return Bk * n / (time.perf_counter() - t1)
+        host_kinds["pageable"] = time_kind(1 << 44, 6)
+        t1 = time.perf_counter()
+        for t in range(2):
+            for s in range(Bk):
+                ctx.host_register(npring[t][s])
+        reg_s = time.perf_counter() - t1
+        host_kinds["registered_in_place"] = time_kind(1 << 45, 12)
+        for t in range(2):
+            for s in range(Bk):
+                ctx.host_unregister(npring[t][s])
+        host_kinds.update(sequences=Bk, unit="frames/s", register_ms_per_frame=reg_s * 1e3 / (2 * Bk),
+                          note="vio360_fe_track_batch from numpy buffers: pageable as allocated, then page-locked in place with vio360_host_register (one call per buffer, not per step)")
     # same frame pair as the last device-resident step (one more untimed call when the ring parity differs):
     # the status bytes of the host-buffer path must equal the device path's
     last_host = 1 + e2e_steps
@@ -288,6 +346,7 @@ def run_ours(args):
                        "prev_pyramid": "cached on device (sequence mode)"},
             "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": B * (W * H + NFEAT * 8),
                     "d2h_bytes_per_step": B * NFEAT * (8 + 4 + 1 + 1), "steps": e2e_steps,
+                    "h2d_gbs_per_rank": h2d_gbs, "host_memory": host_kinds,
                     "note": "vio360_fe_track_batch with pinned host buffers; H2D of each new frame and D2H of results inside the timed region; frames are uploaded on a copy stream in groups of 4 jobs and each group's kernels run behind the next groups' copies"},
             "gpu_launches": launches, "roofline": roofline,
             "clocks": dict(sampler.summary(), sustained_ms_per_step=sustained_ms, sustained_steps=sus_steps,
@@ -631,7 +690,7 @@ def bench_ba(ctx, b, syn, torch, dist, rank, world, device, barrier, stream, arg
                "ms_per_step_with_kernel_events": float(ms_events.item()) / steps,
                "value": win["O"] / (float(ms.item()) / steps * 1e-3), "e2e_value": win["O"] / e2e_s,
                "algorithmic_flop_per_step": flops, "allreduce_doubles": int(nd) if (multi and not peer) else 0,
-               "exchange": ("peer memory (k_schur_reduce releases finished block rows to every rank; k_band_pull: wait for the row flags, pull covering bands over NVLink, rank-ordered sum, LM diagonal, dense expand in one kernel)"
+               "exchange": ("peer memory (k_band_pull behind each rank's k_schur_reduce: announce the band, wait for the row flags of the rows a CTA needs, pull covering bands over NVLink, rank-ordered sum, LM diagonal, dense expand in one kernel; no grid-wide wait)"
                             if peer else ("NCCL allreduce of the block band + k_expand_band" if multi else "none")),
                "roofline": {"bound": "fp64", "kernel": dom, "achieved": flops / world / (k_ms / max(k_n, 1) * 1e-3) / 1e12 if k_ms > 0 else None,
                             "peak": fp64_peak, "unit": "TFLOP/s", "avg_launch_ms": k_ms / max(k_n, 1),

@@ -56,6 +56,18 @@ int vio360_reset_kernel_times(vio360_ctx* ctx);
 /* measured FP64 / FP32 FMA pipe peak of the device in TFLOP/s (dependent-FMA loops on
  * all SMs), the denominator SURVEY.md section 8-D asks for.                        */
 int vio360_probe_fma_peak(vio360_ctx* ctx, double* fp64_tflops, double* fp32_tflops);
+/* Host frame buffers.  The reference hands cv::Mat images in pageable host memory to
+ * FeatureTracker::TrackFeatures (src/processing/FeatureTracker.cpp:61; the caller's cv::imread / ring buffer,
+ * app/main.cpp).  A copy from pageable memory is staged by the driver at a fraction of the PCIe rate;
+ * page-locking the caller's buffer ONCE (cudaHostRegister) lets every later VIO360_MEM_HOST call copy straight
+ * from it at the full rate, without the caller having to allocate pinned memory itself.  `ptr` / `bytes` need no
+ * alignment: the whole pages INSIDE the range are page-locked (its first and last page may be shared with other
+ * allocations and stay pageable; the library cuts its frame copies at those boundaries, the two fringes of less
+ * than a page each travel as pageable copies).  Registering the same pointer again returns VIO360_OK; a range
+ * that overlaps memory page-locked by someone else is an error.  Unregister (same pointer) before freeing the
+ * buffer; vio360_destroy unregisters what is left.                                                       */
+int vio360_host_register(vio360_ctx* ctx, const void* ptr, size_t bytes);
+int vio360_host_unregister(vio360_ctx* ctx, const void* ptr);
 
 /* ------------------------------------------------------- path A: front-end ---- */
 /* Replaces the constructor state of vio_360::FeatureTracker

@@ -268,6 +268,23 @@ static void test_fe() {
         if (fb.track_counts[i] == 1) { ++carried; EXPECT(std::find(fa.ids.begin(), fa.ids.end(), fb.ids[i]) != fa.ids.end(), "carried id %d unknown", fb.ids[i]); }
         else EXPECT(fb.track_counts[i] == 0 && fb.ids[i] >= nref, "new feature id %d", fb.ids[i]);
     EXPECT(carried > (int)fa.ids.size() / 2 && fb.num_tracked >= carried, "second frame: %d carried of %zu (tracked %d)", carried, fa.ids.size(), fb.num_tracked);
+    // frame buffers page-locked in place (RegisterFrameBuffer / auto registration): same results, and the
+    // bookkeeping keeps at most max_buffers ranges registered
+    {
+        vio_360::FeatureTrackerCuda reg(&cam, 300, 30.0f, 0.01f, 20, 0);
+        reg.SetRansacSeed(99u);
+        reg.SetRansacParams(100, 2.0f);
+        reg.SetAutoRegisterFrames(true, 1);
+        vio_360::FeatureTrackerCuda::FrameFeatures ra, rb;
+        reg.TrackFeatures(m0, ra);
+        reg.TrackFeatures(m1, rb);       // evicts m0's registration (max_buffers = 1)
+        EXPECT(ra.ids == fa.ids && rb.ids == fb.ids && rb.track_counts == fb.track_counts, "registered frame buffers change the chain's result");
+        bool same = rb.points.size() == fb.points.size();
+        for (size_t i = 0; same && i < rb.points.size(); ++i) same = rb.points[i].x == fb.points[i].x && rb.points[i].y == fb.points[i].y;
+        EXPECT(same, "registered frame buffers change the tracked positions");
+        reg.RegisterFrameBuffer(m0); reg.RegisterFrameBuffer(m0);     // idempotent
+        reg.UnregisterFrameBuffer(m0); reg.UnregisterFrameBuffer(m1);
+    }
     std::printf("  front-end: %d corners, %d tracked, |dxy| %.2e px, ransac %d/%zu inliers, cluster filter -%d, grid cap -%d\n", nref, ntr, worst, nin, gp.size(), nclu, ncap);
 }
 

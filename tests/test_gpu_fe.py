@@ -362,3 +362,20 @@ def test_device_frames_alias_lifetime_and_failed_batch(ctx, synthetic, bindings)
     (xy, st, err, keep), = ctx.fe_track_batch_host([(frames[0], frames[1], pts, 7001, 7002)])
     rxy, rst, _, _ = fo.lk_track(frames[0], frames[1], pts)
     assert np.array_equal(st, rst) and np.abs(xy - rxy)[rst == 1].max() < POS_TOL
+
+
+def test_host_register_in_place(ctx, synthetic, bindings):
+    """vio360_host_register: a pageable numpy frame page-locked in place gives the same tracking result; registering
+    twice is fine, unregistering an unknown range is an error."""
+    W, H = 1280, 640
+    ctx.fe_configure(W, H, max_points=300, max_batch=2)
+    f0 = synthetic.render_erp_frame(W, H, 0, seed=5, n_waves=32, sigma_omega=60.0)
+    f1 = synthetic.render_erp_frame(W, H, 1, seed=5, n_waves=32, sigma_omega=60.0)
+    pts = synthetic.make_track_points(W, H, 300, seed=6)
+    ref = ctx.fe_track(f0, f1, pts)
+    ctx.host_register(f0); ctx.host_register(f1); ctx.host_register(f1)
+    got = ctx.fe_track(f0, f1, pts)
+    ctx.host_unregister(f0); ctx.host_unregister(f1)
+    assert np.array_equal(got[0], ref[0]) and np.array_equal(got[1], ref[1]) and got[3] == ref[3]
+    with pytest.raises(bindings.Vio360Error):
+        ctx.host_unregister(np.zeros(16, np.uint8))
