@@ -5,6 +5,7 @@ fallback.  Loading fails loudly when the library has not been built, and every c
 raises Vio360Error when the C ABI reports an error (e.g. no CUDA device).
 """
 import ctypes as C
+import weakref
 import os
 
 import numpy as np
@@ -191,6 +192,7 @@ class Context:
             raise Vio360Error("vio360_create failed (%d): %s" % (rc, self.lib.vio360_last_error(None).decode()))
         self.h = h
         self.device = device
+        self._children = weakref.WeakSet()    # BA windows of this context: destroyed before it, whatever the GC order
 
     def check(self, rc):
         if rc != 0:
@@ -198,6 +200,8 @@ class Context:
 
     def close(self):
         if getattr(self, "h", None):
+            for c in list(getattr(self, "_children", ())):
+                c.close()
             self.lib.vio360_destroy(self.h)
             self.h = None
 
@@ -473,6 +477,7 @@ class BAWindow:
         h = C.c_void_p()
         ctx.check(self.lib.vio360_ba_create(ctx.h, self.K, self.M, self.O, C.byref(h)))
         self.h = h
+        ctx._children.add(self)
         a = dict(pose_idx=np.ascontiguousarray(win["pose_idx"], np.int32),
                  point_idx=np.ascontiguousarray(win["point_idx"], np.int32),
                  u=np.ascontiguousarray(win["obs_u"], np.float64), v=np.ascontiguousarray(win["obs_v"], np.float64),
@@ -488,7 +493,8 @@ class BAWindow:
 
     def close(self):
         if getattr(self, "h", None):
-            self.lib.vio360_ba_destroy(self.h)
+            if getattr(self.ctx, "h", None):      # the native window points into its context
+                self.lib.vio360_ba_destroy(self.h)
             self.h = None
 
     def __del__(self):

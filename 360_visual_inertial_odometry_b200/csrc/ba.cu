@@ -1649,6 +1649,7 @@ static int solve_reduced_dev(vio360_ba* ba, bool want_points) {
         if (!ba->chol_attr_set) {
             VIO_CUDA(ctx, cudaFuncSetAttribute(k_chol_skyline, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
             VIO_CUDA(ctx, cudaFuncSetAttribute(k_chol_band, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+            VIO_CUDA(ctx, cudaFuncSetAttribute(k_chol_band_reg, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
             ba->chol_attr_set = true;
         }
         int* d_status = reinterpret_cast<int*>(ba->d_x.as<double>() + n);
@@ -1657,9 +1658,18 @@ static int solve_reduced_dev(vio360_ba* ba, bool want_points) {
             // banded window: trailing matrix in shared memory, S itself is only read
             VIO_CUDA(ctx, ba->d_chol.reserve(((size_t)nb * (kCholWb - 1) * 36 + (size_t)nb * 42) * 8));
             double* Lcol = ba->d_chol.as<double>();
+            // Windows of up to 24 free poses (the reference's local BA: 10 keyframes) fit the shared-memory window whole
+            // and finish in a few columns: 25 us against 34 us for the register-window kernel, whose set-up they do not
+            // amortise.  Larger systems: registers (0.45 ms against 0.81 ms at 199 free poses).  VIO360_CHOL_SMEM=1: A/B switch.
+            static const bool force_smem_window = getenv("VIO360_CHOL_SMEM") != nullptr;
+            const bool smem_window = force_smem_window || nb <= kCholWb;
             { KernelTimer kt_(ctx, "k_chol_band");
-            k_chol_band<<<1, kCholThreads, band_smem, st>>>(dS, nb, ba->d_reachF.as<int>(), Lcol, Lcol + (size_t)nb * (kCholWb - 1) * 36,
-                                                           ba->d_x.as<double>(), d_status);
+            if (smem_window)
+                k_chol_band<<<1, kCholThreads, band_smem, st>>>(dS, nb, ba->d_reachF.as<int>(), Lcol, Lcol + (size_t)nb * (kCholWb - 1) * 36,
+                                                               ba->d_x.as<double>(), d_status);
+            else
+                k_chol_band_reg<<<1, kChol2Threads, (size_t)(2 * 6 * kCholWb * 6 + kChol2Threads * 36 + n) * sizeof(double), st>>>(
+                    dS, nb, Lcol, Lcol + (size_t)nb * (kCholWb - 1) * 36, ba->d_x.as<double>(), d_status);
             }
             VIO_LAUNCH_CHECK(ctx);
             KernelTimer kt_(ctx, "k_chol_band_back");

@@ -276,6 +276,262 @@ __global__ void __launch_bounds__(kCholThreads) k_chol_band(const double* __rest
     if (tid == 0) status[0] = sbad;
 }
 
+// Register-window form of the banded factorisation (round 2).  k_chol_band keeps the active window in shared memory
+// and its trailing update issues one broadcast load per multiply-add: the shared-memory pipe, not the FP64 pipe, sets
+// its 4 us per column.  Here every 6x6 block of the window lives in the REGISTERS of one thread for as long as it is
+// in the window:
+//   * an owner thread stands for an unordered pair {a, b} of residues mod Wb = 24.  At column j the window holds block
+//     rows / columns j .. j + 23, one per residue; the pair's block is (i, k) = the two window indices with those
+//     residues, larger first.  When column k leaves the window its block (i, k) is finished, and the block that enters
+//     with the new row, (k + 24, i), has the SAME residue pair: the thread moves straight on to it (prefetched with
+//     cp.async from the untouched S into the thread's shared-memory slot when the previous block was taken up), so no
+//     register block ever idles;
+//   * twelve warps own the 276 off-diagonal pairs as 8 x 4 tiles of (a, b): a warp's loads of P touch at most 12
+//     distinct rows (one or two shared-memory wavefronts per 128-bit load) instead of 32 unrelated ones;
+//   * warp 0 owns the 24 diagonal blocks (lower triangles) and has its scheduler (and FP64 pipe quarter) to itself: the
+//     tile warps are the warps 1-3, 5-7, 9-11, 13-15.  In the update phase of column j its lane of residue j + 1 updates
+//     and then factorises the next pivot -- the only serial part of the whole factorisation -- while the tile warps are
+//     busy with their 216 DFMA per thread (measured: one warp alone saturates its scheduler's FP64 pipe,
+//     tools/ubench_dfma_warps.cu, so the pivot chain would otherwise queue behind them);
+//   * per column: [panel] 138 threads solve one row each of the column's blocks against L_jj (handed over through
+//     shared memory by their owners), results go to shared memory transposed ([m][residue][6]) and to Lcol; one more
+//     thread finishes the right-hand side of block j.  barrier.  [update] as above; the owners of column j + 1 hand
+//     their blocks over.  barrier.
+// Output layout identical to k_chol_band (Lcol, Ldiag, b), so k_chol_band_back serves both.
+constexpr int kChol2Threads = 384;        // 12 warps at <= 168 registers: warp 0 = diagonal blocks, nine tile warps, two that only help with the panel
+constexpr int kChol2PanelT0 = 192;        // the panel rows are solved by threads 192 .. 330
+
+// block (i, k) of S (zeros outside the matrix) -> a thread's prefetch slot, asynchronously
+__device__ __forceinline__ void chol2_prefetch(const double* __restrict__ S, int n, int nb, int i, int k, double* slot) {
+    if (i < nb && k < nb) {
+        const double* src = S + (size_t)(6 * i) * n + 6 * k;
+        const uint32_t dst = (uint32_t)__cvta_generic_to_shared(slot);
+#pragma unroll
+        for (int r = 0; r < 6; ++r)
+#pragma unroll
+            for (int h = 0; h < 3; ++h)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(dst + (r * 6 + 2 * h) * 8), "l"(src + (size_t)r * n + 2 * h) : "memory");
+    } else {
+#pragma unroll
+        for (int e = 0; e < 18; ++e) reinterpret_cast<double2*>(slot)[e] = make_double2(0.0, 0.0);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+// slot (row-major block) -> registers
+__device__ __forceinline__ void chol2_take(double (&blk)[36], const double* slot) {
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+#pragma unroll
+    for (int e = 0; e < 18; ++e) { const double2 v = reinterpret_cast<const double2*>(slot)[e]; blk[2 * e] = v.x; blk[2 * e + 1] = v.y; }
+}
+__device__ __forceinline__ void chol2_store(const double (&blk)[36], double* dst) {
+#pragma unroll
+    for (int e = 0; e < 18; ++e) reinterpret_cast<double2*>(dst)[e] = make_double2(blk[2 * e], blk[2 * e + 1]);
+}
+// dg = lower triangle (packed, dg[i * (i + 1) / 2 + k]) of the updated diagonal block (j, j): right-looking in-place
+// Cholesky (the dependent chain per step is rsqrt, one product, one update); L_jj and the reciprocal pivots go to
+// Ldiag, L_jj^-1 to shared memory for the panel; false if not positive definite
+__device__ __forceinline__ bool chol2_factor(double (&dg)[21], double* sLi, double* __restrict__ Ldiag_j) {
+    bool ok = true;
+    double inv[6];
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+        double d = dg[j * (j + 1) / 2 + j];
+        if (!(d > 0.0)) { ok = false; d = 1.0; }
+        const double iv = vio_rsqrt(d);
+        inv[j] = iv;
+        dg[j * (j + 1) / 2 + j] = d * iv;
+#pragma unroll
+        for (int i = 0; i < 6; ++i)
+            if (i > j) dg[i * (i + 1) / 2 + j] *= iv;
+#pragma unroll
+        for (int i = 0; i < 6; ++i)
+#pragma unroll
+            for (int k = 0; k < 6; ++k)
+                if (i > j && k > j && k <= i) dg[i * (i + 1) / 2 + k] -= dg[i * (i + 1) / 2 + j] * dg[k * (k + 1) / 2 + j];
+    }
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+        for (int k = 0; k < 6; ++k) Ldiag_j[i * 6 + k] = k <= i ? dg[i * (i + 1) / 2 + k] : 0.0;
+#pragma unroll
+    for (int e = 0; e < 6; ++e) Ldiag_j[36 + e] = inv[e];
+    // Li = L^-1 (lower triangular), column by column; the panel rows are then independent dot products
+    // P[r][c] = sum_{k <= c} A[r][k] Li[c][k] instead of a 21-deep substitution chain
+    double li[21];
+#pragma unroll
+    for (int c = 0; c < 6; ++c)
+#pragma unroll
+        for (int i = 0; i < 6; ++i)
+            if (i >= c) {
+                double sacc = (i == c) ? 1.0 : 0.0;
+#pragma unroll
+                for (int k = 0; k < 6; ++k)
+                    if (k >= c && k < i) sacc -= dg[i * (i + 1) / 2 + k] * li[k * (k + 1) / 2 + c];
+                li[i * (i + 1) / 2 + c] = sacc * inv[i];
+            }
+#pragma unroll
+    for (int i = 0; i < 6; ++i)
+#pragma unroll
+        for (int k = 0; k < 6; ++k) sLi[i * 6 + k] = k <= i ? li[i * (i + 1) / 2 + k] : 0.0;
+    return ok;
+}
+
+__global__ void __maxnreg__(168) k_chol_band_reg(const double* __restrict__ S, int nb, double* __restrict__ Lcol,
+                                                  double* __restrict__ Ldiag, double* __restrict__ b, int* __restrict__ status) {
+    extern __shared__ double sm2[];
+    double* panelT = sm2;                               // [6][Wb][6]: panelT[m][res][r] = P_res[r][m]
+    double* Acol = panelT + 6 * kCholWb * 6;            // [Wb][36]: blocks (i, j + 1), i by residue, for the next panel phase
+    double* pref = Acol + kCholWb * 36;                 // [threads][36]: every owner's NEXT block, prefetched with cp.async
+    double* sb = pref + kChol2Threads * 36;             // [n]
+    __shared__ __align__(16) double sLi[36], sY[6];   // L_jj^-1 of the current column, y_j
+    __shared__ int sbad;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, n = 6 * nb;
+    const bool diag = warp == 0 && lane < kCholWb;
+    // Residue pair of this thread.  The 24 residues form three groups of 8; nine warps hold the 276 off-diagonal pairs:
+    // three the 28 pairs inside one group (8 distinct rows of P per load), six an 8 x 4 tile between two groups (12 rows).
+    // Warp w runs on scheduler w % 4: the diagonal warp shares scheduler 0 with two tile warps only, the others get
+    // 3 + 2 + 2, so that the serial pivot chain never queues behind three streams of DFMA.
+    int a = lane, bb = lane;
+    bool bulk = false;
+    {
+        const int tile_of_warp[12] = {-1, 2, 5, 7, 0, 3, 6, 8, 1, 4, -1, -1};
+        const int t = tile_of_warp[warp];
+        if (t >= 0 && t < 3) {   // pairs inside group t: lane -> (x, y), x > y
+            int x = 1;
+            while ((x + 1) * x / 2 <= lane) ++x;
+            const int y = lane - x * (x - 1) / 2;
+            a = 8 * t + x; bb = 8 * t + y;
+            bulk = lane < 28;
+        } else if (t >= 3) {     // tiles 3, 4: groups 1 x 0; 5, 6: 2 x 0; 7, 8: 2 x 1 (two halves of the lower group each)
+            const int q = (t - 3) >> 1, ga = q == 0 ? 1 : 2, gb = q == 2 ? 1 : 0;
+            a = 8 * ga + (lane >> 2); bb = 8 * gb + 4 * ((t - 3) & 1) + (lane & 3);
+            bulk = true;
+        }
+    }
+    const int prow = tid - kChol2PanelT0;               // panel row of this thread (0 .. 138 take part)
+    double* mine = pref + tid * 36;
+    if (tid == 0) sbad = 0;
+    for (int e = tid; e < n; e += kChol2Threads) sb[e] = b[e];
+    double blk[36];   // tile warps: the block, row-major; diagonal lanes: dg = the packed lower triangle in blk[0..20]
+    double (&dg)[21] = reinterpret_cast<double (&)[21]>(blk);
+    // column 0: block (a, b), the block after it is (b + 24, a); a diagonal owner moves down the diagonal
+    if (diag) {
+        chol2_prefetch(S, n, nb, a, a, mine);
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+#pragma unroll
+        for (int i = 0; i < 6; ++i)
+#pragma unroll
+            for (int k = 0; k <= i; ++k) dg[i * (i + 1) / 2 + k] = mine[i * 6 + k];
+        chol2_prefetch(S, n, nb, a + kCholWb, a + kCholWb, mine);
+        if (a == 0 && !chol2_factor(dg, sLi, Ldiag)) sbad = 1;
+    } else if (bulk) {
+        chol2_prefetch(S, n, nb, a, bb, mine);
+        chol2_take(blk, mine);
+        chol2_prefetch(S, n, nb, bb + kCholWb, a, mine);
+        if (bb == 0) chol2_store(blk, Acol + a * 36);
+    }
+    __syncthreads();
+    for (int j = 0; j < nb; ++j) {
+        const int jm = j % kCholWb;
+        // ---- panel: one row of the column's blocks per thread, X = A L_jj^-T; row 138 finishes rhs block j
+        if (prow >= 0 && prow <= (kCholWb - 1) * 6) {
+            const bool rhs = prow == (kCholWb - 1) * 6;
+            const int bi = prow / 6, ar = prow - bi * 6;
+            const int res = (jm + 1 + bi) % kCholWb;
+            const double* src = rhs ? sb + 6 * j : Acol + res * 36 + ar * 6;
+            double v[6], o[6];
+#pragma unroll
+            for (int c = 0; c < 6; ++c) v[c] = src[c];
+#pragma unroll
+            for (int c = 0; c < 6; ++c) {   // o = v L^-T: six independent dot products
+                double acc = v[c] * sLi[c * 6 + c];
+#pragma unroll
+                for (int k = 0; k < c; ++k) acc += v[k] * sLi[c * 6 + k];
+                o[c] = acc;
+            }
+            if (rhs) {
+#pragma unroll
+                for (int c = 0; c < 6; ++c) { sb[6 * j + c] = o[c]; sY[c] = o[c]; }
+            } else {
+#pragma unroll
+                for (int c = 0; c < 6; ++c) {
+                    panelT[(c * kCholWb + res) * 6 + ar] = o[c];
+                    Lcol[((size_t)j * (kCholWb - 1) + bi) * 36 + ar * 6 + c] = o[c];
+                }
+            }
+        }
+        __syncthreads();
+        // ---- update
+        if (diag) {
+            const int dd = (a - jm + kCholWb) % kCholWb;   // this lane's block is (j + dd, j + dd)
+            if (dd >= 1) {
+                const double* pd = panelT + a * 6;
+#pragma unroll
+                for (int m = 0; m < 6; ++m) {
+                    const double2 r0 = *reinterpret_cast<const double2*>(pd + m * kCholWb * 6), r1 = *reinterpret_cast<const double2*>(pd + m * kCholWb * 6 + 2),
+                                  r2 = *reinterpret_cast<const double2*>(pd + m * kCholWb * 6 + 4);
+                    const double rv[6] = {r0.x, r0.y, r1.x, r1.y, r2.x, r2.y};
+#pragma unroll
+                    for (int r = 0; r < 6; ++r)
+#pragma unroll
+                        for (int c = 0; c <= r; ++c) dg[r * (r + 1) / 2 + c] -= rv[r] * rv[c];
+                }
+                if (dd == 1 && j + 1 < nb) {   // the next pivot: the serial part, overlapped with the other warps' updates
+                                if (!chol2_factor(dg, sLi, Ldiag + (size_t)(j + 1) * 42)) sbad = 1;
+                            }
+            } else {   // (j, j) is finished: (j + 24, j + 24) enters, (j + 48, j + 48) is prefetched
+                asm volatile("cp.async.wait_group 0;" ::: "memory");
+#pragma unroll
+                for (int i = 0; i < 6; ++i)
+#pragma unroll
+                    for (int k = 0; k <= i; ++k) dg[i * (i + 1) / 2 + k] = mine[i * 6 + k];
+                chol2_prefetch(S, n, nb, j + 2 * kCholWb, j + 2 * kCholWb, mine);
+            }
+        } else {
+            if (prow >= 0 && prow < (kCholWb - 1) * 6) {   // right-hand side rows below block j: b -= P y_j
+                const int row = 6 * (j + 1) + prow;
+                if (row < n) {
+                    const int res = (jm + 1 + prow / 6) % kCholWb, ar = prow % 6;
+                    double acc = 0.0;
+#pragma unroll
+                    for (int m = 0; m < 6; ++m) acc += panelT[(m * kCholWb + res) * 6 + ar] * sY[m];
+                    sb[row] -= acc;
+                }
+            }
+            if (bulk) {
+                const int da = (a - jm + kCholWb) % kCholWb, db = (bb - jm + kCholWb) % kCholWb;
+                const int di = max(da, db), dk = min(da, db);
+                if (dk != 0) {
+                    // block (i, k) = (j + di, j + dk): rows of P_i times rows of P_k; the residue of i is a's when da > db
+                    const double* pr = panelT + (da > db ? a : bb) * 6;
+                    const double* pc = panelT + (da > db ? bb : a) * 6;
+#pragma unroll
+                    for (int m = 0; m < 6; ++m) {
+                        const double2 r0 = *reinterpret_cast<const double2*>(pr + m * kCholWb * 6), r1 = *reinterpret_cast<const double2*>(pr + m * kCholWb * 6 + 2),
+                                      r2 = *reinterpret_cast<const double2*>(pr + m * kCholWb * 6 + 4);
+                        const double2 c0 = *reinterpret_cast<const double2*>(pc + m * kCholWb * 6), c1 = *reinterpret_cast<const double2*>(pc + m * kCholWb * 6 + 2),
+                                      c2 = *reinterpret_cast<const double2*>(pc + m * kCholWb * 6 + 4);
+                        const double rv[6] = {r0.x, r0.y, r1.x, r1.y, r2.x, r2.y}, cv[6] = {c0.x, c0.y, c1.x, c1.y, c2.x, c2.y};
+#pragma unroll
+                        for (int r = 0; r < 6; ++r)
+#pragma unroll
+                            for (int c = 0; c < 6; ++c) blk[r * 6 + c] -= rv[r] * cv[c];
+                    }
+                } else {
+                    // block (j + di, j) is finished: take up (j + 24, j + di), prefetch the one after it, (j + di + 24, j + 24)
+                    chol2_take(blk, mine);
+                    chol2_prefetch(S, n, nb, j + di + kCholWb, j + kCholWb, mine);
+                }
+                // blocks of column j + 1 join the next panel: (j + di, j + 1) after its update, (j + 24, j + 1) as taken up
+                if (dk == 1 || (dk == 0 && di == 1)) chol2_store(blk, Acol + (dk == 1 ? (da > db ? a : bb) : jm) * 36);
+            }
+        }
+        __syncthreads();
+    }
+    for (int e = tid; e < n; e += kChol2Threads) b[e] = sb[e];
+    if (tid == 0) status[0] = sbad;
+}
+
 // Backward substitution L^T x = y for the banded factor: one warp, the next column's data is
 // fetched while the current one is reduced (the chain is nb dependent 6x6 solves).
 __global__ void __launch_bounds__(32) k_chol_band_back(int nb, const int* __restrict__ reach, const double* __restrict__ Lcol,

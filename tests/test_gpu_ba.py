@@ -464,8 +464,12 @@ def test_large_window_properties(bindings, ctx, synthetic):
     assert rel_err(r[idx], ro) < TOL and rel_err(Jp[idx], Jpo) < TOL and rel_err(Jl[idx], Jlo) < TOL
     # full Schur parity on this size too (the oracle needs a few seconds)
     Wo = ba_oracle.Window(win)
-    So, rhso, _ = Wo.schur(r, Jp, Jl, D)
+    So, rhso, fm = Wo.schur(r, Jp, Jl, D)
     assert rel_err(S, So) < TOL and rel_err(rhs, rhso) < TOL
+    # and the solve at this size: 199 dependent block columns through the register-window band Cholesky
+    dp_ref, dl_ref = Wo.solve_step(r, Jp, Jl, D, So, rhso, fm)
+    dp, dl = ba.solve_reduced(True)
+    assert rel_err(dp, dp_ref) < 1e-7 and rel_err(dl, dl_ref) < 1e-7
     ba.close()
 
 
