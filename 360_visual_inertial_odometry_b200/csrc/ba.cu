@@ -1760,10 +1760,12 @@ extern "C" int vio360_ba_lm_solve(vio360_ba* ba, const vio360_lm_options* opt, d
     VIO_CUDA(ctx, ba->d_step.reserve((size_t)nvar * 8)); VIO_CUDA(ctx, ba->d_colsq.reserve((size_t)nvar * 8));
     VIO_CUDA(ctx, ba->d_scale.reserve((size_t)nvar * 8)); VIO_CUDA(ctx, ba->d_lm_state.reserve(2 * sizeof(LmState)));
     const int nbo = std::max(1, (O + 127) / 128), nbc = std::min(64, std::max(1, (nvar + kLmRedThreads - 1) / kLmRedThreads));
-    VIO_CUDA(ctx, ba->d_lm_part.reserve((size_t)(2 * nbo + nbc + 8) * 8));
+    const int nbl = std::min(148, std::max(1, (nvar + kLmRedThreads - 1) / kLmRedThreads));   // CTAs of k_lm_linearized
+    VIO_CUDA(ctx, ba->d_lm_part.reserve((size_t)(2 * nbo + nbc + 2 * nbl + 8) * 8));
     VIO_CUDA(ctx, ba->h_lm.reserve(sizeof(LmState)));
     VIO_CUDA(ctx, ba->d_x.reserve(6 * (size_t)std::max(ba->n_free, 1) * 8 + 16));
     double* part_step = ba->d_lm_part.as<double>(); double* part_model = part_step + nbc; double* part_cost = part_model + nbo;
+    double* part_lin = part_cost + nbo;
     LmState* d_state = ba->d_lm_state.as<LmState>();
     LmState* h_state = ba->h_lm.as<LmState>();
     LmOptionsDev od;
@@ -1817,10 +1819,12 @@ extern "C" int vio360_ba_lm_solve(vio360_ba* ba, const vio360_lm_options* opt, d
             if (rc) return rc;
             const double* Hpp = ba->d_blocks.as<double>(); const double* bp = Hpp + Ks * 36; const double* Hll = bp + Ks * 6; const double* bl = Hll + Ms * 9;
             { KernelTimer kt_(ctx, "k_lm_linearized");
-            k_lm_linearized<<<1, kLmRedThreads, 0, st>>>(K, M, Hpp, bp, Hll, bl, ba->d_free_map.as<int>(), ba->d_point_fixed.as<unsigned char>(),
-                                                       ba->d_pose_delta.as<double>(), ba->d_points.as<double>(), ba->d_colsq.as<double>(),
-                                                       ba->d_scale.as<double>(), first ? 1 : 0, od.jacobi_scaling, d_state);
+            k_lm_linearized<<<nbl, kLmRedThreads, 0, st>>>(K, M, Hpp, bp, Hll, bl, ba->d_free_map.as<int>(), ba->d_point_fixed.as<unsigned char>(),
+                                                         ba->d_pose_delta.as<double>(), ba->d_points.as<double>(), ba->d_colsq.as<double>(),
+                                                         ba->d_scale.as<double>(), first ? 1 : 0, od.jacobi_scaling, part_lin);
             }
+            VIO_LAUNCH_CHECK(ctx);
+            k_lm_linearized_finish<<<1, kLmRedThreads, 0, st>>>(part_lin, nbl, d_state);
             VIO_LAUNCH_CHECK(ctx);
             if ((rc = read_state())) return rc;
             last = *h_state;

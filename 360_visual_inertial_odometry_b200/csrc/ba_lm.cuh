@@ -59,16 +59,17 @@ __device__ __forceinline__ double lm_block_max(double v) {
 
 // After k_blocks_*: squared column norms of J (diagonals of Hpp / Hll, zero for constant blocks), the max norm of
 // the gradient J'r over the free parameters, |x| over the free parameters; on the first linearisation also the
-// Jacobi scaling 1 / (1 + sqrt(|column|^2)).   One CTA (the vectors are 6K + 3M long).
+// Jacobi scaling 1 / (1 + sqrt(|column|^2)).   The vectors are 6K + 3M long (151 200 entries for the 200-keyframe
+// window): a grid of CTAs leaves per-CTA partials (max, sum), k_lm_linearized_finish combines them in index order.
 __global__ void __launch_bounds__(kLmRedThreads) k_lm_linearized(int K, int M, const double* __restrict__ Hpp, const double* __restrict__ bp,
                                                                  const double* __restrict__ Hll, const double* __restrict__ bl,
                                                                  const int* __restrict__ free_map, const unsigned char* __restrict__ point_fixed,
                                                                  const double* __restrict__ pose_delta, const double* __restrict__ points,
                                                                  double* __restrict__ colsq, double* __restrict__ scale, int first, int jacobi_scaling,
-                                                                 LmState* __restrict__ st) {
+                                                                 double* __restrict__ partials) {
     const int np = 6 * K, n = np + 3 * M;
     double gmax = 0.0, x2 = 0.0;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         double c, g, x;
         bool is_free;
         if (i < np) {
@@ -84,6 +85,13 @@ __global__ void __launch_bounds__(kLmRedThreads) k_lm_linearized(int K, int M, c
         if (first) scale[i] = jacobi_scaling ? 1.0 / (1.0 + sqrt(is_free ? c : 0.0)) : 1.0;
         if (is_free) { gmax = fmax(gmax, fabs(g)); x2 += x * x; }
     }
+    const double gm = lm_block_max(gmax);
+    const double xs = lm_block_sum(x2);
+    if (threadIdx.x == 0) { partials[blockIdx.x] = gm; partials[gridDim.x + blockIdx.x] = xs; }
+}
+__global__ void __launch_bounds__(kLmRedThreads) k_lm_linearized_finish(const double* __restrict__ partials, int nparts, LmState* __restrict__ st) {
+    double gmax = 0.0, x2 = 0.0;
+    for (int i = threadIdx.x; i < nparts; i += blockDim.x) { gmax = fmax(gmax, partials[i]); x2 += partials[nparts + i]; }
     const double gm = lm_block_max(gmax);
     const double xs = lm_block_sum(x2);
     if (threadIdx.x == 0) { st->gradient_max_norm = gm; st->x_norm = sqrt(xs); }
