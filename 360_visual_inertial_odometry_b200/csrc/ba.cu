@@ -1656,8 +1656,10 @@ static int solve_reduced_dev(vio360_ba* ba, bool want_points) {
         const size_t band_smem = ((size_t)kCholWb * kCholWb * 36 + ((kCholWb - 1) * 6 + 1) * 6 + n) * sizeof(double);
         if (ba->max_reach < kCholWb && band_smem <= (size_t)220 * 1024) {
             // banded window: trailing matrix in shared memory, S itself is only read
-            VIO_CUDA(ctx, ba->d_chol.reserve(((size_t)nb * (kCholWb - 1) * 36 + (size_t)nb * 42) * 8));
+            VIO_CUDA(ctx, ba->d_chol.reserve(((size_t)nb * (kCholWb - 1) * 36 + (size_t)nb * 42 + (size_t)nb * 36) * 8));
             double* Lcol = ba->d_chol.as<double>();
+            double* Ldiag = Lcol + (size_t)nb * (kCholWb - 1) * 36;
+            double* Linv = Ldiag + (size_t)nb * 42;
             // Windows of up to 24 free poses (the reference's local BA: 10 keyframes) fit the shared-memory window whole
             // and finish in a few columns: 25 us against 34 us for the register-window kernel, whose set-up they do not
             // amortise.  Larger systems: registers (0.45 ms against 0.81 ms at 199 free poses).  VIO360_CHOL_SMEM=1: A/B switch.
@@ -1669,11 +1671,14 @@ static int solve_reduced_dev(vio360_ba* ba, bool want_points) {
                                                                ba->d_x.as<double>(), d_status);
             else
                 k_chol_band_reg<<<1, kChol2Threads, (size_t)(2 * 6 * kCholWb * 6 + kChol2Threads * 36 + n) * sizeof(double), st>>>(
-                    dS, nb, Lcol, Lcol + (size_t)nb * (kCholWb - 1) * 36, ba->d_x.as<double>(), d_status);
+                    dS, nb, Lcol, Ldiag, Linv, ba->d_x.as<double>(), d_status);
             }
             VIO_LAUNCH_CHECK(ctx);
             KernelTimer kt_(ctx, "k_chol_band_back");
-            k_chol_band_back<<<1, 32, n * sizeof(double), st>>>(nb, ba->d_reachF.as<int>(), Lcol, Lcol + (size_t)nb * (kCholWb - 1) * 36, ba->d_x.as<double>());
+            if (smem_window)
+                k_chol_band_back<<<1, 32, n * sizeof(double), st>>>(nb, ba->d_reachF.as<int>(), Lcol, Ldiag, ba->d_x.as<double>());
+            else
+                k_chol_band_back_col<<<1, kCholBackThreads, 2 * n * sizeof(double), st>>>(nb, Lcol, Linv, ba->d_x.as<double>());
         } else {
             VIO_CUDA(ctx, ba->d_chol.reserve(n * n * 8));
             VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_chol.p, dS, n * n * 8, cudaMemcpyDeviceToDevice, st));

@@ -329,8 +329,8 @@ __device__ __forceinline__ void chol2_store(const double (&blk)[36], double* dst
 }
 // dg = lower triangle (packed, dg[i * (i + 1) / 2 + k]) of the updated diagonal block (j, j): right-looking in-place
 // Cholesky (the dependent chain per step is rsqrt, one product, one update); L_jj and the reciprocal pivots go to
-// Ldiag, L_jj^-1 to shared memory for the panel; false if not positive definite
-__device__ __forceinline__ bool chol2_factor(double (&dg)[21], double* sLi, double* __restrict__ Ldiag_j) {
+// Ldiag, L_jj^-1 to shared memory for the panel and to Linv for the backward substitution; false if not positive definite
+__device__ __forceinline__ bool chol2_factor(double (&dg)[21], double* sLi, double* __restrict__ Ldiag_j, double* __restrict__ Linv_j) {
     bool ok = true;
     double inv[6];
 #pragma unroll
@@ -372,12 +372,12 @@ __device__ __forceinline__ bool chol2_factor(double (&dg)[21], double* sLi, doub
 #pragma unroll
     for (int i = 0; i < 6; ++i)
 #pragma unroll
-        for (int k = 0; k < 6; ++k) sLi[i * 6 + k] = k <= i ? li[i * (i + 1) / 2 + k] : 0.0;
+        for (int k = 0; k < 6; ++k) { const double v = k <= i ? li[i * (i + 1) / 2 + k] : 0.0; sLi[i * 6 + k] = v; Linv_j[i * 6 + k] = v; }
     return ok;
 }
 
 __global__ void __maxnreg__(168) k_chol_band_reg(const double* __restrict__ S, int nb, double* __restrict__ Lcol,
-                                                  double* __restrict__ Ldiag, double* __restrict__ b, int* __restrict__ status) {
+                                                  double* __restrict__ Ldiag, double* __restrict__ Linv, double* __restrict__ b, int* __restrict__ status) {
     extern __shared__ double sm2[];
     double* panelT = sm2;                               // [6][Wb][6]: panelT[m][res][r] = P_res[r][m]
     double* Acol = panelT + 6 * kCholWb * 6;            // [Wb][36]: blocks (i, j + 1), i by residue, for the next panel phase
@@ -423,7 +423,7 @@ __global__ void __maxnreg__(168) k_chol_band_reg(const double* __restrict__ S, i
 #pragma unroll
             for (int k = 0; k <= i; ++k) dg[i * (i + 1) / 2 + k] = mine[i * 6 + k];
         chol2_prefetch(S, n, nb, a + kCholWb, a + kCholWb, mine);
-        if (a == 0 && !chol2_factor(dg, sLi, Ldiag)) sbad = 1;
+        if (a == 0 && !chol2_factor(dg, sLi, Ldiag, Linv)) sbad = 1;
     } else if (bulk) {
         chol2_prefetch(S, n, nb, a, bb, mine);
         chol2_take(blk, mine);
@@ -477,7 +477,7 @@ __global__ void __maxnreg__(168) k_chol_band_reg(const double* __restrict__ S, i
                         for (int c = 0; c <= r; ++c) dg[r * (r + 1) / 2 + c] -= rv[r] * rv[c];
                 }
                 if (dd == 1 && j + 1 < nb) {   // the next pivot: the serial part, overlapped with the other warps' updates
-                                if (!chol2_factor(dg, sLi, Ldiag + (size_t)(j + 1) * 42)) sbad = 1;
+                                if (!chol2_factor(dg, sLi, Ldiag + (size_t)(j + 1) * 42, Linv + (size_t)(j + 1) * 36)) sbad = 1;
                             }
             } else {   // (j, j) is finished: (j + 24, j + 24) enters, (j + 48, j + 48) is prefetched
                 asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -530,6 +530,76 @@ __global__ void __maxnreg__(168) k_chol_band_reg(const double* __restrict__ S, i
     }
     for (int e = tid; e < n; e += kChol2Threads) b[e] = sb[e];
     if (tid == 0) status[0] = sbad;
+}
+
+// Column-oriented backward substitution L^T x = y for the factor of k_chol_band_reg (which writes all 23 block rows of a
+// column, zeros beyond its reach, and the inverses of the diagonal factors).  k_chol_band_back reduces 138 rows per
+// column on one warp (0.7 us per column).  Here the sums are kept per block and updated in parallel the moment an x_j is
+// known: thread (q, c) adds (L(j, k)' x_j)[c] to the pending sum of block k = j - 1 - q, a 6-term dot product; the sum
+// of block j - 1 is then complete, and the six lanes that hold it go straight on to x_{j-1} = L^-T (y - sum) with the
+// stored inverse.  One barrier per column; the next column's 6 + 6 factor entries are in flight meanwhile
+// (two columns ahead measured the same: the chain, not the loads, sets the 0.44 us per column).
+constexpr int kCholBackThreads = 160;   // 23 x 6 = 138 workers
+__global__ void __launch_bounds__(kCholBackThreads) k_chol_band_back_col(int nb, const double* __restrict__ Lcol, const double* __restrict__ Linv,
+                                                                         double* __restrict__ b) {
+    extern __shared__ double sbk[];
+    double* sx = sbk;            // [n]: y in, x out
+    double* sacc = sbk + 6 * nb; // [n]: pending sums
+    const int tid = threadIdx.x, n = 6 * nb;
+    const int q = tid / 6, c = tid - 6 * q;
+    const bool worker = q < kCholWb - 1;
+    for (int e = tid; e < n; e += kCholBackThreads) { sx[e] = b[e]; sacc[e] = 0.0; }
+    // column c of the block L(j, j - 1 - q) = Lcol[(j - 1 - q) * 23 + q][a][c], a = 0 .. 5
+    auto fetch_l = [&](int j, double* dst) {
+        const int k = j - 1 - q;
+#pragma unroll
+        for (int a = 0; a < 6; ++a) dst[a] = (worker && k >= 0) ? Lcol[((size_t)k * (kCholWb - 1) + q) * 36 + a * 6 + c] : 0.0;
+    };
+    // column t = tid of L_jj^-1 (rows k >= t), for the six solving lanes
+    auto fetch_inv = [&](int j, double* dst) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) dst[k] = (tid < 6 && j >= 0) ? Linv[(size_t)j * 36 + k * 6 + tid] : 0.0;
+    };
+    double lcur[6], lnxt[6], icur[6], inxt[6];
+    fetch_l(nb - 1, lcur);
+    fetch_inv(nb - 1, icur);
+    __syncthreads();
+    if (tid < 6) {   // x_{nb-1} = L^-T y
+        double xv = 0.0;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) xv += icur[k] * sx[6 * (nb - 1) + k];
+        __syncwarp(0x3f);
+        sx[6 * (nb - 1) + tid] = xv;
+    }
+    fetch_inv(nb - 2, icur);
+    __syncthreads();
+    for (int j = nb - 1; j > 0; --j) {
+        fetch_l(j - 1, lnxt);
+        fetch_inv(j - 2, inxt);
+        // pending sums of the blocks j - 23 .. j - 1 take x_j in
+        const int k = j - 1 - q;
+        double s0 = 0.0;
+        if (worker && k >= 0) {
+            const double* xj = sx + 6 * j;
+            double s1 = 0.0;
+            s0 = lcur[0] * xj[0]; s1 = lcur[1] * xj[1];
+            s0 += lcur[2] * xj[2]; s1 += lcur[3] * xj[3];
+            s0 += lcur[4] * xj[4]; s1 += lcur[5] * xj[5];
+            s0 = sacc[6 * k + c] + (s0 + s1);
+            if (q > 0) sacc[6 * k + c] = s0;
+        }
+        if (tid < 6) {   // q == 0: block j - 1 is complete; x_{j-1} = L^-T (y - sum), the six components across six lanes
+            const double sv = sx[6 * (j - 1) + tid] - s0;
+            double xv = 0.0;
+#pragma unroll
+            for (int kk = 0; kk < 6; ++kk) xv += icur[kk] * __shfl_sync(0x3fu, sv, kk);
+            sx[6 * (j - 1) + tid] = xv;
+        }
+#pragma unroll
+        for (int a = 0; a < 6; ++a) { lcur[a] = lnxt[a]; icur[a] = inxt[a]; }
+        __syncthreads();
+    }
+    for (int e = tid; e < n; e += kCholBackThreads) b[e] = sx[e];
 }
 
 // Backward substitution L^T x = y for the banded factor: one warp, the next column's data is
