@@ -49,6 +49,7 @@ struct vio360_fe_state {
     // tracking pools
     DevBuf d_jobs, d_pyrjobs, d_pts_in, d_pts_out, d_status, d_err, d_keep;
     DevBuf d_lk_queue;           // k_lk_track's work counter {next item, finished warps}; zero between launches
+    cudaEvent_t det_ev[2] = {nullptr, nullptr};   // fork / join of the detector's second stream
     PinBuf h_pts_in, h_out;
     // ring of pinned descriptor staging so that device-space calls never wait for the stream
     struct Stage { PinBuf jobs, pyrjobs; cudaEvent_t ev = nullptr; bool used = false; };
@@ -91,6 +92,7 @@ void vio360_fe_release(vio360_ctx* ctx) {
     for (auto& d : s->d_jobs_ring) d.release();
     for (auto& d : s->d_pyrjobs_ring) d.release();
     for (cudaEvent_t e : s->grp_ev) cudaEventDestroy(e);
+    for (cudaEvent_t e : s->det_ev) if (e) cudaEventDestroy(e);
     if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
     if (s->pyr_stream) cudaStreamDestroy(s->pyr_stream);
     delete s;
@@ -149,6 +151,7 @@ extern "C" int vio360_fe_configure(vio360_ctx* ctx, int width, int height, int m
     VIO_CUDA(ctx, s->d_status.reserve(np)); VIO_CUDA(ctx, s->d_err.reserve(np * 4)); VIO_CUDA(ctx, s->d_keep.reserve(np));
     VIO_CUDA(ctx, s->h_pts_in.reserve(np * 8));
     VIO_CUDA(ctx, s->h_out.reserve(np * (8 + 1 + 4 + 1)));
+    for (cudaEvent_t& e : s->det_ev) VIO_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     VIO_CUDA(ctx, s->d_lk_queue.reserve(256));
     VIO_CUDA(ctx, cudaMemsetAsync(s->d_lk_queue.p, 0, 256, ctx->stream));
     if (const char* e = getenv("VIO360_LK_MB")) s->lk_mb = atoi(e);
@@ -653,20 +656,21 @@ static DiscTable disc_table(int radius) {
     return T;
 }
 
-static void launch_min_eig(vio360_ctx* ctx, const DetectJobDev* dj, const DetectParams& P, int n_jobs, bool any_mask) {
+static void launch_min_eig(vio360_ctx* ctx, const DetectJobDev* dj, const DetectParams& P, int n_jobs, bool any_mask, cudaStream_t on = nullptr) {
     const int nwx = (P.W + kEigWarpCols - 1) / kEigWarpCols;
     const dim3 grid((nwx + kEigWarps - 1) / kEigWarps, n_jobs);
+    const cudaStream_t st = on ? on : ctx->stream;
     KernelTimer kt_(ctx, "k_min_eig");
-    if (any_mask) k_min_eig<true><<<grid, kEigWarps * 32, 0, ctx->stream>>>(dj, P, nwx);
-    else k_min_eig<false><<<grid, kEigWarps * 32, 0, ctx->stream>>>(dj, P, nwx);
+    if (any_mask) k_min_eig<true><<<grid, kEigWarps * 32, 0, st>>>(dj, P, nwx);
+    else k_min_eig<false><<<grid, kEigWarps * 32, 0, st>>>(dj, P, nwx);
 }
 
 // K4 + K5 for a batch whose job table is already on the device: response map, candidates, lazy sort + greedy filter.
-static int launch_detect_pipeline(vio360_ctx* ctx, const DetectJobDev* dj, const DetectParams& P, int n_jobs, bool any_mask, int max_corners,
-                                  double quality, double min_dist, bool smem_grid, size_t grid_bytes) {
+// one group of images: response map, candidates, lazy sort + greedy filter, on stream `st`
+static int launch_detect_group(vio360_ctx* ctx, const DetectJobDev* dj, const DetectParams& P, int n_jobs, bool any_mask, int max_corners,
+                               double quality, double min_dist, bool smem_grid, size_t grid_bytes, float* pool_xy, cudaStream_t st) {
     vio360_fe_state* s = ctx->fe;
-    cudaStream_t st = ctx->stream;
-    launch_min_eig(ctx, dj, P, n_jobs, any_mask);
+    launch_min_eig(ctx, dj, P, n_jobs, any_mask, st);
     VIO_LAUNCH_CHECK(ctx);
     { KernelTimer kt_(ctx, "k_candidates");
     if ((s->W & 3) == 0)
@@ -680,7 +684,6 @@ static int launch_detect_pipeline(vio360_ctx* ctx, const DetectJobDev* dj, const
     int tranche = kSelMaxTranche;
     while (tranche > 1024 && (size_t)tranche * 8 > budget) tranche >>= 1;
     const size_t smem = (smem_grid ? grid_bytes : 0) + (size_t)tranche * 8;
-    float* pool_xy = s->d_corners.as<float>();
     { KernelTimer kt_(ctx, "k_sort_select");
     if (smem_grid) {
         VIO_CUDA(ctx, cudaFuncSetAttribute(k_sort_select<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
@@ -691,6 +694,33 @@ static int launch_detect_pipeline(vio360_ctx* ctx, const DetectJobDev* dj, const
     }
     }
     VIO_LAUNCH_CHECK(ctx);
+    return VIO360_OK;
+}
+
+// K4 + K5 for a batch whose job table is already on the device.  The three kernels want different things -- k_min_eig
+// is bound by instruction issue, k_candidates by HBM, k_sort_select is one latency-bound CTA per image -- so cutting the
+// batch into groups that alternate between two streams (a group's candidates / sort beside the next group's response
+// maps) was tried: 64 frames of 3840x1920 take 3.55 ms in one group, 3.60 in 2, 4.06 in 4, 5.56 in 8 -- the smaller
+// k_min_eig grids lose more than the overlap gains.  VIO360_DET_GROUPS=n keeps the experiment reachable; default 1.
+static int launch_detect_pipeline(vio360_ctx* ctx, const DetectJobDev* dj, const DetectParams& P, int n_jobs, bool any_mask, int max_corners,
+                                  double quality, double min_dist, bool smem_grid, size_t grid_bytes) {
+    vio360_fe_state* s = ctx->fe;
+    cudaStream_t st = ctx->stream;
+    float* pool_xy = s->d_corners.as<float>();
+    static const int want_groups = getenv("VIO360_DET_GROUPS") ? std::max(1, atoi(getenv("VIO360_DET_GROUPS"))) : 1;
+    const int groups = (ctx->timing || n_jobs < 8) ? 1 : std::min(want_groups, n_jobs);
+    if (groups == 1) return launch_detect_group(ctx, dj, P, n_jobs, any_mask, max_corners, quality, min_dist, smem_grid, grid_bytes, pool_xy, st);
+    VIO_CUDA(ctx, cudaEventRecord(s->det_ev[0], st));
+    VIO_CUDA(ctx, cudaStreamWaitEvent(s->pyr_stream, s->det_ev[0], 0));
+    for (int g = 0; g < groups; ++g) {
+        const int j0 = (int)((long long)n_jobs * g / groups), j1 = (int)((long long)n_jobs * (g + 1) / groups);
+        if (j1 <= j0) continue;
+        int rc = launch_detect_group(ctx, dj + j0, P, j1 - j0, any_mask, max_corners, quality, min_dist, smem_grid, grid_bytes,
+                                     pool_xy + 2 * (size_t)P.max_cand * j0, (g & 1) ? s->pyr_stream : st);
+        if (rc) return rc;
+    }
+    VIO_CUDA(ctx, cudaEventRecord(s->det_ev[1], s->pyr_stream));
+    VIO_CUDA(ctx, cudaStreamWaitEvent(st, s->det_ev[1], 0));
     return VIO360_OK;
 }
 
