@@ -34,3 +34,24 @@ def test_reference_arm_line():
 def test_reference_arm_other_ranks_exit_quietly():
     out = _run({"RANK": "1", "LOCAL_RANK": "1", "WORLD_SIZE": "2"})
     assert out.returncode == 0 and out.stdout.strip() == ""
+
+
+def test_ncu_traffic_record_is_tied_to_source_and_workload(tmp_path, monkeypatch):
+    """roofline.traffic comes from the committed ncu capture only while the kernel source (sha1) and the workload are the
+    ones it was taken on (no literal constants); anything else reports None with the reason."""
+    sys.path.insert(0, ROOT)
+    import bench
+    val, src = bench.ncu_traffic("k_lk_track", 64)
+    rec = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["k_lk_track"]
+    assert val == rec["bytes_per_launch"] and val > 2.6e8 and "ncu --set full" in src, src   # the committed capture is current
+    assert bench.ncu_traffic("k_lk_track", 32)[0] is None                                   # another batch size: stale
+    assert bench.ncu_traffic("k_no_such_kernel", 64)[0] is None
+    # a changed kernel source invalidates the record: point ROOT at a copy whose fe_lk.cuh differs by one byte
+    fake = tmp_path / "repo"
+    (fake / "profiles").mkdir(parents=True)
+    (fake / bench.PKG / "csrc").mkdir(parents=True)
+    (fake / "profiles" / "ncu_traffic.json").write_text(json.dumps({"k_lk_track": rec}))
+    (fake / bench.PKG / "csrc" / "fe_lk.cuh").write_bytes(open(os.path.join(ROOT, bench.PKG, "csrc", "fe_lk.cuh"), "rb").read() + b"\n")
+    monkeypatch.setattr(bench, "ROOT", str(fake))
+    val2, why = bench.ncu_traffic("k_lk_track", 64)
+    assert val2 is None and why.startswith("stale")
