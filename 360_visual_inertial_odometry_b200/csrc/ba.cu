@@ -950,14 +950,16 @@ extern "C" int vio360_ba_get_residuals_jacobians(vio360_ba* ba, double* r, doubl
     return VIO360_OK;
 }
 
-static int run_blocks(vio360_ba* ba, int apply_loss) {
+// want_hpl = false: the LM loop only needs the diagonal blocks and the gradient; the O x 18 cross blocks (138 MB of
+// stores for the 1M-observation window) are skipped
+static int run_blocks(vio360_ba* ba, int apply_loss, bool want_hpl = true) {
     // layout of d_blocks: Hpp K*36 | bp K*6 | Hll M*9 | bl M*3 | Hpl O*18
     vio360_ctx* ctx = ba->ctx;
     const size_t K = ba->K, M = ba->M, O = ba->O;
-    const size_t tot = K * 42 + M * 12 + O * 18;
+    const size_t tot = K * 42 + M * 12 + (want_hpl ? O * 18 : 0);
     VIO_CUDA(ctx, ba->d_blocks.reserve(std::max<size_t>(tot, 1) * 8));
     double* Hpp = ba->d_blocks.as<double>(); double* bp = Hpp + K * 36; double* Hll = bp + K * 6;
-    double* bl = Hll + M * 9; double* Hpl = bl + M * 3;
+    double* bl = Hll + M * 9; double* Hpl = want_hpl ? bl + M * 3 : nullptr;
     BaDev d = make_dev(ba);
     { KernelTimer kt_(ctx, "k_blocks_landmark");
     if (ba->eval_f32) k_blocks_landmark<float><<<(int)((M * 32 + 127) / 128), 128, 0, ctx->stream>>>(d, apply_loss != 0, Hll, bl, Hpl);
@@ -1820,7 +1822,7 @@ extern "C" int vio360_ba_lm_solve(vio360_ba* ba, const vio360_lm_options* opt, d
     for (;;) {
         if (relinearize) {
             // Evaluator::Evaluate with Jacobian at x: the Gauss-Newton blocks give the squared column norms and J'r
-            rc = run_blocks(ba, loss ? 1 : 0);
+            rc = run_blocks(ba, loss ? 1 : 0, false);
             if (rc) return rc;
             const double* Hpp = ba->d_blocks.as<double>(); const double* bp = Hpp + Ks * 36; const double* Hll = bp + Ks * 6; const double* bl = Hll + Ms * 9;
             { KernelTimer kt_(ctx, "k_lm_linearized");
