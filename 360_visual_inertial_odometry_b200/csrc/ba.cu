@@ -1673,14 +1673,14 @@ static int solve_reduced_dev(vio360_ba* ba, bool want_points) {
                                                                ba->d_x.as<double>(), d_status);
             else
                 k_chol_band_reg<<<1, kChol2Threads, (size_t)(2 * 6 * kCholWb * 6 + kChol2Threads * 36 + n) * sizeof(double), st>>>(
-                    dS, nb, Lcol, Ldiag, Linv, ba->d_x.as<double>(), d_status);
+                    dS, nb, Lcol, Ldiag, ba->d_x.as<double>(), d_status);
             }
             VIO_LAUNCH_CHECK(ctx);
             KernelTimer kt_(ctx, "k_chol_band_back");
             if (smem_window)
                 k_chol_band_back<<<1, 32, n * sizeof(double), st>>>(nb, ba->d_reachF.as<int>(), Lcol, Ldiag, ba->d_x.as<double>());
             else
-                k_chol_band_back_col<<<1, kCholBackThreads, 2 * n * sizeof(double), st>>>(nb, Lcol, Linv, ba->d_x.as<double>());
+                k_chol_band_back_col<<<1, kCholBackThreads, 2 * n * sizeof(double), st>>>(nb, Lcol, Ldiag, Linv, ba->d_x.as<double>());
         } else {
             VIO_CUDA(ctx, ba->d_chol.reserve(n * n * 8));
             VIO_CUDA(ctx, cudaMemcpyAsync(ba->d_chol.p, dS, n * n * 8, cudaMemcpyDeviceToDevice, st));

@@ -329,8 +329,9 @@ __device__ __forceinline__ void chol2_store(const double (&blk)[36], double* dst
 }
 // dg = lower triangle (packed, dg[i * (i + 1) / 2 + k]) of the updated diagonal block (j, j): right-looking in-place
 // Cholesky (the dependent chain per step is rsqrt, one product, one update); L_jj and the reciprocal pivots go to
-// Ldiag, L_jj^-1 to shared memory for the panel and to Linv for the backward substitution; false if not positive definite
-__device__ __forceinline__ bool chol2_factor(double (&dg)[21], double* sLi, double* __restrict__ Ldiag_j, double* __restrict__ Linv_j) {
+// shared memory for the panel and to Ldiag; false if not positive definite.  (The inverse of L_jj, which would turn the
+// panel rows into independent dot products, costs this chain more than it saves the panel: measured, removed.)
+__device__ __forceinline__ bool chol2_factor(double (&dg)[21], double* sL, double* sInv, double* __restrict__ Ldiag_j) {
     bool ok = true;
     double inv[6];
 #pragma unroll
@@ -352,38 +353,20 @@ __device__ __forceinline__ bool chol2_factor(double (&dg)[21], double* sLi, doub
 #pragma unroll
     for (int i = 0; i < 6; ++i)
 #pragma unroll
-        for (int k = 0; k < 6; ++k) Ldiag_j[i * 6 + k] = k <= i ? dg[i * (i + 1) / 2 + k] : 0.0;
+        for (int k = 0; k < 6; ++k) { const double v = k <= i ? dg[i * (i + 1) / 2 + k] : 0.0; sL[i * 6 + k] = v; Ldiag_j[i * 6 + k] = v; }
 #pragma unroll
-    for (int e = 0; e < 6; ++e) Ldiag_j[36 + e] = inv[e];
-    // Li = L^-1 (lower triangular), column by column; the panel rows are then independent dot products
-    // P[r][c] = sum_{k <= c} A[r][k] Li[c][k] instead of a 21-deep substitution chain
-    double li[21];
-#pragma unroll
-    for (int c = 0; c < 6; ++c)
-#pragma unroll
-        for (int i = 0; i < 6; ++i)
-            if (i >= c) {
-                double sacc = (i == c) ? 1.0 : 0.0;
-#pragma unroll
-                for (int k = 0; k < 6; ++k)
-                    if (k >= c && k < i) sacc -= dg[i * (i + 1) / 2 + k] * li[k * (k + 1) / 2 + c];
-                li[i * (i + 1) / 2 + c] = sacc * inv[i];
-            }
-#pragma unroll
-    for (int i = 0; i < 6; ++i)
-#pragma unroll
-        for (int k = 0; k < 6; ++k) { const double v = k <= i ? li[i * (i + 1) / 2 + k] : 0.0; sLi[i * 6 + k] = v; Linv_j[i * 6 + k] = v; }
+    for (int e = 0; e < 6; ++e) { sInv[e] = inv[e]; Ldiag_j[36 + e] = inv[e]; }
     return ok;
 }
 
 __global__ void __maxnreg__(168) k_chol_band_reg(const double* __restrict__ S, int nb, double* __restrict__ Lcol,
-                                                  double* __restrict__ Ldiag, double* __restrict__ Linv, double* __restrict__ b, int* __restrict__ status) {
+                                                  double* __restrict__ Ldiag, double* __restrict__ b, int* __restrict__ status) {
     extern __shared__ double sm2[];
     double* panelT = sm2;                               // [6][Wb][6]: panelT[m][res][r] = P_res[r][m]
     double* Acol = panelT + 6 * kCholWb * 6;            // [Wb][36]: blocks (i, j + 1), i by residue, for the next panel phase
     double* pref = Acol + kCholWb * 36;                 // [threads][36]: every owner's NEXT block, prefetched with cp.async
     double* sb = pref + kChol2Threads * 36;             // [n]
-    __shared__ __align__(16) double sLi[36], sY[6];   // L_jj^-1 of the current column, y_j
+    __shared__ __align__(16) double sL[36], sInv[6], sY[6];   // L_jj and its reciprocal pivots, y_j
     __shared__ int sbad;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, n = 6 * nb;
     const bool diag = warp == 0 && lane < kCholWb;
@@ -423,7 +406,7 @@ __global__ void __maxnreg__(168) k_chol_band_reg(const double* __restrict__ S, i
 #pragma unroll
             for (int k = 0; k <= i; ++k) dg[i * (i + 1) / 2 + k] = mine[i * 6 + k];
         chol2_prefetch(S, n, nb, a + kCholWb, a + kCholWb, mine);
-        if (a == 0 && !chol2_factor(dg, sLi, Ldiag, Linv)) sbad = 1;
+        if (a == 0 && !chol2_factor(dg, sL, sInv, Ldiag)) sbad = 1;
     } else if (bulk) {
         chol2_prefetch(S, n, nb, a, bb, mine);
         chol2_take(blk, mine);
@@ -433,21 +416,19 @@ __global__ void __maxnreg__(168) k_chol_band_reg(const double* __restrict__ S, i
     __syncthreads();
     for (int j = 0; j < nb; ++j) {
         const int jm = j % kCholWb;
-        // ---- panel: one row of the column's blocks per thread, X = A L_jj^-T; row 138 finishes rhs block j
+        // ---- panel: one row of the column's blocks per thread, X L_jj' = A by substitution; row 138 finishes rhs block j
         if (prow >= 0 && prow <= (kCholWb - 1) * 6) {
             const bool rhs = prow == (kCholWb - 1) * 6;
             const int bi = prow / 6, ar = prow - bi * 6;
             const int res = (jm + 1 + bi) % kCholWb;
             const double* src = rhs ? sb + 6 * j : Acol + res * 36 + ar * 6;
-            double v[6], o[6];
+            double o[6];
 #pragma unroll
-            for (int c = 0; c < 6; ++c) v[c] = src[c];
+            for (int c = 0; c < 6; ++c) {   // o L_jj' = v by substitution
+                double v = src[c];
 #pragma unroll
-            for (int c = 0; c < 6; ++c) {   // o = v L^-T: six independent dot products
-                double acc = v[c] * sLi[c * 6 + c];
-#pragma unroll
-                for (int k = 0; k < c; ++k) acc += v[k] * sLi[c * 6 + k];
-                o[c] = acc;
+                for (int k = 0; k < c; ++k) v -= o[k] * sL[c * 6 + k];
+                o[c] = v * sInv[c];
             }
             if (rhs) {
 #pragma unroll
@@ -477,7 +458,7 @@ __global__ void __maxnreg__(168) k_chol_band_reg(const double* __restrict__ S, i
                         for (int c = 0; c <= r; ++c) dg[r * (r + 1) / 2 + c] -= rv[r] * rv[c];
                 }
                 if (dd == 1 && j + 1 < nb) {   // the next pivot: the serial part, overlapped with the other warps' updates
-                                if (!chol2_factor(dg, sLi, Ldiag + (size_t)(j + 1) * 42, Linv + (size_t)(j + 1) * 36)) sbad = 1;
+                                if (!chol2_factor(dg, sL, sInv, Ldiag + (size_t)(j + 1) * 42)) sbad = 1;
                             }
             } else {   // (j, j) is finished: (j + 24, j + 24) enters, (j + 48, j + 48) is prefetched
                 asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -533,15 +514,15 @@ __global__ void __maxnreg__(168) k_chol_band_reg(const double* __restrict__ S, i
 }
 
 // Column-oriented backward substitution L^T x = y for the factor of k_chol_band_reg (which writes all 23 block rows of a
-// column, zeros beyond its reach, and the inverses of the diagonal factors).  k_chol_band_back reduces 138 rows per
+// column, zeros beyond its reach).  k_chol_band_back reduces 138 rows per
 // column on one warp (0.7 us per column).  Here the sums are kept per block and updated in parallel the moment an x_j is
 // known: thread (q, c) adds (L(j, k)' x_j)[c] to the pending sum of block k = j - 1 - q, a 6-term dot product; the sum
 // of block j - 1 is then complete, and the six lanes that hold it go straight on to x_{j-1} = L^-T (y - sum) with the
 // stored inverse.  One barrier per column; the next column's 6 + 6 factor entries are in flight meanwhile
 // (two columns ahead measured the same: the chain, not the loads, sets the 0.44 us per column).
 constexpr int kCholBackThreads = 160;   // 23 x 6 = 138 workers
-__global__ void __launch_bounds__(kCholBackThreads) k_chol_band_back_col(int nb, const double* __restrict__ Lcol, const double* __restrict__ Linv,
-                                                                         double* __restrict__ b) {
+__global__ void __launch_bounds__(kCholBackThreads) k_chol_band_back_col(int nb, const double* __restrict__ Lcol, const double* __restrict__ Ldiag,
+                                                                         double* __restrict__ Linv, double* __restrict__ b) {
     extern __shared__ double sbk[];
     double* sx = sbk;            // [n]: y in, x out
     double* sacc = sbk + 6 * nb; // [n]: pending sums
@@ -549,6 +530,27 @@ __global__ void __launch_bounds__(kCholBackThreads) k_chol_band_back_col(int nb,
     const int q = tid / 6, c = tid - 6 * q;
     const bool worker = q < kCholWb - 1;
     for (int e = tid; e < n; e += kCholBackThreads) { sx[e] = b[e]; sacc[e] = 0.0; }
+    // the inverses of all diagonal factors, in parallel (one thread per block column): off the factorisation's chain
+    for (int j = tid; j < nb; j += kCholBackThreads) {
+        const double* L = Ldiag + (size_t)j * 42;
+        double li[36];
+#pragma unroll
+        for (int e = 0; e < 36; ++e) li[e] = 0.0;
+#pragma unroll
+        for (int cc = 0; cc < 6; ++cc)
+#pragma unroll
+            for (int i = 0; i < 6; ++i)
+                if (i >= cc) {
+                    double sacc2 = (i == cc) ? 1.0 : 0.0;
+#pragma unroll
+                    for (int k = 0; k < 6; ++k)
+                        if (k >= cc && k < i) sacc2 -= L[i * 6 + k] * li[k * 6 + cc];
+                    li[i * 6 + cc] = sacc2 * L[36 + i];
+                }
+#pragma unroll
+        for (int e = 0; e < 36; ++e) Linv[(size_t)j * 36 + e] = li[e];
+    }
+    __syncthreads();   // Linv is read back through global memory by other threads of this CTA
     // column c of the block L(j, j - 1 - q) = Lcol[(j - 1 - q) * 23 + q][a][c], a = 0 .. 5
     auto fetch_l = [&](int j, double* dst) {
         const int k = j - 1 - q;
