@@ -13,10 +13,10 @@
 #include <algorithm>
 #include <numeric>
 
+#include "common.cuh"
 #include "ba_math.cuh"
 #include "ba_peer.cuh"
 #include "ba_schur.cuh"
-#include "common.cuh"
 
 using namespace vio360;
 
@@ -1187,14 +1187,17 @@ extern "C" int vio360_ba_build_reduced_system(vio360_ba* ba, const double* lm_di
                 int max_cov = 0;
                 for (int p = 0; p < ba->K; ++p) max_cov = std::max(max_cov, ba->cov_ptr[p + 1] - ba->cov_ptr[p]);
                 static const int force_lanes = getenv("VIO360_BA_RED_LANES") ? atoi(getenv("VIO360_BA_RED_LANES")) : 0;
+                static const bool no_pdl = getenv("VIO360_BA_NO_PDL") != nullptr;   // A/B switch
+                const bool use_pdl = !no_pdl && !ctx->timing && nch > 0;           // event pairs between the kernels would serialise them anyway
                 int lanes = (size_t)nblk.x * nblk.y >= 2000 ? 7 : 14;
                 if ((size_t)nblk.x * nblk.y >= 2000 && max_cov <= 20) lanes = 5;
                 if (force_lanes) lanes = force_lanes;
 #define VIO_REDUCE_LAUNCH(L)                                                                                                   \
-                k_schur_reduce<true, L><<<nblk, 36 * L, 0, st>>>(dS, n, drhs, dcost, ba->d_partS.as<double>(), ba->d_partRhs.as<double>(), \
-                                                           ba->d_partials.as<double>(), nch, ba->d_chunks.as<SchurChunk>(),  \
-                                                           ba->d_cov_ptr.as<int>(), ba->d_cov_idx.as<int4>(), ba->d_reach.as<int>(), \
-                                                           ba->d_free_pose.as<int>(), Dp, add_diag, band, band_w, row0, ba->n_free, pub)
+                VIO_CUDA(ctx, vio360_launch_pdl(use_pdl, k_schur_reduce<true, L>, nblk, dim3(36 * L), 0, st, dS, n, drhs, dcost, (const double*)ba->d_partS.as<double>(), \
+                                                (const double*)ba->d_partRhs.as<double>(), (const double*)ba->d_partials.as<double>(), nch,              \
+                                                (const SchurChunk*)ba->d_chunks.as<SchurChunk>(), (const int*)ba->d_cov_ptr.as<int>(),                   \
+                                                (const int4*)ba->d_cov_idx.as<int4>(), (const int*)ba->d_reach.as<int>(), (const int*)ba->d_free_pose.as<int>(), \
+                                                Dp, add_diag, band, band_w, row0, ba->n_free, pub))
                 if (lanes <= 3) VIO_REDUCE_LAUNCH(3);
                 else if (lanes <= 5) VIO_REDUCE_LAUNCH(5);
                 else if (lanes <= 7) VIO_REDUCE_LAUNCH(7);
@@ -1409,8 +1412,9 @@ extern "C" int vio360_ba_peer_exchange(vio360_ba* ba) {
     // 8 x 256-thread CTAs per SM.
     const unsigned grid = (unsigned)std::min<size_t>((total + 255) / 256, std::max<size_t>(1, (size_t)8 * ctx->num_sms / std::max(1, P.same_device)));
     { KernelTimer kt_(ctx, "k_band_pull");
-    k_band_pull<<<grid, 256, 0, st>>>(pv, epoch, ba->n_free, P.band_w, ba->d_free_pose.as<int>(),
-                                          ba->use_D ? ba->d_D.as<double>() : nullptr, dS, d_err, d_trace);
+    static const bool no_pdl = getenv("VIO360_BA_NO_PDL") != nullptr;
+    VIO_CUDA(ctx, vio360_launch_pdl(!no_pdl && !ctx->timing, k_band_pull, dim3(grid), dim3(256), 0, st, pv, epoch, ba->n_free, P.band_w,
+                                    (const int*)ba->d_free_pose.as<int>(), (const double*)(ba->use_D ? ba->d_D.as<double>() : nullptr), dS, d_err, d_trace));
     }
     VIO_LAUNCH_CHECK(ctx);
     ba->dense_stale = false; ba->band_zero_n = -1;

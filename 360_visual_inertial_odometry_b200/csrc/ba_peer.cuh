@@ -145,6 +145,7 @@ __global__ void __launch_bounds__(256)
 k_band_pull(const PeerView pv, const unsigned epoch, const int n_free, const int band_w,
             const int* __restrict__ free_pose, const double* __restrict__ D,
             double* __restrict__ packed, int* __restrict__ err_flag, unsigned long long* __restrict__ trace) {
+    pdl_wait();   // launched with programmatic dependent launch behind this rank's k_schur_reduce: its band is complete from here on
     unsigned long long t_start = 0;
     if (trace && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
     // rows touched by this CTA's elements (grid-stride: the same relative rows every round would need per-round

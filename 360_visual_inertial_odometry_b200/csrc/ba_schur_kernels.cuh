@@ -38,6 +38,7 @@ k_schur_tile(BaDev d, const SchurChunk* __restrict__ chunks, const int* __restri
     double* sLmk = sPose + kSWin * kPoseStride;                 // [kSMaxLm][9]: L^-1 (6), (E'E)^-1 g (3)
     double* sBlk = sLmk + kSMaxLm * 9;                          // [32] block-sum scratch
     float* sPoseF = reinterpret_cast<float*>(reinterpret_cast<int*>(sBlk + 32) + 32);   // [kSWin][kPoseStride] (PT = float only)
+    pdl_launch_dependents();   // the slab reduce may be scheduled as soon as SMs free up; it waits for this grid before reading
     const SchurChunk ch = chunks[blockIdx.x];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int i = tid; i < kSTiles * 64; i += kSThreads) St[i] = 0.0;
@@ -530,6 +531,8 @@ k_schur_reduce(double* __restrict__ S, int n, double* __restrict__ rhs, double* 
     // band_grid: blockIdx.x counts block columns from the diagonal (the host sized the grid to the
     // widest row of the envelope and zeroed S outside it once per structure).  row0: first block row
     // of the grid (a rank of a peer-memory exchange sums only the rows its landmarks touch).
+    pdl_wait();                // launched with programmatic dependent launch behind k_schur_tile: its slabs are complete from here on
+    pdl_launch_dependents();   // (multi-GPU) k_band_pull may be scheduled behind this grid
     const int bi = blockIdx.y + row0, bj = band_grid ? bi + blockIdx.x : blockIdx.x;
     if (bi > bj || bj >= n_free) return;
     __shared__ double part[kRedLanes][36];

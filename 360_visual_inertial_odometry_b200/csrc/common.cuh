@@ -11,6 +11,7 @@
 #include <map>
 #include <string>
 #include <unordered_map>
+#include <utility>
 #include <vector>
 
 #include "../../include/vio360.h"
@@ -115,6 +116,23 @@ struct PinBuf {
 };
 
 void vio360_fe_release(vio360_ctx* ctx);  // fe.cu
+
+// Launch with programmatic dependent launch allowed: the kernel may be scheduled while the previous kernel of the
+// stream is still draining (once all of that kernel's CTAs have executed griddepcontrol.launch_dependents or exited);
+// it must execute griddepcontrol.wait before it touches anything the previous kernel wrote.  Hides the launch gap
+// between the short kernels of one BA step (tile -> reduce -> pull).
+template <typename... KArgs, typename... Args>
+inline cudaError_t vio360_launch_pdl(bool pdl, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl ? 1 : 0;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 // Host-to-device copy of `bytes` contiguous bytes, cut at the boundaries of the registered host ranges so that every
 // piece lies inside one registration (DMA straight from the caller's pages) or in pageable memory (the short fringes).
