@@ -122,71 +122,114 @@ __global__ void __launch_bounds__(kSeqThreads) k_seq_post_lk(const SeqDev* __res
     if (threadIdx.x == 0) { sd.c->n_good = ng; sd.rjob->n = ng; }
 }
 
-// grid filters on a list held in global memory, cell ids in shared memory (same arithmetic as fe_grid.cuh)
-__device__ __forceinline__ void cta_cluster_keep(const float* __restrict__ xy, int n, const SeqParams& P, unsigned short* s_cell,
-                                                 unsigned char* s_clustered, uint8_t* __restrict__ keep) {
+// shared-memory carve-up of the list kernels (cap = list capacity, ncell = grid cells)
+struct SeqSmem {
+    int* idx; int* track; int* cell_start; float* xy;              // 4-byte arrays: cap, cap, ncell + 2, 2 cap
+    unsigned short* cell; unsigned short* member;                  // cap each
+    unsigned char* clustered; uint8_t* keep;                       // ncell, cap
+    __device__ SeqSmem(int* base, int cap, int ncell) {
+        idx = base; track = base + cap; cell_start = base + 2 * cap;
+        xy = reinterpret_cast<float*>(base + 2 * cap + ((ncell + 2 + 1) & ~1));
+        cell = reinterpret_cast<unsigned short*>(xy + 2 * cap);
+        member = cell + ((cap + 1) & ~1);
+        clustered = reinterpret_cast<unsigned char*>(member + ((cap + 1) & ~1));
+        keep = clustered + ((ncell + 3) & ~3);
+    }
+};
+inline size_t seq_smem_bytes(int cap, int ncell) {
+    return (size_t)cap * 16 + (size_t)((ncell + 3) & ~1) * 4 + (size_t)((cap + 1) & ~1) * 4 + (size_t)((ncell + 3) & ~3) + (size_t)cap + 16;
+}
+
+// Member lists of the grid cells: member[cell_start[c] .. cell_start[c + 1]) = the features of cell c in list order.
+// One thread per cell scans the cell ids twice (count, fill): O(n) per thread instead of the O(n) scan per cell AND
+// per statistic (or per feature, for the ranks) that the filters would otherwise need.  sm.cell must be filled.
+__device__ __forceinline__ void cta_build_cells(int n, int ncell, const SeqSmem& sm) {
+    for (int c = threadIdx.x; c < ncell; c += kSeqThreads) {
+        int cnt = 0;
+        for (int i = 0; i < n; ++i) cnt += sm.cell[i] == c;
+        sm.cell_start[c + 1] = cnt;
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) {   // exclusive scan of the counts by one warp: a contiguous chunk per lane
+        const int lane = threadIdx.x, per = (ncell + 31) / 32, c0 = min(lane * per, ncell), c1 = min(c0 + per, ncell);
+        int sum = 0;
+        for (int c = c0; c < c1; ++c) sum += sm.cell_start[c + 1];
+        int incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+        int run = incl - sum;
+        if (lane == 0) sm.cell_start[0] = 0;
+        for (int c = c0; c < c1; ++c) { run += sm.cell_start[c + 1]; sm.cell_start[c + 1] = run; }
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < ncell; c += kSeqThreads) {
+        int pos = sm.cell_start[c];
+        for (int i = 0; i < n; ++i)
+            if (sm.cell[i] == c) sm.member[pos++] = (unsigned short)i;
+    }
+    __syncthreads();
+}
+
+// grid filters on a list held in global memory (same arithmetic as fe_grid.cuh); positions, cell ids and the cells'
+// member lists in shared memory
+__device__ __forceinline__ void cta_cluster_keep(const float* __restrict__ xy, int n, const SeqParams& P, const SeqSmem& sm, uint8_t* __restrict__ keep) {
     const int ncell = P.grid_cols * P.grid_rows;
     const float cw = (float)P.W / P.grid_cols, chh = (float)P.H / P.grid_rows;
     const float diag = sqrtf(cw * cw + chh * chh);
     const float thr = diag * P.std_ratio;
-    for (int i = threadIdx.x; i < n; i += kSeqThreads) s_cell[i] = (unsigned short)grid_cell_of(xy[2 * i], xy[2 * i + 1], cw, chh, P.grid_cols, P.grid_rows);
+    for (int i = threadIdx.x; i < n; i += kSeqThreads) {
+        const float x = xy[2 * i], y = xy[2 * i + 1];
+        sm.xy[2 * i] = x; sm.xy[2 * i + 1] = y;
+        sm.cell[i] = (unsigned short)grid_cell_of(x, y, cw, chh, P.grid_cols, P.grid_rows);
+    }
     __syncthreads();
+    cta_build_cells(n, ncell, sm);
     for (int c = threadIdx.x; c < ncell; c += kSeqThreads) {
-        int cnt = 0;
-        float mx = 0.f, my = 0.f;
-        for (int i = 0; i < n; ++i)
-            if (s_cell[i] == c) { mx += xy[2 * i]; my += xy[2 * i + 1]; ++cnt; }
+        const int k0 = sm.cell_start[c], k1 = sm.cell_start[c + 1], cnt = k1 - k0;
         bool clustered = false;
-        if (n >= 4 && cnt >= 4) {
+        if (n >= 4 && cnt >= 4) {   // sums in list order, as the reference's loops over the frame's features
+            float mx = 0.f, my = 0.f;
+            for (int k = k0; k < k1; ++k) { const int i = sm.member[k]; mx += sm.xy[2 * i]; my += sm.xy[2 * i + 1]; }
             mx /= (float)cnt; my /= (float)cnt;
             float var = 0.f;
-            for (int i = 0; i < n; ++i)
-                if (s_cell[i] == c) { const float dx = xy[2 * i] - mx, dy = xy[2 * i + 1] - my; var += (dx * dx + dy * dy); }
+            for (int k = k0; k < k1; ++k) { const int i = sm.member[k]; const float dx = sm.xy[2 * i] - mx, dy = sm.xy[2 * i + 1] - my; var += (dx * dx + dy * dy); }
             var /= (float)cnt;
             clustered = sqrtf(var) < thr;
         }
-        s_clustered[c] = clustered;
+        sm.clustered[c] = clustered;
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < n; i += kSeqThreads) keep[i] = !s_clustered[s_cell[i]];
+    for (int i = threadIdx.x; i < n; i += kSeqThreads) keep[i] = !sm.clustered[sm.cell[i]];
     __syncthreads();
 }
 
 __device__ __forceinline__ void cta_grid_cap_keep(const float* __restrict__ xy, const int* __restrict__ tc, int n, const SeqParams& P,
-                                                  unsigned short* s_cell, int* s_track, uint8_t* __restrict__ keep) {
+                                                  const SeqSmem& sm, uint8_t* __restrict__ keep) {
     const float cw = (float)P.W / P.grid_cols, chh = (float)P.H / P.grid_rows;
     for (int i = threadIdx.x; i < n; i += kSeqThreads) {
         const float x = xy[2 * i], y = xy[2 * i + 1];
         const bool inside = !(x < 0 || x >= P.W || y < 0 || y >= P.H);
-        s_cell[i] = inside ? (unsigned short)grid_cell_of(x, y, cw, chh, P.grid_cols, P.grid_rows) : (unsigned short)0xffff;
-        s_track[i] = tc[i];
+        sm.cell[i] = inside ? (unsigned short)grid_cell_of(x, y, cw, chh, P.grid_cols, P.grid_rows) : (unsigned short)0xffff;
+        sm.track[i] = tc[i];
     }
     __syncthreads();
+    cta_build_cells(n, P.grid_cols * P.grid_rows, sm);
     for (int i = threadIdx.x; i < n; i += kSeqThreads) {
-        const unsigned short c = s_cell[i];
+        const unsigned short c = sm.cell[i];
         bool k = false;
-        if (c != 0xffff) {
-            const int t = s_track[i];
+        if (c != 0xffff) {   // rank among the cell's members by (track count desc, list index asc)
+            const int t = sm.track[i];
             int rank = 0;
-            for (int j = 0; j < n; ++j) rank += (s_cell[j] == c) && (s_track[j] > t || (s_track[j] == t && j < i));
+            for (int q = sm.cell_start[c]; q < sm.cell_start[c + 1]; ++q) {
+                const int j = sm.member[q];
+                rank += (sm.track[j] > t) || (sm.track[j] == t && j < i);
+            }
             k = rank < P.max_per_cell;
         }
         keep[i] = k;
     }
     __syncthreads();
 }
-
-// shared-memory carve-up of the list kernels: [s_idx cap ints | s_track cap ints | s_cell cap shorts | flags cells bytes | keep cap bytes]
-struct SeqSmem {
-    int* idx; int* track; unsigned short* cell; unsigned char* clustered; uint8_t* keep;
-    __device__ SeqSmem(int* base, int cap, int ncell) {
-        idx = base; track = base + cap;
-        cell = reinterpret_cast<unsigned short*>(base + 2 * cap);
-        clustered = reinterpret_cast<unsigned char*>(cell + ((cap + 1) & ~1));
-        keep = clustered + ((ncell + 3) & ~3);
-    }
-};
-inline size_t seq_smem_bytes(int cap, int ncell) { return (size_t)cap * 8 + (size_t)((cap + 1) & ~1) * 2 + (size_t)((ncell + 3) & ~3) + (size_t)cap + 16; }
 
 __device__ __forceinline__ void cta_gather(const SeqDev& sd, int from, int to, const int* s_idx, int m) {
     for (int k = threadIdx.x; k < m; k += kSeqThreads) {
@@ -215,12 +258,12 @@ __global__ void __launch_bounds__(kSeqThreads) k_seq_post_ransac(const SeqDev* _
     const int n_tracked = m;
     int cur = 1;
     if (P.remove_clustered && m >= 4) {                            // :168, :411
-        cta_cluster_keep(sd.xy[cur], m, P, sm.cell, sm.clustered, sm.keep);
+        cta_cluster_keep(sd.xy[cur], m, P, sm, sm.keep);
         const int m2 = cta_compact(sm.keep, m, sm.idx, s_scan);
         cta_gather(sd, cur, cur ^ 1, sm.idx, m2);
         cur ^= 1; m = m2;
     }
-    cta_grid_cap_keep(sd.xy[cur], sd.tc[cur], m, P, sm.cell, sm.track, sm.keep);   // :171-172
+    cta_grid_cap_keep(sd.xy[cur], sd.tc[cur], m, P, sm, sm.keep);   // :171-172
     const int m3 = cta_compact(sm.keep, m, sm.idx, s_scan);
     cta_gather(sd, cur, cur ^ 1, sm.idx, m3);
     cur ^= 1; m = m3;
@@ -267,7 +310,7 @@ __global__ void __launch_bounds__(kSeqThreads) k_seq_append(const SeqDev* __rest
         }
         __syncthreads();
         m += nd;
-        cta_grid_cap_keep(sd.xy[0], sd.tc[0], m, P, sm.cell, sm.track, sm.keep);
+        cta_grid_cap_keep(sd.xy[0], sd.tc[0], m, P, sm, sm.keep);
         const int m2 = cta_compact(sm.keep, m, sm.idx, s_scan);
         cta_gather(sd, 0, 1, sm.idx, m2);
         m = m2;

@@ -509,6 +509,25 @@ def bench_sequence(ctx, b, syn, torch, device, barrier, args, rank):
             out[name]["h2d_bytes_per_call"] = S * (Ws * Hs + 12000); out[name]["d2h_bytes_per_call"] = S * (16 * cap + 80)
         for h in seqs:
             ctx.seq_destroy(h)
+    # the reference's own situation: ONE sequence, frame after frame from host memory -- the latency of a frame
+    seq1 = ctx.seq_create(**cfg)
+    job1 = (b.FrameJob * 1)()
+
+    def step1(t):
+        j = job1[0]
+        j.seq = seq1; j.pitch = Ws
+        j.image, j.ransac_words = hframes[0][t].data_ptr(), words[t, 0].data_ptr()
+        j.ids, j.xy, j.track_count = ids[0].data_ptr(), xy[0].data_ptr(), tc[0].data_ptr()
+        j.n_features, j.n_tracked, j.n_detected = C.addressof(cnt), C.addressof(cnt) + 4, C.addressof(cnt) + 8
+        ctx.fe_track_frame_batch_raw(job1, 1, b.MEM_HOST)
+    step1(0); step1(1)
+    t0 = time.perf_counter()
+    for t in range(2, T):
+        step1(t)
+    dt1 = time.perf_counter() - t0
+    ctx.seq_destroy(seq1)
+    out["single_sequence"] = {"ms_per_frame": dt1 / (T - 2) * 1e3, "value": (T - 2) / dt1, "unit": "frames/s", "frames_timed": T - 2,
+                              "note": "one sequence, host frames, one call per frame (H2D of the frame and D2H of the feature list inside)"}
     res = {"metric": "TrackFeatures chain frames/s @1920x960 (configs[0] headless): track + filter + RANSAC + cluster + grid cap + re-detect",
            "value": out["host_frames"]["value"], "unit": "frames/s", **out}
     if rank == 0 and not args.skip_cpu:
