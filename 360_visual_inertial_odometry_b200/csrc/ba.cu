@@ -1564,22 +1564,26 @@ extern "C" int vio360_pnp_evaluate(vio360_ctx* ctx, int N, const double* obs_uv,
     // one scratch allocation: inputs | outputs
     const size_t in_d = n * 2 + n * 3 + 16 + 16 + 6;          // doubles
     const size_t out_d = n * 2 + n * 12 + n + (size_t)nb * 28 + 28 + kPoseStride;
-    DevBuf scratch, flags;
-    VIO_CUDA(ctx, scratch.reserve((in_d + out_d) * 8));
-    VIO_CUDA(ctx, flags.reserve(n * 2));
-    double* d_obs = scratch.as<double>(); double* d_pts = d_obs + n * 2; double* d_Twb = d_pts + n * 3;
+    void* scratch_p = nullptr;
+    VIO_CUDA(ctx, vio360_scratch(ctx, (in_d + out_d) * 8 + n * 2, &scratch_p));   // the context's scratch: no allocation per call
+    double* d_obs = static_cast<double*>(scratch_p); double* d_pts = d_obs + n * 2; double* d_Twb = d_pts + n * 3;
     double* d_Tcb = d_Twb + 16; double* d_xi = d_Tcb + 16;
     double* d_r = d_xi + 6; double* d_J = d_r + n * 2; double* d_chi = d_J + n * 12; double* d_part = d_chi + n;
     double* d_out28 = d_part + (size_t)nb * 28; double* d_pose = d_out28 + 28;
-    unsigned char* d_outl = flags.as<unsigned char>(); unsigned char* d_valid = d_outl + n;
-    auto cleanup = [&]() { scratch.release(); flags.release(); };
+    unsigned char* d_outl = reinterpret_cast<unsigned char*>(d_obs + in_d + out_d); unsigned char* d_valid = d_outl + n;
+    auto cleanup = [&]() {};
 #define PNP_CUDA(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { cleanup(); return vio360_fail(ctx, VIO360_ERR_CUDA, "%s -> %s", #call, cudaGetErrorString(e_)); } } while (0)
-    PNP_CUDA(cudaMemcpyAsync(d_obs, obs_uv, n * 16, cudaMemcpyHostToDevice, st));
-    PNP_CUDA(cudaMemcpyAsync(d_pts, world_pts, n * 24, cudaMemcpyHostToDevice, st));
-    PNP_CUDA(cudaMemcpyAsync(d_Twb, T_wb_init, 128, cudaMemcpyHostToDevice, st));
-    PNP_CUDA(cudaMemcpyAsync(d_Tcb, T_cb, 128, cudaMemcpyHostToDevice, st));
-    PNP_CUDA(cudaMemcpyAsync(d_xi, pose_delta, 48, cudaMemcpyHostToDevice, st));
-    if (outlier) PNP_CUDA(cudaMemcpyAsync(d_outl, outlier, n, cudaMemcpyHostToDevice, st));
+    // inputs and outputs travel through the context's pinned staging buffer: one copy in (plus the outlier flags), one
+    // out (plus the valid flags) instead of eleven pageable copies of a few hundred bytes each
+    const size_t out_copy_d = n * 15 + (size_t)nb * 28 + 28;          // r | J | chi2 | partials | H, b, cost
+    void* pin_p = nullptr;
+    PNP_CUDA(vio360_pinned(ctx, (in_d + out_copy_d) * 8 + 2 * n, &pin_p));
+    double* h_in = static_cast<double*>(pin_p); double* h_out = h_in + in_d;
+    unsigned char* h_flags = reinterpret_cast<unsigned char*>(h_out + out_copy_d);
+    memcpy(h_in, obs_uv, n * 16); memcpy(h_in + n * 2, world_pts, n * 24);
+    memcpy(h_in + n * 5, T_wb_init, 128); memcpy(h_in + n * 5 + 16, T_cb, 128); memcpy(h_in + n * 5 + 32, pose_delta, 48);
+    PNP_CUDA(cudaMemcpyAsync(d_obs, h_in, in_d * 8, cudaMemcpyHostToDevice, st));
+    if (outlier) { memcpy(h_flags, outlier, n); PNP_CUDA(cudaMemcpyAsync(d_outl, h_flags, n, cudaMemcpyHostToDevice, st)); }
     CamConst cam;
     cam_const_init(cam, cols, rows, info, T_cb, huber_delta);
     k_pose_prepare<<<1, 32, 0, st>>>(1, d_Twb, d_Tcb, d_xi, d_pose);
@@ -1589,13 +1593,14 @@ extern "C" int vio360_pnp_evaluate(vio360_ctx* ctx, int N, const double* obs_uv,
     k_pnp_reduce<<<1, 32, 0, st>>>(d_part, nb, d_out28);
     ctx->launches++;
     PNP_CUDA(cudaGetLastError());
-    double h28[28];
-    PNP_CUDA(cudaMemcpyAsync(r, d_r, n * 16, cudaMemcpyDeviceToHost, st));
-    if (Jp) PNP_CUDA(cudaMemcpyAsync(Jp, d_J, n * 96, cudaMemcpyDeviceToHost, st));
-    if (chi2) PNP_CUDA(cudaMemcpyAsync(chi2, d_chi, n * 8, cudaMemcpyDeviceToHost, st));
-    PNP_CUDA(cudaMemcpyAsync(valid, d_valid, n, cudaMemcpyDeviceToHost, st));
-    PNP_CUDA(cudaMemcpyAsync(h28, d_out28, sizeof(h28), cudaMemcpyDeviceToHost, st));
+    PNP_CUDA(cudaMemcpyAsync(h_out, d_r, out_copy_d * 8, cudaMemcpyDeviceToHost, st));
+    PNP_CUDA(cudaMemcpyAsync(h_flags + n, d_valid, n, cudaMemcpyDeviceToHost, st));
     PNP_CUDA(cudaStreamSynchronize(st));
+    memcpy(r, h_out, n * 16);
+    if (Jp) memcpy(Jp, h_out + n * 2, n * 96);
+    if (chi2) memcpy(chi2, h_out + n * 14, n * 8);
+    memcpy(valid, h_flags + n, n);
+    const double* h28 = h_out + n * 15 + (size_t)nb * 28;
 #undef PNP_CUDA
     cleanup();
     if (H) {
@@ -1931,10 +1936,10 @@ extern "C" int vio360_triangulate(vio360_ctx* ctx, const float* bearing1, const 
     if (n == 0) return VIO360_OK;
     VIO_CUDA(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
-    DevBuf buf;
     const size_t nf = 3 * (size_t)n;
-    VIO_CUDA(ctx, buf.reserve(nf * 4 * 3 + (size_t)n));
-    float* d_b1 = buf.as<float>(); float* d_b2 = d_b1 + nf; float* d_pts = d_b2 + nf;
+    void* scratch_p = nullptr;
+    VIO_CUDA(ctx, vio360_scratch(ctx, nf * 4 * 3 + (size_t)n, &scratch_p));
+    float* d_b1 = static_cast<float*>(scratch_p); float* d_b2 = d_b1 + nf; float* d_pts = d_b2 + nf;
     unsigned char* d_valid = reinterpret_cast<unsigned char*>(d_pts + nf);
     VIO_CUDA(ctx, cudaMemcpyAsync(d_b1, bearing1, nf * 4, cudaMemcpyHostToDevice, st));
     VIO_CUDA(ctx, cudaMemcpyAsync(d_b2, bearing2, nf * 4, cudaMemcpyHostToDevice, st));
@@ -1945,11 +1950,10 @@ extern "C" int vio360_triangulate(vio360_ctx* ctx, const float* bearing1, const 
     }
     ctx->launches++;
     cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) { buf.release(); return vio360_fail(ctx, VIO360_ERR_CUDA, "k_triangulate: %s", cudaGetErrorString(e)); }
+    if (e != cudaSuccess) return vio360_fail(ctx, VIO360_ERR_CUDA, "k_triangulate: %s", cudaGetErrorString(e));
     cudaMemcpyAsync(points, d_pts, nf * 4, cudaMemcpyDeviceToHost, st);
     cudaMemcpyAsync(valid, d_valid, (size_t)n, cudaMemcpyDeviceToHost, st);
     e = cudaStreamSynchronize(st);
-    buf.release();
     if (e != cudaSuccess) return vio360_fail(ctx, VIO360_ERR_CUDA, "triangulate: %s", cudaGetErrorString(e));
     return VIO360_OK;
 }

@@ -29,6 +29,10 @@ struct vio360_ctx {
     // small pinned + device scratch used to ship descriptor tables
     void* pinned = nullptr;
     size_t pinned_bytes = 0;
+    // device scratch of the stateless entry points (vio360_pnp_evaluate, vio360_triangulate): grown on demand, kept
+    // between calls (those calls end with a stream synchronise, so it is never in use when the next one starts)
+    void* dscratch = nullptr;
+    size_t dscratch_bytes = 0;
     // optional per-kernel CUDA-event timing (bench.py's roofline numbers)
     bool timing = false;
     bool debug_sync = false;     // VIO360_DEBUG_SYNC=1: synchronise after every launch so a fault names its kernel
@@ -116,6 +120,31 @@ struct PinBuf {
 };
 
 void vio360_fe_release(vio360_ctx* ctx);  // fe.cu
+
+inline cudaError_t vio360_pinned(vio360_ctx* ctx, size_t bytes, void** out) {   // the context's pinned staging buffer, grown on demand
+    if (bytes > ctx->pinned_bytes) {
+        if (ctx->pinned) cudaFreeHost(ctx->pinned);
+        ctx->pinned = nullptr; ctx->pinned_bytes = 0;
+        const size_t want = (bytes + (1u << 16) - 1) & ~(size_t)((1u << 16) - 1);
+        cudaError_t e = cudaMallocHost(&ctx->pinned, want);
+        if (e != cudaSuccess) return e;
+        ctx->pinned_bytes = want;
+    }
+    *out = ctx->pinned;
+    return cudaSuccess;
+}
+inline cudaError_t vio360_scratch(vio360_ctx* ctx, size_t bytes, void** out) {
+    if (bytes > ctx->dscratch_bytes) {
+        if (ctx->dscratch) cudaFree(ctx->dscratch);
+        ctx->dscratch = nullptr; ctx->dscratch_bytes = 0;
+        const size_t want = (bytes + (1u << 20) - 1) & ~(size_t)((1u << 20) - 1);
+        cudaError_t e = cudaMalloc(&ctx->dscratch, want);
+        if (e != cudaSuccess) return e;
+        ctx->dscratch_bytes = want;
+    }
+    *out = ctx->dscratch;
+    return cudaSuccess;
+}
 
 // Launch with programmatic dependent launch allowed: the kernel may be scheduled while the previous kernel of the
 // stream is still draining (once all of that kernel's CTAs have executed griddepcontrol.launch_dependents or exited);

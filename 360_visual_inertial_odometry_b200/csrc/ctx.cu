@@ -50,6 +50,7 @@ extern "C" void vio360_destroy(vio360_ctx* ctx) {
     for (auto& t : ctx->timed) { cudaEventDestroy(t.e0); cudaEventDestroy(t.e1); }
     for (auto e : ctx->event_pool) cudaEventDestroy(e);
     if (ctx->pinned) cudaFreeHost(ctx->pinned);
+    if (ctx->dscratch) cudaFree(ctx->dscratch);
     for (auto& r : ctx->registered) cudaHostUnregister(reinterpret_cast<void*>(r.first));   // ranges the caller forgot
     cudaStreamDestroy(ctx->stream);
     delete ctx;

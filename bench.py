@@ -357,6 +357,7 @@ def run_ours(args):
     if not args.skip_detect:
         line["detect"] = bench_detect(ctx, b, torch, ring, B, world, device, barrier, stream)
         line["ransac"] = bench_ransac(ctx, syn)
+        line["pnp_triangulate"] = bench_pnp_triangulate(ctx, syn, args, rank)
         line["sequence_chain"] = bench_sequence(ctx, b, syn, torch, device, barrier, args, rank)
     # ---- BA factor evaluation
     if not args.skip_ba:
@@ -576,6 +577,50 @@ def bench_ransac(ctx, syn):
     return {"metric": "rotation RANSAC frames/s (1000 points, 1000 hypotheses)", "value": nb / dt, "unit": "frames/s",
             "frames_per_call": nb, "ms_per_call": dt * 1e3, "kernel_ms_per_launch": kern,
             "inliers_first_frame": int(res[0][0])}
+
+
+def bench_pnp_triangulate(ctx, syn, args, rank):
+    """SURVEY 8-F rank 4: batched PnP evaluation (PnPFactor::Evaluate + compute_chi_square for all matches of a frame,
+    Optimizer.cpp:180-267) and batched DLT triangulation (Estimator::TriangulateSinglePoint, Estimator.cpp:1082-1139),
+    through the host-memory C ABI (copies inside the timed region), beside the C restatement on one host core."""
+    out = {}
+    win = syn.make_ba_window(K=3, M=1000, degree=3, seed=77, mid_iteration=True)
+    k = 1
+    sel = np.where(win["pose_idx"] == k)[0]
+    obs = np.stack([win["obs_u"][sel], win["obs_v"][sel]], axis=1)
+    pts = win["points"][win["point_idx"][sel]].copy()
+    call = lambda: ctx.pnp_evaluate(obs, pts, win["Twb_init"][k], win["Tcb"], win["cols"], win["rows"], win["info"], 1.0, win["pose_delta"][k])
+    for _ in range(3):
+        call()
+    reps = 50
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        call()
+    dt = (time.perf_counter() - t0) / reps
+    out["pnp"] = {"metric": "PnP factor evaluations/s (residual, Jacobian, Huber, H = J'J, b = J'r, chi2 of one frame's matches)",
+                  "value": len(sel) / dt, "unit": "obs/s", "observations_per_call": int(len(sel)), "ms_per_call": dt * 1e3}
+    b1, b2, T1, T2, _ = syn.make_triangulation_pairs(20000, seed=6)
+    for _ in range(3):
+        ctx.triangulate(b1, b2, T1, T2)
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        ctx.triangulate(b1, b2, T1, T2)
+    dtt = (time.perf_counter() - t0) / reps
+    out["triangulate"] = {"metric": "DLT triangulations/s", "value": len(b1) / dtt, "unit": "points/s", "points_per_call": int(len(b1)), "ms_per_call": dtt * 1e3}
+    if rank == 0 and not args.skip_cpu:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import ba_oracle
+        n = min(len(sel), 300)
+        t0 = time.perf_counter()
+        for i in range(n):
+            f = ba_oracle.make_factor(obs[i], win["cols"], win["rows"], win["Tcb"], win["Twb_init"][k], win["info"], world_point=tuple(pts[i]))
+            ba_oracle.pnp_evaluate(f, win["pose_delta"][k]); ba_oracle.pnp_chi2(f, win["pose_delta"][k])
+        out["pnp"]["cpu_baseline"] = {"value": n / (time.perf_counter() - t0), "unit": "obs/s", "cores": 1, "kind": "port",
+                                      "sample": "%d factors, one call per factor as Ceres does (C restatement behind ctypes; the per-call overhead of the binding is included)" % n}
+        t0 = time.perf_counter()
+        ba_oracle.triangulate(b1[:5000], b2[:5000], T1, T2)
+        out["triangulate"]["cpu_baseline"] = {"value": 5000 / (time.perf_counter() - t0), "unit": "points/s", "cores": 1, "kind": "port", "sample": "5000 pairs"}
+    return out
 
 
 def bench_detect(ctx, b, torch, ring, B, world, device, barrier, stream):
