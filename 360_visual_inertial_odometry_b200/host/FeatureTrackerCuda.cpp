@@ -148,13 +148,13 @@ int FeatureTrackerCuda::TrackOpticalFlow(const cv::Mat& prev_image, const cv::Ma
     curr_points.resize((size_t)n);
     status.resize((size_t)n);
     m_keep.resize((size_t)n);
-    std::vector<float> error((size_t)n);   // the reference requests err and discards it (:237)
     vio360_track_job job;
     job.prev = prev_image.data; job.prev_pitch = (size_t)prev_image.step; job.prev_key = m_prev_key;
     job.cur = curr_image.data; job.cur_pitch = (size_t)curr_image.step; job.cur_key = m_curr_key;
     job.prev_xy = reinterpret_cast<const float*>(prev_points.data()); job.n = n;
     job.cur_xy = reinterpret_cast<float*>(curr_points.data()); job.status = status.data();
-    job.err = error.data(); job.keep = m_keep.data();
+    job.err = nullptr;      // the reference requests err and discards it (:237): not computed (status is unaffected)
+    job.keep = m_keep.data();
     check(vio360_fe_track_batch(m_ctx, &job, 1, VIO360_MEM_HOST), "vio360_fe_track_batch");
     int num_tracked = 0;
     for (size_t i = 0; i < status.size(); ++i)
