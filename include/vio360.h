@@ -241,7 +241,10 @@ typedef struct {
                                                                     visualization_clustered_std_ratio (FeatureTracker.cpp:407-423) */
     int ransac_iterations; float ransac_threshold_deg;           /* FeatureTracker.cpp:36-37 (1000, 2.0)                  */
 } vio360_seq_config;
-/* vio360_fe_configure must have been called; a later vio360_fe_configure invalidates the sequence. */
+/* vio360_fe_configure must have been called (max_points >= 2 * max_features); a later vio360_fe_configure invalidates
+ * the sequence.  Limit: the list kernels keep one frame's list (positions, cells, member lists) in shared memory,
+ * 21 bytes per entry of the 2 * max_features capacity + 4 bytes per grid cell <= 200 KB, i.e. about 4700 features
+ * at 20 x 10 cells (the reference uses 500 .. 1000); larger values are rejected here.                          */
 int vio360_seq_create(vio360_ctx* ctx, const vio360_seq_config* cfg, vio360_seq** out);
 void vio360_seq_destroy(vio360_seq* seq);
 int vio360_seq_reset(vio360_seq* seq);          /* forget the features and the previous frame; ids restart at 0 */
