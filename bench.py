@@ -914,7 +914,7 @@ def cpu_baseline_tracking(ring, pts_h, torch, gpu_out=None, max_pairs=24, budget
             ntr += int(ok.sum())
             if ok.any():
                 maxd = max(maxd, float(np.abs(gxy[s] - cxy)[ok].max()))
-                maxe = max(maxe, float(np.abs(gerr[s] - cerr)[ok].max()))
+                maxe = max(maxe, float(np.abs(gerr[s][ok] - cerr[ok]).max()))   # err of untracked points is undefined on both sides
                 moved.append(float(np.median(np.linalg.norm(cxy - pts_h[s], axis=1)[ok])))
         parity = {"lk_vs_cv2": {"pairs": n, "points": int(n * pts_h.shape[1]), "frames": "consecutive rendered frames t=0,1 at %dx%d (the timed inputs)" % (W, H),
                                 "status_mismatches": mism, "status_equal": mism == 0, "tracked_both": ntr,
