@@ -658,9 +658,21 @@ static DiscTable disc_table(int radius) {
 
 static void launch_min_eig(vio360_ctx* ctx, const DetectJobDev* dj, const DetectParams& P, int n_jobs, bool any_mask, cudaStream_t on = nullptr) {
     const int nwx = (P.W + kEigWarpCols - 1) / kEigWarpCols;
-    const dim3 grid((nwx + kEigWarps - 1) / kEigWarps, n_jobs);
     const cudaStream_t st = on ? on : ctx->stream;
     KernelTimer kt_(ctx, "k_min_eig");
+    // few frames: the march is latency bound (rows x one row's latency) and one column per lane halves that latency;
+    // a batch that fills the 14 warps per SM of the 2-column form twice over issues fewer instructions with it
+    const char* env_narrow = getenv("VIO360_EIG_NARROW");   // read per call: the tests switch it
+    const int force_narrow = env_narrow ? atoi(env_narrow) : -1;
+    const bool narrow = force_narrow >= 0 ? force_narrow != 0 : (long long)nwx * n_jobs < (long long)ctx->num_sms * 14;
+    if (narrow) {
+        const int nw1 = (P.W + kEigWarpCols1 - 1) / kEigWarpCols1;
+        const dim3 grid1((nw1 + kEigWarps - 1) / kEigWarps, n_jobs);
+        if (any_mask) k_min_eig_narrow<true><<<grid1, kEigWarps * 32, 0, st>>>(dj, P, nw1);
+        else k_min_eig_narrow<false><<<grid1, kEigWarps * 32, 0, st>>>(dj, P, nw1);
+        return;
+    }
+    const dim3 grid((nwx + kEigWarps - 1) / kEigWarps, n_jobs);
     if (any_mask) k_min_eig<true><<<grid, kEigWarps * 32, 0, st>>>(dj, P, nwx);
     else k_min_eig<false><<<grid, kEigWarps * 32, 0, st>>>(dj, P, nwx);
 }

@@ -172,6 +172,19 @@ def test_detect_vs_oracle(ctx, synthetic, size, seed):
     assert len(ctx.fe_detect(f0, np.zeros_like(mask), 1000)) == 0
 
 
+@pytest.mark.parametrize("narrow", ["0", "1"])
+def test_min_eigen_strip_seams(ctx, monkeypatch, narrow):
+    """Every position of the right image border inside a strip of k_min_eig (60 columns per warp) and of
+    k_min_eig_narrow (28): a last strip of one column puts the reflected column into the halo lane of the strip before."""
+    monkeypatch.setenv("VIO360_EIG_NARROW", narrow)
+    rng = np.random.default_rng(17)
+    H = 37
+    for W in list(range(56, 64)) + list(range(84, 92)) + list(range(118, 124)) + [180, 181, 182, 481]:
+        img = rng.integers(0, 256, (H, W), dtype=np.uint8)
+        ctx.fe_configure(W, H, max_points=8, max_batch=1)
+        assert np.array_equal(ctx.fe_min_eigen_val(img), fo.min_eigen_val(img)), W
+
+
 def test_detect_batch_and_grid_variants(ctx, synthetic, monkeypatch):
     """One batched call over different images (single merged sort), odd image size (byte loads /
     scalar stores), a small minDistance (cell grid in global memory), minDistance < 1 (no grid),
