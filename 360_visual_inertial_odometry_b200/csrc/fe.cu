@@ -59,7 +59,7 @@ struct vio360_fe_state {
     Stage* cur_stage = nullptr;
     int cur_stage_i = 0;
     // detection pools
-    DevBuf d_djobs, d_eig, d_mask, d_small, d_cand, d_grid, d_corners;
+    DevBuf d_djobs, d_eig, d_mask, d_small, d_cand, d_grid, d_corners, d_edge;
     PinBuf h_djobs, h_dout;
     DevBuf d_occ;
     PinBuf h_occ;
@@ -84,7 +84,7 @@ void vio360_fe_release(vio360_ctx* ctx) {
     s->d_seq.release(); s->h_seq.release();
     DevBuf* db[] = {&s->d_jobs, &s->d_pyrjobs, &s->d_pts_in, &s->d_pts_out, &s->d_status, &s->d_err, &s->d_keep,
                     &s->d_djobs, &s->d_eig, &s->d_mask, &s->d_small, &s->d_cand, &s->d_grid,
-                    &s->d_corners, &s->d_ransac, &s->d_occ, &s->d_lk_queue};
+                    &s->d_corners, &s->d_ransac, &s->d_occ, &s->d_lk_queue, &s->d_edge};
     for (DevBuf* b : db) b->release();
     PinBuf* pb[] = {&s->h_pts_in, &s->h_out, &s->h_djobs, &s->h_dout, &s->h_ransac, &s->h_occ};
     for (PinBuf* b : pb) b->release();
@@ -682,15 +682,41 @@ static void launch_min_eig(vio360_ctx* ctx, const DetectJobDev* dj, const Detect
 static int launch_detect_group(vio360_ctx* ctx, const DetectJobDev* dj, const DetectParams& P, int n_jobs, bool any_mask, int max_corners,
                                double quality, double min_dist, bool smem_grid, size_t grid_bytes, float* pool_xy, cudaStream_t st) {
     vio360_fe_state* s = ctx->fe;
+    // Fused form (VIO360_DET_FUSED=1): no response map.  The march emits the candidates of its strip's interior columns
+    // itself, k_seam_candidates those of the strip seams, k_sort_select applies the final threshold.  Bit exact like the
+    // default, a seventh of its DRAM traffic and no 4*W*H buffer per image -- and 13 % slower on 64 frames of 3840x1920
+    // (4.09 against 3.61 ms): the march is bound by instruction issue and the test costs it 58 instructions per strip
+    // row (2.21 -> 3.36 ms), more than the HBM-bound k_candidates4 it replaces (0.76 -> 0.16 ms).  Kept as an option
+    // for callers that are short of memory; default off.
+    const int nwx60 = (P.W + kEigWarpCols - 1) / kEigWarpCols;
+    const char* env_fused = getenv("VIO360_DET_FUSED");
+    const bool fused = env_fused && atoi(env_fused) != 0;
+    if (fused) {
+        const size_t edge_elems = (size_t)n_jobs * nwx60 * P.H;
+        if (s->d_edge.reserve(edge_elems * sizeof(float4)) != cudaSuccess) return vio360_fail(ctx, VIO360_ERR_CUDA, "fe_detect: seam buffer allocation failed");
+        float4* edge = s->d_edge.as<float4>() + (size_t)(dj - s->d_djobs.as<DetectJobDev>()) * nwx60 * P.H;   // a group's own part
+        const dim3 grid((nwx60 + kEigWarps - 1) / kEigWarps, n_jobs);
+        { KernelTimer kt_(ctx, "k_min_eig");
+        if (any_mask) k_min_eig_cand<true><<<grid, kEigWarps * 32, 0, st>>>(dj, P, nwx60, quality, edge);
+        else k_min_eig_cand<false><<<grid, kEigWarps * 32, 0, st>>>(dj, P, nwx60, quality, edge);
+        }
+        VIO_LAUNCH_CHECK(ctx);
+        if (nwx60 > 1) {
+            KernelTimer kt_(ctx, "k_candidates");
+            k_seam_candidates<<<dim3((P.H + 127) / 128, nwx60 - 1, n_jobs), 128, 0, st>>>(dj, P, nwx60, quality, edge);
+        }
+        VIO_LAUNCH_CHECK(ctx);
+    } else {
     launch_min_eig(ctx, dj, P, n_jobs, any_mask, st);
     VIO_LAUNCH_CHECK(ctx);
     { KernelTimer kt_(ctx, "k_candidates");
     if ((s->W & 3) == 0)
-        k_candidates4<<<dim3((s->W / 4 + kCand4Threads - 1) / kCand4Threads, (s->H - 2 + kCandTY - 1) / kCandTY, n_jobs), kCand4Threads, 0, st>>>(dj, P, quality);
+        k_candidates4<<<dim3((s->W / 4 + kCand4Threads - 1) / kCand4Threads, (s->H - 2 + kCand4TY - 1) / kCand4TY, n_jobs), kCand4Threads, 0, st>>>(dj, P, quality);
     else
         k_candidates<<<dim3((s->W - 2 + kCandTX - 1) / kCandTX, (s->H - 2 + kCandTY - 1) / kCandTY, n_jobs), kCandTX, 0, st>>>(dj, P, quality);
     }
     VIO_LAUNCH_CHECK(ctx);
+    }
     // shared memory: the cell grid (when it fits) + one tranche of keys, a power of two
     const size_t budget = (size_t)200 * 1024 - (smem_grid ? grid_bytes : 0);
     int tranche = kSelMaxTranche;
@@ -699,10 +725,10 @@ static int launch_detect_group(vio360_ctx* ctx, const DetectJobDev* dj, const De
     { KernelTimer kt_(ctx, "k_sort_select");
     if (smem_grid) {
         VIO_CUDA(ctx, cudaFuncSetAttribute(k_sort_select<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-        k_sort_select<true><<<n_jobs, kSelThreads, smem, st>>>(dj, P, max_corners, min_dist, tranche, pool_xy);
+        k_sort_select<true><<<n_jobs, kSelThreads, smem, st>>>(dj, P, max_corners, min_dist, tranche, pool_xy, fused ? quality : 0.0);
     } else {
         VIO_CUDA(ctx, cudaFuncSetAttribute(k_sort_select<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-        k_sort_select<false><<<n_jobs, kSelThreads, smem, st>>>(dj, P, max_corners, min_dist, tranche, pool_xy);
+        k_sort_select<false><<<n_jobs, kSelThreads, smem, st>>>(dj, P, max_corners, min_dist, tranche, pool_xy, fused ? quality : 0.0);
     }
     }
     VIO_LAUNCH_CHECK(ctx);

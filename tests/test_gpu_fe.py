@@ -205,6 +205,49 @@ def test_detect_batch_and_grid_variants(ctx, synthetic, monkeypatch):
             assert len(ref) > 20
 
 
+@pytest.mark.parametrize("size", [(963, 481), (1920, 960), (61, 45)])
+def test_detect_fused_variant(ctx, synthetic, monkeypatch, size):
+    """VIO360_DET_FUSED=1: no response map; the march applies the 3x3 test to its strip's interior columns against a
+    threshold that is still rising, k_seam_candidates judges the strip seams, k_sort_select cuts at the final
+    threshold.  Same corners as the default path: masks, no corner limit (every candidate comes back), a candidate
+    segment that starts too small, a width of 1 mod 60."""
+    W, H = size
+    monkeypatch.setenv("VIO360_DET_FUSED", "1")
+    monkeypatch.setenv("VIO360_DET_CAND", "256")
+    frames = [synthetic.render_erp_frame(W, H, t, seed=51 + t, n_waves=40, sigma_omega=45.0 * max(1.0, W / 960)) for t in range(2)]
+    mask = fo.base_mask(W, H)
+    occ = mask.copy()
+    occ[:, W // 3:W // 2] = 0
+    ctx.fe_configure(W, H, max_points=8, max_batch=2)
+    for md, mc in ((30.0, 1000), (3.0, 0), (12.0, 40)):
+        got = ctx.fe_detect_batch(frames, [None, occ], mc, min_dist=md)
+        for b in range(2):
+            ref = fo.good_features(frames[b], occ if b == 1 else mask, mc, min_dist=md)
+            assert np.array_equal(got[b], ref), (md, mc, b)
+    assert len(ctx.fe_detect(frames[0], np.zeros_like(mask), 1000)) == 0
+
+
+@pytest.mark.parametrize("fused", ["0", "1"])
+def test_detect_dense_candidates(ctx, monkeypatch, fused):
+    """A 3 x 3 periodic texture: every 3x3 box sees each phase once, so the response is one constant plateau and EVERY
+    pixel of that half is a candidate (ties broken by raster index, as cv2's pointer comparison does) -- more than a
+    block of k_candidates4 compacts in shared memory (1024 keys per 512 x 16 pixels; the rest is appended one by one),
+    more than a warp of the fused march buffers between two flushes, and more than the first candidate segment holds."""
+    monkeypatch.setenv("VIO360_DET_FUSED", fused)
+    monkeypatch.setenv("VIO360_DET_CAND", "4096")
+    W, H = 1024, 96
+    rng = np.random.default_rng(77)
+    tile = rng.integers(0, 256, (3, 3), dtype=np.uint8)
+    img = np.tile(tile, (H // 3, W // 3 + 1))[:, :W].copy()
+    img[:, W // 2:] = np.maximum(img[:, W // 2:] // 4, rng.integers(0, 60, (H, W // 2), dtype=np.uint8))   # half plateau, half noise
+    ctx.fe_configure(W, H, max_points=8, max_batch=1)
+    for md, mc in ((1.0, 0), (5.0, 3000)):
+        ref = fo.good_features(img, fo.base_mask(W, H), mc, min_dist=md)
+        got = ctx.fe_detect(img, None, mc, min_dist=md)
+        assert np.array_equal(got, ref), (md, mc)
+        assert len(ref) > 2000
+
+
 def test_detect_with_occupied_features(ctx, synthetic):
     """the occupancy mask of CreateFeatureMask (FeatureTracker.cpp:386-402) built on
     the device from the feature positions equals detection with the rasterised cv::circle mask."""
