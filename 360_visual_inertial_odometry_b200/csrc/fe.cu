@@ -684,10 +684,10 @@ static int launch_detect_group(vio360_ctx* ctx, const DetectJobDev* dj, const De
     vio360_fe_state* s = ctx->fe;
     // Fused form (VIO360_DET_FUSED=1): no response map.  The march emits the candidates of its strip's interior columns
     // itself, k_seam_candidates those of the strip seams, k_sort_select applies the final threshold.  Bit exact like the
-    // default, a seventh of its DRAM traffic and no 4*W*H buffer per image -- and 13 % slower on 64 frames of 3840x1920
-    // (4.09 against 3.61 ms): the march is bound by instruction issue and the test costs it 58 instructions per strip
-    // row (2.21 -> 3.36 ms), more than the HBM-bound k_candidates4 it replaces (0.76 -> 0.16 ms).  Kept as an option
-    // for callers that are short of memory; default off.
+    // default, a seventh of its DRAM traffic and no 4*W*H buffer per image -- and 10 % slower on 64 frames of 3840x1920
+    // (3.34 against 3.02 ms): the march is bound by instruction issue and the test costs it 58 instructions per strip
+    // row (1.94 -> 2.68 ms), more than the k_candidates4 it replaces (0.54 -> 0.16 ms).  Kept as an option for callers
+    // that are short of memory; default off.
     const int nwx60 = (P.W + kEigWarpCols - 1) / kEigWarpCols;
     const char* env_fused = getenv("VIO360_DET_FUSED");
     const bool fused = env_fused && atoi(env_fused) != 0;
