@@ -67,6 +67,7 @@ struct vio360_fe_state {
     DevBuf d_ransac;
     PinBuf h_ransac;
     int det_batch_cap = 0, max_cand = 1 << 17;   // initial candidate capacity per image (grown on demand)
+    int eig_jobs = 0;                             // images the response-map pool holds (none while only the fused detector runs)
     size_t cand_cap = 0;
     int lk_mb = 2;               // occupancy variant of k_lk_track (tuning knob: VIO360_LK_MB)
     // host-space batches: frames are uploaded on a second stream in groups of h2d_group jobs, and a group's
@@ -604,11 +605,19 @@ static int reserve_candidates(vio360_ctx* ctx, size_t per_image, int n_jobs) {
     return VIO360_OK;
 }
 
-static int ensure_detect_pools(vio360_ctx* ctx, int n_jobs, int max_corners) {
+static bool detect_fused_requested() {
+    const char* e = getenv("VIO360_DET_FUSED");   // read per call: the tests switch it
+    return e && atoi(e) != 0;
+}
+
+static int ensure_detect_pools(vio360_ctx* ctx, int n_jobs, int max_corners, bool need_map = true) {
     vio360_fe_state* s = ctx->fe;
     const size_t WH = (size_t)s->W * s->H;
-    if (n_jobs > s->det_batch_cap) {
+    if (need_map && n_jobs > s->eig_jobs) {   // 4*W*H per image: not taken by the fused detector
         VIO_CUDA(ctx, s->d_eig.reserve(WH * 4 * n_jobs));
+        s->eig_jobs = n_jobs;
+    }
+    if (n_jobs > s->det_batch_cap) {
         VIO_CUDA(ctx, s->d_small.reserve(16 * (size_t)(n_jobs + 1)));
         VIO_CUDA(ctx, s->d_djobs.reserve(sizeof(DetectJobDev) * (size_t)n_jobs));
         VIO_CUDA(ctx, s->h_djobs.reserve(sizeof(DetectJobDev) * (size_t)n_jobs));
@@ -689,8 +698,7 @@ static int launch_detect_group(vio360_ctx* ctx, const DetectJobDev* dj, const De
     // row (1.94 -> 2.68 ms), more than the k_candidates4 it replaces (0.54 -> 0.16 ms).  Kept as an option for callers
     // that are short of memory; default off.
     const int nwx60 = (P.W + kEigWarpCols - 1) / kEigWarpCols;
-    const char* env_fused = getenv("VIO360_DET_FUSED");
-    const bool fused = env_fused && atoi(env_fused) != 0;
+    const bool fused = detect_fused_requested();
     if (fused) {
         const size_t edge_elems = (size_t)n_jobs * nwx60 * P.H;
         if (s->d_edge.reserve(edge_elems * sizeof(float4)) != cudaSuccess) return vio360_fail(ctx, VIO360_ERR_CUDA, "fe_detect: seam buffer allocation failed");
@@ -774,7 +782,7 @@ extern "C" int vio360_fe_detect_batch(vio360_ctx* ctx, const vio360_detect_job* 
     if (max_corners > 0 && (size_t)max_corners > WH) max_corners = (int)WH;
     VIO_CUDA(ctx, cudaSetDevice(ctx->device));
     VIO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    int rc = ensure_detect_pools(ctx, n_jobs, max_corners);
+    int rc = ensure_detect_pools(ctx, n_jobs, max_corners, !detect_fused_requested());
     if (rc) return rc;
     DetectParams P = detect_params(s);
     cudaStream_t st = ctx->stream;
