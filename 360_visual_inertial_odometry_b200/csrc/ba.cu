@@ -1840,14 +1840,18 @@ extern "C" int vio360_ba_lm_solve(vio360_ba* ba, const vio360_lm_options* opt, d
                                                          ba->d_scale.as<double>(), first ? 1 : 0, od.jacobi_scaling, part_lin);
             }
             VIO_LAUNCH_CHECK(ctx);
-            k_lm_linearized_finish<<<1, kLmRedThreads, 0, st>>>(part_lin, nbl, d_state);
+            k_lm_linearized_finish<<<1, kLmRedThreads, 0, st>>>(part_lin, nbl, d_state, od.gradient_tolerance);
             VIO_LAUNCH_CHECK(ctx);
-            if ((rc = read_state())) return rc;
-            last = *h_state;
-            if (first) push_trace(last, last.x_cost);
-            first = false; relinearize = false;
-            if (last.gradient_max_norm <= od.gradient_tolerance) { termination = 1; break; }   // GradientToleranceReached (:674-692)
-            if (last.termination != 0) { termination = last.termination; break; }
+            relinearize = false;
+            if (first) {   // iteration 0: its trace row needs the gradient norm; later re-linearisations are not read back --
+                           // k_lm_linearized_finish makes the gradient test (:674-692) and a terminated state makes the
+                           // step below a no-op that the read after k_lm_decide reports
+                if ((rc = read_state())) return rc;
+                last = *h_state;
+                push_trace(last, last.x_cost);
+                first = false;
+                if (last.termination != 0) { termination = last.termination; break; }
+            }
         }
         // ---- ComputeTrustRegionStep: LM diagonal, fused build of the reduced system, Cholesky, back substitution
         { KernelTimer kt_(ctx, "k_lm_diagonal");
@@ -1883,6 +1887,7 @@ extern "C" int vio360_ba_lm_solve(vio360_ba* ba, const vio360_lm_options* opt, d
         VIO_LAUNCH_CHECK(ctx);
         if ((rc = read_state())) return rc;
         last = *h_state;
+        if (last.termination == 1) { termination = 1; break; }   // set by the re-linearisation of the previous step: no step was taken
         push_trace(last, last.step_successful ? last.x_cost : last.candidate_cost);
         if (last.step_successful) {   // x = candidate_x (HandleSuccessfulStep): swap the current and candidate buffers
             std::swap(ba->d_pose_delta, ba->d_cand_pose_delta); std::swap(ba->d_points, ba->d_cand_points); std::swap(ba->d_posebuf, ba->d_cand_posebuf);

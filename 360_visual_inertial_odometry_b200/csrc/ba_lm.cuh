@@ -89,12 +89,18 @@ __global__ void __launch_bounds__(kLmRedThreads) k_lm_linearized(int K, int M, c
     const double xs = lm_block_sum(x2);
     if (threadIdx.x == 0) { partials[blockIdx.x] = gm; partials[gridDim.x + blockIdx.x] = xs; }
 }
-__global__ void __launch_bounds__(kLmRedThreads) k_lm_linearized_finish(const double* __restrict__ partials, int nparts, LmState* __restrict__ st) {
+// The gradient test of trust_region_minimizer.cc:674-692 is made here, so that the host does not have to read the state
+// back between the re-linearisation and the next step: a state that has terminated makes k_lm_decide a no-op.
+__global__ void __launch_bounds__(kLmRedThreads) k_lm_linearized_finish(const double* __restrict__ partials, int nparts, LmState* __restrict__ st,
+                                                                        double gradient_tolerance) {
     double gmax = 0.0, x2 = 0.0;
     for (int i = threadIdx.x; i < nparts; i += blockDim.x) { gmax = fmax(gmax, partials[i]); x2 += partials[nparts + i]; }
     const double gm = lm_block_max(gmax);
     const double xs = lm_block_sum(x2);
-    if (threadIdx.x == 0) { st->gradient_max_norm = gm; st->x_norm = sqrt(xs); }
+    if (threadIdx.x == 0) {
+        st->gradient_max_norm = gm; st->x_norm = sqrt(xs);
+        if (st->termination == 0 && gm <= gradient_tolerance) st->termination = 1;   // GradientToleranceReached
+    }
 }
 
 // LevenbergMarquardtStrategy::ComputeStep (:78-89) on the Jacobi-scaled Jacobian, expressed for the unscaled
@@ -218,6 +224,7 @@ __global__ void __launch_bounds__(kLmRedThreads) k_lm_decide(const double* __res
     const double step2 = lm_block_sum(a), model = lm_block_sum(b), cand = lm_block_sum(c);
     if (threadIdx.x != 0) return;
     LmState s = *st;
+    if (s.termination != 0) { *host_copy = s; return; }   // the gradient test after the last re-linearisation ended the solve
     s.iteration += 1;
     s.step_norm = sqrt(step2); s.model_cost_change = model; s.candidate_cost = cand;
     s.step_valid = (chol_status[0] == 0) && (model > 0.0);        // LINEAR_SOLVER_FAILURE or model_cost_change <= 0

@@ -543,6 +543,39 @@ def test_lm_solve_vs_oracle(bindings, ctx, synthetic, K, M, degree, seed):
     ba.close()
 
 
+def test_lm_solve_gradient_tolerance(bindings, ctx, synthetic):
+    """GradientToleranceReached (trust_region_minimizer.cc:674-692).  The device loop makes this test in
+    k_lm_linearized_finish and does not read the state back after a re-linearisation: the step that follows is a no-op
+    and the read after k_lm_decide reports the termination.  Tolerances between the gradient norms of two consecutive
+    accepted steps, and one above the initial gradient (no iteration at all)."""
+    win = synthetic.make_ba_window(K=10, M=600, seed=11, mid_iteration=True)
+    W = ba_oracle.Window(win)
+    _, _, sm0, tr0 = W.lm_solve(win["pose_delta"], win["points"])
+    g = np.array(tr0)[:, 2]
+    assert sm0["iterations"] >= 3
+    ba = bindings.BAWindow(ctx, win)
+    picked = 0
+    for i in range(1, len(g) - 1):
+        if not (np.array(tr0)[i, 6] == 1 and g[i] < g[:i].min()):
+            continue
+        tol = 0.5 * (g[i] + g[:i].min())                       # first reached after iteration i
+        xp, xl, sm, tr = W.lm_solve(win["pose_delta"], win["points"], gradient_tolerance=tol)
+        gp, gl, gs, gt = ba.lm_solve(win["pose_delta"], win["points"], gradient_tolerance=tol)
+        assert sm["termination"] == 1 and sm["iterations"] == i
+        assert gs["termination"] == 1 and gs["iterations"] == i and len(gt) == len(tr)
+        assert np.array_equal(gt[:, 6], np.array(tr)[:, 6]) and abs(gs["final_cost"] - sm["final_cost"]) < 1e-9 * sm["final_cost"]
+        assert np.abs(gp - xp).max() < 1e-7 * max(np.abs(xp).max(), 1e-3) and np.abs(gl - xl).max() < 1e-7 * np.abs(xl).max()
+        picked += 1
+        if picked == 2:
+            break
+    assert picked >= 1
+    xp, xl, sm, tr = W.lm_solve(win["pose_delta"], win["points"], gradient_tolerance=2.0 * g[0])
+    gp, gl, gs, gt = ba.lm_solve(win["pose_delta"], win["points"], gradient_tolerance=2.0 * g[0])
+    assert sm["termination"] == gs["termination"] == 1 and gs["iterations"] == sm["iterations"] == 0 and len(gt) == len(tr) == 1
+    assert np.array_equal(gp, np.asarray(win["pose_delta"], np.float64).reshape(gp.shape))
+    ba.close()
+
+
 def test_lm_solve_rejected_steps(bindings, ctx, synthetic):
     """A start far from the optimum, no loss function and a huge initial radius: the 100-pixel clamp of
     BAFactor::Evaluate (Factors.cpp:424-441) makes the model over-predict, steps are REJECTED and the radius shrinks by
