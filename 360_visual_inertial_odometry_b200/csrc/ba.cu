@@ -60,7 +60,8 @@ struct vio360_ba {
     CamConst cam;
     DevBuf d_u, d_v, d_pose, d_point, d_orig, d_outlier, d_lm_ptr, d_pose_ptr, d_pose_order;
     DevBuf d_Twb, d_Tcb, d_posebuf, d_pose_delta, d_points, d_free_map, d_point_fixed, d_D;
-    DevBuf d_r, d_Jp, d_Jl, d_partials, d_packed, d_blocks, d_chi2, d_flag;
+    DevBuf d_r, d_Jp, d_Jl, d_partials, d_packed, d_blocks, d_chi2, d_flag, d_blk_part;
+    size_t blk_part_bytes = 0;
     PinBuf pin;
     bool use_D = false;
     bool eval_f32 = false;       // vio360_ba_set_eval_precision: per-observation math of the fused build / blocks in float
@@ -324,11 +325,18 @@ __global__ void __launch_bounds__(128) k_blocks_landmark(BaDev d, bool apply_los
 
 // K8b: one block per pose: Hpp (6x6), bp (6) by a segmented block reduction over the
 // pose's observations (no atomics, fixed summation order).
+// gridDim.y > 1: the pose's observation list is cut into gridDim.y slices, one CTA each (a 10-keyframe window is 10
+// poses of ~1900 observations: ten CTAs would leave the GPU empty); every CTA leaves its 27 sums in `part`, and the
+// CTA that arrives last at the pose's counter adds the slices in slice order (fixed order, no atomics on the sums)
+// and resets the counter for the next launch.
 template <typename PT>
 __global__ void __launch_bounds__(256) k_blocks_pose(BaDev d, bool apply_loss, bool skip_fixed_points_never,
-                                                     double* __restrict__ Hpp, double* __restrict__ bp) {
+                                                     double* __restrict__ Hpp, double* __restrict__ bp,
+                                                     double* __restrict__ part, unsigned int* __restrict__ arrived) {
     const int k = blockIdx.x;
-    const int lo = d.pose_ptr[k], hi = d.pose_ptr[k + 1];
+    const int nsl = gridDim.y, sl = blockIdx.y;
+    const int lo0 = d.pose_ptr[k], hi0 = d.pose_ptr[k + 1];
+    const int lo = lo0 + (int)((long long)(hi0 - lo0) * sl / nsl), hi = lo0 + (int)((long long)(hi0 - lo0) * (sl + 1) / nsl);
     double acc[27];
 #pragma unroll
     for (int j = 0; j < 27; ++j) acc[j] = 0.0;
@@ -365,6 +373,23 @@ __global__ void __launch_bounds__(256) k_blocks_pose(BaDev d, bool apply_loss, b
         sm[0][threadIdx.x] = s;
     }
     __syncthreads();
+    if (nsl > 1) {
+        __shared__ int s_last;
+        if (threadIdx.x < 27) part[((size_t)k * nsl + sl) * 27 + threadIdx.x] = sm[0][threadIdx.x];
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) s_last = atomicAdd(arrived + k, 1u) == (unsigned int)(nsl - 1);
+        __syncthreads();
+        if (!s_last) return;
+        __threadfence();
+        if (threadIdx.x < 27) {
+            double s = 0.0;
+            for (int j = 0; j < nsl; ++j) s += __ldcg(part + ((size_t)k * nsl + j) * 27 + threadIdx.x);
+            sm[0][threadIdx.x] = s;
+        }
+        if (threadIdx.x == 0) arrived[k] = 0u;
+        __syncthreads();
+    }
     if (threadIdx.x < 36 && Hpp) {
         const int a = threadIdx.x / 6, b = threadIdx.x % 6;
         const int aa = a < b ? a : b, bb = a < b ? b : a;
@@ -572,7 +597,7 @@ extern "C" void vio360_ba_destroy(vio360_ba* ba) {
                       &ba->d_batch_lm, &ba->d_wide, &ba->d_wide_inv,
                       &ba->d_chol, &ba->d_linv, &ba->d_x, &ba->d_dl, &ba->d_reachF, &ba->d_band,
                       &ba->d_cand_pose_delta, &ba->d_cand_points, &ba->d_cand_posebuf, &ba->d_step, &ba->d_colsq, &ba->d_scale,
-                      &ba->d_lm_state, &ba->d_lm_part};
+                      &ba->d_lm_state, &ba->d_lm_part, &ba->d_blk_part};
     for (DevBuf* b : bufs) b->release();
     peer_release(ba);
     ba->pin.release();
@@ -967,8 +992,17 @@ static int run_blocks(vio360_ba* ba, int apply_loss, bool want_hpl = true) {
     }
     VIO_LAUNCH_CHECK(ctx);
     { KernelTimer kt_(ctx, "k_blocks_pose");
-    if (ba->eval_f32) k_blocks_pose<float><<<(int)K, 256, 0, ctx->stream>>>(d, apply_loss != 0, false, Hpp, bp);
-    else k_blocks_pose<double><<<(int)K, 256, 0, ctx->stream>>>(d, apply_loss != 0, false, Hpp, bp);
+    const int slices = (int)std::min<size_t>(16, std::max<size_t>(1, (2 * (size_t)ctx->num_sms + K - 1) / K));
+    const size_t part_bytes = K * (size_t)slices * 27 * 8, need = part_bytes + K * 4;
+    if (slices > 1 && need != ba->blk_part_bytes) {   // layout [partial sums | counters]; the counters start at zero and reset themselves
+        VIO_CUDA(ctx, ba->d_blk_part.reserve(need));
+        VIO_CUDA(ctx, cudaMemsetAsync(ba->d_blk_part.p, 0, need, ctx->stream));
+        ba->blk_part_bytes = need;                    // (a window of another size moves the counters: cleared again)
+    }
+    double* part = slices > 1 ? ba->d_blk_part.as<double>() : nullptr;
+    unsigned int* arrived = slices > 1 ? reinterpret_cast<unsigned int*>(ba->d_blk_part.as<unsigned char>() + part_bytes) : nullptr;
+    if (ba->eval_f32) k_blocks_pose<float><<<dim3((unsigned)K, slices), 256, 0, ctx->stream>>>(d, apply_loss != 0, false, Hpp, bp, part, arrived);
+    else k_blocks_pose<double><<<dim3((unsigned)K, slices), 256, 0, ctx->stream>>>(d, apply_loss != 0, false, Hpp, bp, part, arrived);
     }
     VIO_LAUNCH_CHECK(ctx);
     return VIO360_OK;
