@@ -876,7 +876,7 @@ extern "C" int vio360_fe_detect_batch(vio360_ctx* ctx, const vio360_detect_job* 
         if (any_occ && !discs_drawn) {
             const DiscTable T = disc_table(occ_radius);
             { KernelTimer kt_(ctx, "k_occupancy_discs");
-            k_occupancy_discs<<<dim3(max_occ, n_jobs), 2 * kMaxDiscRadius + 1, 0, st>>>(dj, s->d_occ.as<const float*>(), reinterpret_cast<const int*>(s->d_occ.as<const float*>() + n_jobs), s->W, s->H, T);
+            k_occupancy_discs<<<dim3((max_occ + kDiscWarps - 1) / kDiscWarps, n_jobs), kDiscWarps * 32, 0, st>>>(dj, s->d_occ.as<const float*>(), reinterpret_cast<const int*>(s->d_occ.as<const float*>() + n_jobs), s->W, s->H, T);
             }
             VIO_LAUNCH_CHECK(ctx);
             discs_drawn = true;
