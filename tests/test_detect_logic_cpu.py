@@ -87,3 +87,19 @@ def test_pruning_covered_candidates_keeps_the_greedy_result(seed, min_dist, max_
     for every in (1, 7, 64, 512):
         assert _greedy(pts, min_dist, max_corners, prune_every=every) == ref
     assert len(ref) > 10
+
+
+def test_integer_widening_of_squares_is_exact():
+    """widen_sq (fe_detect.cuh): float -> double on the integer pipe for non-negative NORMAL floats and zero --
+    hi = (bits >> 3) + 0x38000000, lo = bits << 29.  The march feeds it squares of Sobel gradients scaled by
+    float(1/3060): zero or >= 2^-70, never subnormal."""
+    rng = np.random.default_rng(5)
+    f = np.concatenate([
+        np.zeros(4, np.float32),
+        np.float32(2.0) ** rng.integers(-70, 20, 20000).astype(np.float32) * (1 + rng.random(20000).astype(np.float32)),
+        np.array([np.finfo(np.float32).tiny, 1.0, 3060.0 ** -2, np.finfo(np.float32).max], np.float32)])
+    b = f.view(np.uint32).astype(np.uint64)
+    hi = np.where(b != 0, (b >> np.uint64(3)) + np.uint64(0x38000000), np.uint64(0))
+    lo = (b << np.uint64(29)) & np.uint64(0xffffffff)
+    d = ((hi << np.uint64(32)) | lo).view(np.float64)
+    assert np.array_equal(d, f.astype(np.float64))
